@@ -1,0 +1,81 @@
+"""ctypes binding of libgp_b200.so (C ABI declared in include/gp_b200.h).
+
+There is NO fallback: if the shared library is missing or a call fails, an exception is raised.
+The library is built in-tree by ``python -m gaussianprediction_b200.build`` (or ``__graft_entry__.build()``).
+"""
+import ctypes
+import os
+from ctypes import POINTER, c_char_p, c_float, c_int, c_longlong, c_size_t, c_void_p
+
+PKG_DIR = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(PKG_DIR, "libgp_b200.so")
+
+
+class GpError(RuntimeError):
+    pass
+
+
+class RasterCfg(ctypes.Structure):
+    """Mirror of ``gp_raster_cfg``."""
+    _fields_ = [
+        ("P", c_int), ("width", c_int), ("height", c_int), ("sh_degree", c_int), ("sh_coeffs", c_int),
+        ("tanfovx", c_float), ("tanfovy", c_float), ("scale_modifier", c_float), ("prefiltered", c_int),
+    ]
+
+
+HDR_NUM_RENDERED, HDR_OVERFLOW, HDR_NUM_POINTS, HDR_NUM_SORTED, HDR_WORDS = 0, 1, 2, 3, 64
+
+_P = c_void_p  # every device pointer crosses the ABI as a plain address
+
+# name -> (restype, argtypes); must list every symbol include/gp_b200.h declares (tests check this).
+SIGNATURES = {
+    "gp_abi_version": (c_int, []),
+    "gp_error_string": (c_char_p, [c_int]),
+    "gp_raster_sizes": (c_int, [c_int, c_int, c_int, c_longlong, POINTER(c_size_t), POINTER(c_size_t), POINTER(c_size_t)]),
+    "gp_raster_preprocess": (c_int, [POINTER(RasterCfg)] + [_P] * 10 + [_P, _P, _P]),
+    "gp_raster_num_rendered": (c_int, [_P, _P, POINTER(c_int)]),
+    "gp_raster_render": (c_int, [POINTER(RasterCfg), _P, _P, _P, _P, c_longlong, _P, _P, _P, _P, _P, _P]),
+    "gp_raster_backward_ws_bytes": (c_size_t, [c_int]),
+    "gp_raster_backward": (c_int, [POINTER(RasterCfg)] + [_P] * 13 + [c_longlong] + [_P] * 12),
+    "gp_mark_visible": (c_int, [c_int, _P, _P, _P, _P, _P]),
+    "gp_raster_export_state": (c_int, [POINTER(RasterCfg)] + [_P] * 13),
+    "gp_raster_export_binning": (c_int, [POINTER(RasterCfg), _P, _P, c_longlong, _P, _P, _P]),
+}
+
+_lib = None
+
+
+def lib():
+    """Load (once) and return the ctypes handle; raises GpError if the library has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise GpError(
+                f"{LIB_PATH} not found: the CUDA library has not been built. Run "
+                "`python -m gaussianprediction_b200.build` (there is no CPU fallback).")
+        handle = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(handle, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = handle
+    return _lib
+
+
+def check(code, what=""):
+    if code != 0:
+        msg = lib().gp_error_string(int(code))
+        raise GpError(f"{what}: error {code}: {msg.decode() if msg else '?'}")
+
+
+def ptr(t):
+    """Device address of a torch tensor (None -> NULL).  The tensor must be contiguous."""
+    if t is None:
+        return None
+    assert t.is_contiguous(), "gp_b200: tensor must be contiguous"
+    return t.data_ptr()
+
+
+def stream_ptr():
+    import torch
+    return torch.cuda.current_stream().cuda_stream

@@ -1,0 +1,522 @@
+// Rasterizer backward for sm_100a.
+//
+// Reference path replaced: CudaRasterizer::Rasterizer::backward
+// (submodules/diff-gaussian-rasterization-w-depth/cuda_rasterizer/rasterizer_impl.cu:346-439):
+// renderCUDA backward (backward.cu:399-557), computeCov2DCUDA (:144-274), preprocessCUDA (:346-396).
+//
+// Structure:
+//  * Blend backward: same back-to-front traversal per pixel as the reference (T is rebuilt by the
+//    same division), but the reference's 9 global atomicAdd per pixel x Gaussian pair are replaced
+//    by a warp-level transposing reduction (14 shuffles per Gaussian per warp), shared-memory
+//    accumulation per tile, and three 128-bit vector reductions (red.global.add.v4.f32) per
+//    tile x Gaussian instance into one packed 48-byte record per Gaussian.
+//  * Per-Gaussian backward: the reference's two kernels are fused; the packed record is read once
+//    and every output gradient is written exactly once, including zeros for culled Gaussians, so no
+//    output tensor needs a memset (the reference zero-fills 300 B per Gaussian per call,
+//    rasterize_points.cu:153-161).
+#include "gmath.cuh"
+#include "raster_state.cuh"
+
+// packed per-Gaussian accumulator filled by the blend backward: 12 floats
+//   [0] dL/dmean2D.x  [1] dL/dmean2D.y  [2] dL/dconic.x  [3] dL/dconic.y
+//   [4] dL/dconic.w   [5] dL/dopacity   [6] dL/dr        [7] dL/dg
+//   [8] dL/db         [9..11] unused
+#define GP_GREC 12
+
+__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
+// Sum v[0..7] over the 32 lanes with a transposing butterfly: after the call lane L (L % 4 == 0)
+// holds the warp total of component L / 4.  9 shuffles instead of 40.
+__device__ __forceinline__ float warp_transpose_reduce8(float (&v)[8], int lane) {
+  const bool h16 = lane & 16;
+  float w4[4];
+#pragma unroll
+  for (int i = 0; i < 4; i++) {
+    const float send = h16 ? v[i] : v[i + 4];
+    const float keep = h16 ? v[i + 4] : v[i];
+    w4[i] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+  }
+  const bool h8 = lane & 8;
+  float w2[2];
+#pragma unroll
+  for (int i = 0; i < 2; i++) {
+    const float send = h8 ? w4[i] : w4[i + 2];
+    const float keep = h8 ? w4[i + 2] : w4[i];
+    w2[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+  }
+  const bool h4 = lane & 4;
+  const float send = h4 ? w2[0] : w2[1];
+  const float keep = h4 ? w2[1] : w2[0];
+  float r = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+  r += __shfl_xor_sync(0xffffffffu, r, 2);
+  r += __shfl_xor_sync(0xffffffffu, r, 1);
+  return r;  // component index = ((lane>>4)&1)*4 + ((lane>>3)&1)*2 + ((lane>>2)&1)
+}
+
+__global__ void __launch_bounds__(GP_TILE_PIX)
+gp_render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H,
+                     unsigned grid_x, const float* __restrict__ bg_color, const float4* __restrict__ xy_depth,
+                     const float4* __restrict__ conic_opacity, const float4* __restrict__ rgb4,
+                     const float* __restrict__ colors_precomp, const float* __restrict__ final_Ts,
+                     const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpixels,
+                     const int* __restrict__ hdr, float* __restrict__ grec) {
+  __shared__ float4 s_co[GP_TILE_PIX];
+  __shared__ float4 s_xyd[GP_TILE_PIX];
+  __shared__ float4 s_rgb[GP_TILE_PIX];
+  __shared__ int s_id[GP_TILE_PIX];
+  __shared__ float s_acc[GP_TILE_PIX * GP_GREC];
+
+  if (hdr[GP_HDR_OVERFLOW]) return;
+  const int t = threadIdx.x, w = t >> 5, lane = t & 31;
+  const unsigned tile = blockIdx.x;
+  const unsigned tile_x = tile % grid_x, tile_y = tile / grid_x;
+  const unsigned px = tile_x * GP_TILE_X + (w & 1) * 8 + (lane & 7);
+  const unsigned py = tile_y * GP_TILE_Y + (w >> 1) * 4 + (lane >> 3);
+  const bool inside = px < (unsigned)W && py < (unsigned)H;
+  const unsigned pix_id = (unsigned)W * py + px;
+  const float pixfx = (float)px, pixfy = (float)py;
+
+  const uint2 range = ranges[tile];
+  const int rounds = ((range.y - range.x + GP_TILE_PIX - 1) / GP_TILE_PIX);
+  int toDo = range.y - range.x;
+
+  const float T_final = inside ? final_Ts[pix_id] : 0.f;
+  float T = T_final;
+  uint32_t contributor = toDo;
+  const uint32_t last_contributor = inside ? n_contrib[pix_id] : 0u;
+
+  float accum0 = 0.f, accum1 = 0.f, accum2 = 0.f;
+  float dpx0 = 0.f, dpx1 = 0.f, dpx2 = 0.f;
+  if (inside) {
+    const size_t hw = (size_t)H * W;
+    dpx0 = dL_dpixels[pix_id];
+    dpx1 = dL_dpixels[hw + pix_id];
+    dpx2 = dL_dpixels[2 * hw + pix_id];
+  }
+  float last_alpha = 0.f, lc0 = 0.f, lc1 = 0.f, lc2 = 0.f;
+  const float ddelx_dx = 0.5f * W;
+  const float ddely_dy = 0.5f * H;
+  const float bg_dot_dpixel = bg_color[0] * dpx0 + bg_color[1] * dpx1 + bg_color[2] * dpx2;
+
+  // the largest list position any pixel of this warp still has to visit
+  unsigned warp_last = last_contributor;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) warp_last = max(warp_last, __shfl_xor_sync(0xffffffffu, warp_last, o));
+
+  for (int i = 0; i < rounds; i++, toDo -= GP_TILE_PIX) {
+    __syncthreads();
+    const int progress = i * GP_TILE_PIX + t;
+    if (range.x + progress < range.y) {
+      const int id = point_list[range.y - progress - 1];
+      s_id[t] = id;
+      s_co[t] = __ldg(conic_opacity + id);
+      s_xyd[t] = __ldg(xy_depth + id);
+      if (colors_precomp != nullptr)
+        s_rgb[t] = make_float4(colors_precomp[3 * (size_t)id], colors_precomp[3 * (size_t)id + 1],
+                               colors_precomp[3 * (size_t)id + 2], 0.f);
+      else
+        s_rgb[t] = __ldg(rgb4 + id);
+    }
+#pragma unroll
+    for (int k = 0; k < GP_GREC; k++) s_acc[k * GP_TILE_PIX + t] = 0.f;
+    __syncthreads();
+
+    const int nb = min(GP_TILE_PIX, toDo);
+    for (int j = 0; j < nb; j++) {
+      contributor--;
+      if (contributor >= warp_last) continue;  // warp-uniform: nobody in this warp reaches it
+      bool active = inside && contributor < last_contributor;
+      const float4 xyd = s_xyd[j];
+      const float4 co = s_co[j];
+      const float dx = xyd.x - pixfx;
+      const float dy = xyd.y - pixfy;
+      const float qa = __fmul_rn(co.x, dx);
+      const float qb = __fmul_rn(__fmul_rn(co.z, dy), dy);
+      const float qs = __fmaf_rn(qa, dx, qb);
+      const float qc = __fmul_rn(__fmul_rn(co.y, dx), dy);
+      const float power = __fmaf_rn(qs, -0.5f, -qc);
+      active = active && !(power > 0.0f);
+      const float G = expf(power);
+      const float alpha = fminf(0.99f, __fmul_rn(co.w, G));
+      active = active && !(alpha < 1.0f / 255.0f);
+      if (!__any_sync(0xffffffffu, active)) continue;
+
+      float v[8];
+      float v_op = 0.f;
+#pragma unroll
+      for (int k = 0; k < 8; k++) v[k] = 0.f;
+      if (active) {
+        T = T / (1.f - alpha);
+        const float dchannel_dcolor = alpha * T;
+        const float4 col = s_rgb[j];
+        float dL_dalpha = 0.0f;
+        accum0 = last_alpha * lc0 + (1.f - last_alpha) * accum0;
+        lc0 = col.x;
+        dL_dalpha += (col.x - accum0) * dpx0;
+        accum1 = last_alpha * lc1 + (1.f - last_alpha) * accum1;
+        lc1 = col.y;
+        dL_dalpha += (col.y - accum1) * dpx1;
+        accum2 = last_alpha * lc2 + (1.f - last_alpha) * accum2;
+        lc2 = col.z;
+        dL_dalpha += (col.z - accum2) * dpx2;
+        dL_dalpha *= T;
+        last_alpha = alpha;
+        dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot_dpixel;
+
+        const float dL_dG = co.w * dL_dalpha;
+        const float gdx = G * dx;
+        const float gdy = G * dy;
+        const float dG_ddelx = -gdx * co.x - gdy * co.y;
+        const float dG_ddely = -gdy * co.z - gdx * co.y;
+        v[0] = dL_dG * dG_ddelx * ddelx_dx;
+        v[1] = dL_dG * dG_ddely * ddely_dy;
+        v[2] = -0.5f * gdx * dx * dL_dG;
+        v[3] = -0.5f * gdx * dy * dL_dG;
+        v[4] = -0.5f * gdy * dy * dL_dG;
+        v[5] = dchannel_dcolor * dpx0;
+        v[6] = dchannel_dcolor * dpx1;
+        v[7] = dchannel_dcolor * dpx2;
+        v_op = G * dL_dalpha;
+      }
+      const float r = warp_transpose_reduce8(v, lane);
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) v_op += __shfl_xor_sync(0xffffffffu, v_op, o);
+      if ((lane & 3) == 0) {
+        const int comp = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
+        // record slots: comps 0..4 -> 0..4, colours 5..7 -> 6..8, opacity -> 5
+        const int slot = comp < 5 ? comp : comp + 1;
+        atomicAdd(&s_acc[slot * GP_TILE_PIX + j], r);
+      }
+      if (lane == 1) atomicAdd(&s_acc[5 * GP_TILE_PIX + j], v_op);
+    }
+    __syncthreads();
+    if (t < nb) {
+      float* dst = grec + (size_t)s_id[t] * GP_GREC;
+      const float a0 = s_acc[0 * GP_TILE_PIX + t], a1 = s_acc[1 * GP_TILE_PIX + t], a2 = s_acc[2 * GP_TILE_PIX + t],
+                  a3 = s_acc[3 * GP_TILE_PIX + t], a4 = s_acc[4 * GP_TILE_PIX + t], a5 = s_acc[5 * GP_TILE_PIX + t],
+                  a6 = s_acc[6 * GP_TILE_PIX + t], a7 = s_acc[7 * GP_TILE_PIX + t], a8 = s_acc[8 * GP_TILE_PIX + t];
+      if (a0 != 0.f || a1 != 0.f || a2 != 0.f || a3 != 0.f) red_add_v4(dst, a0, a1, a2, a3);
+      if (a4 != 0.f || a5 != 0.f || a6 != 0.f || a7 != 0.f) red_add_v4(dst + 4, a4, a5, a6, a7);
+      if (a8 != 0.f) atomicAdd(dst + 8, a8);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// per-Gaussian backward (fused cov2D + projection + SH + cov3D)
+// ------------------------------------------------------------------------------------------------
+
+__device__ __forceinline__ V3 dnormvdv3(const V3& v, const V3& dv) {
+  const float sum2 = v.x * v.x + v.y * v.y + v.z * v.z;
+  const float invsum32 = 1.0f / sqrtf(sum2 * sum2 * sum2);
+  V3 r;
+  r.x = ((+sum2 - v.x * v.x) * dv.x - v.y * v.x * dv.y - v.z * v.x * dv.z) * invsum32;
+  r.y = (-v.x * v.y * dv.x + (sum2 - v.y * v.y) * dv.y - v.z * v.y * dv.z) * invsum32;
+  r.z = (-v.x * v.z * dv.x - v.y * v.z * dv.y + (sum2 - v.z * v.z) * dv.z) * invsum32;
+  return r;
+}
+
+// SH backward (reference backward.cu:20-139): writes dL/dsh for the active degree and returns the
+// view-direction part of dL/dmean.
+__device__ __forceinline__ V3 sh_backward(int deg, int M, const V3& pos, const V3& campos,
+                                          const float* __restrict__ shp, unsigned clamp_bits, V3 dL_dRGB,
+                                          float* __restrict__ dL_dshp) {
+  const V3 dir_orig = pos - campos;
+  const V3 dir = dir_orig / len3(dir_orig);
+  const V3* sh = (const V3*)shp;
+  V3* dL_dsh = (V3*)dL_dshp;
+  dL_dRGB.x *= (clamp_bits & 1u) ? 0.f : 1.f;
+  dL_dRGB.y *= (clamp_bits & 2u) ? 0.f : 1.f;
+  dL_dRGB.z *= (clamp_bits & 4u) ? 0.f : 1.f;
+  V3 dRGBdx = v3(0, 0, 0), dRGBdy = v3(0, 0, 0), dRGBdz = v3(0, 0, 0);
+  const float x = dir.x, y = dir.y, z = dir.z;
+
+  dL_dsh[0] = GP_SH_C0 * dL_dRGB;
+  int written = 1;
+  if (deg > 0) {
+    dL_dsh[1] = (-GP_SH_C1 * y) * dL_dRGB;
+    dL_dsh[2] = (GP_SH_C1 * z) * dL_dRGB;
+    dL_dsh[3] = (-GP_SH_C1 * x) * dL_dRGB;
+    written = 4;
+    dRGBdx = -GP_SH_C1 * sh[3];
+    dRGBdy = -GP_SH_C1 * sh[1];
+    dRGBdz = GP_SH_C1 * sh[2];
+    if (deg > 1) {
+      const float xx = x * x, yy = y * y, zz = z * z;
+      const float xy = x * y, yz = y * z, xz = x * z;
+      dL_dsh[4] = (GP_SH_C2[0] * xy) * dL_dRGB;
+      dL_dsh[5] = (GP_SH_C2[1] * yz) * dL_dRGB;
+      dL_dsh[6] = (GP_SH_C2[2] * (2.f * zz - xx - yy)) * dL_dRGB;
+      dL_dsh[7] = (GP_SH_C2[3] * xz) * dL_dRGB;
+      dL_dsh[8] = (GP_SH_C2[4] * (xx - yy)) * dL_dRGB;
+      written = 9;
+      dRGBdx += GP_SH_C2[0] * y * sh[4] + GP_SH_C2[2] * 2.f * -x * sh[6] + GP_SH_C2[3] * z * sh[7] +
+                GP_SH_C2[4] * 2.f * x * sh[8];
+      dRGBdy += GP_SH_C2[0] * x * sh[4] + GP_SH_C2[1] * z * sh[5] + GP_SH_C2[2] * 2.f * -y * sh[6] +
+                GP_SH_C2[4] * 2.f * -y * sh[8];
+      dRGBdz += GP_SH_C2[1] * y * sh[5] + GP_SH_C2[2] * 2.f * 2.f * z * sh[6] + GP_SH_C2[3] * x * sh[7];
+      if (deg > 2) {
+        dL_dsh[9] = (GP_SH_C3[0] * y * (3.f * xx - yy)) * dL_dRGB;
+        dL_dsh[10] = (GP_SH_C3[1] * xy * z) * dL_dRGB;
+        dL_dsh[11] = (GP_SH_C3[2] * y * (4.f * zz - xx - yy)) * dL_dRGB;
+        dL_dsh[12] = (GP_SH_C3[3] * z * (2.f * zz - 3.f * xx - 3.f * yy)) * dL_dRGB;
+        dL_dsh[13] = (GP_SH_C3[4] * x * (4.f * zz - xx - yy)) * dL_dRGB;
+        dL_dsh[14] = (GP_SH_C3[5] * z * (xx - yy)) * dL_dRGB;
+        dL_dsh[15] = (GP_SH_C3[6] * x * (xx - 3.f * yy)) * dL_dRGB;
+        written = 16;
+        dRGBdx += (GP_SH_C3[0] * sh[9] * 3.f * 2.f * xy + GP_SH_C3[1] * sh[10] * yz + GP_SH_C3[2] * sh[11] * -2.f * xy +
+                   GP_SH_C3[3] * sh[12] * -3.f * 2.f * xz + GP_SH_C3[4] * sh[13] * (-3.f * xx + 4.f * zz - yy) +
+                   GP_SH_C3[5] * sh[14] * 2.f * xz + GP_SH_C3[6] * sh[15] * 3.f * (xx - yy));
+        dRGBdy += (GP_SH_C3[0] * sh[9] * 3.f * (xx - yy) + GP_SH_C3[1] * sh[10] * xz +
+                   GP_SH_C3[2] * sh[11] * (-3.f * yy + 4.f * zz - xx) + GP_SH_C3[3] * sh[12] * -3.f * 2.f * yz +
+                   GP_SH_C3[4] * sh[13] * -2.f * xy + GP_SH_C3[5] * sh[14] * -2.f * yz +
+                   GP_SH_C3[6] * sh[15] * -3.f * 2.f * xy);
+        dRGBdz += (GP_SH_C3[1] * sh[10] * xy + GP_SH_C3[2] * sh[11] * 4.f * 2.f * yz +
+                   GP_SH_C3[3] * sh[12] * 3.f * (2.f * zz - xx - yy) + GP_SH_C3[4] * sh[13] * 4.f * 2.f * xz +
+                   GP_SH_C3[5] * sh[14] * (xx - yy));
+      }
+    }
+  }
+  for (int k = written; k < M; k++) dL_dsh[k] = v3(0.f, 0.f, 0.f);  // coefficients above the active degree
+  const V3 dL_ddir = v3(dot3(dRGBdx, dL_dRGB), dot3(dRGBdy, dL_dRGB), dot3(dRGBdz, dL_dRGB));
+  return dnormvdv3(dir_orig, dL_ddir);
+}
+
+__global__ void __launch_bounds__(256)
+gp_preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, const int* __restrict__ radii,
+                         const float* __restrict__ shs, const uint8_t* __restrict__ clamped,
+                         const float* __restrict__ scales, const float* __restrict__ rotations, float scale_modifier,
+                         const float* __restrict__ cov3Ds, const float* __restrict__ view,
+                         const float* __restrict__ proj, float h_x, float h_y, float tan_fovx, float tan_fovy,
+                         const float* __restrict__ campos, const float* __restrict__ grec,
+                         float* __restrict__ dL_dmean2D_out, float* __restrict__ dL_dcolors_out,
+                         float* __restrict__ dL_dopacity_out, float* __restrict__ dL_dmeans_out,
+                         float* __restrict__ dL_dcov3D_out, float* __restrict__ dL_dsh_out,
+                         float* __restrict__ dL_dscale_out, float* __restrict__ dL_drot_out) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= P) return;
+  const bool visible = radii[idx] > 0;
+
+  float rec[GP_GREC];
+  if (visible) {
+    const float4* r4 = (const float4*)(grec + (size_t)idx * GP_GREC);
+    const float4 a = r4[0], b = r4[1], c = r4[2];
+    rec[0] = a.x; rec[1] = a.y; rec[2] = a.z; rec[3] = a.w;
+    rec[4] = b.x; rec[5] = b.y; rec[6] = b.z; rec[7] = b.w;
+    rec[8] = c.x; rec[9] = 0.f; rec[10] = 0.f; rec[11] = 0.f;
+  } else {
+#pragma unroll
+    for (int k = 0; k < GP_GREC; k++) rec[k] = 0.f;
+  }
+  // gradients that are plain copies of the accumulator
+  dL_dmean2D_out[3 * (size_t)idx] = rec[0];
+  dL_dmean2D_out[3 * (size_t)idx + 1] = rec[1];
+  dL_dmean2D_out[3 * (size_t)idx + 2] = 0.f;
+  dL_dopacity_out[idx] = rec[5];
+  if (dL_dcolors_out) {
+    dL_dcolors_out[3 * (size_t)idx] = rec[6];
+    dL_dcolors_out[3 * (size_t)idx + 1] = rec[7];
+    dL_dcolors_out[3 * (size_t)idx + 2] = rec[8];
+  }
+
+  V3 dL_dmean = v3(0.f, 0.f, 0.f);
+  float dL_dcov[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  if (!visible) {
+    dL_dmeans_out[3 * (size_t)idx] = 0.f;
+    dL_dmeans_out[3 * (size_t)idx + 1] = 0.f;
+    dL_dmeans_out[3 * (size_t)idx + 2] = 0.f;
+    if (dL_dcov3D_out)
+      for (int k = 0; k < 6; k++) dL_dcov3D_out[6 * (size_t)idx + k] = 0.f;
+    if (dL_dsh_out)
+      for (int k = 0; k < 3 * M; k++) dL_dsh_out[(size_t)idx * 3 * M + k] = 0.f;
+    if (dL_dscale_out) {
+      for (int k = 0; k < 3; k++) dL_dscale_out[3 * (size_t)idx + k] = 0.f;
+      for (int k = 0; k < 4; k++) dL_drot_out[4 * (size_t)idx + k] = 0.f;
+    }
+    return;
+  }
+
+  const V3 mean = v3(means3D[3 * (size_t)idx], means3D[3 * (size_t)idx + 1], means3D[3 * (size_t)idx + 2]);
+
+  // ---- 2D covariance / conic backward (reference computeCov2DCUDA, backward.cu:144-274) ----
+  {
+    const float* cov3D = cov3Ds + 6 * (size_t)idx;
+    const float dconx = rec[2], dcony = rec[3], dconw = rec[4];
+    V3 t = xform4x3(mean, view);
+    const float limx = 1.3f * tan_fovx;
+    const float limy = 1.3f * tan_fovy;
+    const float txtz = t.x / t.z;
+    const float tytz = t.y / t.z;
+    t.x = min(limx, max(-limx, txtz)) * t.z;
+    t.y = min(limy, max(-limy, tytz)) * t.z;
+    const float x_grad_mul = txtz < -limx || txtz > limx ? 0.f : 1.f;
+    const float y_grad_mul = tytz < -limy || tytz > limy ? 0.f : 1.f;
+
+    const M3 J = m3(h_x / t.z, 0.0f, -(h_x * t.x) / (t.z * t.z), 0.0f, h_y / t.z, -(h_y * t.y) / (t.z * t.z), 0, 0, 0);
+    const M3 Wm = m3(view[0], view[4], view[8], view[1], view[5], view[9], view[2], view[6], view[10]);
+    const M3 Vrk = m3(cov3D[0], cov3D[1], cov3D[2], cov3D[1], cov3D[3], cov3D[4], cov3D[2], cov3D[4], cov3D[5]);
+    const M3 T = m3mul(Wm, J);
+    M3 cov2D = m3mul(m3mul(m3t(T), m3t(Vrk)), T);
+    const float a = cov2D.c[0][0] += 0.3f;
+    const float b = cov2D.c[0][1];
+    const float c = cov2D.c[1][1] += 0.3f;
+    const float denom = a * c - b * b;
+    float dL_da = 0, dL_db = 0, dL_dc = 0;
+    const float denom2inv = 1.0f / ((denom * denom) + 0.0000001f);
+    if (denom2inv != 0) {
+      dL_da = denom2inv * (-c * c * dconx + 2 * b * c * dcony + (denom - a * c) * dconw);
+      dL_dc = denom2inv * (-a * a * dconw + 2 * a * b * dcony + (denom - a * c) * dconx);
+      dL_db = denom2inv * 2 * (b * c * dconx - (denom + 2 * b * b) * dcony + a * b * dconw);
+      dL_dcov[0] = (T.c[0][0] * T.c[0][0] * dL_da + T.c[0][0] * T.c[1][0] * dL_db + T.c[1][0] * T.c[1][0] * dL_dc);
+      dL_dcov[3] = (T.c[0][1] * T.c[0][1] * dL_da + T.c[0][1] * T.c[1][1] * dL_db + T.c[1][1] * T.c[1][1] * dL_dc);
+      dL_dcov[5] = (T.c[0][2] * T.c[0][2] * dL_da + T.c[0][2] * T.c[1][2] * dL_db + T.c[1][2] * T.c[1][2] * dL_dc);
+      dL_dcov[1] = 2 * T.c[0][0] * T.c[0][1] * dL_da + (T.c[0][0] * T.c[1][1] + T.c[0][1] * T.c[1][0]) * dL_db +
+                   2 * T.c[1][0] * T.c[1][1] * dL_dc;
+      dL_dcov[2] = 2 * T.c[0][0] * T.c[0][2] * dL_da + (T.c[0][0] * T.c[1][2] + T.c[0][2] * T.c[1][0]) * dL_db +
+                   2 * T.c[1][0] * T.c[1][2] * dL_dc;
+      dL_dcov[4] = 2 * T.c[0][2] * T.c[0][1] * dL_da + (T.c[0][1] * T.c[1][2] + T.c[0][2] * T.c[1][1]) * dL_db +
+                   2 * T.c[1][1] * T.c[1][2] * dL_dc;
+    }
+    const float dL_dT00 = 2 * (T.c[0][0] * Vrk.c[0][0] + T.c[0][1] * Vrk.c[0][1] + T.c[0][2] * Vrk.c[0][2]) * dL_da +
+                          (T.c[1][0] * Vrk.c[0][0] + T.c[1][1] * Vrk.c[0][1] + T.c[1][2] * Vrk.c[0][2]) * dL_db;
+    const float dL_dT01 = 2 * (T.c[0][0] * Vrk.c[1][0] + T.c[0][1] * Vrk.c[1][1] + T.c[0][2] * Vrk.c[1][2]) * dL_da +
+                          (T.c[1][0] * Vrk.c[1][0] + T.c[1][1] * Vrk.c[1][1] + T.c[1][2] * Vrk.c[1][2]) * dL_db;
+    const float dL_dT02 = 2 * (T.c[0][0] * Vrk.c[2][0] + T.c[0][1] * Vrk.c[2][1] + T.c[0][2] * Vrk.c[2][2]) * dL_da +
+                          (T.c[1][0] * Vrk.c[2][0] + T.c[1][1] * Vrk.c[2][1] + T.c[1][2] * Vrk.c[2][2]) * dL_db;
+    const float dL_dT10 = 2 * (T.c[1][0] * Vrk.c[0][0] + T.c[1][1] * Vrk.c[0][1] + T.c[1][2] * Vrk.c[0][2]) * dL_dc +
+                          (T.c[0][0] * Vrk.c[0][0] + T.c[0][1] * Vrk.c[0][1] + T.c[0][2] * Vrk.c[0][2]) * dL_db;
+    const float dL_dT11 = 2 * (T.c[1][0] * Vrk.c[1][0] + T.c[1][1] * Vrk.c[1][1] + T.c[1][2] * Vrk.c[1][2]) * dL_dc +
+                          (T.c[0][0] * Vrk.c[1][0] + T.c[0][1] * Vrk.c[1][1] + T.c[0][2] * Vrk.c[1][2]) * dL_db;
+    const float dL_dT12 = 2 * (T.c[1][0] * Vrk.c[2][0] + T.c[1][1] * Vrk.c[2][1] + T.c[1][2] * Vrk.c[2][2]) * dL_dc +
+                          (T.c[0][0] * Vrk.c[2][0] + T.c[0][1] * Vrk.c[2][1] + T.c[0][2] * Vrk.c[2][2]) * dL_db;
+    const float dL_dJ00 = Wm.c[0][0] * dL_dT00 + Wm.c[0][1] * dL_dT01 + Wm.c[0][2] * dL_dT02;
+    const float dL_dJ02 = Wm.c[2][0] * dL_dT00 + Wm.c[2][1] * dL_dT01 + Wm.c[2][2] * dL_dT02;
+    const float dL_dJ11 = Wm.c[1][0] * dL_dT10 + Wm.c[1][1] * dL_dT11 + Wm.c[1][2] * dL_dT12;
+    const float dL_dJ12 = Wm.c[2][0] * dL_dT10 + Wm.c[2][1] * dL_dT11 + Wm.c[2][2] * dL_dT12;
+    const float tz = 1.f / t.z;
+    const float tz2 = tz * tz;
+    const float tz3 = tz2 * tz;
+    const float dL_dtx = x_grad_mul * -h_x * tz2 * dL_dJ02;
+    const float dL_dty = y_grad_mul * -h_y * tz2 * dL_dJ12;
+    const float dL_dtz = -h_x * tz2 * dL_dJ00 - h_y * tz2 * dL_dJ11 + (2 * h_x * t.x) * tz3 * dL_dJ02 +
+                         (2 * h_y * t.y) * tz3 * dL_dJ12;
+    dL_dmean = xformvec4x3T(v3(dL_dtx, dL_dty, dL_dtz), view);
+  }
+
+  // ---- projection part of dL/dmean (reference backward.cu:367-387) ----
+  {
+    const float4 m_hom = xform4x4(mean, proj);
+    const float m_w = 1.0f / (m_hom.w + 0.0000001f);
+    const float mul1 = (proj[0] * mean.x + proj[4] * mean.y + proj[8] * mean.z + proj[12]) * m_w * m_w;
+    const float mul2 = (proj[1] * mean.x + proj[5] * mean.y + proj[9] * mean.z + proj[13]) * m_w * m_w;
+    const float gx = rec[0], gy = rec[1];
+    V3 d;
+    d.x = (proj[0] * m_w - proj[3] * mul1) * gx + (proj[1] * m_w - proj[3] * mul2) * gy;
+    d.y = (proj[4] * m_w - proj[7] * mul1) * gx + (proj[5] * m_w - proj[7] * mul2) * gy;
+    d.z = (proj[8] * m_w - proj[11] * mul1) * gx + (proj[9] * m_w - proj[11] * mul2) * gy;
+    dL_dmean += d;
+  }
+
+  // ---- SH backward ----
+  if (shs) {
+    const V3 dm = sh_backward(D, M, mean, v3(campos[0], campos[1], campos[2]), shs + (size_t)idx * M * 3, clamped[idx],
+                              v3(rec[6], rec[7], rec[8]), dL_dsh_out + (size_t)idx * M * 3);
+    dL_dmean += dm;
+  }
+  dL_dmeans_out[3 * (size_t)idx] = dL_dmean.x;
+  dL_dmeans_out[3 * (size_t)idx + 1] = dL_dmean.y;
+  dL_dmeans_out[3 * (size_t)idx + 2] = dL_dmean.z;
+  if (dL_dcov3D_out)
+    for (int k = 0; k < 6; k++) dL_dcov3D_out[6 * (size_t)idx + k] = dL_dcov[k];
+
+  // ---- 3D covariance backward to scale / raw quaternion (reference backward.cu:278-341) ----
+  if (scales) {
+    const float4 q = *(const float4*)(rotations + 4 * (size_t)idx);
+    const float r = q.x, x = q.y, y = q.z, z = q.w;
+    const M3 R = m3(1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y),
+                    2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x),
+                    2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y));
+    const V3 s = v3(scale_modifier * scales[3 * (size_t)idx], scale_modifier * scales[3 * (size_t)idx + 1],
+                    scale_modifier * scales[3 * (size_t)idx + 2]);
+    M3 S = m3(1.0f, 0.0f, 0.0f, 0.0f, 1.0f, 0.0f, 0.0f, 0.0f, 1.0f);
+    S.c[0][0] = s.x;
+    S.c[1][1] = s.y;
+    S.c[2][2] = s.z;
+    const M3 Mm = m3mul(S, R);
+    const M3 dL_dSigma = m3(dL_dcov[0], 0.5f * dL_dcov[1], 0.5f * dL_dcov[2], 0.5f * dL_dcov[1], dL_dcov[3],
+                            0.5f * dL_dcov[4], 0.5f * dL_dcov[2], 0.5f * dL_dcov[4], dL_dcov[5]);
+    const M3 dL_dM = m3mul(m3scale(2.0f, Mm), dL_dSigma);
+    const M3 Rt = m3t(R);
+    M3 dL_dMt = m3t(dL_dM);
+    dL_dscale_out[3 * (size_t)idx] =
+        Rt.c[0][0] * dL_dMt.c[0][0] + Rt.c[0][1] * dL_dMt.c[0][1] + Rt.c[0][2] * dL_dMt.c[0][2];
+    dL_dscale_out[3 * (size_t)idx + 1] =
+        Rt.c[1][0] * dL_dMt.c[1][0] + Rt.c[1][1] * dL_dMt.c[1][1] + Rt.c[1][2] * dL_dMt.c[1][2];
+    dL_dscale_out[3 * (size_t)idx + 2] =
+        Rt.c[2][0] * dL_dMt.c[2][0] + Rt.c[2][1] * dL_dMt.c[2][1] + Rt.c[2][2] * dL_dMt.c[2][2];
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+      dL_dMt.c[0][k] *= s.x;
+      dL_dMt.c[1][k] *= s.y;
+      dL_dMt.c[2][k] *= s.z;
+    }
+    float4 dq;
+    dq.x = 2 * z * (dL_dMt.c[0][1] - dL_dMt.c[1][0]) + 2 * y * (dL_dMt.c[2][0] - dL_dMt.c[0][2]) +
+           2 * x * (dL_dMt.c[1][2] - dL_dMt.c[2][1]);
+    dq.y = 2 * y * (dL_dMt.c[1][0] + dL_dMt.c[0][1]) + 2 * z * (dL_dMt.c[2][0] + dL_dMt.c[0][2]) +
+           2 * r * (dL_dMt.c[1][2] - dL_dMt.c[2][1]) - 4 * x * (dL_dMt.c[2][2] + dL_dMt.c[1][1]);
+    dq.z = 2 * x * (dL_dMt.c[1][0] + dL_dMt.c[0][1]) + 2 * r * (dL_dMt.c[2][0] - dL_dMt.c[0][2]) +
+           2 * z * (dL_dMt.c[1][2] + dL_dMt.c[2][1]) - 4 * y * (dL_dMt.c[2][2] + dL_dMt.c[0][0]);
+    dq.w = 2 * r * (dL_dMt.c[0][1] - dL_dMt.c[1][0]) + 2 * x * (dL_dMt.c[2][0] + dL_dMt.c[0][2]) +
+           2 * y * (dL_dMt.c[1][2] + dL_dMt.c[2][1]) - 4 * z * (dL_dMt.c[1][1] + dL_dMt.c[0][0]);
+    *(float4*)(dL_drot_out + 4 * (size_t)idx) = dq;  // w.r.t. the raw (un-normalised) quaternion
+  }
+}
+
+extern "C" size_t gp_raster_backward_ws_bytes(int P) { return gp_align_up((size_t)(P > 0 ? P : 1) * GP_GREC * 4, 256); }
+
+extern "C" int gp_raster_backward(const gp_raster_cfg* cfg, const float* bg, const float* means3D, const float* shs,
+                                  const float* colors_precomp, const float* scales, const float* rotations,
+                                  const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
+                                  const float* campos, const int* radii, const void* geom_ws, const void* binning_ws,
+                                  long long capacity, const void* image_ws, const float* dL_dpix, void* grad_ws, float* dL_dmeans2D,
+                                  float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D, float* dL_dcov3D,
+                                  float* dL_dsh, float* dL_dscales, float* dL_drots, gp_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (!cfg || !bg || !means3D || !radii || !geom_ws || !binning_ws || !image_ws || !dL_dpix || !grad_ws ||
+      !dL_dmeans2D || !dL_dopacity || !dL_dmeans3D)
+    return GP_ERR_BAD_ARG;
+  const int P = cfg->P, W = cfg->width, H = cfg->height;
+  if (P <= 0 || W <= 0 || H <= 0 || capacity < 0) return GP_ERR_BAD_ARG;
+  if ((shs == nullptr) == (colors_precomp == nullptr)) return GP_ERR_BAD_ARG;
+  if (shs && !dL_dsh) return GP_ERR_BAD_ARG;
+  if (colors_precomp && !dL_dcolors) return GP_ERR_BAD_ARG;
+  const bool has_sr = scales != nullptr && rotations != nullptr;
+  if (has_sr == (cov3D_precomp != nullptr)) return GP_ERR_BAD_ARG;
+  if (has_sr && (!dL_dscales || !dL_drots)) return GP_ERR_BAD_ARG;
+  if (!has_sr && !dL_dcov3D) return GP_ERR_BAD_ARG;
+
+  GpGeom g = gp_carve_geom(const_cast<void*>(geom_ws), P);
+  GpBinning bn = gp_carve_binning(const_cast<void*>(binning_ws), capacity);
+  GpImage im = gp_carve_image(const_cast<void*>(image_ws), W, H);
+  const unsigned gx = (W + GP_TILE_X - 1) / GP_TILE_X, gy = (H + GP_TILE_Y - 1) / GP_TILE_Y;
+  const float focal_y = H / (2.0f * cfg->tanfovy);
+  const float focal_x = W / (2.0f * cfg->tanfovx);
+  float* grec = (float*)grad_ws;
+  GP_CUDA_TRY(cudaMemsetAsync(grec, 0, (size_t)P * GP_GREC * 4, stream));
+  const uint32_t* point_list = bn.tvals[gp_tile_sort_sel(W, H)];
+  gp_render_bwd_kernel<<<gx * gy, GP_TILE_PIX, 0, stream>>>(im.ranges, point_list, W, H, gx, bg, g.xy_depth,
+                                                           g.conic_opacity, g.rgb, colors_precomp, im.final_T,
+                                                           im.n_contrib, dL_dpix, g.hdr, grec);
+  GP_LAUNCH_CHECK();
+  const float* cov3D_ptr = cov3D_precomp ? cov3D_precomp : g.cov3D;
+  gp_preprocess_bwd_kernel<<<(P + 255) / 256, 256, 0, stream>>>(
+      P, cfg->sh_degree, cfg->sh_coeffs, means3D, radii, shs, g.clamped, has_sr ? scales : nullptr,
+      has_sr ? rotations : nullptr, cfg->scale_modifier, cov3D_ptr, viewmatrix, projmatrix, focal_x, focal_y,
+      cfg->tanfovx, cfg->tanfovy, campos, grec, dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh,
+      dL_dscales, dL_drots);
+  GP_LAUNCH_CHECK();
+  return GP_OK;
+}

@@ -1,0 +1,620 @@
+// Rasterizer forward for sm_100a: preprocess -> depth sort -> tile-count scan -> duplicate ->
+// tile sort -> tile ranges -> alpha / median-depth blending.
+//
+// Reference path replaced: CudaRasterizer::Rasterizer::forward
+// (submodules/diff-gaussian-rasterization-w-depth/cuda_rasterizer/rasterizer_impl.cu:198-342),
+// kernels forward.cu:155-256 (preprocessCUDA), rasterizer_impl.cu:70-138 (duplicateWithKeys,
+// identifyTileRanges), forward.cu:261-398 (renderCUDA).
+//
+// Differences in structure (results are identical, see tests/test_raster_parity.py):
+//  * The reference sorts R 64-bit (tile|depth) keys (6 radix passes over R).  Here the P Gaussians
+//    are sorted once by depth bits (ties by index, as a stable sort of the reference's emission
+//    order gives), instances are emitted in that order, and only the tile id (<= 2 passes) is sorted
+//    over R.  A stable sort by tile of a depth-ordered list is the (tile, depth, index) order.
+//  * No host round trip: R lives in the workspace header, every R-sized kernel has a fixed grid.
+//  * The blend kernel stages colour and depth in shared memory with the conic, so the inner loop
+//    touches no global memory.
+#include "gmath.cuh"
+#include "raster_state.cuh"
+
+// ------------------------------------------------------------------------------------------------
+// preprocess
+// ------------------------------------------------------------------------------------------------
+
+__device__ __forceinline__ void cov3d_from_scale_rot(const V3 scale, float mod, const float4 rot, float* cov3D) {
+  // rot is used as given: this fork does NOT normalise the quaternion (reference forward.cu:127).
+  M3 S = m3(1.0f, 0.0f, 0.0f, 0.0f, 1.0f, 0.0f, 0.0f, 0.0f, 1.0f);
+  S.c[0][0] = mod * scale.x;
+  S.c[1][1] = mod * scale.y;
+  S.c[2][2] = mod * scale.z;
+  const float r = rot.x, x = rot.y, y = rot.z, z = rot.w;
+  M3 R = m3(1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y),
+            2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x),
+            2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y));
+  M3 M = m3mul(S, R);
+  M3 Sigma = m3mul(m3t(M), M);
+  cov3D[0] = Sigma.c[0][0];
+  cov3D[1] = Sigma.c[0][1];
+  cov3D[2] = Sigma.c[0][2];
+  cov3D[3] = Sigma.c[1][1];
+  cov3D[4] = Sigma.c[1][2];
+  cov3D[5] = Sigma.c[2][2];
+}
+
+__device__ __forceinline__ float3 cov2d_from_cov3d(const V3& mean, float focal_x, float focal_y, float tan_fovx,
+                                                   float tan_fovy, const float* cov3D, const float* view) {
+  V3 t = xform4x3(mean, view);
+  const float limx = 1.3f * tan_fovx;
+  const float limy = 1.3f * tan_fovy;
+  const float txtz = t.x / t.z;
+  const float tytz = t.y / t.z;
+  t.x = min(limx, max(-limx, txtz)) * t.z;
+  t.y = min(limy, max(-limy, tytz)) * t.z;
+  M3 J = m3(focal_x / t.z, 0.0f, -(focal_x * t.x) / (t.z * t.z), 0.0f, focal_y / t.z,
+            -(focal_y * t.y) / (t.z * t.z), 0, 0, 0);
+  M3 Wm = m3(view[0], view[4], view[8], view[1], view[5], view[9], view[2], view[6], view[10]);
+  M3 T = m3mul(Wm, J);
+  M3 Vrk = m3(cov3D[0], cov3D[1], cov3D[2], cov3D[1], cov3D[3], cov3D[4], cov3D[2], cov3D[4], cov3D[5]);
+  M3 cov = m3mul(m3mul(m3t(T), m3t(Vrk)), T);
+  cov.c[0][0] += 0.3f;  // low-pass: at least one pixel wide
+  cov.c[1][1] += 0.3f;
+  return float3{cov.c[0][0], cov.c[0][1], cov.c[1][1]};
+}
+
+__device__ __forceinline__ V3 sh_to_rgb(int deg, const V3& pos, const V3& campos, const float* __restrict__ shp,
+                                        unsigned& clamp_bits) {
+  V3 dir = pos - campos;
+  dir = dir / len3(dir);
+  const V3* sh = (const V3*)shp;
+  V3 result = GP_SH_C0 * sh[0];
+  if (deg > 0) {
+    const float x = dir.x, y = dir.y, z = dir.z;
+    result = result - GP_SH_C1 * y * sh[1] + GP_SH_C1 * z * sh[2] - GP_SH_C1 * x * sh[3];
+    if (deg > 1) {
+      const float xx = x * x, yy = y * y, zz = z * z;
+      const float xy = x * y, yz = y * z, xz = x * z;
+      result = result + GP_SH_C2[0] * xy * sh[4] + GP_SH_C2[1] * yz * sh[5] +
+               GP_SH_C2[2] * (2.0f * zz - xx - yy) * sh[6] + GP_SH_C2[3] * xz * sh[7] +
+               GP_SH_C2[4] * (xx - yy) * sh[8];
+      if (deg > 2) {
+        result = result + GP_SH_C3[0] * y * (3.0f * xx - yy) * sh[9] + GP_SH_C3[1] * xy * z * sh[10] +
+                 GP_SH_C3[2] * y * (4.0f * zz - xx - yy) * sh[11] +
+                 GP_SH_C3[3] * z * (2.0f * zz - 3.0f * xx - 3.0f * yy) * sh[12] +
+                 GP_SH_C3[4] * x * (4.0f * zz - xx - yy) * sh[13] + GP_SH_C3[5] * z * (xx - yy) * sh[14] +
+                 GP_SH_C3[6] * x * (xx - 3.0f * yy) * sh[15];
+      }
+    }
+  }
+  result.x += 0.5f;
+  result.y += 0.5f;
+  result.z += 0.5f;
+  clamp_bits = (result.x < 0 ? 1u : 0u) | (result.y < 0 ? 2u : 0u) | (result.z < 0 ? 4u : 0u);
+  return V3{fmaxf(result.x, 0.0f), fmaxf(result.y, 0.0f), fmaxf(result.z, 0.0f)};
+}
+
+__global__ void __launch_bounds__(256)
+gp_preprocess_kernel(int P, int D, int M, const float* __restrict__ means3D, const float* __restrict__ scales,
+                     float scale_modifier, const float* __restrict__ rotations, const float* __restrict__ opacities,
+                     const float* __restrict__ shs, const float* __restrict__ cov3D_precomp,
+                     const float* __restrict__ colors_precomp, const float* __restrict__ viewmatrix,
+                     const float* __restrict__ projmatrix, const float* __restrict__ cam_pos, int W, int H,
+                     float tan_fovx, float tan_fovy, float focal_x, float focal_y, int prefiltered, unsigned grid_x,
+                     unsigned grid_y, GpGeom g, int* __restrict__ radii) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx == 0) {
+    g.hdr[GP_HDR_NUM_POINTS] = P;
+    g.hdr[GP_HDR_NUM_RENDERED] = 0;
+    g.hdr[GP_HDR_OVERFLOW] = 0;
+    g.hdr[GP_HDR_NUM_SORTED] = 0;
+  }
+  if (idx >= P) return;
+
+  int radius_out = 0;
+  unsigned tiles_out = 0;
+  unsigned key_out = 0xFFFFFFFFu;
+
+  const V3 p_orig = v3(means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]);
+  // near culling exactly as the reference's in_frustum (auxiliary.h:139-163)
+  const V3 p_view = xform4x3(p_orig, viewmatrix);
+  bool alive = true;
+  if (p_view.z <= 0.2f) {
+    if (prefiltered) __trap();
+    alive = false;
+  }
+  if (alive) {
+    const float4 p_hom = xform4x4(p_orig, projmatrix);
+    const float p_w = 1.0f / (p_hom.w + 0.0000001f);
+    const V3 p_proj = v3(p_hom.x * p_w, p_hom.y * p_w, p_hom.z * p_w);
+
+    float cov3D_local[6];
+    const float* cov3D;
+    if (cov3D_precomp != nullptr) {
+      cov3D = cov3D_precomp + (size_t)idx * 6;
+    } else {
+      const V3 sc = v3(scales[3 * idx], scales[3 * idx + 1], scales[3 * idx + 2]);
+      const float4 rot = *(const float4*)(rotations + 4 * (size_t)idx);
+      cov3d_from_scale_rot(sc, scale_modifier, rot, cov3D_local);
+#pragma unroll
+      for (int k = 0; k < 6; k++) g.cov3D[(size_t)idx * 6 + k] = cov3D_local[k];
+      cov3D = cov3D_local;
+    }
+    const float3 cov = cov2d_from_cov3d(p_orig, focal_x, focal_y, tan_fovx, tan_fovy, cov3D, viewmatrix);
+    const float det = (cov.x * cov.z - cov.y * cov.y);
+    if (det != 0.0f) {
+      const float det_inv = 1.f / det;
+      const float3 conic = {cov.z * det_inv, -cov.y * det_inv, cov.x * det_inv};
+      const float mid = 0.5f * (cov.x + cov.z);
+      const float lambda1 = mid + sqrtf(max(0.1f, mid * mid - det));
+      const float lambda2 = mid - sqrtf(max(0.1f, mid * mid - det));
+      const float my_radius = ceilf(3.f * sqrtf(max(lambda1, lambda2)));
+      const float2 point_image = {ndc2pix(p_proj.x, W), ndc2pix(p_proj.y, H)};
+      uint2 rect_min, rect_max;
+      tile_rect(point_image.x, point_image.y, (int)my_radius, grid_x, grid_y, rect_min, rect_max);
+      const unsigned ntiles = (rect_max.x - rect_min.x) * (rect_max.y - rect_min.y);
+      if (ntiles != 0) {
+        if (colors_precomp == nullptr) {
+          unsigned cb;
+          const V3 c = sh_to_rgb(D, p_orig, v3(cam_pos[0], cam_pos[1], cam_pos[2]), shs + (size_t)idx * M * 3, cb);
+          g.rgb[idx] = make_float4(c.x, c.y, c.z, 0.f);
+          g.clamped[idx] = (uint8_t)cb;
+        }
+        g.xy_depth[idx] = make_float4(point_image.x, point_image.y, p_view.z, 0.f);
+        g.conic_opacity[idx] = make_float4(conic.x, conic.y, conic.z, opacities[idx]);
+        radius_out = (int)my_radius;
+        tiles_out = ntiles;
+        key_out = __float_as_uint(p_view.z);
+      }
+    }
+  }
+  radii[idx] = radius_out;
+  g.tiles_touched[idx] = tiles_out;
+  g.dkeys[0][idx] = key_out;
+  g.dvals[0][idx] = (uint32_t)idx;
+}
+
+// ------------------------------------------------------------------------------------------------
+// scan of tiles touched in depth order, and instance emission
+// ------------------------------------------------------------------------------------------------
+
+// block b: sum of tiles_touched over sorted positions [b*256, b*256+256)
+__global__ void __launch_bounds__(GP_SCAN_BLOCK)
+gp_block_sum_kernel(int P, const uint32_t* __restrict__ sorted_idx, const uint32_t* __restrict__ tiles_touched,
+                    uint32_t* __restrict__ block_sums) {
+  __shared__ uint32_t ws[GP_SCAN_BLOCK / 32];
+  const int s = blockIdx.x * GP_SCAN_BLOCK + threadIdx.x;
+  uint32_t v = s < P ? tiles_touched[sorted_idx[s]] : 0u;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  if ((threadIdx.x & 31) == 0) ws[threadIdx.x >> 5] = v;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t t = 0;
+#pragma unroll
+    for (int j = 0; j < GP_SCAN_BLOCK / 32; j++) t += ws[j];
+    block_sums[blockIdx.x] = t;
+  }
+}
+
+// single block: exclusive scan of block_sums[nb] in place, total -> header.
+__global__ void __launch_bounds__(1024)
+gp_spine_scan_kernel(int nb, uint32_t* __restrict__ block_sums, int* __restrict__ hdr, long long capacity) {
+  __shared__ unsigned long long warp_tot[32];
+  __shared__ unsigned long long carry_s;
+  const int t = threadIdx.x, lane = t & 31, w = t >> 5;
+  if (t == 0) carry_s = 0;
+  __syncthreads();
+  for (int base = 0; base < nb; base += 1024) {
+    const int i = base + t;
+    const unsigned long long v = i < nb ? block_sums[i] : 0ull;
+    unsigned long long incl = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      unsigned long long y = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += y;
+    }
+    if (lane == 31) warp_tot[w] = incl;
+    __syncthreads();
+    unsigned long long wbase = 0;
+    for (int j = 0; j < w; j++) wbase += warp_tot[j];
+    const unsigned long long carry = carry_s;
+    const unsigned long long excl = carry + wbase + incl - v;
+    if (i < nb) block_sums[i] = (uint32_t)(excl > 0xFFFFFFFFull ? 0xFFFFFFFFull : excl);
+    __syncthreads();
+    if (t == 1023) carry_s = carry + wbase + incl;
+    __syncthreads();
+  }
+  if (t == 0) {
+    const unsigned long long total = carry_s;
+    const bool over = total > (unsigned long long)capacity || total > 0x7FFFFFFFull;
+    hdr[GP_HDR_NUM_RENDERED] = (int)(total > 0x7FFFFFFFull ? 0x7FFFFFFFull : total);
+    hdr[GP_HDR_OVERFLOW] = over ? 1 : 0;
+    hdr[GP_HDR_NUM_SORTED] = over ? 0 : (int)total;
+  }
+}
+
+// Emits (tile id, Gaussian index) for every tile of every visible Gaussian, in depth order.
+// One block per 256 sorted Gaussians; the block's instances are produced cooperatively (one
+// instance per thread per step) so a huge splat does not serialise on one thread as in the
+// reference's per-Gaussian loop (rasterizer_impl.cu:98-109).
+__global__ void __launch_bounds__(GP_SCAN_BLOCK)
+gp_duplicate_kernel(int P, const uint32_t* __restrict__ sorted_idx, const uint32_t* __restrict__ tiles_touched,
+                    const float4* __restrict__ xy_depth, const int* __restrict__ radii,
+                    const uint32_t* __restrict__ block_excl, const int* __restrict__ hdr, unsigned grid_x,
+                    unsigned grid_y, uint32_t* __restrict__ tkeys, uint32_t* __restrict__ tvals) {
+  __shared__ uint32_t s_off[GP_SCAN_BLOCK + 1];  // exclusive offsets inside the block
+  __shared__ uint32_t s_g[GP_SCAN_BLOCK];
+  __shared__ uint32_t s_rx[GP_SCAN_BLOCK], s_ry[GP_SCAN_BLOCK], s_rw[GP_SCAN_BLOCK];
+  __shared__ uint32_t ws[GP_SCAN_BLOCK / 32];
+  if (hdr[GP_HDR_OVERFLOW]) return;
+  const int t = threadIdx.x, lane = t & 31, w = t >> 5;
+  const int s = blockIdx.x * GP_SCAN_BLOCK + t;
+  uint32_t gidx = 0, tt = 0;
+  if (s < P) {
+    gidx = sorted_idx[s];
+    tt = tiles_touched[gidx];
+  }
+  uint2 rmin = {0, 0}, rmax = {0, 0};
+  if (tt) {
+    const float4 xyd = xy_depth[gidx];
+    tile_rect(xyd.x, xyd.y, radii[gidx], grid_x, grid_y, rmin, rmax);
+  }
+  s_g[t] = gidx;
+  s_rx[t] = rmin.x;
+  s_ry[t] = rmin.y;
+  s_rw[t] = rmax.x - rmin.x;
+  uint32_t incl = tt;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    uint32_t y = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += y;
+  }
+  if (lane == 31) ws[w] = incl;
+  __syncthreads();
+  uint32_t wbase = 0;
+  for (int j = 0; j < w; j++) wbase += ws[j];
+  s_off[t] = wbase + incl - tt;
+  if (t == GP_SCAN_BLOCK - 1) s_off[GP_SCAN_BLOCK] = wbase + incl;
+  __syncthreads();
+  const uint32_t total = s_off[GP_SCAN_BLOCK];
+  const uint32_t base = block_excl[blockIdx.x];
+  for (uint32_t e = t; e < total; e += GP_SCAN_BLOCK) {
+    // largest j with s_off[j] <= e
+    int lo = 0, hi = GP_SCAN_BLOCK;
+#pragma unroll
+    for (int it = 0; it < 8; it++) {
+      const int mid = (lo + hi) >> 1;
+      if (s_off[mid] <= e) lo = mid; else hi = mid;
+    }
+    const uint32_t local = e - s_off[lo];
+    const uint32_t rw = s_rw[lo];
+    const uint32_t ty = s_ry[lo] + local / rw;
+    const uint32_t tx = s_rx[lo] + local % rw;
+    tkeys[base + e] = ty * grid_x + tx;
+    tvals[base + e] = s_g[lo];
+  }
+}
+
+__global__ void __launch_bounds__(256)
+gp_tile_ranges_kernel(const int* __restrict__ hdr, const uint32_t* __restrict__ tkeys, uint2* __restrict__ ranges) {
+  const int L = hdr[GP_HDR_NUM_SORTED];
+  for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < L; idx += gridDim.x * blockDim.x) {
+    const uint32_t cur = tkeys[idx];
+    if (idx == 0) {
+      ranges[cur].x = 0;
+    } else {
+      const uint32_t prev = tkeys[idx - 1];
+      if (cur != prev) {
+        ranges[prev].y = idx;
+        ranges[cur].x = idx;
+      }
+    }
+    if (idx == L - 1) ranges[cur].y = L;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// blending
+// ------------------------------------------------------------------------------------------------
+
+// One 16x16 tile per block; warp w owns an 8x4 pixel patch (lane = 8*row + col) so that the 32
+// pixels of a warp are spatially compact.  Batches of 256 Gaussians are staged in shared memory:
+// conic+opacity, centre+depth, colour and index (52 B each).  The per-pair arithmetic is written
+// with explicit round-to-nearest intrinsics in the exact sequence the reference build executes
+// (forward.cu:341-379 as contracted by nvcc), because median depth / tidx / n_contrib are discrete
+// picks that flip on a 1-ulp change.
+__global__ void __launch_bounds__(GP_TILE_PIX)
+gp_render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H,
+                     unsigned grid_x, const float4* __restrict__ xy_depth, const float4* __restrict__ conic_opacity,
+                     const float4* __restrict__ rgb4, const float* __restrict__ colors_precomp,
+                     const float* __restrict__ bg_color, const int* __restrict__ hdr, float* __restrict__ final_T,
+                     uint32_t* __restrict__ n_contrib, float* __restrict__ out_color, float* __restrict__ out_depth,
+                     int* __restrict__ out_tidx) {
+  __shared__ float4 s_co[GP_TILE_PIX];
+  __shared__ float4 s_xyd[GP_TILE_PIX];
+  __shared__ float4 s_rgb[GP_TILE_PIX];
+  __shared__ int s_id[GP_TILE_PIX];
+
+  if (hdr[GP_HDR_OVERFLOW]) return;
+  const int t = threadIdx.x, w = t >> 5, lane = t & 31;
+  const unsigned tile = blockIdx.x;
+  const unsigned tile_x = tile % grid_x, tile_y = tile / grid_x;
+  const unsigned px = tile_x * GP_TILE_X + (w & 1) * 8 + (lane & 7);
+  const unsigned py = tile_y * GP_TILE_Y + (w >> 1) * 4 + (lane >> 3);
+  const bool inside = px < (unsigned)W && py < (unsigned)H;
+  const unsigned pix_id = (unsigned)W * py + px;
+  const float pixfx = (float)px, pixfy = (float)py;
+
+  const uint2 range = ranges[tile];
+  const int rounds = ((range.y - range.x + GP_TILE_PIX - 1) / GP_TILE_PIX);
+  int toDo = range.y - range.x;
+  bool done = !inside;
+
+  float T = 1.0f;
+  uint32_t contributor = 0, last_contributor = 0;
+  float C0 = 0.f, C1 = 0.f, C2 = 0.f;
+  float Dm = 15.0f;  // median-depth sentinel of this fork (forward.cu:310)
+  int tid = -1;
+
+  for (int i = 0; i < rounds; i++, toDo -= GP_TILE_PIX) {
+    const int num_done = __syncthreads_count(done);
+    if (num_done == GP_TILE_PIX) break;
+    const int progress = i * GP_TILE_PIX + t;
+    if (range.x + progress < range.y) {
+      const int id = point_list[range.x + progress];
+      s_id[t] = id;
+      s_co[t] = __ldg(conic_opacity + id);
+      s_xyd[t] = __ldg(xy_depth + id);
+      if (colors_precomp != nullptr)
+        s_rgb[t] = make_float4(colors_precomp[3 * (size_t)id], colors_precomp[3 * (size_t)id + 1],
+                               colors_precomp[3 * (size_t)id + 2], 0.f);
+      else
+        s_rgb[t] = __ldg(rgb4 + id);
+    }
+    __syncthreads();
+    const int nb = min(GP_TILE_PIX, toDo);
+    for (int j = 0; !done && j < nb; j++) {
+      contributor++;
+      const float4 xyd = s_xyd[j];
+      const float4 co = s_co[j];
+      const float dx = xyd.x - pixfx;
+      const float dy = xyd.y - pixfy;
+      const float qa = __fmul_rn(co.x, dx);
+      const float qb = __fmul_rn(__fmul_rn(co.z, dy), dy);
+      const float qs = __fmaf_rn(qa, dx, qb);
+      const float qc = __fmul_rn(__fmul_rn(co.y, dx), dy);
+      const float power = __fmaf_rn(qs, -0.5f, -qc);
+      if (power > 0.0f) continue;
+      const float alpha = fminf(0.99f, __fmul_rn(co.w, expf(power)));
+      if (alpha < 1.0f / 255.0f) continue;
+      const float test_T = __fmul_rn(T, __fadd_rn(1.0f, -alpha));
+      if (test_T < 0.0001f) {
+        done = true;
+        continue;
+      }
+      const float4 col = s_rgb[j];
+      C0 = __fmaf_rn(T, __fmul_rn(alpha, col.x), C0);
+      C1 = __fmaf_rn(T, __fmul_rn(alpha, col.y), C1);
+      C2 = __fmaf_rn(T, __fmul_rn(alpha, col.z), C2);
+      if (T > 0.5f && test_T < 0.5f) {
+        Dm = xyd.z;
+        tid = s_id[j];
+      }
+      T = test_T;
+      last_contributor = contributor;
+    }
+  }
+  if (inside) {
+    final_T[pix_id] = T;
+    n_contrib[pix_id] = last_contributor;
+    const size_t hw = (size_t)H * W;
+    out_color[pix_id] = __fmaf_rn(bg_color[0], T, C0);
+    out_color[hw + pix_id] = __fmaf_rn(bg_color[1], T, C1);
+    out_color[2 * hw + pix_id] = __fmaf_rn(bg_color[2], T, C2);
+    out_depth[pix_id] = Dm;
+    out_tidx[pix_id] = tid;
+  }
+}
+
+__global__ void gp_check_frustum_kernel(int P, const float* __restrict__ means3D, const float* __restrict__ view,
+                                        uint8_t* __restrict__ present) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= P) return;
+  const V3 p = v3(means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]);
+  const V3 pv = xform4x3(p, view);
+  present[idx] = pv.z > 0.2f ? 1 : 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------
+
+extern "C" int gp_raster_sizes(int P, int width, int height, long long capacity, size_t* geom_bytes,
+                               size_t* binning_bytes, size_t* image_bytes) {
+  if (P < 0 || width < 0 || height < 0 || capacity < 0) return GP_ERR_BAD_ARG;
+  if (geom_bytes) *geom_bytes = gp_carve_geom(nullptr, P).bytes;
+  if (binning_bytes) *binning_bytes = gp_carve_binning(nullptr, capacity).bytes;
+  if (image_bytes) *image_bytes = gp_carve_image(nullptr, width, height).bytes;
+  return GP_OK;
+}
+
+extern "C" int gp_raster_preprocess(const gp_raster_cfg* cfg, const float* means3D, const float* shs,
+                                    const float* colors_precomp, const float* opacities, const float* scales,
+                                    const float* rotations, const float* cov3D_precomp, const float* viewmatrix,
+                                    const float* projmatrix, const float* campos, void* geom_ws, int* radii,
+                                    gp_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (!cfg || !geom_ws || !radii) return GP_ERR_BAD_ARG;
+  const int P = cfg->P;
+  if (P <= 0 || cfg->width <= 0 || cfg->height <= 0) return GP_ERR_BAD_ARG;
+  if ((shs == nullptr) == (colors_precomp == nullptr)) return GP_ERR_BAD_ARG;
+  const bool has_sr = scales != nullptr && rotations != nullptr;
+  if (has_sr == (cov3D_precomp != nullptr)) return GP_ERR_BAD_ARG;
+  if (shs && (cfg->sh_degree < 0 || cfg->sh_degree > 3 || cfg->sh_coeffs < (cfg->sh_degree + 1) * (cfg->sh_degree + 1)))
+    return GP_ERR_BAD_ARG;
+  GpGeom g = gp_carve_geom(geom_ws, P);
+  const int W = cfg->width, H = cfg->height;
+  const float focal_y = H / (2.0f * cfg->tanfovy);
+  const float focal_x = W / (2.0f * cfg->tanfovx);
+  const unsigned gx = (W + GP_TILE_X - 1) / GP_TILE_X, gy = (H + GP_TILE_Y - 1) / GP_TILE_Y;
+  gp_preprocess_kernel<<<(P + 255) / 256, 256, 0, stream>>>(
+      P, cfg->sh_degree, cfg->sh_coeffs, means3D, scales, cfg->scale_modifier, rotations, opacities, shs, cov3D_precomp,
+      colors_precomp, viewmatrix, projmatrix, campos, W, H, cfg->tanfovx, cfg->tanfovy, focal_x, focal_y,
+      cfg->prefiltered, gx, gy, g, radii);
+  GP_LAUNCH_CHECK();
+  // depth sort: P keys, all 32 bits; result lands back in buffer 0 (4 passes)
+  gp_radix_sort_pairs(g.dkeys, g.dvals, g.hdr + GP_HDR_NUM_POINTS, 0, 32, g.radix, stream);
+  GP_LAUNCH_CHECK();
+  const int nb = (P + GP_SCAN_BLOCK - 1) / GP_SCAN_BLOCK;
+  gp_block_sum_kernel<<<nb, GP_SCAN_BLOCK, 0, stream>>>(P, g.dvals[0], g.tiles_touched, g.block_sums);
+  GP_LAUNCH_CHECK();
+  // capacity is not known yet: the spine scan runs again (cheaply) in gp_raster_render with the real
+  // capacity; here it publishes R for callers that size the binning workspace exactly.
+  gp_spine_scan_kernel<<<1, 1024, 0, stream>>>(nb, g.block_sums, g.hdr, 0x7FFFFFFFll);
+  GP_LAUNCH_CHECK();
+  return GP_OK;
+}
+
+extern "C" int gp_raster_num_rendered(const void* geom_ws, gp_stream_t stream_, int* num_rendered) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (!geom_ws || !num_rendered) return GP_ERR_BAD_ARG;
+  GP_CUDA_TRY(cudaMemcpyAsync(num_rendered, (const int*)geom_ws + GP_HDR_NUM_RENDERED, sizeof(int),
+                              cudaMemcpyDeviceToHost, stream));
+  GP_CUDA_TRY(cudaStreamSynchronize(stream));
+  return GP_OK;
+}
+
+__global__ void gp_set_capacity_kernel(int* hdr, long long capacity) {
+  const long long R = hdr[GP_HDR_NUM_RENDERED];
+  const bool over = R > capacity || R >= 0x7FFFFFFFll;
+  hdr[GP_HDR_OVERFLOW] = over ? 1 : 0;
+  hdr[GP_HDR_NUM_SORTED] = over ? 0 : (int)R;
+}
+
+extern "C" int gp_raster_render(const gp_raster_cfg* cfg, const float* bg, const float* colors_precomp, void* geom_ws,
+                                void* binning_ws, long long capacity, void* image_ws, const int* radii,
+                                float* out_color, float* out_depth, int* out_tidx, gp_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (!cfg || !bg || !geom_ws || !binning_ws || !image_ws || !radii || !out_color || !out_depth || !out_tidx)
+    return GP_ERR_BAD_ARG;
+  const int P = cfg->P, W = cfg->width, H = cfg->height;
+  if (P <= 0 || W <= 0 || H <= 0 || capacity < 0) return GP_ERR_BAD_ARG;
+  GpGeom g = gp_carve_geom(geom_ws, P);
+  GpBinning b = gp_carve_binning(binning_ws, capacity);
+  GpImage im = gp_carve_image(image_ws, W, H);
+  const unsigned gx = (W + GP_TILE_X - 1) / GP_TILE_X, gy = (H + GP_TILE_Y - 1) / GP_TILE_Y;
+  const int nb = (P + GP_SCAN_BLOCK - 1) / GP_SCAN_BLOCK;
+
+  gp_set_capacity_kernel<<<1, 1, 0, stream>>>(g.hdr, capacity);
+  GP_LAUNCH_CHECK();
+  gp_duplicate_kernel<<<nb, GP_SCAN_BLOCK, 0, stream>>>(P, g.dvals[0], g.tiles_touched, g.xy_depth, radii, g.block_sums,
+                                                        g.hdr, gx, gy, b.tkeys[0], b.tvals[0]);
+  GP_LAUNCH_CHECK();
+  const int bits = gp_tile_bits(W, H);
+  const int sel = gp_radix_sort_pairs(b.tkeys, b.tvals, g.hdr + GP_HDR_NUM_SORTED, 0, bits, g.radix, stream);
+  GP_LAUNCH_CHECK();
+  GP_CUDA_TRY(cudaMemsetAsync(im.ranges, 0, (size_t)gx * gy * sizeof(uint2), stream));
+  gp_tile_ranges_kernel<<<148 * 4, 256, 0, stream>>>(g.hdr, b.tkeys[sel], im.ranges);
+  GP_LAUNCH_CHECK();
+  gp_render_fwd_kernel<<<gx * gy, GP_TILE_PIX, 0, stream>>>(im.ranges, b.tvals[sel], W, H, gx, g.xy_depth,
+                                                           g.conic_opacity, g.rgb, colors_precomp, bg, g.hdr,
+                                                           im.final_T, im.n_contrib, out_color, out_depth, out_tidx);
+  GP_LAUNCH_CHECK();
+  return GP_OK;
+}
+
+extern "C" int gp_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                               uint8_t* present, gp_stream_t stream_) {
+  (void)projmatrix;  // the reference computes the projection but only tests view-space z (auxiliary.h:154)
+  if (P < 0 || (P > 0 && (!means3D || !viewmatrix || !present))) return GP_ERR_BAD_ARG;
+  if (P == 0) return GP_OK;
+  gp_check_frustum_kernel<<<(P + 255) / 256, 256, 0, (cudaStream_t)stream_>>>(P, means3D, viewmatrix, present);
+  GP_LAUNCH_CHECK();
+  return GP_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// state export for parity tests
+// ------------------------------------------------------------------------------------------------
+
+__global__ void gp_export_geom_kernel(int P, GpGeom g, float* depths,
+                                      float* means2D, float* cov3D, float* conic_opacity, float* rgb,
+                                      uint32_t* tiles_touched, uint8_t* clamped) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= P) return;
+  const bool vis = g.tiles_touched[i] != 0;
+  const float4 xyd = vis ? g.xy_depth[i] : make_float4(0, 0, 0, 0);
+  const float4 co = vis ? g.conic_opacity[i] : make_float4(0, 0, 0, 0);
+  const float4 c = vis ? g.rgb[i] : make_float4(0, 0, 0, 0);
+  if (depths) depths[i] = xyd.z;
+  if (means2D) {
+    means2D[2 * i] = xyd.x;
+    means2D[2 * i + 1] = xyd.y;
+  }
+  if (cov3D)
+    for (int k = 0; k < 6; k++) cov3D[6 * (size_t)i + k] = g.cov3D[6 * (size_t)i + k];
+  if (conic_opacity) {
+    conic_opacity[4 * (size_t)i] = co.x;
+    conic_opacity[4 * (size_t)i + 1] = co.y;
+    conic_opacity[4 * (size_t)i + 2] = co.z;
+    conic_opacity[4 * (size_t)i + 3] = co.w;
+  }
+  if (rgb) {
+    rgb[3 * (size_t)i] = c.x;
+    rgb[3 * (size_t)i + 1] = c.y;
+    rgb[3 * (size_t)i + 2] = c.z;
+  }
+  if (tiles_touched) tiles_touched[i] = g.tiles_touched[i];
+  if (clamped) {
+    const unsigned cb = vis ? g.clamped[i] : 0;
+    clamped[3 * (size_t)i] = cb & 1;
+    clamped[3 * (size_t)i + 1] = (cb >> 1) & 1;
+    clamped[3 * (size_t)i + 2] = (cb >> 2) & 1;
+  }
+}
+
+__global__ void gp_export_binning_kernel(const int* __restrict__ hdr, const uint32_t* __restrict__ tkeys,
+                                         const uint32_t* __restrict__ tvals, const float4* __restrict__ xy_depth,
+                                         uint32_t* point_list, uint64_t* keys) {
+  const int L = hdr[GP_HDR_NUM_SORTED];
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < L; i += gridDim.x * blockDim.x) {
+    const uint32_t gidx = tvals[i];
+    if (point_list) point_list[i] = gidx;
+    if (keys) keys[i] = ((uint64_t)tkeys[i] << 32) | (uint64_t)__float_as_uint(xy_depth[gidx].z);
+  }
+}
+
+extern "C" int gp_raster_export_state(const gp_raster_cfg* cfg, const void* geom_ws, const void* image_ws,
+                                      float* depths, float* means2D, float* cov3D, float* conic_opacity, float* rgb,
+                                      uint32_t* tiles_touched, uint8_t* clamped, uint32_t* ranges, float* final_T,
+                                      uint32_t* n_contrib, gp_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (!cfg || !geom_ws) return GP_ERR_BAD_ARG;
+  const int P = cfg->P, W = cfg->width, H = cfg->height;
+  GpGeom g = gp_carve_geom(const_cast<void*>(geom_ws), P);
+  gp_export_geom_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, g, depths, means2D, cov3D, conic_opacity, rgb,
+                                                            tiles_touched, clamped);
+  GP_LAUNCH_CHECK();
+  if (image_ws) {
+    GpImage im = gp_carve_image(const_cast<void*>(image_ws), W, H);
+    const size_t npix = (size_t)W * H;
+    const size_t tiles = (size_t)((W + GP_TILE_X - 1) / GP_TILE_X) * ((H + GP_TILE_Y - 1) / GP_TILE_Y);
+    if (ranges) GP_CUDA_TRY(cudaMemcpyAsync(ranges, im.ranges, tiles * sizeof(uint2), cudaMemcpyDeviceToDevice, stream));
+    if (final_T) GP_CUDA_TRY(cudaMemcpyAsync(final_T, im.final_T, npix * 4, cudaMemcpyDeviceToDevice, stream));
+    if (n_contrib) GP_CUDA_TRY(cudaMemcpyAsync(n_contrib, im.n_contrib, npix * 4, cudaMemcpyDeviceToDevice, stream));
+  }
+  return GP_OK;
+}
+
+extern "C" int gp_raster_export_binning(const gp_raster_cfg* cfg, const void* geom_ws, const void* binning_ws,
+                                        long long capacity, uint32_t* point_list, uint64_t* point_list_keys,
+                                        gp_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (!cfg || !geom_ws || !binning_ws) return GP_ERR_BAD_ARG;
+  GpGeom g = gp_carve_geom(const_cast<void*>(geom_ws), cfg->P);
+  GpBinning b = gp_carve_binning(const_cast<void*>(binning_ws), capacity);
+  const int sel = gp_tile_sort_sel(cfg->width, cfg->height);
+  gp_export_binning_kernel<<<148 * 4, 256, 0, stream>>>(g.hdr, b.tkeys[sel], b.tvals[sel], g.xy_depth, point_list,
+                                                       point_list_keys);
+  GP_LAUNCH_CHECK();
+  return GP_OK;
+}

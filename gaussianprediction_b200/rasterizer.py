@@ -1,0 +1,254 @@
+"""Drop-in for the reference's ``diff_gaussian_rasterization`` package, backed by libgp_b200.so.
+
+Mirrors submodules/diff-gaussian-rasterization-w-depth/diff_gaussian_rasterization/__init__.py:
+``GaussianRasterizationSettings`` (:134-145), ``GaussianRasterizer`` (:147-196), the autograd
+function ``_RasterizeGaussians`` (:40-132) and ``rasterize_gaussians`` (:16-38): same names, argument
+order, outputs ``(color[3,H,W], radii[P] int32, depth[1,H,W], tidx[1,H,W] int32)``, gradient order and
+the same ``Exception`` when not exactly one of SHs/colours or scale+rotation/covariance is given.
+
+Two ways to size the tile-instance buffers:
+  * default ("exact"): one host read of the instance count R per frame, like the reference's own
+    ``cudaMemcpy`` of ``num_rendered`` (rasterizer_impl.cu:283-284);
+  * ``capacity=...`` on ``rasterize_gaussians``/``GaussianRasterizer``: no host round trip at all; if R
+    exceeds the capacity the frame is not rendered and ``last_overflow()`` reports it (used by the
+    frame pipelines in ``pipeline.py``, which own the retry policy).
+"""
+import ctypes
+from typing import NamedTuple, Optional
+
+import torch
+import torch.nn as nn
+
+from . import _lib
+from ._lib import RasterCfg, check, ptr
+
+
+class GaussianRasterizationSettings(NamedTuple):
+    image_height: int
+    image_width: int
+    tanfovx: float
+    tanfovy: float
+    bg: torch.Tensor
+    scale_modifier: float
+    viewmatrix: torch.Tensor
+    projmatrix: torch.Tensor
+    sh_degree: int
+    campos: torch.Tensor
+    prefiltered: bool
+
+
+def _f32c(t):
+    if t.dtype != torch.float32:
+        t = t.float()
+    return t.contiguous()
+
+
+def _opt(t):
+    """Empty tensors stand for 'not given' in the reference API (:173-183)."""
+    return None if t is None or t.numel() == 0 else _f32c(t)
+
+
+def workspace_sizes(P, W, H, capacity):
+    g, b, i = ctypes.c_size_t(), ctypes.c_size_t(), ctypes.c_size_t()
+    check(_lib.lib().gp_raster_sizes(P, W, H, int(capacity), ctypes.byref(g), ctypes.byref(b), ctypes.byref(i)),
+          "gp_raster_sizes")
+    return g.value, b.value, i.value
+
+
+def _make_cfg(P, raster_settings, sh):
+    M = 0 if sh is None else int(sh.shape[1])
+    return RasterCfg(P, int(raster_settings.image_width), int(raster_settings.image_height),
+                     int(raster_settings.sh_degree), M, float(raster_settings.tanfovx), float(raster_settings.tanfovy),
+                     float(raster_settings.scale_modifier), 1 if raster_settings.prefiltered else 0)
+
+
+class RasterState:
+    """What the backward needs from a forward (the reference keeps geom/binning/img byte tensors, :84)."""
+    __slots__ = ("cfg", "geom", "binning", "image", "radii", "capacity", "num_rendered")
+
+
+def raster_forward(means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, raster_settings,
+                   capacity: Optional[int] = None):
+    """Runs the two forward stages; returns (color, radii, depth, tidx, RasterState)."""
+    L = _lib.lib()
+    dev = means3D.device
+    if means3D.dim() != 2 or means3D.shape[1] != 3:
+        raise RuntimeError("means3D must have dimensions (num_points, 3)")  # reference rasterize_points.cu:56-58
+    if not means3D.is_cuda:
+        raise RuntimeError("gaussianprediction_b200 rasterizer needs CUDA tensors (there is no CPU path)")
+    P = int(means3D.shape[0])
+    H, W = int(raster_settings.image_height), int(raster_settings.image_width)
+    color = torch.empty((3, H, W), dtype=torch.float32, device=dev)
+    depth = torch.empty((1, H, W), dtype=torch.float32, device=dev)
+    tidx = torch.empty((1, H, W), dtype=torch.int32, device=dev)
+    radii = torch.empty((P,), dtype=torch.int32, device=dev)
+    st = RasterState()
+    if P == 0:  # reference returns its zero-filled outputs untouched (rasterize_points.cu:67-82)
+        color.zero_(); depth.zero_(); tidx.zero_()
+        st.cfg = None
+        st.num_rendered = 0
+        return color, radii, depth, tidx, st
+
+    means3D = _f32c(means3D)
+    sh, colors_precomp = _opt(sh), _opt(colors_precomp)
+    scales, rotations, cov3Ds_precomp = _opt(scales), _opt(rotations), _opt(cov3Ds_precomp)
+    opacities = _f32c(opacities)
+    bg = _f32c(raster_settings.bg)
+    view, proj, campos = _f32c(raster_settings.viewmatrix), _f32c(raster_settings.projmatrix), _f32c(raster_settings.campos)
+    cfg = _make_cfg(P, raster_settings, sh)
+    gbytes, _, ibytes = workspace_sizes(P, W, H, 0)
+    geom = torch.empty((gbytes,), dtype=torch.uint8, device=dev)
+    image = torch.empty((ibytes,), dtype=torch.uint8, device=dev)
+    stream = _lib.stream_ptr()
+    check(L.gp_raster_preprocess(ctypes.byref(cfg), ptr(means3D), ptr(sh), ptr(colors_precomp), ptr(opacities),
+                                 ptr(scales), ptr(rotations), ptr(cov3Ds_precomp), ptr(view), ptr(proj), ptr(campos),
+                                 ptr(geom), ptr(radii), stream), "gp_raster_preprocess")
+    if capacity is None:
+        n = ctypes.c_int(0)
+        check(L.gp_raster_num_rendered(ptr(geom), stream, ctypes.byref(n)), "gp_raster_num_rendered")
+        st.num_rendered = int(n.value)
+        capacity = max(int(n.value), 1)
+    else:
+        st.num_rendered = None  # still on the device: geom header word 0
+    _, bbytes, _ = workspace_sizes(P, W, H, capacity)
+    binning = torch.empty((bbytes,), dtype=torch.uint8, device=dev)
+    check(L.gp_raster_render(ctypes.byref(cfg), ptr(bg), ptr(colors_precomp), ptr(geom), ptr(binning), int(capacity),
+                             ptr(image), ptr(radii), ptr(color), ptr(depth), ptr(tidx), stream), "gp_raster_render")
+    st.cfg, st.geom, st.binning, st.image, st.radii, st.capacity = cfg, geom, binning, image, radii, int(capacity)
+    return color, radii, depth, tidx, st
+
+
+def raster_backward(st, grad_out_color, means3D, sh, colors_precomp, scales, rotations, cov3Ds_precomp,
+                    raster_settings):
+    """Returns (grad_means2D, grad_colors, grad_opacity, grad_means3D, grad_cov3D, grad_sh, grad_scales, grad_rots)."""
+    L = _lib.lib()
+    dev = means3D.device
+    P = int(means3D.shape[0])
+    sh, colors_precomp = _opt(sh), _opt(colors_precomp)
+    scales, rotations, cov3Ds_precomp = _opt(scales), _opt(rotations), _opt(cov3Ds_precomp)
+    M = 0 if sh is None else int(sh.shape[1])
+    f = dict(dtype=torch.float32, device=dev)
+    if P == 0:
+        z = lambda *s: torch.zeros(s, **f)
+        return z(0, 3), z(0, 3), z(0, 1), z(0, 3), z(0, 6), z(0, M, 3), z(0, 3), z(0, 4)
+    g_means2D = torch.empty((P, 3), **f)
+    g_opacity = torch.empty((P, 1), **f)
+    g_means3D = torch.empty((P, 3), **f)
+    g_colors = torch.empty((P, 3), **f) if colors_precomp is not None else None
+    g_sh = torch.empty((P, M, 3), **f) if sh is not None else None
+    g_scales = torch.empty((P, 3), **f) if scales is not None else None
+    g_rots = torch.empty((P, 4), **f) if scales is not None else None
+    g_cov3D = torch.empty((P, 6), **f) if cov3Ds_precomp is not None else None
+    ws = torch.empty((L.gp_raster_backward_ws_bytes(P),), dtype=torch.uint8, device=dev)
+    bg = _f32c(raster_settings.bg)
+    view, proj, campos = _f32c(raster_settings.viewmatrix), _f32c(raster_settings.projmatrix), _f32c(raster_settings.campos)
+    check(L.gp_raster_backward(ctypes.byref(st.cfg), ptr(bg), ptr(_f32c(means3D)), ptr(sh), ptr(colors_precomp),
+                               ptr(scales), ptr(rotations), ptr(cov3Ds_precomp), ptr(view), ptr(proj), ptr(campos),
+                               ptr(st.radii), ptr(st.geom), ptr(st.binning), st.capacity, ptr(st.image),
+                               ptr(_f32c(grad_out_color)), ptr(ws), ptr(g_means2D), ptr(g_colors), ptr(g_opacity),
+                               ptr(g_means3D), ptr(g_cov3D), ptr(g_sh), ptr(g_scales), ptr(g_rots),
+                               _lib.stream_ptr()), "gp_raster_backward")
+    return g_means2D, g_colors, g_opacity, g_means3D, g_cov3D, g_sh, g_scales, g_rots
+
+
+class _RasterizeGaussians(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
+                raster_settings, capacity=None):
+        color, radii, depth, tidx, st = raster_forward(means3D, sh, colors_precomp, opacities, scales, rotations,
+                                                       cov3Ds_precomp, raster_settings, capacity)
+        ctx.raster_settings = raster_settings
+        ctx.state = st
+        ctx.num_rendered = st.num_rendered
+        ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, sh)
+        ctx.mark_non_differentiable(radii, depth, tidx)  # the reference has no depth gradient (:88)
+        return color, radii, depth, tidx
+
+    @staticmethod
+    def backward(ctx, grad_out_color, _radii, _depth, _tidx):
+        colors_precomp, means3D, scales, rotations, cov3Ds_precomp, sh = ctx.saved_tensors
+        (g_means2D, g_colors, g_opacity, g_means3D, g_cov3D, g_sh, g_scales, g_rots) = raster_backward(
+            ctx.state, grad_out_color, means3D, sh, colors_precomp, scales, rotations, cov3Ds_precomp,
+            ctx.raster_settings)
+        # order of the reference's backward (:120-130)
+        return (g_means3D, g_means2D, g_sh, g_colors, g_opacity, g_scales, g_rots, g_cov3D, None, None)
+
+
+def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
+                        raster_settings, capacity=None):
+    return _RasterizeGaussians.apply(means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
+                                     cov3Ds_precomp, raster_settings, capacity)
+
+
+def mark_visible(positions, viewmatrix, projmatrix):
+    """Stand-in for ``_C.mark_visible`` (rasterize_points.cu:199-218): bool[P], view-space z > 0.2."""
+    P = int(positions.shape[0])
+    out = torch.zeros((P,), dtype=torch.uint8, device=positions.device)
+    if P:
+        check(_lib.lib().gp_mark_visible(P, ptr(_f32c(positions)), ptr(_f32c(viewmatrix)), ptr(_f32c(projmatrix)),
+                                         ptr(out), _lib.stream_ptr()), "gp_mark_visible")
+    return out.bool()
+
+
+class GaussianRasterizer(nn.Module):
+    def __init__(self, raster_settings, capacity=None):
+        super().__init__()
+        self.raster_settings = raster_settings
+        self.capacity = capacity
+
+    def markVisible(self, positions):
+        with torch.no_grad():
+            rs = self.raster_settings
+            return mark_visible(positions, rs.viewmatrix, rs.projmatrix)
+
+    def forward(self, means3D, means2D, opacities, shs=None, colors_precomp=None, scales=None, rotations=None,
+                cov3D_precomp=None):
+        raster_settings = self.raster_settings
+        if (shs is None and colors_precomp is None) or (shs is not None and colors_precomp is not None):
+            raise Exception('Please provide excatly one of either SHs or precomputed colors!')
+        if ((scales is None or rotations is None) and cov3D_precomp is None) or \
+                ((scales is not None or rotations is not None) and cov3D_precomp is not None):
+            raise Exception('Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!')
+        if shs is None:
+            shs = torch.Tensor([])
+        if colors_precomp is None:
+            colors_precomp = torch.Tensor([])
+        if scales is None:
+            scales = torch.Tensor([])
+        if rotations is None:
+            rotations = torch.Tensor([])
+        if cov3D_precomp is None:
+            cov3D_precomp = torch.Tensor([])
+        return rasterize_gaussians(means3D, means2D, shs, colors_precomp, opacities, scales, rotations, cov3D_precomp,
+                                   raster_settings, self.capacity)
+
+
+def export_state(st):
+    """Test/introspection: the internal forward state in the reference's array shapes (dict of torch tensors)."""
+    L = _lib.lib()
+    cfg = st.cfg
+    P, W, H = cfg.P, cfg.width, cfg.height
+    dev = st.geom.device
+    tiles = ((W + 15) // 16) * ((H + 15) // 16)
+    f = dict(dtype=torch.float32, device=dev)
+    o = dict(depths=torch.zeros(P, **f), means2D=torch.zeros(P, 2, **f), cov3D=torch.zeros(P, 6, **f),
+             conic_opacity=torch.zeros(P, 4, **f), rgb=torch.zeros(P, 3, **f),
+             tiles_touched=torch.zeros(P, dtype=torch.int32, device=dev),
+             clamped=torch.zeros(P, 3, dtype=torch.uint8, device=dev),
+             ranges=torch.zeros(tiles, 2, dtype=torch.int32, device=dev), final_T=torch.zeros(H * W, **f),
+             n_contrib=torch.zeros(H * W, dtype=torch.int32, device=dev))
+    stream = _lib.stream_ptr()
+    check(L.gp_raster_export_state(ctypes.byref(cfg), ptr(st.geom), ptr(st.image), ptr(o["depths"]), ptr(o["means2D"]),
+                                   ptr(o["cov3D"]), ptr(o["conic_opacity"]), ptr(o["rgb"]), ptr(o["tiles_touched"]),
+                                   ptr(o["clamped"]), ptr(o["ranges"]), ptr(o["final_T"]), ptr(o["n_contrib"]), stream),
+          "gp_raster_export_state")
+    hdr = st.geom[:16].view(torch.int32).cpu()
+    R = int(hdr[_lib.HDR_NUM_SORTED])
+    o["num_rendered"] = int(hdr[_lib.HDR_NUM_RENDERED])
+    o["overflow"] = int(hdr[_lib.HDR_OVERFLOW])
+    o["point_list"] = torch.zeros(max(R, 1), dtype=torch.int32, device=dev)
+    o["point_list_keys"] = torch.zeros(max(R, 1), dtype=torch.int64, device=dev)
+    check(L.gp_raster_export_binning(ctypes.byref(cfg), ptr(st.geom), ptr(st.binning), st.capacity, ptr(o["point_list"]),
+                                     ptr(o["point_list_keys"]), stream), "gp_raster_export_binning")
+    o["point_list"], o["point_list_keys"] = o["point_list"][:R], o["point_list_keys"][:R]
+    return o

@@ -1,0 +1,119 @@
+/*
+ * gp_b200.h -- C ABI of libgp_b200.so, the B200 (sm_100a) hot path of GaussianPrediction:
+ * keypoint-driven deformation followed by depth-aware tile rasterization, forward + backward.
+ *
+ * The reference has no C ABI for this path: it is reached through pybind11 torch-extension
+ * modules.  Each entry point below names the reference binding it stands in for (paths relative to
+ * the reference root).  Conventions: plain device pointers and sizes, caller-owned outputs and
+ * workspaces, an explicit cudaStream_t, no exceptions; the return value is 0 on success, a positive
+ * cudaError_t, or a negative GP_ERR_* code.  Nothing here allocates device memory unless stated.
+ */
+#ifndef GP_B200_H
+#define GP_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct CUstream_st* gp_stream_t; /* == cudaStream_t */
+
+#define GP_OK 0
+#define GP_ERR_BAD_ARG (-1)
+#define GP_ERR_WORKSPACE_TOO_SMALL (-2)
+#define GP_ERR_UNSUPPORTED (-3)
+#define GP_ERR_LIMIT (-4)
+
+/* Version of this ABI (bumped on any signature change). */
+int gp_abi_version(void);
+/* Static text for an error code returned by any entry point. */
+const char* gp_error_string(int code);
+
+/* ------------------------------------------------------------------------------------------------
+ * Rasterizer.  Stands in for diff_gaussian_rasterization._C.rasterize_gaussians /
+ * rasterize_gaussians_backward / mark_visible
+ * (submodules/diff-gaussian-rasterization-w-depth/ext.cpp:15-19, rasterize_points.cu:35-218,
+ *  cuda_rasterizer/rasterizer_impl.cu:141-439).
+ * ---------------------------------------------------------------------------------------------- */
+
+typedef struct {
+  int P;              /* number of Gaussians */
+  int width, height;  /* image size in pixels */
+  int sh_degree;      /* active SH degree D (0..3) */
+  int sh_coeffs;      /* M: coefficients stored per Gaussian (0 when colours are precomputed) */
+  float tanfovx, tanfovy;
+  float scale_modifier;
+  int prefiltered;
+} gp_raster_cfg;
+
+/* Header words at the start of the geometry workspace (int32 each); readable by the host. */
+#define GP_HDR_NUM_RENDERED 0 /* R = sum of tiles touched (may exceed the binning capacity) */
+#define GP_HDR_OVERFLOW 1     /* 1 if R > capacity: the frame was NOT rendered, retry with more */
+#define GP_HDR_NUM_POINTS 2   /* P */
+#define GP_HDR_NUM_SORTED 3   /* min(R, capacity) */
+#define GP_HDR_WORDS 64
+
+/* Workspace sizes in bytes for P Gaussians, a width x height image and room for `capacity` tile
+ * instances.  (The reference grows three torch byte tensors through callbacks instead,
+ * rasterize_points.cu:27-33,72-79.) */
+int gp_raster_sizes(int P, int width, int height, long long capacity, size_t* geom_bytes, size_t* binning_bytes,
+                    size_t* image_bytes);
+
+/* Stage 1 of the forward: per-Gaussian preprocess, depth sort and tile-count scan.
+ * Reference: FORWARD::preprocess + cub InclusiveSum, rasterizer_impl.cu:250-280.
+ * Writes radii[P] and the geometry workspace; leaves R in header word GP_HDR_NUM_RENDERED.
+ * shs / colors_precomp: exactly one non-NULL.  scales+rotations / cov3D_precomp: exactly one set. */
+int gp_raster_preprocess(const gp_raster_cfg* cfg, const float* means3D, const float* shs, const float* colors_precomp,
+                         const float* opacities, const float* scales, const float* rotations,
+                         const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
+                         const float* campos, void* geom_ws, int* radii, gp_stream_t stream);
+
+/* Blocking read of R after gp_raster_preprocess (the reference's own D2H sync, rasterizer_impl.cu:283-284). */
+int gp_raster_num_rendered(const void* geom_ws, gp_stream_t stream, int* num_rendered);
+
+/* Stage 2 of the forward: duplicate-with-keys, tile sort, tile ranges, alpha/median-depth blending.
+ * Reference: rasterizer_impl.cu:286-339, forward.cu:261-398.  `capacity` is the number of tile
+ * instances binning_ws was sized for; if R > capacity nothing is rendered and GP_HDR_OVERFLOW is set
+ * (no host sync is needed to launch this stage). */
+int gp_raster_render(const gp_raster_cfg* cfg, const float* bg, const float* colors_precomp, void* geom_ws,
+                     void* binning_ws, long long capacity, void* image_ws, const int* radii, float* out_color,
+                     float* out_depth, int* out_tidx, gp_stream_t stream);
+
+/* Backward of the two stages above.  Reference: Rasterizer::backward, rasterizer_impl.cu:346-439,
+ * backward.cu:144-557.  `capacity` must be the value given to gp_raster_render for this frame.  All
+ * dL_* outputs are fully written (no pre-zeroing required); 12 floats per Gaussian of scratch are
+ * taken from `grad_ws` (size: gp_raster_backward_ws_bytes).  Outputs that do not apply may be NULL:
+ * dL_dsh (colours precomputed), dL_dcolors (SH given), dL_dscales/dL_drots (cov3D precomputed),
+ * dL_dcov3D (scales/rotations given). */
+size_t gp_raster_backward_ws_bytes(int P);
+int gp_raster_backward(const gp_raster_cfg* cfg, const float* bg, const float* means3D, const float* shs,
+                       const float* colors_precomp, const float* scales, const float* rotations,
+                       const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
+                       const float* campos, const int* radii, const void* geom_ws, const void* binning_ws,
+                       long long capacity, const void* image_ws, const float* dL_dpix, void* grad_ws, float* dL_dmeans2D /*[P,3]*/,
+                       float* dL_dcolors /*[P,3]*/, float* dL_dopacity /*[P,1]*/, float* dL_dmeans3D /*[P,3]*/,
+                       float* dL_dcov3D /*[P,6]*/, float* dL_dsh /*[P,M,3]*/, float* dL_dscales /*[P,3]*/,
+                       float* dL_drots /*[P,4]*/, gp_stream_t stream);
+
+/* present[i] = (view-space z > 0.2).  Reference: checkFrustum, rasterizer_impl.cu:54-66,141-153. */
+int gp_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix, uint8_t* present,
+                    gp_stream_t stream);
+
+/* Test/introspection: unpack the internal state into the reference's array shapes so parity tests can
+ * compare them bit for bit with the reference's geom/binning/image buffers.  Any output may be NULL. */
+int gp_raster_export_state(const gp_raster_cfg* cfg, const void* geom_ws, const void* image_ws, float* depths /*[P]*/,
+                           float* means2D /*[P,2]*/, float* cov3D /*[P,6]*/, float* conic_opacity /*[P,4]*/,
+                           float* rgb /*[P,3]*/, uint32_t* tiles_touched /*[P]*/, uint8_t* clamped /*[P,3]*/,
+                           uint32_t* ranges /*[tiles,2]*/, float* final_T /*[H*W]*/, uint32_t* n_contrib /*[H*W]*/,
+                           gp_stream_t stream);
+/* Sorted instance list: point_list[R] (Gaussian index) and the reference's 64-bit keys
+ * (tile << 32 | depth bits, rasterizer_impl.cu:101-104) rebuilt from tile id and depth. */
+int gp_raster_export_binning(const gp_raster_cfg* cfg, const void* geom_ws, const void* binning_ws, long long capacity,
+                             uint32_t* point_list, uint64_t* point_list_keys, gp_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GP_B200_H */
