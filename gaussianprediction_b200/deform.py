@@ -1,0 +1,302 @@
+"""Keypoint-driven deformation: the ``GaussianModel.forward`` call of the reference, on B200 kernels.
+
+Mirrors scene/gaussian_model.py:231-304 (control flow), :110-125 (``get_nearest_mask``), :214-229
+(``fill_nearest``), :180-189 (``get_motion_delta``), :314-315 (``get_rotation_``) and
+scene/deformable_field.py:63-127 (``positional_encoding``, ``Deformable_Field``).  The K-nearest-keypoint
+search and the blend (softmax, gather, weighted sums, quaternion compose, activations) run in
+libgp_b200.so; the small keypoint MLP stays a torch/cuBLAS call as BASELINE.json's north_star says.
+
+The hash-grid blend-weight network (tinycudann, scene/gaussian_model.py:370-392) is not available
+(un-vendored third-party code): ``weights_model`` is any callable [N,3] -> [N,2K];
+the default is a learnable logits table.
+"""
+import ctypes
+from types import SimpleNamespace
+
+import torch
+import torch.nn as nn
+
+from . import _lib
+from ._lib import check, ptr
+
+
+# ------------------------------------------------------------------------------------------------ small torch pieces
+
+def positional_encoding(positions, freqs):
+    """[sin(2^k x), cos(2^k x)] interleaved per input dim (scene/deformable_field.py:63-72, ori=False)."""
+    freq_bands = (2 ** torch.arange(freqs).float()).to(positions.device)
+    pts = (positions[..., None] * freq_bands).reshape(positions.shape[:-1] + (freqs * positions.shape[-1],))
+    pts = torch.stack([torch.sin(pts), torch.cos(pts)], dim=-1).reshape(pts.shape[:-1] + (pts.shape[-1] * 2,))
+    return pts
+
+
+class DeformableField(nn.Module):
+    """d x (Linear + ReLU) then Linear: the non-split ``Deformable_Field`` (scene/deformable_field.py:74-127).
+    Sub-module names match the reference so a reference ``state_dict`` loads unchanged."""
+
+    def __init__(self, input_dim, output_dim=7, d=4, w=256):
+        super().__init__()
+        layers = []
+        for i in range(d):
+            layers.append(nn.Linear(input_dim if i == 0 else w, w))
+            layers.append(nn.ReLU())
+        self.mlp = nn.Sequential(*layers)
+        self.feature_to_deformation = nn.Sequential(nn.Linear(w, output_dim))
+
+    def forward(self, x):
+        return self.feature_to_deformation(self.mlp(x))
+
+
+def quat_mul(q1, q2):
+    """(w,x,y,z) product with the operand order of utils/camera_utils.py:158-170 (torch; used off the hot path)."""
+    w = q2[..., 0] * q1[..., 0] - q2[..., 1] * q1[..., 1] - q2[..., 2] * q1[..., 2] - q2[..., 3] * q1[..., 3]
+    x = q2[..., 1] * q1[..., 0] + q2[..., 0] * q1[..., 1] + q2[..., 3] * q1[..., 2] - q2[..., 2] * q1[..., 3]
+    y = q2[..., 2] * q1[..., 0] - q2[..., 3] * q1[..., 1] + q2[..., 0] * q1[..., 2] + q2[..., 1] * q1[..., 3]
+    z = q2[..., 3] * q1[..., 0] + q2[..., 2] * q1[..., 1] - q2[..., 1] * q1[..., 2] + q2[..., 0] * q1[..., 3]
+    return torch.stack([w, x, y, z], dim=-1)
+
+
+# ------------------------------------------------------------------------------------------------ kernels
+
+def _c(t):
+    t = t.detach()
+    if t.dtype != torch.float32:
+        t = t.float()
+    return t.contiguous()
+
+
+def _need_cuda(*ts):
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise TypeError("for now only cuda version is supported")  # same error as frnn.py:295-296
+
+
+@torch.no_grad()
+def knn_keypoints(xyz, motion_feature, kp_xyz, kp_feature, K, knn_type="hybird", feature_amplify=5.0,
+                  return_dists=False, idx32_only=False):
+    """``get_nearest_mask`` (scene/gaussian_model.py:110-125) without the torch.cat and the FRNN grid set-up.
+    Returns (idx64 [N,K] or None, idx32 [N,K], dists or None)."""
+    _need_cuda(xyz, kp_xyz)
+    N, Kp = int(xyz.shape[0]), int(kp_xyz.shape[0])
+    dev = xyz.device
+    if knn_type == "3D":
+        F, r, mf, kf = 0, 1e3, None, None
+    elif knn_type == "hybird":
+        F, r, mf, kf = int(motion_feature.shape[1]), 1e8, _c(motion_feature), _c(kp_feature)
+    else:
+        raise ValueError('knn_type should be "3D" or "hybird"')
+    idx32 = torch.empty((N, K), dtype=torch.int32, device=dev)
+    idx64 = None if idx32_only else torch.empty((N, K), dtype=torch.int64, device=dev)
+    dists = torch.empty((N, K), dtype=torch.float32, device=dev) if return_dists else None
+    check(_lib.lib().gp_knn_keypoints(N, Kp, F, int(K), float(r), float(feature_amplify), ptr(_c(xyz)), ptr(mf),
+                                      ptr(_c(kp_xyz)), ptr(kf), ptr(idx64), ptr(idx32), ptr(dists), _lib.stream_ptr()),
+          "gp_knn_keypoints")
+    return idx64, idx32, dists
+
+
+class _KeypointBlend(torch.autograd.Function):
+    """xyz_t, q_t, s_t, o_t = blend(logits, idx, kp deltas, canonical params) with the sparse kernels."""
+
+    @staticmethod
+    def forward(ctx, logits, idx32, kp_dxyz, kp_dq, xyz, rot, scaling, opacity):
+        L = _lib.lib()
+        N, K, Kp = int(xyz.shape[0]), int(idx32.shape[1]), int(kp_dxyz.shape[0])
+        dev = xyz.device
+        f = dict(dtype=torch.float32, device=dev)
+        logits_c, kpx, kpq, xyz_c, rot_c = _c(logits), _c(kp_dxyz), _c(kp_dq), _c(xyz), _c(rot)
+        sc_c, op_c = _c(scaling), _c(opacity)
+        xyz_t, q_t = torch.empty((N, 3), **f), torch.empty((N, 4), **f)
+        s_t, o_t = torch.empty((N, 3), **f), torch.empty((N, 1), **f)
+        check(L.gp_blend_forward(N, Kp, K, ptr(logits_c), ptr(idx32), None, ptr(kpx), ptr(kpq), ptr(xyz_c), ptr(rot_c),
+                                 ptr(sc_c), ptr(op_c), ptr(xyz_t), ptr(q_t), ptr(s_t), ptr(o_t), _lib.stream_ptr()),
+              "gp_blend_forward")
+        ctx.save_for_backward(logits_c, idx32, kpx, kpq, rot_c, s_t, o_t)
+        ctx.dims = (N, Kp, K)
+        return xyz_t, q_t, s_t, o_t
+
+    @staticmethod
+    def backward(ctx, g_xyz_t, g_q_t, g_s_t, g_o_t):
+        L = _lib.lib()
+        logits, idx32, kpx, kpq, rot, s_t, o_t = ctx.saved_tensors
+        N, Kp, K = ctx.dims
+        f = dict(dtype=torch.float32, device=logits.device)
+        need = ctx.needs_input_grad
+        g_logits = torch.empty((N, 2 * K), **f) if need[0] else None
+        g_kpx, g_kpq = torch.empty((Kp, 3), **f), torch.empty((Kp, 4), **f)
+        g_xyz = torch.empty((N, 3), **f) if need[4] else None
+        g_rot = torch.empty((N, 4), **f) if need[5] else None
+        g_sc = torch.empty((N, 3), **f) if need[6] else None
+        g_op = torch.empty((N, 1), **f) if need[7] else None
+        gc = lambda g: None if g is None else _c(g)
+        check(L.gp_blend_backward(N, Kp, K, ptr(logits), ptr(idx32), None, ptr(kpx), ptr(kpq), ptr(rot), ptr(s_t), ptr(o_t),
+                                  ptr(gc(g_xyz_t)), ptr(gc(g_q_t)), ptr(gc(g_s_t)), ptr(gc(g_o_t)), ptr(g_logits),
+                                  ptr(g_xyz), ptr(g_rot), ptr(g_sc), ptr(g_op), ptr(g_kpx), ptr(g_kpq),
+                                  _lib.stream_ptr()), "gp_blend_backward")
+        return g_logits, None, (g_kpx if need[2] else None), (g_kpq if need[3] else None), g_xyz, g_rot, g_sc, g_op
+
+
+def keypoint_blend(logits, idx32, kp_delta_xyz, kp_delta_q, xyz, rot, scaling, opacity):
+    return _KeypointBlend.apply(logits, idx32, kp_delta_xyz, kp_delta_q, xyz, rot, scaling, opacity)
+
+
+@torch.no_grad()
+def dense_weights(logits, idx32, Kp, want_sum=False):
+    """Dense ``weights_xyz, weights_r`` [N,Kp] as ``fill_nearest`` builds them (scene/gaussian_model.py:214-229)."""
+    N, K = int(idx32.shape[0]), int(idx32.shape[1])
+    f = dict(dtype=torch.float32, device=logits.device)
+    wx, wr = torch.empty((N, Kp), **f), torch.empty((N, Kp), **f)
+    ws = torch.empty((N, Kp), **f) if want_sum else None
+    check(_lib.lib().gp_blend_dense_weights(N, Kp, K, ptr(_c(logits)), ptr(idx32), None, ptr(wx), ptr(wr), ptr(ws),
+                                            _lib.stream_ptr()), "gp_blend_dense_weights")
+    return (wx, wr, ws) if want_sum else (wx, wr)
+
+
+# ------------------------------------------------------------------------------------------------ the model call
+
+def default_args(**over):
+    """The hot-path sizing flags with the reference's defaults (options/gaussian_option.py:41-90,
+    arguments/__init__.py:97-98)."""
+    a = dict(nearest_num=6, knn_type="hybird", feature_amplify=5.0, norm_rotation=False, step_opacity=False,
+             step_opacity_iteration=5000, opacity_type="implicit", beta=0.1, jointly_iteration=1000,
+             second_stage_iteration=30000, xyz_noise_iteration=10000, feature_dim=32, d=4, w=256, max_points=100,
+             xyz_freq=10, time_freq=6)
+    a.update(over)
+    return SimpleNamespace(**a)
+
+
+class LogitsTable(nn.Module):
+    """Stand-in for the absent tinycudann network: one learnable row of 2K logits per Gaussian."""
+
+    def __init__(self, logits):
+        super().__init__()
+        self.logits = nn.Parameter(logits.clone())
+
+    def forward(self, xyz):
+        return self.logits
+
+
+class KeypointDeformation(nn.Module):
+    """Holds the tensors ``GaussianModel.forward`` reads and reproduces its call:
+    ``xyz, q, s, opacity = model(t, iteration)`` (+ dense weights with ``return_weights=True``).
+    Side-effect attributes other reference code reads are kept: ``kpts_xyz_motion``, ``kpts_rotation_motion``,
+    ``nearest_mask``, ``lifecycle_opacity``, ``weights_sum`` (lazy: built on first access)."""
+
+    def __init__(self, args, xyz, rotation, scaling, opacity, motion_feature, super_gaussians, super_gaussians_feature,
+                 weights_model=None, logits=None):
+        super().__init__()
+        self.args = args
+        P = nn.Parameter
+        self._xyz, self._rotation, self._scaling, self._opacity = P(xyz), P(rotation), P(scaling), P(opacity)
+        self.motion_feature = P(motion_feature)
+        self.super_gaussians, self.super_gaussians_feature = P(super_gaussians), P(super_gaussians_feature)
+        self.time_input_dim = 2 * args.time_freq
+        self.xyz_input_dim = 6 * args.xyz_freq
+        delta_dim = 8 if args.step_opacity else 7
+        if args.step_opacity:  # step-opacity threshold (scene/gaussian_model.py:358-361)
+            self.opacity_thres = P(-2 * torch.ones_like(opacity))
+        self.df_model = DeformableField(self.time_input_dim + self.xyz_input_dim + args.feature_dim, delta_dim, args.d, args.w)
+        if weights_model is None:
+            if logits is None:
+                logits = torch.zeros(xyz.shape[0], 2 * args.nearest_num)
+            weights_model = LogitsTable(logits)
+        self.weights_model = weights_model
+        self.second_stage_iter = args.second_stage_iteration
+        self.beta = args.beta
+        self.nearest_mask = None
+        self.lifecycle_opacity = None
+        self._idx32 = None
+        self._last_logits = None
+        self.knn_cache = False  # eval: the search inputs are parameters only, so it can be hoisted out of the frame loop
+
+    # getters with the reference's names (scene/gaussian_model.py:138-162)
+    @property
+    def get_xyz(self):
+        return self._xyz
+
+    @property
+    def get_scaling(self):
+        return torch.exp(self._scaling)
+
+    @property
+    def get_rotation(self):
+        return torch.nn.functional.normalize(self._rotation)
+
+    @property
+    def get_opacity(self):
+        return torch.sigmoid(self._opacity)
+
+    @property
+    def weights_sum(self):
+        if self._idx32 is None:
+            return None
+        return dense_weights(self._last_logits, self._idx32, self.super_gaussians.shape[0], want_sum=True)[2]
+
+    def get_nearest_mask(self, keepshape=False):
+        idx64, idx32, _ = knn_keypoints(self._xyz, self.motion_feature, self.super_gaussians, self.super_gaussians_feature,
+                                        self.args.nearest_num, self.args.knn_type, self.args.feature_amplify)
+        self._idx32 = idx32
+        self.nearest_mask = idx64 if keepshape else idx64.view([-1])
+
+    def get_motion_delta(self, xyz_embed, motion_feature, t):
+        t = t.repeat((motion_feature.shape[0], 1))
+        delta = self.df_model(torch.cat([motion_feature, xyz_embed, t], dim=-1))
+        delta_o = delta[..., 7:8] if self.args.step_opacity else None
+        return delta[..., 0:3], delta[..., 3:7], delta_o
+
+    def forward(self, t, iteration, return_weights=False):
+        args = self.args
+        t_input = t
+        t = positional_encoding(t, self.time_input_dim // 2).unsqueeze(0)
+        if torch.is_tensor(iteration):
+            iteration = iteration.item()
+        if iteration < args.jointly_iteration:  # warm-up: canonical parameters (:237-238)
+            return self.get_xyz, self.get_rotation, self.get_scaling, self.get_opacity
+        normalize = torch.nn.functional.normalize
+        if iteration <= self.second_stage_iter:
+            # first stage (:240-244): per-Gaussian MLP, torch ops (not the keypoint hot path)
+            noise = torch.randn_like(self._xyz) * 0.1 * (1 - min(1, iteration / args.xyz_noise_iteration))
+            xyz_embed = positional_encoding(self._xyz.detach() + noise, int(self.xyz_input_dim / 6))
+            delta_xyz, delta_q, _ = self.get_motion_delta(xyz_embed, self.motion_feature, t)
+            if args.norm_rotation:
+                delta_q = normalize(delta_q)
+            self.kpts_xyz_motion, self.kpts_rotation_motion = delta_xyz, delta_q
+            xyz = self._xyz + delta_xyz
+            q = normalize(quat_mul(normalize(delta_q), self._rotation))
+            s, opacity = self.get_scaling, self.get_opacity
+        else:
+            # second stage (:251-273, :285-287): keypoints
+            factor = 0.1 * (1 - min(1, (iteration - self.second_stage_iter) / args.xyz_noise_iteration))
+            noise = torch.randn_like(self.super_gaussians) * factor  # RNG consumed even when the factor is 0 (:254)
+            xyz_embed = positional_encoding(self.super_gaussians + noise, int(self.xyz_input_dim / 6))
+            logits = self.weights_model(self._xyz.detach())
+            if not (self.knn_cache and self._idx32 is not None):
+                self.get_nearest_mask(keepshape=True)
+            self._last_logits = logits.detach()
+            delta_xyz, delta_q, _ = self.get_motion_delta(xyz_embed, self.super_gaussians_feature, t)
+            if args.norm_rotation:
+                delta_q = normalize(delta_q)
+            self.kpts_xyz_motion, self.kpts_rotation_motion = delta_xyz, delta_q
+            xyz, q, s, opacity = keypoint_blend(logits, self._idx32, delta_xyz, delta_q, self._xyz, self._rotation,
+                                                self._scaling, self._opacity)
+        self.lifecycle_opacity = None
+        base_opacity = opacity
+        if args.step_opacity and iteration > args.step_opacity_iteration:  # (:291-301) per-Gaussian MLP, torch ops
+            xyz_embed = positional_encoding(self._xyz, int(self.xyz_input_dim / 6))
+            _, _, delta_o = self.get_motion_delta(xyz_embed, self.motion_feature, t)
+            if args.opacity_type == "explicit":
+                opacity = base_opacity * (1 / (1 + torch.exp(-(t_input - self.opacity_thres) / self.beta)))
+            else:
+                opacity = base_opacity * (1 / (1 + torch.exp(-delta_o / self.beta)))
+            self.lifecycle_opacity = opacity
+        if return_weights and iteration > self.second_stage_iter:
+            wx, wr = dense_weights(self._last_logits, self._idx32, self.super_gaussians.shape[0])
+            return xyz, q, s, base_opacity, wx, wr
+        return xyz, q, s, opacity
+
+    @torch.no_grad()
+    def extrapolate(self, kpts_i, kpts_rotation_i):
+        """One frame of ``render_kpts`` (eval.py:140-141): xyz + W_x (kpts_i - kpts), quaternion compose with
+        W_r kpts_rotation_i, using the cached indices / logits of the last forward (no dense matrices)."""
+        xyz_t, q_t, _, _ = keypoint_blend(self._last_logits, self._idx32, kpts_i - self.super_gaussians, kpts_rotation_i,
+                                          self._xyz, self._rotation, self._scaling, self._opacity)
+        return xyz_t, q_t

@@ -113,6 +113,59 @@ int gp_raster_export_state(const gp_raster_cfg* cfg, const void* geom_ws, const 
 int gp_raster_export_binning(const gp_raster_cfg* cfg, const void* geom_ws, const void* binning_ws, long long capacity,
                              uint32_t* point_list, uint64_t* point_list_keys, gp_stream_t stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * Keypoint search.  Stands in for frnn.frnn_grid_points as get_nearest_mask calls it
+ * (scene/gaussian_model.py:110-125 -> submodules/FRNN/frnn/frnn.py:210-347 -> frnn._C.insert_points_cuda,
+ * prefix_sum_cuda, counting_sort_cuda, find_nbrs_cuda; frnn/csrc/ext.cpp:10-27).
+ * ---------------------------------------------------------------------------------------------- */
+
+/* K nearest points2 (within radius r) of every points1 row, both row-major [n, D].  idxs int64 [N,K] and
+ * dists [N,K] (squared), ascending, padded with -1 like the reference (find_nbrs.cu:621-622).  K <= 32. */
+int gp_knn_points(int N, int Kp, int D, int K, float r, const float* points1, const float* points2, long long* idxs,
+                  float* dists, gp_stream_t stream);
+
+/* Same search on the un-concatenated model tensors: query = [xyz | motion_feature * feature_amplify]
+ * (the torch.cat of scene/gaussian_model.py:115-116 is folded into the kernel; F = 0 selects the "3D" mode of
+ * :112-113).  Either index output may be NULL. */
+int gp_knn_keypoints(int N, int Kp, int F, int K, float r, float feature_amplify, const float* xyz,
+                     const float* motion_feature, const float* kp_xyz, const float* kp_feature, long long* idx64,
+                     int* idx32, float* dists, gp_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Keypoint blending.  Stands in for the torch ops of GaussianModel.forward's keypoint stage
+ * (scene/gaussian_model.py:214-229 fill_nearest, :272-273 dense products, :285-287, :304, :314-315;
+ * quat_mul utils/camera_utils.py:158-170) and of render_kpts (eval.py:140-141).
+ * ---------------------------------------------------------------------------------------------- */
+
+/* logits [N,2K] (translation weights then rotation weights, softmax-ed inside), idx (int32 or int64, [N,K]),
+ * per-keypoint deltas [Kp,3] / [Kp,4], canonical xyz [N,3], raw rotation [N,4], log-scale [N,3], opacity
+ * logit [N,1].  Outputs xyz_t [N,3], q_t [N,4] (normalised), s_t [N,3] = exp, o_t [N,1] = sigmoid (the last
+ * two optional).  K <= 16, Kp <= 3200. */
+int gp_blend_forward(int N, int Kp, int K, const float* logits, const int* idx32, const long long* idx64,
+                     const float* kp_delta_xyz, const float* kp_delta_q, const float* xyz, const float* rot,
+                     const float* scaling, const float* opacity, float* xyz_t, float* q_t, float* s_t, float* o_t,
+                     gp_stream_t stream);
+
+/* Backward of gp_blend_forward (what torch autograd computes through the reference's dense ops).
+ * g_kp_delta_* are zeroed here and accumulated; other outputs are written; any g_* input may be NULL (= 0). */
+int gp_blend_backward(int N, int Kp, int K, const float* logits, const int* idx32, const long long* idx64,
+                      const float* kp_delta_xyz, const float* kp_delta_q, const float* rot, const float* s_t,
+                      const float* o_t, const float* g_xyz_t, const float* g_q_t, const float* g_s_t,
+                      const float* g_o_t, float* g_logits, float* g_xyz, float* g_rot, float* g_scaling,
+                      float* g_opacity, float* g_kp_delta_xyz, float* g_kp_delta_q, gp_stream_t stream);
+
+/* Dense [N,Kp] weight matrices for API parity: weights_xyz / weights_r (return_weights=True,
+ * scene/gaussian_model.py:302-303) and weights_sum (:263).  Any output may be NULL. */
+int gp_blend_dense_weights(int N, int Kp, int K, const float* logits, const int* idx32, const long long* idx64,
+                           float* w_xyz, float* w_r, float* w_sum, gp_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Initial scale estimate.  Stands in for simple_knn._C.distCUDA2 (submodules/simple-knn/ext.cpp:15-17,
+ * spatial.cu:15-26, simple_knn.cu:185-221): mean of the 3 smallest squared distances to other points.
+ * ---------------------------------------------------------------------------------------------- */
+size_t gp_dist2_ws_bytes(int P);
+int gp_dist2_knn3(int P, const float* points /*[P,3]*/, float* mean_dist2 /*[P]*/, void* ws, gp_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

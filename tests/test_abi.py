@@ -1,0 +1,79 @@
+"""CPU-side checks of the drop-in boundary: the shared library loads and exports exactly what include/gp_b200.h
+declares, the ctypes table matches the header, and argument errors are reported without touching a GPU."""
+import ctypes
+import os
+import re
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def header_functions():
+    text = open(os.path.join(ROOT, "include", "gp_b200.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    names = re.findall(r"\b(gp_[a-z0-9_]+)\s*\(", text)
+    return sorted(set(names))
+
+
+def test_header_symbols_exported(gplib):
+    from gaussianprediction_b200 import _lib
+    names = header_functions()
+    assert len(names) >= 15
+    for n in names:
+        assert hasattr(gplib, n), f"{n} declared in include/gp_b200.h but not exported by libgp_b200.so"
+        assert n in _lib.SIGNATURES, f"{n} has no ctypes signature in _lib.SIGNATURES"
+    for n in _lib.SIGNATURES:
+        assert n in names, f"{n} bound in _lib.py but not declared in the header"
+
+
+def test_version_and_error_strings(gplib):
+    assert gplib.gp_abi_version() == 1
+    assert b"bad argument" in gplib.gp_error_string(-1)
+    assert b"limit" in gplib.gp_error_string(-4)
+    assert gplib.gp_error_string(0) == b"ok"
+
+
+def test_sizes_and_argument_errors_without_gpu(gplib):
+    g, b, i = ctypes.c_size_t(), ctypes.c_size_t(), ctypes.c_size_t()
+    assert gplib.gp_raster_sizes(1000, 640, 480, 50000, ctypes.byref(g), ctypes.byref(b), ctypes.byref(i)) == 0
+    assert g.value > 1000 * 100 and b.value >= 50000 * 16 and i.value >= 640 * 480 * 8
+    assert gplib.gp_raster_sizes(-1, 640, 480, 0, None, None, None) == -1
+    assert gplib.gp_knn_points(10, 5, 3, 64, 1.0, None, None, None, None, None) != 0      # K > 32 / NULL pointers
+    assert gplib.gp_raster_preprocess(None, *([None] * 13)) == -1
+    assert gplib.gp_dist2_ws_bytes(10) > 0 and gplib.gp_raster_backward_ws_bytes(10) >= 480
+
+
+def test_missing_library_fails_loudly(monkeypatch, tmp_path):
+    from gaussianprediction_b200 import _lib
+    monkeypatch.setattr(_lib, "_lib", None)
+    monkeypatch.setattr(_lib, "LIB_PATH", str(tmp_path / "nope.so"))
+    with pytest.raises(_lib.GpError):
+        _lib.lib()
+
+
+def test_cpu_tensors_are_rejected(gplib):
+    import torch
+    from gaussianprediction_b200 import GaussianRasterizer, frnn
+    from gaussianprediction_b200.simple_knn import distCUDA2
+    from helpers import raster_case, settings_of
+    case = raster_case(N=50, W=32, H=32)
+    with pytest.raises(RuntimeError):
+        GaussianRasterizer(settings_of(case))(case["means3D"], torch.zeros(50, 3), case["opacities"], shs=case["shs"],
+                                              scales=case["scales"], rotations=case["rotations"])
+    with pytest.raises(TypeError):
+        frnn.frnn_grid_points(torch.zeros(1, 4, 3), torch.zeros(1, 4, 3), K=2, r=1.0)
+    with pytest.raises(RuntimeError):
+        distCUDA2(torch.zeros(4, 3))
+
+
+def test_dropin_import_names():
+    import gaussianprediction_b200 as g
+    g.install_dropin()
+    import diff_gaussian_rasterization as dgr
+    import frnn
+    from simple_knn._C import distCUDA2
+    assert dgr.GaussianRasterizer is g.GaussianRasterizer and callable(frnn.frnn_grid_points) and callable(distCUDA2)
+    assert dgr.GaussianRasterizationSettings._fields == (
+        "image_height", "image_width", "tanfovx", "tanfovy", "bg", "scale_modifier", "viewmatrix", "projmatrix",
+        "sh_degree", "campos", "prefiltered")

@@ -1,0 +1,191 @@
+"""GPU parity of the deformation stage (kNN, blend fwd/bwd, distCUDA2, the model call) through the C ABI.
+
+  kNN      : bit-exact indices AND squared distances vs the reference FRNN CUDA path (oracle/_ref/ref_frnn.so) on
+             tie-free inputs (SURVEY.md §8c tie policy: min relative gap among the K+1 nearest >= 1e-6), and vs the
+             FMA-ordered CPU oracle; golden vectors from tests/golden/knn_gpu.npz.
+  blend    : forward <= 1e-5 max-abs, gradients <= 1e-3 relative vs the dense torch formulation of the oracle
+             (scatter + [N,Kp] matmul, autograd).
+  distCUDA2: bit-exact vs the reference simple-knn build and the O(P^2) oracle.
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from helpers import count_diff, rel_err, to_np
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def scene(N=20000, Kp=512, seed=2024, amplify=0.5):
+    from gaussianprediction_b200 import synthetic as syn
+    gs = syn.make_gaussians(N, seed=seed)
+    kp, kf = syn.make_keypoints(gs, Kp=Kp, seed=seed + 1)
+    logits = syn.make_logits(N, 6, seed=seed + 2)
+    return gs, kp, kf, logits
+
+
+@pytest.mark.parametrize("N,Kp", [(700, 64), (20000, 512), (5000, 37)])
+@pytest.mark.parametrize("mode", ["hybird", "3D"])
+def test_knn_bit_exact_vs_reference(gplib, N, Kp, mode):
+    from gaussianprediction_b200.deform import knn_keypoints
+    from oracle import deform_oracle as do
+    from oracle import ref_cuda
+    gs, kp, kf, _ = scene(N, Kp, seed=5)
+    amplify = 0.5
+    p1, p2 = do.hybrid_points(gs.xyz, gs.motion_feature, kp, kf, amplify)
+    if mode == "3D":
+        p1, p2 = gs.xyz, kp
+    gap = do.knn_min_rel_gap(p1.numpy(), p2.numpy(), 6)
+    assert gap >= 1e-6, f"input has near-ties (gap {gap}); regenerate"
+    idx64, idx32, dists = knn_keypoints(gs.xyz.cuda(), gs.motion_feature.cuda(), kp.cuda(), kf.cuda(), 6, mode, amplify,
+                                        return_dists=True)
+    od, oi = do.knn(p1.numpy(), p2.numpy(), 6, r=1e8 if mode == "hybird" else 1e3, fma=True)
+    assert count_diff(idx64, oi) == 0 and count_diff(idx32, oi.astype(np.int32)) == 0
+    assert np.abs(to_np(dists) - od).max() <= 1e-6 * max(od.max(), 1.0)
+    if ref_cuda.available("ref_frnn") and ref_cuda.available("ref_prefix_sum"):
+        rd, ri = ref_cuda.frnn_grid_points(p1[None].cuda().contiguous(), p2[None].cuda().contiguous(), 6,
+                                           1e8 if mode == "hybird" else 1e3)
+        assert count_diff(idx64, ri[0]) == 0, "indices differ from the reference CUDA kNN"
+        assert count_diff(dists, rd[0]) == 0, "squared distances are not bit-identical to the reference CUDA kNN"
+
+
+def test_knn_golden_and_frnn_api(gplib):
+    from gaussianprediction_b200 import frnn
+    g = np.load(os.path.join(GOLD, "knn_gpu.npz")) if os.path.exists(os.path.join(GOLD, "knn_gpu.npz")) else None
+    c = np.load(os.path.join(GOLD, "knn_cpu.npz"))
+    p1, p2 = torch.tensor(c["p1"]).cuda(), torch.tensor(c["p2"]).cuda()
+    dists, idxs, nn, grid = frnn.frnn_grid_points(p1[None], p2[None], K=6, r=1e8, return_nn=True)
+    assert idxs.dtype == torch.int64 and idxs.shape == (1, 700, 6) and nn.shape == (1, 700, 6, 35) and grid is None
+    assert count_diff(idxs[0], c["i35"]) == 0                       # the reference's CPU brute force
+    assert np.abs(to_np(dists[0]) - c["d35"]).max() <= 1e-5
+    if g is not None:
+        assert count_diff(idxs[0], g["i35"]) == 0 and count_diff(dists[0], g["d35"]) == 0   # reference CUDA, bit-exact
+        d3, i3, _, _ = frnn.frnn_grid_points(p1[None, :, :3].contiguous(), p2[None, :, :3].contiguous(), K=6, r=1e3)
+        assert count_diff(i3[0], g["i3"]) == 0 and count_diff(d3[0], g["d3"]) == 0
+    # generic-D path (D = 7), radius that excludes most points, K > number of references
+    q, r = torch.randn(1, 300, 7, device="cuda"), torch.randn(1, 5, 7, device="cuda")
+    d, i, _, _ = frnn.frnn_grid_points(q, r, K=8, r=2.0)
+    from oracle import deform_oracle as do
+    od, oi = do.knn(to_np(q[0]), to_np(r[0]), 8, r=2.0, fma=True)
+    assert count_diff(i[0], oi) == 0 and (to_np(i[0])[:, 5:] == -1).all()
+    with pytest.raises(ValueError):
+        frnn.frnn_grid_points(q, r[:, :, :3], K=2, r=1.0)
+    with pytest.raises(TypeError):
+        frnn.frnn_grid_points(q.cpu(), r.cpu(), K=2, r=1.0)
+
+
+def test_knn_ties_break_by_index(gplib):
+    from gaussianprediction_b200 import frnn
+    r = torch.zeros(1, 8, 3, device="cuda")          # eight identical reference points: all distances tie
+    q = torch.ones(1, 4, 3, device="cuda")
+    _, i, _, _ = frnn.frnn_grid_points(q, r, K=3, r=10.0)
+    assert (to_np(i[0]) == np.array([0, 1, 2])).all()
+
+
+def _dense_reference(gs, kp, kf, logits, idx64, kp_dxyz, kp_dq, dev):
+    from oracle import deform_oracle as do
+    leaf = dict(logits=logits, kp_dxyz=kp_dxyz, kp_dq=kp_dq, xyz=gs.xyz, rot=gs.rotation, sc=gs.scaling, op=gs.opacity)
+    leaf = {k: v.clone().to(dev).requires_grad_(True) for k, v in leaf.items()}
+    K, Kp = idx64.shape[1], kp.shape[0]
+    wx, wr = do.fill_nearest(leaf["logits"], idx64.to(dev), Kp, K)
+    normalize = torch.nn.functional.normalize
+    dq = wr @ leaf["kp_dq"]
+    dx = wx @ leaf["kp_dxyz"]
+    xyz_t = leaf["xyz"] + dx
+    q_t = normalize(do.quat_mul(normalize(dq), leaf["rot"]))
+    return leaf, (xyz_t, q_t, torch.exp(leaf["sc"]), torch.sigmoid(leaf["op"]))
+
+
+@pytest.mark.parametrize("N,Kp", [(3000, 100), (20000, 512)])
+def test_blend_forward_backward_vs_dense_torch(gplib, N, Kp):
+    from gaussianprediction_b200.deform import dense_weights, keypoint_blend, knn_keypoints
+    from oracle import deform_oracle as do
+    gs, kp, kf, logits = scene(N, Kp, seed=8)
+    g = torch.Generator().manual_seed(3)
+    kp_dxyz = 0.2 * torch.randn(Kp, 3, generator=g)
+    kp_dq = torch.nn.functional.normalize(torch.randn(Kp, 4, generator=g))
+    idx64, idx32, _ = knn_keypoints(gs.xyz.cuda(), gs.motion_feature.cuda(), kp.cuda(), kf.cuda(), 6, "hybird", 0.5)
+    mine_leaf = dict(logits=logits, kp_dxyz=kp_dxyz, kp_dq=kp_dq, xyz=gs.xyz, rot=gs.rotation, sc=gs.scaling, op=gs.opacity)
+    mine_leaf = {k: v.clone().cuda().requires_grad_(True) for k, v in mine_leaf.items()}
+    outs = keypoint_blend(mine_leaf["logits"], idx32, mine_leaf["kp_dxyz"], mine_leaf["kp_dq"], mine_leaf["xyz"],
+                          mine_leaf["rot"], mine_leaf["sc"], mine_leaf["op"])
+    ref_leaf, ref_outs = _dense_reference(gs, kp, kf, logits, idx64.cpu(), kp_dxyz, kp_dq, "cpu")
+    for a, b, name in zip(outs, ref_outs, ("xyz_t", "q_t", "s_t", "o_t")):
+        assert float((a.cpu() - b).abs().max()) <= 1e-5, name
+    gens = [torch.randn(o.shape, generator=g) for o in ref_outs]
+    sum((o * w.cuda()).sum() for o, w in zip(outs, gens)).backward()
+    sum((o * w).sum() for o, w in zip(ref_outs, gens)).backward()
+    for k in mine_leaf:
+        assert rel_err(mine_leaf[k].grad, ref_leaf[k].grad) <= 1e-3, k
+    # dense weights for API parity (return_weights=True)
+    wx, wr = dense_weights(mine_leaf["logits"].detach(), idx32, Kp)
+    ox, orr = do.fill_nearest(logits, idx64.cpu(), Kp, 6)
+    assert float((wx.cpu() - ox).abs().max()) <= 1e-6 and float((wr.cpu() - orr).abs().max()) <= 1e-6
+
+
+def test_dist2_bit_exact(gplib):
+    from gaussianprediction_b200.simple_knn import distCUDA2
+    from oracle import deform_oracle as do
+    from oracle import ref_cuda
+    gs, *_ = scene(3000, 8, seed=11)
+    pts = gs.xyz[:3000].contiguous()
+    mine = distCUDA2(pts.cuda())
+    assert count_diff(mine, do.dist2_knn3(pts.numpy())) == 0
+    gpath = os.path.join(GOLD, "dist2.npz")
+    if os.path.exists(gpath):
+        g = np.load(gpath)
+        assert count_diff(distCUDA2(torch.tensor(g["points"]).cuda()), g["dist2"]) == 0
+    if ref_cuda.available("ref_sknn"):
+        for n, seed, shape in [(50000, 12, "dnerf"), (200000, 13, "hyper"), (5, 14, "dnerf"), (1000, 15, "dnerf")]:
+            from gaussianprediction_b200 import synthetic as syn
+            p = syn.make_gaussians(n, seed=seed, shape=shape).xyz.cuda()
+            if n == 1000:
+                p = torch.cat([p, p[:100]], 0).contiguous()      # duplicated points -> zero distances
+            assert count_diff(distCUDA2(p), ref_cuda.dist_cuda2(p)) == 0, (n, shape)
+
+
+def test_model_call_matches_oracle_and_render_runs(gplib):
+    from gaussianprediction_b200 import synthetic as syn
+    from gaussianprediction_b200.deform import KeypointDeformation, default_args
+    from gaussianprediction_b200.renderer import SceneModel, render
+    from oracle import deform_oracle as do
+    N, Kp = 6000, 128
+    gs, kp, kf, logits = scene(N, Kp, seed=21)
+    args = default_args(feature_amplify=0.5, norm_rotation=True, second_stage_iteration=100, jointly_iteration=10,
+                        xyz_noise_iteration=50)
+    torch.manual_seed(0)
+    model = KeypointDeformation(args, gs.xyz, gs.rotation, gs.scaling, gs.opacity, gs.motion_feature, kp, kf, logits=logits).cuda()
+    t = torch.tensor([0.37], device="cuda")
+    it = 1000    # past second_stage + noise window: deterministic
+    xyz_t, q_t, s_t, o_t, wx, wr = model(t, it, return_weights=True)
+    assert wx.shape == (N, Kp) and model.nearest_mask.shape == (N, 6) and model.nearest_mask.dtype == torch.int64
+    assert model.kpts_xyz_motion.shape == (Kp, 3) and model.kpts_rotation_motion.shape == (Kp, 4)
+    sd = {k: v.detach().cpu() for k, v in model.df_model.state_dict().items()}
+    o = do.keypoint_forward(t.cpu(), gs.xyz, gs.rotation, gs.scaling, gs.opacity, kp, kf, logits, model.nearest_mask.cpu(),
+                            sd, norm_rotation=True)
+    for a, b, name in zip((xyz_t, q_t, s_t, o_t), o[:4], ("xyz", "q", "s", "o")):
+        assert float((a.detach().cpu() - b).abs().max()) <= 2e-5, name
+    # warm-up stage returns canonical parameters
+    c = model(t, 0)
+    assert float((c[0] - model.get_xyz).abs().max()) == 0 and float((c[1] - model.get_rotation).abs().max()) == 0
+    # extrapolation frame (eval.py:140-141)
+    kpts, krot = syn.keypoint_trajectory(kp, frames=4)
+    xe, qe = model.extrapolate(kpts[2].cuda(), krot[2].cuda())
+    xo, qo = do.extrapolate_frame(gs.xyz, gs.rotation, wx.cpu(), wr.cpu(), kpts[2], kp, krot[2])
+    assert float((xe.cpu() - xo).abs().max()) <= 2e-5 and float((qe.cpu() - qo).abs().max()) <= 2e-5
+    # full render(): deformation -> rasterizer, forward + backward through both
+    cam = syn.make_camera(160, 112)
+    for k in ("world_view_transform", "full_proj_transform", "camera_center"):
+        setattr(cam, k, getattr(cam, k).cuda())
+    pc = SceneModel(model, gs.features_dc, gs.features_rest).cuda()
+    pkg = render(cam, pc, None, torch.zeros(3, device="cuda"), time=t, it=it)
+    assert pkg["render"].shape == (3, 112, 160) and pkg["depth"].shape == (1, 112, 160)
+    pkg["render"].square().mean().backward()
+    for name, p in pc.named_parameters():
+        if name.endswith("motion_feature"):
+            continue            # only feeds the (non-differentiable) search
+        assert p.grad is not None and torch.isfinite(p.grad).all(), name
+    assert float(model.super_gaussians.grad.abs().sum()) > 0 and float(model.weights_model.logits.grad.abs().sum()) > 0
