@@ -75,12 +75,17 @@ def knn(points1, points2, K, r=1e8, fma=True):
     return d_sorted, idx
 
 
-def knn_min_rel_gap(points1, points2, K):
-    """Smallest relative gap between consecutive entries among the K+1 nearest distances of any query: the tie
-    policy of SURVEY.md §8c rejects scenes where this is < 1e-6."""
+def knn_rel_gaps(points1, points2, K):
+    """Per query: the smallest relative gap between consecutive entries among its K+1 nearest distances.  The tie
+    policy of SURVEY.md §8c excludes queries where this is < 1e-6 (exact ties are broken nondeterministically by
+    the reference, and an FMA-vs-no-FMA ulp can swap near-ties)."""
     d, _ = knn(points1, points2, min(K + 1, points2.shape[0]), fma=False)
     gap = (d[:, 1:] - d[:, :-1]) / np.maximum(d[:, 1:], 1e-30)
-    return float(gap.min())
+    return gap.min(axis=1)
+
+
+def knn_min_rel_gap(points1, points2, K):
+    return float(knn_rel_gaps(points1, points2, K).min())
 
 
 def hybrid_points(xyz, motion_feature, kp_xyz, kp_feature, feature_amplify):
