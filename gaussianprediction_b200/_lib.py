@@ -31,6 +31,9 @@ _P = c_void_p  # every device pointer crosses the ABI as a plain address
 SIGNATURES = {
     "gp_abi_version": (c_int, []),
     "gp_error_string": (c_char_p, [c_int]),
+    "gp_launch_count": (c_longlong, []),
+    "gp_profile_enable": (c_int, [c_int]),
+    "gp_profile_report": (c_int, [ctypes.c_char_p, c_size_t]),
     "gp_raster_sizes": (c_int, [c_int, c_int, c_int, c_longlong, POINTER(c_size_t), POINTER(c_size_t), POINTER(c_size_t)]),
     "gp_raster_preprocess": (c_int, [POINTER(RasterCfg)] + [_P] * 10 + [_P, _P, _P]),
     "gp_raster_num_rendered": (c_int, [_P, _P, POINTER(c_int)]),

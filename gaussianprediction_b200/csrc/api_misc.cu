@@ -16,3 +16,77 @@ extern "C" const char* gp_error_string(int code) {
   if (code > 0) return cudaGetErrorString((cudaError_t)code);
   return "gp_b200: unknown error";
 }
+
+// ------------------------------------------------------------------------------------------------
+// launch counter + per-kernel event timing
+// ------------------------------------------------------------------------------------------------
+#include <string.h>
+#include <stdio.h>
+#include <atomic>
+#include <mutex>
+#include <vector>
+#include <string>
+#include <map>
+#include "common.cuh"
+
+namespace {
+std::atomic<long long> g_launches{0};
+bool g_prof_on = false;
+std::mutex g_prof_mu;
+struct ProfRec { const char* name; cudaEvent_t a, b; };
+std::vector<ProfRec> g_recs;
+std::vector<cudaEvent_t> g_pool;
+thread_local cudaEvent_t t_open_b = nullptr;
+
+cudaEvent_t prof_event() {
+  if (!g_pool.empty()) { cudaEvent_t e = g_pool.back(); g_pool.pop_back(); return e; }
+  cudaEvent_t e; cudaEventCreate(&e); return e;
+}
+}  // namespace
+
+void gp_prof_begin(const char* name, cudaStream_t stream) {
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  if (!g_prof_on) return;
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  ProfRec r{name, prof_event(), prof_event()};
+  cudaEventRecord(r.a, stream);
+  t_open_b = r.b;
+  g_recs.push_back(r);
+}
+void gp_prof_end(cudaStream_t stream) {
+  if (!g_prof_on || !t_open_b) return;
+  cudaEventRecord(t_open_b, stream);
+  t_open_b = nullptr;
+}
+
+extern "C" long long gp_launch_count(void) { return g_launches.load(); }
+
+extern "C" int gp_profile_enable(int on) {
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  for (auto& r : g_recs) { g_pool.push_back(r.a); g_pool.push_back(r.b); }
+  g_recs.clear();
+  g_prof_on = on != 0;
+  return GP_OK;
+}
+
+extern "C" int gp_profile_report(char* buf, size_t buf_bytes) {
+  if (!buf || buf_bytes == 0) return GP_ERR_BAD_ARG;
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  std::map<std::string, std::pair<long long, double>> agg;
+  for (auto& r : g_recs) {
+    if (cudaEventSynchronize(r.b) != cudaSuccess) continue;
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, r.a, r.b) != cudaSuccess) continue;
+    auto& e = agg[r.name];
+    e.first += 1;
+    e.second += ms;
+  }
+  size_t off = 0;
+  buf[0] = 0;
+  for (auto& kv : agg) {
+    int n = snprintf(buf + off, buf_bytes - off, "%s %lld %.6f\n", kv.first.c_str(), kv.second.first, kv.second.second);
+    if (n < 0 || (size_t)n >= buf_bytes - off) return GP_ERR_WORKSPACE_TOO_SMALL;
+    off += (size_t)n;
+  }
+  return GP_OK;
+}

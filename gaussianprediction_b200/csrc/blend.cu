@@ -274,8 +274,8 @@ extern "C" int gp_blend_forward(int N, int Kp, int K, const float* logits, const
   const size_t smem = (size_t)Kp * 8 * 4;
   if (smem > 48 * 1024)
     GP_CUDA_TRY(cudaFuncSetAttribute(gp_blend_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  gp_blend_fwd_kernel<<<(N + GP_BLEND_THREADS - 1) / GP_BLEND_THREADS, GP_BLEND_THREADS, smem, (cudaStream_t)stream_>>>(
-      N, Kp, K, logits, idx32, idx64, kp_delta_xyz, kp_delta_q, xyz, rot, scaling, opacity, xyz_t, q_t, s_t, o_t);
+  GP_KERNEL("gp_blend_fwd_kernel", (cudaStream_t)stream_, gp_blend_fwd_kernel<<<(N + GP_BLEND_THREADS - 1) / GP_BLEND_THREADS, GP_BLEND_THREADS, smem, (cudaStream_t)stream_>>>(
+      N, Kp, K, logits, idx32, idx64, kp_delta_xyz, kp_delta_q, xyz, rot, scaling, opacity, xyz_t, q_t, s_t, o_t));
   GP_LAUNCH_CHECK();
   return GP_OK;
 }
@@ -297,9 +297,9 @@ extern "C" int gp_blend_backward(int N, int Kp, int K, const float* logits, cons
   const size_t smem = (size_t)Kp * 16 * 4;
   if (smem > 48 * 1024)
     GP_CUDA_TRY(cudaFuncSetAttribute(gp_blend_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  gp_blend_bwd_kernel<<<(N + GP_BLEND_THREADS - 1) / GP_BLEND_THREADS, GP_BLEND_THREADS, smem, stream>>>(
+  GP_KERNEL("gp_blend_bwd_kernel", stream, gp_blend_bwd_kernel<<<(N + GP_BLEND_THREADS - 1) / GP_BLEND_THREADS, GP_BLEND_THREADS, smem, stream>>>(
       N, Kp, K, logits, idx32, idx64, kp_delta_xyz, kp_delta_q, rot, s_t, o_t, g_xyz_t, g_q_t, g_s_t, g_o_t, g_logits,
-      g_xyz, g_rot, g_scaling, g_opacity, g_kp_delta_xyz, g_kp_delta_q);
+      g_xyz, g_rot, g_scaling, g_opacity, g_kp_delta_xyz, g_kp_delta_q));
   GP_LAUNCH_CHECK();
   return GP_OK;
 }
@@ -316,8 +316,8 @@ extern "C" int gp_blend_dense_weights(int N, int Kp, int K, const float* logits,
   if (w_xyz) GP_CUDA_TRY(cudaMemsetAsync(w_xyz, 0, bytes, stream));
   if (w_r) GP_CUDA_TRY(cudaMemsetAsync(w_r, 0, bytes, stream));
   if (w_sum) GP_CUDA_TRY(cudaMemsetAsync(w_sum, 0, bytes, stream));
-  gp_dense_weights_kernel<<<(N + GP_BLEND_THREADS - 1) / GP_BLEND_THREADS, GP_BLEND_THREADS, 0, stream>>>(
-      N, Kp, K, logits, idx32, idx64, w_xyz, w_r, w_sum);
+  GP_KERNEL("gp_dense_weights_kernel", stream, gp_dense_weights_kernel<<<(N + GP_BLEND_THREADS - 1) / GP_BLEND_THREADS, GP_BLEND_THREADS, 0, stream>>>(
+      N, Kp, K, logits, idx32, idx64, w_xyz, w_r, w_sum));
   GP_LAUNCH_CHECK();
   return GP_OK;
 }

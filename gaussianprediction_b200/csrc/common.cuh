@@ -40,6 +40,17 @@ struct GpCarver {
   __host__ size_t used() const { return gp_align_up(off, 256); }
 };
 
+// Launch accounting and optional per-kernel timing (api_misc.cu).  GP_KERNEL(name, stream, launch) counts the
+// launch and, when profiling is enabled, brackets it with CUDA events on the launching stream.
+void gp_prof_begin(const char* name, cudaStream_t stream);
+void gp_prof_end(cudaStream_t stream);
+#define GP_KERNEL(name, stream, ...) \
+  do {                               \
+    gp_prof_begin(name, stream);     \
+    __VA_ARGS__;                     \
+    gp_prof_end(stream);             \
+  } while (0)
+
 #ifdef __CUDACC__
 __device__ __forceinline__ unsigned gp_lanemask_lt() {
   unsigned m;

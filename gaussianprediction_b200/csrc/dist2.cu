@@ -294,16 +294,16 @@ extern "C" int gp_dist2_knn3(int P, const float* points, float* mean_dist2, void
   if (!points || !mean_dist2 || !ws) return GP_ERR_BAD_ARG;
   GpDist2Ws w = gp_carve_dist2(ws, P);
   const int grid = 148 * 4;
-  gp_d2_init_kernel<<<1, 32, 0, stream>>>(w);
-  gp_d2_bbox_kernel<<<grid, 256, 0, stream>>>(P, points, w);
-  gp_d2_grid_kernel<<<1, 32, 0, stream>>>(P, w);
-  gp_d2_zero_kernel<<<grid, 256, 0, stream>>>(w);
-  gp_d2_count_kernel<<<grid, 256, 0, stream>>>(P, points, w);
-  gp_d2_scan1_kernel<<<grid, 1024, 0, stream>>>(w);
-  gp_d2_scan2_kernel<<<1, 1024, 0, stream>>>(w);
-  gp_d2_scan3_kernel<<<grid, 1024, 0, stream>>>(w);
-  gp_d2_scatter_kernel<<<grid, 256, 0, stream>>>(P, points, w);
-  gp_d2_query_kernel<<<(P + 127) / 128, 128, 0, stream>>>(P, w, mean_dist2);
+  GP_KERNEL("gp_d2_init_kernel", stream, gp_d2_init_kernel<<<1, 32, 0, stream>>>(w));
+  GP_KERNEL("gp_d2_bbox_kernel", stream, gp_d2_bbox_kernel<<<grid, 256, 0, stream>>>(P, points, w));
+  GP_KERNEL("gp_d2_grid_kernel", stream, gp_d2_grid_kernel<<<1, 32, 0, stream>>>(P, w));
+  GP_KERNEL("gp_d2_zero_kernel", stream, gp_d2_zero_kernel<<<grid, 256, 0, stream>>>(w));
+  GP_KERNEL("gp_d2_count_kernel", stream, gp_d2_count_kernel<<<grid, 256, 0, stream>>>(P, points, w));
+  GP_KERNEL("gp_d2_scan1_kernel", stream, gp_d2_scan1_kernel<<<grid, 1024, 0, stream>>>(w));
+  GP_KERNEL("gp_d2_scan2_kernel", stream, gp_d2_scan2_kernel<<<1, 1024, 0, stream>>>(w));
+  GP_KERNEL("gp_d2_scan3_kernel", stream, gp_d2_scan3_kernel<<<grid, 1024, 0, stream>>>(w));
+  GP_KERNEL("gp_d2_scatter_kernel", stream, gp_d2_scatter_kernel<<<grid, 256, 0, stream>>>(P, points, w));
+  GP_KERNEL("gp_d2_query_kernel", stream, gp_d2_query_kernel<<<(P + 127) / 128, 128, 0, stream>>>(P, w, mean_dist2));
   GP_LAUNCH_CHECK();
   return GP_OK;
 }

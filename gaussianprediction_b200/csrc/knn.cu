@@ -165,8 +165,8 @@ static int launch_knn(int N, int Kp, int Drt, int K, const float* q_points, cons
   const size_t smem = (size_t)kp_chunk * DP * 4;
   auto kern = gp_knn_kernel<D, KMAX>;
   if (smem > 48 * 1024) GP_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  kern<<<(N + GP_KNN_THREADS - 1) / GP_KNN_THREADS, GP_KNN_THREADS, smem, stream>>>(
-      N, Kp, Drt, K, q_points, q_feat, r_points, r_feat, F, amplify, r2, kp_chunk, idx64, idx32, dists);
+  GP_KERNEL("gp_knn_kernel", stream, kern<<<(N + GP_KNN_THREADS - 1) / GP_KNN_THREADS, GP_KNN_THREADS, smem, stream>>>(
+      N, Kp, Drt, K, q_points, q_feat, r_points, r_feat, F, amplify, r2, kp_chunk, idx64, idx32, dists));
   GP_LAUNCH_CHECK();
   return GP_OK;
 }

@@ -168,10 +168,10 @@ static inline int gp_radix_sort_pairs(uint32_t* keys[2], uint32_t* vals[2], cons
                                       int end_bit, const GpRadixTemp& tmp, cudaStream_t stream) {
   int sel = 0;
   for (int shift = begin_bit; shift < end_bit; shift += 8) {
-    gp_rs_hist_kernel<<<GP_RS_BLOCKS, GP_RS_THREADS, 0, stream>>>(keys[sel], n_ptr, shift, tmp.hist);
-    gp_rs_scan_kernel<<<GP_RS_RADIX, 256, 0, stream>>>(tmp.hist, tmp.totals);
-    gp_rs_scatter_kernel<<<GP_RS_BLOCKS, GP_RS_THREADS, 0, stream>>>(keys[sel], vals[sel], keys[sel ^ 1], vals[sel ^ 1],
-                                                                    n_ptr, shift, tmp.hist, tmp.totals);
+    GP_KERNEL("gp_rs_hist_kernel", stream, gp_rs_hist_kernel<<<GP_RS_BLOCKS, GP_RS_THREADS, 0, stream>>>(keys[sel], n_ptr, shift, tmp.hist));
+    GP_KERNEL("gp_rs_scan_kernel", stream, gp_rs_scan_kernel<<<GP_RS_RADIX, 256, 0, stream>>>(tmp.hist, tmp.totals));
+    GP_KERNEL("gp_rs_scatter_kernel", stream, gp_rs_scatter_kernel<<<GP_RS_BLOCKS, GP_RS_THREADS, 0, stream>>>(keys[sel], vals[sel], keys[sel ^ 1], vals[sel ^ 1],
+                                                                    n_ptr, shift, tmp.hist, tmp.totals));
     sel ^= 1;
   }
   return sel;

@@ -507,16 +507,16 @@ extern "C" int gp_raster_backward(const gp_raster_cfg* cfg, const float* bg, con
   float* grec = (float*)grad_ws;
   GP_CUDA_TRY(cudaMemsetAsync(grec, 0, (size_t)P * GP_GREC * 4, stream));
   const uint32_t* point_list = bn.tvals[gp_tile_sort_sel(W, H)];
-  gp_render_bwd_kernel<<<gx * gy, GP_TILE_PIX, 0, stream>>>(im.ranges, point_list, W, H, gx, bg, g.xy_depth,
+  GP_KERNEL("gp_render_bwd_kernel", stream, gp_render_bwd_kernel<<<gx * gy, GP_TILE_PIX, 0, stream>>>(im.ranges, point_list, W, H, gx, bg, g.xy_depth,
                                                            g.conic_opacity, g.rgb, colors_precomp, im.final_T,
-                                                           im.n_contrib, dL_dpix, g.hdr, grec);
+                                                           im.n_contrib, dL_dpix, g.hdr, grec));
   GP_LAUNCH_CHECK();
   const float* cov3D_ptr = cov3D_precomp ? cov3D_precomp : g.cov3D;
-  gp_preprocess_bwd_kernel<<<(P + 255) / 256, 256, 0, stream>>>(
+  GP_KERNEL("gp_preprocess_bwd_kernel", stream, gp_preprocess_bwd_kernel<<<(P + 255) / 256, 256, 0, stream>>>(
       P, cfg->sh_degree, cfg->sh_coeffs, means3D, radii, shs, g.clamped, has_sr ? scales : nullptr,
       has_sr ? rotations : nullptr, cfg->scale_modifier, cov3D_ptr, viewmatrix, projmatrix, focal_x, focal_y,
       cfg->tanfovx, cfg->tanfovy, campos, grec, dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh,
-      dL_dscales, dL_drots);
+      dL_dscales, dL_drots));
   GP_LAUNCH_CHECK();
   return GP_OK;
 }

@@ -456,20 +456,20 @@ extern "C" int gp_raster_preprocess(const gp_raster_cfg* cfg, const float* means
   const float focal_y = H / (2.0f * cfg->tanfovy);
   const float focal_x = W / (2.0f * cfg->tanfovx);
   const unsigned gx = (W + GP_TILE_X - 1) / GP_TILE_X, gy = (H + GP_TILE_Y - 1) / GP_TILE_Y;
-  gp_preprocess_kernel<<<(P + 255) / 256, 256, 0, stream>>>(
+  GP_KERNEL("gp_preprocess_kernel", stream, gp_preprocess_kernel<<<(P + 255) / 256, 256, 0, stream>>>(
       P, cfg->sh_degree, cfg->sh_coeffs, means3D, scales, cfg->scale_modifier, rotations, opacities, shs, cov3D_precomp,
       colors_precomp, viewmatrix, projmatrix, campos, W, H, cfg->tanfovx, cfg->tanfovy, focal_x, focal_y,
-      cfg->prefiltered, gx, gy, g, radii);
+      cfg->prefiltered, gx, gy, g, radii));
   GP_LAUNCH_CHECK();
   // depth sort: P keys, all 32 bits; result lands back in buffer 0 (4 passes)
   gp_radix_sort_pairs(g.dkeys, g.dvals, g.hdr + GP_HDR_NUM_POINTS, 0, 32, g.radix, stream);
   GP_LAUNCH_CHECK();
   const int nb = (P + GP_SCAN_BLOCK - 1) / GP_SCAN_BLOCK;
-  gp_block_sum_kernel<<<nb, GP_SCAN_BLOCK, 0, stream>>>(P, g.dvals[0], g.tiles_touched, g.block_sums);
+  GP_KERNEL("gp_block_sum_kernel", stream, gp_block_sum_kernel<<<nb, GP_SCAN_BLOCK, 0, stream>>>(P, g.dvals[0], g.tiles_touched, g.block_sums));
   GP_LAUNCH_CHECK();
   // capacity is not known yet: the spine scan runs again (cheaply) in gp_raster_render with the real
   // capacity; here it publishes R for callers that size the binning workspace exactly.
-  gp_spine_scan_kernel<<<1, 1024, 0, stream>>>(nb, g.block_sums, g.hdr, 0x7FFFFFFFll);
+  GP_KERNEL("gp_spine_scan_kernel", stream, gp_spine_scan_kernel<<<1, 1024, 0, stream>>>(nb, g.block_sums, g.hdr, 0x7FFFFFFFll));
   GP_LAUNCH_CHECK();
   return GP_OK;
 }
@@ -504,20 +504,20 @@ extern "C" int gp_raster_render(const gp_raster_cfg* cfg, const float* bg, const
   const unsigned gx = (W + GP_TILE_X - 1) / GP_TILE_X, gy = (H + GP_TILE_Y - 1) / GP_TILE_Y;
   const int nb = (P + GP_SCAN_BLOCK - 1) / GP_SCAN_BLOCK;
 
-  gp_set_capacity_kernel<<<1, 1, 0, stream>>>(g.hdr, capacity);
+  GP_KERNEL("gp_set_capacity_kernel", stream, gp_set_capacity_kernel<<<1, 1, 0, stream>>>(g.hdr, capacity));
   GP_LAUNCH_CHECK();
-  gp_duplicate_kernel<<<nb, GP_SCAN_BLOCK, 0, stream>>>(P, g.dvals[0], g.tiles_touched, g.xy_depth, radii, g.block_sums,
-                                                        g.hdr, gx, gy, b.tkeys[0], b.tvals[0]);
+  GP_KERNEL("gp_duplicate_kernel", stream, gp_duplicate_kernel<<<nb, GP_SCAN_BLOCK, 0, stream>>>(P, g.dvals[0], g.tiles_touched, g.xy_depth, radii, g.block_sums,
+                                                        g.hdr, gx, gy, b.tkeys[0], b.tvals[0]));
   GP_LAUNCH_CHECK();
   const int bits = gp_tile_bits(W, H);
   const int sel = gp_radix_sort_pairs(b.tkeys, b.tvals, g.hdr + GP_HDR_NUM_SORTED, 0, bits, g.radix, stream);
   GP_LAUNCH_CHECK();
   GP_CUDA_TRY(cudaMemsetAsync(im.ranges, 0, (size_t)gx * gy * sizeof(uint2), stream));
-  gp_tile_ranges_kernel<<<148 * 4, 256, 0, stream>>>(g.hdr, b.tkeys[sel], im.ranges);
+  GP_KERNEL("gp_tile_ranges_kernel", stream, gp_tile_ranges_kernel<<<148 * 4, 256, 0, stream>>>(g.hdr, b.tkeys[sel], im.ranges));
   GP_LAUNCH_CHECK();
-  gp_render_fwd_kernel<<<gx * gy, GP_TILE_PIX, 0, stream>>>(im.ranges, b.tvals[sel], W, H, gx, g.xy_depth,
+  GP_KERNEL("gp_render_fwd_kernel", stream, gp_render_fwd_kernel<<<gx * gy, GP_TILE_PIX, 0, stream>>>(im.ranges, b.tvals[sel], W, H, gx, g.xy_depth,
                                                            g.conic_opacity, g.rgb, colors_precomp, bg, g.hdr,
-                                                           im.final_T, im.n_contrib, out_color, out_depth, out_tidx);
+                                                           im.final_T, im.n_contrib, out_color, out_depth, out_tidx));
   GP_LAUNCH_CHECK();
   return GP_OK;
 }
@@ -527,7 +527,7 @@ extern "C" int gp_mark_visible(int P, const float* means3D, const float* viewmat
   (void)projmatrix;  // the reference computes the projection but only tests view-space z (auxiliary.h:154)
   if (P < 0 || (P > 0 && (!means3D || !viewmatrix || !present))) return GP_ERR_BAD_ARG;
   if (P == 0) return GP_OK;
-  gp_check_frustum_kernel<<<(P + 255) / 256, 256, 0, (cudaStream_t)stream_>>>(P, means3D, viewmatrix, present);
+  GP_KERNEL("gp_check_frustum_kernel", (cudaStream_t)stream_, gp_check_frustum_kernel<<<(P + 255) / 256, 256, 0, (cudaStream_t)stream_>>>(P, means3D, viewmatrix, present));
   GP_LAUNCH_CHECK();
   return GP_OK;
 }
@@ -591,8 +591,8 @@ extern "C" int gp_raster_export_state(const gp_raster_cfg* cfg, const void* geom
   if (!cfg || !geom_ws) return GP_ERR_BAD_ARG;
   const int P = cfg->P, W = cfg->width, H = cfg->height;
   GpGeom g = gp_carve_geom(const_cast<void*>(geom_ws), P);
-  gp_export_geom_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, g, depths, means2D, cov3D, conic_opacity, rgb,
-                                                            tiles_touched, clamped);
+  GP_KERNEL("gp_export_geom_kernel", stream, gp_export_geom_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, g, depths, means2D, cov3D, conic_opacity, rgb,
+                                                            tiles_touched, clamped));
   GP_LAUNCH_CHECK();
   if (image_ws) {
     GpImage im = gp_carve_image(const_cast<void*>(image_ws), W, H);
@@ -613,8 +613,8 @@ extern "C" int gp_raster_export_binning(const gp_raster_cfg* cfg, const void* ge
   GpGeom g = gp_carve_geom(const_cast<void*>(geom_ws), cfg->P);
   GpBinning b = gp_carve_binning(const_cast<void*>(binning_ws), capacity);
   const int sel = gp_tile_sort_sel(cfg->width, cfg->height);
-  gp_export_binning_kernel<<<148 * 4, 256, 0, stream>>>(g.hdr, b.tkeys[sel], b.tvals[sel], g.xy_depth, point_list,
-                                                       point_list_keys);
+  GP_KERNEL("gp_export_binning_kernel", stream, gp_export_binning_kernel<<<148 * 4, 256, 0, stream>>>(g.hdr, b.tkeys[sel], b.tvals[sel], g.xy_depth, point_list,
+                                                       point_list_keys));
   GP_LAUNCH_CHECK();
   return GP_OK;
 }

@@ -31,6 +31,14 @@ int gp_abi_version(void);
 /* Static text for an error code returned by any entry point. */
 const char* gp_error_string(int code);
 
+/* Measurement hooks (no reference counterpart; the reference only brackets a whole iteration with CUDA events,
+ * train.py:62-63,77,135).  gp_launch_count: kernels launched by this library since load.  gp_profile_enable(1)
+ * makes every launch record a CUDA event pair on its stream; gp_profile_report writes one line
+ * "<kernel> <launches> <total ms>" per kernel into buf (synchronises on the recorded events). */
+long long gp_launch_count(void);
+int gp_profile_enable(int on);
+int gp_profile_report(char* buf, size_t buf_bytes);
+
 /* ------------------------------------------------------------------------------------------------
  * Rasterizer.  Stands in for diff_gaussian_rasterization._C.rasterize_gaussians /
  * rasterize_gaussians_backward / mark_visible
