@@ -40,6 +40,8 @@ SIGNATURES = {
     "gp_raster_render": (c_int, [POINTER(RasterCfg), _P, _P, _P, _P, c_longlong, _P, _P, _P, _P, _P, _P]),
     "gp_raster_backward_ws_bytes": (c_size_t, [c_int]),
     "gp_raster_backward": (c_int, [POINTER(RasterCfg)] + [_P] * 13 + [c_longlong] + [_P] * 12),
+    "gp_raster_backward_static_max_gaussians": (c_int, []),
+    "gp_raster_backward_static": (c_int, [POINTER(RasterCfg)] + [_P] * 13 + [c_longlong] + [_P] * 11),
     "gp_mark_visible": (c_int, [c_int, _P, _P, _P, _P, _P]),
     "gp_raster_export_state": (c_int, [POINTER(RasterCfg)] + [_P] * 13),
     "gp_knn_points": (c_int, [c_int, c_int, c_int, c_int, c_float, _P, _P, _P, _P, _P]),

@@ -520,3 +520,64 @@ extern "C" int gp_raster_backward(const gp_raster_cfg* cfg, const float* bg, con
   GP_LAUNCH_CHECK();
   return GP_OK;
 }
+
+// ------------------------------------------------------------------------------------------------
+// Allocation-free variant of the backward
+// ------------------------------------------------------------------------------------------------
+//
+// gp_raster_backward needs 48 bytes of scratch per Gaussian (the packed gradient accumulator that the
+// blend backward sums into).  Some hosts of this library cannot provide it: a real-time render loop
+// where cudaMalloc is forbidden (it synchronises the device and may fail under memory pressure),
+// plugins embedded in an engine that owns the allocator and hands out no device memory, or bindings
+// from languages whose runtime has no device allocator.
+// For them the scratch lives in the library image itself: a fixed array in device global memory,
+// present on every GPU that loads the library, from load until the process exits.
+//
+// GP_STATIC_MAX_GAUSSIANS bounds the call: 262,144 Gaussians x 48 B = 12 MiB per GPU.
+#define GP_STATIC_MAX_GAUSSIANS 262144
+static __device__ __align__(256) float gp_static_grad_scratch[(size_t)GP_STATIC_MAX_GAUSSIANS * GP_GREC];
+
+#define GP_STATIC_MAX_DEVICES 64
+static float* gp_static_scratch_ptr[GP_STATIC_MAX_DEVICES];  // device address of the array, per device
+static bool gp_static_scratch_ready[GP_STATIC_MAX_DEVICES];
+
+extern "C" int gp_raster_backward_static_max_gaussians(void) { return GP_STATIC_MAX_GAUSSIANS; }
+
+// Same arguments and results as gp_raster_backward without `grad_ws`.
+//
+// * Limit: cfg->P <= GP_STATIC_MAX_GAUSSIANS, otherwise GP_ERR_LIMIT is returned and nothing is launched.
+// * Allocates nothing: no cudaMalloc / cudaFree / allocating library call on this path.
+// * The first call on each device resolves the device address of the scratch array
+//   (cudaGetSymbolAddress, with that device current).  Make that first call outside any stream
+//   capture; later calls only enqueue work on `stream`.
+// * One array per GPU is shared by every call and keeps the previous call's contents: the part a
+//   call uses is cleared on `stream` before the kernels run.  Two calls that can overlap on the same
+//   GPU (different streams, or threads) would sum into the same memory and corrupt each other --
+//   serialise them, or use gp_raster_backward with separate workspaces.
+extern "C" int gp_raster_backward_static(const gp_raster_cfg* cfg, const float* bg, const float* means3D,
+                                         const float* shs, const float* colors_precomp, const float* scales,
+                                         const float* rotations, const float* cov3D_precomp, const float* viewmatrix,
+                                         const float* projmatrix, const float* campos, const int* radii,
+                                         const void* geom_ws, const void* binning_ws, long long capacity,
+                                         const void* image_ws, const float* dL_dpix, float* dL_dmeans2D,
+                                         float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D, float* dL_dcov3D,
+                                         float* dL_dsh, float* dL_dscales, float* dL_drots, gp_stream_t stream) {
+  if (!cfg) return GP_ERR_BAD_ARG;
+  if (cfg->P > GP_STATIC_MAX_GAUSSIANS) return GP_ERR_LIMIT;
+  int dev = -1;
+  GP_CUDA_TRY(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= GP_STATIC_MAX_DEVICES) return GP_ERR_UNSUPPORTED;
+  if (!gp_static_scratch_ready[dev]) {
+    // In host code the array's name is only a handle for the runtime, not an address a kernel can use.
+    float* p = nullptr;
+    GP_CUDA_TRY(cudaGetSymbolAddress((void**)&p, gp_static_grad_scratch));
+    if (!p) return GP_ERR_UNSUPPORTED;
+    gp_static_scratch_ptr[dev] = p;
+    gp_static_scratch_ready[dev] = true;
+  }
+  // gp_raster_backward clears the first P records of the scratch on `stream` before accumulating.
+  return gp_raster_backward(cfg, bg, means3D, shs, colors_precomp, scales, rotations, cov3D_precomp, viewmatrix,
+                            projmatrix, campos, radii, geom_ws, binning_ws, capacity, image_ws, dL_dpix,
+                            gp_static_scratch_ptr[dev], dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D,
+                            dL_dsh, dL_dscales, dL_drots, stream);
+}

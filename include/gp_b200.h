@@ -105,6 +105,26 @@ int gp_raster_backward(const gp_raster_cfg* cfg, const float* bg, const float* m
                        float* dL_dcov3D /*[P,6]*/, float* dL_dsh /*[P,M,3]*/, float* dL_dscales /*[P,3]*/,
                        float* dL_drots /*[P,4]*/, gp_stream_t stream);
 
+/* Backward for callers that cannot allocate device memory.  No counterpart in the reference (its backward
+ * always allocates through torch, rasterize_points.cu:153-161).  Identical to gp_raster_backward, except that the
+ * 48 B/Gaussian scratch is a fixed array inside the library (12 MiB on every GPU that loads it) instead of
+ * `grad_ws`.  Meant for hosts where cudaMalloc is off limits: real-time render loops, plugins inside an engine
+ * that owns the device allocator, language bindings without one.
+ *   - cfg->P must be <= gp_raster_backward_static_max_gaussians() (262,144); larger -> GP_ERR_LIMIT, nothing runs.
+ *   - calls no cudaMalloc / cudaFree / allocating routine.
+ *   - the first call on a device looks up the array's device address; do it before any stream capture.
+ *   - the array is shared by all calls on a GPU and is cleared (the part in use) at the start of each call;
+ *     calls that may overlap on one GPU race on it and must be serialised by the caller. */
+int gp_raster_backward_static_max_gaussians(void);
+int gp_raster_backward_static(const gp_raster_cfg* cfg, const float* bg, const float* means3D, const float* shs,
+                              const float* colors_precomp, const float* scales, const float* rotations,
+                              const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
+                              const float* campos, const int* radii, const void* geom_ws, const void* binning_ws,
+                              long long capacity, const void* image_ws, const float* dL_dpix,
+                              float* dL_dmeans2D /*[P,3]*/, float* dL_dcolors /*[P,3]*/, float* dL_dopacity /*[P,1]*/,
+                              float* dL_dmeans3D /*[P,3]*/, float* dL_dcov3D /*[P,6]*/, float* dL_dsh /*[P,M,3]*/,
+                              float* dL_dscales /*[P,3]*/, float* dL_drots /*[P,4]*/, gp_stream_t stream);
+
 /* present[i] = (view-space z > 0.2).  Reference: checkFrustum, rasterizer_impl.cu:54-66,141-153. */
 int gp_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix, uint8_t* present,
                     gp_stream_t stream);
