@@ -51,6 +51,7 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-profile", action="store_true")
     ap.add_argument("--ncams", type=int, default=16)
+    ap.add_argument("--eager", action="store_true", help="ours: do not capture the iteration into a CUDA graph")
     return ap.parse_args()
 
 
@@ -183,6 +184,23 @@ class OurRunner:
             self.allreduce()
         return loss
 
+    def enable_graph(self):
+        """Capture the whole iteration into one CUDA graph (gaussianprediction_b200.pipeline.TrainStep)."""
+        from gaussianprediction_b200.pipeline import RenderStep, TrainStep
+        self.train_step = TrainStep(self.pc, self.cams_dev[0], self.capacity, bg=self.bg, iteration=ITER)
+        self.render_step = RenderStep(self.pc, self.cams_dev[0], self.capacity, bg=self.bg, iteration=ITER)
+
+    def step_graph(self, i, host_inputs=False):
+        k = i % len(self.cams_dev)
+        if host_inputs:
+            cam, t, G = self.cams_host[k], self.times_host[k:k + 1], self.grads_host[i % len(self.grads_host)]
+        else:
+            cam, t, G = self.cams_dev[k], self.times_dev[k], self.grads_dev[i % len(self.grads_dev)]
+        loss = self.train_step(cam, t, G)
+        if self.world > 1:
+            self.allreduce()
+        return loss
+
     def allreduce(self):
         import torch.distributed as dist
         off = 0
@@ -200,7 +218,7 @@ class OurRunner:
         for p, v in zip(self.params, views):
             p.grad = v.view_as(p)
 
-    def eval_fps(self, steps):
+    def eval_fps(self, steps, graph=False):
         """Forward-only render FPS in the reference's own span (eval.py:210-214: sync, render(), sync)."""
         from gaussianprediction_b200.renderer import render
         ts = []
@@ -209,7 +227,10 @@ class OurRunner:
                 k = i % len(self.cams_dev)
                 torch.cuda.synchronize()
                 t0 = time.perf_counter()
-                render(self.cams_dev[k], self.pc, None, self.bg, time=self.times_dev[k], it=ITER, capacity=self.capacity)
+                if graph:
+                    self.render_step(self.cams_dev[k], self.times_dev[k])
+                else:
+                    render(self.cams_dev[k], self.pc, None, self.bg, time=self.times_dev[k], it=ITER, capacity=self.capacity)
                 torch.cuda.synchronize()
                 if i >= 3:
                     ts.append(time.perf_counter() - t0)
@@ -273,12 +294,13 @@ class RefRunner:
 
 # ------------------------------------------------------------------------------------------------ timing
 
-def timed_steps(runner, steps, warmup, world, host_inputs, flush):
+def timed_steps(runner, steps, warmup, world, host_inputs, flush, graph=False):
     """W untimed steps, then exactly K steps; every step is bracketed by CUDA events on the current stream, L2 is
     flushed (256 MiB write) between steps outside the events; returns (sum of per-step device ms, wall ms)."""
     import torch.distributed as dist
+    step = runner.step_graph if graph else runner.step
     for i in range(warmup):
-        loss = runner.step(i, host_inputs)
+        loss = step(i, host_inputs)
         if host_inputs:
             loss.item()
     torch.cuda.synchronize()
@@ -290,7 +312,7 @@ def timed_steps(runner, steps, warmup, world, host_inputs, flush):
     for i in range(steps):
         flush.add_(1.0)                      # evict L2 (126 MB) between timed iterations
         evs[i][0].record()
-        loss = runner.step(warmup + i, host_inputs)
+        loss = step(warmup + i, host_inputs)
         if host_inputs:
             loss.item()                      # D2H read of the step's result inside the timed region
         evs[i][1].record()
@@ -482,11 +504,30 @@ def main():
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
-    launches0 = _lib.lib().gp_launch_count() if args.impl == "ours" else 0
-    dev_ms, wall_ms = timed_steps(runner, steps, warmup, eff_world, False, flush)
-    launches = (_lib.lib().gp_launch_count() - launches0) if args.impl == "ours" else 0
-    e2e_dev_ms, e2e_wall_ms = timed_steps(runner, steps, warmup, eff_world, True, flush)
+    use_graph, graph_note = False, "eager launches"
+    eager_ms = None
+    if args.impl == "ours":
+        # eager pass first: it counts the kernels of one step (a graph replay re-issues exactly those launches)
+        launches0 = _lib.lib().gp_launch_count()
+        eager_dev_ms, _ = timed_steps(runner, steps, warmup, eff_world, False, flush)
+        launches = _lib.lib().gp_launch_count() - launches0
+        launches = launches * steps // (steps + warmup)
+        eager_ms = max_over_ranks(eager_dev_ms, eff_world, dev) / steps / eff_world
+        if not args.eager:
+            try:
+                runner.enable_graph()
+                use_graph, graph_note = True, "whole iteration replayed as one CUDA graph (pipeline.TrainStep)"
+            except Exception as e:                                  # pragma: no cover
+                graph_note = f"eager launches (graph capture failed: {type(e).__name__}: {e})"
+    else:
+        launches = 0
+    dev_ms, wall_ms = timed_steps(runner, steps, warmup, eff_world, False, flush, graph=use_graph)
+    e2e_dev_ms, e2e_wall_ms = timed_steps(runner, steps, warmup, eff_world, True, flush, graph=use_graph)
     clocks = sampler.stop() if rank == 0 else None
+    if use_graph:
+        R_last, over = runner.train_step.overflowed()
+        if over:
+            raise SystemExit("tile-instance capacity overflowed during the timed region: result invalid")
 
     dev_ms = max_over_ranks(dev_ms, eff_world, dev)
     e2e_dev_ms = max_over_ranks(e2e_dev_ms, eff_world, dev)
@@ -495,7 +536,7 @@ def main():
     value = ms_per_step / eff_world                                # whole job: ms per (camera, time) sample
     e2e_value = e2e_ms_per_step / eff_world
 
-    fps = runner.eval_fps(min(steps, 20))
+    fps = runner.eval_fps(min(steps, 20), graph=True) if use_graph else runner.eval_fps(min(steps, 20))
 
     line = {
         "metric": METRIC, "value": round(value, 4), "unit": "ms/iter", "n_gpus": eff_world if args.impl == "ours" else args.gpus,
@@ -511,6 +552,9 @@ def main():
         "train_iters_per_s": round(1e3 / value, 2), "render_fps": round(fps * eff_world, 2),
         "wall_ms_per_step": round(wall_ms / steps, 4),
     }
+    line["config"]["launch"] = graph_note
+    if eager_ms is not None:
+        line["eager_ms_per_iter"] = round(eager_ms, 4)
     if args.impl == "reference":
         line["impl"] = "reference"
         line["n_gpus"] = args.gpus

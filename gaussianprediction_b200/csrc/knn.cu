@@ -16,10 +16,13 @@
 #include "../../include/gp_b200.h"
 #include "common.cuh"
 
-#define GP_KNN_THREADS 128
+#define GP_KNN_THREADS 256
 
-template <int KMAX>
+// Top-K in registers.  KT > 0: K is the compile-time constant KT (the repo's nearest_num <= 8 cases: every index is
+// static, nothing spills).  KT == 0: runtime K <= 32 with predicated indexing.
+template <int KT>
 struct TopK {
+  static constexpr int KMAX = KT > 0 ? KT : 32;
   float d[KMAX];
   int i[KMAX];
   __device__ __forceinline__ void init() {
@@ -32,15 +35,20 @@ struct TopK {
   // keep the K smallest (d, index) pairs in ascending order; candidates arrive in ascending index
   // order, so a strict '<' keeps the smaller index first among equal distances.
   __device__ __forceinline__ void insert(float dist, int idx, int K) {
+    if (KT > 0) {
+      d[KMAX - 1] = dist;
+      i[KMAX - 1] = idx;
+    } else {
 #pragma unroll
-    for (int k = 0; k < KMAX; k++)
-      if (k == K - 1) {
-        d[k] = dist;
-        i[k] = idx;
-      }
+      for (int k = 0; k < KMAX; k++)
+        if (k == K - 1) {
+          d[k] = dist;
+          i[k] = idx;
+        }
+    }
 #pragma unroll
     for (int k = KMAX - 1; k > 0; k--) {
-      if (k < K && d[k] < d[k - 1]) {
+      if ((KT > 0 || k < K) && d[k] < d[k - 1]) {
         const float td = d[k];
         d[k] = d[k - 1];
         d[k - 1] = td;
@@ -51,6 +59,7 @@ struct TopK {
     }
   }
   __device__ __forceinline__ float worst(int K) const {
+    if (KT > 0) return d[KMAX - 1];
     float wv = d[0];
 #pragma unroll
     for (int k = 0; k < KMAX; k++)
@@ -62,7 +71,7 @@ struct TopK {
 // Query = [xyz (3) | feat (F) * amplify] assembled on the fly when `q_feat` is given, otherwise the
 // D floats of q_points.  Same for the keypoints.  D is a template parameter for the two shapes the
 // repo uses (3 and 35); D == 0 selects the generic runtime-D path (query re-read from L1).
-template <int D, int KMAX>
+template <int D, int KT>
 __global__ void __launch_bounds__(GP_KNN_THREADS)
 gp_knn_kernel(int N, int Kp, int Drt, int K, const float* __restrict__ q_points, const float* __restrict__ q_feat,
               const float* __restrict__ r_points, const float* __restrict__ r_feat, int F, float amplify, float r2,
@@ -85,7 +94,7 @@ gp_knn_kernel(int N, int Kp, int Drt, int K, const float* __restrict__ q_points,
         qv[d] = q_points[(size_t)qc * Dn + d];
     }
   }
-  TopK<KMAX> top;
+  TopK<KT> top;
   top.init();
   float worst = __int_as_float(0x7f800000);
   int filled = 0;
@@ -93,24 +102,83 @@ gp_knn_kernel(int N, int Kp, int Drt, int K, const float* __restrict__ q_points,
   for (int base = 0; base < Kp; base += kp_chunk) {
     const int cnt = min(kp_chunk, Kp - base);
     __syncthreads();
-    for (int e = threadIdx.x; e < cnt * DP; e += GP_KNN_THREADS) {
-      const int j = e / DP, d = e - j * DP;
-      float v = 0.f;
-      if (d < Dn) {
-        if (r_feat != nullptr)
-          v = d < 3 ? r_points[(size_t)(base + j) * 3 + d] : __fmul_rn(r_feat[(size_t)(base + j) * F + (d - 3)], amplify);
-        else
-          v = r_points[(size_t)(base + j) * Dn + d];
+    // ---- stage the keypoints of this chunk (zero padded to DP floats per row) ----
+    if (r_feat != nullptr) {
+      for (int j = threadIdx.x; j < cnt; j += GP_KNN_THREADS) {
+        const float* src = r_points + (size_t)(base + j) * 3;
+        float* dst = s_ref + j * DP;
+        dst[0] = src[0];
+        dst[1] = src[1];
+        dst[2] = src[2];
+        for (int d = 3 + F; d < DP; d++) dst[d] = 0.f;
       }
-      s_ref[e] = v;
+      if ((F & 3) == 0 && ((((size_t)r_feat) & 15) == 0)) {
+        const int f4 = F >> 2;
+        const int total = cnt * f4;
+        for (int e0 = threadIdx.x; e0 < total; e0 += 4 * GP_KNN_THREADS) {
+          float4 v[4];
+#pragma unroll
+          for (int u = 0; u < 4; u++) {
+            const int e = e0 + u * GP_KNN_THREADS;
+            if (e < total) v[u] = __ldg((const float4*)(r_feat + (size_t)base * F) + e);
+          }
+#pragma unroll
+          for (int u = 0; u < 4; u++) {
+            const int e = e0 + u * GP_KNN_THREADS;
+            if (e < total) {
+              const int j = e / f4, c = e - j * f4;
+              float* dst = s_ref + j * DP + 3 + 4 * c;
+              dst[0] = __fmul_rn(v[u].x, amplify);
+              dst[1] = __fmul_rn(v[u].y, amplify);
+              dst[2] = __fmul_rn(v[u].z, amplify);
+              dst[3] = __fmul_rn(v[u].w, amplify);
+            }
+          }
+        }
+      } else {
+        for (int e = threadIdx.x; e < cnt * F; e += GP_KNN_THREADS) {
+          const int j = e / F, c = e - j * F;
+          s_ref[j * DP + 3 + c] = __fmul_rn(r_feat[(size_t)(base + j) * F + c], amplify);
+        }
+      }
+    } else {
+      const int total = cnt * DP;
+      for (int e0 = threadIdx.x; e0 < total; e0 += 4 * GP_KNN_THREADS) {
+        float v[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+          const int e = e0 + u * GP_KNN_THREADS;
+          const int j = e / DP, d = e - j * DP;
+          v[u] = (e < total && d < Dn) ? r_points[(size_t)(base + j) * Dn + d] : 0.f;
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+          const int e = e0 + u * GP_KNN_THREADS;
+          if (e < total) s_ref[e] = v[u];
+        }
+      }
     }
     __syncthreads();
     for (int j = 0; j < cnt; j++) {
       const float* rp = s_ref + j * DP;
       float acc = 0.f;
       if (D > 0) {
+        {
+          const float4 r4 = *(const float4*)(rp);
+          const float rr[4] = {r4.x, r4.y, r4.z, r4.w};
 #pragma unroll
-        for (int d4 = 0; d4 < (DD + 3) / 4; d4++) {
+          for (int u = 0; u < 4; u++) {
+            if (u < DD) {
+              const float diff = rr[u] - qv[u];
+              acc = __fmaf_rn(diff, diff, acc);
+            }
+          }
+        }
+        // Exact early exit: the partial sum never decreases, so once it has reached this lane's K-th best for
+        // every lane of the warp, no lane can accept the keypoint and the remaining dimensions are skipped.
+        if (DD > 8 && __all_sync(0xffffffffu, acc >= worst)) continue;
+#pragma unroll
+        for (int d4 = 1; d4 < (DD + 3) / 4; d4++) {
           const float4 r4 = *(const float4*)(rp + 4 * d4);
           const float rr[4] = {r4.x, r4.y, r4.z, r4.w};
 #pragma unroll
@@ -142,7 +210,7 @@ gp_knn_kernel(int N, int Kp, int Drt, int K, const float* __restrict__ q_points,
   }
   if (!valid) return;
 #pragma unroll
-  for (int k = 0; k < KMAX; k++) {
+  for (int k = 0; k < TopK<KT>::KMAX; k++) {
     if (k < K) {
       const bool has = k < filled;
       if (idx64) idx64[(size_t)q * K + k] = has ? (long long)top.i[k] : -1ll;
@@ -152,7 +220,7 @@ gp_knn_kernel(int N, int Kp, int Drt, int K, const float* __restrict__ q_points,
   }
 }
 
-template <int D, int KMAX>
+template <int D, int KT>
 static int launch_knn(int N, int Kp, int Drt, int K, const float* q_points, const float* q_feat, const float* r_points,
                       const float* r_feat, int F, float amplify, float r2, long long* idx64, int* idx32, float* dists,
                       cudaStream_t stream) {
@@ -163,12 +231,32 @@ static int launch_knn(int N, int Kp, int Drt, int K, const float* q_points, cons
   if ((size_t)kp_chunk * DP * 4 > max_smem) kp_chunk = (int)(max_smem / ((size_t)DP * 4));
   if (kp_chunk < 1) kp_chunk = 1;
   const size_t smem = (size_t)kp_chunk * DP * 4;
-  auto kern = gp_knn_kernel<D, KMAX>;
+  auto kern = gp_knn_kernel<D, KT>;
   if (smem > 48 * 1024) GP_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   GP_KERNEL("gp_knn_kernel", stream, kern<<<(N + GP_KNN_THREADS - 1) / GP_KNN_THREADS, GP_KNN_THREADS, smem, stream>>>(
       N, Kp, Drt, K, q_points, q_feat, r_points, r_feat, F, amplify, r2, kp_chunk, idx64, idx32, dists));
   GP_LAUNCH_CHECK();
   return GP_OK;
+}
+
+template <int D>
+static int knn_dispatch_k(int N, int Kp, int Drt, int K, const float* q_points, const float* q_feat,
+                          const float* r_points, const float* r_feat, int F, float amplify, float r2, long long* idx64,
+                          int* idx32, float* dists, cudaStream_t stream) {
+#define GP_KNN_GO(KT) \
+  return launch_knn<D, KT>(N, Kp, Drt, K, q_points, q_feat, r_points, r_feat, F, amplify, r2, idx64, idx32, dists, stream)
+  switch (K) {
+    case 1: GP_KNN_GO(1);
+    case 2: GP_KNN_GO(2);
+    case 3: GP_KNN_GO(3);
+    case 4: GP_KNN_GO(4);
+    case 5: GP_KNN_GO(5);
+    case 6: GP_KNN_GO(6);
+    case 7: GP_KNN_GO(7);
+    case 8: GP_KNN_GO(8);
+    default: GP_KNN_GO(0);
+  }
+#undef GP_KNN_GO
 }
 
 static int knn_dispatch(int N, int Kp, int D, int K, const float* q_points, const float* q_feat, const float* r_points,
@@ -178,18 +266,9 @@ static int knn_dispatch(int N, int Kp, int D, int K, const float* q_points, cons
   if (K > 32) return GP_ERR_UNSUPPORTED;
   if (N == 0) return GP_OK;
   const float r2 = r * r;  // the reference passes r*r computed in float (frnn.py:176)
-#define GP_KNN_GO(DV, KM) \
-  return launch_knn<DV, KM>(N, Kp, D, K, q_points, q_feat, r_points, r_feat, F, amplify, r2, idx64, idx32, dists, stream)
-  if (K <= 8) {
-    if (D == 3) GP_KNN_GO(3, 8);
-    if (D == 35) GP_KNN_GO(35, 8);
-    GP_KNN_GO(0, 8);
-  } else {
-    if (D == 3) GP_KNN_GO(3, 32);
-    if (D == 35) GP_KNN_GO(35, 32);
-    GP_KNN_GO(0, 32);
-  }
-#undef GP_KNN_GO
+  if (D == 3) return knn_dispatch_k<3>(N, Kp, D, K, q_points, q_feat, r_points, r_feat, F, amplify, r2, idx64, idx32, dists, stream);
+  if (D == 35) return knn_dispatch_k<35>(N, Kp, D, K, q_points, q_feat, r_points, r_feat, F, amplify, r2, idx64, idx32, dists, stream);
+  return knn_dispatch_k<0>(N, Kp, D, K, q_points, q_feat, r_points, r_feat, F, amplify, r2, idx64, idx32, dists, stream);
 }
 
 extern "C" int gp_knn_points(int N, int Kp, int D, int K, float r, const float* points1, const float* points2,

@@ -31,13 +31,22 @@ static inline size_t gp_radix_temp_bytes() {
 }
 
 #ifdef __CUDACC__
+// Number of warp chunks in use for n keys: at least GP_RS_MIN_CHUNK keys per chunk, so that a small sort does not
+// pay for 256 x GV histogram counters (the scan only touches the chunks in use).
+#define GP_RS_MIN_CHUNK 2048
+__device__ __forceinline__ int gp_rs_num_chunks(int n) {
+  int c = (n + GP_RS_MIN_CHUNK - 1) / GP_RS_MIN_CHUNK;
+  return c < 1 ? 1 : (c > GP_RS_GV ? GP_RS_GV : c);
+}
 __device__ __forceinline__ void gp_rs_chunk(int n, int gw, int& start, int& end) {
-  int sub = (n + GP_RS_GV - 1) / GP_RS_GV;
+  const int nch = gp_rs_num_chunks(n);
+  int sub = (n + nch - 1) / nch;
   sub = (sub + 31) & ~31;
   long long s = (long long)gw * sub;
   long long e = s + sub;
   start = (int)(s < n ? s : n);
   end = (int)(e < n ? e : n);
+  if (gw >= nch) start = end = n;
 }
 
 static __global__ void __launch_bounds__(GP_RS_THREADS)
@@ -47,6 +56,7 @@ gp_rs_hist_kernel(const uint32_t* __restrict__ keys, const int* __restrict__ n_p
   const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int gw = blockIdx.x * GP_RS_WARPS + w;
   const int n = *n_ptr;
+  if (gw >= gp_rs_num_chunks(n)) return;
   for (int d = lane; d < GP_RS_RADIX; d += 32) wh[w][d] = 0;
   __syncwarp();
   int start, end;
@@ -64,17 +74,19 @@ gp_rs_hist_kernel(const uint32_t* __restrict__ keys, const int* __restrict__ n_p
 }
 
 // One block per digit: exclusive scan of hist[d][0..GV) in place; totals[d] = sum.
-static __global__ void __launch_bounds__(256) gp_rs_scan_kernel(uint32_t* __restrict__ hist, uint32_t* __restrict__ totals) {
+static __global__ void __launch_bounds__(256)
+gp_rs_scan_kernel(uint32_t* __restrict__ hist, uint32_t* __restrict__ totals, const int* __restrict__ n_ptr) {
   constexpr int PER = (GP_RS_GV + 255) / 256;
   __shared__ uint32_t warp_sums[8];
   uint32_t* row = hist + (size_t)blockIdx.x * GP_RS_GV;
   const int t = threadIdx.x, lane = t & 31, w = t >> 5;
+  const int nch = gp_rs_num_chunks(*n_ptr);
   uint32_t v[PER];
   uint32_t local = 0;
 #pragma unroll
   for (int j = 0; j < PER; j++) {
     const int i = t * PER + j;
-    v[j] = i < GP_RS_GV ? row[i] : 0u;
+    v[j] = i < nch ? row[i] : 0u;
     local += v[j];
   }
   uint32_t incl = local;
@@ -91,7 +103,7 @@ static __global__ void __launch_bounds__(256) gp_rs_scan_kernel(uint32_t* __rest
 #pragma unroll
   for (int j = 0; j < PER; j++) {
     const int i = t * PER + j;
-    if (i < GP_RS_GV) row[i] = run;
+    if (i < nch) row[i] = run;
     run += v[j];
   }
   if (t == 255) totals[blockIdx.x] = run;
@@ -106,6 +118,7 @@ gp_rs_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __res
   const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int gw = blockIdx.x * GP_RS_WARPS + w;
   const int n = *n_ptr;
+  if (gw >= gp_rs_num_chunks(n)) return;
   // digit bases: exclusive scan of totals[256]; every warp does it redundantly (8 digits per lane).
   {
     uint32_t tv[8];
@@ -169,7 +182,7 @@ static inline int gp_radix_sort_pairs(uint32_t* keys[2], uint32_t* vals[2], cons
   int sel = 0;
   for (int shift = begin_bit; shift < end_bit; shift += 8) {
     GP_KERNEL("gp_rs_hist_kernel", stream, gp_rs_hist_kernel<<<GP_RS_BLOCKS, GP_RS_THREADS, 0, stream>>>(keys[sel], n_ptr, shift, tmp.hist));
-    GP_KERNEL("gp_rs_scan_kernel", stream, gp_rs_scan_kernel<<<GP_RS_RADIX, 256, 0, stream>>>(tmp.hist, tmp.totals));
+    GP_KERNEL("gp_rs_scan_kernel", stream, gp_rs_scan_kernel<<<GP_RS_RADIX, 256, 0, stream>>>(tmp.hist, tmp.totals, n_ptr));
     GP_KERNEL("gp_rs_scatter_kernel", stream, gp_rs_scatter_kernel<<<GP_RS_BLOCKS, GP_RS_THREADS, 0, stream>>>(keys[sel], vals[sel], keys[sel ^ 1], vals[sel ^ 1],
                                                                     n_ptr, shift, tmp.hist, tmp.totals));
     sel ^= 1;

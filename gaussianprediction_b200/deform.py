@@ -22,9 +22,23 @@ from ._lib import check, ptr
 
 # ------------------------------------------------------------------------------------------------ small torch pieces
 
+_FREQ_BANDS = {}
+
+
+def _freq_bands(freqs, device):
+    # cached per device: building it on the CPU and copying it over is a pageable H2D copy, which is slow in the
+    # frame loop and illegal while a CUDA graph is being captured
+    key = (int(freqs), str(device))
+    fb = _FREQ_BANDS.get(key)
+    if fb is None:
+        fb = (2 ** torch.arange(freqs).float()).to(device)
+        _FREQ_BANDS[key] = fb
+    return fb
+
+
 def positional_encoding(positions, freqs):
     """[sin(2^k x), cos(2^k x)] interleaved per input dim (scene/deformable_field.py:63-72, ori=False)."""
-    freq_bands = (2 ** torch.arange(freqs).float()).to(positions.device)
+    freq_bands = _freq_bands(freqs, positions.device)
     pts = (positions[..., None] * freq_bands).reshape(positions.shape[:-1] + (freqs * positions.shape[-1],))
     pts = torch.stack([torch.sin(pts), torch.cos(pts)], dim=-1).reshape(pts.shape[:-1] + (pts.shape[-1] * 2,))
     return pts

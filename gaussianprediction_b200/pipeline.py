@@ -1,0 +1,131 @@
+"""Whole-iteration CUDA graphs for the frame loop.
+
+The reference's train iteration (train.py:77-135) issues ~150 small torch/CUDA launches and one blocking D2H per
+frame; at 100k Gaussians the GPU work is ~1.5 ms, so launch latency is a large share of the iteration.  Because this
+implementation has no host round trip inside a frame (the tile-instance count stays on the device, see
+rasterizer.py ``capacity=``), the complete step -- deformation forward, rasterizer forward, loss, rasterizer
+backward, deformation backward -- can be captured once into a CUDA graph and replayed with new camera / time /
+target tensors.  Kernels and results are the same as the eager path; only the launch mechanism changes.
+
+A graph is tied to (image size, tan-fov, SH degree, parameter shapes, capacity): those are kernel arguments by value.
+"""
+import torch
+
+from . import _lib
+from .rasterizer import export_state  # noqa: F401  (kept importable for diagnostics)
+from .renderer import render
+
+
+class _StaticCamera:
+    def __init__(self, cam, device):
+        self.image_width, self.image_height = int(cam.image_width), int(cam.image_height)
+        self.FoVx, self.FoVy = float(cam.FoVx), float(cam.FoVy)
+        self.world_view_transform = torch.empty(4, 4, device=device)
+        self.full_proj_transform = torch.empty(4, 4, device=device)
+        self.camera_center = torch.empty(3, device=device)
+
+    def load(self, cam, non_blocking=True):
+        assert int(cam.image_width) == self.image_width and int(cam.image_height) == self.image_height
+        assert abs(float(cam.FoVx) - self.FoVx) < 1e-12 and abs(float(cam.FoVy) - self.FoVy) < 1e-12, \
+            "a captured step is tied to the camera intrinsics; build another TrainStep for other intrinsics"
+        self.world_view_transform.copy_(cam.world_view_transform, non_blocking=non_blocking)
+        self.full_proj_transform.copy_(cam.full_proj_transform, non_blocking=non_blocking)
+        self.camera_center.copy_(cam.camera_center, non_blocking=non_blocking)
+
+
+class TrainStep:
+    """``loss = step(cam, t, target)``: render(cam, pc, time=t) -> loss_fn(image, target) -> backward, as one graph.
+
+    After the call ``p.grad`` of every parameter of ``pc`` holds the gradients of this sample (static tensors,
+    overwritten by the next call).  ``loss_fn`` defaults to ``(image * target).sum()`` (an upstream-gradient probe);
+    any capturable torch function of (image, target) works.  ``capacity`` bounds the tile instances of a frame;
+    ``overflowed()`` tells whether the last frame exceeded it (that frame's image and gradients are then invalid).
+    """
+
+    def __init__(self, pc, cam, capacity, bg=None, iteration=50_000, loss_fn=None, warmup=3):
+        self.pc = pc
+        self.params = [p for p in pc.parameters() if p.requires_grad]
+        dev = self.params[0].device
+        self.dev = dev
+        self.capacity = int(capacity)
+        self.iteration = int(iteration)
+        self.bg = torch.zeros(3, device=dev) if bg is None else bg
+        self.loss_fn = loss_fn or (lambda image, target: (image * target).sum())
+        self.cam = _StaticCamera(cam, dev)
+        self.cam.load(cam, non_blocking=False)
+        self.t = torch.zeros(1, device=dev)
+        self.target = torch.zeros(3, self.cam.image_height, self.cam.image_width, device=dev)
+        self.loss = None
+        self.pkg = None
+        _lib.lib()
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):
+            for _ in range(max(warmup, 1)):       # also resolves lazy inits (cuBLAS handles, cached tables)
+                self._body()
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        for p in self.params:
+            p.grad = None
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self._body()
+        from . import rasterizer as _r
+        self._state = _r.LAST_STATE          # workspaces of the captured frame (static addresses)
+        torch.cuda.synchronize(dev)
+
+    def overflowed(self):
+        """(R, flag) of the last replay, read from the device header; if flag is set the frame was not rendered."""
+        hdr = self._state.geom[:16].view(torch.int32).cpu()
+        return int(hdr[_lib.HDR_NUM_RENDERED]), bool(int(hdr[_lib.HDR_OVERFLOW]))
+
+    def _body(self):
+        for p in self.params:
+            p.grad = None
+        self.pkg = render(self.cam, self.pc, None, self.bg, time=self.t, it=self.iteration, capacity=self.capacity)
+        self.loss = self.loss_fn(self.pkg["render"], self.target)
+        self.loss.backward()
+
+    def __call__(self, cam, t, target, non_blocking=True):
+        self.cam.load(cam, non_blocking)
+        self.t.copy_(t, non_blocking=non_blocking)
+        self.target.copy_(target, non_blocking=non_blocking)
+        self.graph.replay()
+        return self.loss
+
+    @property
+    def image(self):
+        return self.pkg["render"]
+
+
+class RenderStep:
+    """Forward-only ``render()`` as one graph (the eval / extrapolation frame loop, eval.py:192-226)."""
+
+    def __init__(self, pc, cam, capacity, bg=None, iteration=50_000, warmup=3):
+        self.pc = pc
+        dev = next(pc.parameters()).device
+        self.dev, self.capacity, self.iteration = dev, int(capacity), int(iteration)
+        self.bg = torch.zeros(3, device=dev) if bg is None else bg
+        self.cam = _StaticCamera(cam, dev)
+        self.cam.load(cam, non_blocking=False)
+        self.t = torch.zeros(1, device=dev)
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side), torch.no_grad():
+            for _ in range(max(warmup, 1)):
+                self._body()
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.no_grad(), torch.cuda.graph(self.graph):
+            self._body()
+        torch.cuda.synchronize(dev)
+
+    def _body(self):
+        self.pkg = render(self.cam, self.pc, None, self.bg, time=self.t, it=self.iteration, capacity=self.capacity)
+
+    def __call__(self, cam, t, non_blocking=True):
+        self.cam.load(cam, non_blocking)
+        self.t.copy_(t, non_blocking=non_blocking)
+        self.graph.replay()
+        return self.pkg

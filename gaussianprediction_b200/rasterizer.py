@@ -67,6 +67,18 @@ class RasterState:
     __slots__ = ("cfg", "geom", "binning", "image", "radii", "capacity", "num_rendered")
 
 
+LAST_STATE = None   # state of the most recent forward (diagnostics: header words, overflow flag)
+
+
+def last_overflow():
+    """(num_rendered, overflowed) of the most recent forward, read from the device header (synchronises)."""
+    st = LAST_STATE
+    if st is None or st.cfg is None:
+        return 0, False
+    hdr = st.geom[:16].view(torch.int32).cpu()
+    return int(hdr[_lib.HDR_NUM_RENDERED]), bool(int(hdr[_lib.HDR_OVERFLOW]))
+
+
 def raster_forward(means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, raster_settings,
                    capacity: Optional[int] = None):
     """Runs the two forward stages; returns (color, radii, depth, tidx, RasterState)."""
@@ -115,6 +127,8 @@ def raster_forward(means3D, sh, colors_precomp, opacities, scales, rotations, co
     check(L.gp_raster_render(ctypes.byref(cfg), ptr(bg), ptr(colors_precomp), ptr(geom), ptr(binning), int(capacity),
                              ptr(image), ptr(radii), ptr(color), ptr(depth), ptr(tidx), stream), "gp_raster_render")
     st.cfg, st.geom, st.binning, st.image, st.radii, st.capacity = cfg, geom, binning, image, radii, int(capacity)
+    global LAST_STATE
+    LAST_STATE = st
     return color, radii, depth, tidx, st
 
 

@@ -191,3 +191,48 @@ def test_model_call_matches_oracle_and_render_runs(gplib):
             continue            # only feeds the (non-differentiable) search
         assert p.grad is not None and torch.isfinite(p.grad).all(), name
     assert float(model.super_gaussians.grad.abs().sum()) > 0 and float(model.weights_model.logits.grad.abs().sum()) > 0
+
+
+def test_graph_step_matches_eager(gplib):
+    """pipeline.TrainStep (whole iteration as one CUDA graph, sync-free capacity mode) gives the eager results."""
+    from gaussianprediction_b200 import synthetic as syn
+    from gaussianprediction_b200.deform import KeypointDeformation, default_args
+    from gaussianprediction_b200.pipeline import RenderStep, TrainStep
+    from gaussianprediction_b200.renderer import SceneModel, render
+    N, Kp, W, H = 8000, 128, 160, 112
+    gs, kp, kf, logits = scene(N, Kp, seed=31)
+    args = default_args(feature_amplify=0.5, norm_rotation=True)
+    torch.manual_seed(0)
+    model = KeypointDeformation(args, gs.xyz, gs.rotation, gs.scaling, gs.opacity, gs.motion_feature, kp, kf, logits=logits)
+    pc = SceneModel(model, gs.features_dc, gs.features_rest).cuda()
+    cams = syn.camera_ring(3, W, H, seed=5)
+    for c in cams:
+        for k in ("world_view_transform", "full_proj_transform", "camera_center"):
+            setattr(c, k, getattr(c, k).cuda())
+    bg = torch.zeros(3, device="cuda")
+    g = torch.Generator().manual_seed(1)
+    targets = [(torch.randn(3, H, W, generator=g) * 1e-2).cuda() for _ in cams]
+    times = [torch.tensor([0.2 + 0.3 * i], device="cuda") for i in range(len(cams))]
+    step = TrainStep(pc, cams[0], capacity=400_000, bg=bg)
+    rstep = RenderStep(pc, cams[0], capacity=400_000, bg=bg)
+    for cam, t, tgt in zip(cams, times, targets):
+        loss_g = float(step(cam, t, tgt))
+        R, over = step.overflowed()
+        assert not over and R > 0
+        grads_g = {n: p.grad.clone() for n, p in pc.named_parameters() if p.grad is not None}
+        img_g = step.image.clone()
+        for p in pc.parameters():
+            p.grad = None
+        pkg = render(cam, pc, None, bg, time=t, it=50_000)
+        loss_e = (pkg["render"] * tgt).sum()
+        loss_e.backward()
+        assert count_diff(img_g, pkg["render"]) == 0                 # same kernels, same inputs: bit-identical image
+        assert abs(loss_g - float(loss_e)) <= 1e-6 * max(1.0, abs(float(loss_e)))
+        for n, p in pc.named_parameters():
+            if p.grad is not None:
+                assert rel_err(grads_g[n], p.grad) <= 1e-3, n
+        assert count_diff(rstep(cam, t)["render"], pkg["render"]) == 0
+    # a capacity that is too small is reported, not silently rendered
+    small = TrainStep(pc, cams[0], capacity=1000, bg=bg)
+    small(cams[0], times[0], targets[0])
+    assert small.overflowed()[1]
