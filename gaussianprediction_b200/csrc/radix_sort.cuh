@@ -33,7 +33,7 @@ static inline size_t gp_radix_temp_bytes() {
 #ifdef __CUDACC__
 // Number of warp chunks in use for n keys: at least GP_RS_MIN_CHUNK keys per chunk, so that a small sort does not
 // pay for 256 x GV histogram counters (the scan only touches the chunks in use).
-#define GP_RS_MIN_CHUNK 2048
+#define GP_RS_MIN_CHUNK 256
 __device__ __forceinline__ int gp_rs_num_chunks(int n) {
   int c = (n + GP_RS_MIN_CHUNK - 1) / GP_RS_MIN_CHUNK;
   return c < 1 ? 1 : (c > GP_RS_GV ? GP_RS_GV : c);
@@ -61,14 +61,23 @@ gp_rs_hist_kernel(const uint32_t* __restrict__ keys, const int* __restrict__ n_p
   __syncwarp();
   int start, end;
   gp_rs_chunk(n, gw, start, end);
-  for (int i0 = start; i0 < end; i0 += 32) {
-    const int i = i0 + lane;
-    const bool valid = i < end;
-    const uint32_t k = valid ? __ldg(keys + i) : 0u;
-    const uint32_t d = valid ? ((k >> shift) & 0xFFu) : 0x100u;
-    const unsigned peers = __match_any_sync(0xffffffffu, d);
-    if (valid && (peers & gp_lanemask_lt()) == 0) wh[w][d] += __popc(peers);
-    __syncwarp();
+  constexpr int U = 4;
+  for (int i0 = start; i0 < end; i0 += 32 * U) {
+    uint32_t k[U];
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      const int i = i0 + u * 32 + lane;
+      k[u] = i < end ? __ldg(keys + i) : 0u;
+    }
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      const int i = i0 + u * 32 + lane;
+      const bool valid = i < end;
+      const uint32_t d = valid ? ((k[u] >> shift) & 0xFFu) : 0x100u;
+      const unsigned peers = __match_any_sync(0xffffffffu, d);
+      if (valid && (peers & gp_lanemask_lt()) == 0) wh[w][d] += __popc(peers);
+      __syncwarp();
+    }
   }
   for (int d = lane; d < GP_RS_RADIX; d += 32) hist[(size_t)d * GP_RS_GV + gw] = wh[w][d];
 }

@@ -15,6 +15,7 @@
 //    output tensor needs a memset (the reference zero-fills 300 B per Gaussian per call,
 //    rasterize_points.cu:153-161).
 #include "gmath.cuh"
+#include "raster_common.cuh"
 #include "raster_state.cuh"
 
 // packed per-Gaussian accumulator filled by the blend backward: 12 floats
@@ -67,6 +68,7 @@ gp_render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
   __shared__ float4 s_rgb[GP_TILE_PIX];
   __shared__ int s_id[GP_TILE_PIX];
   __shared__ float s_acc[GP_TILE_PIX * GP_GREC];
+  __shared__ unsigned s_mask[GP_TILE_PIX];
 
   if (hdr[GP_HDR_OVERFLOW]) return;
   const int t = threadIdx.x, w = t >> 5, lane = t & 31;
@@ -84,7 +86,7 @@ gp_render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
 
   const float T_final = inside ? final_Ts[pix_id] : 0.f;
   float T = T_final;
-  uint32_t contributor = toDo;
+  const int total = toDo;
   const uint32_t last_contributor = inside ? n_contrib[pix_id] : 0u;
 
   float accum0 = 0.f, accum1 = 0.f, accum2 = 0.f;
@@ -105,27 +107,38 @@ gp_render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) warp_last = max(warp_last, __shfl_xor_sync(0xffffffffu, warp_last, o));
 
+  const float tile_fx0 = (float)(tile_x * GP_TILE_X), tile_fy0 = (float)(tile_y * GP_TILE_Y);
   for (int i = 0; i < rounds; i++, toDo -= GP_TILE_PIX) {
     __syncthreads();
     const int progress = i * GP_TILE_PIX + t;
+    unsigned pmask = 0u;
     if (range.x + progress < range.y) {
       const int id = point_list[range.y - progress - 1];
       s_id[t] = id;
-      s_co[t] = __ldg(conic_opacity + id);
-      s_xyd[t] = __ldg(xy_depth + id);
+      const float4 co = __ldg(conic_opacity + id);
+      const float4 xyd = __ldg(xy_depth + id);
+      s_co[t] = co;
+      s_xyd[t] = xyd;
       if (colors_precomp != nullptr)
         s_rgb[t] = make_float4(colors_precomp[3 * (size_t)id], colors_precomp[3 * (size_t)id + 1],
                                colors_precomp[3 * (size_t)id + 2], 0.f);
       else
         s_rgb[t] = __ldg(rgb4 + id);
+      pmask = gp_patch_mask(co, xyd.x, xyd.y, tile_fx0, tile_fy0);
     }
+    s_mask[t] = pmask;
 #pragma unroll
     for (int k = 0; k < GP_GREC; k++) s_acc[k * GP_TILE_PIX + t] = 0.f;
     __syncthreads();
 
     const int nb = min(GP_TILE_PIX, toDo);
-    for (int j = 0; j < nb; j++) {
-      contributor--;
+    for (int c0 = 0; c0 < nb; c0 += 32) {
+      unsigned bits = __ballot_sync(0xffffffffu, (s_mask[c0 + lane] >> w) & 1u);
+      while (bits) {
+      const int j = c0 + __ffs(bits) - 1;
+      bits &= bits - 1;
+      // 0-based position of this Gaussian in the tile's front-to-back list
+      const uint32_t contributor = (uint32_t)(total - 1 - (i * GP_TILE_PIX + j));
       if (contributor >= warp_last) continue;  // warp-uniform: nobody in this warp reaches it
       bool active = inside && contributor < last_contributor;
       const float4 xyd = s_xyd[j];
@@ -190,6 +203,7 @@ gp_render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
         atomicAdd(&s_acc[slot * GP_TILE_PIX + j], r);
       }
       if (lane == 1) atomicAdd(&s_acc[5 * GP_TILE_PIX + j], v_op);
+      }
     }
     __syncthreads();
     if (t < nb) {

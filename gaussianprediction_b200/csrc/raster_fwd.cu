@@ -15,6 +15,7 @@
 //  * The blend kernel stages colour and depth in shared memory with the conic, so the inner loop
 //    touches no global memory.
 #include "gmath.cuh"
+#include "raster_common.cuh"
 #include "raster_state.cuh"
 
 // ------------------------------------------------------------------------------------------------
@@ -333,6 +334,7 @@ gp_render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
   __shared__ float4 s_xyd[GP_TILE_PIX];
   __shared__ float4 s_rgb[GP_TILE_PIX];
   __shared__ int s_id[GP_TILE_PIX];
+  __shared__ unsigned s_mask[GP_TILE_PIX];
 
   if (hdr[GP_HDR_OVERFLOW]) return;
   const int t = threadIdx.x, w = t >> 5, lane = t & 31;
@@ -350,57 +352,69 @@ gp_render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
   bool done = !inside;
 
   float T = 1.0f;
-  uint32_t contributor = 0, last_contributor = 0;
+  uint32_t last_contributor = 0;
   float C0 = 0.f, C1 = 0.f, C2 = 0.f;
   float Dm = 15.0f;  // median-depth sentinel of this fork (forward.cu:310)
   int tid = -1;
 
+  const float tile_fx0 = (float)(tile_x * GP_TILE_X), tile_fy0 = (float)(tile_y * GP_TILE_Y);
   for (int i = 0; i < rounds; i++, toDo -= GP_TILE_PIX) {
     const int num_done = __syncthreads_count(done);
     if (num_done == GP_TILE_PIX) break;
     const int progress = i * GP_TILE_PIX + t;
+    unsigned pmask = 0u;
     if (range.x + progress < range.y) {
       const int id = point_list[range.x + progress];
       s_id[t] = id;
-      s_co[t] = __ldg(conic_opacity + id);
-      s_xyd[t] = __ldg(xy_depth + id);
+      const float4 co = __ldg(conic_opacity + id);
+      const float4 xyd = __ldg(xy_depth + id);
+      s_co[t] = co;
+      s_xyd[t] = xyd;
       if (colors_precomp != nullptr)
         s_rgb[t] = make_float4(colors_precomp[3 * (size_t)id], colors_precomp[3 * (size_t)id + 1],
                                colors_precomp[3 * (size_t)id + 2], 0.f);
       else
         s_rgb[t] = __ldg(rgb4 + id);
+      pmask = gp_patch_mask(co, xyd.x, xyd.y, tile_fx0, tile_fy0);
     }
+    s_mask[t] = pmask;
     __syncthreads();
     const int nb = min(GP_TILE_PIX, toDo);
-    for (int j = 0; !done && j < nb; j++) {
-      contributor++;
-      const float4 xyd = s_xyd[j];
-      const float4 co = s_co[j];
-      const float dx = xyd.x - pixfx;
-      const float dy = xyd.y - pixfy;
-      const float qa = __fmul_rn(co.x, dx);
-      const float qb = __fmul_rn(__fmul_rn(co.z, dy), dy);
-      const float qs = __fmaf_rn(qa, dx, qb);
-      const float qc = __fmul_rn(__fmul_rn(co.y, dx), dy);
-      const float power = __fmaf_rn(qs, -0.5f, -qc);
-      if (power > 0.0f) continue;
-      const float alpha = fminf(0.99f, __fmul_rn(co.w, expf(power)));
-      if (alpha < 1.0f / 255.0f) continue;
-      const float test_T = __fmul_rn(T, __fadd_rn(1.0f, -alpha));
-      if (test_T < 0.0001f) {
-        done = true;
-        continue;
+    for (int c0 = 0; c0 < nb; c0 += 32) {
+      if (__all_sync(0xffffffffu, done)) break;
+      unsigned bits = __ballot_sync(0xffffffffu, (s_mask[c0 + lane] >> w) & 1u);
+      while (bits) {
+        const int j = c0 + __ffs(bits) - 1;
+        bits &= bits - 1;
+        if (done) continue;
+        const float4 xyd = s_xyd[j];
+        const float4 co = s_co[j];
+        const float dx = xyd.x - pixfx;
+        const float dy = xyd.y - pixfy;
+        const float qa = __fmul_rn(co.x, dx);
+        const float qb = __fmul_rn(__fmul_rn(co.z, dy), dy);
+        const float qs = __fmaf_rn(qa, dx, qb);
+        const float qc = __fmul_rn(__fmul_rn(co.y, dx), dy);
+        const float power = __fmaf_rn(qs, -0.5f, -qc);
+        if (power > 0.0f) continue;
+        const float alpha = fminf(0.99f, __fmul_rn(co.w, expf(power)));
+        if (alpha < 1.0f / 255.0f) continue;
+        const float test_T = __fmul_rn(T, __fadd_rn(1.0f, -alpha));
+        if (test_T < 0.0001f) {
+          done = true;
+          continue;
+        }
+        const float4 col = s_rgb[j];
+        C0 = __fmaf_rn(T, __fmul_rn(alpha, col.x), C0);
+        C1 = __fmaf_rn(T, __fmul_rn(alpha, col.y), C1);
+        C2 = __fmaf_rn(T, __fmul_rn(alpha, col.z), C2);
+        if (T > 0.5f && test_T < 0.5f) {
+          Dm = xyd.z;
+          tid = s_id[j];
+        }
+        T = test_T;
+        last_contributor = (uint32_t)(i * GP_TILE_PIX + j + 1);  // position in the tile list, 1-based
       }
-      const float4 col = s_rgb[j];
-      C0 = __fmaf_rn(T, __fmul_rn(alpha, col.x), C0);
-      C1 = __fmaf_rn(T, __fmul_rn(alpha, col.y), C1);
-      C2 = __fmaf_rn(T, __fmul_rn(alpha, col.z), C2);
-      if (T > 0.5f && test_T < 0.5f) {
-        Dm = xyd.z;
-        tid = s_id[j];
-      }
-      T = test_T;
-      last_contributor = contributor;
     }
   }
   if (inside) {

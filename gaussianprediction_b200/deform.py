@@ -273,7 +273,7 @@ class KeypointDeformation(nn.Module):
             delta_xyz, delta_q, _ = self.get_motion_delta(xyz_embed, self.motion_feature, t)
             if args.norm_rotation:
                 delta_q = normalize(delta_q)
-            self.kpts_xyz_motion, self.kpts_rotation_motion = delta_xyz, delta_q
+            self.kpts_xyz_motion, self.kpts_rotation_motion = delta_xyz.detach(), delta_q.detach()
             xyz = self._xyz + delta_xyz
             q = normalize(quat_mul(normalize(delta_q), self._rotation))
             s, opacity = self.get_scaling, self.get_opacity
@@ -289,7 +289,9 @@ class KeypointDeformation(nn.Module):
             delta_xyz, delta_q, _ = self.get_motion_delta(xyz_embed, self.super_gaussians_feature, t)
             if args.norm_rotation:
                 delta_q = normalize(delta_q)
-            self.kpts_xyz_motion, self.kpts_rotation_motion = delta_xyz, delta_q
+            # detached: the readers (motion_model/dataset.py:120-123) only take values, and a live reference would keep
+            # this frame's autograd graph (and its stream-bound AccumulateGrad nodes) alive across iterations
+            self.kpts_xyz_motion, self.kpts_rotation_motion = delta_xyz.detach(), delta_q.detach()
             xyz, q, s, opacity = keypoint_blend(logits, self._idx32, delta_xyz, delta_q, self._xyz, self._rotation,
                                                 self._scaling, self._opacity)
         self.lifecycle_opacity = None

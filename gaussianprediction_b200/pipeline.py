@@ -72,6 +72,7 @@ class TrainStep:
             self._body()
         from . import rasterizer as _r
         self._state = _r.LAST_STATE          # workspaces of the captured frame (static addresses)
+        self.grads = [p.grad for p in self.params]   # the tensors the graph writes; re-attached after every replay
         torch.cuda.synchronize(dev)
 
     def overflowed(self):
@@ -91,6 +92,8 @@ class TrainStep:
         self.t.copy_(t, non_blocking=non_blocking)
         self.target.copy_(target, non_blocking=non_blocking)
         self.graph.replay()
+        for p, g in zip(self.params, self.grads):     # p.grad may have been replaced / cleared by the caller
+            p.grad = g
         return self.loss
 
     @property
