@@ -159,10 +159,7 @@ class OurRunner:
         self.grads_dev = [g.to(dev) for g in grads]
         self.bg = torch.zeros(3, device=dev)
         self.capacity = None
-        self.flat_grad = None
-        if world > 1:
-            n = sum(p.numel() for p in self.params)
-            self.flat_grad = torch.zeros(n, device=dev)
+        self.reducer = None
         self.h2d_bytes = grads[0].numel() * 4 + (16 + 16 + 3 + 1) * 4
         self.d2h_bytes = 4
 
@@ -202,21 +199,10 @@ class OurRunner:
         return loss
 
     def allreduce(self):
-        import torch.distributed as dist
-        off = 0
-        views = []
-        for p in self.params:
-            n = p.numel()
-            v = self.flat_grad[off:off + n]
-            if p.grad is None:
-                v.zero_()
-            else:
-                v.copy_(p.grad.reshape(-1))
-            views.append(v)
-            off += n
-        dist.all_reduce(self.flat_grad, op=dist.ReduceOp.SUM)
-        for p, v in zip(self.params, views):
-            p.grad = v.view_as(p)
+        if self.reducer is None:
+            from gaussianprediction_b200.parallel import FlatGradAllReduce
+            self.reducer = FlatGradAllReduce(self.params)
+        self.reducer.reduce()
 
     def eval_fps(self, steps, graph=False):
         """Forward-only render FPS in the reference's own span (eval.py:210-214: sync, render(), sync)."""

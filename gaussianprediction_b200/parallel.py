@@ -1,0 +1,58 @@
+"""Data-parallel plumbing for the frame loop (one process per GPU, torch.distributed over NCCL / NVLink).
+
+The path shards by (camera, timestep) sample: parameters are replicated, every rank renders its own
+samples, and one exchange per optimizer step sums the parameter gradients.  The reference has no distributed code;
+its single-GPU analogue is the ``--batch`` accumulation of train.py:113-133, which SUMS the losses of consecutive
+samples -- hence ``all_reduce(SUM)`` with no averaging -- and keeps ``max`` of the radii and ``or`` of the visibility
+masks (train.py:122-123).  Evaluation / extrapolation frames shard with no communication at all.
+"""
+import torch
+import torch.distributed as dist
+
+
+def shard_samples(n_samples, rank, world_size):
+    """Indices of the samples rank ``rank`` renders: r, r + W, r + 2W, ... (frames f = r mod W)."""
+    return list(range(rank, n_samples, world_size))
+
+
+class FlatGradAllReduce:
+    """One flat buffer for all parameter gradients -> a single all-reduce per step.
+
+    ``reduce()`` packs ``p.grad`` of every parameter into the buffer (zeros where a parameter got no gradient on
+    this rank), sums it over the process group and points ``p.grad`` at views of the reduced buffer, so every rank
+    ends the step with identical gradients (and, with identical optimizer state, identical parameters)."""
+
+    def __init__(self, params, group=None):
+        self.params = [p for p in params if p.requires_grad]
+        self.group = group
+        n = sum(p.numel() for p in self.params)
+        p0 = self.params[0]
+        self.flat = torch.zeros(n, dtype=p0.dtype, device=p0.device)
+        self.views = []
+        off = 0
+        for p in self.params:
+            self.views.append(self.flat[off:off + p.numel()].view_as(p))
+            off += p.numel()
+
+    @property
+    def nbytes(self):
+        return self.flat.numel() * self.flat.element_size()
+
+    def reduce(self, async_op=False):
+        for p, v in zip(self.params, self.views):
+            if p.grad is None:
+                v.zero_()
+            elif p.grad.data_ptr() != v.data_ptr():
+                v.copy_(p.grad)
+        work = dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=self.group, async_op=async_op)
+        for p, v in zip(self.params, self.views):
+            p.grad = v
+        return work
+
+
+def reduce_densification_stats(radii, visibility_filter, group=None):
+    """``radii = max over samples``, ``visibility = or over samples`` (train.py:122-123) across ranks, in place."""
+    dist.all_reduce(radii, op=dist.ReduceOp.MAX, group=group)
+    vis = visibility_filter.to(torch.int32)
+    dist.all_reduce(vis, op=dist.ReduceOp.MAX, group=group)
+    return radii, vis.bool()

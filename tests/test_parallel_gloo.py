@@ -1,0 +1,50 @@
+"""Host-side multi-rank logic on CPU: gloo backend, world_size 2 (the GPU path uses the same code over NCCL)."""
+import os
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+
+def _worker(rank, world, port, out):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from gaussianprediction_b200.parallel import FlatGradAllReduce, reduce_densification_stats, shard_samples
+    torch.manual_seed(0)                                    # replicated parameters
+    params = [torch.nn.Parameter(torch.randn(5, 3)), torch.nn.Parameter(torch.randn(7)), torch.nn.Parameter(torch.randn(2, 2))]
+    n_samples = 8
+    mine = shard_samples(n_samples, rank, world)
+    # per-sample "loss": deterministic function of the sample index; losses of a step are summed (train.py:113-133)
+    loss = sum(((s + 1) * (params[0] ** 2).sum() + (s + 2) * params[1].sum()) for s in mine)
+    loss.backward()                                         # params[2] gets no gradient on any rank
+    red = FlatGradAllReduce(params)
+    red.reduce()
+    radii = torch.tensor([rank + 1, 5 - rank, 0], dtype=torch.int32)
+    vis = torch.tensor([rank == 0, rank == 1, False])
+    radii, vis = reduce_densification_stats(radii, vis)
+    if rank == 0:
+        torch.save(dict(g0=params[0].grad.clone(), g1=params[1].grad.clone(), g2=params[2].grad.clone(), mine=mine,
+                        radii=radii, vis=vis, same_storage=params[0].grad.data_ptr() == red.views[0].data_ptr(),
+                        nbytes=red.nbytes), out)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_sample_sharding_and_flat_allreduce_gloo(tmp_path):
+    from gaussianprediction_b200.parallel import shard_samples
+    assert shard_samples(8, 1, 2) == [1, 3, 5, 7] and shard_samples(5, 3, 4) == [3] and shard_samples(3, 3, 4) == []
+    allidx = sorted(sum((shard_samples(10, r, 4) for r in range(4)), []))
+    assert allidx == list(range(10))                        # every sample rendered exactly once
+    out = str(tmp_path / "r0.pt")
+    port = 29500 + (os.getpid() % 2000)
+    mp.spawn(_worker, args=(2, port, out), nprocs=2, join=True)
+    r = torch.load(out)
+    torch.manual_seed(0)
+    p0, p1 = torch.randn(5, 3), torch.randn(7)
+    w0 = sum(s + 1 for s in range(8))
+    w1 = sum(s + 2 for s in range(8))
+    assert torch.allclose(r["g0"], 2 * w0 * p0) and torch.allclose(r["g1"], torch.full((7,), float(w1)))
+    assert float(r["g2"].abs().sum()) == 0 and r["mine"] == [0, 2, 4, 6] and r["same_storage"] and r["nbytes"] == 26 * 4
+    assert r["radii"].tolist() == [2, 5, 0] and r["vis"].tolist() == [True, True, False]
