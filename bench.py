@@ -145,6 +145,7 @@ class OurRunner:
         from gaussianprediction_b200.deform import KeypointDeformation
         from gaussianprediction_b200.renderer import SceneModel
         self.wl, self.dev, self.world = wl, dev, world
+        self.rank = int(os.environ.get("RANK", "0")) if world > 1 else 0
         gs, kp, kf, logits, cams, times, grads = build_inputs(wl, ncams)
         torch.manual_seed(2024)
         deform = KeypointDeformation(model_args(), gs.xyz, gs.rotation, gs.scaling, gs.opacity, gs.motion_feature, kp, kf,
@@ -165,6 +166,7 @@ class OurRunner:
 
     def step(self, i, host_inputs=False):
         from gaussianprediction_b200.renderer import render
+        i = i * self.world + self.rank          # samples r, r + W, r + 2W, ... of the global sequence (parallel.shard_samples)
         k = i % len(self.cams_dev)
         if host_inputs:
             cam = cam_to(self.cams_host[k], self.dev, non_blocking=True)
@@ -188,6 +190,7 @@ class OurRunner:
         self.render_step = RenderStep(self.pc, self.cams_dev[0], self.capacity, bg=self.bg, iteration=ITER)
 
     def step_graph(self, i, host_inputs=False):
+        i = i * self.world + self.rank
         k = i % len(self.cams_dev)
         if host_inputs:
             cam, t, G = self.cams_host[k], self.times_host[k:k + 1], self.grads_host[i % len(self.grads_host)]
