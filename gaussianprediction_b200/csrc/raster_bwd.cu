@@ -23,6 +23,7 @@
 //   [4] dL/dconic.w   [5] dL/dopacity   [6] dL/dr        [7] dL/dg
 //   [8] dL/db         [9..11] unused
 #define GP_GREC 12
+#define GP_SACC 9
 
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
@@ -56,7 +57,7 @@ __device__ __forceinline__ float warp_transpose_reduce8(float (&v)[8], int lane)
   return r;  // component index = ((lane>>4)&1)*4 + ((lane>>3)&1)*2 + ((lane>>2)&1)
 }
 
-__global__ void __launch_bounds__(GP_TILE_PIX)
+__global__ void __launch_bounds__(GP_TILE_PIX, 4)
 gp_render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H,
                      unsigned grid_x, const float* __restrict__ bg_color, const float4* __restrict__ xy_depth,
                      const float4* __restrict__ conic_opacity, const float4* __restrict__ rgb4,
@@ -67,7 +68,7 @@ gp_render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
   __shared__ float4 s_xyd[GP_TILE_PIX];
   __shared__ float4 s_rgb[GP_TILE_PIX];
   __shared__ int s_id[GP_TILE_PIX];
-  __shared__ float s_acc[GP_TILE_PIX * GP_GREC];
+  __shared__ float s_acc[GP_TILE_PIX * GP_SACC];  // [Gaussian in batch][9 sums]; odd stride: conflict-free both ways
   __shared__ unsigned s_mask[GP_TILE_PIX];
 
   if (hdr[GP_HDR_OVERFLOW]) return;
@@ -128,7 +129,7 @@ gp_render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
     }
     s_mask[t] = pmask;
 #pragma unroll
-    for (int k = 0; k < GP_GREC; k++) s_acc[k * GP_TILE_PIX + t] = 0.f;
+    for (int k = 0; k < GP_SACC; k++) s_acc[k * GP_TILE_PIX + t] = 0.f;
     __syncthreads();
 
     const int nb = min(GP_TILE_PIX, toDo);
@@ -193,24 +194,32 @@ gp_render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
         v[7] = dchannel_dcolor * dpx2;
         v_op = G * dL_dalpha;
       }
-      const float r = warp_transpose_reduce8(v, lane);
+      float* acc = s_acc + j * GP_SACC;   // slots: 0..4 = v[0..4], 5 = opacity, 6..8 = colour
+      const unsigned amask = __ballot_sync(0xffffffffu, active);
+      if (__popc(amask) <= 2) {
+        // one or two pixels of this patch see the Gaussian: adding them directly is cheaper than a 32-lane reduction
+        if (active) {
+          atomicAdd(acc + 0, v[0]); atomicAdd(acc + 1, v[1]); atomicAdd(acc + 2, v[2]);
+          atomicAdd(acc + 3, v[3]); atomicAdd(acc + 4, v[4]); atomicAdd(acc + 5, v_op);
+          atomicAdd(acc + 6, v[5]); atomicAdd(acc + 7, v[6]); atomicAdd(acc + 8, v[7]);
+        }
+      } else {
+        const float r = warp_transpose_reduce8(v, lane);
 #pragma unroll
-      for (int o = 16; o > 0; o >>= 1) v_op += __shfl_xor_sync(0xffffffffu, v_op, o);
-      if ((lane & 3) == 0) {
-        const int comp = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
-        // record slots: comps 0..4 -> 0..4, colours 5..7 -> 6..8, opacity -> 5
-        const int slot = comp < 5 ? comp : comp + 1;
-        atomicAdd(&s_acc[slot * GP_TILE_PIX + j], r);
+        for (int o = 16; o > 0; o >>= 1) v_op += __shfl_xor_sync(0xffffffffu, v_op, o);
+        if ((lane & 3) == 0) {
+          const int comp = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
+          atomicAdd(acc + (comp < 5 ? comp : comp + 1), r);
+        }
+        if (lane == 1) atomicAdd(acc + 5, v_op);
       }
-      if (lane == 1) atomicAdd(&s_acc[5 * GP_TILE_PIX + j], v_op);
       }
     }
     __syncthreads();
     if (t < nb) {
       float* dst = grec + (size_t)s_id[t] * GP_GREC;
-      const float a0 = s_acc[0 * GP_TILE_PIX + t], a1 = s_acc[1 * GP_TILE_PIX + t], a2 = s_acc[2 * GP_TILE_PIX + t],
-                  a3 = s_acc[3 * GP_TILE_PIX + t], a4 = s_acc[4 * GP_TILE_PIX + t], a5 = s_acc[5 * GP_TILE_PIX + t],
-                  a6 = s_acc[6 * GP_TILE_PIX + t], a7 = s_acc[7 * GP_TILE_PIX + t], a8 = s_acc[8 * GP_TILE_PIX + t];
+      const float* ac = s_acc + t * GP_SACC;
+      const float a0 = ac[0], a1 = ac[1], a2 = ac[2], a3 = ac[3], a4 = ac[4], a5 = ac[5], a6 = ac[6], a7 = ac[7], a8 = ac[8];
       if (a0 != 0.f || a1 != 0.f || a2 != 0.f || a3 != 0.f) red_add_v4(dst, a0, a1, a2, a3);
       if (a4 != 0.f || a5 != 0.f || a6 != 0.f || a7 != 0.f) red_add_v4(dst + 4, a4, a5, a6, a7);
       if (a8 != 0.f) atomicAdd(dst + 8, a8);
