@@ -68,8 +68,7 @@ gp_blend_fwd_kernel(int N, int Kp, int K, const float* __restrict__ logits, cons
   extern __shared__ __align__(16) float s_kp[];
   stage_keypoints(s_kp, Kp, kp_dxyz, kp_dq);
   __syncthreads();
-  const int i = blockIdx.x * GP_BLEND_THREADS + threadIdx.x;
-  if (i >= N) return;
+  for (int i = blockIdx.x * GP_BLEND_THREADS + threadIdx.x; i < N; i += gridDim.x * GP_BLEND_THREADS) {
   float wx[GP_BLEND_KMAX], wr[GP_BLEND_KMAX];
   const float* lg = logits + (size_t)i * 2 * K;
   softmax_k<GP_BLEND_KMAX>(lg, K, wx);
@@ -104,6 +103,7 @@ gp_blend_fwd_kernel(int N, int Kp, int K, const float* __restrict__ logits, cons
     s_t[(size_t)i * 3 + 2] = expf(scaling[(size_t)i * 3 + 2]);
   }
   if (o_t) o_t[i] = 1.0f / (1.0f + expf(-opacity[i]));
+  }
 }
 
 // d/dv of normalize(v) = v / max(|v|, eps), applied to an upstream gradient g
@@ -128,12 +128,11 @@ gp_blend_bwd_kernel(int N, int Kp, int K, const float* __restrict__ logits, cons
                     float* __restrict__ g_opacity, float* __restrict__ g_kp_dxyz, float* __restrict__ g_kp_dq) {
   extern __shared__ __align__(16) float smem[];
   float* s_kp = smem;            // [Kp][8]
-  float* s_g = smem + Kp * 8;    // [Kp][8] gradient accumulators
+  float* s_g = smem + Kp * 8;    // [Kp][9] gradient accumulators (7 used; odd stride spreads the banks)
   stage_keypoints(s_kp, Kp, kp_dxyz, kp_dq);
-  for (int e = threadIdx.x; e < Kp * 8; e += blockDim.x) s_g[e] = 0.f;
+  for (int e = threadIdx.x; e < Kp * 9; e += blockDim.x) s_g[e] = 0.f;
   __syncthreads();
-  const int i = blockIdx.x * GP_BLEND_THREADS + threadIdx.x;
-  if (i < N) {
+  for (int i = blockIdx.x * GP_BLEND_THREADS + threadIdx.x; i < N; i += gridDim.x * GP_BLEND_THREADS) {
     float wx[GP_BLEND_KMAX], wr[GP_BLEND_KMAX];
     int jj[GP_BLEND_KMAX];
     const float* lg = logits + (size_t)i * 2 * K;
@@ -191,10 +190,10 @@ gp_blend_bwd_kernel(int N, int Kp, int K, const float* __restrict__ logits, cons
           const float4 b = *(const float4*)(s_kp + 8 * j + 4);
           gwx[k] = gx * a.x + gy * a.y + gz * a.z;
           gwr[k] = gdq.x * b.x + gdq.y * b.y + gdq.z * b.z + gdq.w * b.w;
-          float* ga = s_g + 8 * j;
+          float* ga = s_g + 9 * j;
           atomicAdd(ga + 0, wx[k] * gx); atomicAdd(ga + 1, wx[k] * gy); atomicAdd(ga + 2, wx[k] * gz);
-          atomicAdd(ga + 4, wr[k] * gdq.x); atomicAdd(ga + 5, wr[k] * gdq.y);
-          atomicAdd(ga + 6, wr[k] * gdq.z); atomicAdd(ga + 7, wr[k] * gdq.w);
+          atomicAdd(ga + 3, wr[k] * gdq.x); atomicAdd(ga + 4, wr[k] * gdq.y);
+          atomicAdd(ga + 5, wr[k] * gdq.z); atomicAdd(ga + 6, wr[k] * gdq.w);
         }
         sx += wx[k] * gwx[k];
         sr += wr[k] * gwr[k];
@@ -220,12 +219,12 @@ gp_blend_bwd_kernel(int N, int Kp, int K, const float* __restrict__ logits, cons
     }
   }
   __syncthreads();
-  for (int e = threadIdx.x; e < Kp * 8; e += blockDim.x) {
-    const float v = s_g[e];
+  for (int e = threadIdx.x; e < Kp * 7; e += blockDim.x) {
+    const int j = e / 7, c = e - j * 7;
+    const float v = s_g[9 * j + c];
     if (v != 0.f) {
-      const int j = e >> 3, c = e & 7;
       if (c < 3) atomicAdd(g_kp_dxyz + (size_t)j * 3 + c, v);
-      else if (c >= 4) atomicAdd(g_kp_dq + (size_t)j * 4 + (c - 4), v);
+      else atomicAdd(g_kp_dq + (size_t)j * 4 + (c - 3), v);
     }
   }
 }
@@ -254,10 +253,16 @@ gp_dense_weights_kernel(int N, int Kp, int K, const float* __restrict__ logits, 
   }
 }
 
+// persistent grid: two blocks per SM, each staging the keypoint table once and flushing its keypoint gradients once
+static int gp_blend_grid(int N) {
+  const int need = (N + GP_BLEND_THREADS - 1) / GP_BLEND_THREADS;
+  return need < 148 * 2 ? need : 148 * 2;
+}
+
 static int blend_check(int N, int Kp, int K) {
   if (N < 0 || Kp < 0 || K < 1) return GP_ERR_BAD_ARG;
   if (K > GP_BLEND_KMAX) return GP_ERR_UNSUPPORTED;
-  if ((size_t)Kp * 16 * 4 > 200 * 1024) return GP_ERR_UNSUPPORTED;  // keypoint table must fit in shared memory
+  if ((size_t)Kp * 17 * 4 > 200 * 1024) return GP_ERR_UNSUPPORTED;  // keypoint table must fit in shared memory
   return GP_OK;
 }
 
@@ -274,7 +279,7 @@ extern "C" int gp_blend_forward(int N, int Kp, int K, const float* logits, const
   const size_t smem = (size_t)Kp * 8 * 4;
   if (smem > 48 * 1024)
     GP_CUDA_TRY(cudaFuncSetAttribute(gp_blend_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  GP_KERNEL("gp_blend_fwd_kernel", (cudaStream_t)stream_, gp_blend_fwd_kernel<<<(N + GP_BLEND_THREADS - 1) / GP_BLEND_THREADS, GP_BLEND_THREADS, smem, (cudaStream_t)stream_>>>(
+  GP_KERNEL("gp_blend_fwd_kernel", (cudaStream_t)stream_, gp_blend_fwd_kernel<<<gp_blend_grid(N), GP_BLEND_THREADS, smem, (cudaStream_t)stream_>>>(
       N, Kp, K, logits, idx32, idx64, kp_delta_xyz, kp_delta_q, xyz, rot, scaling, opacity, xyz_t, q_t, s_t, o_t));
   GP_LAUNCH_CHECK();
   return GP_OK;
@@ -294,10 +299,10 @@ extern "C" int gp_blend_backward(int N, int Kp, int K, const float* logits, cons
   if (N == 0) return GP_OK;
   if (!logits || (!idx32 && !idx64) || !rot || !kp_delta_xyz || !kp_delta_q) return GP_ERR_BAD_ARG;
   if ((g_scaling && g_s_t && !s_t) || (g_opacity && !o_t)) return GP_ERR_BAD_ARG;
-  const size_t smem = (size_t)Kp * 16 * 4;
+  const size_t smem = (size_t)Kp * 17 * 4;
   if (smem > 48 * 1024)
     GP_CUDA_TRY(cudaFuncSetAttribute(gp_blend_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  GP_KERNEL("gp_blend_bwd_kernel", stream, gp_blend_bwd_kernel<<<(N + GP_BLEND_THREADS - 1) / GP_BLEND_THREADS, GP_BLEND_THREADS, smem, stream>>>(
+  GP_KERNEL("gp_blend_bwd_kernel", stream, gp_blend_bwd_kernel<<<gp_blend_grid(N), GP_BLEND_THREADS, smem, stream>>>(
       N, Kp, K, logits, idx32, idx64, kp_delta_xyz, kp_delta_q, rot, s_t, o_t, g_xyz_t, g_q_t, g_s_t, g_o_t, g_logits,
       g_xyz, g_rot, g_scaling, g_opacity, g_kp_delta_xyz, g_kp_delta_q));
   GP_LAUNCH_CHECK();

@@ -15,6 +15,7 @@
 // keypoint index (the reference's tie order depends on an atomicAdd race).
 #include "../../include/gp_b200.h"
 #include "common.cuh"
+#include "radix_sort.cuh"
 
 #define GP_KNN_THREADS 256
 
@@ -72,17 +73,21 @@ struct TopK {
 // D floats of q_points.  Same for the keypoints.  D is a template parameter for the two shapes the
 // repo uses (3 and 35); D == 0 selects the generic runtime-D path (query re-read from L1).
 template <int D, int KT>
-__global__ void __launch_bounds__(GP_KNN_THREADS)
+__global__ void __launch_bounds__(GP_KNN_THREADS, 3)
 gp_knn_kernel(int N, int Kp, int Drt, int K, const float* __restrict__ q_points, const float* __restrict__ q_feat,
               const float* __restrict__ r_points, const float* __restrict__ r_feat, int F, float amplify, float r2,
-              int kp_chunk, long long* __restrict__ idx64, int* __restrict__ idx32, float* __restrict__ dists) {
+              int kp_chunk, const int* __restrict__ order, long long* __restrict__ idx64, int* __restrict__ idx32,
+              float* __restrict__ dists) {
   extern __shared__ __align__(16) float s_ref[];  // [kp_chunk][DP]
   constexpr int DD = D > 0 ? D : 1;
   const int Dn = D > 0 ? D : Drt;
   const int DP = (Dn + 3) & ~3;
-  const int q = blockIdx.x * GP_KNN_THREADS + threadIdx.x;
-  const bool valid = q < N;
-  const int qc = valid ? q : (N - 1);
+  const int slot = blockIdx.x * GP_KNN_THREADS + threadIdx.x;
+  const bool valid = slot < N;
+  // `order` (optional) is a permutation of the queries that puts spatial neighbours in the same warp, which makes
+  // the warp-wide early exit below fire for most keypoints.  It only changes which thread serves which query.
+  const int q = order ? order[valid ? slot : (N - 1)] : slot;
+  const int qc = order ? q : (valid ? slot : (N - 1));
 
   float qv[DD];
   if (D > 0) {
@@ -222,8 +227,8 @@ gp_knn_kernel(int N, int Kp, int Drt, int K, const float* __restrict__ q_points,
 
 template <int D, int KT>
 static int launch_knn(int N, int Kp, int Drt, int K, const float* q_points, const float* q_feat, const float* r_points,
-                      const float* r_feat, int F, float amplify, float r2, long long* idx64, int* idx32, float* dists,
-                      cudaStream_t stream) {
+                      const float* r_feat, int F, float amplify, float r2, const int* order, long long* idx64, int* idx32,
+                      float* dists, cudaStream_t stream) {
   const int Dn = D > 0 ? D : Drt;
   const int DP = (Dn + 3) & ~3;
   const size_t max_smem = 200 * 1024;
@@ -234,17 +239,17 @@ static int launch_knn(int N, int Kp, int Drt, int K, const float* q_points, cons
   auto kern = gp_knn_kernel<D, KT>;
   if (smem > 48 * 1024) GP_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   GP_KERNEL("gp_knn_kernel", stream, kern<<<(N + GP_KNN_THREADS - 1) / GP_KNN_THREADS, GP_KNN_THREADS, smem, stream>>>(
-      N, Kp, Drt, K, q_points, q_feat, r_points, r_feat, F, amplify, r2, kp_chunk, idx64, idx32, dists));
+      N, Kp, Drt, K, q_points, q_feat, r_points, r_feat, F, amplify, r2, kp_chunk, order, idx64, idx32, dists));
   GP_LAUNCH_CHECK();
   return GP_OK;
 }
 
 template <int D>
 static int knn_dispatch_k(int N, int Kp, int Drt, int K, const float* q_points, const float* q_feat,
-                          const float* r_points, const float* r_feat, int F, float amplify, float r2, long long* idx64,
-                          int* idx32, float* dists, cudaStream_t stream) {
+                          const float* r_points, const float* r_feat, int F, float amplify, float r2, const int* order,
+                          long long* idx64, int* idx32, float* dists, cudaStream_t stream) {
 #define GP_KNN_GO(KT) \
-  return launch_knn<D, KT>(N, Kp, Drt, K, q_points, q_feat, r_points, r_feat, F, amplify, r2, idx64, idx32, dists, stream)
+  return launch_knn<D, KT>(N, Kp, Drt, K, q_points, q_feat, r_points, r_feat, F, amplify, r2, order, idx64, idx32, dists, stream)
   switch (K) {
     case 1: GP_KNN_GO(1);
     case 2: GP_KNN_GO(2);
@@ -260,34 +265,145 @@ static int knn_dispatch_k(int N, int Kp, int Drt, int K, const float* q_points, 
 }
 
 static int knn_dispatch(int N, int Kp, int D, int K, const float* q_points, const float* q_feat, const float* r_points,
-                        const float* r_feat, int F, float amplify, float r, long long* idx64, int* idx32, float* dists,
-                        cudaStream_t stream) {
+                        const float* r_feat, int F, float amplify, float r, const int* order, long long* idx64, int* idx32,
+                        float* dists, cudaStream_t stream) {
   if (N < 0 || Kp < 0 || D < 1 || K < 1) return GP_ERR_BAD_ARG;
   if (K > 32) return GP_ERR_UNSUPPORTED;
   if (N == 0) return GP_OK;
   const float r2 = r * r;  // the reference passes r*r computed in float (frnn.py:176)
-  if (D == 3) return knn_dispatch_k<3>(N, Kp, D, K, q_points, q_feat, r_points, r_feat, F, amplify, r2, idx64, idx32, dists, stream);
-  if (D == 35) return knn_dispatch_k<35>(N, Kp, D, K, q_points, q_feat, r_points, r_feat, F, amplify, r2, idx64, idx32, dists, stream);
-  return knn_dispatch_k<0>(N, Kp, D, K, q_points, q_feat, r_points, r_feat, F, amplify, r2, idx64, idx32, dists, stream);
+  if (D == 3) return knn_dispatch_k<3>(N, Kp, D, K, q_points, q_feat, r_points, r_feat, F, amplify, r2, order, idx64, idx32, dists, stream);
+  if (D == 35) return knn_dispatch_k<35>(N, Kp, D, K, q_points, q_feat, r_points, r_feat, F, amplify, r2, order, idx64, idx32, dists, stream);
+  return knn_dispatch_k<0>(N, Kp, D, K, q_points, q_feat, r_points, r_feat, F, amplify, r2, order, idx64, idx32, dists, stream);
 }
 
 extern "C" int gp_knn_points(int N, int Kp, int D, int K, float r, const float* points1, const float* points2,
                              long long* idxs, float* dists, gp_stream_t stream) {
   if (N > 0 && (!points1 || !idxs)) return GP_ERR_BAD_ARG;
   if (Kp > 0 && !points2) return GP_ERR_BAD_ARG;
-  return knn_dispatch(N, Kp, D, K, points1, nullptr, points2, nullptr, 0, 1.0f, r, idxs, nullptr, dists,
+  return knn_dispatch(N, Kp, D, K, points1, nullptr, points2, nullptr, 0, 1.0f, r, nullptr, idxs, nullptr, dists,
                       (cudaStream_t)stream);
 }
 
 extern "C" int gp_knn_keypoints(int N, int Kp, int F, int K, float r, float feature_amplify, const float* xyz,
                                 const float* motion_feature, const float* kp_xyz, const float* kp_feature,
-                                long long* idx64, int* idx32, float* dists, gp_stream_t stream) {
+                                const int* order, long long* idx64, int* idx32, float* dists, gp_stream_t stream) {
   if (N > 0 && !xyz) return GP_ERR_BAD_ARG;
   if (Kp > 0 && !kp_xyz) return GP_ERR_BAD_ARG;
   if (F < 0 || (F > 0 && (!motion_feature || !kp_feature))) return GP_ERR_BAD_ARG;
   if (!idx64 && !idx32) return GP_ERR_BAD_ARG;
   if (F == 0)
-    return knn_dispatch(N, Kp, 3, K, xyz, nullptr, kp_xyz, nullptr, 0, 1.0f, r, idx64, idx32, dists, (cudaStream_t)stream);
-  return knn_dispatch(N, Kp, 3 + F, K, xyz, motion_feature, kp_xyz, kp_feature, F, feature_amplify, r, idx64, idx32,
-                      dists, (cudaStream_t)stream);
+    return knn_dispatch(N, Kp, 3, K, xyz, nullptr, kp_xyz, nullptr, 0, 1.0f, r, order, idx64, idx32, dists, (cudaStream_t)stream);
+  return knn_dispatch(N, Kp, 3 + F, K, xyz, motion_feature, kp_xyz, kp_feature, F, feature_amplify, r, order, idx64,
+                      idx32, dists, (cudaStream_t)stream);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Spatial (Morton) order of a point set: an acceleration hint for the search above.
+// ------------------------------------------------------------------------------------------------
+
+struct GpOrderWs {
+  int* bbox;  // 6 ordered ints + 1 count
+  uint32_t* keys[2];
+  uint32_t* vals[2];
+  GpRadixTemp radix;
+  size_t bytes;
+};
+static inline GpOrderWs gp_carve_order(void* ws, int N) {
+  GpCarver c(ws);
+  GpOrderWs w;
+  const size_t n = (size_t)(N > 0 ? N : 1);
+  w.bbox = c.take<int>(8);
+  w.keys[0] = c.take<uint32_t>(n);
+  w.keys[1] = c.take<uint32_t>(n);
+  w.vals[0] = c.take<uint32_t>(n);
+  w.vals[1] = c.take<uint32_t>(n);
+  w.radix.hist = c.take<uint32_t>((size_t)GP_RS_RADIX * GP_RS_GV);
+  w.radix.totals = c.take<uint32_t>(GP_RS_RADIX);
+  w.bytes = c.used();
+  return w;
+}
+__device__ __forceinline__ int gp_f2ord(float f) {
+  const int i = __float_as_int(f);
+  return i >= 0 ? i : i ^ 0x7fffffff;
+}
+__device__ __forceinline__ float gp_ord2f(int i) { return __int_as_float(i >= 0 ? i : i ^ 0x7fffffff); }
+
+__global__ void gp_order_init_kernel(int N, int* bbox) {
+  if (threadIdx.x < 3) bbox[threadIdx.x] = 0x7fffffff;
+  else if (threadIdx.x < 6) bbox[threadIdx.x] = (int)0x80000000;
+  else if (threadIdx.x == 6) bbox[6] = N;
+}
+__global__ void __launch_bounds__(256) gp_order_bbox_kernel(int N, const float* __restrict__ pts, int* bbox) {
+  float mn[3] = {3.4e38f, 3.4e38f, 3.4e38f}, mx[3] = {-3.4e38f, -3.4e38f, -3.4e38f};
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) {
+#pragma unroll
+    for (int a = 0; a < 3; a++) {
+      const float v = pts[(size_t)i * 3 + a];
+      mn[a] = fminf(mn[a], v);
+      mx[a] = fmaxf(mx[a], v);
+    }
+  }
+#pragma unroll
+  for (int a = 0; a < 3; a++) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      mn[a] = fminf(mn[a], __shfl_xor_sync(0xffffffffu, mn[a], o));
+      mx[a] = fmaxf(mx[a], __shfl_xor_sync(0xffffffffu, mx[a], o));
+    }
+  }
+  if ((threadIdx.x & 31) == 0) {
+#pragma unroll
+    for (int a = 0; a < 3; a++) {
+      atomicMin(&bbox[a], gp_f2ord(mn[a]));
+      atomicMax(&bbox[3 + a], gp_f2ord(mx[a]));
+    }
+  }
+}
+__device__ __forceinline__ uint32_t gp_spread10(uint32_t x) {
+  x &= 0x3ffu;
+  x = (x | (x << 16)) & 0x030000FFu;
+  x = (x | (x << 8)) & 0x0300F00Fu;
+  x = (x | (x << 4)) & 0x030C30C3u;
+  x = (x | (x << 2)) & 0x09249249u;
+  return x;
+}
+__global__ void __launch_bounds__(256)
+gp_order_code_kernel(int N, const float* __restrict__ pts, const int* __restrict__ bbox, uint32_t* __restrict__ keys,
+                     uint32_t* __restrict__ vals) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= N) return;
+  uint32_t c[3];
+#pragma unroll
+  for (int a = 0; a < 3; a++) {
+    const float lo = gp_ord2f(bbox[a]), hi = gp_ord2f(bbox[3 + a]);
+    const float ext = hi - lo;
+    float u = ext > 0.f ? (pts[(size_t)i * 3 + a] - lo) / ext : 0.f;
+    u = fminf(fmaxf(u, 0.f), 1.f);
+    c[a] = (uint32_t)(u * 1023.0f);
+  }
+  keys[i] = gp_spread10(c[0]) | (gp_spread10(c[1]) << 1) | (gp_spread10(c[2]) << 2);
+  vals[i] = (uint32_t)i;
+}
+__global__ void gp_order_copy_kernel(int N, const uint32_t* __restrict__ src, int* __restrict__ dst) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < N) dst[i] = (int)src[i];
+}
+
+extern "C" size_t gp_spatial_order_ws_bytes(int N) { return gp_carve_order(nullptr, N).bytes; }
+
+extern "C" int gp_spatial_order(int N, const float* xyz, int* order, void* ws, gp_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (N < 0) return GP_ERR_BAD_ARG;
+  if (N == 0) return GP_OK;
+  if (!xyz || !order || !ws) return GP_ERR_BAD_ARG;
+  GpOrderWs w = gp_carve_order(ws, N);
+  GP_KERNEL("gp_order_init_kernel", stream, gp_order_init_kernel<<<1, 32, 0, stream>>>(N, w.bbox));
+  GP_KERNEL("gp_order_bbox_kernel", stream, gp_order_bbox_kernel<<<148 * 2, 256, 0, stream>>>(N, xyz, w.bbox));
+  GP_KERNEL("gp_order_code_kernel", stream,
+            gp_order_code_kernel<<<(N + 255) / 256, 256, 0, stream>>>(N, xyz, w.bbox, w.keys[0], w.vals[0]));
+  const int sel = gp_radix_sort_pairs(w.keys, w.vals, w.bbox + 6, 0, 30, w.radix, stream);
+  GP_KERNEL("gp_order_copy_kernel", stream,
+            gp_order_copy_kernel<<<(N + 255) / 256, 256, 0, stream>>>(N, w.vals[sel], order));
+  GP_LAUNCH_CHECK();
+  return GP_OK;
 }

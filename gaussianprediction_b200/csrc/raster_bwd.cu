@@ -133,7 +133,10 @@ gp_render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
     __syncthreads();
 
     const int nb = min(GP_TILE_PIX, toDo);
-    for (int c0 = 0; c0 < nb; c0 += 32) {
+    // elements of this batch in front of index (total - warp_last) lie behind the last contributor of every pixel
+    // of this warp: start at the first 32-chunk that can matter
+    const int first = total - (int)warp_last - i * GP_TILE_PIX;
+    for (int c0 = max(first, 0) & ~31; c0 < nb; c0 += 32) {
       unsigned bits = __ballot_sync(0xffffffffu, (s_mask[c0 + lane] >> w) & 1u);
       while (bits) {
       const int j = c0 + __ffs(bits) - 1;
@@ -162,7 +165,9 @@ gp_render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
 #pragma unroll
       for (int k = 0; k < 8; k++) v[k] = 0.f;
       if (active) {
-        T = T / (1.f - alpha);
+        // one correctly rounded reciprocal serves both divisions by (1 - alpha) (reference backward.cu:503,533)
+        const float inv1ma = __frcp_rn(1.f - alpha);
+        T = T * inv1ma;
         const float dchannel_dcolor = alpha * T;
         const float4 col = s_rgb[j];
         float dL_dalpha = 0.0f;
@@ -177,7 +182,7 @@ gp_render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
         dL_dalpha += (col.z - accum2) * dpx2;
         dL_dalpha *= T;
         last_alpha = alpha;
-        dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot_dpixel;
+        dL_dalpha += (-T_final * inv1ma) * bg_dot_dpixel;
 
         const float dL_dG = co.w * dL_dalpha;
         const float gdx = G * dx;

@@ -86,10 +86,23 @@ def _need_cuda(*ts):
 
 
 @torch.no_grad()
+def spatial_order(xyz):
+    """Morton-order permutation of the points (int32 [N]): an optional speed hint for ``knn_keypoints``."""
+    _need_cuda(xyz)
+    N = int(xyz.shape[0])
+    order = torch.empty((N,), dtype=torch.int32, device=xyz.device)
+    if N:
+        L = _lib.lib()
+        ws = torch.empty((L.gp_spatial_order_ws_bytes(N),), dtype=torch.uint8, device=xyz.device)
+        check(L.gp_spatial_order(N, ptr(_c(xyz)), ptr(order), ptr(ws), _lib.stream_ptr()), "gp_spatial_order")
+    return order
+
+
+@torch.no_grad()
 def knn_keypoints(xyz, motion_feature, kp_xyz, kp_feature, K, knn_type="hybird", feature_amplify=5.0,
-                  return_dists=False, idx32_only=False):
+                  return_dists=False, idx32_only=False, order=None):
     """``get_nearest_mask`` (scene/gaussian_model.py:110-125) without the torch.cat and the FRNN grid set-up.
-    Returns (idx64 [N,K] or None, idx32 [N,K], dists or None)."""
+    Returns (idx64 [N,K] or None, idx32 [N,K], dists or None).  ``order``: optional ``spatial_order(xyz)``."""
     _need_cuda(xyz, kp_xyz)
     N, Kp = int(xyz.shape[0]), int(kp_xyz.shape[0])
     dev = xyz.device
@@ -103,7 +116,8 @@ def knn_keypoints(xyz, motion_feature, kp_xyz, kp_feature, K, knn_type="hybird",
     idx64 = None if idx32_only else torch.empty((N, K), dtype=torch.int64, device=dev)
     dists = torch.empty((N, K), dtype=torch.float32, device=dev) if return_dists else None
     check(_lib.lib().gp_knn_keypoints(N, Kp, F, int(K), float(r), float(feature_amplify), ptr(_c(xyz)), ptr(mf),
-                                      ptr(_c(kp_xyz)), ptr(kf), ptr(idx64), ptr(idx32), ptr(dists), _lib.stream_ptr()),
+                                      ptr(_c(kp_xyz)), ptr(kf), ptr(order), ptr(idx64), ptr(idx32), ptr(dists),
+                                      _lib.stream_ptr()),
           "gp_knn_keypoints")
     return idx64, idx32, dists
 
@@ -221,6 +235,9 @@ class KeypointDeformation(nn.Module):
         self._idx32 = None
         self._last_logits = None
         self.knn_cache = False  # eval: the search inputs are parameters only, so it can be hoisted out of the frame loop
+        # Morton order of the Gaussians, a speed hint for the search (results do not depend on it).  Built on first use
+        # and whenever N changes; call refresh_knn_order() after the cloud has moved a lot (e.g. after densification).
+        self._knn_order = None
 
     # getters with the reference's names (scene/gaussian_model.py:138-162)
     @property
@@ -245,9 +262,15 @@ class KeypointDeformation(nn.Module):
             return None
         return dense_weights(self._last_logits, self._idx32, self.super_gaussians.shape[0], want_sum=True)[2]
 
+    def refresh_knn_order(self):
+        self._knn_order = spatial_order(self._xyz)
+
     def get_nearest_mask(self, keepshape=False):
+        if self._knn_order is None or self._knn_order.shape[0] != self._xyz.shape[0]:
+            self.refresh_knn_order()
         idx64, idx32, _ = knn_keypoints(self._xyz, self.motion_feature, self.super_gaussians, self.super_gaussians_feature,
-                                        self.args.nearest_num, self.args.knn_type, self.args.feature_amplify)
+                                        self.args.nearest_num, self.args.knn_type, self.args.feature_amplify,
+                                        order=self._knn_order)
         self._idx32 = idx32
         self.nearest_mask = idx64 if keepshape else idx64.view([-1])
 

@@ -154,10 +154,17 @@ int gp_knn_points(int N, int Kp, int D, int K, float r, const float* points1, co
 
 /* Same search on the un-concatenated model tensors: query = [xyz | motion_feature * feature_amplify]
  * (the torch.cat of scene/gaussian_model.py:115-116 is folded into the kernel; F = 0 selects the "3D" mode of
- * :112-113).  Either index output may be NULL. */
+ * :112-113).  Either index output may be NULL; `order` may be NULL. */
 int gp_knn_keypoints(int N, int Kp, int F, int K, float r, float feature_amplify, const float* xyz,
-                     const float* motion_feature, const float* kp_xyz, const float* kp_feature, long long* idx64,
-                     int* idx32, float* dists, gp_stream_t stream);
+                     const float* motion_feature, const float* kp_xyz, const float* kp_feature, const int* order,
+                     long long* idx64, int* idx32, float* dists, gp_stream_t stream);
+
+/* Optional acceleration hint for gp_knn_keypoints: `order` = a permutation of 0..N-1 in Morton order of xyz, so that
+ * the 32 queries of a warp are spatial neighbours and the kernel's exact warp-wide early exit skips most keypoints.
+ * The search result does not depend on `order` (NULL = identity); a stale order only costs speed.  (The reference's
+ * FRNN path sorts the queries into grid cells for the same reason, frnn.py:137-170 -- with one cell here.) */
+size_t gp_spatial_order_ws_bytes(int N);
+int gp_spatial_order(int N, const float* xyz, int* order /*[N]*/, void* ws, gp_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Keypoint blending.  Stands in for the torch ops of GaussianModel.forward's keypoint stage
