@@ -317,8 +317,7 @@ static inline GpOrderWs gp_carve_order(void* ws, int N) {
   w.keys[1] = c.take<uint32_t>(n);
   w.vals[0] = c.take<uint32_t>(n);
   w.vals[1] = c.take<uint32_t>(n);
-  w.radix.hist = c.take<uint32_t>((size_t)GP_RS_RADIX * GP_RS_GV);
-  w.radix.totals = c.take<uint32_t>(GP_RS_RADIX);
+  w.radix = gp_radix_carve(c, (long long)n);
   w.bytes = c.used();
   return w;
 }

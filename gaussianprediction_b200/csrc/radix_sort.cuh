@@ -7,176 +7,173 @@
 // count of tile instances R is only known on the device, every kernel takes `n_ptr` and uses a
 // fixed grid (a multiple of the 148 SMs) so no host round trip is needed to size a launch.
 //
-// Layout: the n keys are cut into GV contiguous "warp chunks" (one per warp of the grid).  A pass is
-//   hist    : each warp counts the digits of its chunk                 -> hist[digit][chunk]
-//   scan    : one block per digit, exclusive scan over chunks          -> hist (in place), totals[digit]
-//   scatter : each warp walks its chunk 32 keys at a time; ranks inside a step come from
-//             __match_any_sync (stable: lower lane = earlier key), running offsets live in shared memory.
+// One launch computes the digit histograms of ALL passes (they do not depend on the order of the
+// keys); then each pass is ONE kernel in the "onesweep" style: a block takes the next 1024-key tile
+// (atomic ticket, so lower tiles are always already running), ranks its keys stably
+// (warp = 128 consecutive keys walked 32 at a time, rank inside a step from __match_any_sync, lower
+// lane = earlier key), publishes its per-digit counts, finds the counts of all earlier tiles by
+// decoupled look-back over per-tile status words (2 flag bits + 30-bit count), and scatters.
+// A 4-pass sort of the depth keys is 6 launches, the tile sort 4, instead of 3 launches per pass.
 #pragma once
 #include "common.cuh"
 
-#define GP_RS_BLOCKS (148 * 2)
+#define GP_RS_BLOCKS (148 * 4)
 #define GP_RS_WARPS 8
 #define GP_RS_THREADS (GP_RS_WARPS * 32)
-#define GP_RS_GV (GP_RS_BLOCKS * GP_RS_WARPS)
 #define GP_RS_RADIX 256
+#define GP_RS_STEPS 4                                // 32-key steps per warp per tile
+#define GP_RS_TILE (GP_RS_WARPS * GP_RS_STEPS * 32)  // 1024 keys
+#define GP_RS_MAX_PASSES 4
+
+#define GP_RS_FLAG_AGG 0x40000000u
+#define GP_RS_FLAG_PREFIX 0x80000000u
+#define GP_RS_COUNT_MASK 0x3FFFFFFFu
 
 struct GpRadixTemp {
-  uint32_t* hist;    // [256][GV]
-  uint32_t* totals;  // [256]
+  uint32_t* hist;     // [MAX_PASSES][256] digit counts
+  uint32_t* tickets;  // [MAX_PASSES]
+  uint32_t* status;   // [MAX_PASSES][tiles_max][256]
+  int tiles_max;
 };
 
-static inline size_t gp_radix_temp_bytes() {
-  return gp_align_up((size_t)GP_RS_RADIX * GP_RS_GV * 4, 256) + gp_align_up(GP_RS_RADIX * 4, 256);
+static inline int gp_radix_tiles(long long n_max) { return (int)((n_max + GP_RS_TILE - 1) / GP_RS_TILE) + 1; }
+
+// carve the temporaries for sorts of up to n_max elements out of a GpCarver
+static inline GpRadixTemp gp_radix_carve(GpCarver& c, long long n_max) {
+  GpRadixTemp t;
+  t.tiles_max = gp_radix_tiles(n_max);
+  t.hist = c.take<uint32_t>((size_t)GP_RS_MAX_PASSES * GP_RS_RADIX);
+  t.tickets = c.take<uint32_t>(GP_RS_MAX_PASSES);
+  t.status = c.take<uint32_t>((size_t)GP_RS_MAX_PASSES * t.tiles_max * GP_RS_RADIX);
+  return t;
 }
 
 #ifdef __CUDACC__
-// Number of warp chunks in use for n keys: at least GP_RS_MIN_CHUNK keys per chunk, so that a small sort does not
-// pay for 256 x GV histogram counters (the scan only touches the chunks in use).
-#define GP_RS_MIN_CHUNK 256
-__device__ __forceinline__ int gp_rs_num_chunks(int n) {
-  int c = (n + GP_RS_MIN_CHUNK - 1) / GP_RS_MIN_CHUNK;
-  return c < 1 ? 1 : (c > GP_RS_GV ? GP_RS_GV : c);
-}
-__device__ __forceinline__ void gp_rs_chunk(int n, int gw, int& start, int& end) {
-  const int nch = gp_rs_num_chunks(n);
-  int sub = (n + nch - 1) / nch;
-  sub = (sub + 31) & ~31;
-  long long s = (long long)gw * sub;
-  long long e = s + sub;
-  start = (int)(s < n ? s : n);
-  end = (int)(e < n ? e : n);
-  if (gw >= nch) start = end = n;
+static __global__ void gp_rs_reset_kernel(GpRadixTemp t) {
+  // hist and tickets must be zero before gp_rs_prepare_kernel accumulates into them
+  for (int i = threadIdx.x; i < GP_RS_MAX_PASSES * GP_RS_RADIX; i += blockDim.x) t.hist[i] = 0u;
+  if (threadIdx.x < GP_RS_MAX_PASSES) t.tickets[threadIdx.x] = 0u;
 }
 
+// Digit histograms of every pass + reset of the status words the passes will use.
 static __global__ void __launch_bounds__(GP_RS_THREADS)
-gp_rs_hist_kernel(const uint32_t* __restrict__ keys, const int* __restrict__ n_ptr, int shift,
-                  uint32_t* __restrict__ hist) {
-  __shared__ uint32_t wh[GP_RS_WARPS][GP_RS_RADIX];
-  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int gw = blockIdx.x * GP_RS_WARPS + w;
+gp_rs_prepare_kernel(const uint32_t* __restrict__ keys, const int* __restrict__ n_ptr, int begin_bit, int passes,
+                     GpRadixTemp t) {
+  __shared__ uint32_t sh[GP_RS_MAX_PASSES][GP_RS_RADIX];
   const int n = *n_ptr;
-  if (gw >= gp_rs_num_chunks(n)) return;
-  for (int d = lane; d < GP_RS_RADIX; d += 32) wh[w][d] = 0;
-  __syncwarp();
-  int start, end;
-  gp_rs_chunk(n, gw, start, end);
-  constexpr int U = 4;
-  for (int i0 = start; i0 < end; i0 += 32 * U) {
-    uint32_t k[U];
-#pragma unroll
-    for (int u = 0; u < U; u++) {
-      const int i = i0 + u * 32 + lane;
-      k[u] = i < end ? __ldg(keys + i) : 0u;
-    }
-#pragma unroll
-    for (int u = 0; u < U; u++) {
-      const int i = i0 + u * 32 + lane;
-      const bool valid = i < end;
-      const uint32_t d = valid ? ((k[u] >> shift) & 0xFFu) : 0x100u;
-      const unsigned peers = __match_any_sync(0xffffffffu, d);
-      if (valid && (peers & gp_lanemask_lt()) == 0) wh[w][d] += __popc(peers);
-      __syncwarp();
-    }
-  }
-  for (int d = lane; d < GP_RS_RADIX; d += 32) hist[(size_t)d * GP_RS_GV + gw] = wh[w][d];
-}
-
-// One block per digit: exclusive scan of hist[d][0..GV) in place; totals[d] = sum.
-static __global__ void __launch_bounds__(256)
-gp_rs_scan_kernel(uint32_t* __restrict__ hist, uint32_t* __restrict__ totals, const int* __restrict__ n_ptr) {
-  constexpr int PER = (GP_RS_GV + 255) / 256;
-  __shared__ uint32_t warp_sums[8];
-  uint32_t* row = hist + (size_t)blockIdx.x * GP_RS_GV;
-  const int t = threadIdx.x, lane = t & 31, w = t >> 5;
-  const int nch = gp_rs_num_chunks(*n_ptr);
-  uint32_t v[PER];
-  uint32_t local = 0;
-#pragma unroll
-  for (int j = 0; j < PER; j++) {
-    const int i = t * PER + j;
-    v[j] = i < nch ? row[i] : 0u;
-    local += v[j];
-  }
-  uint32_t incl = local;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    uint32_t y = __shfl_up_sync(0xffffffffu, incl, o);
-    if (lane >= o) incl += y;
-  }
-  if (lane == 31) warp_sums[w] = incl;
+  const int tid = threadIdx.x;
+  for (int p = 0; p < passes; p++) sh[p][tid] = 0;
   __syncthreads();
-  uint32_t wbase = 0;
-  for (int j = 0; j < w; j++) wbase += warp_sums[j];
-  uint32_t run = wbase + incl - local;
-#pragma unroll
-  for (int j = 0; j < PER; j++) {
-    const int i = t * PER + j;
-    if (i < nch) row[i] = run;
-    run += v[j];
+  const int stride = gridDim.x * GP_RS_THREADS;
+  bool any = false;
+  for (int i = blockIdx.x * GP_RS_THREADS + tid; i < n; i += stride) {
+    const uint32_t k = __ldg(keys + i);
+    for (int p = 0; p < passes; p++) atomicAdd(&sh[p][(k >> (begin_bit + 8 * p)) & 0xFFu], 1u);
+    any = true;
   }
-  if (t == 255) totals[blockIdx.x] = run;
+  if (__syncthreads_or(any)) {
+    for (int p = 0; p < passes; p++) {
+      const uint32_t v = sh[p][tid];
+      if (v) atomicAdd(&t.hist[p * GP_RS_RADIX + tid], v);
+    }
+  }
+  // status words of the tiles in use
+  const int ntiles = (n + GP_RS_TILE - 1) / GP_RS_TILE;
+  const long long words = (long long)ntiles * GP_RS_RADIX;
+  for (int p = 0; p < passes; p++) {
+    uint32_t* st = t.status + (size_t)p * t.tiles_max * GP_RS_RADIX;
+    for (long long i = (long long)blockIdx.x * GP_RS_THREADS + tid; i < words; i += stride) st[i] = 0u;
+  }
 }
 
 static __global__ void __launch_bounds__(GP_RS_THREADS)
-gp_rs_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
-                     uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
-                     const int* __restrict__ n_ptr, int shift, const uint32_t* __restrict__ hist,
-                     const uint32_t* __restrict__ totals) {
-  __shared__ uint32_t off[GP_RS_WARPS][GP_RS_RADIX];
-  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int gw = blockIdx.x * GP_RS_WARPS + w;
+gp_rs_pass_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
+                  uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, const int* __restrict__ n_ptr,
+                  int shift, int pass, GpRadixTemp t) {
+  __shared__ uint32_t wcnt[GP_RS_WARPS][GP_RS_RADIX];
+  __shared__ uint32_t tile_off[GP_RS_RADIX];
+  __shared__ uint32_t digit_base[GP_RS_RADIX];
+  __shared__ uint32_t warp_tot[GP_RS_WARPS];
+  __shared__ int s_tile;
+  const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
   const int n = *n_ptr;
-  if (gw >= gp_rs_num_chunks(n)) return;
-  // digit bases: exclusive scan of totals[256]; every warp does it redundantly (8 digits per lane).
+  const int ntiles = (n + GP_RS_TILE - 1) / GP_RS_TILE;
+  if ((int)blockIdx.x >= ntiles) return;  // tickets are handed out in order: this block could only draw a tile >= ntiles
+  volatile uint32_t* status = t.status + (size_t)pass * t.tiles_max * GP_RS_RADIX;
+
+  // exclusive scan of this pass's digit histogram -> first output position of every digit
   {
-    uint32_t tv[8];
-    uint32_t s = 0;
-#pragma unroll
-    for (int j = 0; j < 8; j++) {
-      tv[j] = totals[lane * 8 + j];
-      s += tv[j];
-    }
-    uint32_t incl = s;
+    const uint32_t v = t.hist[pass * GP_RS_RADIX + tid];
+    uint32_t incl = v;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
-      uint32_t y = __shfl_up_sync(0xffffffffu, incl, o);
+      const uint32_t y = __shfl_up_sync(0xffffffffu, incl, o);
       if (lane >= o) incl += y;
     }
-    uint32_t run = incl - s;
-#pragma unroll
-    for (int j = 0; j < 8; j++) {
-      const int d = lane * 8 + j;
-      off[w][d] = run + hist[(size_t)d * GP_RS_GV + gw];
-      run += tv[j];
-    }
+    if (lane == 31) warp_tot[w] = incl;
+    __syncthreads();
+    uint32_t wb = 0;
+    for (int j = 0; j < w; j++) wb += warp_tot[j];
+    digit_base[tid] = wb + incl - v;
   }
-  __syncwarp();
-  int start, end;
-  gp_rs_chunk(n, gw, start, end);
-  constexpr int U = 4;
-  for (int i0 = start; i0 < end; i0 += 32 * U) {
-    uint32_t k[U], v[U];
+  for (;;) {
+    __syncthreads();
+    if (tid == 0) s_tile = (int)atomicAdd(&t.tickets[pass], 1u);
 #pragma unroll
-    for (int u = 0; u < U; u++) {
-      const int i = i0 + u * 32 + lane;
-      const bool valid = i < end;
-      k[u] = valid ? __ldg(keys_in + i) : 0u;
-      v[u] = valid ? __ldg(vals_in + i) : 0u;
+    for (int d = lane; d < GP_RS_RADIX; d += 32) wcnt[w][d] = 0u;
+    __syncthreads();
+    const int tile = s_tile;
+    if (tile >= ntiles) break;
+    const int base = tile * GP_RS_TILE + w * (GP_RS_STEPS * 32);
+    uint32_t k[GP_RS_STEPS], v[GP_RS_STEPS], local[GP_RS_STEPS];
+#pragma unroll
+    for (int u = 0; u < GP_RS_STEPS; u++) {
+      const int i = base + u * 32 + lane;
+      k[u] = i < n ? __ldg(keys_in + i) : 0u;
+      v[u] = i < n ? __ldg(vals_in + i) : 0u;
     }
 #pragma unroll
-    for (int u = 0; u < U; u++) {
-      const int i = i0 + u * 32 + lane;
-      const bool valid = i < end;
+    for (int u = 0; u < GP_RS_STEPS; u++) {
+      const int i = base + u * 32 + lane;
+      const bool valid = i < n;
       const uint32_t d = valid ? ((k[u] >> shift) & 0xFFu) : 0x100u;
       const unsigned peers = __match_any_sync(0xffffffffu, d);
       const unsigned before = peers & gp_lanemask_lt();
-      uint32_t pos = 0;
-      if (valid) pos = off[w][d] + __popc(before);
+      local[u] = valid ? wcnt[w][d] + __popc(before) : 0u;
       __syncwarp();
-      if (valid && before == 0) off[w][d] += __popc(peers);
+      if (valid && before == 0) wcnt[w][d] += __popc(peers);
       __syncwarp();
-      if (valid) {
+    }
+    __syncthreads();
+    // thread `tid` owns digit `tid`: exclusive prefix over the 8 warps, tile total, look-back
+    uint32_t run = 0;
+#pragma unroll
+    for (int ww = 0; ww < GP_RS_WARPS; ww++) {
+      const uint32_t c = wcnt[ww][tid];
+      wcnt[ww][tid] = run;
+      run += c;
+    }
+    status[(size_t)tile * GP_RS_RADIX + tid] = GP_RS_FLAG_AGG | run;
+    uint32_t excl = 0;
+    for (int tt = tile - 1; tt >= 0; --tt) {
+      uint32_t s;
+      unsigned polls = 0;
+      do {
+        s = status[(size_t)tt * GP_RS_RADIX + tid];
+        if (++polls > (1u << 26)) __trap();  // an earlier tile never published: fail loudly instead of hanging
+      } while ((s & (GP_RS_FLAG_AGG | GP_RS_FLAG_PREFIX)) == 0u);
+      excl += s & GP_RS_COUNT_MASK;
+      if (s & GP_RS_FLAG_PREFIX) break;
+    }
+    status[(size_t)tile * GP_RS_RADIX + tid] = GP_RS_FLAG_PREFIX | (excl + run);
+    tile_off[tid] = digit_base[tid] + excl;
+    __syncthreads();
+#pragma unroll
+    for (int u = 0; u < GP_RS_STEPS; u++) {
+      const int i = base + u * 32 + lane;
+      if (i < n) {
+        const uint32_t d = (k[u] >> shift) & 0xFFu;
+        const uint32_t pos = tile_off[d] + wcnt[w][d] + local[u];
         keys_out[pos] = k[u];
         vals_out[pos] = v[u];
       }
@@ -184,16 +181,20 @@ gp_rs_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __res
   }
 }
 
-// Sort bits [begin_bit, end_bit) of keys.  keys[0]/vals[0] hold the input; buffers ping-pong.
-// Returns the index (0/1) of the buffer pair holding the sorted result.
+// Sort bits [begin_bit, end_bit) of keys (at most 32 bits = 4 passes).  keys[0]/vals[0] hold the input; buffers
+// ping-pong.  Returns the index (0/1) of the buffer pair holding the sorted result.
 static inline int gp_radix_sort_pairs(uint32_t* keys[2], uint32_t* vals[2], const int* n_ptr, int begin_bit,
                                       int end_bit, const GpRadixTemp& tmp, cudaStream_t stream) {
+  const int passes = (end_bit - begin_bit + 7) / 8;
+  GP_KERNEL("gp_rs_reset_kernel", stream, gp_rs_reset_kernel<<<1, 256, 0, stream>>>(tmp));
+  GP_KERNEL("gp_rs_prepare_kernel", stream,
+            gp_rs_prepare_kernel<<<GP_RS_BLOCKS, GP_RS_THREADS, 0, stream>>>(keys[0], n_ptr, begin_bit, passes, tmp));
   int sel = 0;
-  for (int shift = begin_bit; shift < end_bit; shift += 8) {
-    GP_KERNEL("gp_rs_hist_kernel", stream, gp_rs_hist_kernel<<<GP_RS_BLOCKS, GP_RS_THREADS, 0, stream>>>(keys[sel], n_ptr, shift, tmp.hist));
-    GP_KERNEL("gp_rs_scan_kernel", stream, gp_rs_scan_kernel<<<GP_RS_RADIX, 256, 0, stream>>>(tmp.hist, tmp.totals, n_ptr));
-    GP_KERNEL("gp_rs_scatter_kernel", stream, gp_rs_scatter_kernel<<<GP_RS_BLOCKS, GP_RS_THREADS, 0, stream>>>(keys[sel], vals[sel], keys[sel ^ 1], vals[sel ^ 1],
-                                                                    n_ptr, shift, tmp.hist, tmp.totals));
+  for (int p = 0; p < passes; p++) {
+    GP_KERNEL("gp_rs_pass_kernel", stream,
+              gp_rs_pass_kernel<<<GP_RS_BLOCKS, GP_RS_THREADS, 0, stream>>>(keys[sel], vals[sel], keys[sel ^ 1],
+                                                                          vals[sel ^ 1], n_ptr, begin_bit + 8 * p, p,
+                                                                          tmp));
     sel ^= 1;
   }
   return sel;

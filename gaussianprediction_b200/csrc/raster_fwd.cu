@@ -524,7 +524,7 @@ extern "C" int gp_raster_render(const gp_raster_cfg* cfg, const float* bg, const
                                                         g.hdr, gx, gy, b.tkeys[0], b.tvals[0]));
   GP_LAUNCH_CHECK();
   const int bits = gp_tile_bits(W, H);
-  const int sel = gp_radix_sort_pairs(b.tkeys, b.tvals, g.hdr + GP_HDR_NUM_SORTED, 0, bits, g.radix, stream);
+  const int sel = gp_radix_sort_pairs(b.tkeys, b.tvals, g.hdr + GP_HDR_NUM_SORTED, 0, bits, b.radix, stream);
   GP_LAUNCH_CHECK();
   GP_CUDA_TRY(cudaMemsetAsync(im.ranges, 0, (size_t)gx * gy * sizeof(uint2), stream));
   GP_KERNEL("gp_tile_ranges_kernel", stream, gp_tile_ranges_kernel<<<148 * 4, 256, 0, stream>>>(g.hdr, b.tkeys[sel], im.ranges));

@@ -29,6 +29,7 @@ struct GpGeom {
 struct GpBinning {
   uint32_t* tkeys[2];  // [capacity] tile id
   uint32_t* tvals[2];  // [capacity] Gaussian index
+  GpRadixTemp radix;   // look-back status words of the tile sort
   size_t bytes;
 };
 
@@ -55,8 +56,7 @@ static inline GpGeom gp_carve_geom(void* ws, int P) {
   g.dvals[0] = c.take<uint32_t>(n);
   g.dvals[1] = c.take<uint32_t>(n);
   g.block_sums = c.take<uint32_t>((n + GP_SCAN_BLOCK - 1) / GP_SCAN_BLOCK + 1);
-  g.radix.hist = c.take<uint32_t>((size_t)GP_RS_RADIX * GP_RS_GV);
-  g.radix.totals = c.take<uint32_t>(GP_RS_RADIX);
+  g.radix = gp_radix_carve(c, (long long)n);
   g.bytes = c.used();
   return g;
 }
@@ -69,6 +69,7 @@ static inline GpBinning gp_carve_binning(void* ws, long long capacity) {
   b.tkeys[1] = c.take<uint32_t>(n);
   b.tvals[0] = c.take<uint32_t>(n);
   b.tvals[1] = c.take<uint32_t>(n);
+  b.radix = gp_radix_carve(c, (long long)n);
   b.bytes = c.used();
   return b;
 }
