@@ -45,7 +45,7 @@ SIGNATURES = {
     "gp_mark_visible": (c_int, [c_int, _P, _P, _P, _P, _P]),
     "gp_raster_export_state": (c_int, [POINTER(RasterCfg)] + [_P] * 13),
     "gp_knn_points": (c_int, [c_int, c_int, c_int, c_int, c_float, _P, _P, _P, _P, _P]),
-    "gp_knn_keypoints": (c_int, [c_int, c_int, c_int, c_int, c_float, c_float, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
+    "gp_knn_keypoints": (c_int, [c_int, c_int, c_int, c_int, c_float, c_float, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "gp_spatial_order_ws_bytes": (c_size_t, [c_int]),
     "gp_spatial_order": (c_int, [c_int, _P, _P, _P, _P]),
     "gp_blend_forward": (c_int, [c_int, c_int, c_int] + [_P] * 14),

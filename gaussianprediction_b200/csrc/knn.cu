@@ -73,16 +73,19 @@ struct TopK {
 // D floats of q_points.  Same for the keypoints.  D is a template parameter for the two shapes the
 // repo uses (3 and 35); D == 0 selects the generic runtime-D path (query re-read from L1).
 template <int D, int KT>
-__global__ void __launch_bounds__(GP_KNN_THREADS, 3)
+__global__ void __launch_bounds__(GP_KNN_THREADS, 2)
 gp_knn_kernel(int N, int Kp, int Drt, int K, const float* __restrict__ q_points, const float* __restrict__ q_feat,
               const float* __restrict__ r_points, const float* __restrict__ r_feat, int F, float amplify, float r2,
-              int kp_chunk, const int* __restrict__ order, long long* __restrict__ idx64, int* __restrict__ idx32,
-              float* __restrict__ dists) {
+              int kp_chunk, const int* __restrict__ order, const int* hint, long long* __restrict__ idx64,
+              int* idx32, float* __restrict__ dists) {
   extern __shared__ __align__(16) float s_ref[];  // [kp_chunk][DP]
   constexpr int DD = D > 0 ? D : 1;
   const int Dn = D > 0 ? D : Drt;
   const int DP = (Dn + 3) & ~3;
-  const int slot = blockIdx.x * GP_KNN_THREADS + threadIdx.x;
+  const int n_groups = (N + GP_KNN_THREADS - 1) / GP_KNN_THREADS;
+  const bool single_chunk = kp_chunk >= Kp;
+  for (int group = blockIdx.x; group < n_groups; group += gridDim.x) {
+  const int slot = group * GP_KNN_THREADS + threadIdx.x;
   const bool valid = slot < N;
   // `order` (optional) is a permutation of the queries that puts spatial neighbours in the same warp, which makes
   // the warp-wide early exit below fire for most keypoints.  It only changes which thread serves which query.
@@ -91,12 +94,28 @@ gp_knn_kernel(int N, int Kp, int Drt, int K, const float* __restrict__ q_points,
 
   float qv[DD];
   if (D > 0) {
+    if (q_feat != nullptr && DD > 3 && ((DD - 3) & 3) == 0 && ((((size_t)q_feat) & 15) == 0)) {
+      // feature rows are 16-byte aligned multiples of 4 floats: gather them with 128-bit loads (the rows of the 32
+      // lanes are far apart, so every load instruction costs one sector per lane whatever its width)
 #pragma unroll
-    for (int d = 0; d < DD; d++) {
-      if (q_feat != nullptr)
-        qv[d] = d < 3 ? q_points[(size_t)qc * 3 + d] : __fmul_rn(q_feat[(size_t)qc * F + (d - 3)], amplify);
-      else
-        qv[d] = q_points[(size_t)qc * Dn + d];
+      for (int d = 0; d < 3; d++) qv[d] = q_points[(size_t)qc * 3 + d];
+      const float4* frow = (const float4*)(q_feat + (size_t)qc * F);
+#pragma unroll
+      for (int c = 0; c < (DD > 3 ? (DD - 3) / 4 : 0); c++) {
+        const float4 f4 = __ldg(frow + c);
+        qv[3 + 4 * c + 0] = __fmul_rn(f4.x, amplify);
+        qv[3 + 4 * c + 1] = __fmul_rn(f4.y, amplify);
+        qv[3 + 4 * c + 2] = __fmul_rn(f4.z, amplify);
+        qv[3 + 4 * c + 3] = __fmul_rn(f4.w, amplify);
+      }
+    } else {
+#pragma unroll
+      for (int d = 0; d < DD; d++) {
+        if (q_feat != nullptr)
+          qv[d] = d < 3 ? q_points[(size_t)qc * 3 + d] : __fmul_rn(q_feat[(size_t)qc * F + (d - 3)], amplify);
+        else
+          qv[d] = q_points[(size_t)qc * Dn + d];
+      }
     }
   }
   TopK<KT> top;
@@ -106,9 +125,12 @@ gp_knn_kernel(int N, int Kp, int Drt, int K, const float* __restrict__ q_points,
 
   for (int base = 0; base < Kp; base += kp_chunk) {
     const int cnt = min(kp_chunk, Kp - base);
-    __syncthreads();
-    // ---- stage the keypoints of this chunk (zero padded to DP floats per row) ----
-    if (r_feat != nullptr) {
+    // ---- stage the keypoints of this chunk (zero padded to DP floats per row); a block whose keypoints fit in one
+    //      chunk stages them once and keeps them for all its query groups ----
+    const bool stage = !single_chunk || group == (int)blockIdx.x;
+    if (stage) __syncthreads();
+    if (!stage) {
+    } else if (r_feat != nullptr) {
       for (int j = threadIdx.x; j < cnt; j += GP_KNN_THREADS) {
         const float* src = r_points + (size_t)(base + j) * 3;
         float* dst = s_ref + j * DP;
@@ -163,8 +185,134 @@ gp_knn_kernel(int N, int Kp, int Drt, int K, const float* __restrict__ q_points,
         }
       }
     }
-    __syncthreads();
-    for (int j = 0; j < cnt; j++) {
+    if (stage) __syncthreads();
+    // ---- warp-level pruning (exact): keep only the keypoints that can enter the top K of one of the warp's 32
+    //      queries.  With the queries in Morton order a warp covers a small box, and the survivors are the few
+    //      keypoints around it; the search stays exhaustive in effect because a dropped keypoint is provably farther
+    //      than every query's K-th candidate.
+    const int lane = threadIdx.x & 31, wp = threadIdx.x >> 5;
+    unsigned short* s_list = (unsigned short*)(s_ref + (size_t)kp_chunk * DP) + (size_t)wp * kp_chunk;  // per warp
+    float* s_lb = (float*)((unsigned short*)(s_ref + (size_t)kp_chunk * DP) + (size_t)(GP_KNN_THREADS / 32) * kp_chunk) +
+                  (size_t)wp * kp_chunk;                                                                 // per warp
+    int n_list = cnt;
+    if (D > 0) {
+      constexpr int SD = DD < 3 ? DD : 3;   // leading dimensions used for the bound (xyz in the repo's two modes)
+      // (a) bounding box of the warp's queries
+      float bmin[3], bmax[3];
+#pragma unroll
+      for (int a = 0; a < SD; a++) {
+        float lo = qv[a], hi = qv[a];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+          lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+          hi = fmaxf(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+        }
+        bmin[a] = lo;
+        bmax[a] = hi;
+      }
+      // (b) per keypoint: squared distance from the box in the leading dimensions, shrunk a little so that it stays a
+      //     lower bound of the fma-accumulated distance of every query in the box
+      for (int j = lane; j < cnt; j += 32) {
+        float lb = 0.f;
+#pragma unroll
+        for (int a = 0; a < SD; a++) {
+          const float kx = s_ref[j * DP + a];
+          const float dd = fmaxf(0.f, fmaxf(bmin[a] - kx, kx - bmax[a]));
+          lb += dd * dd;
+        }
+        s_lb[j] = lb * (1.0f - 1e-5f);
+      }
+      __syncwarp();
+      // (c) the K keypoints closest to the box -> an upper bound U of every query's K-th distance
+      float U = __int_as_float(0x7f800000);
+      // A caller-supplied hint (e.g. the neighbours found for the previous frame) gives the bound directly: the
+      // largest distance to ANY K distinct keypoints is an upper bound of the K-th nearest distance.
+      bool hinted = false;
+      if (KT > 0 && hint != nullptr && single_chunk) {
+        int h[KT > 0 ? KT : 1];
+        bool ok = true;
+#pragma unroll
+        for (int k = 0; k < (KT > 0 ? KT : 1); k++) {
+          h[k] = hint[(size_t)qc * K + k];
+          ok = ok && h[k] >= 0 && h[k] < cnt;
+        }
+#pragma unroll
+        for (int a = 0; a < (KT > 0 ? KT : 1); a++)
+#pragma unroll
+          for (int b = a + 1; b < (KT > 0 ? KT : 1); b++) ok = ok && h[a] != h[b];
+        if (__all_sync(0xffffffffu, ok)) {
+          float uq = 0.f;
+#pragma unroll
+          for (int k = 0; k < (KT > 0 ? KT : 1); k++) {
+            const float* rp = s_ref + h[k] * DP;
+            float acc = 0.f;
+#pragma unroll
+            for (int d = 0; d < DD; d++) {
+              const float diff = rp[d] - qv[d];
+              acc = __fmaf_rn(diff, diff, acc);
+            }
+            uq = fmaxf(uq, acc);
+          }
+          if (!(uq <= r2)) uq = __int_as_float(0x7f800000);
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) uq = fmaxf(uq, __shfl_xor_sync(0xffffffffu, uq, o));
+          U = uq;
+          hinted = true;
+        }
+      }
+      if (!hinted && cnt >= K) {
+        int cand[KT > 0 ? KT : 32];
+        float uq = 0.f;
+#pragma unroll
+        for (int r = 0; r < (KT > 0 ? KT : 32); r++) {
+          if (r < K) {
+            unsigned long long best = ~0ull;
+            for (int j = lane; j < cnt; j += 32) {
+              bool taken = false;
+#pragma unroll
+              for (int c = 0; c < (KT > 0 ? KT : 32); c++)
+                if (c < r) taken |= (cand[c] == j);
+              if (!taken) {
+                const unsigned long long key = ((unsigned long long)__float_as_uint(s_lb[j]) << 32) | (unsigned)j;
+                best = key < best ? key : best;
+              }
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+              const unsigned long long y = __shfl_xor_sync(0xffffffffu, best, o);
+              best = y < best ? y : best;
+            }
+            cand[r] = (int)(best & 0xffffffffu);
+            const float* rp = s_ref + cand[r] * DP;
+            float acc = 0.f;
+#pragma unroll
+            for (int d = 0; d < DD; d++) {
+              const float diff = rp[d] - qv[d];
+              acc = __fmaf_rn(diff, diff, acc);
+            }
+            uq = fmaxf(uq, acc);
+          }
+        }
+        if (!(uq <= r2)) uq = __int_as_float(0x7f800000);   // a candidate outside the radius gives no bound
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) uq = fmaxf(uq, __shfl_xor_sync(0xffffffffu, uq, o));
+        U = uq;
+      }
+      U = fminf(U, r2);
+      // (d) ordered compaction of the keypoints with lower bound <= U
+      int running = 0;
+      for (int j0 = 0; j0 < cnt; j0 += 32) {
+        const int j = j0 + lane;
+        const bool keep = j < cnt && s_lb[j] <= U;
+        const unsigned bal = __ballot_sync(0xffffffffu, keep);
+        if (keep) s_list[running + __popc(bal & gp_lanemask_lt())] = (unsigned short)j;
+        running += __popc(bal);
+      }
+      __syncwarp();
+      n_list = running;
+    }
+    for (int jj = 0; jj < n_list; jj++) {
+      const int j = D > 0 ? s_list[jj] : jj;
       const float* rp = s_ref + j * DP;
       float acc = 0.f;
       if (D > 0) {
@@ -213,33 +361,41 @@ gp_knn_kernel(int N, int Kp, int Drt, int K, const float* __restrict__ q_points,
       }
     }
   }
-  if (!valid) return;
+  if (valid) {
 #pragma unroll
-  for (int k = 0; k < TopK<KT>::KMAX; k++) {
-    if (k < K) {
-      const bool has = k < filled;
-      if (idx64) idx64[(size_t)q * K + k] = has ? (long long)top.i[k] : -1ll;
-      if (idx32) idx32[(size_t)q * K + k] = has ? top.i[k] : -1;
-      if (dists) dists[(size_t)q * K + k] = has ? top.d[k] : -1.0f;
+    for (int k = 0; k < TopK<KT>::KMAX; k++) {
+      if (k < K) {
+        const bool has = k < filled;
+        if (idx64) idx64[(size_t)q * K + k] = has ? (long long)top.i[k] : -1ll;
+        if (idx32) idx32[(size_t)q * K + k] = has ? top.i[k] : -1;
+        if (dists) dists[(size_t)q * K + k] = has ? top.d[k] : -1.0f;
+      }
     }
   }
+  }  // query groups
 }
 
 template <int D, int KT>
 static int launch_knn(int N, int Kp, int Drt, int K, const float* q_points, const float* q_feat, const float* r_points,
-                      const float* r_feat, int F, float amplify, float r2, const int* order, long long* idx64, int* idx32,
-                      float* dists, cudaStream_t stream) {
+                      const float* r_feat, int F, float amplify, float r2, const int* order, const int* hint,
+                      long long* idx64, int* idx32, float* dists, cudaStream_t stream) {
   const int Dn = D > 0 ? D : Drt;
   const int DP = (Dn + 3) & ~3;
   const size_t max_smem = 200 * 1024;
   int kp_chunk = Kp;
-  if ((size_t)kp_chunk * DP * 4 > max_smem) kp_chunk = (int)(max_smem / ((size_t)DP * 4));
+  // keypoints (DP floats each) + per warp: surviving-index list (u16) and lower bounds (f32)
+  const size_t per_kp = (size_t)DP * 4 + (GP_KNN_THREADS / 32) * (2 + 4);
+  if ((size_t)kp_chunk * per_kp > max_smem) kp_chunk = (int)(max_smem / per_kp);
+  if (kp_chunk > 65535) kp_chunk = 65535;
   if (kp_chunk < 1) kp_chunk = 1;
-  const size_t smem = (size_t)kp_chunk * DP * 4;
+  const size_t smem = (size_t)kp_chunk * per_kp;
   auto kern = gp_knn_kernel<D, KT>;
   if (smem > 48 * 1024) GP_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  GP_KERNEL("gp_knn_kernel", stream, kern<<<(N + GP_KNN_THREADS - 1) / GP_KNN_THREADS, GP_KNN_THREADS, smem, stream>>>(
-      N, Kp, Drt, K, q_points, q_feat, r_points, r_feat, F, amplify, r2, kp_chunk, order, idx64, idx32, dists));
+  // persistent grid: two blocks per SM (register-limited), each looping over groups of 256 queries
+  const int n_groups = (N + GP_KNN_THREADS - 1) / GP_KNN_THREADS;
+  const int grid = n_groups < 148 * 2 ? n_groups : 148 * 2;
+  GP_KERNEL("gp_knn_kernel", stream, kern<<<grid, GP_KNN_THREADS, smem, stream>>>(
+      N, Kp, Drt, K, q_points, q_feat, r_points, r_feat, F, amplify, r2, kp_chunk, order, hint, idx64, idx32, dists));
   GP_LAUNCH_CHECK();
   return GP_OK;
 }
@@ -247,9 +403,9 @@ static int launch_knn(int N, int Kp, int Drt, int K, const float* q_points, cons
 template <int D>
 static int knn_dispatch_k(int N, int Kp, int Drt, int K, const float* q_points, const float* q_feat,
                           const float* r_points, const float* r_feat, int F, float amplify, float r2, const int* order,
-                          long long* idx64, int* idx32, float* dists, cudaStream_t stream) {
+                          const int* hint, long long* idx64, int* idx32, float* dists, cudaStream_t stream) {
 #define GP_KNN_GO(KT) \
-  return launch_knn<D, KT>(N, Kp, Drt, K, q_points, q_feat, r_points, r_feat, F, amplify, r2, order, idx64, idx32, dists, stream)
+  return launch_knn<D, KT>(N, Kp, Drt, K, q_points, q_feat, r_points, r_feat, F, amplify, r2, order, hint, idx64, idx32, dists, stream)
   switch (K) {
     case 1: GP_KNN_GO(1);
     case 2: GP_KNN_GO(2);
@@ -265,36 +421,38 @@ static int knn_dispatch_k(int N, int Kp, int Drt, int K, const float* q_points, 
 }
 
 static int knn_dispatch(int N, int Kp, int D, int K, const float* q_points, const float* q_feat, const float* r_points,
-                        const float* r_feat, int F, float amplify, float r, const int* order, long long* idx64, int* idx32,
-                        float* dists, cudaStream_t stream) {
+                        const float* r_feat, int F, float amplify, float r, const int* order, const int* hint,
+                        long long* idx64, int* idx32, float* dists, cudaStream_t stream) {
   if (N < 0 || Kp < 0 || D < 1 || K < 1) return GP_ERR_BAD_ARG;
   if (K > 32) return GP_ERR_UNSUPPORTED;
   if (N == 0) return GP_OK;
   const float r2 = r * r;  // the reference passes r*r computed in float (frnn.py:176)
-  if (D == 3) return knn_dispatch_k<3>(N, Kp, D, K, q_points, q_feat, r_points, r_feat, F, amplify, r2, order, idx64, idx32, dists, stream);
-  if (D == 35) return knn_dispatch_k<35>(N, Kp, D, K, q_points, q_feat, r_points, r_feat, F, amplify, r2, order, idx64, idx32, dists, stream);
-  return knn_dispatch_k<0>(N, Kp, D, K, q_points, q_feat, r_points, r_feat, F, amplify, r2, order, idx64, idx32, dists, stream);
+  if (D == 3) return knn_dispatch_k<3>(N, Kp, D, K, q_points, q_feat, r_points, r_feat, F, amplify, r2, order, hint, idx64, idx32, dists, stream);
+  if (D == 35) return knn_dispatch_k<35>(N, Kp, D, K, q_points, q_feat, r_points, r_feat, F, amplify, r2, order, hint, idx64, idx32, dists, stream);
+  return knn_dispatch_k<0>(N, Kp, D, K, q_points, q_feat, r_points, r_feat, F, amplify, r2, order, hint, idx64, idx32, dists, stream);
 }
 
 extern "C" int gp_knn_points(int N, int Kp, int D, int K, float r, const float* points1, const float* points2,
                              long long* idxs, float* dists, gp_stream_t stream) {
   if (N > 0 && (!points1 || !idxs)) return GP_ERR_BAD_ARG;
   if (Kp > 0 && !points2) return GP_ERR_BAD_ARG;
-  return knn_dispatch(N, Kp, D, K, points1, nullptr, points2, nullptr, 0, 1.0f, r, nullptr, idxs, nullptr, dists,
+  return knn_dispatch(N, Kp, D, K, points1, nullptr, points2, nullptr, 0, 1.0f, r, nullptr, nullptr, idxs, nullptr, dists,
                       (cudaStream_t)stream);
 }
 
 extern "C" int gp_knn_keypoints(int N, int Kp, int F, int K, float r, float feature_amplify, const float* xyz,
                                 const float* motion_feature, const float* kp_xyz, const float* kp_feature,
-                                const int* order, long long* idx64, int* idx32, float* dists, gp_stream_t stream) {
+                                const int* order, const int* hint, long long* idx64, int* idx32, float* dists,
+                                gp_stream_t stream) {
   if (N > 0 && !xyz) return GP_ERR_BAD_ARG;
   if (Kp > 0 && !kp_xyz) return GP_ERR_BAD_ARG;
   if (F < 0 || (F > 0 && (!motion_feature || !kp_feature))) return GP_ERR_BAD_ARG;
   if (!idx64 && !idx32) return GP_ERR_BAD_ARG;
   if (F == 0)
-    return knn_dispatch(N, Kp, 3, K, xyz, nullptr, kp_xyz, nullptr, 0, 1.0f, r, order, idx64, idx32, dists, (cudaStream_t)stream);
-  return knn_dispatch(N, Kp, 3 + F, K, xyz, motion_feature, kp_xyz, kp_feature, F, feature_amplify, r, order, idx64,
-                      idx32, dists, (cudaStream_t)stream);
+    return knn_dispatch(N, Kp, 3, K, xyz, nullptr, kp_xyz, nullptr, 0, 1.0f, r, order, hint, idx64, idx32, dists,
+                        (cudaStream_t)stream);
+  return knn_dispatch(N, Kp, 3 + F, K, xyz, motion_feature, kp_xyz, kp_feature, F, feature_amplify, r, order, hint,
+                      idx64, idx32, dists, (cudaStream_t)stream);
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -100,9 +100,11 @@ def spatial_order(xyz):
 
 @torch.no_grad()
 def knn_keypoints(xyz, motion_feature, kp_xyz, kp_feature, K, knn_type="hybird", feature_amplify=5.0,
-                  return_dists=False, idx32_only=False, order=None):
+                  return_dists=False, idx32_only=False, order=None, hint=None):
     """``get_nearest_mask`` (scene/gaussian_model.py:110-125) without the torch.cat and the FRNN grid set-up.
-    Returns (idx64 [N,K] or None, idx32 [N,K], dists or None).  ``order``: optional ``spatial_order(xyz)``."""
+    Returns (idx64 [N,K] or None, idx32 [N,K], dists or None).  ``order``: optional ``spatial_order(xyz)``;
+    ``hint``: optional int32 [N,K] neighbours of a previous call (speed only; it is overwritten with the new result
+    when given, so the same buffer serves as hint and output across frames)."""
     _need_cuda(xyz, kp_xyz)
     N, Kp = int(xyz.shape[0]), int(kp_xyz.shape[0])
     dev = xyz.device
@@ -112,11 +114,13 @@ def knn_keypoints(xyz, motion_feature, kp_xyz, kp_feature, K, knn_type="hybird",
         F, r, mf, kf = int(motion_feature.shape[1]), 1e8, _c(motion_feature), _c(kp_feature)
     else:
         raise ValueError('knn_type should be "3D" or "hybird"')
-    idx32 = torch.empty((N, K), dtype=torch.int32, device=dev)
+    if hint is not None and (hint.shape != (N, K) or hint.dtype != torch.int32 or not hint.is_contiguous()):
+        hint = None
+    idx32 = hint if hint is not None else torch.empty((N, K), dtype=torch.int32, device=dev)
     idx64 = None if idx32_only else torch.empty((N, K), dtype=torch.int64, device=dev)
     dists = torch.empty((N, K), dtype=torch.float32, device=dev) if return_dists else None
     check(_lib.lib().gp_knn_keypoints(N, Kp, F, int(K), float(r), float(feature_amplify), ptr(_c(xyz)), ptr(mf),
-                                      ptr(_c(kp_xyz)), ptr(kf), ptr(order), ptr(idx64), ptr(idx32), ptr(dists),
+                                      ptr(_c(kp_xyz)), ptr(kf), ptr(order), ptr(hint), ptr(idx64), ptr(idx32), ptr(dists),
                                       _lib.stream_ptr()),
           "gp_knn_keypoints")
     return idx64, idx32, dists
@@ -270,7 +274,7 @@ class KeypointDeformation(nn.Module):
             self.refresh_knn_order()
         idx64, idx32, _ = knn_keypoints(self._xyz, self.motion_feature, self.super_gaussians, self.super_gaussians_feature,
                                         self.args.nearest_num, self.args.knn_type, self.args.feature_amplify,
-                                        order=self._knn_order)
+                                        order=self._knn_order, hint=self._idx32)
         self._idx32 = idx32
         self.nearest_mask = idx64 if keepshape else idx64.view([-1])
 

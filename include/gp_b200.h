@@ -154,10 +154,13 @@ int gp_knn_points(int N, int Kp, int D, int K, float r, const float* points1, co
 
 /* Same search on the un-concatenated model tensors: query = [xyz | motion_feature * feature_amplify]
  * (the torch.cat of scene/gaussian_model.py:115-116 is folded into the kernel; F = 0 selects the "3D" mode of
- * :112-113).  Either index output may be NULL; `order` may be NULL. */
+ * :112-113).  Either index output may be NULL; `order` and `hint` may be NULL.
+ * `hint` (int32 [N,K], e.g. the idx32 output of the previous frame; may alias idx32) only speeds the search up: the
+ * distances to any K distinct keypoints bound the K-th nearest distance, which lets a warp drop every keypoint whose
+ * distance from the warp's bounding box exceeds that bound.  Invalid hint rows are ignored; results never depend on it. */
 int gp_knn_keypoints(int N, int Kp, int F, int K, float r, float feature_amplify, const float* xyz,
                      const float* motion_feature, const float* kp_xyz, const float* kp_feature, const int* order,
-                     long long* idx64, int* idx32, float* dists, gp_stream_t stream);
+                     const int* hint, long long* idx64, int* idx32, float* dists, gp_stream_t stream);
 
 /* Optional acceleration hint for gp_knn_keypoints: `order` = a permutation of 0..N-1 in Morton order of xyz, so that
  * the 32 queries of a warp are spatial neighbours and the kernel's exact warp-wide early exit skips most keypoints.
