@@ -249,8 +249,7 @@ __device__ __forceinline__ V3 dnormvdv3(const V3& v, const V3& dv) {
 // SH backward (reference backward.cu:20-139): writes dL/dsh for the active degree and returns the
 // view-direction part of dL/dmean.
 __device__ __forceinline__ V3 sh_backward(int deg, int M, const V3& pos, const V3& campos,
-                                          const float* __restrict__ shp, unsigned clamp_bits, V3 dL_dRGB,
-                                          float* __restrict__ dL_dshp) {
+                                          const float* shp, unsigned clamp_bits, V3 dL_dRGB, float* dL_dshp) {
   const V3 dir_orig = pos - campos;
   const V3 dir = dir_orig / len3(dir_orig);
   const V3* sh = (const V3*)shp;
@@ -312,19 +311,21 @@ __device__ __forceinline__ V3 sh_backward(int deg, int M, const V3& pos, const V
   return dnormvdv3(dir_orig, dL_ddir);
 }
 
-__global__ void __launch_bounds__(256)
-gp_preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, const int* __restrict__ radii,
-                         const float* __restrict__ shs, const uint8_t* __restrict__ clamped,
-                         const float* __restrict__ scales, const float* __restrict__ rotations, float scale_modifier,
-                         const float* __restrict__ cov3Ds, const float* __restrict__ view,
-                         const float* __restrict__ proj, float h_x, float h_y, float tan_fovx, float tan_fovy,
-                         const float* __restrict__ campos, const float* __restrict__ grec,
-                         float* __restrict__ dL_dmean2D_out, float* __restrict__ dL_dcolors_out,
-                         float* __restrict__ dL_dopacity_out, float* __restrict__ dL_dmeans_out,
-                         float* __restrict__ dL_dcov3D_out, float* __restrict__ dL_dsh_out,
-                         float* __restrict__ dL_dscale_out, float* __restrict__ dL_drot_out) {
-  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= P) return;
+#define GP_SH_ROW 52  // floats per staged SH row in shared memory: 48 + 4 pad (16-byte aligned rows, conflict-free LDS.128)
+
+// Per-Gaussian part of the backward.  sh_row / dsh_row point at this Gaussian's 3*M SH coefficients and at where
+// their gradients go (global memory, or the warp's staging tile in shared memory).
+__device__ __forceinline__ void
+gp_preprocess_bwd_body(int idx, int D, int M, const float* __restrict__ means3D, const int* __restrict__ radii,
+                       const float* sh_row, const uint8_t* __restrict__ clamped,
+                       const float* __restrict__ scales, const float* __restrict__ rotations, float scale_modifier,
+                       const float* __restrict__ cov3Ds, const float* __restrict__ view,
+                       const float* __restrict__ proj, float h_x, float h_y, float tan_fovx, float tan_fovy,
+                       const float* __restrict__ campos, const float* __restrict__ grec,
+                       float* __restrict__ dL_dmean2D_out, float* __restrict__ dL_dcolors_out,
+                       float* __restrict__ dL_dopacity_out, float* __restrict__ dL_dmeans_out,
+                       float* __restrict__ dL_dcov3D_out, float* dsh_row,
+                       float* __restrict__ dL_dscale_out, float* __restrict__ dL_drot_out) {
   const bool visible = radii[idx] > 0;
 
   float rec[GP_GREC];
@@ -357,8 +358,8 @@ gp_preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
     dL_dmeans_out[3 * (size_t)idx + 2] = 0.f;
     if (dL_dcov3D_out)
       for (int k = 0; k < 6; k++) dL_dcov3D_out[6 * (size_t)idx + k] = 0.f;
-    if (dL_dsh_out)
-      for (int k = 0; k < 3 * M; k++) dL_dsh_out[(size_t)idx * 3 * M + k] = 0.f;
+    if (dsh_row)
+      for (int k = 0; k < 3 * M; k++) dsh_row[k] = 0.f;
     if (dL_dscale_out) {
       for (int k = 0; k < 3; k++) dL_dscale_out[3 * (size_t)idx + k] = 0.f;
       for (int k = 0; k < 4; k++) dL_drot_out[4 * (size_t)idx + k] = 0.f;
@@ -448,9 +449,9 @@ gp_preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
   }
 
   // ---- SH backward ----
-  if (shs) {
-    const V3 dm = sh_backward(D, M, mean, v3(campos[0], campos[1], campos[2]), shs + (size_t)idx * M * 3, clamped[idx],
-                              v3(rec[6], rec[7], rec[8]), dL_dsh_out + (size_t)idx * M * 3);
+  if (sh_row) {
+    const V3 dm = sh_backward(D, M, mean, v3(campos[0], campos[1], campos[2]), sh_row, clamped[idx],
+                              v3(rec[6], rec[7], rec[8]), dsh_row);
     dL_dmean += dm;
   }
   dL_dmeans_out[3 * (size_t)idx] = dL_dmean.x;
@@ -503,6 +504,59 @@ gp_preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
   }
 }
 
+// Thread per Gaussian.  The SH coefficients (read) and their gradients (written) are 192-byte rows: accessed
+// thread-per-row they cost one 32-byte sector per lane per instruction.  Each warp therefore moves the 6 KB of its
+// 32 consecutive Gaussians with fully coalesced 128-bit accesses through a shared-memory tile (rows padded to 52
+// floats so that the per-lane row reads are conflict-free).
+__global__ void __launch_bounds__(256)
+gp_preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, const int* __restrict__ radii,
+                         const float* __restrict__ shs, const uint8_t* __restrict__ clamped,
+                         const float* __restrict__ scales, const float* __restrict__ rotations, float scale_modifier,
+                         const float* __restrict__ cov3Ds, const float* __restrict__ view,
+                         const float* __restrict__ proj, float h_x, float h_y, float tan_fovx, float tan_fovy,
+                         const float* __restrict__ campos, const float* __restrict__ grec,
+                         float* __restrict__ dL_dmean2D_out, float* __restrict__ dL_dcolors_out,
+                         float* __restrict__ dL_dopacity_out, float* __restrict__ dL_dmeans_out,
+                         float* __restrict__ dL_dcov3D_out, float* __restrict__ dL_dsh_out,
+                         float* __restrict__ dL_dscale_out, float* __restrict__ dL_drot_out, int staged) {
+  extern __shared__ __align__(16) float s_tiles[];  // staged: [8 warps][32][52] in, then [8 warps][32][52] out
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int warp_base = idx - lane;
+  const float* sh_row = shs ? shs + (size_t)idx * M * 3 : nullptr;
+  float* dsh_row = dL_dsh_out ? dL_dsh_out + (size_t)idx * M * 3 : nullptr;
+  float* tin = s_tiles + (size_t)w * 32 * GP_SH_ROW;
+  float* tout = s_tiles + (size_t)(8 + w) * 32 * GP_SH_ROW;
+  if (staged) {
+    const float4* src = (const float4*)(shs + (size_t)warp_base * 48);
+    const int rows = min(32, P - warp_base);
+#pragma unroll
+    for (int it = 0; it < 12; it++) {
+      const int i4 = it * 32 + lane;
+      const int row = i4 / 12, c4 = i4 - row * 12;
+      if (row < rows) *(float4*)(tin + row * GP_SH_ROW + 4 * c4) = __ldg(src + i4);
+    }
+    __syncwarp();
+    sh_row = tin + lane * GP_SH_ROW;
+    dsh_row = tout + lane * GP_SH_ROW;
+  }
+  if (idx < P)
+    gp_preprocess_bwd_body(idx, D, M, means3D, radii, sh_row, clamped, scales, rotations, scale_modifier, cov3Ds, view,
+                           proj, h_x, h_y, tan_fovx, tan_fovy, campos, grec, dL_dmean2D_out, dL_dcolors_out,
+                           dL_dopacity_out, dL_dmeans_out, dL_dcov3D_out, dsh_row, dL_dscale_out, dL_drot_out);
+  if (staged) {
+    __syncwarp();
+    float4* dst = (float4*)(dL_dsh_out + (size_t)warp_base * 48);
+    const int rows = min(32, P - warp_base);
+#pragma unroll
+    for (int it = 0; it < 12; it++) {
+      const int i4 = it * 32 + lane;
+      const int row = i4 / 12, c4 = i4 - row * 12;
+      if (row < rows) dst[i4] = *(const float4*)(tout + row * GP_SH_ROW + 4 * c4);
+    }
+  }
+}
+
 extern "C" size_t gp_raster_backward_ws_bytes(int P) { return gp_align_up((size_t)(P > 0 ? P : 1) * GP_GREC * 4, 256); }
 
 extern "C" int gp_raster_backward(const gp_raster_cfg* cfg, const float* bg, const float* means3D, const float* shs,
@@ -540,11 +594,16 @@ extern "C" int gp_raster_backward(const gp_raster_cfg* cfg, const float* bg, con
                                                            im.n_contrib, dL_dpix, g.hdr, grec));
   GP_LAUNCH_CHECK();
   const float* cov3D_ptr = cov3D_precomp ? cov3D_precomp : g.cov3D;
-  GP_KERNEL("gp_preprocess_bwd_kernel", stream, gp_preprocess_bwd_kernel<<<(P + 255) / 256, 256, 0, stream>>>(
+  // SH rows go through shared memory when they are the standard 16 coefficients and 16-byte aligned
+  const int staged = (shs != nullptr && cfg->sh_coeffs == 16 && ((((size_t)shs) | ((size_t)dL_dsh)) & 15) == 0) ? 1 : 0;
+  const size_t pb_smem = staged ? (size_t)16 * 32 * GP_SH_ROW * sizeof(float) : 0;
+  if (pb_smem > 48 * 1024)
+    GP_CUDA_TRY(cudaFuncSetAttribute(gp_preprocess_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pb_smem));
+  GP_KERNEL("gp_preprocess_bwd_kernel", stream, gp_preprocess_bwd_kernel<<<(P + 255) / 256, 256, pb_smem, stream>>>(
       P, cfg->sh_degree, cfg->sh_coeffs, means3D, radii, shs, g.clamped, has_sr ? scales : nullptr,
       has_sr ? rotations : nullptr, cfg->scale_modifier, cov3D_ptr, viewmatrix, projmatrix, focal_x, focal_y,
       cfg->tanfovx, cfg->tanfovy, campos, grec, dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh,
-      dL_dscales, dL_drots));
+      dL_dscales, dL_drots, staged));
   GP_LAUNCH_CHECK();
   return GP_OK;
 }
