@@ -22,6 +22,7 @@ CASES = {
     "behind": dict(N=4000, W=128, H=128, seed=6, cam_kwargs=dict(radius=0.8)),  # camera inside the cloud: near culling
     "hyper": dict(N=20000, W=134, H=240, seed=7, shape="hyper"),
     "c2": dict(N=100000, W=800, H=800, seed=2024),
+    "c3": dict(N=500000, W=536, H=960, seed=2025, shape="hyper"),           # BASELINE.json configs[2] shape
 }
 
 
@@ -103,7 +104,7 @@ def test_forward_bit_exact_vs_reference(gplib, name):
     assert dc <= FWD_TOL and dd <= FWD_TOL, (dc, dd)
 
 
-@pytest.mark.parametrize("name", ["small", "ragged", "big_splats", "hyper", "c2"])
+@pytest.mark.parametrize("name", ["small", "ragged", "big_splats", "hyper", "c2", "c3"])
 def test_backward_vs_reference(gplib, name):
     need_ref()
     case = raster_case(**CASES[name])
@@ -225,3 +226,46 @@ def test_capacity_mode_and_overflow(gplib):
     *_, st2 = R.raster_forward(*args, capacity=Rn // 2)
     s2 = R.export_state(st2)
     assert s2["overflow"] == 1 and s2["num_rendered"] == Rn
+
+
+def test_full_size_invariants_1m(gplib):
+    """BASELINE.json configs[3]/[4] sizes (1M Gaussians, 800x800): size-independent properties of the pipeline --
+    sum of tiles touched = R, the instance list is sorted by (tile, depth bits, index), ranges partition it, every
+    pixel's n_contrib lies inside its tile's range, a second run is bit-identical (idempotence), gradients are finite
+    and exactly zero for culled Gaussians, and (when the reference build is present) the image matches it bit for bit."""
+    case = raster_case(N=1_000_000, W=800, H=800, seed=77)
+    grad = seeded_grad(case)
+    a = run_mine(case, grad)
+    st = a["state"]
+    R = st["num_rendered"]
+    assert int(st["tiles_touched"].to(torch.int64).sum()) == R and st["overflow"] == 0
+    keys = st["point_list_keys"]
+    assert bool((keys[1:] >= keys[:-1]).all())
+    eq = keys[1:] == keys[:-1]
+    pl = st["point_list"]
+    assert bool((pl[1:][eq] > pl[:-1][eq]).all())                      # ties: ascending Gaussian index
+    rng = st["ranges"].to(torch.int64)
+    nonempty = rng[:, 1] > rng[:, 0]
+    assert int((rng[nonempty, 1] - rng[nonempty, 0]).sum()) == R       # ranges partition the list
+    tiles_of_key = (keys >> 32)
+    starts = rng[nonempty, 0]
+    assert bool((tiles_of_key[starts] == torch.nonzero(nonempty).squeeze(1)).all())
+    gx = (case["W"] + 15) // 16
+    ys, xs = torch.meshgrid(torch.arange(case["H"], device="cuda"), torch.arange(case["W"], device="cuda"), indexing="ij")
+    tile_of_pix = ((ys // 16) * gx + xs // 16).reshape(-1)
+    lens = (rng[:, 1] - rng[:, 0])[tile_of_pix]
+    assert bool((st["n_contrib"].to(torch.int64) <= lens).all())
+    b = run_mine(case, grad)
+    for k in ("color", "depth", "tidx", "radii"):
+        assert count_diff(a[k], b[k]) == 0, k                           # idempotent
+    inv = ~(a["radii"] > 0)
+    for k in ("means2D", "opacity", "means3D", "sh", "scales", "rotations"):
+        g = a["grads"][k]
+        assert bool(torch.isfinite(g).all()) and float(g[inv].abs().sum()) == 0.0, k
+    from oracle import ref_cuda
+    if ref_cuda.available("ref_dgr"):
+        ref = run_ref(case, grad)
+        assert count_diff(a["color"], ref["fwd"]["color"]) == 0 and count_diff(a["tidx"], ref["fwd"]["tidx"]) == 0
+        assert count_diff(a["radii"], ref["fwd"]["radii"]) == 0
+        for k in ("means2D", "opacity", "means3D", "sh", "scales", "rotations"):
+            assert rel_err(a["grads"][k], ref["grads"][k]) <= GRAD_TOL, k
