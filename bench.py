@@ -203,8 +203,8 @@ class OurRunner:
 
     def allreduce(self):
         if self.reducer is None:
-            from gaussianprediction_b200.parallel import FlatGradAllReduce
-            self.reducer = FlatGradAllReduce(self.params)
+            from gaussianprediction_b200.parallel import GroupedGradAllReduce
+            self.reducer = GroupedGradAllReduce(self.params)
         self.reducer.reduce()
 
     def eval_fps(self, steps, graph=False):

@@ -50,6 +50,42 @@ class FlatGradAllReduce:
         return work
 
 
+class GroupedGradAllReduce:
+    """Sum the parameter gradients over the ranks WITHOUT packing them: all tensors go into one NCCL group call
+    (ncclGroupStart/End through torch's coalescing manager), i.e. one fused collective over NVLink with no staging
+    copy of the ~236 B per Gaussian.  Parameters that got no gradient on this rank contribute zeros (every rank must
+    issue the same sequence of collectives).  Falls back to ``FlatGradAllReduce`` on backends without coalescing (gloo)."""
+
+    def __init__(self, params, group=None):
+        self.params = [p for p in params if p.requires_grad]
+        self.group = group
+        self._flat = None
+
+    @property
+    def nbytes(self):
+        return sum(p.numel() * p.element_size() for p in self.params)
+
+    def reduce(self):
+        backend = dist.get_backend(self.group)
+        if backend != "nccl":
+            if self._flat is None:
+                self._flat = FlatGradAllReduce(self.params, self.group)
+            return self._flat.reduce()
+        grads = []
+        for p in self.params:
+            if p.grad is None:
+                p.grad = torch.zeros_like(p)
+            grads.append(p.grad if p.grad.is_contiguous() else p.grad.contiguous())
+        from torch.distributed.distributed_c10d import _coalescing_manager
+        with _coalescing_manager(group=self.group, device=grads[0].device, async_ops=False):
+            for g in grads:
+                dist.all_reduce(g, op=dist.ReduceOp.SUM, group=self.group)
+        for p, g in zip(self.params, grads):
+            if p.grad is not g:
+                p.grad = g
+        return None
+
+
 def reduce_densification_stats(radii, visibility_filter, group=None):
     """``radii = max over samples``, ``visibility = or over samples`` (train.py:122-123) across ranks, in place."""
     dist.all_reduce(radii, op=dist.ReduceOp.MAX, group=group)

@@ -21,6 +21,13 @@ def _worker(rank, world, port, out):
     loss.backward()                                         # params[2] gets no gradient on any rank
     red = FlatGradAllReduce(params)
     red.reduce()
+    # the grouped variant falls back to the flat path on gloo and must agree with it
+    from gaussianprediction_b200.parallel import GroupedGradAllReduce
+    params2 = [torch.nn.Parameter(p.detach().clone()) for p in params]
+    loss2 = sum(((s + 1) * (params2[0] ** 2).sum() + (s + 2) * params2[1].sum()) for s in mine)
+    loss2.backward()
+    GroupedGradAllReduce(params2).reduce()
+    assert torch.allclose(params2[0].grad, params[0].grad) and torch.allclose(params2[1].grad, params[1].grad)
     radii = torch.tensor([rank + 1, 5 - rank, 0], dtype=torch.int32)
     vis = torch.tensor([rank == 0, rank == 1, False])
     radii, vis = reduce_densification_stats(radii, vis)
