@@ -186,7 +186,12 @@ class OurRunner:
     def enable_graph(self):
         """Capture the whole iteration into one CUDA graph (gaussianprediction_b200.pipeline.TrainStep)."""
         from gaussianprediction_b200.pipeline import RenderStep, TrainStep
-        self.train_step = TrainStep(self.pc, self.cams_dev[0], self.capacity, bg=self.bg, iteration=ITER)
+        reducer = None
+        if self.world > 1:
+            from gaussianprediction_b200.parallel import FlatGradAllReduce
+            reducer = FlatGradAllReduce(self.params)
+        self.graph_reducer = reducer
+        self.train_step = TrainStep(self.pc, self.cams_dev[0], self.capacity, bg=self.bg, iteration=ITER, reducer=reducer)
         self.render_step = RenderStep(self.pc, self.cams_dev[0], self.capacity, bg=self.bg, iteration=ITER)
 
     def step_graph(self, i, host_inputs=False):
@@ -196,9 +201,7 @@ class OurRunner:
             cam, t, G = self.cams_host[k], self.times_host[k:k + 1], self.grads_host[i % len(self.grads_host)]
         else:
             cam, t, G = self.cams_dev[k], self.times_dev[k], self.grads_dev[i % len(self.grads_dev)]
-        loss = self.train_step(cam, t, G)
-        if self.world > 1:
-            self.allreduce()
+        loss = self.train_step(cam, t, G)       # with world > 1 the step includes the gradient all-reduce
         return loss
 
     def allreduce(self):

@@ -42,9 +42,19 @@ class TrainStep:
     ``overflowed()`` tells whether the last frame exceeded it (that frame's image and gradients are then invalid).
     """
 
-    def __init__(self, pc, cam, capacity, bg=None, iteration=50_000, loss_fn=None, warmup=3):
+    def __init__(self, pc, cam, capacity, bg=None, iteration=50_000, loss_fn=None, warmup=3, reducer=None,
+                 capture_collective=False):
+        """``reducer``: a ``parallel.FlatGradAllReduce`` over the same parameters.  The gradients are then accumulated
+        straight into its flat buffer inside the graph (no packing copies) and summed over the ranks with ONE
+        all-reduce per step, issued right after the replay.  ``capture_collective=True`` records the all-reduce into
+        the graph as well; EXPERIMENTAL -- with torch 2.11 / NCCL 2.28 on the B200 test box that capture hung, so it is
+        off by default and not used by bench.py."""
         self.pc = pc
+        self.reducer = reducer
+        self.capture_collective = bool(capture_collective and reducer is not None)
         self.params = [p for p in pc.parameters() if p.requires_grad]
+        if reducer is not None:
+            assert [id(p) for p in reducer.params] == [id(p) for p in self.params], "reducer must cover pc's parameters"
         dev = self.params[0].device
         self.dev = dev
         self.capacity = int(capacity)
@@ -65,8 +75,9 @@ class TrainStep:
                 self._body()
         torch.cuda.current_stream(dev).wait_stream(side)
         torch.cuda.synchronize(dev)
-        for p in self.params:
-            p.grad = None
+        if self.reducer is None:
+            for p in self.params:
+                p.grad = None
         self.graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(self.graph):
             self._body()
@@ -81,17 +92,28 @@ class TrainStep:
         return int(hdr[_lib.HDR_NUM_RENDERED]), bool(int(hdr[_lib.HDR_OVERFLOW]))
 
     def _body(self):
-        for p in self.params:
-            p.grad = None
+        if self.reducer is None:
+            for p in self.params:
+                p.grad = None
+        else:
+            self.reducer.flat.zero_()                 # autograd then accumulates in place into the flat views
+            for p, v in zip(self.params, self.reducer.views):
+                p.grad = v
         self.pkg = render(self.cam, self.pc, None, self.bg, time=self.t, it=self.iteration, capacity=self.capacity)
         self.loss = self.loss_fn(self.pkg["render"], self.target)
         self.loss.backward()
+        if self.capture_collective:
+            import torch.distributed as dist
+            dist.all_reduce(self.reducer.flat, op=dist.ReduceOp.SUM, group=self.reducer.group)
 
     def __call__(self, cam, t, target, non_blocking=True):
         self.cam.load(cam, non_blocking)
         self.t.copy_(t, non_blocking=non_blocking)
         self.target.copy_(target, non_blocking=non_blocking)
         self.graph.replay()
+        if self.reducer is not None and not self.capture_collective:
+            import torch.distributed as dist
+            dist.all_reduce(self.reducer.flat, op=dist.ReduceOp.SUM, group=self.reducer.group)
         for p, g in zip(self.params, self.grads):     # p.grad may have been replaced / cleared by the caller
             p.grad = g
         return self.loss
