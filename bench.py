@@ -189,7 +189,8 @@ class OurRunner:
         reducer = None
         if self.world > 1:
             from gaussianprediction_b200.parallel import FlatGradAllReduce
-            reducer = FlatGradAllReduce(self.params)
+            # only parameters that receive a gradient on this path take part in the exchange (known after the eager pass)
+            reducer = FlatGradAllReduce([p for p in self.params if p.grad is not None])
         self.graph_reducer = reducer
         self.train_step = TrainStep(self.pc, self.cams_dev[0], self.capacity, bg=self.bg, iteration=ITER, reducer=reducer)
         self.render_step = RenderStep(self.pc, self.cams_dev[0], self.capacity, bg=self.bg, iteration=ITER)

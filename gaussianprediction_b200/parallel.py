@@ -53,8 +53,7 @@ class FlatGradAllReduce:
 class GroupedGradAllReduce:
     """Sum the parameter gradients over the ranks WITHOUT packing them: all tensors go into one NCCL group call
     (ncclGroupStart/End through torch's coalescing manager), i.e. one fused collective over NVLink with no staging
-    copy of the ~236 B per Gaussian.  Parameters that got no gradient on this rank contribute zeros (every rank must
-    issue the same sequence of collectives).  Falls back to ``FlatGradAllReduce`` on backends without coalescing (gloo)."""
+    copy of the ~236 B per Gaussian.  Falls back to ``FlatGradAllReduce`` on backends without coalescing (gloo)."""
 
     def __init__(self, params, group=None):
         self.params = [p for p in params if p.requires_grad]
@@ -71,16 +70,17 @@ class GroupedGradAllReduce:
             if self._flat is None:
                 self._flat = FlatGradAllReduce(self.params, self.group)
             return self._flat.reduce()
-        grads = []
-        for p in self.params:
-            if p.grad is None:
-                p.grad = torch.zeros_like(p)
-            grads.append(p.grad if p.grad.is_contiguous() else p.grad.contiguous())
+        # Parameters without a gradient are skipped: which leaves receive one is a property of the model graph, so it
+        # is the same on every rank and the ranks still issue identical collectives.
+        live = [p for p in self.params if p.grad is not None]
+        grads = [p.grad if p.grad.is_contiguous() else p.grad.contiguous() for p in live]
+        if not grads:
+            return None
         from torch.distributed.distributed_c10d import _coalescing_manager
         with _coalescing_manager(group=self.group, device=grads[0].device, async_ops=False):
             for g in grads:
                 dist.all_reduce(g, op=dist.ReduceOp.SUM, group=self.group)
-        for p, g in zip(self.params, grads):
+        for p, g in zip(live, grads):
             if p.grad is not g:
                 p.grad = g
         return None

@@ -54,7 +54,11 @@ class TrainStep:
         self.capture_collective = bool(capture_collective and reducer is not None)
         self.params = [p for p in pc.parameters() if p.requires_grad]
         if reducer is not None:
-            assert [id(p) for p in reducer.params] == [id(p) for p in self.params], "reducer must cover pc's parameters"
+            # the reducer may cover a subset (parameters that never receive a gradient on this path, e.g. the
+            # per-Gaussian motion_feature in the keypoint stage, need no exchange)
+            ids = {id(p) for p in self.params}
+            assert all(id(p) in ids for p in reducer.params), "reducer parameters must belong to pc"
+        self._reduced = {id(p) for p in reducer.params} if reducer is not None else set()
         dev = self.params[0].device
         self.dev = dev
         self.capacity = int(capacity)
@@ -97,7 +101,10 @@ class TrainStep:
                 p.grad = None
         else:
             self.reducer.flat.zero_()                 # autograd then accumulates in place into the flat views
-            for p, v in zip(self.params, self.reducer.views):
+            for p in self.params:
+                if id(p) not in self._reduced:
+                    p.grad = None
+            for p, v in zip(self.reducer.params, self.reducer.views):
                 p.grad = v
         self.pkg = render(self.cam, self.pc, None, self.bg, time=self.t, it=self.iteration, capacity=self.capacity)
         self.loss = self.loss_fn(self.pkg["render"], self.target)
