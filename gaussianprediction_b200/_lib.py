@@ -53,6 +53,9 @@ SIGNATURES = {
     "gp_blend_dense_weights": (c_int, [c_int, c_int, c_int] + [_P] * 7),
     "gp_dist2_ws_bytes": (c_size_t, [c_int]),
     "gp_dist2_knn3": (c_int, [c_int, _P, _P, _P, _P]),
+    "gp_image_loss_ws_bytes": (c_size_t, [c_int, c_int, c_int]),
+    "gp_image_loss_forward": (c_int, [c_int, c_int, c_int, _P, _P, _P, _P, _P, _P]),
+    "gp_image_loss_backward": (c_int, [c_int, c_int, c_int, _P, _P, _P, c_float, c_float, _P, _P, _P]),
     "gp_raster_export_binning": (c_int, [POINTER(RasterCfg), _P, _P, c_longlong, _P, _P, _P]),
 }
 

@@ -204,6 +204,22 @@ int gp_blend_dense_weights(int N, int Kp, int K, const float* logits, const int*
 size_t gp_dist2_ws_bytes(int P);
 int gp_dist2_knn3(int P, const float* points /*[P,3]*/, float* mean_dist2 /*[P]*/, void* ws, gp_stream_t stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * Image loss (the step right after the rasterizer).  Stands in for the torch ops of
+ * utils/loss_utils.py:54-100 (l1_loss, ssim/_ssim with the 11x11 sigma-1.5 window, zero padding) as train.py:105-108
+ * combines them, and for their autograd backward.  Images are [C,H,W] float32 planes (any leading dims folded into C).
+ * ---------------------------------------------------------------------------------------------- */
+
+/* sums[0] = mean |img - gt|, sums[1] = mean SSIM map (device floats).  dmaps: scratch of 3*C*H*W floats that the
+ * backward reads (NULL if no backward will follow); ws: gp_image_loss_ws_bytes bytes. */
+size_t gp_image_loss_ws_bytes(int C, int H, int W);
+int gp_image_loss_forward(int C, int H, int W, const float* img, const float* gt, float* dmaps, void* ws, float* sums,
+                          gp_stream_t stream);
+/* grad_img = (*grad_scale) * d/d img [ w_l1 * mean|img-gt| + w_ssim * mean SSIM ];  grad_scale: device scalar or NULL (=1).
+ * train.py:108 is w_l1 = 1 - lambda_dssim, w_ssim = -lambda_dssim. */
+int gp_image_loss_backward(int C, int H, int W, const float* img, const float* gt, const float* dmaps, float w_l1,
+                           float w_ssim, const float* grad_scale, float* grad_img, gp_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

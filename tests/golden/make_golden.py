@@ -57,7 +57,20 @@ def make_cpu(out_dir):
     d3, i3 = ref_cuda.frnn_bf_cpu(p1[None, :, :3].contiguous(), p2[None, :, :3].contiguous(), 6, 1e3)
     np.savez_compressed(os.path.join(out_dir, "knn_cpu.npz"), p1=p1.numpy(), p2=p2.numpy(), d35=d35[0].numpy(),
                         i35=i35[0].numpy(), d3=d3[0].numpy(), i3=i3[0].numpy())
-    print("wrote deform_mlp_pe.npz, knn_cpu.npz to", out_dir)
+    # image loss: the reference's own l1_loss / ssim (utils/loss_utils.py) and their autograd gradient
+    spec = importlib.util.spec_from_file_location("ref_loss_utils", os.path.join(ref_root, "utils", "loss_utils.py"))
+    lu = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(lu)
+    g = torch.Generator().manual_seed(7)
+    img = torch.rand(3, 45, 70, generator=g).requires_grad_(True)
+    gt = (img.detach() + 0.1 * torch.randn(3, 45, 70, generator=g)).clamp(0, 1)
+    l1 = lu.l1_loss(img, gt)
+    ss = lu.ssim(img, gt)
+    loss = (1.0 - 0.2) * l1 + 0.2 * (1.0 - ss)
+    loss.backward()
+    np.savez_compressed(os.path.join(out_dir, "loss.npz"), img=img.detach().numpy(), gt=gt.numpy(), l1=l1.item(),
+                        ssim=ss.item(), loss=loss.item(), grad=img.grad.numpy())
+    print("wrote deform_mlp_pe.npz, knn_cpu.npz, loss.npz to", out_dir)
 
 
 def make_gpu(out_dir):

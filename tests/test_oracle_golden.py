@@ -138,3 +138,17 @@ def test_blend_oracle_dense_vs_sparse_identity():
     sr = (torch.softmax(logits[:, K:], -1)[..., None] * dq[idx]).sum(1)
     assert float((wx @ dx - sx).abs().max()) <= 1e-5 and float((wr @ dq - sr).abs().max()) <= 1e-5
     assert float((wx.sum(1) - 1).abs().max()) <= 1e-5
+
+
+def test_loss_oracle_vs_reference_functions():
+    """oracle/loss_oracle.py against the reference's own l1_loss / ssim and their autograd gradient (loss.npz)."""
+    from oracle import loss_oracle as lo
+    g = np.load(os.path.join(GOLD, "loss.npz"))
+    img = torch.tensor(g["img"]).requires_grad_(True)
+    gt = torch.tensor(g["gt"])
+    assert abs(float(lo.l1_loss(img, gt)) - float(g["l1"])) <= 1e-7
+    assert abs(float(lo.ssim(img, gt)) - float(g["ssim"])) <= 1e-6
+    loss = lo.image_loss(img, gt, 0.2)
+    loss.backward()
+    assert abs(float(loss) - float(g["loss"])) <= 1e-6
+    assert rel(img.grad.numpy(), g["grad"]) <= 1e-5

@@ -149,6 +149,21 @@ def test_lower_sh_degree_vs_reference(gplib, deg):
     assert rel_err(mine["grads"]["means3D"], ref["grads"]["means3D"]) <= GRAD_TOL
 
 
+@pytest.mark.parametrize("deg,M", [(0, 1), (1, 4), (2, 9)])
+def test_fewer_sh_coefficients_vs_reference(gplib, deg, M):
+    """max_sh_degree < 3: SH tensors with M = (deg+1)^2 coefficients take the non-staged row path."""
+    need_ref()
+    case = raster_case(**CASES["small"])
+    case["shs"] = case["shs"][:, :M, :].contiguous()
+    case["sh_degree"] = deg
+    grad = seeded_grad(case)
+    mine, ref = run_mine(case, grad), run_ref(case, grad)
+    assert count_diff(mine["color"], ref["fwd"]["color"]) == 0 and count_diff(mine["radii"], ref["fwd"]["radii"]) == 0
+    assert mine["grads"]["sh"].shape == (case["means3D"].shape[0], M, 3)
+    for k in ("sh", "means3D", "opacity", "scales", "rotations"):
+        assert rel_err(mine["grads"][k], ref["grads"][k]) <= GRAD_TOL, k
+
+
 def test_forward_backward_vs_cpu_oracle(gplib):
     from oracle import raster_oracle as ro
     case = raster_case(**CASES["small"])
