@@ -195,7 +195,20 @@ class OurRunner:
         self.train_step = TrainStep(self.pc, self.cams_dev[0], self.capacity, bg=self.bg, iteration=ITER, reducer=reducer)
         self.render_step = RenderStep(self.pc, self.cams_dev[0], self.capacity, bg=self.bg, iteration=ITER)
 
+    def _host_sample(self, i):
+        i = i * self.world + self.rank
+        k = i % len(self.cams_dev)
+        return self.cams_host[k], self.times_host[k:k + 1], self.grads_host[i % len(self.grads_host)]
+
     def step_graph(self, i, host_inputs=False):
+        if host_inputs:
+            # end-to-end: every sample comes from pinned host memory; sample i+1 is copied while step i computes
+            if getattr(self, "_prefetched", None) != i:
+                self.train_step.prefetch(*self._host_sample(i))
+            loss = self.train_step.step_prefetched()
+            self.train_step.prefetch(*self._host_sample(i + 1))
+            self._prefetched = i + 1
+            return loss
         i = i * self.world + self.rank
         k = i % len(self.cams_dev)
         if host_inputs:

@@ -113,10 +113,50 @@ class TrainStep:
             import torch.distributed as dist
             dist.all_reduce(self.reducer.flat, op=dist.ReduceOp.SUM, group=self.reducer.group)
 
+    # ---- input prefetch: the next sample's host->device copies overlap the current step's kernels ----
+    def prefetch(self, cam, t, target):
+        """Start copying the NEXT sample (pinned host tensors) on a side stream into a staging slot; the following
+        ``step_prefetched()`` moves it into the graph's static inputs (device-to-device) and replays."""
+        if not hasattr(self, "_stage"):
+            self._copy_stream = torch.cuda.Stream(device=self.dev)
+            self._stage = [dict(view=torch.empty(4, 4, device=self.dev), proj=torch.empty(4, 4, device=self.dev),
+                                center=torch.empty(3, device=self.dev), t=torch.empty(1, device=self.dev),
+                                target=torch.empty_like(self.target), ready=torch.cuda.Event(), free=torch.cuda.Event())
+                           for _ in range(2)]
+            self._slot = 0
+            for s in self._stage:
+                s["free"].record(torch.cuda.current_stream(self.dev))
+        s = self._stage[self._slot]
+        with torch.cuda.stream(self._copy_stream):
+            self._copy_stream.wait_event(s["free"])          # the step that consumed this slot has read it
+            s["view"].copy_(cam.world_view_transform, non_blocking=True)
+            s["proj"].copy_(cam.full_proj_transform, non_blocking=True)
+            s["center"].copy_(cam.camera_center, non_blocking=True)
+            s["t"].copy_(t, non_blocking=True)
+            s["target"].copy_(target, non_blocking=True)
+            s["ready"].record(self._copy_stream)
+        self._pending = s
+        self._slot ^= 1
+
+    def step_prefetched(self):
+        s = self._pending
+        cur = torch.cuda.current_stream(self.dev)
+        cur.wait_event(s["ready"])
+        self.cam.world_view_transform.copy_(s["view"])
+        self.cam.full_proj_transform.copy_(s["proj"])
+        self.cam.camera_center.copy_(s["center"])
+        self.t.copy_(s["t"])
+        self.target.copy_(s["target"])
+        s["free"].record(cur)
+        return self._replay()
+
     def __call__(self, cam, t, target, non_blocking=True):
         self.cam.load(cam, non_blocking)
         self.t.copy_(t, non_blocking=non_blocking)
         self.target.copy_(target, non_blocking=non_blocking)
+        return self._replay()
+
+    def _replay(self):
         self.graph.replay()
         if self.reducer is not None and not self.capture_collective:
             import torch.distributed as dist
