@@ -1,0 +1,475 @@
+// The keypoint-motion MLP of the deformation stage, forward and backward, as three small kernels.
+//
+// Stands in for the torch ops of reference scene/gaussian_model.py:180-189 (get_motion_delta: repeat t, cat, df_model)
+// on top of scene/deformable_field.py:63-72 (positional_encoding) and :74-127 (Deformable_Field: d x (Linear+ReLU),
+// then Linear) for the keypoint call sites (:255-265).  With ~512 keypoints the torch path is ~70 launches of
+// 3-10 us each per iteration (0.26 ms of a 1.18 ms train iteration on B200, profiles/r1_keypoint_mlp.md); the work
+// itself is ~1 GFLOP, so it is launch/latency bound and is fused here:
+//
+//   forward    : a block owns 4 keypoints; thread j owns hidden unit j.  Builds the input row
+//                [feature | PE(xyz) | PE(t)] in shared memory, walks the layers with the activations ping-ponging
+//                between two shared-memory rows, keeps the post-ReLU activations for the backward.  The weights stream
+//                through a 4-stage cp.async ring of 32 KB chunks that runs ahead across layer boundaries.
+//   bwd (data) : same tiling and ring walked backwards, ReLU masks from the saved activations; writes
+//                dL/d(pre-activation) of every layer, the feature gradient and the xyz gradient through the encoding.
+//   bwd (weights): all layers in one launch, 32x64 output tiles of dW_l = dZ_l^T H_{l-1} summed over the keypoints
+//                in a fixed order (no atomics: bit-reproducible), bias gradient alongside, 3-stage cp.async ring.
+// Every block re-reads all the weights (1 MB), so the kernels are bound by L2 -> SM bandwidth, not HBM.
+//
+// fp32 FMA throughout like the reference's fp32 cuBLAS GEMMs (no TF32); sums run in index order.
+#include "../../include/gp_b200.h"
+#include "common.cuh"
+
+#define MLP_ROWS 4
+#define MLP_MAXW 256
+#define MLP_MAXL 9  // hidden layers + the output layer
+#define MLP_THREADS 256
+
+struct MlpDims {
+  int rows, F, xf, tf, depth, w, out, din;
+};
+struct MlpPtrs {
+  const float* W[MLP_MAXL];
+  const float* b[MLP_MAXL];
+  float* gW[MLP_MAXL];
+  float* gb[MLP_MAXL];
+};
+struct MlpTiles {
+  int first[MLP_MAXL + 1];
+};
+
+static int mlp_dims(const gp_mlp_cfg* c, MlpDims* d) {
+  if (!c) return GP_ERR_BAD_ARG;
+  d->rows = c->rows; d->F = c->feature_dim; d->xf = c->xyz_freq; d->tf = c->time_freq;
+  d->depth = c->depth; d->w = c->width; d->out = c->out_dim;
+  d->din = c->feature_dim + 6 * c->xyz_freq + 2 * c->time_freq;
+  if (c->rows < 0 || c->feature_dim < 0 || c->xyz_freq < 0 || c->time_freq < 0) return GP_ERR_BAD_ARG;
+  if (c->xyz_freq > 24 || c->time_freq > 24) return GP_ERR_LIMIT;  // 2^f must stay exact in the encoding
+  if (c->depth < 1 || c->depth > MLP_MAXL - 1) return GP_ERR_LIMIT;
+  if (c->width < 4 || c->width > MLP_MAXW || (c->width & 3)) return GP_ERR_LIMIT;
+  if (d->din < 4 || d->din > MLP_MAXW || (d->din & 3)) return GP_ERR_LIMIT;
+  if (c->out_dim < 1 || c->out_dim > 8) return GP_ERR_LIMIT;
+  return GP_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ async copies
+
+// Ampere-style asynchronous global->shared copies: the weight chunks of the next stages are in flight while the current
+// one is being consumed, with no staging registers.  (A weight matrix is re-read by every block, so it comes from L2.)
+__device__ __forceinline__ void mlp_cp16(float* smem, const float* gmem, bool valid = true) {
+  const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+  const int n = valid ? 16 : 0;  // 0 source bytes: the 16 destination bytes are zero-filled
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(s), "l"(gmem), "r"(n) : "memory");
+}
+__device__ __forceinline__ void mlp_cp4(float* smem, const float* gmem, bool valid = true) {
+  const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+  const int n = valid ? 4 : 0;
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(s), "l"(gmem), "r"(n) : "memory");
+}
+__device__ __forceinline__ void mlp_cp_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void mlp_cp_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+#define MLP_CH 32     // weight columns (forward) / rows (backward) per chunk
+#define MLP_STAGES 4  // chunks resident in shared memory
+#define MLP_STAGE_FLOATS (MLP_CH * MLP_MAXW)
+#define MLP_SMEM_BYTES ((2 * MLP_ROWS * MLP_MAXW + MLP_STAGES * MLP_STAGE_FLOATS) * sizeof(float))
+
+extern __shared__ __align__(16) float mlp_smem[];
+
+// ------------------------------------------------------------------------------------------------ forward
+
+// column c of the network input of keypoint `row` (scene/gaussian_model.py:188: cat([feature, xyz_embed, t]))
+__device__ __forceinline__ float mlp_input(const MlpDims& d, const float* __restrict__ xyz, const float* __restrict__ feat,
+                                           float t, int row, int c) {
+  if (c < d.F) return __ldg(feat + (size_t)row * d.F + c);
+  c -= d.F;
+  float x;
+  int f;
+  if (c < 6 * d.xf) {
+    const int dim = c / (2 * d.xf);
+    f = (c >> 1) % d.xf;
+    x = __ldg(xyz + (size_t)row * 3 + dim);
+  } else {
+    c -= 6 * d.xf;
+    f = c >> 1;
+    x = t;
+  }
+  const float u = x * (float)(1u << f);  // scene/deformable_field.py:66-67: positions * 2^f
+  return (c & 1) ? cosf(u) : sinf(u);    // :69: [sin, cos] interleaved
+}
+
+// Hidden unit `tid` needs row `tid` of W_l ([out][in]).  A chunk is 32 input columns of all rows; in shared memory row j
+// keeps its eight 16-byte granules at positions g ^ (j & 7), so that the 128-bit reads of 8 consecutive threads (one
+// granule index, 8 consecutive rows) fall on 8 different bank groups.
+static __global__ void __launch_bounds__(MLP_THREADS)
+gp_kpmlp_fwd_kernel(MlpDims d, MlpPtrs p, const float* __restrict__ xyz, const float* __restrict__ feat,
+                    const float* __restrict__ t_ptr, float* __restrict__ x0, float* __restrict__ acts,
+                    float* __restrict__ out) {
+  float(*xs)[MLP_ROWS][MLP_MAXW] = reinterpret_cast<float(*)[MLP_ROWS][MLP_MAXW]>(mlp_smem);
+  float* stages = mlp_smem + 2 * MLP_ROWS * MLP_MAXW;
+  const int tid = threadIdx.x;
+  const int r0 = blockIdx.x * MLP_ROWS;
+  const int n0 = (d.din + MLP_CH - 1) / MLP_CH, nw = (d.w + MLP_CH - 1) / MLP_CH;
+  const int total = n0 + (d.depth - 1) * nw;
+  auto issue = [&](int c) {
+    if (c < total) {
+      const int l = c < n0 ? 0 : 1 + (c - n0) / nw;
+      const int k0 = MLP_CH * (c < n0 ? c : (c - n0) % nw);
+      const int K = l == 0 ? d.din : d.w;
+      const float* __restrict__ W = p.W[l];
+      float* st = stages + (c % MLP_STAGES) * MLP_STAGE_FLOATS;
+#pragma unroll
+      for (int i = 0; i < MLP_CH * MLP_MAXW / 4 / MLP_THREADS; i++) {
+        const int idx = tid + i * MLP_THREADS, j = idx >> 3, g = idx & 7;
+        if (j < d.w && k0 + 4 * g < K) mlp_cp16(st + (j * 8 + (g ^ (j & 7))) * 4, W + (size_t)j * K + k0 + 4 * g);
+      }
+    }
+    mlp_cp_commit();
+  };
+  for (int c = 0; c < MLP_STAGES - 1; c++) issue(c);
+  const float t = (d.tf > 0 && t_ptr) ? __ldg(t_ptr) : 0.f;
+  for (int i = tid; i < MLP_ROWS * d.din; i += MLP_THREADS) {
+    const int r = i / d.din, c = i - r * d.din, row = r0 + r;
+    float v = 0.f;
+    if (row < d.rows) {
+      v = mlp_input(d, xyz, feat, t, row, c);
+      x0[(size_t)row * d.din + c] = v;
+    }
+    xs[0][r][c] = v;
+  }
+  int cur = 0;
+  float acc[MLP_ROWS];
+  for (int c = 0; c < total; c++) {
+    mlp_cp_wait<MLP_STAGES - 2>();
+    __syncthreads();  // chunk c is visible to all; every thread is done with chunk c-1, whose stage is refilled next
+    issue(c + MLP_STAGES - 1);
+    const int l = c < n0 ? 0 : 1 + (c - n0) / nw;
+    const int k0 = MLP_CH * (c < n0 ? c : (c - n0) % nw);
+    const int K = l == 0 ? d.din : d.w;
+    if (tid < d.w) {
+      if (k0 == 0) {
+        const float b = __ldg(p.b[l] + tid);
+#pragma unroll
+        for (int r = 0; r < MLP_ROWS; r++) acc[r] = b;
+      }
+      const float* st = stages + (c % MLP_STAGES) * MLP_STAGE_FLOATS + tid * 32;
+      const int ng = min(8, (K - k0) >> 2);
+#pragma unroll 4
+      for (int g = 0; g < ng; g++) {
+        const float4 wv = *reinterpret_cast<const float4*>(st + ((g ^ (tid & 7)) << 2));
+#pragma unroll
+        for (int r = 0; r < MLP_ROWS; r++) {
+          const float4 xv = *reinterpret_cast<const float4*>(&xs[cur][r][k0 + 4 * g]);
+          acc[r] = fmaf(xv.x, wv.x, acc[r]);
+          acc[r] = fmaf(xv.y, wv.y, acc[r]);
+          acc[r] = fmaf(xv.z, wv.z, acc[r]);
+          acc[r] = fmaf(xv.w, wv.w, acc[r]);
+        }
+      }
+      if (k0 + MLP_CH >= K) {  // layer complete: ReLU, keep for the backward, hand to the next layer
+#pragma unroll
+        for (int r = 0; r < MLP_ROWS; r++) {
+          const float h = fmaxf(acc[r], 0.f);
+          xs[cur ^ 1][r][tid] = h;
+          if (r0 + r < d.rows) acts[((size_t)l * d.rows + r0 + r) * d.w + tid] = h;
+        }
+      }
+    }
+    if (k0 + MLP_CH >= K) cur ^= 1;
+  }
+  mlp_cp_wait<0>();
+  __syncthreads();
+  // output layer: (row, output, k-slice) = (4, 8, 8) threads, slices summed by shuffles
+  {
+    const int r = tid >> 6, j = (tid >> 3) & 7, s = tid & 7;
+    const float* __restrict__ Wl = p.W[d.depth];
+    float part = 0.f;
+    if (j < d.out)
+      for (int k = s; k < d.w; k += 8) part = fmaf(xs[cur][r][k], __ldg(Wl + (size_t)j * d.w + k), part);
+    part += __shfl_xor_sync(0xffffffffu, part, 1);
+    part += __shfl_xor_sync(0xffffffffu, part, 2);
+    part += __shfl_xor_sync(0xffffffffu, part, 4);
+    if (s == 0 && j < d.out && r0 + r < d.rows) out[(size_t)(r0 + r) * d.out + j] = part + __ldg(p.b[d.depth] + j);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ backward: data
+
+// Input unit `tid` of layer l needs column `tid` of W_l: a chunk is 32 whole rows of W_l (contiguous in memory), read
+// from shared memory with consecutive threads on consecutive words.
+static __global__ void __launch_bounds__(MLP_THREADS)
+gp_kpmlp_bwd_data_kernel(MlpDims d, MlpPtrs p, const float* __restrict__ xyz, const float* __restrict__ t_ptr,
+                         const float* __restrict__ acts, const float* __restrict__ dout, float* __restrict__ dz,
+                         float* __restrict__ g_xyz, float* __restrict__ g_feat) {
+  float(*gs)[MLP_ROWS][MLP_MAXW] = reinterpret_cast<float(*)[MLP_ROWS][MLP_MAXW]>(mlp_smem);
+  float* stages = mlp_smem + 2 * MLP_ROWS * MLP_MAXW;
+  __shared__ float go[MLP_ROWS][8];
+  const int tid = threadIdx.x;
+  const int r0 = blockIdx.x * MLP_ROWS;
+  const int nw = (d.w + MLP_CH - 1) / MLP_CH;
+  const int total = d.depth * nw;
+  auto issue = [&](int c) {
+    if (c < total) {
+      const int l = d.depth - 1 - c / nw, j0 = MLP_CH * (c % nw);
+      const int K = l == 0 ? d.din : d.w;
+      const int granules = (min(MLP_CH, d.w - j0) * K) >> 2;
+      const float* __restrict__ src = p.W[l] + (size_t)j0 * K;
+      float* st = stages + (c % MLP_STAGES) * MLP_STAGE_FLOATS;
+      for (int idx = tid; idx < granules; idx += MLP_THREADS) mlp_cp16(st + idx * 4, src + idx * 4);
+    }
+    mlp_cp_commit();
+  };
+  for (int c = 0; c < MLP_STAGES - 1; c++) issue(c);
+  if (tid < MLP_ROWS * 8) {
+    const int r = tid >> 3, j = tid & 7;
+    go[r][j] = (j < d.out && r0 + r < d.rows) ? __ldg(dout + (size_t)(r0 + r) * d.out + j) : 0.f;
+  }
+  __syncthreads();
+  if (tid < d.w) {  // through the output Linear, then the ReLU of the last hidden layer
+    float a0[MLP_ROWS];
+#pragma unroll
+    for (int r = 0; r < MLP_ROWS; r++) a0[r] = 0.f;
+    for (int j = 0; j < d.out; j++) {
+      const float wv = __ldg(p.W[d.depth] + (size_t)j * d.w + tid);
+#pragma unroll
+      for (int r = 0; r < MLP_ROWS; r++) a0[r] = fmaf(go[r][j], wv, a0[r]);
+    }
+#pragma unroll
+    for (int r = 0; r < MLP_ROWS; r++) {
+      const int row = r0 + r;
+      const size_t a = ((size_t)(d.depth - 1) * d.rows + row) * d.w + tid;
+      const float v = (row < d.rows && __ldg(acts + a) > 0.f) ? a0[r] : 0.f;
+      gs[0][r][tid] = v;
+      if (row < d.rows) dz[a] = v;
+    }
+  }
+  int cur = 0;
+  float acc[MLP_ROWS];
+  for (int c = 0; c < total; c++) {
+    mlp_cp_wait<MLP_STAGES - 2>();
+    __syncthreads();
+    issue(c + MLP_STAGES - 1);
+    // gradient wrt the input of layer l: sum_j gs[r][j] W_l[j][k]; for l > 0 masked by the ReLU of layer l-1
+    const int l = d.depth - 1 - c / nw, j0 = MLP_CH * (c % nw);
+    const int K = l == 0 ? d.din : d.w;
+    const int jn = min(MLP_CH, d.w - j0);
+    if (tid < K) {
+      if (j0 == 0) {
+#pragma unroll
+        for (int r = 0; r < MLP_ROWS; r++) acc[r] = 0.f;
+      }
+      const float* st = stages + (c % MLP_STAGES) * MLP_STAGE_FLOATS + tid;
+#pragma unroll 2
+      for (int jj = 0; jj < jn; jj += 4) {
+        const float w0 = st[(jj + 0) * K], w1 = st[(jj + 1) * K], w2 = st[(jj + 2) * K], w3 = st[(jj + 3) * K];
+#pragma unroll
+        for (int r = 0; r < MLP_ROWS; r++) {
+          const float4 gv = *reinterpret_cast<const float4*>(&gs[cur][r][j0 + jj]);
+          acc[r] = fmaf(gv.x, w0, acc[r]);
+          acc[r] = fmaf(gv.y, w1, acc[r]);
+          acc[r] = fmaf(gv.z, w2, acc[r]);
+          acc[r] = fmaf(gv.w, w3, acc[r]);
+        }
+      }
+      if (j0 + MLP_CH >= d.w) {
+#pragma unroll
+        for (int r = 0; r < MLP_ROWS; r++) {
+          if (l > 0) {
+            const int row = r0 + r;
+            const size_t a = ((size_t)(l - 1) * d.rows + row) * d.w + tid;
+            const float v = (row < d.rows && __ldg(acts + a) > 0.f) ? acc[r] : 0.f;
+            gs[cur ^ 1][r][tid] = v;
+            if (row < d.rows) dz[a] = v;
+          } else {
+            gs[cur ^ 1][r][tid] = acc[r];
+          }
+        }
+      }
+    }
+    if (j0 + MLP_CH >= d.w) cur ^= 1;
+  }
+  mlp_cp_wait<0>();
+  __syncthreads();
+  // gs[cur] now holds dL/d(input row).  Features pass through; xyz goes back through the encoding.
+  if (g_feat) {
+    for (int i = tid; i < MLP_ROWS * d.F; i += MLP_THREADS) {
+      const int r = i / d.F, c = i - r * d.F;
+      if (r0 + r < d.rows) g_feat[(size_t)(r0 + r) * d.F + c] = gs[cur][r][c];
+    }
+  }
+  if (g_xyz && tid < MLP_ROWS * 3) {
+    const int r = tid / 3, dim = tid - r * 3, row = r0 + r;
+    if (row < d.rows) {
+      const float x = __ldg(xyz + (size_t)row * 3 + dim);
+      float a = 0.f;
+      for (int f = 0; f < d.xf; f++) {
+        const float sc = (float)(1u << f), u = x * sc;
+        const int c = d.F + (dim * d.xf + f) * 2;
+        a += sc * (gs[cur][r][c] * cosf(u) - gs[cur][r][c + 1] * sinf(u));
+      }
+      g_xyz[(size_t)row * 3 + dim] = a;
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ backward: weights
+
+#define MLP_TJ 32
+#define MLP_TK 64
+#define MLP_RC 32
+#define MLP_WSTAGES 3
+
+static __global__ void __launch_bounds__(MLP_THREADS)
+gp_kpmlp_bwd_weights_kernel(MlpDims d, MlpPtrs p, MlpTiles tl, const float* __restrict__ x0,
+                            const float* __restrict__ acts, const float* __restrict__ dz,
+                            const float* __restrict__ dout) {
+  __shared__ __align__(16) float a_s[MLP_WSTAGES][MLP_RC][MLP_TJ];
+  __shared__ __align__(16) float b_s[MLP_WSTAGES][MLP_RC][MLP_TK];
+  int l = 0;
+  while (l < d.depth && (int)blockIdx.x >= tl.first[l + 1]) l++;
+  const int J = l < d.depth ? d.w : d.out, K = l == 0 ? d.din : d.w;
+  const float* __restrict__ A = l < d.depth ? dz + (size_t)l * d.rows * d.w : dout;  // [rows][J]
+  const float* __restrict__ B = l == 0 ? x0 : acts + (size_t)(l - 1) * d.rows * d.w;    // [rows][K]
+  const int tiles_k = (K + MLP_TK - 1) / MLP_TK;
+  const int local = blockIdx.x - tl.first[l];
+  const int tk = local % tiles_k;
+  const int j0 = (local / tiles_k) * MLP_TJ, k0 = tk * MLP_TK;
+  const int tid = threadIdx.x, ty = tid >> 4, tx = tid & 15;
+  const bool a_vec = (J & 3) == 0;
+  const int nchunks = (d.rows + MLP_RC - 1) / MLP_RC;
+  auto issue = [&](int c) {
+    if (c < nchunks) {
+      const int s = c % MLP_WSTAGES, rc = c * MLP_RC;
+      {
+        const int rr = tid >> 3, c4 = (tid & 7) * 4, row = rc + rr, j = j0 + c4;
+        const float* src = A + (size_t)min(row, d.rows - 1) * J;
+        if (a_vec) {
+          const bool ok = row < d.rows && j < J;
+          mlp_cp16(&a_s[s][rr][c4], ok ? src + j : A, ok);
+        } else {
+#pragma unroll
+          for (int i = 0; i < 4; i++) {
+            const bool ok = row < d.rows && j + i < J;
+            mlp_cp4(&a_s[s][rr][c4 + i], ok ? src + j + i : A, ok);
+          }
+        }
+      }
+#pragma unroll
+      for (int q = 0; q < 2; q++) {
+        const int e = tid + q * MLP_THREADS;
+        const int rr = e >> 4, c4 = (e & 15) * 4, row = rc + rr, k = k0 + c4;
+        const bool ok = row < d.rows && k < K;
+        mlp_cp16(&b_s[s][rr][c4], ok ? B + (size_t)row * K + k : B, ok);
+      }
+    }
+    mlp_cp_commit();
+  };
+  for (int c = 0; c < MLP_WSTAGES - 1; c++) issue(c);
+  float acc[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
+  float bacc[2] = {0.f, 0.f};
+  for (int c = 0; c < nchunks; c++) {
+    mlp_cp_wait<MLP_WSTAGES - 2>();
+    __syncthreads();
+    issue(c + MLP_WSTAGES - 1);
+    const int s = c % MLP_WSTAGES;
+#pragma unroll 8
+    for (int rr = 0; rr < MLP_RC; rr++) {
+      const float2 a = *reinterpret_cast<const float2*>(&a_s[s][rr][2 * ty]);
+      const float4 b = *reinterpret_cast<const float4*>(&b_s[s][rr][4 * tx]);
+      acc[0][0] = fmaf(a.x, b.x, acc[0][0]); acc[0][1] = fmaf(a.x, b.y, acc[0][1]);
+      acc[0][2] = fmaf(a.x, b.z, acc[0][2]); acc[0][3] = fmaf(a.x, b.w, acc[0][3]);
+      acc[1][0] = fmaf(a.y, b.x, acc[1][0]); acc[1][1] = fmaf(a.y, b.y, acc[1][1]);
+      acc[1][2] = fmaf(a.y, b.z, acc[1][2]); acc[1][3] = fmaf(a.y, b.w, acc[1][3]);
+      if (tk == 0) { bacc[0] += a.x; bacc[1] += a.y; }
+    }
+  }
+  mlp_cp_wait<0>();
+#pragma unroll
+  for (int jj = 0; jj < 2; jj++) {
+    const int j = j0 + 2 * ty + jj, k = k0 + 4 * tx;
+    if (j < J) {
+      if (k < K) *reinterpret_cast<float4*>(p.gW[l] + (size_t)j * K + k) = make_float4(acc[jj][0], acc[jj][1], acc[jj][2], acc[jj][3]);
+      if (tk == 0 && tx == 0) p.gb[l][j] = bacc[jj];
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ entry points
+
+extern "C" int gp_kpmlp_sizes(const gp_mlp_cfg* cfg, size_t* saved_bytes, size_t* bwd_scratch_bytes) {
+  MlpDims d;
+  int rc = mlp_dims(cfg, &d);
+  if (rc) return rc;
+  const size_t rows = (size_t)(d.rows > 0 ? d.rows : 1);
+  if (saved_bytes) *saved_bytes = gp_align_up(rows * ((size_t)d.din + (size_t)d.depth * d.w) * sizeof(float), 256);
+  if (bwd_scratch_bytes) *bwd_scratch_bytes = gp_align_up(rows * (size_t)d.depth * d.w * sizeof(float), 256);
+  return GP_OK;
+}
+
+extern "C" int gp_kpmlp_forward(const gp_mlp_cfg* cfg, const float* kp_xyz, const float* kp_feat, const float* t,
+                                const float* const* weights, const float* const* biases, void* saved, float* out,
+                                gp_stream_t stream_) {
+  MlpDims d;
+  int rc = mlp_dims(cfg, &d);
+  if (rc) return rc;
+  if (!weights || !biases || !saved || !out) return GP_ERR_BAD_ARG;
+  if ((d.xf > 0 && !kp_xyz) || (d.F > 0 && !kp_feat) || (d.tf > 0 && !t)) return GP_ERR_BAD_ARG;
+  if (d.rows == 0) return GP_OK;
+  cudaStream_t stream = (cudaStream_t)stream_;
+  MlpPtrs p = {};
+  for (int l = 0; l <= d.depth; l++) {
+    if (!weights[l] || !biases[l]) return GP_ERR_BAD_ARG;
+    p.W[l] = weights[l];
+    p.b[l] = biases[l];
+  }
+  float* x0 = (float*)saved;
+  float* acts = x0 + (size_t)d.rows * d.din;
+  GP_CUDA_TRY(cudaFuncSetAttribute(gp_kpmlp_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MLP_SMEM_BYTES));
+  const int blocks = (d.rows + MLP_ROWS - 1) / MLP_ROWS;
+  GP_KERNEL("gp_kpmlp_fwd_kernel", stream,
+            gp_kpmlp_fwd_kernel<<<blocks, MLP_THREADS, MLP_SMEM_BYTES, stream>>>(d, p, kp_xyz, kp_feat, t, x0, acts, out));
+  GP_LAUNCH_CHECK();
+  return GP_OK;
+}
+
+extern "C" int gp_kpmlp_backward(const gp_mlp_cfg* cfg, const float* kp_xyz, const float* t,
+                                 const float* const* weights, const void* saved, const float* dL_dout,
+                                 void* bwd_scratch, float* dL_dxyz, float* dL_dfeat, float* const* dL_dweights,
+                                 float* const* dL_dbiases, gp_stream_t stream_) {
+  MlpDims d;
+  int rc = mlp_dims(cfg, &d);
+  if (rc) return rc;
+  if (!weights || !saved || !dL_dout || !bwd_scratch || !dL_dweights || !dL_dbiases) return GP_ERR_BAD_ARG;
+  if (d.xf > 0 && dL_dxyz && !kp_xyz) return GP_ERR_BAD_ARG;
+  if (d.rows == 0) return GP_OK;
+  cudaStream_t stream = (cudaStream_t)stream_;
+  MlpPtrs p = {};
+  for (int l = 0; l <= d.depth; l++) {
+    if (!weights[l] || !dL_dweights[l] || !dL_dbiases[l]) return GP_ERR_BAD_ARG;
+    p.W[l] = weights[l];
+    p.gW[l] = dL_dweights[l];
+    p.gb[l] = dL_dbiases[l];
+  }
+  const float* x0 = (const float*)saved;
+  const float* acts = x0 + (size_t)d.rows * d.din;
+  float* dz = (float*)bwd_scratch;
+  const int blocks = (d.rows + MLP_ROWS - 1) / MLP_ROWS;
+  GP_CUDA_TRY(cudaFuncSetAttribute(gp_kpmlp_bwd_data_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MLP_SMEM_BYTES));
+  GP_KERNEL("gp_kpmlp_bwd_data_kernel", stream,
+            gp_kpmlp_bwd_data_kernel<<<blocks, MLP_THREADS, MLP_SMEM_BYTES, stream>>>(d, p, kp_xyz, t, acts, dL_dout, dz, dL_dxyz,
+                                                                        dL_dfeat));
+  GP_LAUNCH_CHECK();
+  MlpTiles tl = {};
+  for (int l = 0; l <= d.depth; l++) {
+    const int J = l < d.depth ? d.w : d.out, K = l == 0 ? d.din : d.w;
+    tl.first[l + 1] = tl.first[l] + ((J + MLP_TJ - 1) / MLP_TJ) * ((K + MLP_TK - 1) / MLP_TK);
+  }
+  GP_KERNEL("gp_kpmlp_bwd_weights_kernel", stream,
+            gp_kpmlp_bwd_weights_kernel<<<tl.first[d.depth + 1], MLP_THREADS, 0, stream>>>(d, p, tl, x0, acts, dz,
+                                                                                          dL_dout));
+  GP_LAUNCH_CHECK();
+  return GP_OK;
+}

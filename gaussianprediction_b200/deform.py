@@ -4,7 +4,8 @@ Mirrors scene/gaussian_model.py:231-304 (control flow), :110-125 (``get_nearest_
 (``fill_nearest``), :180-189 (``get_motion_delta``), :314-315 (``get_rotation_``) and
 scene/deformable_field.py:63-127 (``positional_encoding``, ``Deformable_Field``).  The K-nearest-keypoint
 search and the blend (softmax, gather, weighted sums, quaternion compose, activations) run in
-libgp_b200.so; the small keypoint MLP stays a torch/cuBLAS call as BASELINE.json's north_star says.
+libgp_b200.so, and so does the small keypoint MLP: north_star leaves it a cuBLAS/torch call "unless ncu shows it
+matters", and as ~70 tiny launches it was 0.26 ms of a 1.18 ms iteration (profiles/r1_keypoint_mlp.md).
 
 The hash-grid blend-weight network (tinycudann, scene/gaussian_model.py:370-392) is not available
 (un-vendored third-party code, SURVEY.md §8c): ``weights_model`` is any callable [N,3] -> [N,2K];
@@ -59,6 +60,14 @@ class DeformableField(nn.Module):
 
     def forward(self, x):
         return self.feature_to_deformation(self.mlp(x))
+
+    def linears(self):
+        """The Linear layers in order, or None if the module is not the plain Linear/ReLU stack."""
+        mods = list(self.mlp) + list(self.feature_to_deformation)
+        lin = [m for m in mods if isinstance(m, nn.Linear)]
+        if any(not isinstance(m, (nn.Linear, nn.ReLU)) for m in mods) or len(self.feature_to_deformation) != 1:
+            return None
+        return lin
 
 
 def quat_mul(q1, q2):
@@ -171,6 +180,73 @@ def keypoint_blend(logits, idx32, kp_delta_xyz, kp_delta_q, xyz, rot, scaling, o
     return _KeypointBlend.apply(logits, idx32, kp_delta_xyz, kp_delta_q, xyz, rot, scaling, opacity)
 
 
+class _KeypointMLP(torch.autograd.Function):
+    """delta = df_model(cat([feature, PE(xyz), PE(t)])) for the keypoints, forward and backward in libgp_b200.so."""
+
+    @staticmethod
+    def forward(ctx, dims, kp_xyz, kp_feat, t, *params):
+        L = _lib.lib()
+        xyz_freq, time_freq, depth, width, out_dim = dims
+        n = depth + 1
+        weights, biases = [_c(w) for w in params[:n]], [_c(b) for b in params[n:]]
+        xyz_c, feat_c = _c(kp_xyz), _c(kp_feat)
+        t_c = _c(t).reshape(-1)[:1]
+        cfg = _lib.MlpCfg(int(xyz_c.shape[0]), int(feat_c.shape[1]), xyz_freq, time_freq, depth, width, out_dim)
+        sv, bs = ctypes.c_size_t(), ctypes.c_size_t()
+        check(L.gp_kpmlp_sizes(ctypes.byref(cfg), ctypes.byref(sv), ctypes.byref(bs)), "gp_kpmlp_sizes")
+        dev = xyz_c.device
+        saved = torch.empty(sv.value, dtype=torch.uint8, device=dev)
+        out = torch.empty((cfg.rows, out_dim), dtype=torch.float32, device=dev)
+        wp = (ctypes.c_void_p * n)(*[w.data_ptr() for w in weights])
+        bp = (ctypes.c_void_p * n)(*[b.data_ptr() for b in biases])
+        check(L.gp_kpmlp_forward(ctypes.byref(cfg), ptr(xyz_c), ptr(feat_c), ptr(t_c), wp, bp, ptr(saved), ptr(out),
+                                 _lib.stream_ptr()), "gp_kpmlp_forward")
+        ctx.save_for_backward(xyz_c, t_c, saved, *weights)
+        ctx.cfg, ctx.bwd_bytes = cfg, bs.value
+        return out
+
+    @staticmethod
+    def backward(ctx, g_out):
+        L = _lib.lib()
+        xyz_c, t_c, saved, *weights = ctx.saved_tensors
+        cfg = ctx.cfg
+        n = cfg.depth + 1
+        dev = xyz_c.device
+        need = ctx.needs_input_grad
+        g_xyz = torch.empty_like(xyz_c) if need[1] else None
+        g_feat = torch.empty((cfg.rows, cfg.feature_dim), dtype=torch.float32, device=dev) if need[2] else None
+        gw = [torch.empty_like(w) for w in weights]
+        gb = [torch.empty(w.shape[0], dtype=torch.float32, device=dev) for w in weights]
+        scratch = torch.empty(ctx.bwd_bytes, dtype=torch.uint8, device=dev)
+        wp = (ctypes.c_void_p * n)(*[w.data_ptr() for w in weights])
+        gwp = (ctypes.c_void_p * n)(*[g.data_ptr() for g in gw])
+        gbp = (ctypes.c_void_p * n)(*[g.data_ptr() for g in gb])
+        check(L.gp_kpmlp_backward(ctypes.byref(cfg), ptr(xyz_c), ptr(t_c), wp, ptr(saved), ptr(_c(g_out)), ptr(scratch),
+                                  ptr(g_xyz), ptr(g_feat), gwp, gbp, _lib.stream_ptr()), "gp_kpmlp_backward")
+        return (None, g_xyz, g_feat, None) + tuple(gw) + tuple(gb)
+
+
+def keypoint_mlp_supported(df_model, feature_dim, xyz_freq, time_freq):
+    """Shapes the fused kernels take (include/gp_b200.h, gp_kpmlp_*); anything else goes through the torch modules."""
+    lin = df_model.linears() if hasattr(df_model, "linears") else None
+    if lin is None:
+        return False
+    din = feature_dim + 6 * xyz_freq + 2 * time_freq
+    w = lin[0].out_features
+    ok = din % 4 == 0 and 4 <= din <= 256 and w % 4 == 0 and 4 <= w <= 256 and 2 <= len(lin) <= 9
+    ok = ok and lin[0].in_features == din and lin[-1].out_features <= 8 and lin[-1].in_features == w
+    ok = ok and all(l.in_features == w and l.out_features == w for l in lin[1:-1])
+    return ok and all(l.bias is not None and l.weight.is_cuda and l.weight.dtype == torch.float32 for l in lin)
+
+
+def keypoint_mlp(df_model, kp_xyz, kp_feat, t, xyz_freq, time_freq):
+    """``df_model(cat([kp_feat, PE(kp_xyz), PE(t).repeat]))`` (scene/gaussian_model.py:180-189 at the keypoint call
+    site) through the fused kernels.  ``t``: tensor with one element."""
+    lin = df_model.linears()
+    dims = (int(xyz_freq), int(time_freq), len(lin) - 1, lin[0].out_features, lin[-1].out_features)
+    return _KeypointMLP.apply(dims, kp_xyz, kp_feat, t, *[l.weight for l in lin], *[l.bias for l in lin])
+
+
 @torch.no_grad()
 def dense_weights(logits, idx32, Kp, want_sum=False):
     """Dense ``weights_xyz, weights_r`` [N,Kp] as ``fill_nearest`` builds them (scene/gaussian_model.py:214-229)."""
@@ -238,6 +314,7 @@ class KeypointDeformation(nn.Module):
         self.lifecycle_opacity = None
         self._idx32 = None
         self._last_logits = None
+        self.fused_mlp = True   # keypoint MLP through gp_kpmlp_* (False: the torch modules, e.g. to compare)
         self.knn_cache = False  # eval: the search inputs are parameters only, so it can be hoisted out of the frame loop
         # Morton order of the Gaussians, a speed hint for the search (results do not depend on it).  Built on first use
         # and whenever N changes; call refresh_knn_order() after the cloud has moved a lot (e.g. after densification).
@@ -287,7 +364,7 @@ class KeypointDeformation(nn.Module):
     def forward(self, t, iteration, return_weights=False):
         args = self.args
         t_input = t
-        t = positional_encoding(t, self.time_input_dim // 2).unsqueeze(0)
+        t_embed = lambda: positional_encoding(t_input, self.time_input_dim // 2).unsqueeze(0)  # (:233), where it is used
         if torch.is_tensor(iteration):
             iteration = iteration.item()
         if iteration < args.jointly_iteration:  # warm-up: canonical parameters (:237-238)
@@ -297,7 +374,7 @@ class KeypointDeformation(nn.Module):
             # first stage (:240-244): per-Gaussian MLP, torch ops (not the keypoint hot path)
             noise = torch.randn_like(self._xyz) * 0.1 * (1 - min(1, iteration / args.xyz_noise_iteration))
             xyz_embed = positional_encoding(self._xyz.detach() + noise, int(self.xyz_input_dim / 6))
-            delta_xyz, delta_q, _ = self.get_motion_delta(xyz_embed, self.motion_feature, t)
+            delta_xyz, delta_q, _ = self.get_motion_delta(xyz_embed, self.motion_feature, t_embed())
             if args.norm_rotation:
                 delta_q = normalize(delta_q)
             self.kpts_xyz_motion, self.kpts_rotation_motion = delta_xyz.detach(), delta_q.detach()
@@ -308,12 +385,19 @@ class KeypointDeformation(nn.Module):
             # second stage (:251-273, :285-287): keypoints
             factor = 0.1 * (1 - min(1, (iteration - self.second_stage_iter) / args.xyz_noise_iteration))
             noise = torch.randn_like(self.super_gaussians) * factor  # RNG consumed even when the factor is 0 (:254)
-            xyz_embed = positional_encoding(self.super_gaussians + noise, int(self.xyz_input_dim / 6))
             logits = self.weights_model(self._xyz.detach())
             if not (self.knn_cache and self._idx32 is not None):
                 self.get_nearest_mask(keepshape=True)
             self._last_logits = logits.detach()
-            delta_xyz, delta_q, _ = self.get_motion_delta(xyz_embed, self.super_gaussians_feature, t)
+            xf, tf = int(self.xyz_input_dim / 6), self.time_input_dim // 2
+            if self.fused_mlp and self.super_gaussians.is_cuda and \
+                    keypoint_mlp_supported(self.df_model, args.feature_dim, xf, tf):
+                delta = keypoint_mlp(self.df_model, self.super_gaussians + noise, self.super_gaussians_feature, t_input,
+                                     xf, tf)
+                delta_xyz, delta_q = delta[..., 0:3], delta[..., 3:7]
+            else:
+                xyz_embed = positional_encoding(self.super_gaussians + noise, xf)
+                delta_xyz, delta_q, _ = self.get_motion_delta(xyz_embed, self.super_gaussians_feature, t_embed())
             if args.norm_rotation:
                 delta_q = normalize(delta_q)
             # detached: the readers (motion_model/dataset.py:120-123) only take values, and a live reference would keep
@@ -325,7 +409,7 @@ class KeypointDeformation(nn.Module):
         base_opacity = opacity
         if args.step_opacity and iteration > args.step_opacity_iteration:  # (:291-301) per-Gaussian MLP, torch ops
             xyz_embed = positional_encoding(self._xyz, int(self.xyz_input_dim / 6))
-            _, _, delta_o = self.get_motion_delta(xyz_embed, self.motion_feature, t)
+            _, _, delta_o = self.get_motion_delta(xyz_embed, self.motion_feature, t_embed())
             if args.opacity_type == "explicit":
                 opacity = base_opacity * (1 / (1 + torch.exp(-(t_input - self.opacity_thres) / self.beta)))
             else:

@@ -220,6 +220,37 @@ int gp_image_loss_forward(int C, int H, int W, const float* img, const float* gt
 int gp_image_loss_backward(int C, int H, int W, const float* img, const float* gt, const float* dmaps, float w_l1,
                            float w_ssim, const float* grad_scale, float* grad_img, gp_stream_t stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * Keypoint-motion MLP, fused.  Stands in for the torch ops of scene/gaussian_model.py:180-189 (get_motion_delta:
+ * repeat t, cat([feature, xyz_embed, t]), df_model) with scene/deformable_field.py:63-72 (positional_encoding of the
+ * keypoint positions and of t) and :74-127 (Deformable_Field: depth x (Linear+ReLU), then Linear), and for their
+ * autograd backward, at the keypoint call site (:255-265).  Input row = [feature(F) | PE(xyz)(6*xyz_freq) |
+ * PE(t)(2*time_freq)].  weights[l] / biases[l], l = 0..depth: device pointers in nn.Linear layout ([out][in] row-major);
+ * the arrays of pointers themselves live on the host.  Limits (GP_ERR_LIMIT otherwise): width and input row length
+ * multiples of 4 and <= 256, depth <= 8, out_dim <= 8.
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct gp_mlp_cfg {
+  int rows;        /* number of keypoints */
+  int feature_dim; /* F */
+  int xyz_freq;    /* frequencies of the position encoding (0: no such columns) */
+  int time_freq;   /* frequencies of the time encoding (0: no such columns) */
+  int depth;       /* hidden Linear+ReLU layers */
+  int width;       /* hidden width */
+  int out_dim;     /* columns of the last Linear (7; 8 with step opacity) */
+} gp_mlp_cfg;
+
+/* saved: activations the backward needs (forward writes, backward reads); bwd_scratch holds no state between calls */
+int gp_kpmlp_sizes(const gp_mlp_cfg* cfg, size_t* saved_bytes, size_t* bwd_scratch_bytes);
+/* out[rows, out_dim] = MLP(input rows).  t: device scalar. */
+int gp_kpmlp_forward(const gp_mlp_cfg* cfg, const float* kp_xyz /*[rows,3]*/, const float* kp_feat /*[rows,F]*/,
+                     const float* t, const float* const* weights, const float* const* biases, void* saved, float* out,
+                     gp_stream_t stream);
+/* Every requested gradient is fully written (no accumulation).  dL_dxyz / dL_dfeat may be NULL. */
+int gp_kpmlp_backward(const gp_mlp_cfg* cfg, const float* kp_xyz, const float* t, const float* const* weights,
+                      const void* saved, const float* dL_dout /*[rows,out_dim]*/, void* bwd_scratch,
+                      float* dL_dxyz /*[rows,3]*/, float* dL_dfeat /*[rows,F]*/, float* const* dL_dweights,
+                      float* const* dL_dbiases, gp_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -236,3 +236,110 @@ def test_graph_step_matches_eager(gplib):
     small = TrainStep(pc, cams[0], capacity=1000, bg=bg)
     small(cams[0], times[0], targets[0])
     assert small.overflowed()[1]
+
+
+def _torch_motion_delta(net, kp, kf, t, xf, tf):
+    """get_motion_delta at the keypoint call site with the torch modules (scene/gaussian_model.py:180-189)."""
+    from gaussianprediction_b200.deform import positional_encoding
+    cols = [kf]
+    if xf:
+        cols.append(positional_encoding(kp, xf))
+    if tf:
+        cols.append(positional_encoding(t, tf).unsqueeze(0).repeat((kp.shape[0], 1)))
+    return net(torch.cat(cols, dim=-1))
+
+
+@pytest.mark.parametrize("Kp,F,xf,tf,d,w,out", [(512, 32, 10, 6, 4, 256, 7), (515, 32, 10, 6, 4, 256, 8),
+                                                (1, 32, 10, 6, 4, 256, 7), (37, 8, 4, 2, 2, 64, 7),
+                                                (130, 16, 0, 0, 1, 32, 3), (64, 0, 10, 6, 8, 128, 7)])
+def test_keypoint_mlp_vs_torch_modules(gplib, Kp, F, xf, tf, d, w, out):
+    """gp_kpmlp_forward/backward against the torch fp32 modules they replace (PE + cat + Linear/ReLU stack + autograd).
+    Tolerances: values 1e-5 of the output scale, gradients 1e-4 relative (fp32 sums in a different order than cuBLAS)."""
+    from gaussianprediction_b200.deform import DeformableField, keypoint_mlp, keypoint_mlp_supported
+    dev = "cuda"
+    torch.manual_seed(Kp + w)
+    net = DeformableField(F + 6 * xf + 2 * tf, out, d, w).to(dev)
+    assert keypoint_mlp_supported(net, F, xf, tf)
+    g = torch.Generator().manual_seed(3)
+    kp = (torch.rand(Kp, 3, generator=g) * 2 - 1).to(dev).requires_grad_(True)
+    kf = torch.randn(Kp, F, generator=g).to(dev).requires_grad_(True)
+    t = torch.tensor([0.37], device=dev)
+    gout = torch.randn(Kp, out, generator=g).to(dev)
+    y_ref = _torch_motion_delta(net, kp, kf, t, xf, tf)
+    y_ref.backward(gout)
+    ref = {n: p.grad.clone() for n, p in net.named_parameters()}
+    ref["kp"], ref["kf"] = (kp.grad.clone() if xf else None), (kf.grad.clone() if F else None)
+    for p in list(net.parameters()) + [kp, kf]:
+        p.grad = None
+    y = keypoint_mlp(net, kp, kf, t, xf, tf)
+    assert y.shape == (Kp, out)
+    assert float((y - y_ref).abs().max()) <= 1e-5 * max(1.0, float(y_ref.abs().max()))
+    y.backward(gout)
+    for n, p in net.named_parameters():
+        assert rel_err(p.grad, ref[n]) <= 1e-4, n
+    if xf:
+        assert rel_err(kp.grad, ref["kp"]) <= 1e-4
+    else:
+        assert float(kp.grad.abs().max()) == 0
+    if F:
+        assert rel_err(kf.grad, ref["kf"]) <= 1e-4
+    # bit-reproducible: fixed summation order, no atomics
+    first = [p.grad.clone() for p in net.parameters()]
+    for p in list(net.parameters()) + [kp, kf]:
+        p.grad = None
+    y2 = keypoint_mlp(net, kp, kf, t, xf, tf)
+    y2.backward(gout)
+    assert count_diff(y, y2) == 0 and all(count_diff(a, p.grad) == 0 for a, p in zip(first, net.parameters()))
+
+
+def test_keypoint_mlp_golden_and_limits(gplib):
+    """The reference's own Deformable_Field output (tests/golden/deform_mlp_pe.npz, made by importing
+    scene/deformable_field.py) through the fused kernel: feature_dim = the whole 104-column input, no encodings."""
+    from gaussianprediction_b200.deform import DeformableField, keypoint_mlp, keypoint_mlp_supported
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "deform_mlp_pe.npz"))
+    net = DeformableField(104, 7, 4, 32)
+    net.load_state_dict({k[3:]: torch.from_numpy(z[k]) for k in z.files if k.startswith("sd_")})
+    net = net.cuda()
+    x = torch.from_numpy(z["x"]).cuda()
+    y = keypoint_mlp(net, torch.zeros(x.shape[0], 3, device="cuda"), x, torch.zeros(1, device="cuda"), 0, 0)
+    assert float((y.cpu() - torch.from_numpy(z["y"])).abs().max()) <= 1e-5
+    # the encoding columns: PE(pos) / PE(t) of the golden file pass through a 1-layer identity-like probe
+    pos, tt = torch.from_numpy(z["pos"]).cuda(), torch.from_numpy(z["t"]).cuda()
+    probe = DeformableField(60 + 12, 8, 1, 72).cuda()
+    with torch.no_grad():
+        probe.mlp[0].weight.copy_(torch.eye(72)); probe.mlp[0].bias.fill_(2.0)       # +2: keeps sin/cos above the ReLU
+        probe.feature_to_deformation[0].weight.zero_(); probe.feature_to_deformation[0].bias.zero_()
+        sel = [0, 1, 19, 20, 59, 60, 61, 71]
+        for j, c in enumerate(sel):
+            probe.feature_to_deformation[0].weight[j, c] = 1.0
+    yp = keypoint_mlp(probe, pos, torch.zeros(pos.shape[0], 0, device="cuda"), tt, 10, 6).cpu() - 2.0
+    want = torch.cat([torch.from_numpy(z["pe_xyz"]), torch.from_numpy(z["pe_t"]).reshape(1, -1).repeat(pos.shape[0], 1)], 1)[:, sel]
+    assert float((yp - want).abs().max()) <= 1e-6
+    # shapes outside the kernel's limits are refused by the C ABI and routed to the torch modules by the model
+    assert not keypoint_mlp_supported(DeformableField(104, 7, 4, 260).cuda(), 32, 10, 6)
+    assert not keypoint_mlp_supported(DeformableField(102, 7, 4, 64).cuda(), 30, 10, 6)
+
+
+def test_model_fused_mlp_equals_torch_mlp(gplib):
+    """KeypointDeformation with the fused keypoint MLP vs the same model on the torch modules."""
+    from gaussianprediction_b200.deform import KeypointDeformation, default_args
+    N, Kp = 5000, 200
+    gs, kp, kf, logits = scene(N, Kp, seed=41)
+    args = default_args(feature_amplify=0.5, norm_rotation=True)
+    torch.manual_seed(0)
+    model = KeypointDeformation(args, gs.xyz, gs.rotation, gs.scaling, gs.opacity, gs.motion_feature, kp, kf, logits=logits).cuda()
+    t = torch.tensor([0.61], device="cuda")
+    outs, grads = [], []
+    for fused in (True, False):
+        model.fused_mlp = fused
+        for p in model.parameters():
+            p.grad = None
+        o = model(t, 50_000)
+        sum((a * (i + 1)).sum() for i, a in enumerate(o)).backward()
+        outs.append([a.detach().clone() for a in o])
+        grads.append({n: p.grad.clone() for n, p in model.named_parameters() if p.grad is not None})
+    for a, b in zip(*outs):
+        assert float((a - b).abs().max()) <= 2e-5
+    assert grads[0].keys() == grads[1].keys()
+    for n in grads[0]:
+        assert rel_err(grads[0][n], grads[1][n]) <= 1e-3, n
