@@ -66,16 +66,24 @@ __device__ __forceinline__ void mlp_cp4(float* smem, const float* gmem, bool val
   const int n = valid ? 4 : 0;
   asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(s), "l"(gmem), "r"(n) : "memory");
 }
+__device__ __forceinline__ void mlp_cp16s(unsigned smem_addr, const float* gmem) {  // shared address already converted
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr), "l"(gmem) : "memory");
+}
 __device__ __forceinline__ void mlp_cp_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N>
 __device__ __forceinline__ void mlp_cp_wait() {
   asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
 
-#define MLP_CH 32     // weight columns (forward) / rows (backward) per chunk
-#define MLP_STAGES 4  // chunks resident in shared memory
+#define MLP_CH 64     // weight columns (forward) / rows (backward) per chunk
+#define MLP_STAGES 3  // chunks resident in shared memory
+#define MLP_SPLIT 2   // thread groups sharing one chunk: group h takes half of the chunk's summation range
+#define MLP_BIG (MLP_MAXW * MLP_SPLIT)  // 512 threads: thread = (group h, unit u)
 #define MLP_STAGE_FLOATS (MLP_CH * MLP_MAXW)
-#define MLP_SMEM_BYTES ((2 * MLP_ROWS * MLP_MAXW + MLP_STAGES * MLP_STAGE_FLOATS) * sizeof(float))
+#define MLP_STAGE_BYTES (MLP_STAGE_FLOATS * 4)
+// activations ping-pong | weight ring | output-layer weights | partial sums of the groups
+#define MLP_SMEM_FLOATS (2 * MLP_ROWS * MLP_MAXW + MLP_STAGES * MLP_STAGE_FLOATS + 8 * MLP_MAXW + MLP_SPLIT * MLP_ROWS * MLP_MAXW)
+#define MLP_SMEM_BYTES (MLP_SMEM_FLOATS * sizeof(float))
 
 extern __shared__ __align__(16) float mlp_smem[];
 
@@ -101,37 +109,56 @@ __device__ __forceinline__ float mlp_input(const MlpDims& d, const float* __rest
   return (c & 1) ? cosf(u) : sinf(u);    // :69: [sin, cos] interleaved
 }
 
-// Hidden unit `tid` needs row `tid` of W_l ([out][in]).  A chunk is 32 input columns of all rows; in shared memory row j
-// keeps its eight 16-byte granules at positions g ^ (j & 7), so that the 128-bit reads of 8 consecutive threads (one
-// granule index, 8 consecutive rows) fall on 8 different bank groups.
-static __global__ void __launch_bounds__(MLP_THREADS)
+// Hidden unit u needs row u of W_l ([out][in]).  A chunk is 64 input columns of all rows; in shared memory row j keeps
+// its sixteen 16-byte granules at positions g ^ (j & 7), so that the 128-bit reads of 8 consecutive threads (one
+// granule index, 8 consecutive rows) fall on 8 different bank groups.  One block = 4 keypoints x 256 units x 2 groups;
+// group h accumulates granules 8h..8h+7 of every chunk and the partial sums meet in shared memory at the end of a
+// layer.  (History, profiles/r1_keypoint_mlp.md: 256 threads and 32-column chunks sat at 2 warps per scheduler and 41%
+// issue utilisation; 1024 threads were issue-bound on per-chunk bookkeeping, 110 of 155 instructions per chunk.)
+static __global__ void __launch_bounds__(MLP_BIG)
 gp_kpmlp_fwd_kernel(MlpDims d, MlpPtrs p, const float* __restrict__ xyz, const float* __restrict__ feat,
                     const float* __restrict__ t_ptr, float* __restrict__ x0, float* __restrict__ acts,
                     float* __restrict__ out) {
   float(*xs)[MLP_ROWS][MLP_MAXW] = reinterpret_cast<float(*)[MLP_ROWS][MLP_MAXW]>(mlp_smem);
   float* stages = mlp_smem + 2 * MLP_ROWS * MLP_MAXW;
-  const int tid = threadIdx.x;
+  float* wlast = stages + MLP_STAGES * MLP_STAGE_FLOATS;  // [out][w]
+  float(*red)[MLP_ROWS][MLP_MAXW] = reinterpret_cast<float(*)[MLP_ROWS][MLP_MAXW]>(wlast + 8 * MLP_MAXW);
+  const int tid = threadIdx.x, h = tid >> 8, u = tid & (MLP_MAXW - 1);
   const int r0 = blockIdx.x * MLP_ROWS;
   const int n0 = (d.din + MLP_CH - 1) / MLP_CH, nw = (d.w + MLP_CH - 1) / MLP_CH;
   const int total = n0 + (d.depth - 1) * nw;
-  auto issue = [&](int c) {
-    if (c < total) {
-      const int l = c < n0 ? 0 : 1 + (c - n0) / nw;
-      const int k0 = MLP_CH * (c < n0 ? c : (c - n0) % nw);
-      const int K = l == 0 ? d.din : d.w;
-      const float* __restrict__ W = p.W[l];
-      float* st = stages + (c % MLP_STAGES) * MLP_STAGE_FLOATS;
+  // The stream of chunks: layer 0 (n0 chunks), then layers 1..depth-1 (nw each).  Blocks walk the chunks of a layer in
+  // rotated orders (start = blockIdx mod n) so that the blocks are not all pulling the same 64 KB at the same moment.
+  // Two cursors (copy-issue and consume) step through the stream; everything per-thread about a copy is hoisted.
+  const int rot0 = blockIdx.x % n0, rotw = blockIdx.x % nw;
+  const unsigned stages_s = (unsigned)__cvta_generic_to_shared(stages);
+  const int jb = tid >> 4, g = tid & 15;  // this thread copies granule g of rows jb, jb+32, ..., jb+224
+  const unsigned dst_thread = (unsigned)((jb * 16 + (g ^ (jb & 7))) * 16);
+  int il = 0, ikc = 0, istage = 0;
+  auto issue = [&]() {
+    if (il < d.depth) {
+      const int n = il == 0 ? n0 : nw, K = il == 0 ? d.din : d.w;
+      int kq = ikc + (il == 0 ? rot0 : rotw);
+      if (kq >= n) kq -= n;
+      const int k = kq * MLP_CH + 4 * g;
+      if (k < K) {
+        const float* src = p.W[il] + (unsigned)(jb * K + k);
+        const unsigned dst = stages_s + istage * MLP_STAGE_BYTES + dst_thread;
+        const unsigned step = 32u * K;
 #pragma unroll
-      for (int i = 0; i < MLP_CH * MLP_MAXW / 4 / MLP_THREADS; i++) {
-        const int idx = tid + i * MLP_THREADS, j = idx >> 3, g = idx & 7;
-        if (j < d.w && k0 + 4 * g < K) mlp_cp16(st + (j * 8 + (g ^ (j & 7))) * 4, W + (size_t)j * K + k0 + 4 * g);
+        for (int i = 0; i < 8; i++)
+          if (jb + 32 * i < d.w) mlp_cp16s(dst + i * (32 * 16 * 16), src + i * step);
       }
+      if (++ikc == n) { ikc = 0; il++; }
     }
+    if (++istage == MLP_STAGES) istage = 0;
     mlp_cp_commit();
   };
-  for (int c = 0; c < MLP_STAGES - 1; c++) issue(c);
+  // the output layer's weights ride along with the first chunk
+  for (int idx = tid; idx < (d.out * d.w) >> 2; idx += MLP_BIG) mlp_cp16(wlast + idx * 4, p.W[d.depth] + idx * 4);
+  for (int c = 0; c < MLP_STAGES - 1; c++) issue();
   const float t = (d.tf > 0 && t_ptr) ? __ldg(t_ptr) : 0.f;
-  for (int i = tid; i < MLP_ROWS * d.din; i += MLP_THREADS) {
+  for (int i = tid; i < MLP_ROWS * d.din; i += MLP_BIG) {
     const int r = i / d.din, c = i - r * d.din, row = r0 + r;
     float v = 0.f;
     if (row < d.rows) {
@@ -140,55 +167,77 @@ gp_kpmlp_fwd_kernel(MlpDims d, MlpPtrs p, const float* __restrict__ xyz, const f
     }
     xs[0][r][c] = v;
   }
-  int cur = 0;
+  int cur = 0, cl = 0, ckc = 0, cstage = 0;
   float acc[MLP_ROWS];
+  const int sw = u & 7;
+  constexpr int GPT = MLP_CH / 4 / MLP_SPLIT;  // granules per thread per chunk
   for (int c = 0; c < total; c++) {
     mlp_cp_wait<MLP_STAGES - 2>();
     __syncthreads();  // chunk c is visible to all; every thread is done with chunk c-1, whose stage is refilled next
-    issue(c + MLP_STAGES - 1);
-    const int l = c < n0 ? 0 : 1 + (c - n0) / nw;
-    const int k0 = MLP_CH * (c < n0 ? c : (c - n0) % nw);
-    const int K = l == 0 ? d.din : d.w;
-    if (tid < d.w) {
-      if (k0 == 0) {
-        const float b = __ldg(p.b[l] + tid);
+    issue();
+    const int n = cl == 0 ? n0 : nw, K = cl == 0 ? d.din : d.w;
+    int kq = ckc + (cl == 0 ? rot0 : rotw);
+    if (kq >= n) kq -= n;
+    const int k0 = kq * MLP_CH;
+    if (ckc == 0) {
 #pragma unroll
-        for (int r = 0; r < MLP_ROWS; r++) acc[r] = b;
-      }
-      const float* st = stages + (c % MLP_STAGES) * MLP_STAGE_FLOATS + tid * 32;
-      const int ng = min(8, (K - k0) >> 2);
-#pragma unroll 4
-      for (int g = 0; g < ng; g++) {
-        const float4 wv = *reinterpret_cast<const float4*>(st + ((g ^ (tid & 7)) << 2));
+      for (int r = 0; r < MLP_ROWS; r++) acc[r] = 0.f;
+    }
+    if (u < d.w) {
+      const float* st = stages + cstage * MLP_STAGE_FLOATS + u * MLP_CH + h * (GPT * 4);
+      const float* xr = &xs[cur][0][k0 + h * (GPT * 4)];
+      auto granule = [&](int q) {  // granule h*GPT + q of the chunk; the swizzle only touches the low 3 bits
+        const float4 wv = *reinterpret_cast<const float4*>(st + ((q ^ sw) << 2));
 #pragma unroll
         for (int r = 0; r < MLP_ROWS; r++) {
-          const float4 xv = *reinterpret_cast<const float4*>(&xs[cur][r][k0 + 4 * g]);
+          const float4 xv = *reinterpret_cast<const float4*>(xr + r * MLP_MAXW + 4 * q);
           acc[r] = fmaf(xv.x, wv.x, acc[r]);
           acc[r] = fmaf(xv.y, wv.y, acc[r]);
           acc[r] = fmaf(xv.z, wv.z, acc[r]);
           acc[r] = fmaf(xv.w, wv.w, acc[r]);
         }
-      }
-      if (k0 + MLP_CH >= K) {  // layer complete: ReLU, keep for the backward, hand to the next layer
+      };
+      const int left = (K - k0 - h * (GPT * 4)) >> 2;  // valid granules of this thread's range
+      if (left >= GPT) {
 #pragma unroll
-        for (int r = 0; r < MLP_ROWS; r++) {
-          const float h = fmaxf(acc[r], 0.f);
-          xs[cur ^ 1][r][tid] = h;
-          if (r0 + r < d.rows) acts[((size_t)l * d.rows + r0 + r) * d.w + tid] = h;
-        }
+        for (int q = 0; q < GPT; q++) granule(q);
+      } else {
+        for (int q = 0; q < left; q++) granule(q);
       }
     }
-    if (k0 + MLP_CH >= K) cur ^= 1;
+    if (ckc == n - 1) {
+      // layer complete: the groups' partial sums meet; thread (h, u) finishes rows 2h, 2h+1 of unit u:
+      // bias, ReLU, keep for the backward, hand to the next layer
+#pragma unroll
+      for (int r = 0; r < MLP_ROWS; r++) red[h][r][u] = acc[r];
+      __syncthreads();
+      if (u < d.w) {
+        const float b = __ldg(p.b[cl] + u);
+#pragma unroll
+        for (int rr = 0; rr < MLP_ROWS / MLP_SPLIT; rr++) {
+          const int r = h * (MLP_ROWS / MLP_SPLIT) + rr;
+          float v = b;
+#pragma unroll
+          for (int hh = 0; hh < MLP_SPLIT; hh++) v += red[hh][r][u];
+          v = fmaxf(v, 0.f);
+          xs[cur ^ 1][r][u] = v;
+          if (r0 + r < d.rows) acts[((size_t)cl * d.rows + r0 + r) * d.w + u] = v;
+        }
+      }
+      ckc = 0; cl++; cur ^= 1;
+    } else {
+      ckc++;
+    }
+    if (++cstage == MLP_STAGES) cstage = 0;
   }
   mlp_cp_wait<0>();
   __syncthreads();
   // output layer: (row, output, k-slice) = (4, 8, 8) threads, slices summed by shuffles
-  {
+  if (tid < 256) {
     const int r = tid >> 6, j = (tid >> 3) & 7, s = tid & 7;
-    const float* __restrict__ Wl = p.W[d.depth];
     float part = 0.f;
     if (j < d.out)
-      for (int k = s; k < d.w; k += 8) part = fmaf(xs[cur][r][k], __ldg(Wl + (size_t)j * d.w + k), part);
+      for (int k = s; k < d.w; k += 8) part = fmaf(xs[cur][r][k], wlast[j * d.w + k], part);
     part += __shfl_xor_sync(0xffffffffu, part, 1);
     part += __shfl_xor_sync(0xffffffffu, part, 2);
     part += __shfl_xor_sync(0xffffffffu, part, 4);
@@ -198,104 +247,146 @@ gp_kpmlp_fwd_kernel(MlpDims d, MlpPtrs p, const float* __restrict__ xyz, const f
 
 // ------------------------------------------------------------------------------------------------ backward: data
 
-// Input unit `tid` of layer l needs column `tid` of W_l: a chunk is 32 whole rows of W_l (contiguous in memory), read
-// from shared memory with consecutive threads on consecutive words.
-static __global__ void __launch_bounds__(MLP_THREADS)
+// Input unit u of layer l needs column u of W_l: a chunk is 64 whole rows of W_l, read from shared memory with
+// consecutive threads on consecutive words; group h takes rows 32h..32h+31 of the chunk.
+static __global__ void __launch_bounds__(MLP_BIG)
 gp_kpmlp_bwd_data_kernel(MlpDims d, MlpPtrs p, const float* __restrict__ xyz, const float* __restrict__ t_ptr,
                          const float* __restrict__ acts, const float* __restrict__ dout, float* __restrict__ dz,
                          float* __restrict__ g_xyz, float* __restrict__ g_feat) {
   float(*gs)[MLP_ROWS][MLP_MAXW] = reinterpret_cast<float(*)[MLP_ROWS][MLP_MAXW]>(mlp_smem);
   float* stages = mlp_smem + 2 * MLP_ROWS * MLP_MAXW;
+  float(*red)[MLP_ROWS][MLP_MAXW] =
+      reinterpret_cast<float(*)[MLP_ROWS][MLP_MAXW]>(stages + MLP_STAGES * MLP_STAGE_FLOATS + 8 * MLP_MAXW);
   __shared__ float go[MLP_ROWS][8];
-  const int tid = threadIdx.x;
+  const int tid = threadIdx.x, h = tid >> 8, u = tid & (MLP_MAXW - 1);
   const int r0 = blockIdx.x * MLP_ROWS;
   const int nw = (d.w + MLP_CH - 1) / MLP_CH;
   const int total = d.depth * nw;
-  auto issue = [&](int c) {
-    if (c < total) {
-      const int l = d.depth - 1 - c / nw, j0 = MLP_CH * (c % nw);
-      const int K = l == 0 ? d.din : d.w;
-      const int granules = (min(MLP_CH, d.w - j0) * K) >> 2;
-      const float* __restrict__ src = p.W[l] + (size_t)j0 * K;
-      float* st = stages + (c % MLP_STAGES) * MLP_STAGE_FLOATS;
-      for (int idx = tid; idx < granules; idx += MLP_THREADS) mlp_cp16(st + idx * 4, src + idx * 4);
+  // chunks: layers depth-1 .. 0, nw row-blocks of 64 rows each, rotated per block like the forward.  In shared memory
+  // the rows keep a fixed stride of MLP_MAXW floats whatever the layer's row length.
+  const int rotw = blockIdx.x % nw;
+  const unsigned stages_s = (unsigned)__cvta_generic_to_shared(stages);
+  const int lane = tid & 31, wp = tid >> 5;  // warp wp copies rows wp, wp+16, wp+32, wp+48 of the chunk
+  int il = d.depth - 1, ijc = 0, istage = 0;
+  auto issue = [&]() {
+    if (il >= 0) {
+      const int K = il == 0 ? d.din : d.w;
+      int jq = ijc + rotw;
+      if (jq >= nw) jq -= nw;
+      const int j = jq * MLP_CH + wp;
+      const float* src = p.W[il] + (unsigned)(j * K + 4 * lane);
+      const unsigned dst = stages_s + istage * MLP_STAGE_BYTES + (unsigned)(wp * MLP_MAXW + 4 * lane) * 4;
+      const unsigned step = 16u * K;
+#pragma unroll
+      for (int i = 0; i < MLP_CH / 16; i++) {
+        if (j + 16 * i < d.w) {
+          if (4 * lane < K) mlp_cp16s(dst + i * (16 * MLP_MAXW * 4), src + i * step);
+          if (4 * lane + 128 < K) mlp_cp16s(dst + i * (16 * MLP_MAXW * 4) + 512, src + i * step + 128);
+        }
+      }
+      if (++ijc == nw) { ijc = 0; il--; }
     }
+    if (++istage == MLP_STAGES) istage = 0;
     mlp_cp_commit();
   };
-  for (int c = 0; c < MLP_STAGES - 1; c++) issue(c);
+  for (int c = 0; c < MLP_STAGES - 1; c++) issue();
   if (tid < MLP_ROWS * 8) {
     const int r = tid >> 3, j = tid & 7;
     go[r][j] = (j < d.out && r0 + r < d.rows) ? __ldg(dout + (size_t)(r0 + r) * d.out + j) : 0.f;
   }
   __syncthreads();
-  if (tid < d.w) {  // through the output Linear, then the ReLU of the last hidden layer
-    float a0[MLP_ROWS];
+  if (u < d.w) {  // thread (h, u): rows 2h, 2h+1 through the output Linear, then the ReLU of the last hidden layer
+    float a0[MLP_ROWS / MLP_SPLIT];
 #pragma unroll
-    for (int r = 0; r < MLP_ROWS; r++) a0[r] = 0.f;
+    for (int rr = 0; rr < MLP_ROWS / MLP_SPLIT; rr++) a0[rr] = 0.f;
     for (int j = 0; j < d.out; j++) {
-      const float wv = __ldg(p.W[d.depth] + (size_t)j * d.w + tid);
+      const float wv = __ldg(p.W[d.depth] + (size_t)j * d.w + u);
 #pragma unroll
-      for (int r = 0; r < MLP_ROWS; r++) a0[r] = fmaf(go[r][j], wv, a0[r]);
+      for (int rr = 0; rr < MLP_ROWS / MLP_SPLIT; rr++) a0[rr] = fmaf(go[h * (MLP_ROWS / MLP_SPLIT) + rr][j], wv, a0[rr]);
     }
 #pragma unroll
-    for (int r = 0; r < MLP_ROWS; r++) {
-      const int row = r0 + r;
-      const size_t a = ((size_t)(d.depth - 1) * d.rows + row) * d.w + tid;
-      const float v = (row < d.rows && __ldg(acts + a) > 0.f) ? a0[r] : 0.f;
-      gs[0][r][tid] = v;
+    for (int rr = 0; rr < MLP_ROWS / MLP_SPLIT; rr++) {
+      const int r = h * (MLP_ROWS / MLP_SPLIT) + rr, row = r0 + r;
+      const size_t a = ((size_t)(d.depth - 1) * d.rows + row) * d.w + u;
+      const float v = (row < d.rows && __ldg(acts + a) > 0.f) ? a0[rr] : 0.f;
+      gs[0][r][u] = v;
       if (row < d.rows) dz[a] = v;
     }
   }
-  int cur = 0;
+  int cur = 0, cl = d.depth - 1, cjc = 0, cstage = 0;
   float acc[MLP_ROWS];
+  float hprev[MLP_ROWS / MLP_SPLIT];  // activations (rows 2h, 2h+1; unit u) of layer cl-1: the ReLU mask
+  constexpr int RPT = MLP_CH / MLP_SPLIT;  // chunk rows per thread
   for (int c = 0; c < total; c++) {
     mlp_cp_wait<MLP_STAGES - 2>();
     __syncthreads();
-    issue(c + MLP_STAGES - 1);
-    // gradient wrt the input of layer l: sum_j gs[r][j] W_l[j][k]; for l > 0 masked by the ReLU of layer l-1
-    const int l = d.depth - 1 - c / nw, j0 = MLP_CH * (c % nw);
-    const int K = l == 0 ? d.din : d.w;
-    const int jn = min(MLP_CH, d.w - j0);
-    if (tid < K) {
-      if (j0 == 0) {
+    issue();
+    // gradient wrt the input of layer cl: sum_j gs[r][j] W[j][k]; for cl > 0 masked by the ReLU of layer cl-1
+    const int K = cl == 0 ? d.din : d.w;
+    int jq = cjc + rotw;
+    if (jq >= nw) jq -= nw;
+    const int j0 = jq * MLP_CH + h * RPT;  // first row of this thread's range
+    if (cjc == 0) {
 #pragma unroll
-        for (int r = 0; r < MLP_ROWS; r++) acc[r] = 0.f;
+      for (int r = 0; r < MLP_ROWS; r++) acc[r] = 0.f;
+#pragma unroll
+      for (int rr = 0; rr < MLP_ROWS / MLP_SPLIT; rr++) {
+        const int row = r0 + h * (MLP_ROWS / MLP_SPLIT) + rr;
+        hprev[rr] = (cl > 0 && u < d.w && row < d.rows) ? __ldg(acts + ((size_t)(cl - 1) * d.rows + row) * d.w + u) : 0.f;
       }
-      const float* st = stages + (c % MLP_STAGES) * MLP_STAGE_FLOATS + tid;
-#pragma unroll 2
-      for (int jj = 0; jj < jn; jj += 4) {
-        const float w0 = st[(jj + 0) * K], w1 = st[(jj + 1) * K], w2 = st[(jj + 2) * K], w3 = st[(jj + 3) * K];
+    }
+    if (u < K) {
+      const float* st = stages + cstage * MLP_STAGE_FLOATS + h * (RPT * MLP_MAXW) + u;
+      const float* gr = &gs[cur][0][j0];
+      auto quad = [&](int jj) {
+        const float w0 = st[(jj + 0) * MLP_MAXW], w1 = st[(jj + 1) * MLP_MAXW];
+        const float w2 = st[(jj + 2) * MLP_MAXW], w3 = st[(jj + 3) * MLP_MAXW];
 #pragma unroll
         for (int r = 0; r < MLP_ROWS; r++) {
-          const float4 gv = *reinterpret_cast<const float4*>(&gs[cur][r][j0 + jj]);
+          const float4 gv = *reinterpret_cast<const float4*>(gr + r * MLP_MAXW + jj);
           acc[r] = fmaf(gv.x, w0, acc[r]);
           acc[r] = fmaf(gv.y, w1, acc[r]);
           acc[r] = fmaf(gv.z, w2, acc[r]);
           acc[r] = fmaf(gv.w, w3, acc[r]);
         }
-      }
-      if (j0 + MLP_CH >= d.w) {
+      };
+      const int left = d.w - j0;
+      if (left >= RPT) {
 #pragma unroll
-        for (int r = 0; r < MLP_ROWS; r++) {
-          if (l > 0) {
-            const int row = r0 + r;
-            const size_t a = ((size_t)(l - 1) * d.rows + row) * d.w + tid;
-            const float v = (row < d.rows && __ldg(acts + a) > 0.f) ? acc[r] : 0.f;
-            gs[cur ^ 1][r][tid] = v;
-            if (row < d.rows) dz[a] = v;
-          } else {
-            gs[cur ^ 1][r][tid] = acc[r];
-          }
-        }
+        for (int jj = 0; jj < RPT; jj += 4) quad(jj);
+      } else {
+        for (int jj = 0; jj < left; jj += 4) quad(jj);
       }
     }
-    if (j0 + MLP_CH >= d.w) cur ^= 1;
+    if (cjc == nw - 1) {
+#pragma unroll
+      for (int r = 0; r < MLP_ROWS; r++) red[h][r][u] = acc[r];
+      __syncthreads();
+      if (u < K) {
+#pragma unroll
+        for (int rr = 0; rr < MLP_ROWS / MLP_SPLIT; rr++) {
+          const int r = h * (MLP_ROWS / MLP_SPLIT) + rr;
+          float v = 0.f;
+#pragma unroll
+          for (int hh = 0; hh < MLP_SPLIT; hh++) v += red[hh][r][u];
+          if (cl > 0) {
+            v = hprev[rr] > 0.f ? v : 0.f;
+            if (r0 + r < d.rows) dz[((size_t)(cl - 1) * d.rows + r0 + r) * d.w + u] = v;
+          }
+          gs[cur ^ 1][r][u] = v;
+        }
+      }
+      cjc = 0; cl--; cur ^= 1;
+    } else {
+      cjc++;
+    }
+    if (++cstage == MLP_STAGES) cstage = 0;
   }
   mlp_cp_wait<0>();
   __syncthreads();
   // gs[cur] now holds dL/d(input row).  Features pass through; xyz goes back through the encoding.
   if (g_feat) {
-    for (int i = tid; i < MLP_ROWS * d.F; i += MLP_THREADS) {
+    for (int i = tid; i < MLP_ROWS * d.F; i += MLP_BIG) {
       const int r = i / d.F, c = i - r * d.F;
       if (r0 + r < d.rows) g_feat[(size_t)(r0 + r) * d.F + c] = gs[cur][r][c];
     }
@@ -306,9 +397,9 @@ gp_kpmlp_bwd_data_kernel(MlpDims d, MlpPtrs p, const float* __restrict__ xyz, co
       const float x = __ldg(xyz + (size_t)row * 3 + dim);
       float a = 0.f;
       for (int f = 0; f < d.xf; f++) {
-        const float sc = (float)(1u << f), u = x * sc;
+        const float sc = (float)(1u << f), uu = x * sc;
         const int c = d.F + (dim * d.xf + f) * 2;
-        a += sc * (gs[cur][r][c] * cosf(u) - gs[cur][r][c + 1] * sinf(u));
+        a += sc * (gs[cur][r][c] * cosf(uu) - gs[cur][r][c + 1] * sinf(uu));
       }
       g_xyz[(size_t)row * 3 + dim] = a;
     }
@@ -321,8 +412,9 @@ gp_kpmlp_bwd_data_kernel(MlpDims d, MlpPtrs p, const float* __restrict__ xyz, co
 #define MLP_TK 64
 #define MLP_RC 32
 #define MLP_WSTAGES 3
+#define MLP_WTHREADS 512  // two groups of 256: group h takes keypoints 16h..16h+15 of every 32-keypoint chunk
 
-static __global__ void __launch_bounds__(MLP_THREADS)
+static __global__ void __launch_bounds__(MLP_WTHREADS)
 gp_kpmlp_bwd_weights_kernel(MlpDims d, MlpPtrs p, MlpTiles tl, const float* __restrict__ x0,
                             const float* __restrict__ acts, const float* __restrict__ dz,
                             const float* __restrict__ dout) {
@@ -337,62 +429,85 @@ gp_kpmlp_bwd_weights_kernel(MlpDims d, MlpPtrs p, MlpTiles tl, const float* __re
   const int local = blockIdx.x - tl.first[l];
   const int tk = local % tiles_k;
   const int j0 = (local / tiles_k) * MLP_TJ, k0 = tk * MLP_TK;
-  const int tid = threadIdx.x, ty = tid >> 4, tx = tid & 15;
+  const int tid = threadIdx.x, h = tid >> 8, ty = (tid >> 4) & 15, tx = tid & 15;
   const bool a_vec = (J & 3) == 0;
   const int nchunks = (d.rows + MLP_RC - 1) / MLP_RC;
-  auto issue = [&](int c) {
-    if (c < nchunks) {
-      const int s = c % MLP_WSTAGES, rc = c * MLP_RC;
-      {
+  int ic = blockIdx.x % nchunks, istage = 0, issued = 0;  // rotated start: see the forward
+  auto issue = [&]() {
+    if (issued < nchunks) {
+      const int rc = ic * MLP_RC;
+      if (tid < 256) {
         const int rr = tid >> 3, c4 = (tid & 7) * 4, row = rc + rr, j = j0 + c4;
         const float* src = A + (size_t)min(row, d.rows - 1) * J;
         if (a_vec) {
           const bool ok = row < d.rows && j < J;
-          mlp_cp16(&a_s[s][rr][c4], ok ? src + j : A, ok);
+          mlp_cp16(&a_s[istage][rr][c4], ok ? src + j : A, ok);
         } else {
 #pragma unroll
           for (int i = 0; i < 4; i++) {
             const bool ok = row < d.rows && j + i < J;
-            mlp_cp4(&a_s[s][rr][c4 + i], ok ? src + j + i : A, ok);
+            mlp_cp4(&a_s[istage][rr][c4 + i], ok ? src + j + i : A, ok);
           }
         }
       }
-#pragma unroll
-      for (int q = 0; q < 2; q++) {
-        const int e = tid + q * MLP_THREADS;
-        const int rr = e >> 4, c4 = (e & 15) * 4, row = rc + rr, k = k0 + c4;
+      {
+        const int rr = tid >> 4, c4 = (tid & 15) * 4, row = rc + rr, k = k0 + c4;
         const bool ok = row < d.rows && k < K;
-        mlp_cp16(&b_s[s][rr][c4], ok ? B + (size_t)row * K + k : B, ok);
+        mlp_cp16(&b_s[istage][rr][c4], ok ? B + (size_t)row * K + k : B, ok);
       }
+      issued++;
+      if (++ic == nchunks) ic = 0;
     }
+    if (++istage == MLP_WSTAGES) istage = 0;
     mlp_cp_commit();
   };
-  for (int c = 0; c < MLP_WSTAGES - 1; c++) issue(c);
+  for (int c = 0; c < MLP_WSTAGES - 1; c++) issue();
   float acc[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
   float bacc[2] = {0.f, 0.f};
+  int cstage = 0;
   for (int c = 0; c < nchunks; c++) {
     mlp_cp_wait<MLP_WSTAGES - 2>();
     __syncthreads();
-    issue(c + MLP_WSTAGES - 1);
-    const int s = c % MLP_WSTAGES;
-#pragma unroll 8
-    for (int rr = 0; rr < MLP_RC; rr++) {
-      const float2 a = *reinterpret_cast<const float2*>(&a_s[s][rr][2 * ty]);
-      const float4 b = *reinterpret_cast<const float4*>(&b_s[s][rr][4 * tx]);
+    issue();
+#pragma unroll
+    for (int q = 0; q < MLP_RC / 2; q++) {
+      const int rr = h * (MLP_RC / 2) + q;
+      const float2 a = *reinterpret_cast<const float2*>(&a_s[cstage][rr][2 * ty]);
+      const float4 b = *reinterpret_cast<const float4*>(&b_s[cstage][rr][4 * tx]);
       acc[0][0] = fmaf(a.x, b.x, acc[0][0]); acc[0][1] = fmaf(a.x, b.y, acc[0][1]);
       acc[0][2] = fmaf(a.x, b.z, acc[0][2]); acc[0][3] = fmaf(a.x, b.w, acc[0][3]);
       acc[1][0] = fmaf(a.y, b.x, acc[1][0]); acc[1][1] = fmaf(a.y, b.y, acc[1][1]);
       acc[1][2] = fmaf(a.y, b.z, acc[1][2]); acc[1][3] = fmaf(a.y, b.w, acc[1][3]);
       if (tk == 0) { bacc[0] += a.x; bacc[1] += a.y; }
     }
+    if (++cstage == MLP_WSTAGES) cstage = 0;
   }
   mlp_cp_wait<0>();
+  __syncthreads();
+  // group 1 hands its partial sums to group 0 through the (now idle) b_s ring
+  float* red = &b_s[0][0][0];  // [256][10]
+  if (h == 1) {
+    float* r = red + (tid & 255) * 10;
 #pragma unroll
-  for (int jj = 0; jj < 2; jj++) {
-    const int j = j0 + 2 * ty + jj, k = k0 + 4 * tx;
-    if (j < J) {
-      if (k < K) *reinterpret_cast<float4*>(p.gW[l] + (size_t)j * K + k) = make_float4(acc[jj][0], acc[jj][1], acc[jj][2], acc[jj][3]);
-      if (tk == 0 && tx == 0) p.gb[l][j] = bacc[jj];
+    for (int jj = 0; jj < 2; jj++) {
+#pragma unroll
+      for (int i = 0; i < 4; i++) r[jj * 4 + i] = acc[jj][i];
+      r[8 + jj] = bacc[jj];
+    }
+  }
+  __syncthreads();
+  if (h == 0) {
+    const float* r = red + tid * 10;
+#pragma unroll
+    for (int jj = 0; jj < 2; jj++) {
+      const int j = j0 + 2 * ty + jj, k = k0 + 4 * tx;
+      if (j < J) {
+        if (k < K)
+          *reinterpret_cast<float4*>(p.gW[l] + (size_t)j * K + k) =
+              make_float4(acc[jj][0] + r[jj * 4 + 0], acc[jj][1] + r[jj * 4 + 1], acc[jj][2] + r[jj * 4 + 2],
+                          acc[jj][3] + r[jj * 4 + 3]);
+        if (tk == 0 && tx == 0) p.gb[l][j] = bacc[jj] + r[8 + jj];
+      }
     }
   }
 }
@@ -430,7 +545,7 @@ extern "C" int gp_kpmlp_forward(const gp_mlp_cfg* cfg, const float* kp_xyz, cons
   GP_CUDA_TRY(cudaFuncSetAttribute(gp_kpmlp_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MLP_SMEM_BYTES));
   const int blocks = (d.rows + MLP_ROWS - 1) / MLP_ROWS;
   GP_KERNEL("gp_kpmlp_fwd_kernel", stream,
-            gp_kpmlp_fwd_kernel<<<blocks, MLP_THREADS, MLP_SMEM_BYTES, stream>>>(d, p, kp_xyz, kp_feat, t, x0, acts, out));
+            gp_kpmlp_fwd_kernel<<<blocks, MLP_BIG, MLP_SMEM_BYTES, stream>>>(d, p, kp_xyz, kp_feat, t, x0, acts, out));
   GP_LAUNCH_CHECK();
   return GP_OK;
 }
@@ -459,7 +574,7 @@ extern "C" int gp_kpmlp_backward(const gp_mlp_cfg* cfg, const float* kp_xyz, con
   const int blocks = (d.rows + MLP_ROWS - 1) / MLP_ROWS;
   GP_CUDA_TRY(cudaFuncSetAttribute(gp_kpmlp_bwd_data_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MLP_SMEM_BYTES));
   GP_KERNEL("gp_kpmlp_bwd_data_kernel", stream,
-            gp_kpmlp_bwd_data_kernel<<<blocks, MLP_THREADS, MLP_SMEM_BYTES, stream>>>(d, p, kp_xyz, t, acts, dL_dout, dz, dL_dxyz,
+            gp_kpmlp_bwd_data_kernel<<<blocks, MLP_BIG, MLP_SMEM_BYTES, stream>>>(d, p, kp_xyz, t, acts, dL_dout, dz, dL_dxyz,
                                                                         dL_dfeat));
   GP_LAUNCH_CHECK();
   MlpTiles tl = {};
@@ -468,7 +583,7 @@ extern "C" int gp_kpmlp_backward(const gp_mlp_cfg* cfg, const float* kp_xyz, con
     tl.first[l + 1] = tl.first[l] + ((J + MLP_TJ - 1) / MLP_TJ) * ((K + MLP_TK - 1) / MLP_TK);
   }
   GP_KERNEL("gp_kpmlp_bwd_weights_kernel", stream,
-            gp_kpmlp_bwd_weights_kernel<<<tl.first[d.depth + 1], MLP_THREADS, 0, stream>>>(d, p, tl, x0, acts, dz,
+            gp_kpmlp_bwd_weights_kernel<<<tl.first[d.depth + 1], MLP_WTHREADS, 0, stream>>>(d, p, tl, x0, acts, dz,
                                                                                           dL_dout));
   GP_LAUNCH_CHECK();
   return GP_OK;

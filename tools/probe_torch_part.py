@@ -31,6 +31,25 @@ e0.record()
 for _ in range(50): g.replay()
 e1.record(); torch.cuda.synchronize()
 print("keypoint MLP (PE, cat, 5 Linear, normalize) fwd+bwd as a graph: %.4f ms" % (e0.elapsed_time(e1) / 50))
+from gaussianprediction_b200.deform import keypoint_mlp
+def body_fused():
+    for p in params: p.grad = None
+    noise = torch.randn_like(kp) * 0.0
+    d = keypoint_mlp(net, kp + noise, kf, t, 10, 6)
+    dx, dq = d[..., 0:3], torch.nn.functional.normalize(d[..., 3:7])
+    torch.autograd.backward([dx, dq], [g_dx, g_dq])
+s.wait_stream(torch.cuda.current_stream())
+with torch.cuda.stream(s):
+    for _ in range(3): body_fused()
+torch.cuda.current_stream().wait_stream(s); torch.cuda.synchronize()
+for p in params: p.grad = None
+gf = torch.cuda.CUDAGraph()
+with torch.cuda.graph(gf): body_fused()
+torch.cuda.synchronize()
+e0.record()
+for _ in range(50): gf.replay()
+e1.record(); torch.cuda.synchronize()
+print("same through gp_kpmlp_* as a graph: %.4f ms" % (e0.elapsed_time(e1) / 50))
 # image-sized torch ops of the step: SH cat + probe loss
 N = 100000
 dc = torch.randn(N, 1, 3, device=dev, requires_grad=True); rest = torch.randn(N, 15, 3, device=dev, requires_grad=True)
