@@ -26,7 +26,7 @@ class RasterCfg(ctypes.Structure):
 class MlpCfg(ctypes.Structure):
     """Mirror of ``gp_mlp_cfg``."""
     _fields_ = [("rows", c_int), ("feature_dim", c_int), ("xyz_freq", c_int), ("time_freq", c_int), ("depth", c_int),
-                ("width", c_int), ("out_dim", c_int)]
+                ("width", c_int), ("out_dim", c_int), ("normalize_q", c_int)]
 
 
 HDR_NUM_RENDERED, HDR_OVERFLOW, HDR_NUM_POINTS, HDR_NUM_SORTED, HDR_WORDS = 0, 1, 2, 3, 64
@@ -63,8 +63,8 @@ SIGNATURES = {
     "gp_image_loss_forward": (c_int, [c_int, c_int, c_int, _P, _P, _P, _P, _P, _P]),
     "gp_image_loss_backward": (c_int, [c_int, c_int, c_int, _P, _P, _P, c_float, c_float, _P, _P, _P]),
     "gp_kpmlp_sizes": (c_int, [POINTER(MlpCfg), POINTER(c_size_t), POINTER(c_size_t)]),
-    "gp_kpmlp_forward": (c_int, [POINTER(MlpCfg), _P, _P, _P, _P, _P, _P, _P, _P]),
-    "gp_kpmlp_backward": (c_int, [POINTER(MlpCfg), _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
+    "gp_kpmlp_forward": (c_int, [POINTER(MlpCfg), _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
+    "gp_kpmlp_backward": (c_int, [POINTER(MlpCfg), _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "gp_raster_export_binning": (c_int, [POINTER(RasterCfg), _P, _P, c_longlong, _P, _P, _P]),
 }
 

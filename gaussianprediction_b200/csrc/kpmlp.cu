@@ -26,7 +26,7 @@
 #define MLP_THREADS 256
 
 struct MlpDims {
-  int rows, F, xf, tf, depth, w, out, din;
+  int rows, F, xf, tf, depth, w, out, din, norm_q;
 };
 struct MlpPtrs {
   const float* W[MLP_MAXL];
@@ -41,14 +41,14 @@ struct MlpTiles {
 static int mlp_dims(const gp_mlp_cfg* c, MlpDims* d) {
   if (!c) return GP_ERR_BAD_ARG;
   d->rows = c->rows; d->F = c->feature_dim; d->xf = c->xyz_freq; d->tf = c->time_freq;
-  d->depth = c->depth; d->w = c->width; d->out = c->out_dim;
+  d->depth = c->depth; d->w = c->width; d->out = c->out_dim; d->norm_q = c->normalize_q != 0;
   d->din = c->feature_dim + 6 * c->xyz_freq + 2 * c->time_freq;
   if (c->rows < 0 || c->feature_dim < 0 || c->xyz_freq < 0 || c->time_freq < 0) return GP_ERR_BAD_ARG;
   if (c->xyz_freq > 24 || c->time_freq > 24) return GP_ERR_LIMIT;  // 2^f must stay exact in the encoding
   if (c->depth < 1 || c->depth > MLP_MAXL - 1) return GP_ERR_LIMIT;
   if (c->width < 4 || c->width > MLP_MAXW || (c->width & 3)) return GP_ERR_LIMIT;
   if (d->din < 4 || d->din > MLP_MAXW || (d->din & 3)) return GP_ERR_LIMIT;
-  if (c->out_dim < 1 || c->out_dim > 8) return GP_ERR_LIMIT;
+  if (c->out_dim != 7 && c->out_dim != 8) return GP_ERR_LIMIT;  // (xyz, quaternion[, opacity]): get_motion_delta's columns
   return GP_OK;
 }
 
@@ -61,11 +61,6 @@ __device__ __forceinline__ void mlp_cp16(float* smem, const float* gmem, bool va
   const int n = valid ? 16 : 0;  // 0 source bytes: the 16 destination bytes are zero-filled
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(s), "l"(gmem), "r"(n) : "memory");
 }
-__device__ __forceinline__ void mlp_cp4(float* smem, const float* gmem, bool valid = true) {
-  const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
-  const int n = valid ? 4 : 0;
-  asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(s), "l"(gmem), "r"(n) : "memory");
-}
 __device__ __forceinline__ void mlp_cp16s(unsigned smem_addr, const float* gmem) {  // shared address already converted
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr), "l"(gmem) : "memory");
 }
@@ -74,6 +69,20 @@ template <int N>
 __device__ __forceinline__ void mlp_cp_wait() {
   asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
+
+// The network's output row is (delta_xyz[3], delta_q[4][, delta_o]) (scene/gaussian_model.py:189); the three tensors
+// cross the ABI separately so that no slicing copies are needed on either side.
+struct MlpOut {
+  float* xyz;  // [rows,3]
+  float* q;    // [rows,4]
+  float* o;    // [rows,1] or NULL
+};
+struct MlpOutGrad {
+  const float* xyz;
+  const float* q;
+  const float* o;
+};
+#define MLP_NORM_EPS 1e-12f  // torch.nn.functional.normalize default eps
 
 #define MLP_CH 64     // weight columns (forward) / rows (backward) per chunk
 #define MLP_STAGES 3  // chunks resident in shared memory
@@ -118,7 +127,7 @@ __device__ __forceinline__ float mlp_input(const MlpDims& d, const float* __rest
 static __global__ void __launch_bounds__(MLP_BIG)
 gp_kpmlp_fwd_kernel(MlpDims d, MlpPtrs p, const float* __restrict__ xyz, const float* __restrict__ feat,
                     const float* __restrict__ t_ptr, float* __restrict__ x0, float* __restrict__ acts,
-                    float* __restrict__ out) {
+                    float* __restrict__ raw_out, MlpOut out) {
   float(*xs)[MLP_ROWS][MLP_MAXW] = reinterpret_cast<float(*)[MLP_ROWS][MLP_MAXW]>(mlp_smem);
   float* stages = mlp_smem + 2 * MLP_ROWS * MLP_MAXW;
   float* wlast = stages + MLP_STAGES * MLP_STAGE_FLOATS;  // [out][w]
@@ -241,7 +250,25 @@ gp_kpmlp_fwd_kernel(MlpDims d, MlpPtrs p, const float* __restrict__ xyz, const f
     part += __shfl_xor_sync(0xffffffffu, part, 1);
     part += __shfl_xor_sync(0xffffffffu, part, 2);
     part += __shfl_xor_sync(0xffffffffu, part, 4);
-    if (s == 0 && j < d.out && r0 + r < d.rows) out[(size_t)(r0 + r) * d.out + j] = part + __ldg(p.b[d.depth] + j);
+    if (s == 0) red[0][r][j] = j < d.out ? part + __ldg(p.b[d.depth] + j) : 0.f;
+  }
+  __syncthreads();
+  if (tid < MLP_ROWS * 8) {
+    // thread (row, column): keep the raw row for the backward, normalise the quaternion if asked
+    // (scene/gaussian_model.py:266-267: rotation_activation = torch.nn.functional.normalize), write the three tensors
+    const int r = tid >> 3, j = tid & 7, row = r0 + r;
+    if (row < d.rows) {
+      const float* o = &red[0][r][0];
+      float v = o[j];
+      raw_out[(size_t)row * 8 + j] = v;
+      if (d.norm_q && j >= 3 && j < 7) {
+        const float n = sqrtf(o[3] * o[3] + o[4] * o[4] + o[5] * o[5] + o[6] * o[6]);
+        v = v / fmaxf(n, MLP_NORM_EPS);
+      }
+      if (j < 3) out.xyz[(size_t)row * 3 + j] = v;
+      else if (j < 7) out.q[(size_t)row * 4 + (j - 3)] = v;
+      else if (j < d.out && out.o) out.o[row] = v;
+    }
   }
 }
 
@@ -251,8 +278,9 @@ gp_kpmlp_fwd_kernel(MlpDims d, MlpPtrs p, const float* __restrict__ xyz, const f
 // consecutive threads on consecutive words; group h takes rows 32h..32h+31 of the chunk.
 static __global__ void __launch_bounds__(MLP_BIG)
 gp_kpmlp_bwd_data_kernel(MlpDims d, MlpPtrs p, const float* __restrict__ xyz, const float* __restrict__ t_ptr,
-                         const float* __restrict__ acts, const float* __restrict__ dout, float* __restrict__ dz,
-                         float* __restrict__ g_xyz, float* __restrict__ g_feat) {
+                         const float* __restrict__ acts, const float* __restrict__ raw_out, MlpOutGrad gout,
+                         float* __restrict__ dout, float* __restrict__ dz, float* __restrict__ g_xyz,
+                         float* __restrict__ g_feat) {
   float(*gs)[MLP_ROWS][MLP_MAXW] = reinterpret_cast<float(*)[MLP_ROWS][MLP_MAXW]>(mlp_smem);
   float* stages = mlp_smem + 2 * MLP_ROWS * MLP_MAXW;
   float(*red)[MLP_ROWS][MLP_MAXW] =
@@ -292,7 +320,32 @@ gp_kpmlp_bwd_data_kernel(MlpDims d, MlpPtrs p, const float* __restrict__ xyz, co
   for (int c = 0; c < MLP_STAGES - 1; c++) issue();
   if (tid < MLP_ROWS * 8) {
     const int r = tid >> 3, j = tid & 7;
-    go[r][j] = (j < d.out && r0 + r < d.rows) ? __ldg(dout + (size_t)(r0 + r) * d.out + j) : 0.f;
+    // dL/d(raw output row): the incoming gradients of the three tensors, the quaternion part taken back through the
+    // normalisation (x / max(|x|, eps)): g/n - x (x.g)/n^3 above eps, g/eps below.  Kept in `dout` ([rows][8], zero
+    // padded) for the weight-gradient kernel.
+    const int row = r0 + r;
+    float v = 0.f;
+    if (row < d.rows) {
+      if (j < 3) v = gout.xyz ? __ldg(gout.xyz + (size_t)row * 3 + j) : 0.f;
+      else if (j < 7) {
+        v = gout.q ? __ldg(gout.q + (size_t)row * 4 + (j - 3)) : 0.f;
+        if (d.norm_q && gout.q) {
+          const float* x = raw_out + (size_t)row * 8 + 3;
+          const float* gq = gout.q + (size_t)row * 4;
+          const float x0 = __ldg(x), x1 = __ldg(x + 1), x2 = __ldg(x + 2), x3 = __ldg(x + 3);
+          const float n = sqrtf(x0 * x0 + x1 * x1 + x2 * x2 + x3 * x3);
+          if (n > MLP_NORM_EPS) {
+            const float dot = x0 * __ldg(gq) + x1 * __ldg(gq + 1) + x2 * __ldg(gq + 2) + x3 * __ldg(gq + 3);
+            const float inv = 1.f / n;
+            v = v * inv - __ldg(x + (j - 3)) * (dot * inv * inv * inv);
+          } else {
+            v = v / MLP_NORM_EPS;
+          }
+        }
+      } else if (j < d.out) v = gout.o ? __ldg(gout.o + row) : 0.f;
+      dout[(size_t)row * 8 + j] = v;
+    }
+    go[r][j] = v;
   }
   __syncthreads();
   if (u < d.w) {  // thread (h, u): rows 2h, 2h+1 through the output Linear, then the ReLU of the last hidden layer
@@ -423,14 +476,14 @@ gp_kpmlp_bwd_weights_kernel(MlpDims d, MlpPtrs p, MlpTiles tl, const float* __re
   int l = 0;
   while (l < d.depth && (int)blockIdx.x >= tl.first[l + 1]) l++;
   const int J = l < d.depth ? d.w : d.out, K = l == 0 ? d.din : d.w;
-  const float* __restrict__ A = l < d.depth ? dz + (size_t)l * d.rows * d.w : dout;  // [rows][J]
+  const float* __restrict__ A = l < d.depth ? dz + (size_t)l * d.rows * d.w : dout;  // [rows][ldA], zero beyond J
+  const int ldA = l < d.depth ? d.w : 8;
   const float* __restrict__ B = l == 0 ? x0 : acts + (size_t)(l - 1) * d.rows * d.w;    // [rows][K]
   const int tiles_k = (K + MLP_TK - 1) / MLP_TK;
   const int local = blockIdx.x - tl.first[l];
   const int tk = local % tiles_k;
   const int j0 = (local / tiles_k) * MLP_TJ, k0 = tk * MLP_TK;
   const int tid = threadIdx.x, h = tid >> 8, ty = (tid >> 4) & 15, tx = tid & 15;
-  const bool a_vec = (J & 3) == 0;
   const int nchunks = (d.rows + MLP_RC - 1) / MLP_RC;
   int ic = blockIdx.x % nchunks, istage = 0, issued = 0;  // rotated start: see the forward
   auto issue = [&]() {
@@ -438,17 +491,8 @@ gp_kpmlp_bwd_weights_kernel(MlpDims d, MlpPtrs p, MlpTiles tl, const float* __re
       const int rc = ic * MLP_RC;
       if (tid < 256) {
         const int rr = tid >> 3, c4 = (tid & 7) * 4, row = rc + rr, j = j0 + c4;
-        const float* src = A + (size_t)min(row, d.rows - 1) * J;
-        if (a_vec) {
-          const bool ok = row < d.rows && j < J;
-          mlp_cp16(&a_s[istage][rr][c4], ok ? src + j : A, ok);
-        } else {
-#pragma unroll
-          for (int i = 0; i < 4; i++) {
-            const bool ok = row < d.rows && j + i < J;
-            mlp_cp4(&a_s[istage][rr][c4 + i], ok ? src + j + i : A, ok);
-          }
-        }
+        const bool ok = row < d.rows && j < ldA;
+        mlp_cp16(&a_s[istage][rr][c4], ok ? A + (size_t)row * ldA + j : A, ok);
       }
       {
         const int rr = tid >> 4, c4 = (tid & 15) * 4, row = rc + rr, k = k0 + c4;
@@ -519,18 +563,18 @@ extern "C" int gp_kpmlp_sizes(const gp_mlp_cfg* cfg, size_t* saved_bytes, size_t
   int rc = mlp_dims(cfg, &d);
   if (rc) return rc;
   const size_t rows = (size_t)(d.rows > 0 ? d.rows : 1);
-  if (saved_bytes) *saved_bytes = gp_align_up(rows * ((size_t)d.din + (size_t)d.depth * d.w) * sizeof(float), 256);
-  if (bwd_scratch_bytes) *bwd_scratch_bytes = gp_align_up(rows * (size_t)d.depth * d.w * sizeof(float), 256);
+  if (saved_bytes) *saved_bytes = gp_align_up(rows * ((size_t)d.din + (size_t)d.depth * d.w + 8) * sizeof(float), 256);
+  if (bwd_scratch_bytes) *bwd_scratch_bytes = gp_align_up(rows * ((size_t)d.depth * d.w + 8) * sizeof(float), 256);
   return GP_OK;
 }
 
 extern "C" int gp_kpmlp_forward(const gp_mlp_cfg* cfg, const float* kp_xyz, const float* kp_feat, const float* t,
-                                const float* const* weights, const float* const* biases, void* saved, float* out,
-                                gp_stream_t stream_) {
+                                const float* const* weights, const float* const* biases, void* saved, float* delta_xyz,
+                                float* delta_q, float* delta_o, gp_stream_t stream_) {
   MlpDims d;
   int rc = mlp_dims(cfg, &d);
   if (rc) return rc;
-  if (!weights || !biases || !saved || !out) return GP_ERR_BAD_ARG;
+  if (!weights || !biases || !saved || !delta_xyz || !delta_q) return GP_ERR_BAD_ARG;
   if ((d.xf > 0 && !kp_xyz) || (d.F > 0 && !kp_feat) || (d.tf > 0 && !t)) return GP_ERR_BAD_ARG;
   if (d.rows == 0) return GP_OK;
   cudaStream_t stream = (cudaStream_t)stream_;
@@ -542,22 +586,25 @@ extern "C" int gp_kpmlp_forward(const gp_mlp_cfg* cfg, const float* kp_xyz, cons
   }
   float* x0 = (float*)saved;
   float* acts = x0 + (size_t)d.rows * d.din;
+  float* raw_out = acts + (size_t)d.depth * d.rows * d.w;
+  MlpOut out = {delta_xyz, delta_q, delta_o};
   GP_CUDA_TRY(cudaFuncSetAttribute(gp_kpmlp_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MLP_SMEM_BYTES));
   const int blocks = (d.rows + MLP_ROWS - 1) / MLP_ROWS;
   GP_KERNEL("gp_kpmlp_fwd_kernel", stream,
-            gp_kpmlp_fwd_kernel<<<blocks, MLP_BIG, MLP_SMEM_BYTES, stream>>>(d, p, kp_xyz, kp_feat, t, x0, acts, out));
+            gp_kpmlp_fwd_kernel<<<blocks, MLP_BIG, MLP_SMEM_BYTES, stream>>>(d, p, kp_xyz, kp_feat, t, x0, acts, raw_out,
+                                                                              out));
   GP_LAUNCH_CHECK();
   return GP_OK;
 }
 
 extern "C" int gp_kpmlp_backward(const gp_mlp_cfg* cfg, const float* kp_xyz, const float* t,
-                                 const float* const* weights, const void* saved, const float* dL_dout,
-                                 void* bwd_scratch, float* dL_dxyz, float* dL_dfeat, float* const* dL_dweights,
+                                 const float* const* weights, const void* saved, const float* dL_ddelta_xyz,
+                                 const float* dL_ddelta_q, const float* dL_ddelta_o, void* bwd_scratch, float* dL_dxyz, float* dL_dfeat, float* const* dL_dweights,
                                  float* const* dL_dbiases, gp_stream_t stream_) {
   MlpDims d;
   int rc = mlp_dims(cfg, &d);
   if (rc) return rc;
-  if (!weights || !saved || !dL_dout || !bwd_scratch || !dL_dweights || !dL_dbiases) return GP_ERR_BAD_ARG;
+  if (!weights || !saved || !bwd_scratch || !dL_dweights || !dL_dbiases) return GP_ERR_BAD_ARG;
   if (d.xf > 0 && dL_dxyz && !kp_xyz) return GP_ERR_BAD_ARG;
   if (d.rows == 0) return GP_OK;
   cudaStream_t stream = (cudaStream_t)stream_;
@@ -570,12 +617,15 @@ extern "C" int gp_kpmlp_backward(const gp_mlp_cfg* cfg, const float* kp_xyz, con
   }
   const float* x0 = (const float*)saved;
   const float* acts = x0 + (size_t)d.rows * d.din;
+  const float* raw_out = acts + (size_t)d.depth * d.rows * d.w;
   float* dz = (float*)bwd_scratch;
+  float* dout = dz + (size_t)d.depth * d.rows * d.w;
+  MlpOutGrad gout = {dL_ddelta_xyz, dL_ddelta_q, dL_ddelta_o};
   const int blocks = (d.rows + MLP_ROWS - 1) / MLP_ROWS;
   GP_CUDA_TRY(cudaFuncSetAttribute(gp_kpmlp_bwd_data_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MLP_SMEM_BYTES));
   GP_KERNEL("gp_kpmlp_bwd_data_kernel", stream,
-            gp_kpmlp_bwd_data_kernel<<<blocks, MLP_BIG, MLP_SMEM_BYTES, stream>>>(d, p, kp_xyz, t, acts, dL_dout, dz, dL_dxyz,
-                                                                        dL_dfeat));
+            gp_kpmlp_bwd_data_kernel<<<blocks, MLP_BIG, MLP_SMEM_BYTES, stream>>>(d, p, kp_xyz, t, acts, raw_out, gout,
+                                                                                   dout, dz, dL_dxyz, dL_dfeat));
   GP_LAUNCH_CHECK();
   MlpTiles tl = {};
   for (int l = 0; l <= d.depth; l++) {
@@ -584,7 +634,7 @@ extern "C" int gp_kpmlp_backward(const gp_mlp_cfg* cfg, const float* kp_xyz, con
   }
   GP_KERNEL("gp_kpmlp_bwd_weights_kernel", stream,
             gp_kpmlp_bwd_weights_kernel<<<tl.first[d.depth + 1], MLP_WTHREADS, 0, stream>>>(d, p, tl, x0, acts, dz,
-                                                                                          dL_dout));
+                                                                                            dout));
   GP_LAUNCH_CHECK();
   return GP_OK;
 }

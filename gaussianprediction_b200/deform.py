@@ -103,7 +103,8 @@ def spatial_order(xyz):
     if N:
         L = _lib.lib()
         ws = torch.empty((L.gp_spatial_order_ws_bytes(N),), dtype=torch.uint8, device=xyz.device)
-        check(L.gp_spatial_order(N, ptr(_c(xyz)), ptr(order), ptr(ws), _lib.stream_ptr()), "gp_spatial_order")
+        xyz_c = _c(xyz)   # named: a contiguous copy must outlive the launch
+        check(L.gp_spatial_order(N, ptr(xyz_c), ptr(order), ptr(ws), _lib.stream_ptr()), "gp_spatial_order")
     return order
 
 
@@ -128,8 +129,9 @@ def knn_keypoints(xyz, motion_feature, kp_xyz, kp_feature, K, knn_type="hybird",
     idx32 = hint if hint is not None else torch.empty((N, K), dtype=torch.int32, device=dev)
     idx64 = None if idx32_only else torch.empty((N, K), dtype=torch.int64, device=dev)
     dists = torch.empty((N, K), dtype=torch.float32, device=dev) if return_dists else None
-    check(_lib.lib().gp_knn_keypoints(N, Kp, F, int(K), float(r), float(feature_amplify), ptr(_c(xyz)), ptr(mf),
-                                      ptr(_c(kp_xyz)), ptr(kf), ptr(order), ptr(hint), ptr(idx64), ptr(idx32), ptr(dists),
+    xyz_c, kp_c = _c(xyz), _c(kp_xyz)   # named: contiguous copies must outlive the launch
+    check(_lib.lib().gp_knn_keypoints(N, Kp, F, int(K), float(r), float(feature_amplify), ptr(xyz_c), ptr(mf),
+                                      ptr(kp_c), ptr(kf), ptr(order), ptr(hint), ptr(idx64), ptr(idx32), ptr(dists),
                                       _lib.stream_ptr()),
           "gp_knn_keypoints")
     return idx64, idx32, dists
@@ -168,9 +170,9 @@ class _KeypointBlend(torch.autograd.Function):
         g_rot = torch.empty((N, 4), **f) if need[5] else None
         g_sc = torch.empty((N, 3), **f) if need[6] else None
         g_op = torch.empty((N, 1), **f) if need[7] else None
-        gc = lambda g: None if g is None else _c(g)
+        g_in = [None if g is None else _c(g) for g in (g_xyz_t, g_q_t, g_s_t, g_o_t)]   # kept alive until the launch
         check(L.gp_blend_backward(N, Kp, K, ptr(logits), ptr(idx32), None, ptr(kpx), ptr(kpq), ptr(rot), ptr(s_t), ptr(o_t),
-                                  ptr(gc(g_xyz_t)), ptr(gc(g_q_t)), ptr(gc(g_s_t)), ptr(gc(g_o_t)), ptr(g_logits),
+                                  ptr(g_in[0]), ptr(g_in[1]), ptr(g_in[2]), ptr(g_in[3]), ptr(g_logits),
                                   ptr(g_xyz), ptr(g_rot), ptr(g_sc), ptr(g_op), ptr(g_kpx), ptr(g_kpq),
                                   _lib.stream_ptr()), "gp_blend_backward")
         return g_logits, None, (g_kpx if need[2] else None), (g_kpq if need[3] else None), g_xyz, g_rot, g_sc, g_op
@@ -181,32 +183,37 @@ def keypoint_blend(logits, idx32, kp_delta_xyz, kp_delta_q, xyz, rot, scaling, o
 
 
 class _KeypointMLP(torch.autograd.Function):
-    """delta = df_model(cat([feature, PE(xyz), PE(t)])) for the keypoints, forward and backward in libgp_b200.so."""
+    """(delta_xyz, delta_q[, delta_o]) = get_motion_delta at the keypoints (cat([feature, PE(xyz), PE(t)]) -> df_model,
+    optional quaternion normalisation), forward and backward in libgp_b200.so."""
 
     @staticmethod
     def forward(ctx, dims, kp_xyz, kp_feat, t, *params):
         L = _lib.lib()
-        xyz_freq, time_freq, depth, width, out_dim = dims
+        xyz_freq, time_freq, depth, width, out_dim, normalize_q = dims
         n = depth + 1
         weights, biases = [_c(w) for w in params[:n]], [_c(b) for b in params[n:]]
         xyz_c, feat_c = _c(kp_xyz), _c(kp_feat)
         t_c = _c(t).reshape(-1)[:1]
-        cfg = _lib.MlpCfg(int(xyz_c.shape[0]), int(feat_c.shape[1]), xyz_freq, time_freq, depth, width, out_dim)
+        cfg = _lib.MlpCfg(int(xyz_c.shape[0]), int(feat_c.shape[1]), xyz_freq, time_freq, depth, width, out_dim,
+                          int(bool(normalize_q)))
         sv, bs = ctypes.c_size_t(), ctypes.c_size_t()
         check(L.gp_kpmlp_sizes(ctypes.byref(cfg), ctypes.byref(sv), ctypes.byref(bs)), "gp_kpmlp_sizes")
         dev = xyz_c.device
+        f = dict(dtype=torch.float32, device=dev)
         saved = torch.empty(sv.value, dtype=torch.uint8, device=dev)
-        out = torch.empty((cfg.rows, out_dim), dtype=torch.float32, device=dev)
+        dxyz, dq = torch.empty((cfg.rows, 3), **f), torch.empty((cfg.rows, 4), **f)
+        do = torch.empty((cfg.rows, 1), **f) if out_dim == 8 else None
         wp = (ctypes.c_void_p * n)(*[w.data_ptr() for w in weights])
         bp = (ctypes.c_void_p * n)(*[b.data_ptr() for b in biases])
-        check(L.gp_kpmlp_forward(ctypes.byref(cfg), ptr(xyz_c), ptr(feat_c), ptr(t_c), wp, bp, ptr(saved), ptr(out),
-                                 _lib.stream_ptr()), "gp_kpmlp_forward")
+        check(L.gp_kpmlp_forward(ctypes.byref(cfg), ptr(xyz_c), ptr(feat_c), ptr(t_c), wp, bp, ptr(saved), ptr(dxyz),
+                                 ptr(dq), ptr(do), _lib.stream_ptr()), "gp_kpmlp_forward")
         ctx.save_for_backward(xyz_c, t_c, saved, *weights)
         ctx.cfg, ctx.bwd_bytes = cfg, bs.value
-        return out
+        ctx.set_materialize_grads(False)     # an unused output arrives as None (= zeros for the kernel), not as a zero tensor
+        return (dxyz, dq) if do is None else (dxyz, dq, do)
 
     @staticmethod
-    def backward(ctx, g_out):
+    def backward(ctx, g_dxyz, g_dq, g_do=None):
         L = _lib.lib()
         xyz_c, t_c, saved, *weights = ctx.saved_tensors
         cfg = ctx.cfg
@@ -221,8 +228,13 @@ class _KeypointMLP(torch.autograd.Function):
         wp = (ctypes.c_void_p * n)(*[w.data_ptr() for w in weights])
         gwp = (ctypes.c_void_p * n)(*[g.data_ptr() for g in gw])
         gbp = (ctypes.c_void_p * n)(*[g.data_ptr() for g in gb])
-        check(L.gp_kpmlp_backward(ctypes.byref(cfg), ptr(xyz_c), ptr(t_c), wp, ptr(saved), ptr(_c(g_out)), ptr(scratch),
-                                  ptr(g_xyz), ptr(g_feat), gwp, gbp, _lib.stream_ptr()), "gp_kpmlp_backward")
+        # contiguous copies (if any) must stay referenced until the launch: a temporary freed right after taking its
+        # address could be handed to the next allocation and overwritten before the kernel reads it
+        g_in = [None if g is None else _c(g) for g in (g_dxyz, g_dq, g_do)]
+        check(L.gp_kpmlp_backward(ctypes.byref(cfg), ptr(xyz_c), ptr(t_c), wp, ptr(saved), ptr(g_in[0]), ptr(g_in[1]),
+                                  ptr(g_in[2]), ptr(scratch), ptr(g_xyz), ptr(g_feat), gwp, gbp, _lib.stream_ptr()),
+              "gp_kpmlp_backward")
+        del g_in
         return (None, g_xyz, g_feat, None) + tuple(gw) + tuple(gb)
 
 
@@ -234,17 +246,19 @@ def keypoint_mlp_supported(df_model, feature_dim, xyz_freq, time_freq):
     din = feature_dim + 6 * xyz_freq + 2 * time_freq
     w = lin[0].out_features
     ok = din % 4 == 0 and 4 <= din <= 256 and w % 4 == 0 and 4 <= w <= 256 and 2 <= len(lin) <= 9
-    ok = ok and lin[0].in_features == din and lin[-1].out_features <= 8 and lin[-1].in_features == w
+    ok = ok and lin[0].in_features == din and lin[-1].out_features in (7, 8) and lin[-1].in_features == w
     ok = ok and all(l.in_features == w and l.out_features == w for l in lin[1:-1])
     return ok and all(l.bias is not None and l.weight.is_cuda and l.weight.dtype == torch.float32 for l in lin)
 
 
-def keypoint_mlp(df_model, kp_xyz, kp_feat, t, xyz_freq, time_freq):
-    """``df_model(cat([kp_feat, PE(kp_xyz), PE(t).repeat]))`` (scene/gaussian_model.py:180-189 at the keypoint call
-    site) through the fused kernels.  ``t``: tensor with one element."""
+def keypoint_mlp(df_model, kp_xyz, kp_feat, t, xyz_freq, time_freq, normalize_q=False):
+    """``get_motion_delta(PE(kp_xyz), kp_feat, PE(t))`` (scene/gaussian_model.py:180-189 at the keypoint call site)
+    through the fused kernels: returns (delta_xyz [Kp,3], delta_q [Kp,4], delta_o [Kp,1] or None); with
+    ``normalize_q`` delta_q is already ``rotation_activation(delta_q)`` (:266-267).  ``t``: tensor with one element."""
     lin = df_model.linears()
-    dims = (int(xyz_freq), int(time_freq), len(lin) - 1, lin[0].out_features, lin[-1].out_features)
-    return _KeypointMLP.apply(dims, kp_xyz, kp_feat, t, *[l.weight for l in lin], *[l.bias for l in lin])
+    dims = (int(xyz_freq), int(time_freq), len(lin) - 1, lin[0].out_features, lin[-1].out_features, bool(normalize_q))
+    out = _KeypointMLP.apply(dims, kp_xyz, kp_feat, t, *[l.weight for l in lin], *[l.bias for l in lin])
+    return out if len(out) == 3 else (out[0], out[1], None)
 
 
 @torch.no_grad()
@@ -254,7 +268,8 @@ def dense_weights(logits, idx32, Kp, want_sum=False):
     f = dict(dtype=torch.float32, device=logits.device)
     wx, wr = torch.empty((N, Kp), **f), torch.empty((N, Kp), **f)
     ws = torch.empty((N, Kp), **f) if want_sum else None
-    check(_lib.lib().gp_blend_dense_weights(N, Kp, K, ptr(_c(logits)), ptr(idx32), None, ptr(wx), ptr(wr), ptr(ws),
+    logits_c = _c(logits)
+    check(_lib.lib().gp_blend_dense_weights(N, Kp, K, ptr(logits_c), ptr(idx32), None, ptr(wx), ptr(wr), ptr(ws),
                                             _lib.stream_ptr()), "gp_blend_dense_weights")
     return (wx, wr, ws) if want_sum else (wx, wr)
 
@@ -392,14 +407,14 @@ class KeypointDeformation(nn.Module):
             xf, tf = int(self.xyz_input_dim / 6), self.time_input_dim // 2
             if self.fused_mlp and self.super_gaussians.is_cuda and \
                     keypoint_mlp_supported(self.df_model, args.feature_dim, xf, tf):
-                delta = keypoint_mlp(self.df_model, self.super_gaussians + noise, self.super_gaussians_feature, t_input,
-                                     xf, tf)
-                delta_xyz, delta_q = delta[..., 0:3], delta[..., 3:7]
+                delta_xyz, delta_q, _ = keypoint_mlp(self.df_model, self.super_gaussians + noise,
+                                                     self.super_gaussians_feature, t_input, xf, tf,
+                                                     normalize_q=args.norm_rotation)
             else:
                 xyz_embed = positional_encoding(self.super_gaussians + noise, xf)
                 delta_xyz, delta_q, _ = self.get_motion_delta(xyz_embed, self.super_gaussians_feature, t_embed())
-            if args.norm_rotation:
-                delta_q = normalize(delta_q)
+                if args.norm_rotation:
+                    delta_q = normalize(delta_q)
             # detached: the readers (motion_model/dataset.py:120-123) only take values, and a live reference would keep
             # this frame's autograd graph (and its stream-bound AccumulateGrad nodes) alive across iterations
             self.kpts_xyz_motion, self.kpts_rotation_motion = delta_xyz.detach(), delta_q.detach()

@@ -156,10 +156,11 @@ def raster_backward(st, grad_out_color, means3D, sh, colors_precomp, scales, rot
     ws = torch.empty((L.gp_raster_backward_ws_bytes(P),), dtype=torch.uint8, device=dev)
     bg = _f32c(raster_settings.bg)
     view, proj, campos = _f32c(raster_settings.viewmatrix), _f32c(raster_settings.projmatrix), _f32c(raster_settings.campos)
-    check(L.gp_raster_backward(ctypes.byref(st.cfg), ptr(bg), ptr(_f32c(means3D)), ptr(sh), ptr(colors_precomp),
+    means3D, grad_out_color = _f32c(means3D), _f32c(grad_out_color)   # named: copies must outlive the launch
+    check(L.gp_raster_backward(ctypes.byref(st.cfg), ptr(bg), ptr(means3D), ptr(sh), ptr(colors_precomp),
                                ptr(scales), ptr(rotations), ptr(cov3Ds_precomp), ptr(view), ptr(proj), ptr(campos),
                                ptr(st.radii), ptr(st.geom), ptr(st.binning), st.capacity, ptr(st.image),
-                               ptr(_f32c(grad_out_color)), ptr(ws), ptr(g_means2D), ptr(g_colors), ptr(g_opacity),
+                               ptr(grad_out_color), ptr(ws), ptr(g_means2D), ptr(g_colors), ptr(g_opacity),
                                ptr(g_means3D), ptr(g_cov3D), ptr(g_sh), ptr(g_scales), ptr(g_rots),
                                _lib.stream_ptr()), "gp_raster_backward")
     return g_means2D, g_colors, g_opacity, g_means3D, g_cov3D, g_sh, g_scales, g_rots
@@ -199,7 +200,8 @@ def mark_visible(positions, viewmatrix, projmatrix):
     P = int(positions.shape[0])
     out = torch.zeros((P,), dtype=torch.uint8, device=positions.device)
     if P:
-        check(_lib.lib().gp_mark_visible(P, ptr(_f32c(positions)), ptr(_f32c(viewmatrix)), ptr(_f32c(projmatrix)),
+        positions, viewmatrix, projmatrix = _f32c(positions), _f32c(viewmatrix), _f32c(projmatrix)
+        check(_lib.lib().gp_mark_visible(P, ptr(positions), ptr(viewmatrix), ptr(projmatrix),
                                          ptr(out), _lib.stream_ptr()), "gp_mark_visible")
     return out.bool()
 

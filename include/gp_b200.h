@@ -227,7 +227,7 @@ int gp_image_loss_backward(int C, int H, int W, const float* img, const float* g
  * autograd backward, at the keypoint call site (:255-265).  Input row = [feature(F) | PE(xyz)(6*xyz_freq) |
  * PE(t)(2*time_freq)].  weights[l] / biases[l], l = 0..depth: device pointers in nn.Linear layout ([out][in] row-major);
  * the arrays of pointers themselves live on the host.  Limits (GP_ERR_LIMIT otherwise): width and input row length
- * multiples of 4 and <= 256, depth <= 8, out_dim <= 8.
+ * multiples of 4 and <= 256, depth <= 8, out_dim 7 or 8.
  * ---------------------------------------------------------------------------------------------- */
 typedef struct gp_mlp_cfg {
   int rows;        /* number of keypoints */
@@ -236,18 +236,22 @@ typedef struct gp_mlp_cfg {
   int time_freq;   /* frequencies of the time encoding (0: no such columns) */
   int depth;       /* hidden Linear+ReLU layers */
   int width;       /* hidden width */
-  int out_dim;     /* columns of the last Linear (7; 8 with step opacity) */
+  int out_dim;     /* columns of the last Linear: 7 = (delta_xyz, delta_q); 8 with step opacity (+ delta_o) */
+  int normalize_q; /* 1: delta_q = normalize(delta_q) as with --norm_rotation (scene/gaussian_model.py:266-267) */
 } gp_mlp_cfg;
 
 /* saved: activations the backward needs (forward writes, backward reads); bwd_scratch holds no state between calls */
 int gp_kpmlp_sizes(const gp_mlp_cfg* cfg, size_t* saved_bytes, size_t* bwd_scratch_bytes);
-/* out[rows, out_dim] = MLP(input rows).  t: device scalar. */
+/* (delta_xyz [rows,3], delta_q [rows,4], delta_o [rows,1] or NULL) = the three tensors get_motion_delta returns
+ * (scene/gaussian_model.py:189), as separate contiguous arrays.  t: device scalar. */
 int gp_kpmlp_forward(const gp_mlp_cfg* cfg, const float* kp_xyz /*[rows,3]*/, const float* kp_feat /*[rows,F]*/,
-                     const float* t, const float* const* weights, const float* const* biases, void* saved, float* out,
-                     gp_stream_t stream);
-/* Every requested gradient is fully written (no accumulation).  dL_dxyz / dL_dfeat may be NULL. */
+                     const float* t, const float* const* weights, const float* const* biases, void* saved,
+                     float* delta_xyz, float* delta_q, float* delta_o, gp_stream_t stream);
+/* Every requested gradient is fully written (no accumulation).  dL_dxyz / dL_dfeat may be NULL; a NULL incoming
+ * gradient (dL_ddelta_*) counts as zeros. */
 int gp_kpmlp_backward(const gp_mlp_cfg* cfg, const float* kp_xyz, const float* t, const float* const* weights,
-                      const void* saved, const float* dL_dout /*[rows,out_dim]*/, void* bwd_scratch,
+                      const void* saved, const float* dL_ddelta_xyz, const float* dL_ddelta_q,
+                      const float* dL_ddelta_o, void* bwd_scratch,
                       float* dL_dxyz /*[rows,3]*/, float* dL_dfeat /*[rows,F]*/, float* const* dL_dweights,
                       float* const* dL_dbiases, gp_stream_t stream);
 

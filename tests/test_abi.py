@@ -82,11 +82,11 @@ def test_dropin_import_names():
 def test_keypoint_mlp_limits_without_gpu(gplib):
     from gaussianprediction_b200._lib import MlpCfg
     sv, bs = ctypes.c_size_t(), ctypes.c_size_t()
-    ok = MlpCfg(512, 32, 10, 6, 4, 256, 7)
+    ok = MlpCfg(512, 32, 10, 6, 4, 256, 7, 1)
     assert gplib.gp_kpmlp_sizes(ctypes.byref(ok), ctypes.byref(sv), ctypes.byref(bs)) == 0
-    assert sv.value >= 512 * (104 + 4 * 256) * 4 and bs.value >= 512 * 4 * 256 * 4
-    for bad in (MlpCfg(512, 32, 10, 6, 4, 260, 7), MlpCfg(512, 30, 10, 6, 4, 256, 7), MlpCfg(512, 32, 10, 6, 9, 256, 7),
-                MlpCfg(512, 32, 10, 6, 4, 256, 9)):
+    assert sv.value >= 512 * (104 + 4 * 256 + 8) * 4 and bs.value >= 512 * (4 * 256 + 8) * 4
+    for bad in (MlpCfg(512, 32, 10, 6, 4, 260, 7, 0), MlpCfg(512, 30, 10, 6, 4, 256, 7, 0), MlpCfg(512, 32, 10, 6, 9, 256, 7, 0),
+                MlpCfg(512, 32, 10, 6, 4, 256, 9, 0), MlpCfg(512, 32, 10, 6, 4, 256, 3, 0)):
         assert gplib.gp_kpmlp_sizes(ctypes.byref(bad), None, None) == -4
     assert gplib.gp_kpmlp_sizes(None, None, None) == -1
-    assert gplib.gp_kpmlp_forward(ctypes.byref(ok), *([None] * 8)) == -1
+    assert gplib.gp_kpmlp_forward(ctypes.byref(ok), *([None] * 10)) == -1

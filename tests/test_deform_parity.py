@@ -249,12 +249,13 @@ def _torch_motion_delta(net, kp, kf, t, xf, tf):
     return net(torch.cat(cols, dim=-1))
 
 
-@pytest.mark.parametrize("Kp,F,xf,tf,d,w,out", [(512, 32, 10, 6, 4, 256, 7), (515, 32, 10, 6, 4, 256, 8),
-                                                (1, 32, 10, 6, 4, 256, 7), (37, 8, 4, 2, 2, 64, 7),
-                                                (130, 16, 0, 0, 1, 32, 3), (64, 0, 10, 6, 8, 128, 7)])
-def test_keypoint_mlp_vs_torch_modules(gplib, Kp, F, xf, tf, d, w, out):
-    """gp_kpmlp_forward/backward against the torch fp32 modules they replace (PE + cat + Linear/ReLU stack + autograd).
-    Tolerances: values 1e-5 of the output scale, gradients 1e-4 relative (fp32 sums in a different order than cuBLAS)."""
+@pytest.mark.parametrize("Kp,F,xf,tf,d,w,out,norm", [(512, 32, 10, 6, 4, 256, 7, True), (515, 32, 10, 6, 4, 256, 8, False),
+                                                     (1, 32, 10, 6, 4, 256, 7, True), (37, 8, 4, 2, 2, 64, 7, True),
+                                                     (130, 16, 0, 0, 1, 32, 8, True), (64, 0, 10, 6, 8, 128, 7, False)])
+def test_keypoint_mlp_vs_torch_modules(gplib, Kp, F, xf, tf, d, w, out, norm):
+    """gp_kpmlp_forward/backward against the torch fp32 modules they replace (PE + cat + Linear/ReLU stack +
+    F.normalize + autograd).  Tolerances: values 1e-5 of the output scale, gradients 1e-4 relative (fp32 sums in a
+    different order than cuBLAS)."""
     from gaussianprediction_b200.deform import DeformableField, keypoint_mlp, keypoint_mlp_supported
     dev = "cuda"
     torch.manual_seed(Kp + w)
@@ -266,30 +267,45 @@ def test_keypoint_mlp_vs_torch_modules(gplib, Kp, F, xf, tf, d, w, out):
     t = torch.tensor([0.37], device=dev)
     gout = torch.randn(Kp, out, generator=g).to(dev)
     y_ref = _torch_motion_delta(net, kp, kf, t, xf, tf)
+    if norm:
+        y_ref = torch.cat([y_ref[:, :3], torch.nn.functional.normalize(y_ref[:, 3:7]), y_ref[:, 7:]], dim=1)
     y_ref.backward(gout)
     ref = {n: p.grad.clone() for n, p in net.named_parameters()}
     ref["kp"], ref["kf"] = (kp.grad.clone() if xf else None), (kf.grad.clone() if F else None)
-    for p in list(net.parameters()) + [kp, kf]:
-        p.grad = None
-    y = keypoint_mlp(net, kp, kf, t, xf, tf)
-    assert y.shape == (Kp, out)
+
+    def run():
+        for p in list(net.parameters()) + [kp, kf]:
+            p.grad = None
+        parts = keypoint_mlp(net, kp, kf, t, xf, tf, normalize_q=norm)
+        assert parts[0].shape == (Kp, 3) and parts[1].shape == (Kp, 4) and (parts[2] is None) == (out == 7)
+        assert all(p.is_contiguous() for p in parts if p is not None)
+        y = torch.cat([p for p in parts if p is not None], dim=1)
+        y.backward(gout)
+        return y.detach(), [p.grad.clone() for p in net.parameters()]
+    y, grads = run()
     assert float((y - y_ref).abs().max()) <= 1e-5 * max(1.0, float(y_ref.abs().max()))
-    y.backward(gout)
-    for n, p in net.named_parameters():
-        assert rel_err(p.grad, ref[n]) <= 1e-4, n
+    for (n, _), gr in zip(net.named_parameters(), grads):
+        assert rel_err(gr, ref[n]) <= 1e-4, n
     if xf:
         assert rel_err(kp.grad, ref["kp"]) <= 1e-4
     else:
         assert float(kp.grad.abs().max()) == 0
     if F:
         assert rel_err(kf.grad, ref["kf"]) <= 1e-4
-    # bit-reproducible: fixed summation order, no atomics
-    first = [p.grad.clone() for p in net.parameters()]
+    # an unused output (no incoming gradient for delta_xyz) counts as zeros
     for p in list(net.parameters()) + [kp, kf]:
         p.grad = None
-    y2 = keypoint_mlp(net, kp, kf, t, xf, tf)
-    y2.backward(gout)
-    assert count_diff(y, y2) == 0 and all(count_diff(a, p.grad) == 0 for a, p in zip(first, net.parameters()))
+    keypoint_mlp(net, kp, kf, t, xf, tf, normalize_q=norm)[1].backward(gout[:, 3:7])
+    part = [p.grad.clone() for p in net.parameters()]
+    for p in list(net.parameters()) + [kp, kf]:
+        p.grad = None
+    y_ref2 = _torch_motion_delta(net, kp, kf, t, xf, tf)[:, 3:7]
+    (torch.nn.functional.normalize(y_ref2) if norm else y_ref2).backward(gout[:, 3:7])
+    for a, p in zip(part, net.parameters()):
+        assert rel_err(a, p.grad) <= 1e-4
+    # bit-reproducible: fixed summation order, no atomics
+    y2, grads2 = run()
+    assert count_diff(y, y2) == 0 and all(count_diff(a, b) == 0 for a, b in zip(grads, grads2))
 
 
 def test_keypoint_mlp_golden_and_limits(gplib):
@@ -301,7 +317,8 @@ def test_keypoint_mlp_golden_and_limits(gplib):
     net.load_state_dict({k[3:]: torch.from_numpy(z[k]) for k in z.files if k.startswith("sd_")})
     net = net.cuda()
     x = torch.from_numpy(z["x"]).cuda()
-    y = keypoint_mlp(net, torch.zeros(x.shape[0], 3, device="cuda"), x, torch.zeros(1, device="cuda"), 0, 0)
+    parts = keypoint_mlp(net, torch.zeros(x.shape[0], 3, device="cuda"), x, torch.zeros(1, device="cuda"), 0, 0)
+    y = torch.cat(parts[:2], dim=1)
     assert float((y.cpu() - torch.from_numpy(z["y"])).abs().max()) <= 1e-5
     # the encoding columns: PE(pos) / PE(t) of the golden file pass through a 1-layer identity-like probe
     pos, tt = torch.from_numpy(z["pos"]).cuda(), torch.from_numpy(z["t"]).cuda()
@@ -312,12 +329,13 @@ def test_keypoint_mlp_golden_and_limits(gplib):
         sel = [0, 1, 19, 20, 59, 60, 61, 71]
         for j, c in enumerate(sel):
             probe.feature_to_deformation[0].weight[j, c] = 1.0
-    yp = keypoint_mlp(probe, pos, torch.zeros(pos.shape[0], 0, device="cuda"), tt, 10, 6).cpu() - 2.0
+    yp = torch.cat(keypoint_mlp(probe, pos, torch.zeros(pos.shape[0], 0, device="cuda"), tt, 10, 6), dim=1).cpu() - 2.0
     want = torch.cat([torch.from_numpy(z["pe_xyz"]), torch.from_numpy(z["pe_t"]).reshape(1, -1).repeat(pos.shape[0], 1)], 1)[:, sel]
     assert float((yp - want).abs().max()) <= 1e-6
     # shapes outside the kernel's limits are refused by the C ABI and routed to the torch modules by the model
     assert not keypoint_mlp_supported(DeformableField(104, 7, 4, 260).cuda(), 32, 10, 6)
     assert not keypoint_mlp_supported(DeformableField(102, 7, 4, 64).cuda(), 30, 10, 6)
+    assert not keypoint_mlp_supported(DeformableField(104, 3, 4, 64).cuda(), 32, 10, 6)
 
 
 def test_model_fused_mlp_equals_torch_mlp(gplib):

@@ -12,7 +12,7 @@ for Kp in (64, 128, 256, 512, 1024, 2048):
     g = torch.randn(Kp, 7, device=dev)
     def body():
         for p in list(net.parameters()) + [kp, kf]: p.grad = None
-        keypoint_mlp(net, kp, kf, t, 10, 6).backward(g)
+        torch.autograd.backward(keypoint_mlp(net, kp, kf, t, 10, 6, normalize_q=True)[:2], [g[:, :3].contiguous(), g[:, 3:].contiguous()])
     for _ in range(3): body()
     torch.cuda.synchronize()
     L.gp_profile_enable(1)

@@ -35,8 +35,7 @@ from gaussianprediction_b200.deform import keypoint_mlp
 def body_fused():
     for p in params: p.grad = None
     noise = torch.randn_like(kp) * 0.0
-    d = keypoint_mlp(net, kp + noise, kf, t, 10, 6)
-    dx, dq = d[..., 0:3], torch.nn.functional.normalize(d[..., 3:7])
+    dx, dq, _ = keypoint_mlp(net, kp + noise, kf, t, 10, 6, normalize_q=True)
     torch.autograd.backward([dx, dq], [g_dx, g_dq])
 s.wait_stream(torch.cuda.current_stream())
 with torch.cuda.stream(s):
