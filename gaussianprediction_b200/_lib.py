@@ -20,6 +20,7 @@ class RasterCfg(ctypes.Structure):
     _fields_ = [
         ("P", c_int), ("width", c_int), ("height", c_int), ("sh_degree", c_int), ("sh_coeffs", c_int),
         ("tanfovx", c_float), ("tanfovy", c_float), ("scale_modifier", c_float), ("prefiltered", c_int),
+        ("sh_rest", c_void_p), ("dL_dsh_rest", c_void_p),
     ]
 
 

@@ -248,24 +248,23 @@ __device__ __forceinline__ V3 dnormvdv3(const V3& v, const V3& dv) {
 
 // SH backward (reference backward.cu:20-139): writes dL/dsh for the active degree and returns the
 // view-direction part of dL/dmean.
-__device__ __forceinline__ V3 sh_backward(int deg, int M, const V3& pos, const V3& campos,
-                                          const float* shp, unsigned clamp_bits, V3 dL_dRGB, float* dL_dshp) {
+template <bool SPLIT>
+__device__ __forceinline__ V3 sh_backward(int deg, int M, const V3& pos, const V3& campos, const GpShRow<SPLIT> sh,
+                                          unsigned clamp_bits, V3 dL_dRGB, const GpShRowOut<SPLIT> dL_dsh) {
   const V3 dir_orig = pos - campos;
   const V3 dir = dir_orig / len3(dir_orig);
-  const V3* sh = (const V3*)shp;
-  V3* dL_dsh = (V3*)dL_dshp;
   dL_dRGB.x *= (clamp_bits & 1u) ? 0.f : 1.f;
   dL_dRGB.y *= (clamp_bits & 2u) ? 0.f : 1.f;
   dL_dRGB.z *= (clamp_bits & 4u) ? 0.f : 1.f;
   V3 dRGBdx = v3(0, 0, 0), dRGBdy = v3(0, 0, 0), dRGBdz = v3(0, 0, 0);
   const float x = dir.x, y = dir.y, z = dir.z;
 
-  dL_dsh[0] = GP_SH_C0 * dL_dRGB;
+  dL_dsh.set(0, GP_SH_C0 * dL_dRGB);
   int written = 1;
   if (deg > 0) {
-    dL_dsh[1] = (-GP_SH_C1 * y) * dL_dRGB;
-    dL_dsh[2] = (GP_SH_C1 * z) * dL_dRGB;
-    dL_dsh[3] = (-GP_SH_C1 * x) * dL_dRGB;
+    dL_dsh.set(1, (-GP_SH_C1 * y) * dL_dRGB);
+    dL_dsh.set(2, (GP_SH_C1 * z) * dL_dRGB);
+    dL_dsh.set(3, (-GP_SH_C1 * x) * dL_dRGB);
     written = 4;
     dRGBdx = -GP_SH_C1 * sh[3];
     dRGBdy = -GP_SH_C1 * sh[1];
@@ -273,11 +272,11 @@ __device__ __forceinline__ V3 sh_backward(int deg, int M, const V3& pos, const V
     if (deg > 1) {
       const float xx = x * x, yy = y * y, zz = z * z;
       const float xy = x * y, yz = y * z, xz = x * z;
-      dL_dsh[4] = (GP_SH_C2[0] * xy) * dL_dRGB;
-      dL_dsh[5] = (GP_SH_C2[1] * yz) * dL_dRGB;
-      dL_dsh[6] = (GP_SH_C2[2] * (2.f * zz - xx - yy)) * dL_dRGB;
-      dL_dsh[7] = (GP_SH_C2[3] * xz) * dL_dRGB;
-      dL_dsh[8] = (GP_SH_C2[4] * (xx - yy)) * dL_dRGB;
+      dL_dsh.set(4, (GP_SH_C2[0] * xy) * dL_dRGB);
+      dL_dsh.set(5, (GP_SH_C2[1] * yz) * dL_dRGB);
+      dL_dsh.set(6, (GP_SH_C2[2] * (2.f * zz - xx - yy)) * dL_dRGB);
+      dL_dsh.set(7, (GP_SH_C2[3] * xz) * dL_dRGB);
+      dL_dsh.set(8, (GP_SH_C2[4] * (xx - yy)) * dL_dRGB);
       written = 9;
       dRGBdx += GP_SH_C2[0] * y * sh[4] + GP_SH_C2[2] * 2.f * -x * sh[6] + GP_SH_C2[3] * z * sh[7] +
                 GP_SH_C2[4] * 2.f * x * sh[8];
@@ -285,13 +284,13 @@ __device__ __forceinline__ V3 sh_backward(int deg, int M, const V3& pos, const V
                 GP_SH_C2[4] * 2.f * -y * sh[8];
       dRGBdz += GP_SH_C2[1] * y * sh[5] + GP_SH_C2[2] * 2.f * 2.f * z * sh[6] + GP_SH_C2[3] * x * sh[7];
       if (deg > 2) {
-        dL_dsh[9] = (GP_SH_C3[0] * y * (3.f * xx - yy)) * dL_dRGB;
-        dL_dsh[10] = (GP_SH_C3[1] * xy * z) * dL_dRGB;
-        dL_dsh[11] = (GP_SH_C3[2] * y * (4.f * zz - xx - yy)) * dL_dRGB;
-        dL_dsh[12] = (GP_SH_C3[3] * z * (2.f * zz - 3.f * xx - 3.f * yy)) * dL_dRGB;
-        dL_dsh[13] = (GP_SH_C3[4] * x * (4.f * zz - xx - yy)) * dL_dRGB;
-        dL_dsh[14] = (GP_SH_C3[5] * z * (xx - yy)) * dL_dRGB;
-        dL_dsh[15] = (GP_SH_C3[6] * x * (xx - 3.f * yy)) * dL_dRGB;
+        dL_dsh.set(9, (GP_SH_C3[0] * y * (3.f * xx - yy)) * dL_dRGB);
+        dL_dsh.set(10, (GP_SH_C3[1] * xy * z) * dL_dRGB);
+        dL_dsh.set(11, (GP_SH_C3[2] * y * (4.f * zz - xx - yy)) * dL_dRGB);
+        dL_dsh.set(12, (GP_SH_C3[3] * z * (2.f * zz - 3.f * xx - 3.f * yy)) * dL_dRGB);
+        dL_dsh.set(13, (GP_SH_C3[4] * x * (4.f * zz - xx - yy)) * dL_dRGB);
+        dL_dsh.set(14, (GP_SH_C3[5] * z * (xx - yy)) * dL_dRGB);
+        dL_dsh.set(15, (GP_SH_C3[6] * x * (xx - 3.f * yy)) * dL_dRGB);
         written = 16;
         dRGBdx += (GP_SH_C3[0] * sh[9] * 3.f * 2.f * xy + GP_SH_C3[1] * sh[10] * yz + GP_SH_C3[2] * sh[11] * -2.f * xy +
                    GP_SH_C3[3] * sh[12] * -3.f * 2.f * xz + GP_SH_C3[4] * sh[13] * (-3.f * xx + 4.f * zz - yy) +
@@ -306,25 +305,25 @@ __device__ __forceinline__ V3 sh_backward(int deg, int M, const V3& pos, const V
       }
     }
   }
-  for (int k = written; k < M; k++) dL_dsh[k] = v3(0.f, 0.f, 0.f);  // coefficients above the active degree
+  for (int k = written; k < M; k++) dL_dsh.set(k, v3(0.f, 0.f, 0.f));  // coefficients above the active degree
   const V3 dL_ddir = v3(dot3(dRGBdx, dL_dRGB), dot3(dRGBdy, dL_dRGB), dot3(dRGBdz, dL_dRGB));
   return dnormvdv3(dir_orig, dL_ddir);
 }
 
-#define GP_SH_ROW 52  // floats per staged SH row in shared memory: 48 + 4 pad (16-byte aligned rows, conflict-free LDS.128)
 
-// Per-Gaussian part of the backward.  sh_row / dsh_row point at this Gaussian's 3*M SH coefficients and at where
-// their gradients go (global memory, or the warp's staging tile in shared memory).
+// Per-Gaussian part of the backward.  sh_row / dsh_row: this Gaussian's 3*M SH coefficients and where their
+// gradients go (global memory, or the warp's staging tile in shared memory).
+template <bool SPLIT>
 __device__ __forceinline__ void
 gp_preprocess_bwd_body(int idx, int D, int M, const float* __restrict__ means3D, const int* __restrict__ radii,
-                       const float* sh_row, const uint8_t* __restrict__ clamped,
+                       const GpShRow<SPLIT> sh_row, const uint8_t* __restrict__ clamped,
                        const float* __restrict__ scales, const float* __restrict__ rotations, float scale_modifier,
                        const float* __restrict__ cov3Ds, const float* __restrict__ view,
                        const float* __restrict__ proj, float h_x, float h_y, float tan_fovx, float tan_fovy,
                        const float* __restrict__ campos, const float* __restrict__ grec,
                        float* __restrict__ dL_dmean2D_out, float* __restrict__ dL_dcolors_out,
                        float* __restrict__ dL_dopacity_out, float* __restrict__ dL_dmeans_out,
-                       float* __restrict__ dL_dcov3D_out, float* dsh_row,
+                       float* __restrict__ dL_dcov3D_out, const GpShRowOut<SPLIT> dsh_row,
                        float* __restrict__ dL_dscale_out, float* __restrict__ dL_drot_out) {
   const bool visible = radii[idx] > 0;
 
@@ -358,8 +357,8 @@ gp_preprocess_bwd_body(int idx, int D, int M, const float* __restrict__ means3D,
     dL_dmeans_out[3 * (size_t)idx + 2] = 0.f;
     if (dL_dcov3D_out)
       for (int k = 0; k < 6; k++) dL_dcov3D_out[6 * (size_t)idx + k] = 0.f;
-    if (dsh_row)
-      for (int k = 0; k < 3 * M; k++) dsh_row[k] = 0.f;
+    if (dsh_row.a)
+      for (int k = 0; k < M; k++) dsh_row.set(k, v3(0.f, 0.f, 0.f));
     if (dL_dscale_out) {
       for (int k = 0; k < 3; k++) dL_dscale_out[3 * (size_t)idx + k] = 0.f;
       for (int k = 0; k < 4; k++) dL_drot_out[4 * (size_t)idx + k] = 0.f;
@@ -449,8 +448,8 @@ gp_preprocess_bwd_body(int idx, int D, int M, const float* __restrict__ means3D,
   }
 
   // ---- SH backward ----
-  if (sh_row) {
-    const V3 dm = sh_backward(D, M, mean, v3(campos[0], campos[1], campos[2]), sh_row, clamped[idx],
+  if (sh_row.a) {
+    const V3 dm = sh_backward<SPLIT>(D, M, mean, v3(campos[0], campos[1], campos[2]), sh_row, clamped[idx],
                               v3(rec[6], rec[7], rec[8]), dsh_row);
     dL_dmean += dm;
   }
@@ -508,9 +507,11 @@ gp_preprocess_bwd_body(int idx, int D, int M, const float* __restrict__ means3D,
 // thread-per-row they cost one 32-byte sector per lane per instruction.  Each warp therefore moves the 6 KB of its
 // 32 consecutive Gaussians with fully coalesced 128-bit accesses through a shared-memory tile (rows padded to 52
 // floats so that the per-lane row reads are conflict-free).
+template <bool SPLIT>
 __global__ void __launch_bounds__(256)
 gp_preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, const int* __restrict__ radii,
-                         const float* __restrict__ shs, const uint8_t* __restrict__ clamped,
+                         const float* __restrict__ shs, const float* __restrict__ shs_rest,
+                         const uint8_t* __restrict__ clamped,
                          const float* __restrict__ scales, const float* __restrict__ rotations, float scale_modifier,
                          const float* __restrict__ cov3Ds, const float* __restrict__ view,
                          const float* __restrict__ proj, float h_x, float h_y, float tan_fovx, float tan_fovy,
@@ -518,41 +519,54 @@ gp_preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
                          float* __restrict__ dL_dmean2D_out, float* __restrict__ dL_dcolors_out,
                          float* __restrict__ dL_dopacity_out, float* __restrict__ dL_dmeans_out,
                          float* __restrict__ dL_dcov3D_out, float* __restrict__ dL_dsh_out,
-                         float* __restrict__ dL_dscale_out, float* __restrict__ dL_drot_out, int staged) {
-  extern __shared__ __align__(16) float s_tiles[];  // staged: [8 warps][32][52] in, then [8 warps][32][52] out
+                         float* __restrict__ dL_dsh_rest_out, float* __restrict__ dL_dscale_out,
+                         float* __restrict__ dL_drot_out, int staged) {
+  extern __shared__ __align__(16) float s_tiles[];  // staged: [8 warps][GP_SH_TILE] in, then [8 warps][GP_SH_TILE] out
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int warp_base = idx - lane;
-  const float* sh_row = shs ? shs + (size_t)idx * M * 3 : nullptr;
-  float* dsh_row = dL_dsh_out ? dL_dsh_out + (size_t)idx * M * 3 : nullptr;
-  float* tin = s_tiles + (size_t)w * 32 * GP_SH_ROW;
-  float* tout = s_tiles + (size_t)(8 + w) * 32 * GP_SH_ROW;
-  if (staged) {
-    const float4* src = (const float4*)(shs + (size_t)warp_base * 48);
-    const int rows = min(32, P - warp_base);
+  const int rows = min(32, P - warp_base);
+  GpShRow<SPLIT> sh_row{shs ? shs + (size_t)idx * M * 3 : nullptr, nullptr};
+  GpShRowOut<SPLIT> dsh_row{dL_dsh_out ? dL_dsh_out + (size_t)idx * M * 3 : nullptr, nullptr};
+  float* tin = s_tiles + (size_t)w * GP_SH_TILE;
+  float* tout = s_tiles + (size_t)(8 + w) * GP_SH_TILE;
+  if (staged && rows > 0) {
+    if (SPLIT) {  // two arrays in, two arrays out (raster_common.cuh)
+      gp_warp_copy_in(tin, shs + (size_t)warp_base * 3, rows * 3, lane);
+      gp_warp_copy_in(tin + GP_SH_SPLIT_REST, shs_rest + (size_t)warp_base * 45, rows * 45, lane);
+      sh_row = GpShRow<SPLIT>{tin + lane * 3, tin + GP_SH_SPLIT_REST + lane * 45};
+      dsh_row = GpShRowOut<SPLIT>{tout + lane * 3, tout + GP_SH_SPLIT_REST + lane * 45};
+    } else {
+      const float4* src = (const float4*)(shs + (size_t)warp_base * 48);
 #pragma unroll
-    for (int it = 0; it < 12; it++) {
-      const int i4 = it * 32 + lane;
-      const int row = i4 / 12, c4 = i4 - row * 12;
-      if (row < rows) *(float4*)(tin + row * GP_SH_ROW + 4 * c4) = __ldg(src + i4);
+      for (int it = 0; it < 12; it++) {
+        const int i4 = it * 32 + lane;
+        const int row = i4 / 12, c4 = i4 - row * 12;
+        if (row < rows) *(float4*)(tin + row * GP_SH_ROW + 4 * c4) = __ldg(src + i4);
+      }
+      sh_row = GpShRow<SPLIT>{tin + lane * GP_SH_ROW, nullptr};
+      dsh_row = GpShRowOut<SPLIT>{tout + lane * GP_SH_ROW, nullptr};
     }
     __syncwarp();
-    sh_row = tin + lane * GP_SH_ROW;
-    dsh_row = tout + lane * GP_SH_ROW;
   }
   if (idx < P)
-    gp_preprocess_bwd_body(idx, D, M, means3D, radii, sh_row, clamped, scales, rotations, scale_modifier, cov3Ds, view,
-                           proj, h_x, h_y, tan_fovx, tan_fovy, campos, grec, dL_dmean2D_out, dL_dcolors_out,
-                           dL_dopacity_out, dL_dmeans_out, dL_dcov3D_out, dsh_row, dL_dscale_out, dL_drot_out);
-  if (staged) {
+    gp_preprocess_bwd_body<SPLIT>(idx, D, M, means3D, radii, sh_row, clamped, scales, rotations, scale_modifier, cov3Ds,
+                                  view, proj, h_x, h_y, tan_fovx, tan_fovy, campos, grec, dL_dmean2D_out,
+                                  dL_dcolors_out, dL_dopacity_out, dL_dmeans_out, dL_dcov3D_out, dsh_row, dL_dscale_out,
+                                  dL_drot_out);
+  if (staged && rows > 0) {
     __syncwarp();
-    float4* dst = (float4*)(dL_dsh_out + (size_t)warp_base * 48);
-    const int rows = min(32, P - warp_base);
+    if (SPLIT) {
+      gp_warp_copy_out(dL_dsh_out + (size_t)warp_base * 3, tout, rows * 3, lane);
+      gp_warp_copy_out(dL_dsh_rest_out + (size_t)warp_base * 45, tout + GP_SH_SPLIT_REST, rows * 45, lane);
+    } else {
+      float4* dst = (float4*)(dL_dsh_out + (size_t)warp_base * 48);
 #pragma unroll
-    for (int it = 0; it < 12; it++) {
-      const int i4 = it * 32 + lane;
-      const int row = i4 / 12, c4 = i4 - row * 12;
-      if (row < rows) dst[i4] = *(const float4*)(tout + row * GP_SH_ROW + 4 * c4);
+      for (int it = 0; it < 12; it++) {
+        const int i4 = it * 32 + lane;
+        const int row = i4 / 12, c4 = i4 - row * 12;
+        if (row < rows) dst[i4] = *(const float4*)(tout + row * GP_SH_ROW + 4 * c4);
+      }
     }
   }
 }
@@ -595,15 +609,18 @@ extern "C" int gp_raster_backward(const gp_raster_cfg* cfg, const float* bg, con
   GP_LAUNCH_CHECK();
   const float* cov3D_ptr = cov3D_precomp ? cov3D_precomp : g.cov3D;
   // SH rows go through shared memory when they are the standard 16 coefficients and 16-byte aligned
-  const int staged = (shs != nullptr && cfg->sh_coeffs == 16 && ((((size_t)shs) | ((size_t)dL_dsh)) & 15) == 0) ? 1 : 0;
-  const size_t pb_smem = staged ? (size_t)16 * 32 * GP_SH_ROW * sizeof(float) : 0;
+  const int staged = (shs != nullptr && cfg->sh_coeffs == 16 &&
+                      ((((size_t)shs) | ((size_t)dL_dsh) | ((size_t)cfg->sh_rest) | ((size_t)cfg->dL_dsh_rest)) & 15) == 0) ? 1 : 0;
+  if (cfg->sh_rest && (!staged || !cfg->dL_dsh_rest)) return GP_ERR_UNSUPPORTED;  // split SH storage (gp_b200.h)
+  const size_t pb_smem = staged ? (size_t)16 * GP_SH_TILE * sizeof(float) : 0;
+  auto kernel = cfg->sh_rest ? gp_preprocess_bwd_kernel<true> : gp_preprocess_bwd_kernel<false>;
   if (pb_smem > 48 * 1024)
-    GP_CUDA_TRY(cudaFuncSetAttribute(gp_preprocess_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pb_smem));
-  GP_KERNEL("gp_preprocess_bwd_kernel", stream, gp_preprocess_bwd_kernel<<<(P + 255) / 256, 256, pb_smem, stream>>>(
-      P, cfg->sh_degree, cfg->sh_coeffs, means3D, radii, shs, g.clamped, has_sr ? scales : nullptr,
+    GP_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pb_smem));
+  GP_KERNEL("gp_preprocess_bwd_kernel", stream, kernel<<<(P + 255) / 256, 256, pb_smem, stream>>>(
+      P, cfg->sh_degree, cfg->sh_coeffs, means3D, radii, shs, cfg->sh_rest, g.clamped, has_sr ? scales : nullptr,
       has_sr ? rotations : nullptr, cfg->scale_modifier, cov3D_ptr, viewmatrix, projmatrix, focal_x, focal_y,
       cfg->tanfovx, cfg->tanfovy, campos, grec, dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh,
-      dL_dscales, dL_drots, staged));
+      cfg->dL_dsh_rest, dL_dscales, dL_drots, staged));
   GP_LAUNCH_CHECK();
   return GP_OK;
 }

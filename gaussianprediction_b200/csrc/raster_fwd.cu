@@ -62,11 +62,11 @@ __device__ __forceinline__ float3 cov2d_from_cov3d(const V3& mean, float focal_x
   return float3{cov.c[0][0], cov.c[0][1], cov.c[1][1]};
 }
 
-__device__ __forceinline__ V3 sh_to_rgb(int deg, const V3& pos, const V3& campos, const float* shp,
+template <bool SPLIT>
+__device__ __forceinline__ V3 sh_to_rgb(int deg, const V3& pos, const V3& campos, const GpShRow<SPLIT> sh,
                                         unsigned& clamp_bits) {
   V3 dir = pos - campos;
   dir = dir / len3(dir);
-  const V3* sh = (const V3*)shp;
   V3 result = GP_SH_C0 * sh[0];
   if (deg > 0) {
     const float x = dir.x, y = dir.y, z = dir.z;
@@ -93,14 +93,13 @@ __device__ __forceinline__ V3 sh_to_rgb(int deg, const V3& pos, const V3& campos
   return V3{fmaxf(result.x, 0.0f), fmaxf(result.y, 0.0f), fmaxf(result.z, 0.0f)};
 }
 
-#define GP_SH_ROW 52  // floats per staged SH row in shared memory: 48 + 4 pad (16-byte aligned rows, conflict-free LDS.128)
-
-// Per-Gaussian part of the preprocess; sh_row points at this Gaussian's 3*M SH coefficients (global memory or the
+// Per-Gaussian part of the preprocess; sh_row holds this Gaussian's 3*M SH coefficients (global memory or the
 // warp's staging tile in shared memory).
+template <bool SPLIT>
 __device__ __forceinline__ void
 gp_preprocess_body(int idx, int D, int M, const float* __restrict__ means3D, const float* __restrict__ scales,
                    float scale_modifier, const float* __restrict__ rotations, const float* __restrict__ opacities,
-                   const float* sh_row, const float* __restrict__ cov3D_precomp,
+                   const GpShRow<SPLIT> sh_row, const float* __restrict__ cov3D_precomp,
                    const float* __restrict__ colors_precomp, const float* __restrict__ viewmatrix,
                    const float* __restrict__ projmatrix, const float* __restrict__ cam_pos, int W, int H,
                    float tan_fovx, float tan_fovy, float focal_x, float focal_y, int prefiltered, unsigned grid_x,
@@ -150,7 +149,7 @@ gp_preprocess_body(int idx, int D, int M, const float* __restrict__ means3D, con
       if (ntiles != 0) {
         if (colors_precomp == nullptr) {
           unsigned cb;
-          const V3 c = sh_to_rgb(D, p_orig, v3(cam_pos[0], cam_pos[1], cam_pos[2]), sh_row, cb);
+          const V3 c = sh_to_rgb<SPLIT>(D, p_orig, v3(cam_pos[0], cam_pos[1], cam_pos[2]), sh_row, cb);
           g.rgb[idx] = make_float4(c.x, c.y, c.z, 0.f);
           g.clamped[idx] = (uint8_t)cb;
         }
@@ -171,15 +170,17 @@ gp_preprocess_body(int idx, int D, int M, const float* __restrict__ means3D, con
 // Thread per Gaussian.  The 192-byte SH rows of a warp's 32 consecutive Gaussians (6 KB, the bulk of the 311 B per
 // Gaussian this kernel moves) are fetched with fully coalesced 128-bit loads into a shared-memory tile (rows padded
 // to 52 floats) and read from there, instead of one 32-byte sector per lane per load.
+template <bool SPLIT>
 __global__ void __launch_bounds__(256)
 gp_preprocess_kernel(int P, int D, int M, const float* __restrict__ means3D, const float* __restrict__ scales,
                      float scale_modifier, const float* __restrict__ rotations, const float* __restrict__ opacities,
-                     const float* __restrict__ shs, const float* __restrict__ cov3D_precomp,
-                     const float* __restrict__ colors_precomp, const float* __restrict__ viewmatrix,
-                     const float* __restrict__ projmatrix, const float* __restrict__ cam_pos, int W, int H,
-                     float tan_fovx, float tan_fovy, float focal_x, float focal_y, int prefiltered, unsigned grid_x,
-                     unsigned grid_y, GpGeom g, int* __restrict__ radii, int staged) {
-  extern __shared__ __align__(16) float s_tiles[];  // staged: [8 warps][32][52]
+                     const float* __restrict__ shs, const float* __restrict__ shs_rest,
+                     const float* __restrict__ cov3D_precomp, const float* __restrict__ colors_precomp,
+                     const float* __restrict__ viewmatrix, const float* __restrict__ projmatrix,
+                     const float* __restrict__ cam_pos, int W, int H, float tan_fovx, float tan_fovy, float focal_x,
+                     float focal_y, int prefiltered, unsigned grid_x, unsigned grid_y, GpGeom g,
+                     int* __restrict__ radii, int staged) {
+  extern __shared__ __align__(16) float s_tiles[];  // staged: [8 warps][GP_SH_TILE]
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx == 0) {
     g.hdr[GP_HDR_NUM_POINTS] = P;
@@ -189,24 +190,30 @@ gp_preprocess_kernel(int P, int D, int M, const float* __restrict__ means3D, con
   }
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int warp_base = idx - lane;
-  const float* sh_row = shs ? shs + (size_t)idx * M * 3 : nullptr;
+  GpShRow<SPLIT> sh_row{shs ? shs + (size_t)idx * M * 3 : nullptr, nullptr};
   if (staged && warp_base < P) {
-    float* tin = s_tiles + (size_t)w * 32 * GP_SH_ROW;
-    const float4* src = (const float4*)(shs + (size_t)warp_base * 48);
+    float* tin = s_tiles + (size_t)w * GP_SH_TILE;
     const int rows = min(32, P - warp_base);
+    if (SPLIT) {  // coefficient 0 and coefficients 1..15 come from two arrays (raster_common.cuh)
+      gp_warp_copy_in(tin, shs + (size_t)warp_base * 3, rows * 3, lane);
+      gp_warp_copy_in(tin + GP_SH_SPLIT_REST, shs_rest + (size_t)warp_base * 45, rows * 45, lane);
+      sh_row = GpShRow<SPLIT>{tin + lane * 3, tin + GP_SH_SPLIT_REST + lane * 45};
+    } else {
+      const float4* src = (const float4*)(shs + (size_t)warp_base * 48);
 #pragma unroll
-    for (int it = 0; it < 12; it++) {
-      const int i4 = it * 32 + lane;
-      const int row = i4 / 12, c4 = i4 - row * 12;
-      if (row < rows) *(float4*)(tin + row * GP_SH_ROW + 4 * c4) = __ldg(src + i4);
+      for (int it = 0; it < 12; it++) {
+        const int i4 = it * 32 + lane;
+        const int row = i4 / 12, c4 = i4 - row * 12;
+        if (row < rows) *(float4*)(tin + row * GP_SH_ROW + 4 * c4) = __ldg(src + i4);
+      }
+      sh_row = GpShRow<SPLIT>{tin + lane * GP_SH_ROW, nullptr};
     }
     __syncwarp();
-    sh_row = tin + lane * GP_SH_ROW;
   }
   if (idx < P)
-    gp_preprocess_body(idx, D, M, means3D, scales, scale_modifier, rotations, opacities, sh_row, cov3D_precomp,
-                       colors_precomp, viewmatrix, projmatrix, cam_pos, W, H, tan_fovx, tan_fovy, focal_x, focal_y,
-                       prefiltered, grid_x, grid_y, g, radii);
+    gp_preprocess_body<SPLIT>(idx, D, M, means3D, scales, scale_modifier, rotations, opacities, sh_row, cov3D_precomp,
+                              colors_precomp, viewmatrix, projmatrix, cam_pos, W, H, tan_fovx, tan_fovy, focal_x,
+                              focal_y, prefiltered, grid_x, grid_y, g, radii);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -506,13 +513,15 @@ extern "C" int gp_raster_preprocess(const gp_raster_cfg* cfg, const float* means
   const float focal_y = H / (2.0f * cfg->tanfovy);
   const float focal_x = W / (2.0f * cfg->tanfovx);
   const unsigned gx = (W + GP_TILE_X - 1) / GP_TILE_X, gy = (H + GP_TILE_Y - 1) / GP_TILE_Y;
-  const int staged = (shs != nullptr && cfg->sh_coeffs == 16 && (((size_t)shs) & 15) == 0) ? 1 : 0;
-  const size_t pp_smem = staged ? (size_t)8 * 32 * GP_SH_ROW * sizeof(float) : 0;
+  const int staged = (shs != nullptr && cfg->sh_coeffs == 16 && ((((size_t)shs) | ((size_t)cfg->sh_rest)) & 15) == 0) ? 1 : 0;
+  if (cfg->sh_rest && !staged) return GP_ERR_UNSUPPORTED;  // split SH storage: 16 coefficients, 16-byte aligned arrays
+  const size_t pp_smem = staged ? (size_t)8 * GP_SH_TILE * sizeof(float) : 0;
+  auto kernel = cfg->sh_rest ? gp_preprocess_kernel<true> : gp_preprocess_kernel<false>;
   if (pp_smem > 48 * 1024)
-    GP_CUDA_TRY(cudaFuncSetAttribute(gp_preprocess_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pp_smem));
-  GP_KERNEL("gp_preprocess_kernel", stream, gp_preprocess_kernel<<<(P + 255) / 256, 256, pp_smem, stream>>>(
-      P, cfg->sh_degree, cfg->sh_coeffs, means3D, scales, cfg->scale_modifier, rotations, opacities, shs, cov3D_precomp,
-      colors_precomp, viewmatrix, projmatrix, campos, W, H, cfg->tanfovx, cfg->tanfovy, focal_x, focal_y,
+    GP_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pp_smem));
+  GP_KERNEL("gp_preprocess_kernel", stream, kernel<<<(P + 255) / 256, 256, pp_smem, stream>>>(
+      P, cfg->sh_degree, cfg->sh_coeffs, means3D, scales, cfg->scale_modifier, rotations, opacities, shs, cfg->sh_rest,
+      cov3D_precomp, colors_precomp, viewmatrix, projmatrix, campos, W, H, cfg->tanfovx, cfg->tanfovy, focal_x, focal_y,
       cfg->prefiltered, gx, gy, g, radii, staged));
   GP_LAUNCH_CHECK();
   // depth sort: P keys, all 32 bits; result lands back in buffer 0 (4 passes)

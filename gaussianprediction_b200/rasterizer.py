@@ -55,11 +55,12 @@ def workspace_sizes(P, W, H, capacity):
     return g.value, b.value, i.value
 
 
-def _make_cfg(P, raster_settings, sh):
-    M = 0 if sh is None else int(sh.shape[1])
+def _make_cfg(P, raster_settings, sh, sh_rest=None):
+    M = 0 if sh is None else int(sh.shape[1]) + (0 if sh_rest is None else int(sh_rest.shape[1]))
     return RasterCfg(P, int(raster_settings.image_width), int(raster_settings.image_height),
                      int(raster_settings.sh_degree), M, float(raster_settings.tanfovx), float(raster_settings.tanfovy),
-                     float(raster_settings.scale_modifier), 1 if raster_settings.prefiltered else 0)
+                     float(raster_settings.scale_modifier), 1 if raster_settings.prefiltered else 0,
+                     ptr(sh_rest), None)
 
 
 class RasterState:
@@ -80,8 +81,9 @@ def last_overflow():
 
 
 def raster_forward(means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, raster_settings,
-                   capacity: Optional[int] = None):
-    """Runs the two forward stages; returns (color, radii, depth, tidx, RasterState)."""
+                   capacity: Optional[int] = None, sh_rest=None):
+    """Runs the two forward stages; returns (color, radii, depth, tidx, RasterState).  With ``sh_rest`` ([P,15,3]),
+    ``sh`` is only coefficient 0 ([P,1,3]): the two parameters of the reference model, read in place."""
     L = _lib.lib()
     dev = means3D.device
     if means3D.dim() != 2 or means3D.shape[1] != 3:
@@ -102,12 +104,12 @@ def raster_forward(means3D, sh, colors_precomp, opacities, scales, rotations, co
         return color, radii, depth, tidx, st
 
     means3D = _f32c(means3D)
-    sh, colors_precomp = _opt(sh), _opt(colors_precomp)
+    sh, colors_precomp, sh_rest = _opt(sh), _opt(colors_precomp), _opt(sh_rest)
     scales, rotations, cov3Ds_precomp = _opt(scales), _opt(rotations), _opt(cov3Ds_precomp)
     opacities = _f32c(opacities)
     bg = _f32c(raster_settings.bg)
     view, proj, campos = _f32c(raster_settings.viewmatrix), _f32c(raster_settings.projmatrix), _f32c(raster_settings.campos)
-    cfg = _make_cfg(P, raster_settings, sh)
+    cfg = _make_cfg(P, raster_settings, sh, sh_rest)
     gbytes, _, ibytes = workspace_sizes(P, W, H, 0)
     geom = torch.empty((gbytes,), dtype=torch.uint8, device=dev)
     image = torch.empty((ibytes,), dtype=torch.uint8, device=dev)
@@ -133,18 +135,20 @@ def raster_forward(means3D, sh, colors_precomp, opacities, scales, rotations, co
 
 
 def raster_backward(st, grad_out_color, means3D, sh, colors_precomp, scales, rotations, cov3Ds_precomp,
-                    raster_settings):
-    """Returns (grad_means2D, grad_colors, grad_opacity, grad_means3D, grad_cov3D, grad_sh, grad_scales, grad_rots)."""
+                    raster_settings, sh_rest=None):
+    """Returns (grad_means2D, grad_colors, grad_opacity, grad_means3D, grad_cov3D, grad_sh, grad_scales, grad_rots);
+    with split SH storage grad_sh is the pair (grad_sh_dc [P,1,3], grad_sh_rest [P,15,3])."""
     L = _lib.lib()
     dev = means3D.device
     P = int(means3D.shape[0])
-    sh, colors_precomp = _opt(sh), _opt(colors_precomp)
+    sh, colors_precomp, sh_rest = _opt(sh), _opt(colors_precomp), _opt(sh_rest)
     scales, rotations, cov3Ds_precomp = _opt(scales), _opt(rotations), _opt(cov3Ds_precomp)
     M = 0 if sh is None else int(sh.shape[1])
     f = dict(dtype=torch.float32, device=dev)
     if P == 0:
         z = lambda *s: torch.zeros(s, **f)
-        return z(0, 3), z(0, 3), z(0, 1), z(0, 3), z(0, 6), z(0, M, 3), z(0, 3), z(0, 4)
+        g_sh0 = z(0, M, 3) if sh_rest is None else (z(0, M, 3), z(0, int(sh_rest.shape[1]), 3))
+        return z(0, 3), z(0, 3), z(0, 1), z(0, 3), z(0, 6), g_sh0, z(0, 3), z(0, 4)
     g_means2D = torch.empty((P, 3), **f)
     g_opacity = torch.empty((P, 1), **f)
     g_means3D = torch.empty((P, 3), **f)
@@ -154,45 +158,59 @@ def raster_backward(st, grad_out_color, means3D, sh, colors_precomp, scales, rot
     g_rots = torch.empty((P, 4), **f) if scales is not None else None
     g_cov3D = torch.empty((P, 6), **f) if cov3Ds_precomp is not None else None
     ws = torch.empty((L.gp_raster_backward_ws_bytes(P),), dtype=torch.uint8, device=dev)
+    cfg = st.cfg
+    g_sh_rest = None
+    if sh_rest is not None:
+        g_sh_rest = torch.empty((P, int(sh_rest.shape[1]), 3), **f)
+        cfg = RasterCfg.from_buffer_copy(st.cfg)
+        cfg.sh_rest, cfg.dL_dsh_rest = ptr(sh_rest), ptr(g_sh_rest)
     bg = _f32c(raster_settings.bg)
     view, proj, campos = _f32c(raster_settings.viewmatrix), _f32c(raster_settings.projmatrix), _f32c(raster_settings.campos)
     means3D, grad_out_color = _f32c(means3D), _f32c(grad_out_color)   # named: copies must outlive the launch
-    check(L.gp_raster_backward(ctypes.byref(st.cfg), ptr(bg), ptr(means3D), ptr(sh), ptr(colors_precomp),
+    check(L.gp_raster_backward(ctypes.byref(cfg), ptr(bg), ptr(means3D), ptr(sh), ptr(colors_precomp),
                                ptr(scales), ptr(rotations), ptr(cov3Ds_precomp), ptr(view), ptr(proj), ptr(campos),
                                ptr(st.radii), ptr(st.geom), ptr(st.binning), st.capacity, ptr(st.image),
                                ptr(grad_out_color), ptr(ws), ptr(g_means2D), ptr(g_colors), ptr(g_opacity),
                                ptr(g_means3D), ptr(g_cov3D), ptr(g_sh), ptr(g_scales), ptr(g_rots),
                                _lib.stream_ptr()), "gp_raster_backward")
+    if sh_rest is not None:
+        g_sh = (g_sh, g_sh_rest)
     return g_means2D, g_colors, g_opacity, g_means3D, g_cov3D, g_sh, g_scales, g_rots
 
 
 class _RasterizeGaussians(torch.autograd.Function):
     @staticmethod
     def forward(ctx, means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
-                raster_settings, capacity=None):
+                raster_settings, capacity=None, sh_rest=None):
         color, radii, depth, tidx, st = raster_forward(means3D, sh, colors_precomp, opacities, scales, rotations,
-                                                       cov3Ds_precomp, raster_settings, capacity)
+                                                       cov3Ds_precomp, raster_settings, capacity, sh_rest)
         ctx.raster_settings = raster_settings
         ctx.state = st
         ctx.num_rendered = st.num_rendered
-        ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, sh)
+        ctx.split_sh = sh_rest is not None
+        ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, sh, sh_rest)
         ctx.mark_non_differentiable(radii, depth, tidx)  # the reference has no depth gradient (:88)
+        ctx.set_materialize_grads(False)                 # no zero tensors built for the outputs that take no gradient
         return color, radii, depth, tidx
 
     @staticmethod
     def backward(ctx, grad_out_color, _radii, _depth, _tidx):
-        colors_precomp, means3D, scales, rotations, cov3Ds_precomp, sh = ctx.saved_tensors
+        colors_precomp, means3D, scales, rotations, cov3Ds_precomp, sh, sh_rest = ctx.saved_tensors
+        if grad_out_color is None:
+            grad_out_color = torch.zeros((3, int(ctx.raster_settings.image_height),
+                                          int(ctx.raster_settings.image_width)), dtype=torch.float32, device=means3D.device)
         (g_means2D, g_colors, g_opacity, g_means3D, g_cov3D, g_sh, g_scales, g_rots) = raster_backward(
             ctx.state, grad_out_color, means3D, sh, colors_precomp, scales, rotations, cov3Ds_precomp,
-            ctx.raster_settings)
+            ctx.raster_settings, sh_rest if ctx.split_sh else None)
+        g_sh, g_sh_rest = g_sh if ctx.split_sh else (g_sh, None)
         # order of the reference's backward (:120-130)
-        return (g_means3D, g_means2D, g_sh, g_colors, g_opacity, g_scales, g_rots, g_cov3D, None, None)
+        return (g_means3D, g_means2D, g_sh, g_colors, g_opacity, g_scales, g_rots, g_cov3D, None, None, g_sh_rest)
 
 
 def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
-                        raster_settings, capacity=None):
+                        raster_settings, capacity=None, sh_rest=None):
     return _RasterizeGaussians.apply(means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
-                                     cov3Ds_precomp, raster_settings, capacity)
+                                     cov3Ds_precomp, raster_settings, capacity, sh_rest)
 
 
 def mark_visible(positions, viewmatrix, projmatrix):
@@ -218,7 +236,10 @@ class GaussianRasterizer(nn.Module):
             return mark_visible(positions, rs.viewmatrix, rs.projmatrix)
 
     def forward(self, means3D, means2D, opacities, shs=None, colors_precomp=None, scales=None, rotations=None,
-                cov3D_precomp=None):
+                cov3D_precomp=None, shs_rest=None):
+        """The reference's call (diff_gaussian_rasterization/__init__.py:186-221).  Extension: with ``shs_rest``
+        ([P,15,3], CUDA float32) ``shs`` is coefficient 0 only ([P,1,3]) -- the model's ``_features_dc`` /
+        ``_features_rest`` read in place, without the per-frame ``torch.cat`` of ``get_features``."""
         raster_settings = self.raster_settings
         if (shs is None and colors_precomp is None) or (shs is not None and colors_precomp is not None):
             raise Exception('Please provide excatly one of either SHs or precomputed colors!')
@@ -235,8 +256,10 @@ class GaussianRasterizer(nn.Module):
             rotations = torch.Tensor([])
         if cov3D_precomp is None:
             cov3D_precomp = torch.Tensor([])
+        if shs_rest is not None and (shs.dim() != 3 or shs.shape[1] != 1 or shs_rest.shape[1] != 15):
+            shs, shs_rest = torch.cat((shs, shs_rest), dim=1), None      # only the 1 + 15 layout is read in place
         return rasterize_gaussians(means3D, means2D, shs, colors_precomp, opacities, scales, rotations, cov3D_precomp,
-                                   raster_settings, self.capacity)
+                                   raster_settings, self.capacity, shs_rest)
 
 
 def export_state(st):

@@ -21,6 +21,21 @@ def _settings(viewpoint_camera, pc, bg_color, scaling_modifier):
         sh_degree=pc.active_sh_degree, campos=viewpoint_camera.camera_center, prefiltered=False)
 
 
+def _sh_inputs(pc, override_color):
+    """(shs, shs_rest, colors_precomp) for the rasterizer.  The reference passes ``pc.get_features`` = cat(_features_dc,
+    _features_rest) (gaussian_renderer/__init__.py:74-78); when the model exposes the two parameters in the usual
+    [N,1,3] / [N,15,3] layout they are handed over separately and read in place (no 192 B/Gaussian copy per frame, and
+    no split of the gradient on the way back)."""
+    if override_color is not None:
+        return None, None, override_color
+    dc, rest = getattr(pc, "_features_dc", None), getattr(pc, "_features_rest", None)
+    if torch.is_tensor(dc) and torch.is_tensor(rest) and dc.is_cuda and dc.dim() == 3 and dc.shape[1] == 1 \
+            and rest.dim() == 3 and rest.shape[1] == 15 and dc.dtype == torch.float32 and rest.dtype == torch.float32 \
+            and dc.is_contiguous() and rest.is_contiguous():
+        return dc, rest, None
+    return pc.get_features, None, None
+
+
 def render(viewpoint_camera, pc, pipe=None, bg_color=None, scaling_modifier=1.0, override_color=None, delta=None,
            time=None, it=1, capacity=None):
     screenspace_points = torch.zeros_like(pc.get_xyz, dtype=pc.get_xyz.dtype, requires_grad=True, device="cuda") + 0
@@ -35,10 +50,10 @@ def render(viewpoint_camera, pc, pipe=None, bg_color=None, scaling_modifier=1.0,
         scales, rotations = pc.get_scaling, pc.get_rotation
     else:
         means3D, rotations, scales, opacity = pc(time, it)
-    shs, colors_precomp = (pc.get_features, None) if override_color is None else (None, override_color)
+    shs, shs_rest, colors_precomp = _sh_inputs(pc, override_color)
     rendered_image, radii, depth, tidx = rasterizer(means3D=means3D, means2D=screenspace_points, shs=shs,
                                                     colors_precomp=colors_precomp, opacities=opacity, scales=scales,
-                                                    rotations=rotations, cov3D_precomp=None)
+                                                    rotations=rotations, cov3D_precomp=None, shs_rest=shs_rest)
     return {"render": rendered_image, "viewspace_points": screenspace_points, "visibility_filter": radii > 0,
             "radii": radii, "depth": depth, "tidx": tidx}
 
@@ -48,10 +63,11 @@ def render_motion(viewpoint_camera, pc, pipe=None, bg_color=None, scaling_modifi
     screenspace_points = torch.zeros_like(pc.get_xyz, dtype=pc.get_xyz.dtype, requires_grad=True, device="cuda") + 0
     rasterizer = GaussianRasterizer(_settings(viewpoint_camera, pc, bg_color, scaling_modifier), capacity=capacity)
     opacity = pc.get_opacity if opacity is None else opacity
-    shs, colors_precomp = (pc.get_features, None) if override_color is None else (None, override_color)
+    shs, shs_rest, colors_precomp = _sh_inputs(pc, override_color)
     rendered_image, radii, depth, tidx = rasterizer(means3D=xyz_t, means2D=screenspace_points, shs=shs,
                                                     colors_precomp=colors_precomp, opacities=opacity,
-                                                    scales=pc.get_scaling, rotations=r_t, cov3D_precomp=None)
+                                                    scales=pc.get_scaling, rotations=r_t, cov3D_precomp=None,
+                                                    shs_rest=shs_rest)
     return {"render": rendered_image, "viewspace_points": screenspace_points, "visibility_filter": radii > 0,
             "radii": radii}
 

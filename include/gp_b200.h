@@ -54,6 +54,13 @@ typedef struct {
   float tanfovx, tanfovy;
   float scale_modifier;
   int prefiltered;
+  /* Optional split SH storage.  The reference keeps coefficient 0 (_features_dc [P,1,3]) and the rest
+   * (_features_rest [P,15,3]) as two parameters and concatenates them every frame (scene/gaussian_model.py:155-158).
+   * With sh_rest non-NULL the `shs` argument of gp_raster_preprocess / gp_raster_backward holds only coefficient 0 and
+   * sh_rest the other 15 (sh_coeffs must be 16, arrays 16-byte aligned; GP_ERR_UNSUPPORTED otherwise); the backward
+   * then writes dL_dsh as [P,1,3] and dL_dsh_rest as [P,15,3].  NULL: `shs` is the concatenated [P,sh_coeffs,3]. */
+  const float* sh_rest;
+  float* dL_dsh_rest;
 } gp_raster_cfg;
 
 /* Header words at the start of the geometry workspace (int32 each); readable by the host. */
