@@ -190,7 +190,8 @@ class OurRunner:
         if self.world > 1:
             from gaussianprediction_b200.parallel import FlatGradAllReduce
             # only parameters that receive a gradient on this path take part in the exchange (known after the eager pass)
-            reducer = FlatGradAllReduce([p for p in self.params if p.grad is not None])
+            reducer = FlatGradAllReduce([p for p in self.params if p.grad is not None],
+                                        first=[self.pc._features_dc, self.pc._features_rest])
         self.graph_reducer = reducer
         self.train_step = TrainStep(self.pc, self.cams_dev[0], self.capacity, bg=self.bg, iteration=ITER, reducer=reducer)
         self.render_step = RenderStep(self.pc, self.cams_dev[0], self.capacity, bg=self.bg, iteration=ITER)

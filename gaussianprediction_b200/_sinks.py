@@ -1,0 +1,47 @@
+"""Gradient sinks: let the backward kernels write parameter gradients straight into caller-owned memory.
+
+Data-parallel training keeps one flat buffer per all-reduce bucket (parallel.FlatGradAllReduce).  Without help, every
+gradient is first produced in a fresh tensor and then added into its slice of that buffer (a zero fill, a read-modify-
+write and a launch per parameter and step).  While a sink map is installed, the autograd Functions of this package
+look up the tensor a gradient belongs to (by storage address) and, if it has a sink, hand the sink to the kernel as
+its output array.  Autograd then finds ``p.grad`` empty, keeps the returned tensor as ``p.grad`` -- which *is* the
+slice of the flat buffer -- and nothing is copied.  Parameters that get their gradient through torch ops instead (or
+from more than one producer) simply miss the sink and are packed the usual way by the reducer.
+"""
+import contextlib
+
+_SINKS = {}
+
+
+def _key(t):
+    return (t.data_ptr(), t.numel())
+
+
+@contextlib.contextmanager
+def grad_sinks(pairs):
+    """``pairs``: iterable of (parameter, destination tensor of the same shape, contiguous float32)."""
+    global _SINKS
+    old = _SINKS
+    _SINKS = dict(old)
+    for p, dst in pairs:
+        assert dst.is_contiguous() and dst.shape == p.shape and dst.dtype == p.dtype
+        _SINKS[_key(p)] = dst
+    try:
+        yield
+    finally:
+        _SINKS = old
+
+
+def sink_for(t):
+    """The destination registered for the tensor whose storage ``t`` is (None if there is none / no map installed)."""
+    if not _SINKS or t is None or t.numel() == 0:
+        return None
+    return _SINKS.get(_key(t))
+
+
+def out_like(sink, shape, **kw):
+    """The sink if there is one (a fresh view object of it, so that autograd may adopt it as .grad), else a new tensor."""
+    import torch
+    if sink is not None:
+        return sink.view(shape)
+    return torch.empty(shape, **kw)

@@ -19,6 +19,7 @@ import torch.nn as nn
 
 from . import _lib
 from ._lib import check, ptr
+from ._sinks import out_like, sink_for
 
 
 # ------------------------------------------------------------------------------------------------ small torch pieces
@@ -155,6 +156,7 @@ class _KeypointBlend(torch.autograd.Function):
               "gp_blend_forward")
         ctx.save_for_backward(logits_c, idx32, kpx, kpq, rot_c, s_t, o_t)
         ctx.dims = (N, Kp, K)
+        ctx.sinks = [sink_for(t) for t in (logits, xyz, rot, scaling, opacity)]
         return xyz_t, q_t, s_t, o_t
 
     @staticmethod
@@ -164,12 +166,13 @@ class _KeypointBlend(torch.autograd.Function):
         N, Kp, K = ctx.dims
         f = dict(dtype=torch.float32, device=logits.device)
         need = ctx.needs_input_grad
-        g_logits = torch.empty((N, 2 * K), **f) if need[0] else None
+        sk = ctx.sinks
+        g_logits = out_like(sk[0], (N, 2 * K), **f) if need[0] else None
         g_kpx, g_kpq = torch.empty((Kp, 3), **f), torch.empty((Kp, 4), **f)
-        g_xyz = torch.empty((N, 3), **f) if need[4] else None
-        g_rot = torch.empty((N, 4), **f) if need[5] else None
-        g_sc = torch.empty((N, 3), **f) if need[6] else None
-        g_op = torch.empty((N, 1), **f) if need[7] else None
+        g_xyz = out_like(sk[1], (N, 3), **f) if need[4] else None
+        g_rot = out_like(sk[2], (N, 4), **f) if need[5] else None
+        g_sc = out_like(sk[3], (N, 3), **f) if need[6] else None
+        g_op = out_like(sk[4], (N, 1), **f) if need[7] else None
         g_in = [None if g is None else _c(g) for g in (g_xyz_t, g_q_t, g_s_t, g_o_t)]   # kept alive until the launch
         check(L.gp_blend_backward(N, Kp, K, ptr(logits), ptr(idx32), None, ptr(kpx), ptr(kpq), ptr(rot), ptr(s_t), ptr(o_t),
                                   ptr(g_in[0]), ptr(g_in[1]), ptr(g_in[2]), ptr(g_in[3]), ptr(g_logits),
@@ -209,6 +212,7 @@ class _KeypointMLP(torch.autograd.Function):
                                  ptr(dq), ptr(do), _lib.stream_ptr()), "gp_kpmlp_forward")
         ctx.save_for_backward(xyz_c, t_c, saved, *weights)
         ctx.cfg, ctx.bwd_bytes = cfg, bs.value
+        ctx.sinks = [sink_for(t) for t in (kp_xyz, kp_feat) + tuple(params)]
         ctx.set_materialize_grads(False)     # an unused output arrives as None (= zeros for the kernel), not as a zero tensor
         return (dxyz, dq) if do is None else (dxyz, dq, do)
 
@@ -220,10 +224,12 @@ class _KeypointMLP(torch.autograd.Function):
         n = cfg.depth + 1
         dev = xyz_c.device
         need = ctx.needs_input_grad
-        g_xyz = torch.empty_like(xyz_c) if need[1] else None
-        g_feat = torch.empty((cfg.rows, cfg.feature_dim), dtype=torch.float32, device=dev) if need[2] else None
-        gw = [torch.empty_like(w) for w in weights]
-        gb = [torch.empty(w.shape[0], dtype=torch.float32, device=dev) for w in weights]
+        sk = ctx.sinks
+        f = dict(dtype=torch.float32, device=dev)
+        g_xyz = out_like(sk[0], tuple(xyz_c.shape), **f) if need[1] else None
+        g_feat = out_like(sk[1], (cfg.rows, cfg.feature_dim), **f) if need[2] else None
+        gw = [out_like(sk[2 + i], tuple(w.shape), **f) for i, w in enumerate(weights)]
+        gb = [out_like(sk[2 + n + i], (w.shape[0],), **f) for i, w in enumerate(weights)]
         scratch = torch.empty(ctx.bwd_bytes, dtype=torch.uint8, device=dev)
         wp = (ctypes.c_void_p * n)(*[w.data_ptr() for w in weights])
         gwp = (ctypes.c_void_p * n)(*[g.data_ptr() for g in gw])
@@ -399,7 +405,8 @@ class KeypointDeformation(nn.Module):
         else:
             # second stage (:251-273, :285-287): keypoints
             factor = 0.1 * (1 - min(1, (iteration - self.second_stage_iter) / args.xyz_noise_iteration))
-            noise = torch.randn_like(self.super_gaussians) * factor  # RNG consumed even when the factor is 0 (:254)
+            noise = torch.randn_like(self.super_gaussians)  # RNG consumed even when the factor is 0 (:254)
+            kp_in = self.super_gaussians + noise * factor if factor != 0 else self.super_gaussians   # + 0 * noise == itself
             logits = self.weights_model(self._xyz.detach())
             if not (self.knn_cache and self._idx32 is not None):
                 self.get_nearest_mask(keepshape=True)
@@ -407,11 +414,11 @@ class KeypointDeformation(nn.Module):
             xf, tf = int(self.xyz_input_dim / 6), self.time_input_dim // 2
             if self.fused_mlp and self.super_gaussians.is_cuda and \
                     keypoint_mlp_supported(self.df_model, args.feature_dim, xf, tf):
-                delta_xyz, delta_q, _ = keypoint_mlp(self.df_model, self.super_gaussians + noise,
+                delta_xyz, delta_q, _ = keypoint_mlp(self.df_model, kp_in,
                                                      self.super_gaussians_feature, t_input, xf, tf,
                                                      normalize_q=args.norm_rotation)
             else:
-                xyz_embed = positional_encoding(self.super_gaussians + noise, xf)
+                xyz_embed = positional_encoding(kp_in, xf)
                 delta_xyz, delta_q, _ = self.get_motion_delta(xyz_embed, self.super_gaussians_feature, t_embed())
                 if args.norm_rotation:
                     delta_q = normalize(delta_q)

@@ -22,32 +22,63 @@ class FlatGradAllReduce:
     this rank), sums it over the process group and points ``p.grad`` at views of the reduced buffer, so every rank
     ends the step with identical gradients (and, with identical optimizer state, identical parameters)."""
 
-    def __init__(self, params, group=None):
-        self.params = [p for p in params if p.requires_grad]
+    def __init__(self, params, group=None, first=()):
+        """``first``: parameters whose gradients are complete earliest in the backward (the SH coefficients: the
+        rasterizer writes them before the deformation backward starts).  They are laid out at the front of the buffer
+        as their own bucket so that ``pipeline.TrainStep`` can start their all-reduce while the rest of the backward
+        is still running; ``reduce()`` itself always exchanges the whole buffer."""
+        params = [p for p in params if p.requires_grad]
+        first_ids = {id(p) for p in first}
+        self.params = [p for p in params if id(p) in first_ids] + [p for p in params if id(p) not in first_ids]
         self.group = group
         n = sum(p.numel() for p in self.params)
         p0 = self.params[0]
         self.flat = torch.zeros(n, dtype=p0.dtype, device=p0.device)
         self.views = []
         off = 0
+        self.split = 0                       # elements of the first bucket
         for p in self.params:
             self.views.append(self.flat[off:off + p.numel()].view_as(p))
             off += p.numel()
+            if id(p) in first_ids:
+                self.split = off
+
+    def buckets(self):
+        """The flat buffer as (early bucket, late bucket); the early one is empty without ``first``."""
+        return self.flat[:self.split], self.flat[self.split:]
+
+    @property
+    def n_first(self):
+        """How many leading parameters form the early bucket."""
+        n, off = 0, 0
+        for p in self.params:
+            if off >= self.split:
+                break
+            off += p.numel()
+            n += 1
+        return n
+
+    def pack(self, lo=0, hi=None):
+        """Make ``p.grad`` of parameters [lo, hi) the parameter's view of the flat buffer (zero / copy where it is not
+        already: gradients the kernels wrote through a grad sink are in place and cost nothing here)."""
+        moved = 0
+        for p, v in list(zip(self.params, self.views))[lo:hi]:
+            if p.grad is None:
+                v.zero_()
+                moved += 1
+            elif p.grad.data_ptr() != v.data_ptr():
+                v.copy_(p.grad)
+                moved += 1
+            p.grad = v
+        return moved                         # how many gradients had to be filled in / copied
 
     @property
     def nbytes(self):
         return self.flat.numel() * self.flat.element_size()
 
     def reduce(self, async_op=False):
-        for p, v in zip(self.params, self.views):
-            if p.grad is None:
-                v.zero_()
-            elif p.grad.data_ptr() != v.data_ptr():
-                v.copy_(p.grad)
-        work = dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=self.group, async_op=async_op)
-        for p, v in zip(self.params, self.views):
-            p.grad = v
-        return work
+        self.pack()
+        return dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=self.group, async_op=async_op)
 
 
 class GroupedGradAllReduce:

@@ -12,6 +12,7 @@ A graph is tied to (image size, tan-fov, SH degree, parameter shapes, capacity):
 import torch
 
 from . import _lib
+from ._sinks import grad_sinks
 from .rasterizer import export_state  # noqa: F401  (kept importable for diagnostics)
 from .renderer import render
 
@@ -44,11 +45,14 @@ class TrainStep:
 
     def __init__(self, pc, cam, capacity, bg=None, iteration=50_000, loss_fn=None, warmup=3, reducer=None,
                  capture_collective=False):
-        """``reducer``: a ``parallel.FlatGradAllReduce`` over the same parameters.  The gradients are then accumulated
-        straight into its flat buffer inside the graph (no packing copies) and summed over the ranks with ONE
-        all-reduce per step, issued right after the replay.  ``capture_collective=True`` records the all-reduce into
-        the graph as well; EXPERIMENTAL -- with torch 2.11 / NCCL 2.28 on the B200 test box that capture hung, so it is
-        off by default and not used by bench.py."""
+        """``reducer``: a ``parallel.FlatGradAllReduce`` over the same parameters.  The backward kernels then write
+        the parameter gradients straight into its flat buffer (``_sinks``: no zero fill, no accumulation pass, no
+        packing copies) and the step is captured as TWO graphs: (A) forward + backward through the rasterizer, after
+        which the SH gradients -- two thirds of the bytes -- are final, (B) the deformation backward.  The all-reduce
+        of the early bucket is issued between the replays and runs over NVLink while (B) computes; the late bucket
+        follows (B).  ``capture_collective=True`` records ONE all-reduce into a single graph instead; EXPERIMENTAL --
+        with torch 2.11 / NCCL 2.28 on the B200 test box that capture hung, so it is off by default and not used by
+        bench.py."""
         self.pc = pc
         self.reducer = reducer
         self.capture_collective = bool(capture_collective and reducer is not None)
@@ -83,8 +87,16 @@ class TrainStep:
             for p in self.params:
                 p.grad = None
         self.graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(self.graph):
-            self._body()
+        self.graph_b = None
+        if self.two_stage:
+            with torch.cuda.graph(self.graph):
+                self._stage_a()
+            self.graph_b = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self.graph_b, pool=self.graph.pool()):
+                self._stage_b()
+        else:
+            with torch.cuda.graph(self.graph):
+                self._body()
         from . import rasterizer as _r
         self._state = _r.LAST_STATE          # workspaces of the captured frame (static addresses)
         self.grads = [p.grad for p in self.params]   # the tensors the graph writes; re-attached after every replay
@@ -95,7 +107,40 @@ class TrainStep:
         hdr = self._state.geom[:16].view(torch.int32).cpu()
         return int(hdr[_lib.HDR_NUM_RENDERED]), bool(int(hdr[_lib.HDR_OVERFLOW]))
 
+    @property
+    def two_stage(self):
+        return self.reducer is not None and not self.capture_collective
+
+    def _stage_a(self):
+        """Forward, loss, backward down to the deformed parameters and the SH leaves (whose gradients are then final)."""
+        r = self.reducer
+        for p in self.params:
+            p.grad = None
+        with grad_sinks(zip(r.params, r.views)):      # looked up while the autograd graph is being built
+            self.pkg = render(self.cam, self.pc, None, self.bg, time=self.t, it=self.iteration, capacity=self.capacity)
+            self.loss = self.loss_fn(self.pkg["render"], self.target)
+        nf = r.n_first
+        deformed = [t for t in self.pkg["deformed"] if t.requires_grad]
+        outs = torch.autograd.grad(self.loss, deformed + r.params[:nf] + [self.pkg["viewspace_points"]],
+                                   allow_unused=True)
+        self._deformed = [(t, g) for t, g in zip(deformed, outs[:len(deformed)]) if g is not None]
+        for p, g in zip(r.params[:nf], outs[len(deformed):len(deformed) + nf]):
+            p.grad = g
+        self.viewspace_grad = outs[-1]
+        self.packed = r.pack(0, nf)           # diagnostics: gradients that did NOT arrive through a sink
+
+    def _stage_b(self):
+        """The deformation backward (blend, keypoint MLP); afterwards every gradient sits in the flat buffer."""
+        r = self.reducer
+        if self._deformed:
+            torch.autograd.backward([t for t, _ in self._deformed], [g for _, g in self._deformed])
+        self.packed += r.pack(r.n_first, None)
+
     def _body(self):
+        if self.two_stage:
+            self._stage_a()
+            self._stage_b()
+            return
         if self.reducer is None:
             for p in self.params:
                 p.grad = None
@@ -157,10 +202,20 @@ class TrainStep:
         return self._replay()
 
     def _replay(self):
-        self.graph.replay()
-        if self.reducer is not None and not self.capture_collective:
+        if self.two_stage:
             import torch.distributed as dist
-            dist.all_reduce(self.reducer.flat, op=dist.ReduceOp.SUM, group=self.reducer.group)
+            early, late = self.reducer.buckets()
+            self.graph.replay()
+            w1 = dist.all_reduce(early, op=dist.ReduceOp.SUM, group=self.reducer.group, async_op=True) \
+                if early.numel() else None
+            self.graph_b.replay()             # runs while the early bucket is on the wire
+            w2 = dist.all_reduce(late, op=dist.ReduceOp.SUM, group=self.reducer.group, async_op=True) \
+                if late.numel() else None
+            for w in (w1, w2):
+                if w is not None:
+                    w.wait()
+        else:
+            self.graph.replay()
         for p, g in zip(self.params, self.grads):     # p.grad may have been replaced / cleared by the caller
             p.grad = g
         return self.loss

@@ -20,6 +20,7 @@ import torch
 import torch.nn as nn
 
 from . import _lib
+from ._sinks import out_like, sink_for
 from ._lib import RasterCfg, check, ptr
 
 
@@ -135,7 +136,7 @@ def raster_forward(means3D, sh, colors_precomp, opacities, scales, rotations, co
 
 
 def raster_backward(st, grad_out_color, means3D, sh, colors_precomp, scales, rotations, cov3Ds_precomp,
-                    raster_settings, sh_rest=None):
+                    raster_settings, sh_rest=None, sinks=(None, None)):
     """Returns (grad_means2D, grad_colors, grad_opacity, grad_means3D, grad_cov3D, grad_sh, grad_scales, grad_rots);
     with split SH storage grad_sh is the pair (grad_sh_dc [P,1,3], grad_sh_rest [P,15,3])."""
     L = _lib.lib()
@@ -153,7 +154,7 @@ def raster_backward(st, grad_out_color, means3D, sh, colors_precomp, scales, rot
     g_opacity = torch.empty((P, 1), **f)
     g_means3D = torch.empty((P, 3), **f)
     g_colors = torch.empty((P, 3), **f) if colors_precomp is not None else None
-    g_sh = torch.empty((P, M, 3), **f) if sh is not None else None
+    g_sh = out_like(sinks[0], (P, M, 3), **f) if sh is not None else None
     g_scales = torch.empty((P, 3), **f) if scales is not None else None
     g_rots = torch.empty((P, 4), **f) if scales is not None else None
     g_cov3D = torch.empty((P, 6), **f) if cov3Ds_precomp is not None else None
@@ -161,7 +162,7 @@ def raster_backward(st, grad_out_color, means3D, sh, colors_precomp, scales, rot
     cfg = st.cfg
     g_sh_rest = None
     if sh_rest is not None:
-        g_sh_rest = torch.empty((P, int(sh_rest.shape[1]), 3), **f)
+        g_sh_rest = out_like(sinks[1], (P, int(sh_rest.shape[1]), 3), **f)
         cfg = RasterCfg.from_buffer_copy(st.cfg)
         cfg.sh_rest, cfg.dL_dsh_rest = ptr(sh_rest), ptr(g_sh_rest)
     bg = _f32c(raster_settings.bg)
@@ -188,6 +189,7 @@ class _RasterizeGaussians(torch.autograd.Function):
         ctx.state = st
         ctx.num_rendered = st.num_rendered
         ctx.split_sh = sh_rest is not None
+        ctx.sinks = (sink_for(sh), sink_for(sh_rest))      # where the SH gradients go, if the caller registered a place
         ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, sh, sh_rest)
         ctx.mark_non_differentiable(radii, depth, tidx)  # the reference has no depth gradient (:88)
         ctx.set_materialize_grads(False)                 # no zero tensors built for the outputs that take no gradient
@@ -201,7 +203,7 @@ class _RasterizeGaussians(torch.autograd.Function):
                                           int(ctx.raster_settings.image_width)), dtype=torch.float32, device=means3D.device)
         (g_means2D, g_colors, g_opacity, g_means3D, g_cov3D, g_sh, g_scales, g_rots) = raster_backward(
             ctx.state, grad_out_color, means3D, sh, colors_precomp, scales, rotations, cov3Ds_precomp,
-            ctx.raster_settings, sh_rest if ctx.split_sh else None)
+            ctx.raster_settings, sh_rest if ctx.split_sh else None, ctx.sinks)
         g_sh, g_sh_rest = g_sh if ctx.split_sh else (g_sh, None)
         # order of the reference's backward (:120-130)
         return (g_means3D, g_means2D, g_sh, g_colors, g_opacity, g_scales, g_rots, g_cov3D, None, None, g_sh_rest)

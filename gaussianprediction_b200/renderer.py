@@ -55,7 +55,10 @@ def render(viewpoint_camera, pc, pipe=None, bg_color=None, scaling_modifier=1.0,
                                                     colors_precomp=colors_precomp, opacities=opacity, scales=scales,
                                                     rotations=rotations, cov3D_precomp=None, shs_rest=shs_rest)
     return {"render": rendered_image, "viewspace_points": screenspace_points, "visibility_filter": radii > 0,
-            "radii": radii, "depth": depth, "tidx": tidx}
+            "radii": radii, "depth": depth, "tidx": tidx,
+            # extra key (not in the reference's dict): the deformed parameters the rasterizer consumed, so that a
+            # caller can run the backward in two stages (pipeline.TrainStep overlaps the gradient exchange with it)
+            "deformed": (means3D, rotations, scales, opacity)}
 
 
 def render_motion(viewpoint_camera, pc, pipe=None, bg_color=None, scaling_modifier=1.0, override_color=None, xyz_t=None,

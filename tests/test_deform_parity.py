@@ -361,3 +361,56 @@ def test_model_fused_mlp_equals_torch_mlp(gplib):
     assert grads[0].keys() == grads[1].keys()
     for n in grads[0]:
         assert rel_err(grads[0][n], grads[1][n]) <= 1e-3, n
+
+
+def test_two_stage_step_with_grad_sinks_matches_eager(gplib):
+    """pipeline.TrainStep with a reducer: two graphs with the gradient exchange issued between them, gradients written
+    by the kernels straight into the reducer's flat buffer.  One-rank NCCL group: the sums are the local gradients."""
+    import torch.distributed as dist
+    from gaussianprediction_b200 import synthetic as syn
+    from gaussianprediction_b200.deform import KeypointDeformation, default_args
+    from gaussianprediction_b200.parallel import FlatGradAllReduce
+    from gaussianprediction_b200.pipeline import TrainStep
+    from gaussianprediction_b200.renderer import SceneModel, render
+    own_group = not dist.is_initialized()
+    if own_group:
+        dist.init_process_group("nccl", init_method="tcp://127.0.0.1:%d" % (32500 + os.getpid() % 2000), rank=0, world_size=1)
+    try:
+        N, Kp, W, H = 6000, 96, 128, 96
+        gs, kp, kf, logits = scene(N, Kp, seed=51)
+        args = default_args(feature_amplify=0.5, norm_rotation=True)
+        torch.manual_seed(0)
+        model = KeypointDeformation(args, gs.xyz, gs.rotation, gs.scaling, gs.opacity, gs.motion_feature, kp, kf, logits=logits)
+        pc = SceneModel(model, gs.features_dc, gs.features_rest).cuda()
+        cams = syn.camera_ring(2, W, H, seed=5)
+        for c in cams:
+            for k in ("world_view_transform", "full_proj_transform", "camera_center"):
+                setattr(c, k, getattr(c, k).cuda())
+        bg = torch.zeros(3, device="cuda")
+        g = torch.Generator().manual_seed(1)
+        targets = [(torch.randn(3, H, W, generator=g) * 1e-2).cuda() for _ in cams]
+        times = [torch.tensor([0.2 + 0.3 * i], device="cuda") for i in range(len(cams))]
+        with_grad = [p for n, p in pc.named_parameters() if not n.endswith("motion_feature")]
+        red = FlatGradAllReduce(with_grad, first=[pc._features_dc, pc._features_rest])
+        step = TrainStep(pc, cams[0], capacity=400_000, bg=bg, reducer=red)
+        assert step.two_stage and step.graph_b is not None
+        assert step.packed == 0            # every gradient reached the flat buffer through a sink: nothing filled or copied
+        for cam, t, tgt in zip(cams, times, targets):
+            loss_g = float(step(cam, t, tgt))
+            assert not step.overflowed()[1]
+            grads_g = {n: p.grad.clone() for n, p in pc.named_parameters() if p.grad is not None}
+            assert all(p.grad.data_ptr() == v.data_ptr() for p, v in zip(red.params, red.views))
+            vs_g = step.viewspace_grad.clone()
+            for p in pc.parameters():
+                p.grad = None
+            pkg = render(cam, pc, None, bg, time=t, it=50_000)
+            loss_e = (pkg["render"] * tgt).sum()
+            loss_e.backward()
+            assert abs(loss_g - float(loss_e)) <= 1e-6 * max(1.0, abs(float(loss_e)))
+            for n, p in pc.named_parameters():
+                if p.grad is not None:
+                    assert rel_err(grads_g[n], p.grad) <= 1e-3, n
+            assert rel_err(vs_g, pkg["viewspace_points"].grad) <= 1e-3
+    finally:
+        if own_group:
+            dist.destroy_process_group()

@@ -55,3 +55,45 @@ def test_sample_sharding_and_flat_allreduce_gloo(tmp_path):
     assert torch.allclose(r["g0"], 2 * w0 * p0) and torch.allclose(r["g1"], torch.full((7,), float(w1)))
     assert float(r["g2"].abs().sum()) == 0 and r["mine"] == [0, 2, 4, 6] and r["same_storage"] and r["nbytes"] == 26 * 4
     assert r["radii"].tolist() == [2, 5, 0] and r["vis"].tolist() == [True, True, False]
+
+
+def _bucket_worker(rank, world, port, out):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from gaussianprediction_b200._sinks import grad_sinks, out_like, sink_for
+    from gaussianprediction_b200.parallel import FlatGradAllReduce
+    torch.manual_seed(0)
+    a, b, c = (torch.nn.Parameter(torch.randn(4, 3)), torch.nn.Parameter(torch.randn(6)), torch.nn.Parameter(torch.randn(2, 5)))
+    red = FlatGradAllReduce([a, b, c], first=[c])           # c's gradient is "ready early": it leads the buffer
+    early, late = red.buckets()
+    layout = (red.params[0] is c, red.n_first, early.numel(), late.numel())
+    # a producer that looks its destination up (what the autograd Functions do in their forward) writes in place
+    with grad_sinks(zip(red.params, red.views)):
+        dst = sink_for(c)
+        hit = dst is not None and dst.data_ptr() == red.views[0].data_ptr() and sink_for(torch.zeros(3)) is None
+        g = out_like(dst, (2, 5), dtype=torch.float32)
+    g.copy_(torch.full((2, 5), float(rank + 1)))
+    c.grad = g
+    a.grad = torch.full((4, 3), 10.0 * (rank + 1))          # arrives in a tensor of its own: packed by copy; b: no gradient
+    moved_early = red.pack(0, red.n_first)
+    w1 = dist.all_reduce(early, async_op=True)              # the early bucket goes first ...
+    moved_late = red.pack(red.n_first, None)
+    w2 = dist.all_reduce(late, async_op=True)               # ... the rest follows (pipeline.TrainStep._replay)
+    w1.wait(); w2.wait()
+    if rank == 0:
+        torch.save(dict(layout=layout, hit=hit, moved=(moved_early, moved_late), c=c.grad.clone(), a=a.grad.clone(),
+                        b=b.grad.clone(), in_flat=all(p.grad.data_ptr() == v.data_ptr() for p, v in zip(red.params, red.views))),
+                   out)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_bucketed_exchange_and_grad_sinks_gloo(tmp_path):
+    out = str(tmp_path / "b0.pt")
+    port = 31500 + (os.getpid() % 2000)
+    mp.spawn(_bucket_worker, args=(2, port, out), nprocs=2, join=True)
+    r = torch.load(out)
+    assert r["layout"] == (True, 1, 10, 18) and r["hit"] and r["moved"] == (0, 2) and r["in_flat"]
+    assert torch.equal(r["c"], torch.full((2, 5), 3.0)) and torch.equal(r["a"], torch.full((4, 3), 30.0))
+    assert float(r["b"].abs().sum()) == 0
