@@ -190,8 +190,10 @@ class OurRunner:
         if self.world > 1:
             from gaussianprediction_b200.parallel import FlatGradAllReduce
             # only parameters that receive a gradient on this path take part in the exchange (known after the eager pass)
+            d = self.pc.deformation
             reducer = FlatGradAllReduce([p for p in self.params if p.grad is not None],
-                                        first=[self.pc._features_dc, self.pc._features_rest])
+                                        first=[self.pc._features_dc, self.pc._features_rest],
+                                        second=[d._xyz, d._rotation, d._scaling, d._opacity] + list(d.weights_model.parameters()))
         self.graph_reducer = reducer
         self.train_step = TrainStep(self.pc, self.cams_dev[0], self.capacity, bg=self.bg, iteration=ITER, reducer=reducer)
         self.render_step = RenderStep(self.pc, self.cams_dev[0], self.capacity, bg=self.bg, iteration=ITER)

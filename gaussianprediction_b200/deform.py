@@ -335,6 +335,7 @@ class KeypointDeformation(nn.Module):
         self.lifecycle_opacity = None
         self._idx32 = None
         self._last_logits = None
+        self.keep_kp_deltas, self._kp_deltas = False, None
         self.fused_mlp = True   # keypoint MLP through gp_kpmlp_* (False: the torch modules, e.g. to compare)
         self.knn_cache = False  # eval: the search inputs are parameters only, so it can be hoisted out of the frame loop
         # Morton order of the Gaussians, a speed hint for the search (results do not depend on it).  Built on first use
@@ -425,6 +426,8 @@ class KeypointDeformation(nn.Module):
             # detached: the readers (motion_model/dataset.py:120-123) only take values, and a live reference would keep
             # this frame's autograd graph (and its stream-bound AccumulateGrad nodes) alive across iterations
             self.kpts_xyz_motion, self.kpts_rotation_motion = delta_xyz.detach(), delta_q.detach()
+            if self.keep_kp_deltas:          # pipeline.TrainStep cuts the backward here (and drops the reference again)
+                self._kp_deltas = (delta_xyz, delta_q)
             xyz, q, s, opacity = keypoint_blend(logits, self._idx32, delta_xyz, delta_q, self._xyz, self._rotation,
                                                 self._scaling, self._opacity)
         self.lifecycle_opacity = None

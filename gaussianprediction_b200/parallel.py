@@ -22,41 +22,41 @@ class FlatGradAllReduce:
     this rank), sums it over the process group and points ``p.grad`` at views of the reduced buffer, so every rank
     ends the step with identical gradients (and, with identical optimizer state, identical parameters)."""
 
-    def __init__(self, params, group=None, first=()):
-        """``first``: parameters whose gradients are complete earliest in the backward (the SH coefficients: the
-        rasterizer writes them before the deformation backward starts).  They are laid out at the front of the buffer
-        as their own bucket so that ``pipeline.TrainStep`` can start their all-reduce while the rest of the backward
-        is still running; ``reduce()`` itself always exchanges the whole buffer."""
+    def __init__(self, params, group=None, first=(), second=()):
+        """``first`` / ``second``: parameters whose gradients are complete early in the backward, in that order -- the
+        SH coefficients (written by the rasterizer backward), then the per-Gaussian deformation parameters (written
+        by the blend backward).  Each group becomes its own bucket at the front of the buffer so that
+        ``pipeline.TrainStep`` can start its all-reduce while the rest of the backward is still running; everything
+        else forms the last bucket.  ``reduce()`` itself always exchanges the whole buffer."""
         params = [p for p in params if p.requires_grad]
-        first_ids = {id(p) for p in first}
-        self.params = [p for p in params if id(p) in first_ids] + [p for p in params if id(p) not in first_ids]
+        groups, seen = [], set()
+        for grp in (first, second):
+            ids = {id(p) for p in grp}
+            groups.append([p for p in params if id(p) in ids and id(p) not in seen])
+            seen |= ids
+        groups.append([p for p in params if id(p) not in seen])
+        self.params = [p for grp in groups for p in grp]
         self.group = group
         n = sum(p.numel() for p in self.params)
         p0 = self.params[0]
         self.flat = torch.zeros(n, dtype=p0.dtype, device=p0.device)
         self.views = []
         off = 0
-        self.split = 0                       # elements of the first bucket
         for p in self.params:
             self.views.append(self.flat[off:off + p.numel()].view_as(p))
             off += p.numel()
-            if id(p) in first_ids:
-                self.split = off
+        # per bucket: (first parameter index, one past the last, first element, one past the last); empty ones dropped
+        self.bucket_ranges = []
+        i = e = 0
+        for grp in groups:
+            ne = sum(p.numel() for p in grp)
+            if grp:
+                self.bucket_ranges.append((i, i + len(grp), e, e + ne))
+            i, e = i + len(grp), e + ne
 
     def buckets(self):
-        """The flat buffer as (early bucket, late bucket); the early one is empty without ``first``."""
-        return self.flat[:self.split], self.flat[self.split:]
-
-    @property
-    def n_first(self):
-        """How many leading parameters form the early bucket."""
-        n, off = 0, 0
-        for p in self.params:
-            if off >= self.split:
-                break
-            off += p.numel()
-            n += 1
-        return n
+        """The flat buffer bucket by bucket, in the order their gradients complete."""
+        return [self.flat[e0:e1] for _, _, e0, e1 in self.bucket_ranges]
 
     def pack(self, lo=0, hi=None):
         """Make ``p.grad`` of parameters [lo, hi) the parameter's view of the flat buffer (zero / copy where it is not

@@ -76,24 +76,30 @@ class TrainStep:
         self.loss = None
         self.pkg = None
         _lib.lib()
+        self._stages = self._stage_fns() if self.two_stage else None
+        self._cut1 = self._cut2 = None
+        self.packed = 0
         side = torch.cuda.Stream(device=dev)
         side.wait_stream(torch.cuda.current_stream(dev))
         with torch.cuda.stream(side):
             for _ in range(max(warmup, 1)):       # also resolves lazy inits (cuBLAS handles, cached tables)
                 self._body()
+            if self.two_stage:
+                self._verify_staging()
         torch.cuda.current_stream(dev).wait_stream(side)
         torch.cuda.synchronize(dev)
         if self.reducer is None:
             for p in self.params:
                 p.grad = None
         self.graph = torch.cuda.CUDAGraph()
-        self.graph_b = None
+        self.stage_graphs = None
         if self.two_stage:
-            with torch.cuda.graph(self.graph):
-                self._stage_a()
-            self.graph_b = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(self.graph_b, pool=self.graph.pool()):
-                self._stage_b()
+            self.stage_graphs = []
+            for k, fn in enumerate(self._stages):
+                g = self.graph if k == 0 else torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, **({} if k == 0 else dict(pool=self.graph.pool()))):
+                    fn()
+                self.stage_graphs.append(g)
         else:
             with torch.cuda.graph(self.graph):
                 self._body()
@@ -111,35 +117,105 @@ class TrainStep:
     def two_stage(self):
         return self.reducer is not None and not self.capture_collective
 
-    def _stage_a(self):
-        """Forward, loss, backward down to the deformed parameters and the SH leaves (whose gradients are then final)."""
+    # The staged backward.  Stage k ends where the gradients of the reducer's bucket k are final:
+    #   0: forward, loss, backward through the rasterizer        -> SH coefficients
+    #   1: blend backward                                        -> per-Gaussian deformation parameters, blend logits
+    #   2: keypoint MLP backward                                 -> keypoints, MLP weights
+    # With fewer buckets (or a model that does not expose its keypoint deltas) the later stages merge.
+    def _stage_fns(self):
         r = self.reducer
+        nb = len(r.bucket_ranges)
+        model = getattr(self.pc, "deformation", None)
+        can_cut_mlp = nb >= 3 and hasattr(model, "keep_kp_deltas")
+
+        def leaves(k):
+            lo, hi, _, _ = r.bucket_ranges[k]
+            return r.params[lo:hi]
+
+        def finish(k, last):
+            lo, hi, _, _ = r.bucket_ranges[k]
+            self.packed += r.pack(lo, len(r.params) if last else hi)
+
+        def stage0():
+            for p in self.params:
+                p.grad = None
+            self.packed = 0                   # diagnostics: gradients that did NOT arrive through a sink
+            if can_cut_mlp:
+                model.keep_kp_deltas = True
+            with grad_sinks(zip(r.params, r.views)):      # looked up while the autograd graph is being built
+                self.pkg = render(self.cam, self.pc, None, self.bg, time=self.t, it=self.iteration,
+                                  capacity=self.capacity)
+                self.loss = self.loss_fn(self.pkg["render"], self.target)
+            if can_cut_mlp:
+                model.keep_kp_deltas = False
+                self._cut2, model._kp_deltas = model._kp_deltas, None
+            deformed = [t for t in self.pkg["deformed"] if t.requires_grad]
+            if nb == 1:
+                self.loss.backward()
+                self.viewspace_grad = self.pkg["viewspace_points"].grad
+                finish(0, True)
+                return
+            early = leaves(0)
+            outs = torch.autograd.grad(self.loss, deformed + early + [self.pkg["viewspace_points"]], allow_unused=True)
+            self._cut1 = [(t, g) for t, g in zip(deformed, outs[:len(deformed)]) if g is not None]
+            for p, g in zip(early, outs[len(deformed):len(deformed) + len(early)]):
+                p.grad = g
+            self.viewspace_grad = outs[-1]
+            finish(0, False)
+
+        def stage1():
+            ts, gs = [t for t, _ in self._cut1], [g for _, g in self._cut1]
+            cut = [t for t in (self._cut2 or ()) if t is not None and t.requires_grad] if can_cut_mlp else []
+            if not cut:
+                if ts:
+                    torch.autograd.backward(ts, gs)
+                finish(1, True)
+                return
+            mine = leaves(1)
+            outs = torch.autograd.grad(ts, cut + mine, grad_outputs=gs, allow_unused=True)
+            self._cut2 = [(t, g) for t, g in zip(cut, outs[:len(cut)]) if g is not None]
+            for p, g in zip(mine, outs[len(cut):]):
+                p.grad = g
+            finish(1, False)
+
+        def stage2():
+            if self._cut2:
+                torch.autograd.backward([t for t, _ in self._cut2], [g for _, g in self._cut2])
+            self._cut2 = None
+            finish(2, True)
+
+        if nb == 1:
+            return [stage0]
+        if not can_cut_mlp:
+            return [stage0, stage1]
+        return [stage0, stage1, stage2]
+
+    def _verify_staging(self):
+        """The staged backward only asks autograd for the leaves of the bucket a stage closes.  A parameter that gets
+        (part of) its gradient in an earlier stage than its bucket says would silently lose it, so the staged result
+        of the warm-up sample is compared once with a plain ``loss.backward()`` before anything is captured."""
+        staged = {id(p): (None if p.grad is None else p.grad.clone()) for p in self.params}
         for p in self.params:
             p.grad = None
-        with grad_sinks(zip(r.params, r.views)):      # looked up while the autograd graph is being built
-            self.pkg = render(self.cam, self.pc, None, self.bg, time=self.t, it=self.iteration, capacity=self.capacity)
-            self.loss = self.loss_fn(self.pkg["render"], self.target)
-        nf = r.n_first
-        deformed = [t for t in self.pkg["deformed"] if t.requires_grad]
-        outs = torch.autograd.grad(self.loss, deformed + r.params[:nf] + [self.pkg["viewspace_points"]],
-                                   allow_unused=True)
-        self._deformed = [(t, g) for t, g in zip(deformed, outs[:len(deformed)]) if g is not None]
-        for p, g in zip(r.params[:nf], outs[len(deformed):len(deformed) + nf]):
-            p.grad = g
-        self.viewspace_grad = outs[-1]
-        self.packed = r.pack(0, nf)           # diagnostics: gradients that did NOT arrive through a sink
-
-    def _stage_b(self):
-        """The deformation backward (blend, keypoint MLP); afterwards every gradient sits in the flat buffer."""
-        r = self.reducer
-        if self._deformed:
-            torch.autograd.backward([t for t, _ in self._deformed], [g for _, g in self._deformed])
-        self.packed += r.pack(r.n_first, None)
+        pkg = render(self.cam, self.pc, None, self.bg, time=self.t, it=self.iteration, capacity=self.capacity)
+        self.loss_fn(pkg["render"], self.target).backward()
+        names = {id(p): n for n, p in self.pc.named_parameters()}
+        for p in self.reducer.params:
+            a, b = staged[id(p)], p.grad
+            if b is None:
+                continue
+            scale = float(b.abs().max())
+            if a is None or float((a - b).abs().max()) > 1e-3 * max(scale, 1e-30):
+                raise RuntimeError(f"TrainStep: the staged backward loses gradient of '{names.get(id(p), '?')}': put it "
+                                   "in the reducer bucket of the stage that produces it (parallel.FlatGradAllReduce "
+                                   "first=/second=) or leave it to the last bucket")
+        for p in self.params:
+            p.grad = None
 
     def _body(self):
         if self.two_stage:
-            self._stage_a()
-            self._stage_b()
+            for fn in self._stages:
+                fn()
             return
         if self.reducer is None:
             for p in self.params:
@@ -204,16 +280,14 @@ class TrainStep:
     def _replay(self):
         if self.two_stage:
             import torch.distributed as dist
-            early, late = self.reducer.buckets()
-            self.graph.replay()
-            w1 = dist.all_reduce(early, op=dist.ReduceOp.SUM, group=self.reducer.group, async_op=True) \
-                if early.numel() else None
-            self.graph_b.replay()             # runs while the early bucket is on the wire
-            w2 = dist.all_reduce(late, op=dist.ReduceOp.SUM, group=self.reducer.group, async_op=True) \
-                if late.numel() else None
-            for w in (w1, w2):
-                if w is not None:
-                    w.wait()
+            buckets, works = self.reducer.buckets(), []
+            last = len(self.stage_graphs) - 1
+            for k, g in enumerate(self.stage_graphs):
+                g.replay()                    # stage k+1 runs while bucket k is on the wire
+                for b in (buckets[k:] if k == last else buckets[k:k + 1]):
+                    works.append(dist.all_reduce(b, op=dist.ReduceOp.SUM, group=self.reducer.group, async_op=True))
+            for w in works:
+                w.wait()
         else:
             self.graph.replay()
         for p, g in zip(self.params, self.grads):     # p.grad may have been replaced / cleared by the caller

@@ -391,9 +391,10 @@ def test_two_stage_step_with_grad_sinks_matches_eager(gplib):
         targets = [(torch.randn(3, H, W, generator=g) * 1e-2).cuda() for _ in cams]
         times = [torch.tensor([0.2 + 0.3 * i], device="cuda") for i in range(len(cams))]
         with_grad = [p for n, p in pc.named_parameters() if not n.endswith("motion_feature")]
-        red = FlatGradAllReduce(with_grad, first=[pc._features_dc, pc._features_rest])
+        red = FlatGradAllReduce(with_grad, first=[pc._features_dc, pc._features_rest],
+                                second=[model._xyz, model._rotation, model._scaling, model._opacity, model.weights_model.logits])
         step = TrainStep(pc, cams[0], capacity=400_000, bg=bg, reducer=red)
-        assert step.two_stage and step.graph_b is not None
+        assert step.two_stage and len(step.stage_graphs) == 3 and len(red.buckets()) == 3
         assert step.packed == 0            # every gradient reached the flat buffer through a sink: nothing filled or copied
         for cam, t, tgt in zip(cams, times, targets):
             loss_g = float(step(cam, t, tgt))

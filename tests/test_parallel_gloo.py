@@ -67,7 +67,7 @@ def _bucket_worker(rank, world, port, out):
     a, b, c = (torch.nn.Parameter(torch.randn(4, 3)), torch.nn.Parameter(torch.randn(6)), torch.nn.Parameter(torch.randn(2, 5)))
     red = FlatGradAllReduce([a, b, c], first=[c])           # c's gradient is "ready early": it leads the buffer
     early, late = red.buckets()
-    layout = (red.params[0] is c, red.n_first, early.numel(), late.numel())
+    layout = (red.params[0] is c, red.bucket_ranges[0][1], early.numel(), late.numel())
     # a producer that looks its destination up (what the autograd Functions do in their forward) writes in place
     with grad_sinks(zip(red.params, red.views)):
         dst = sink_for(c)
@@ -76,9 +76,9 @@ def _bucket_worker(rank, world, port, out):
     g.copy_(torch.full((2, 5), float(rank + 1)))
     c.grad = g
     a.grad = torch.full((4, 3), 10.0 * (rank + 1))          # arrives in a tensor of its own: packed by copy; b: no gradient
-    moved_early = red.pack(0, red.n_first)
+    moved_early = red.pack(0, red.bucket_ranges[0][1])
     w1 = dist.all_reduce(early, async_op=True)              # the early bucket goes first ...
-    moved_late = red.pack(red.n_first, None)
+    moved_late = red.pack(red.bucket_ranges[0][1], None)
     w2 = dist.all_reduce(late, async_op=True)               # ... the rest follows (pipeline.TrainStep._replay)
     w1.wait(); w2.wait()
     if rank == 0:
