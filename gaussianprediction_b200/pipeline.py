@@ -76,6 +76,7 @@ class TrainStep:
         self.loss = None
         self.pkg = None
         _lib.lib()
+        self.max_stages = int(__import__("os").environ.get("GP_TRAINSTEP_STAGES", "3"))   # A/B knob for the bench
         self._stages = self._stage_fns() if self.two_stage else None
         self._cut1 = self._cut2 = None
         self.packed = 0
@@ -126,7 +127,7 @@ class TrainStep:
         r = self.reducer
         nb = len(r.bucket_ranges)
         model = getattr(self.pc, "deformation", None)
-        can_cut_mlp = nb >= 3 and hasattr(model, "keep_kp_deltas")
+        can_cut_mlp = nb >= 3 and hasattr(model, "keep_kp_deltas") and self.max_stages >= 3
 
         def leaves(k):
             lo, hi, _, _ = r.bucket_ranges[k]
