@@ -5,7 +5,7 @@ The library is built in-tree by ``python -m gaussianprediction_b200.build`` (or 
 """
 import ctypes
 import os
-from ctypes import POINTER, c_char_p, c_float, c_int, c_longlong, c_size_t, c_void_p
+from ctypes import POINTER, c_char_p, c_double, c_float, c_int, c_longlong, c_size_t, c_void_p
 
 PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(PKG_DIR, "libgp_b200.so")
@@ -28,6 +28,12 @@ class MlpCfg(ctypes.Structure):
     """Mirror of ``gp_mlp_cfg``."""
     _fields_ = [("rows", c_int), ("feature_dim", c_int), ("xyz_freq", c_int), ("time_freq", c_int), ("depth", c_int),
                 ("width", c_int), ("out_dim", c_int), ("normalize_q", c_int)]
+
+
+class AdamTensor(ctypes.Structure):
+    """Mirror of ``gp_adam_tensor``."""
+    _fields_ = [("param", c_void_p), ("grad", c_void_p), ("exp_avg", c_void_p), ("exp_avg_sq", c_void_p),
+                ("n", c_longlong), ("lr", c_float), ("step", c_int)]
 
 
 HDR_NUM_RENDERED, HDR_OVERFLOW, HDR_NUM_POINTS, HDR_NUM_SORTED, HDR_WORDS = 0, 1, 2, 3, 64
@@ -66,6 +72,8 @@ SIGNATURES = {
     "gp_kpmlp_sizes": (c_int, [POINTER(MlpCfg), POINTER(c_size_t), POINTER(c_size_t)]),
     "gp_kpmlp_forward": (c_int, [POINTER(MlpCfg), _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "gp_kpmlp_backward": (c_int, [POINTER(MlpCfg), _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
+    "gp_adam_step": (c_int, [c_int, POINTER(AdamTensor), c_double, c_double, c_double, _P]),
+    "gp_densification_stats": (c_int, [c_int, _P, _P, _P, _P, _P, _P, _P]),
     "gp_raster_export_binning": (c_int, [POINTER(RasterCfg), _P, _P, c_longlong, _P, _P, _P]),
 }
 

@@ -262,6 +262,29 @@ int gp_kpmlp_backward(const gp_mlp_cfg* cfg, const float* kp_xyz, const float* t
                       float* dL_dxyz /*[rows,3]*/, float* dL_dfeat /*[rows,F]*/, float* const* dL_dweights,
                       float* const* dL_dbiases, gp_stream_t stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * After the backward.  gp_adam_step stands in for `gaussians.optimizer.step()` (train.py:192-194):
+ * torch.optim.Adam without weight decay / amsgrad as scene/gaussian_model.py:452 builds it, one launch for every tensor
+ * of the step.  `tensors` is a HOST array; per tensor its own lr and its 1-based step count (the bias corrections are
+ * computed from it in double on the host, as torch does).  exp_avg / exp_avg_sq are the optimizer state of that name.
+ * gp_densification_stats stands in for train.py:166-167 / scene/gaussian_model.py:756-760: for every Gaussian with
+ * radii > 0: max_radii2D = max(max_radii2D, radii); g = |viewspace_grad.xy|; xyz_gradient_accum += g; denom += 1;
+ * xyz_gradient_accum_max = max(., g).  max_radii2D and xyz_gradient_accum_max may be NULL.
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct gp_adam_tensor {
+  float* param;
+  const float* grad;
+  float* exp_avg;
+  float* exp_avg_sq;
+  long long n; /* elements */
+  float lr;
+  int step;    /* 1 for the first update */
+} gp_adam_tensor;
+int gp_adam_step(int count, const gp_adam_tensor* tensors, double beta1, double beta2, double eps, gp_stream_t stream);
+int gp_densification_stats(int P, const float* viewspace_grad /*[P,3]*/, const int* radii /*[P]*/,
+                           float* max_radii2D /*[P]*/, float* xyz_gradient_accum /*[P,1]*/, float* denom /*[P,1]*/,
+                           float* xyz_gradient_accum_max /*[P,1]*/, gp_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

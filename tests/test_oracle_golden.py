@@ -152,3 +152,46 @@ def test_loss_oracle_vs_reference_functions():
     loss.backward()
     assert abs(float(loss) - float(g["loss"])) <= 1e-6
     assert rel(img.grad.numpy(), g["grad"]) <= 1e-5
+
+
+def test_adam_oracle_vs_torch_optim_adam():
+    """oracle/optim_oracle.adam_step against torch.optim.Adam (what the reference's optimizer.step() is), CPU."""
+    import torch
+    from oracle import optim_oracle as oo
+    torch.manual_seed(3)
+    ps = [torch.nn.Parameter(torch.randn(37, 3)), torch.nn.Parameter(torch.randn(11))]
+    lrs = [1.6e-4, 2.5e-3]
+    opt = torch.optim.Adam([{"params": [p], "lr": lr} for p, lr in zip(ps, lrs)], lr=0.0, eps=1e-15)
+    mine = [dict(p=p.detach().numpy().copy(), m=np.zeros(p.shape, np.float32), v=np.zeros(p.shape, np.float32)) for p in ps]
+    for step in range(1, 6):
+        for p, st, lr in zip(ps, mine, lrs):
+            g = torch.randn(p.shape) * (10.0 ** (-step))
+            p.grad = g.clone()
+            oo.adam_step(st["p"], g.numpy(), st["m"], st["v"], step, lr)
+        opt.step()
+    for p, st in zip(ps, mine):
+        assert np.abs(st["p"] - p.detach().numpy()).max() <= 2e-6 * max(1.0, float(p.detach().abs().max()))
+        assert np.allclose(st["m"], opt.state[p]["exp_avg"].numpy(), rtol=1e-5, atol=1e-12)
+        assert np.allclose(st["v"], opt.state[p]["exp_avg_sq"].numpy(), rtol=1e-5, atol=1e-20)
+
+
+def test_densification_stats_oracle_vs_reference_expressions():
+    """oracle/optim_oracle.densification_stats against train.py:166-167 + scene/gaussian_model.py:756-760 restated."""
+    import torch
+    from oracle import optim_oracle as oo
+    g = torch.Generator().manual_seed(5)
+    P = 500
+    radii = (torch.rand(P, generator=g) * 30).int() * (torch.rand(P, generator=g) > 0.3).int()
+    vgrad = torch.randn(P, 3, generator=g) * 1e-3
+    max_r = torch.rand(P, generator=g) * 20
+    accum, denom, amax = torch.rand(P, 1, generator=g), torch.rand(P, 1, generator=g).round(), torch.rand(P, 1, generator=g) * 1e-3
+    o = [t.numpy().copy() for t in (max_r, accum, denom, amax)]
+    oo.densification_stats(vgrad.numpy(), radii.numpy(), *o)
+    vis = radii > 0
+    max_r[vis] = torch.max(max_r[vis], radii[vis])                        # train.py:166
+    grad = torch.norm(vgrad[vis, :2], dim=-1, keepdim=True)                # gaussian_model.py:757
+    accum[vis] += grad
+    denom[vis] += 1
+    amax[vis] = torch.where(grad > amax[vis], grad, amax[vis])
+    for a, b in zip(o, (max_r, accum, denom, amax)):
+        assert np.allclose(a, b.numpy(), rtol=1e-6, atol=0)
