@@ -383,6 +383,11 @@ def workload_stats(runner):
     return out
 
 
+# dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full captures
+# (profiles/r1_ncu_full.md), C2 workload only; other workloads report null
+NCU_DRAM_BYTES = {"c2_dnerf_100k_800x800": {"gp_render_bwd_kernel": 24.19e6, "gp_render_fwd_kernel": 6.97e6}}
+
+
 def roofline_for(prof, stats, wl, steps, peaks):
     """Dominant kernel of the step and its achieved rate.  Algorithmic work per launch:
     HBM kernels in bytes (SURVEY.md §8d per-unit figures), blend kernels in FP32 operations per evaluated
@@ -416,7 +421,9 @@ def roofline_for(prof, stats, wl, steps, peaks):
     else:
         ach, peak, unit = w / sec / 1e12, fp32_peak, "TFLOP/s"
     return {"kernel": top, "bound": kind, "achieved": round(ach, 3), "peak": round(peak, 3), "unit": unit,
-            "frac": round(ach / peak, 4), "traffic": None, "ms_per_launch": round(per[top], 4),
+            "frac": round(ach / peak, 4), "traffic": NCU_DRAM_BYTES.get(wl.get("name"), {}).get(top),
+            "traffic_unit": "bytes/launch (ncu dram read+write, profiles/r1_ncu_full.md)",
+            "ms_per_launch": round(per[top], 4),
             "share_of_kernel_time": round(tot[top] / sum(tot.values()), 4),
             "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if kind == "hbm" else
             "derived 148 SM x 128 lanes x 2 x sm_max_mhz (FP32 FMA pipe; not in MEASURED_PEAKS.json)"}, table
@@ -484,7 +491,7 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
-    wl = WORKLOADS[args.workload]
+    wl = dict(WORKLOADS[args.workload], name=args.workload)
     steps, warmup = args.steps, max(args.warmup, 3)
 
     if args.impl == "reference" and rank != 0:
