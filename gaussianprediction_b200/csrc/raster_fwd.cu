@@ -182,6 +182,7 @@ gp_preprocess_kernel(int P, int D, int M, const float* __restrict__ means3D, con
                      int* __restrict__ radii, int staged) {
   extern __shared__ __align__(16) float s_tiles[];  // staged: [8 warps][GP_SH_TILE]
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (blockIdx.x == 0) gp_rs_reset_by_block(g.radix);  // the depth sort that follows needs zeroed histograms
   if (idx == 0) {
     g.hdr[GP_HDR_NUM_POINTS] = P;
     g.hdr[GP_HDR_NUM_RENDERED] = 0;
@@ -525,7 +526,7 @@ extern "C" int gp_raster_preprocess(const gp_raster_cfg* cfg, const float* means
       cfg->prefiltered, gx, gy, g, radii, staged));
   GP_LAUNCH_CHECK();
   // depth sort: P keys, all 32 bits; result lands back in buffer 0 (4 passes)
-  gp_radix_sort_pairs(g.dkeys, g.dvals, g.hdr + GP_HDR_NUM_POINTS, 0, 32, g.radix, stream);
+  gp_radix_sort_pairs(g.dkeys, g.dvals, g.hdr + GP_HDR_NUM_POINTS, 0, 32, g.radix, stream, /*reset=*/false);
   GP_LAUNCH_CHECK();
   const int nb = (P + GP_SCAN_BLOCK - 1) / GP_SCAN_BLOCK;
   GP_KERNEL("gp_block_sum_kernel", stream, gp_block_sum_kernel<<<nb, GP_SCAN_BLOCK, 0, stream>>>(P, g.dvals[0], g.tiles_touched, g.block_sums));
@@ -546,11 +547,19 @@ extern "C" int gp_raster_num_rendered(const void* geom_ws, gp_stream_t stream_, 
   return GP_OK;
 }
 
-__global__ void gp_set_capacity_kernel(int* hdr, long long capacity) {
-  const long long R = hdr[GP_HDR_NUM_RENDERED];
-  const bool over = R > capacity || R >= 0x7FFFFFFFll;
-  hdr[GP_HDR_OVERFLOW] = over ? 1 : 0;
-  hdr[GP_HDR_NUM_SORTED] = over ? 0 : (int)R;
+// Decides whether the frame fits the binning buffers, and clears what the next kernels accumulate into: the tile
+// ranges (tiles without instances keep (0,0)) and the histograms of the tile sort.
+__global__ void gp_set_capacity_kernel(int* hdr, long long capacity, uint2* ranges, int tiles, GpRadixTemp tile_radix) {
+  if (blockIdx.x == 0) {
+    gp_rs_reset_by_block(tile_radix);
+    if (threadIdx.x == 0) {
+      const long long R = hdr[GP_HDR_NUM_RENDERED];
+      const bool over = R > capacity || R >= 0x7FFFFFFFll;
+      hdr[GP_HDR_OVERFLOW] = over ? 1 : 0;
+      hdr[GP_HDR_NUM_SORTED] = over ? 0 : (int)R;
+    }
+  }
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < tiles; i += gridDim.x * blockDim.x) ranges[i] = make_uint2(0u, 0u);
 }
 
 extern "C" int gp_raster_render(const gp_raster_cfg* cfg, const float* bg, const float* colors_precomp, void* geom_ws,
@@ -567,15 +576,15 @@ extern "C" int gp_raster_render(const gp_raster_cfg* cfg, const float* bg, const
   const unsigned gx = (W + GP_TILE_X - 1) / GP_TILE_X, gy = (H + GP_TILE_Y - 1) / GP_TILE_Y;
   const int nb = (P + GP_SCAN_BLOCK - 1) / GP_SCAN_BLOCK;
 
-  GP_KERNEL("gp_set_capacity_kernel", stream, gp_set_capacity_kernel<<<1, 1, 0, stream>>>(g.hdr, capacity));
+  GP_KERNEL("gp_set_capacity_kernel", stream,
+            gp_set_capacity_kernel<<<8, 256, 0, stream>>>(g.hdr, capacity, im.ranges, (int)(gx * gy), b.radix));
   GP_LAUNCH_CHECK();
   GP_KERNEL("gp_duplicate_kernel", stream, gp_duplicate_kernel<<<nb, GP_SCAN_BLOCK, 0, stream>>>(P, g.dvals[0], g.tiles_touched, g.xy_depth, radii, g.block_sums,
                                                         g.hdr, gx, gy, b.tkeys[0], b.tvals[0]));
   GP_LAUNCH_CHECK();
   const int bits = gp_tile_bits(W, H);
-  const int sel = gp_radix_sort_pairs(b.tkeys, b.tvals, g.hdr + GP_HDR_NUM_SORTED, 0, bits, b.radix, stream);
+  const int sel = gp_radix_sort_pairs(b.tkeys, b.tvals, g.hdr + GP_HDR_NUM_SORTED, 0, bits, b.radix, stream, /*reset=*/false);
   GP_LAUNCH_CHECK();
-  GP_CUDA_TRY(cudaMemsetAsync(im.ranges, 0, (size_t)gx * gy * sizeof(uint2), stream));
   GP_KERNEL("gp_tile_ranges_kernel", stream, gp_tile_ranges_kernel<<<148 * 4, 256, 0, stream>>>(g.hdr, b.tkeys[sel], im.ranges));
   GP_LAUNCH_CHECK();
   GP_KERNEL("gp_render_fwd_kernel", stream, gp_render_fwd_kernel<<<gx * gy, GP_TILE_PIX, 0, stream>>>(im.ranges, b.tvals[sel], W, H, gx, g.xy_depth,
