@@ -47,6 +47,34 @@ __device__ __forceinline__ void softmax_k(const float* __restrict__ logit, int K
     if (k < K) w[k] *= inv;
 }
 
+// One Gaussian's 2K logits and K neighbour indices into registers.  With the reference's nearest_num = 6 the rows are
+// 48 and 24 bytes: three 128-bit and three 64-bit loads instead of 18 scalar ones.
+template <int KMAX, bool VEC6>
+__device__ __forceinline__ void load_row(int i, int K, const float* __restrict__ logits, const int* __restrict__ idx32,
+                                         const long long* __restrict__ idx64, int Kp, float* lg, int* jj) {
+  if (VEC6) {
+    const float4* l4 = reinterpret_cast<const float4*>(logits + (size_t)i * 12);
+    const float4 a = __ldg(l4), b = __ldg(l4 + 1), c = __ldg(l4 + 2);
+    lg[0] = a.x; lg[1] = a.y; lg[2] = a.z; lg[3] = a.w; lg[4] = b.x; lg[5] = b.y;
+    lg[KMAX + 0] = b.z; lg[KMAX + 1] = b.w; lg[KMAX + 2] = c.x; lg[KMAX + 3] = c.y; lg[KMAX + 4] = c.z; lg[KMAX + 5] = c.w;
+    const int2* j2 = reinterpret_cast<const int2*>(idx32 + (size_t)i * 6);
+    const int2 p = __ldg(j2), q = __ldg(j2 + 1), r = __ldg(j2 + 2);
+    jj[0] = p.x; jj[1] = p.y; jj[2] = q.x; jj[3] = q.y; jj[4] = r.x; jj[5] = r.y;
+  } else {
+#pragma unroll
+    for (int k = 0; k < KMAX; k++) {
+      if (k < K) {
+        lg[k] = logits[(size_t)i * 2 * K + k];
+        lg[KMAX + k] = logits[(size_t)i * 2 * K + K + k];
+        jj[k] = idx32 ? idx32[(size_t)i * K + k] : (int)idx64[(size_t)i * K + k];
+      }
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < KMAX; k++)
+    if (k < K && (jj[k] < 0 || jj[k] >= Kp)) jj[k] = -1;
+}
+
 // s_kp layout: [Kp][8] = (dx, dy, dz, 0, qw, qx, qy, qz)
 __device__ __forceinline__ void stage_keypoints(float* s_kp, int Kp, const float* __restrict__ kp_dxyz,
                                                 const float* __restrict__ kp_dq) {
@@ -59,8 +87,10 @@ __device__ __forceinline__ void stage_keypoints(float* s_kp, int Kp, const float
   }
 }
 
-__global__ void __launch_bounds__(GP_BLEND_THREADS)
-gp_blend_fwd_kernel(int N, int Kp, int K, const float* __restrict__ logits, const int* __restrict__ idx32,
+// VEC6: K == 6 with aligned rows (the host checks): compile-time K, vector row loads.  Otherwise K at run time.
+template <bool VEC6>
+__global__ void __launch_bounds__(GP_BLEND_THREADS, VEC6 ? 4 : 2)
+gp_blend_fwd_kernel(int N, int Kp, int Kr, const float* __restrict__ logits, const int* __restrict__ idx32,
                     const long long* __restrict__ idx64, const float* __restrict__ kp_dxyz,
                     const float* __restrict__ kp_dq, const float* __restrict__ xyz, const float* __restrict__ rot,
                     const float* __restrict__ scaling, const float* __restrict__ opacity, float* __restrict__ xyz_t,
@@ -68,18 +98,21 @@ gp_blend_fwd_kernel(int N, int Kp, int K, const float* __restrict__ logits, cons
   extern __shared__ __align__(16) float s_kp[];
   stage_keypoints(s_kp, Kp, kp_dxyz, kp_dq);
   __syncthreads();
+  const int K = VEC6 ? 6 : Kr;
   for (int i = blockIdx.x * GP_BLEND_THREADS + threadIdx.x; i < N; i += gridDim.x * GP_BLEND_THREADS) {
   float wx[GP_BLEND_KMAX], wr[GP_BLEND_KMAX];
-  const float* lg = logits + (size_t)i * 2 * K;
-  softmax_k<GP_BLEND_KMAX>(lg, K, wx);
-  softmax_k<GP_BLEND_KMAX>(lg + K, K, wr);
+  float lgr[2 * GP_BLEND_KMAX];
+  int jr[GP_BLEND_KMAX];
+  load_row<GP_BLEND_KMAX, VEC6>(i, K, logits, idx32, idx64, Kp, lgr, jr);
+  softmax_k<GP_BLEND_KMAX>(lgr, K, wx);
+  softmax_k<GP_BLEND_KMAX>(lgr + GP_BLEND_KMAX, K, wr);
   float dx = 0.f, dy = 0.f, dz = 0.f;
   float4 dq = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
   for (int k = 0; k < GP_BLEND_KMAX; k++) {
     if (k < K) {
-      const int j = idx32 ? idx32[(size_t)i * K + k] : (int)idx64[(size_t)i * K + k];
-      if (j >= 0 && j < Kp) {
+      const int j = jr[k];
+      if (j >= 0) {
         const float4 a = *(const float4*)(s_kp + 8 * j);
         const float4 b = *(const float4*)(s_kp + 8 * j + 4);
         dx += wx[k] * a.x; dy += wx[k] * a.y; dz += wx[k] * a.z;
@@ -118,8 +151,9 @@ __device__ __forceinline__ float4 normalize_bwd(const float4 v, const float4 g) 
 
 // Backward of gp_blend_fwd_kernel.  Keypoint gradients (Kp x 7) are accumulated in shared memory per
 // block and flushed with one atomicAdd per touched entry; g_kp_* must be zeroed by the caller.
-__global__ void __launch_bounds__(GP_BLEND_THREADS)
-gp_blend_bwd_kernel(int N, int Kp, int K, const float* __restrict__ logits, const int* __restrict__ idx32,
+template <bool VEC6>
+__global__ void __launch_bounds__(GP_BLEND_THREADS, VEC6 ? 4 : 2)
+gp_blend_bwd_kernel(int N, int Kp, int Kr, const float* __restrict__ logits, const int* __restrict__ idx32,
                     const long long* __restrict__ idx64, const float* __restrict__ kp_dxyz,
                     const float* __restrict__ kp_dq, const float* __restrict__ rot, const float* __restrict__ s_t,
                     const float* __restrict__ o_t, const float* __restrict__ g_xyz_t, const float* __restrict__ g_q_t,
@@ -132,19 +166,19 @@ gp_blend_bwd_kernel(int N, int Kp, int K, const float* __restrict__ logits, cons
   stage_keypoints(s_kp, Kp, kp_dxyz, kp_dq);
   for (int e = threadIdx.x; e < Kp * 9; e += blockDim.x) s_g[e] = 0.f;
   __syncthreads();
+  const int K = VEC6 ? 6 : Kr;
   for (int i = blockIdx.x * GP_BLEND_THREADS + threadIdx.x; i < N; i += gridDim.x * GP_BLEND_THREADS) {
     float wx[GP_BLEND_KMAX], wr[GP_BLEND_KMAX];
+    float lgr[2 * GP_BLEND_KMAX];
     int jj[GP_BLEND_KMAX];
-    const float* lg = logits + (size_t)i * 2 * K;
-    softmax_k<GP_BLEND_KMAX>(lg, K, wx);
-    softmax_k<GP_BLEND_KMAX>(lg + K, K, wr);
+    load_row<GP_BLEND_KMAX, VEC6>(i, K, logits, idx32, idx64, Kp, lgr, jj);
+    softmax_k<GP_BLEND_KMAX>(lgr, K, wx);
+    softmax_k<GP_BLEND_KMAX>(lgr + GP_BLEND_KMAX, K, wr);
     float4 dq = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
     for (int k = 0; k < GP_BLEND_KMAX; k++) {
       if (k < K) {
-        int j = idx32 ? idx32[(size_t)i * K + k] : (int)idx64[(size_t)i * K + k];
-        if (j < 0 || j >= Kp) j = -1;
-        jj[k] = j;
+        const int j = jj[k];
         if (j >= 0) {
           const float4 b = *(const float4*)(s_kp + 8 * j + 4);
           dq.x += wr[k] * b.x; dq.y += wr[k] * b.y; dq.z += wr[k] * b.z; dq.w += wr[k] * b.w;
@@ -199,7 +233,12 @@ gp_blend_bwd_kernel(int N, int Kp, int K, const float* __restrict__ logits, cons
         sr += wr[k] * gwr[k];
       }
     }
-    if (g_logits) {
+    if (g_logits && VEC6) {
+      float4* o4 = reinterpret_cast<float4*>(g_logits + (size_t)i * 12);
+      o4[0] = make_float4(wx[0] * (gwx[0] - sx), wx[1] * (gwx[1] - sx), wx[2] * (gwx[2] - sx), wx[3] * (gwx[3] - sx));
+      o4[1] = make_float4(wx[4] * (gwx[4] - sx), wx[5] * (gwx[5] - sx), wr[0] * (gwr[0] - sr), wr[1] * (gwr[1] - sr));
+      o4[2] = make_float4(wr[2] * (gwr[2] - sr), wr[3] * (gwr[3] - sr), wr[4] * (gwr[4] - sr), wr[5] * (gwr[5] - sr));
+    } else if (g_logits) {
 #pragma unroll
       for (int k = 0; k < GP_BLEND_KMAX; k++) {
         if (k < K) {
@@ -253,10 +292,11 @@ gp_dense_weights_kernel(int N, int Kp, int K, const float* __restrict__ logits, 
   }
 }
 
-// persistent grid: two blocks per SM, each staging the keypoint table once and flushing its keypoint gradients once
-static int gp_blend_grid(int N) {
+// persistent grid: `per_sm` blocks per SM (what registers and shared memory allow), each staging the keypoint table once
+// and flushing its keypoint gradients once; the kernels are latency bound, so resident warps are what hides the loads
+static int gp_blend_grid(int N, int per_sm) {
   const int need = (N + GP_BLEND_THREADS - 1) / GP_BLEND_THREADS;
-  return need < 148 * 2 ? need : 148 * 2;
+  return need < 148 * per_sm ? need : 148 * per_sm;
 }
 
 static int blend_check(int N, int Kp, int K) {
@@ -277,9 +317,11 @@ extern "C" int gp_blend_forward(int N, int Kp, int K, const float* logits, const
   if (Kp > 0 && (!kp_delta_xyz || !kp_delta_q)) return GP_ERR_BAD_ARG;
   if ((s_t && !scaling) || (o_t && !opacity)) return GP_ERR_BAD_ARG;
   const size_t smem = (size_t)Kp * 8 * 4;
+  const bool vec6 = K == 6 && idx32 && ((((size_t)logits) & 15) == 0) && ((((size_t)idx32) & 7) == 0);
+  auto kernel = vec6 ? gp_blend_fwd_kernel<true> : gp_blend_fwd_kernel<false>;
   if (smem > 48 * 1024)
-    GP_CUDA_TRY(cudaFuncSetAttribute(gp_blend_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  GP_KERNEL("gp_blend_fwd_kernel", (cudaStream_t)stream_, gp_blend_fwd_kernel<<<gp_blend_grid(N), GP_BLEND_THREADS, smem, (cudaStream_t)stream_>>>(
+    GP_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  GP_KERNEL("gp_blend_fwd_kernel", (cudaStream_t)stream_, kernel<<<gp_blend_grid(N, vec6 ? 4 : 2), GP_BLEND_THREADS, smem, (cudaStream_t)stream_>>>(
       N, Kp, K, logits, idx32, idx64, kp_delta_xyz, kp_delta_q, xyz, rot, scaling, opacity, xyz_t, q_t, s_t, o_t));
   GP_LAUNCH_CHECK();
   return GP_OK;
@@ -300,9 +342,12 @@ extern "C" int gp_blend_backward(int N, int Kp, int K, const float* logits, cons
   if (!logits || (!idx32 && !idx64) || !rot || !kp_delta_xyz || !kp_delta_q) return GP_ERR_BAD_ARG;
   if ((g_scaling && g_s_t && !s_t) || (g_opacity && !o_t)) return GP_ERR_BAD_ARG;
   const size_t smem = (size_t)Kp * 17 * 4;
+  const bool vec6 = K == 6 && idx32 && ((((size_t)logits) & 15) == 0) && ((((size_t)idx32) & 7) == 0) &&
+                    ((((size_t)g_logits) & 15) == 0);
+  auto kernel = vec6 ? gp_blend_bwd_kernel<true> : gp_blend_bwd_kernel<false>;
   if (smem > 48 * 1024)
-    GP_CUDA_TRY(cudaFuncSetAttribute(gp_blend_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  GP_KERNEL("gp_blend_bwd_kernel", stream, gp_blend_bwd_kernel<<<gp_blend_grid(N), GP_BLEND_THREADS, smem, stream>>>(
+    GP_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  GP_KERNEL("gp_blend_bwd_kernel", stream, kernel<<<gp_blend_grid(N, vec6 ? 4 : 2), GP_BLEND_THREADS, smem, stream>>>(
       N, Kp, K, logits, idx32, idx64, kp_delta_xyz, kp_delta_q, rot, s_t, o_t, g_xyz_t, g_q_t, g_s_t, g_o_t, g_logits,
       g_xyz, g_rot, g_scaling, g_opacity, g_kp_delta_xyz, g_kp_delta_q));
   GP_LAUNCH_CHECK();
