@@ -89,36 +89,46 @@ gp_rs_prepare_kernel(const uint32_t* __restrict__ keys, const int* __restrict__ 
   }
 }
 
+// STEPS 32-key steps per warp per tile: tile = 8 warps x STEPS x 32 keys.  Small sorts use 1024-key tiles (enough
+// tiles to occupy the SMs), large ones 4096-key tiles (fewer tickets / look-backs / barriers per key, and longer runs
+// of equal digits per tile: the keys of a tile are first put in digit order in shared memory, then written out by
+// consecutive threads, so a run of m keys with the same digit is one contiguous 4m-byte store).
+template <int STEPS>
 static __global__ void __launch_bounds__(GP_RS_THREADS)
 gp_rs_pass_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                   uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, const int* __restrict__ n_ptr,
                   int shift, int pass, GpRadixTemp t) {
+  constexpr int TILE = GP_RS_WARPS * STEPS * 32;
   __shared__ uint32_t wcnt[GP_RS_WARPS][GP_RS_RADIX];
-  __shared__ uint32_t tile_off[GP_RS_RADIX];
+  __shared__ uint32_t gshift[GP_RS_RADIX];   // (global position of the tile's first key of digit d) - (its slot in the tile)
+  __shared__ uint32_t tstart[GP_RS_RADIX];   // slot of the tile's first key of digit d
   __shared__ uint32_t digit_base[GP_RS_RADIX];
   __shared__ uint32_t warp_tot[GP_RS_WARPS];
+  __shared__ uint32_t sk[TILE], sv[TILE];
   __shared__ int s_tile;
   const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
   const int n = *n_ptr;
-  const int ntiles = (n + GP_RS_TILE - 1) / GP_RS_TILE;
+  const int ntiles = (n + TILE - 1) / TILE;
   if ((int)blockIdx.x >= ntiles) return;  // tickets are handed out in order: this block could only draw a tile >= ntiles
   volatile uint32_t* status = t.status + (size_t)pass * t.tiles_max * GP_RS_RADIX;
 
-  // exclusive scan of this pass's digit histogram -> first output position of every digit
-  {
-    const uint32_t v = t.hist[pass * GP_RS_RADIX + tid];
+  // exclusive scan over the 256 digits of one value per thread (thread = digit)
+  auto digit_scan = [&](uint32_t v) -> uint32_t {
     uint32_t incl = v;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
       const uint32_t y = __shfl_up_sync(0xffffffffu, incl, o);
       if (lane >= o) incl += y;
     }
+    __syncthreads();                       // warp_tot may still be read from the previous use
     if (lane == 31) warp_tot[w] = incl;
     __syncthreads();
     uint32_t wb = 0;
     for (int j = 0; j < w; j++) wb += warp_tot[j];
-    digit_base[tid] = wb + incl - v;
-  }
+    return wb + incl - v;
+  };
+  // this pass's digit histogram -> first output position of every digit
+  digit_base[tid] = digit_scan(t.hist[pass * GP_RS_RADIX + tid]);
   for (;;) {
     __syncthreads();
     if (tid == 0) s_tile = (int)atomicAdd(&t.tickets[pass], 1u);
@@ -127,16 +137,16 @@ gp_rs_pass_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restri
     __syncthreads();
     const int tile = s_tile;
     if (tile >= ntiles) break;
-    const int base = tile * GP_RS_TILE + w * (GP_RS_STEPS * 32);
-    uint32_t k[GP_RS_STEPS], v[GP_RS_STEPS], local[GP_RS_STEPS];
+    const int base = tile * TILE + w * (STEPS * 32);
+    uint32_t k[STEPS], v[STEPS], local[STEPS];
 #pragma unroll
-    for (int u = 0; u < GP_RS_STEPS; u++) {
+    for (int u = 0; u < STEPS; u++) {
       const int i = base + u * 32 + lane;
       k[u] = i < n ? __ldg(keys_in + i) : 0u;
       v[u] = i < n ? __ldg(vals_in + i) : 0u;
     }
 #pragma unroll
-    for (int u = 0; u < GP_RS_STEPS; u++) {
+    for (int u = 0; u < STEPS; u++) {
       const int i = base + u * 32 + lane;
       const bool valid = i < n;
       const uint32_t d = valid ? ((k[u] >> shift) & 0xFFu) : 0x100u;
@@ -157,6 +167,7 @@ gp_rs_pass_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restri
       run += c;
     }
     status[(size_t)tile * GP_RS_RADIX + tid] = GP_RS_FLAG_AGG | run;
+    const uint32_t slot0 = digit_scan(run);  // slot of this digit's first key in the tile (overlaps the look-back latency)
     // look-back: walk the earlier tiles until one has published an inclusive prefix.  The status words of a window of
     // GP_RS_WINDOW tiles are fetched together (independent loads: one L2 round trip instead of one per tile); an entry
     // that is not published yet is polled on its own.  Early in a pass all tiles run at once and nothing but
@@ -182,20 +193,36 @@ gp_rs_pass_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restri
       if (done) break;
     }
     status[(size_t)tile * GP_RS_RADIX + tid] = GP_RS_FLAG_PREFIX | (excl + run);
-    tile_off[tid] = digit_base[tid] + excl;
+    tstart[tid] = slot0;
+    gshift[tid] = digit_base[tid] + excl - slot0;
     __syncthreads();
+    // keys into digit order inside the tile
 #pragma unroll
-    for (int u = 0; u < GP_RS_STEPS; u++) {
+    for (int u = 0; u < STEPS; u++) {
       const int i = base + u * 32 + lane;
       if (i < n) {
         const uint32_t d = (k[u] >> shift) & 0xFFu;
-        const uint32_t pos = tile_off[d] + wcnt[w][d] + local[u];
-        keys_out[pos] = k[u];
-        vals_out[pos] = v[u];
+        const uint32_t slot = tstart[d] + wcnt[w][d] + local[u];
+        sk[slot] = k[u];
+        sv[slot] = v[u];
+      }
+    }
+    __syncthreads();
+    const int nt = min(TILE, n - tile * TILE);
+#pragma unroll
+    for (int u = 0; u < STEPS * 32 / (GP_RS_THREADS / GP_RS_WARPS); u++) {
+      const int slot = u * GP_RS_THREADS + tid;
+      if (slot < nt) {
+        const uint32_t key = sk[slot];
+        const uint32_t pos = gshift[(key >> shift) & 0xFFu] + (uint32_t)slot;
+        keys_out[pos] = key;
+        vals_out[pos] = sv[slot];
       }
     }
   }
 }
+
+#define GP_RS_BIG_SORT (1 << 19)  // from this many keys (upper bound known to the host) on: 4096-key tiles
 
 // Sort bits [begin_bit, end_bit) of keys (at most 32 bits = 4 passes).  keys[0]/vals[0] hold the input; buffers
 // ping-pong.  Returns the index (0/1) of the buffer pair holding the sorted result.
@@ -207,10 +234,10 @@ static inline int gp_radix_sort_pairs(uint32_t* keys[2], uint32_t* vals[2], cons
             gp_rs_prepare_kernel<<<GP_RS_BLOCKS, GP_RS_THREADS, 0, stream>>>(keys[0], n_ptr, begin_bit, passes, tmp));
   int sel = 0;
   for (int p = 0; p < passes; p++) {
+    auto kernel = (long long)tmp.tiles_max * GP_RS_TILE >= GP_RS_BIG_SORT ? gp_rs_pass_kernel<16> : gp_rs_pass_kernel<GP_RS_STEPS>;
     GP_KERNEL("gp_rs_pass_kernel", stream,
-              gp_rs_pass_kernel<<<GP_RS_BLOCKS, GP_RS_THREADS, 0, stream>>>(keys[sel], vals[sel], keys[sel ^ 1],
-                                                                          vals[sel ^ 1], n_ptr, begin_bit + 8 * p, p,
-                                                                          tmp));
+              kernel<<<GP_RS_BLOCKS, GP_RS_THREADS, 0, stream>>>(keys[sel], vals[sel], keys[sel ^ 1], vals[sel ^ 1], n_ptr,
+                                                                  begin_bit + 8 * p, p, tmp));
     sel ^= 1;
   }
   return sel;
