@@ -188,6 +188,7 @@ gp_preprocess_kernel(int P, int D, int M, const float* __restrict__ means3D, con
     g.hdr[GP_HDR_NUM_RENDERED] = 0;
     g.hdr[GP_HDR_OVERFLOW] = 0;
     g.hdr[GP_HDR_NUM_SORTED] = 0;
+    g.hdr[GP_HDR_SCAN_TICKET] = 0;
   }
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int warp_base = idx - lane;
@@ -221,34 +222,16 @@ gp_preprocess_kernel(int P, int D, int M, const float* __restrict__ means3D, con
 // scan of tiles touched in depth order, and instance emission
 // ------------------------------------------------------------------------------------------------
 
-// block b: sum of tiles_touched over sorted positions [b*256, b*256+256)
-__global__ void __launch_bounds__(GP_SCAN_BLOCK)
-gp_block_sum_kernel(int P, const uint32_t* __restrict__ sorted_idx, const uint32_t* __restrict__ tiles_touched,
-                    uint32_t* __restrict__ block_sums) {
-  __shared__ uint32_t ws[GP_SCAN_BLOCK / 32];
-  const int s = blockIdx.x * GP_SCAN_BLOCK + threadIdx.x;
-  uint32_t v = s < P ? tiles_touched[sorted_idx[s]] : 0u;
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-  if ((threadIdx.x & 31) == 0) ws[threadIdx.x >> 5] = v;
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    uint32_t t = 0;
-#pragma unroll
-    for (int j = 0; j < GP_SCAN_BLOCK / 32; j++) t += ws[j];
-    block_sums[blockIdx.x] = t;
-  }
-}
-
-// single block: exclusive scan of block_sums[nb] in place, total -> header.
-__global__ void __launch_bounds__(1024)
-gp_spine_scan_kernel(int nb, uint32_t* __restrict__ block_sums, int* __restrict__ hdr, long long capacity) {
+// exclusive scan of block_sums[nb] in place by ONE block of NT threads, total -> header
+template <int NT>
+__device__ __forceinline__ void gp_spine_scan(int nb, uint32_t* __restrict__ block_sums, int* __restrict__ hdr,
+                                              long long capacity) {
   __shared__ unsigned long long warp_tot[32];
   __shared__ unsigned long long carry_s;
   const int t = threadIdx.x, lane = t & 31, w = t >> 5;
   if (t == 0) carry_s = 0;
   __syncthreads();
-  for (int base = 0; base < nb; base += 1024) {
+  for (int base = 0; base < nb; base += NT) {
     const int i = base + t;
     const unsigned long long v = i < nb ? block_sums[i] : 0ull;
     unsigned long long incl = v;
@@ -265,7 +248,7 @@ gp_spine_scan_kernel(int nb, uint32_t* __restrict__ block_sums, int* __restrict_
     const unsigned long long excl = carry + wbase + incl - v;
     if (i < nb) block_sums[i] = (uint32_t)(excl > 0xFFFFFFFFull ? 0xFFFFFFFFull : excl);
     __syncthreads();
-    if (t == 1023) carry_s = carry + wbase + incl;
+    if (t == NT - 1) carry_s = carry + wbase + incl;
     __syncthreads();
   }
   if (t == 0) {
@@ -275,6 +258,33 @@ gp_spine_scan_kernel(int nb, uint32_t* __restrict__ block_sums, int* __restrict_
     hdr[GP_HDR_OVERFLOW] = over ? 1 : 0;
     hdr[GP_HDR_NUM_SORTED] = over ? 0 : (int)total;
   }
+}
+
+// block b: sum of tiles_touched over sorted positions [b*256, b*256+256).  The block that finishes last (a counter in
+// the header, zeroed by the preprocess kernel) then scans the block sums: one launch instead of two.
+__global__ void __launch_bounds__(GP_SCAN_BLOCK)
+gp_block_sum_kernel(int P, const uint32_t* __restrict__ sorted_idx, const uint32_t* __restrict__ tiles_touched,
+                    uint32_t* __restrict__ block_sums, int* __restrict__ hdr) {
+  __shared__ uint32_t ws[GP_SCAN_BLOCK / 32];
+  __shared__ bool s_last;
+  const int s = blockIdx.x * GP_SCAN_BLOCK + threadIdx.x;
+  uint32_t v = s < P ? tiles_touched[sorted_idx[s]] : 0u;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  if ((threadIdx.x & 31) == 0) ws[threadIdx.x >> 5] = v;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t t = 0;
+#pragma unroll
+    for (int j = 0; j < GP_SCAN_BLOCK / 32; j++) t += ws[j];
+    block_sums[blockIdx.x] = t;
+    __threadfence();                                           // the sum is visible before the ticket is
+    s_last = atomicAdd(hdr + GP_HDR_SCAN_TICKET, 1) == (int)gridDim.x - 1;
+  }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();                                             // and every other block's sum before it is read here
+  gp_spine_scan<GP_SCAN_BLOCK>((int)gridDim.x, block_sums, hdr, 0x7FFFFFFFll);
 }
 
 // Emits (tile id, Gaussian index) for every tile of every visible Gaussian, in depth order.
@@ -529,11 +539,9 @@ extern "C" int gp_raster_preprocess(const gp_raster_cfg* cfg, const float* means
   gp_radix_sort_pairs(g.dkeys, g.dvals, g.hdr + GP_HDR_NUM_POINTS, 0, 32, g.radix, stream, /*reset=*/false);
   GP_LAUNCH_CHECK();
   const int nb = (P + GP_SCAN_BLOCK - 1) / GP_SCAN_BLOCK;
-  GP_KERNEL("gp_block_sum_kernel", stream, gp_block_sum_kernel<<<nb, GP_SCAN_BLOCK, 0, stream>>>(P, g.dvals[0], g.tiles_touched, g.block_sums));
-  GP_LAUNCH_CHECK();
-  // capacity is not known yet: the spine scan runs again (cheaply) in gp_raster_render with the real
-  // capacity; here it publishes R for callers that size the binning workspace exactly.
-  GP_KERNEL("gp_spine_scan_kernel", stream, gp_spine_scan_kernel<<<1, 1024, 0, stream>>>(nb, g.block_sums, g.hdr, 0x7FFFFFFFll));
+  // block sums + (in the last block to finish) their scan; publishes R.  The capacity check follows in
+  // gp_raster_render (gp_set_capacity_kernel), once the caller has sized the binning workspace.
+  GP_KERNEL("gp_block_sum_kernel", stream, gp_block_sum_kernel<<<nb, GP_SCAN_BLOCK, 0, stream>>>(P, g.dvals[0], g.tiles_touched, g.block_sums, g.hdr));
   GP_LAUNCH_CHECK();
   return GP_OK;
 }

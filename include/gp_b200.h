@@ -68,6 +68,7 @@ typedef struct {
 #define GP_HDR_OVERFLOW 1     /* 1 if R > capacity: the frame was NOT rendered, retry with more */
 #define GP_HDR_NUM_POINTS 2   /* P */
 #define GP_HDR_NUM_SORTED 3   /* min(R, capacity) */
+#define GP_HDR_SCAN_TICKET 4  /* internal: blocks of the tiles-touched scan that have finished */
 #define GP_HDR_WORDS 64
 
 /* Workspace sizes in bytes for P Gaussians, a width x height image and room for `capacity` tile
