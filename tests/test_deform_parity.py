@@ -415,3 +415,45 @@ def test_two_stage_step_with_grad_sinks_matches_eager(gplib):
     finally:
         if own_group:
             dist.destroy_process_group()
+
+
+def test_full_size_deformation_properties_1m(gplib):
+    """BASELINE.json's large configs (C4/C5: 1-2 M Gaussians) are too big for the brute-force oracle, so the
+    deformation stage is checked there through size-independent properties: the neighbour lists are sorted, unique and
+    in range; a random sample of queries agrees with the oracle bit for bit; the order / hint arguments (speed hints)
+    do not change the result; the position blend is linear in the keypoint translations; the quaternions come out
+    normalised."""
+    from gaussianprediction_b200.deform import keypoint_blend, knn_keypoints, spatial_order
+    from oracle import deform_oracle as do
+    N, Kp, K = 1_000_000, 512, 6
+    gs, kp, kf, logits = scene(N, Kp, seed=77)
+    dev = "cuda"
+    xyz, mf, kpd, kfd = gs.xyz.to(dev), gs.motion_feature.to(dev), kp.to(dev), kf.to(dev)
+    idx64, idx32, dists = knn_keypoints(xyz, mf, kpd, kfd, K, "hybird", 0.5, return_dists=True)
+    d, i = to_np(dists), to_np(idx32)
+    assert (np.diff(d, axis=1) >= 0).all() and i.min() >= 0 and i.max() < Kp
+    assert (np.sort(i, axis=1)[:, 1:] != np.sort(i, axis=1)[:, :-1]).all()            # no keypoint twice in a row
+    assert count_diff(to_np(idx64), i.astype(np.int64)) == 0
+    sel = np.random.default_rng(0).choice(N, 3000, replace=False)
+    p1, p2 = do.hybrid_points(gs.xyz[sel], gs.motion_feature[sel], kp, kf, 0.5)
+    ok = do.knn_rel_gaps(p1.numpy(), p2.numpy(), K) >= 1e-6
+    od, oi = do.knn(p1.numpy(), p2.numpy(), K, fma=True)
+    assert ok.mean() > 0.995 and count_diff(i[sel][ok], oi[ok].astype(np.int32)) == 0
+    assert np.abs(d[sel] - od)[ok].max() <= 1e-6 * max(float(od.max()), 1.0)
+    # speed hints change nothing
+    order = spatial_order(xyz)
+    _, idx_b, dist_b = knn_keypoints(xyz, mf, kpd, kfd, K, "hybird", 0.5, return_dists=True, order=order, hint=idx32.clone())
+    assert count_diff(idx_b, idx32) == 0 and count_diff(dist_b, dists) == 0
+    # blend: linear in the keypoint translations, unit quaternions
+    g = torch.Generator().manual_seed(3)
+    kdx = (torch.randn(Kp, 3, generator=g) * 0.05).to(dev)
+    kdq = torch.nn.functional.normalize(torch.randn(Kp, 4, generator=g)).to(dev)
+    args = (logits.to(dev), idx32)
+    rest = (xyz, gs.rotation.to(dev), gs.scaling.to(dev), gs.opacity.to(dev))
+    with torch.no_grad():
+        x1, q1, s1, o1 = keypoint_blend(*args, kdx, kdq, *rest)
+        x2, q2, _, _ = keypoint_blend(*args, 2.0 * kdx, kdq, *rest)
+    assert float(((x2 - xyz) - 2.0 * (x1 - xyz)).abs().max()) <= 2e-6
+    assert float((q1.norm(dim=1) - 1).abs().max()) <= 1e-6 and count_diff(q1, q2) == 0
+    assert float((s1 - gs.scaling.to(dev).exp()).abs().max()) <= 1e-6 * float(s1.max())
+    assert float((o1 - torch.sigmoid(gs.opacity.to(dev))).abs().max()) <= 1e-6
