@@ -6,15 +6,17 @@
 // 3-10 us each per iteration (0.26 ms of a 1.18 ms train iteration on B200, profiles/r1_keypoint_mlp.md); the work
 // itself is ~1 GFLOP, so it is launch/latency bound and is fused here:
 //
-//   forward    : a block owns 4 keypoints; thread j owns hidden unit j.  Builds the input row
-//                [feature | PE(xyz) | PE(t)] in shared memory, walks the layers with the activations ping-ponging
-//                between two shared-memory rows, keeps the post-ReLU activations for the backward.  The weights stream
-//                through a 4-stage cp.async ring of 32 KB chunks that runs ahead across layer boundaries.
+//   forward    : a block owns 4 keypoints; 512 threads = 256 hidden units x 2 groups that split every chunk's summation
+//                range.  Builds the input row [feature | PE(xyz) | PE(t)] in shared memory, walks the layers with the
+//                activations ping-ponging between two shared-memory rows, keeps the post-ReLU activations for the
+//                backward, normalises the quaternion part of the output if asked.  The weights stream through a
+//                3-stage cp.async ring of 64 KB chunks that runs ahead across layer boundaries.
 //   bwd (data) : same tiling and ring walked backwards, ReLU masks from the saved activations; writes
 //                dL/d(pre-activation) of every layer, the feature gradient and the xyz gradient through the encoding.
 //   bwd (weights): all layers in one launch, 32x64 output tiles of dW_l = dZ_l^T H_{l-1} summed over the keypoints
 //                in a fixed order (no atomics: bit-reproducible), bias gradient alongside, 3-stage cp.async ring.
-// Every block re-reads all the weights (1 MB), so the kernels are bound by L2 -> SM bandwidth, not HBM.
+// Every block re-reads all the weights (872 KB, L2 hits); what bounds the kernels is one SM's shared-memory / issue
+// rate on the consume side, not L2 or HBM bandwidth (profiles/r1_keypoint_mlp.md).
 //
 // fp32 FMA throughout like the reference's fp32 cuBLAS GEMMs (no TF32); sums run in index order.
 #include "../../include/gp_b200.h"

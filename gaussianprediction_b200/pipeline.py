@@ -9,6 +9,8 @@ target tensors.  Kernels and results are the same as the eager path; only the la
 
 A graph is tied to (image size, tan-fov, SH degree, parameter shapes, capacity): those are kernel arguments by value.
 """
+import os
+
 import torch
 
 from . import _lib
@@ -47,12 +49,11 @@ class TrainStep:
                  capture_collective=False):
         """``reducer``: a ``parallel.FlatGradAllReduce`` over the same parameters.  The backward kernels then write
         the parameter gradients straight into its flat buffer (``_sinks``: no zero fill, no accumulation pass, no
-        packing copies) and the step is captured as TWO graphs: (A) forward + backward through the rasterizer, after
-        which the SH gradients -- two thirds of the bytes -- are final, (B) the deformation backward.  The all-reduce
-        of the early bucket is issued between the replays and runs over NVLink while (B) computes; the late bucket
-        follows (B).  ``capture_collective=True`` records ONE all-reduce into a single graph instead; EXPERIMENTAL --
-        with torch 2.11 / NCCL 2.28 on the B200 test box that capture hung, so it is off by default and not used by
-        bench.py."""
+        packing copies) and the step is captured as one CUDA graph per reducer bucket (up to three, see
+        ``_stage_fns``): each graph ends where the gradients of its bucket are final, its all-reduce is issued right
+        after the replay and runs over NVLink while the next graph computes.  ``capture_collective=True`` records ONE
+        all-reduce into a single graph instead; EXPERIMENTAL -- with torch 2.11 / NCCL 2.28 on the B200 test box
+        that capture hung, so it is off by default and not used by bench.py."""
         self.pc = pc
         self.reducer = reducer
         self.capture_collective = bool(capture_collective and reducer is not None)
@@ -76,7 +77,7 @@ class TrainStep:
         self.loss = None
         self.pkg = None
         _lib.lib()
-        self.max_stages = int(__import__("os").environ.get("GP_TRAINSTEP_STAGES", "3"))   # A/B knob for the bench
+        self.max_stages = int(os.environ.get("GP_TRAINSTEP_STAGES", "3"))   # A/B knob: 2 merges the last two stages
         self._stages = self._stage_fns() if self.two_stage else None
         self._cut1 = self._cut2 = None
         self.packed = 0
