@@ -90,3 +90,32 @@ def test_keypoint_mlp_limits_without_gpu(gplib):
         assert gplib.gp_kpmlp_sizes(ctypes.byref(bad), None, None) == -4
     assert gplib.gp_kpmlp_sizes(None, None, None) == -1
     assert gplib.gp_kpmlp_forward(ctypes.byref(ok), *([None] * 10)) == -1
+
+
+def test_header_is_plain_c_and_struct_layouts_match_ctypes(tmp_path):
+    """include/gp_b200.h compiles as C99 (what a cgo / JNI / ctypes-free binding would include) and the structs that
+    cross the ABI by pointer have the size and field offsets the ctypes mirrors in _lib.py assume."""
+    import shutil
+    import subprocess
+    from gaussianprediction_b200 import _lib
+    if shutil.which("gcc") is None:
+        pytest.skip("gcc not available")
+    src = tmp_path / "abi_probe.c"
+    src.write_text(
+        '#include <stdio.h>\n#include <stddef.h>\n#include "gp_b200.h"\n'
+        'int main(void) {\n'
+        '  printf("%zu %zu %zu %zu\\n", sizeof(gp_raster_cfg), offsetof(gp_raster_cfg, tanfovx), '
+        'offsetof(gp_raster_cfg, sh_rest), offsetof(gp_raster_cfg, dL_dsh_rest));\n'
+        '  printf("%zu %zu\\n", sizeof(gp_mlp_cfg), offsetof(gp_mlp_cfg, normalize_q));\n'
+        '  printf("%zu %zu %zu %zu\\n", sizeof(gp_adam_tensor), offsetof(gp_adam_tensor, n), '
+        'offsetof(gp_adam_tensor, lr), offsetof(gp_adam_tensor, step));\n'
+        '  return 0;\n}\n')
+    exe = tmp_path / "abi_probe"
+    subprocess.run(["gcc", "-std=c99", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"), "-o", str(exe), str(src)],
+                   check=True)
+    rows = [[int(x) for x in line.split()] for line in subprocess.run([str(exe)], check=True, capture_output=True,
+                                                                        text=True).stdout.strip().splitlines()]
+    R, M, A = _lib.RasterCfg, _lib.MlpCfg, _lib.AdamTensor
+    assert rows[0] == [ctypes.sizeof(R), R.tanfovx.offset, R.sh_rest.offset, R.dL_dsh_rest.offset]
+    assert rows[1] == [ctypes.sizeof(M), M.normalize_q.offset]
+    assert rows[2] == [ctypes.sizeof(A), A.n.offset, A.lr.offset, A.step.offset]
