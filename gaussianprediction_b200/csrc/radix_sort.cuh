@@ -58,6 +58,26 @@ __device__ __forceinline__ void gp_rs_reset_by_block(const GpRadixTemp& t) {
 }
 static __global__ void gp_rs_reset_kernel(GpRadixTemp t) { gp_rs_reset_by_block(t); }
 
+// For a kernel that PRODUCES the keys of a sort: clear the look-back status words the passes will use (n keys, spread
+// over the whole grid) ...
+__device__ __forceinline__ void gp_rs_clear_status(const GpRadixTemp& t, int n, int passes) {
+  const int ntiles = (n + GP_RS_TILE - 1) / GP_RS_TILE;
+  const long long words = (long long)ntiles * GP_RS_RADIX;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (int p = 0; p < passes; p++) {
+    uint32_t* st = t.status + (size_t)p * t.tiles_max * GP_RS_RADIX;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < words; i += stride) st[i] = 0u;
+  }
+}
+// ... and add a block's digit counts (sh[pass][digit], built in shared memory while the keys were written) to the
+// global histograms, which some earlier kernel must have zeroed.
+__device__ __forceinline__ void gp_rs_flush_histogram(const GpRadixTemp& t, const uint32_t (*sh)[GP_RS_RADIX], int passes) {
+  for (int e = threadIdx.x; e < passes * GP_RS_RADIX; e += blockDim.x) {
+    const uint32_t v = sh[e / GP_RS_RADIX][e % GP_RS_RADIX];
+    if (v) atomicAdd(&t.hist[e], v);
+  }
+}
+
 // Digit histograms of every pass + reset of the status words the passes will use.
 static __global__ void __launch_bounds__(GP_RS_THREADS)
 gp_rs_prepare_kernel(const uint32_t* __restrict__ keys, const int* __restrict__ n_ptr, int begin_bit, int passes,
@@ -227,11 +247,15 @@ gp_rs_pass_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restri
 // Sort bits [begin_bit, end_bit) of keys (at most 32 bits = 4 passes).  keys[0]/vals[0] hold the input; buffers
 // ping-pong.  Returns the index (0/1) of the buffer pair holding the sorted result.
 static inline int gp_radix_sort_pairs(uint32_t* keys[2], uint32_t* vals[2], const int* n_ptr, int begin_bit,
-                                      int end_bit, const GpRadixTemp& tmp, cudaStream_t stream, bool reset = true) {
+                                      int end_bit, const GpRadixTemp& tmp, cudaStream_t stream, bool reset = true,
+                                      bool prepared = false) {
+  // prepared: the kernel that produced the keys has already built the digit histograms and cleared the status words
+  // (gp_rs_block_histogram / gp_rs_clear_status), so no separate pass over the keys is needed
   const int passes = (end_bit - begin_bit + 7) / 8;
   if (reset) GP_KERNEL("gp_rs_reset_kernel", stream, gp_rs_reset_kernel<<<1, 256, 0, stream>>>(tmp));
-  GP_KERNEL("gp_rs_prepare_kernel", stream,
-            gp_rs_prepare_kernel<<<GP_RS_BLOCKS, GP_RS_THREADS, 0, stream>>>(keys[0], n_ptr, begin_bit, passes, tmp));
+  if (!prepared)
+    GP_KERNEL("gp_rs_prepare_kernel", stream,
+              gp_rs_prepare_kernel<<<GP_RS_BLOCKS, GP_RS_THREADS, 0, stream>>>(keys[0], n_ptr, begin_bit, passes, tmp));
   int sel = 0;
   for (int p = 0; p < passes; p++) {
     auto kernel = (long long)tmp.tiles_max * GP_RS_TILE >= GP_RS_BIG_SORT ? gp_rs_pass_kernel<16> : gp_rs_pass_kernel<GP_RS_STEPS>;

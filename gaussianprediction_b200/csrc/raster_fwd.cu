@@ -295,13 +295,19 @@ __global__ void __launch_bounds__(GP_SCAN_BLOCK)
 gp_duplicate_kernel(int P, const uint32_t* __restrict__ sorted_idx, const uint32_t* __restrict__ tiles_touched,
                     const float4* __restrict__ xy_depth, const int* __restrict__ radii,
                     const uint32_t* __restrict__ block_excl, const int* __restrict__ hdr, unsigned grid_x,
-                    unsigned grid_y, uint32_t* __restrict__ tkeys, uint32_t* __restrict__ tvals) {
+                    unsigned grid_y, uint32_t* __restrict__ tkeys, uint32_t* __restrict__ tvals, GpRadixTemp tile_radix,
+                    int passes) {
+  __shared__ uint32_t s_hist[GP_RS_MAX_PASSES][GP_RS_RADIX];  // digit counts of the tile ids this block emits
   __shared__ uint32_t s_off[GP_SCAN_BLOCK + 1];  // exclusive offsets inside the block
   __shared__ uint32_t s_g[GP_SCAN_BLOCK];
   __shared__ uint32_t s_rx[GP_SCAN_BLOCK], s_ry[GP_SCAN_BLOCK], s_rw[GP_SCAN_BLOCK];
   __shared__ uint32_t ws[GP_SCAN_BLOCK / 32];
   if (hdr[GP_HDR_OVERFLOW]) return;
   const int t = threadIdx.x, lane = t & 31, w = t >> 5;
+  // the tile sort that follows: its status words are cleared and its digit histograms built here, where the keys
+  // are produced, instead of by a separate pass over the R keys (the histograms were zeroed by gp_set_capacity_kernel)
+  gp_rs_clear_status(tile_radix, hdr[GP_HDR_NUM_SORTED], passes);
+  for (int e = t; e < GP_RS_MAX_PASSES * GP_RS_RADIX; e += GP_SCAN_BLOCK) (&s_hist[0][0])[e] = 0u;
   const int s = blockIdx.x * GP_SCAN_BLOCK + t;
   uint32_t gidx = 0, tt = 0;
   if (s < P) {
@@ -344,9 +350,13 @@ gp_duplicate_kernel(int P, const uint32_t* __restrict__ sorted_idx, const uint32
     const uint32_t rw = s_rw[lo];
     const uint32_t ty = s_ry[lo] + local / rw;
     const uint32_t tx = s_rx[lo] + local % rw;
-    tkeys[base + e] = ty * grid_x + tx;
+    const uint32_t key = ty * grid_x + tx;
+    tkeys[base + e] = key;
     tvals[base + e] = s_g[lo];
+    for (int p = 0; p < passes; p++) atomicAdd(&s_hist[p][(key >> (8 * p)) & 0xFFu], 1u);
   }
+  __syncthreads();
+  gp_rs_flush_histogram(tile_radix, s_hist, passes);
 }
 
 __global__ void __launch_bounds__(256)
@@ -584,14 +594,15 @@ extern "C" int gp_raster_render(const gp_raster_cfg* cfg, const float* bg, const
   const unsigned gx = (W + GP_TILE_X - 1) / GP_TILE_X, gy = (H + GP_TILE_Y - 1) / GP_TILE_Y;
   const int nb = (P + GP_SCAN_BLOCK - 1) / GP_SCAN_BLOCK;
 
+  const int bits = gp_tile_bits(W, H);
   GP_KERNEL("gp_set_capacity_kernel", stream,
             gp_set_capacity_kernel<<<8, 256, 0, stream>>>(g.hdr, capacity, im.ranges, (int)(gx * gy), b.radix));
   GP_LAUNCH_CHECK();
   GP_KERNEL("gp_duplicate_kernel", stream, gp_duplicate_kernel<<<nb, GP_SCAN_BLOCK, 0, stream>>>(P, g.dvals[0], g.tiles_touched, g.xy_depth, radii, g.block_sums,
-                                                        g.hdr, gx, gy, b.tkeys[0], b.tvals[0]));
+                                                        g.hdr, gx, gy, b.tkeys[0], b.tvals[0], b.radix, (bits + 7) / 8));
   GP_LAUNCH_CHECK();
-  const int bits = gp_tile_bits(W, H);
-  const int sel = gp_radix_sort_pairs(b.tkeys, b.tvals, g.hdr + GP_HDR_NUM_SORTED, 0, bits, b.radix, stream, /*reset=*/false);
+  const int sel = gp_radix_sort_pairs(b.tkeys, b.tvals, g.hdr + GP_HDR_NUM_SORTED, 0, bits, b.radix, stream, /*reset=*/false,
+                                      /*prepared=*/true);
   GP_LAUNCH_CHECK();
   GP_KERNEL("gp_tile_ranges_kernel", stream, gp_tile_ranges_kernel<<<148 * 4, 256, 0, stream>>>(g.hdr, b.tkeys[sel], im.ranges));
   GP_LAUNCH_CHECK();
