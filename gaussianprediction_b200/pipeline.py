@@ -23,9 +23,12 @@ class _StaticCamera:
     def __init__(self, cam, device):
         self.image_width, self.image_height = int(cam.image_width), int(cam.image_height)
         self.FoVx, self.FoVy = float(cam.FoVx), float(cam.FoVy)
-        self.world_view_transform = torch.empty(4, 4, device=device)
-        self.full_proj_transform = torch.empty(4, 4, device=device)
-        self.camera_center = torch.empty(3, device=device)
+        # one packed buffer (view 16 | proj 16 | centre 3 | time 1) so that a prefetched sample lands with ONE small copy
+        self.packed = torch.empty(36, device=device)
+        self.world_view_transform = self.packed[0:16].view(4, 4)
+        self.full_proj_transform = self.packed[16:32].view(4, 4)
+        self.camera_center = self.packed[32:35]
+        self.time = self.packed[35:36]
 
     def load(self, cam, non_blocking=True):
         assert int(cam.image_width) == self.image_width and int(cam.image_height) == self.image_height
@@ -72,7 +75,8 @@ class TrainStep:
         self.loss_fn = loss_fn or (lambda image, target: (image * target).sum())
         self.cam = _StaticCamera(cam, dev)
         self.cam.load(cam, non_blocking=False)
-        self.t = torch.zeros(1, device=dev)
+        self.t = self.cam.time
+        self.t.zero_()
         self.target = torch.zeros(3, self.cam.image_height, self.cam.image_width, device=dev)
         self.loss = None
         self.pkg = None
@@ -242,22 +246,26 @@ class TrainStep:
         ``step_prefetched()`` moves it into the graph's static inputs (device-to-device) and replays."""
         if not hasattr(self, "_stage"):
             self._copy_stream = torch.cuda.Stream(device=self.dev)
-            self._stage = [dict(view=torch.empty(4, 4, device=self.dev), proj=torch.empty(4, 4, device=self.dev),
-                                center=torch.empty(3, device=self.dev), t=torch.empty(1, device=self.dev),
+            self._stage = [dict(host=torch.empty(36).pin_memory(), small=torch.empty(36, device=self.dev),
                                 target=torch.empty_like(self.target), ready=torch.cuda.Event(), free=torch.cuda.Event())
                            for _ in range(2)]
             self._slot = 0
             for s in self._stage:
                 s["free"].record(torch.cuda.current_stream(self.dev))
         s = self._stage[self._slot]
+        if s.get("used"):
+            s["ready"].synchronize()                         # the slot's previous H2D has left its pinned host buffer
+        h = s["host"]                                        # camera + time packed on the host: one H2D, one D2D later
+        h[0:16].view(4, 4).copy_(cam.world_view_transform)
+        h[16:32].view(4, 4).copy_(cam.full_proj_transform)
+        h[32:35].copy_(cam.camera_center)
+        h[35:36].copy_(t.reshape(-1)[:1])
         with torch.cuda.stream(self._copy_stream):
             self._copy_stream.wait_event(s["free"])          # the step that consumed this slot has read it
-            s["view"].copy_(cam.world_view_transform, non_blocking=True)
-            s["proj"].copy_(cam.full_proj_transform, non_blocking=True)
-            s["center"].copy_(cam.camera_center, non_blocking=True)
-            s["t"].copy_(t, non_blocking=True)
+            s["small"].copy_(h, non_blocking=True)
             s["target"].copy_(target, non_blocking=True)
             s["ready"].record(self._copy_stream)
+        s["used"] = True
         self._pending = s
         self._slot ^= 1
 
@@ -265,10 +273,7 @@ class TrainStep:
         s = self._pending
         cur = torch.cuda.current_stream(self.dev)
         cur.wait_event(s["ready"])
-        self.cam.world_view_transform.copy_(s["view"])
-        self.cam.full_proj_transform.copy_(s["proj"])
-        self.cam.camera_center.copy_(s["center"])
-        self.t.copy_(s["t"])
+        self.cam.packed.copy_(s["small"])
         self.target.copy_(s["target"])
         s["free"].record(cur)
         return self._replay()
