@@ -5,8 +5,10 @@ gradient is first produced in a fresh tensor and then added into its slice of th
 write and a launch per parameter and step).  While a sink map is installed, the autograd Functions of this package
 look up the tensor a gradient belongs to (by storage address) and, if it has a sink, hand the sink to the kernel as
 its output array.  Autograd then finds ``p.grad`` empty, keeps the returned tensor as ``p.grad`` -- which *is* the
-slice of the flat buffer -- and nothing is copied.  Parameters that get their gradient through torch ops instead (or
-from more than one producer) simply miss the sink and are packed the usual way by the reducer.
+slice of the flat buffer -- and nothing is copied.  Parameters that get their gradient through torch ops instead simply
+miss the sink and are packed the usual way by the reducer.  A sink holds what ONE producer wrote: a parameter that feeds
+two of this package's Functions at once would have its sink overwritten rather than summed, which is why the only
+user, ``pipeline.TrainStep``, compares the result with a plain ``loss.backward()`` once before capturing anything.
 """
 import contextlib
 
