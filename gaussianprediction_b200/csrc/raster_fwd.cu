@@ -264,7 +264,7 @@ __device__ __forceinline__ void gp_spine_scan(int nb, uint32_t* __restrict__ blo
 // the header, zeroed by the preprocess kernel) then scans the block sums: one launch instead of two.
 __global__ void __launch_bounds__(GP_SCAN_BLOCK)
 gp_block_sum_kernel(int P, const uint32_t* __restrict__ sorted_idx, const uint32_t* __restrict__ tiles_touched,
-                    uint32_t* __restrict__ block_sums, int* __restrict__ hdr) {
+                    uint32_t* __restrict__ block_sums, int* __restrict__ hdr, GpRadixTemp tile_radix) {
   __shared__ uint32_t ws[GP_SCAN_BLOCK / 32];
   __shared__ bool s_last;
   const int s = blockIdx.x * GP_SCAN_BLOCK + threadIdx.x;
@@ -283,6 +283,7 @@ gp_block_sum_kernel(int P, const uint32_t* __restrict__ sorted_idx, const uint32
   }
   __syncthreads();
   if (!s_last) return;
+  gp_rs_reset_by_block(tile_radix);                            // the tile sort of gp_raster_render starts from zeroed counters
   __threadfence();                                             // and every other block's sum before it is read here
   gp_spine_scan<GP_SCAN_BLOCK>((int)gridDim.x, block_sums, hdr, 0x7FFFFFFFll);
 }
@@ -296,17 +297,26 @@ gp_duplicate_kernel(int P, const uint32_t* __restrict__ sorted_idx, const uint32
                     const float4* __restrict__ xy_depth, const int* __restrict__ radii,
                     const uint32_t* __restrict__ block_excl, const int* __restrict__ hdr, unsigned grid_x,
                     unsigned grid_y, uint32_t* __restrict__ tkeys, uint32_t* __restrict__ tvals, GpRadixTemp tile_radix,
-                    int passes) {
+                    int passes, int* __restrict__ hdr_out, long long capacity, uint2* __restrict__ ranges, int tiles) {
   __shared__ uint32_t s_hist[GP_RS_MAX_PASSES][GP_RS_RADIX];  // digit counts of the tile ids this block emits
   __shared__ uint32_t s_off[GP_SCAN_BLOCK + 1];  // exclusive offsets inside the block
   __shared__ uint32_t s_g[GP_SCAN_BLOCK];
   __shared__ uint32_t s_rx[GP_SCAN_BLOCK], s_ry[GP_SCAN_BLOCK], s_rw[GP_SCAN_BLOCK];
   __shared__ uint32_t ws[GP_SCAN_BLOCK / 32];
-  if (hdr[GP_HDR_OVERFLOW]) return;
   const int t = threadIdx.x, lane = t & 31, w = t >> 5;
+  // does the frame fit the binning buffers?  Every block decides for itself from R (no block reads the flag another
+  // one writes); block 0 publishes the decision for the kernels that follow.  Tiles without instances keep range (0,0).
+  const long long R = hdr[GP_HDR_NUM_RENDERED];
+  const bool over = R > capacity || R >= 0x7FFFFFFFll;
+  if (blockIdx.x == 0 && t == 0) {
+    hdr_out[GP_HDR_OVERFLOW] = over ? 1 : 0;
+    hdr_out[GP_HDR_NUM_SORTED] = over ? 0 : (int)R;
+  }
+  for (int i = blockIdx.x * GP_SCAN_BLOCK + t; i < tiles; i += gridDim.x * GP_SCAN_BLOCK) ranges[i] = make_uint2(0u, 0u);
+  if (over) return;
   // the tile sort that follows: its status words are cleared and its digit histograms built here, where the keys
-  // are produced, instead of by a separate pass over the R keys (the histograms were zeroed by gp_set_capacity_kernel)
-  gp_rs_clear_status(tile_radix, hdr[GP_HDR_NUM_SORTED], passes);
+  // are produced, instead of by a separate pass over the R keys (the counters were zeroed by gp_block_sum_kernel)
+  gp_rs_clear_status(tile_radix, (int)R, passes);
   for (int e = t; e < GP_RS_MAX_PASSES * GP_RS_RADIX; e += GP_SCAN_BLOCK) (&s_hist[0][0])[e] = 0u;
   const int s = blockIdx.x * GP_SCAN_BLOCK + t;
   uint32_t gidx = 0, tt = 0;
@@ -360,7 +370,11 @@ gp_duplicate_kernel(int P, const uint32_t* __restrict__ sorted_idx, const uint32
 }
 
 __global__ void __launch_bounds__(256)
-gp_tile_ranges_kernel(const int* __restrict__ hdr, const uint32_t* __restrict__ tkeys, uint2* __restrict__ ranges) {
+gp_tile_ranges_kernel(const int* __restrict__ hdr, const uint32_t* __restrict__ tkeys, uint2* __restrict__ ranges,
+                      GpRadixTemp tile_radix) {
+  // the tile sort is over: leave its counters zeroed, so that rendering the same preprocessed frame again (e.g. with a
+  // larger capacity after an overflow) starts clean without another preprocess
+  if (blockIdx.x == 0) gp_rs_reset_by_block(tile_radix);
   const int L = hdr[GP_HDR_NUM_SORTED];
   for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < L; idx += gridDim.x * blockDim.x) {
     const uint32_t cur = tkeys[idx];
@@ -550,8 +564,10 @@ extern "C" int gp_raster_preprocess(const gp_raster_cfg* cfg, const float* means
   GP_LAUNCH_CHECK();
   const int nb = (P + GP_SCAN_BLOCK - 1) / GP_SCAN_BLOCK;
   // block sums + (in the last block to finish) their scan; publishes R.  The capacity check follows in
-  // gp_raster_render (gp_set_capacity_kernel), once the caller has sized the binning workspace.
-  GP_KERNEL("gp_block_sum_kernel", stream, gp_block_sum_kernel<<<nb, GP_SCAN_BLOCK, 0, stream>>>(P, g.dvals[0], g.tiles_touched, g.block_sums, g.hdr));
+  // gp_raster_render (first thing gp_duplicate_kernel does), once the caller has sized the binning workspace.
+  GpRadixTemp tile_counters = {g.tile_hist, g.tile_tickets, nullptr, 0};
+  GP_KERNEL("gp_block_sum_kernel", stream,
+            gp_block_sum_kernel<<<nb, GP_SCAN_BLOCK, 0, stream>>>(P, g.dvals[0], g.tiles_touched, g.block_sums, g.hdr, tile_counters));
   GP_LAUNCH_CHECK();
   return GP_OK;
 }
@@ -563,21 +579,6 @@ extern "C" int gp_raster_num_rendered(const void* geom_ws, gp_stream_t stream_, 
                               cudaMemcpyDeviceToHost, stream));
   GP_CUDA_TRY(cudaStreamSynchronize(stream));
   return GP_OK;
-}
-
-// Decides whether the frame fits the binning buffers, and clears what the next kernels accumulate into: the tile
-// ranges (tiles without instances keep (0,0)) and the histograms of the tile sort.
-__global__ void gp_set_capacity_kernel(int* hdr, long long capacity, uint2* ranges, int tiles, GpRadixTemp tile_radix) {
-  if (blockIdx.x == 0) {
-    gp_rs_reset_by_block(tile_radix);
-    if (threadIdx.x == 0) {
-      const long long R = hdr[GP_HDR_NUM_RENDERED];
-      const bool over = R > capacity || R >= 0x7FFFFFFFll;
-      hdr[GP_HDR_OVERFLOW] = over ? 1 : 0;
-      hdr[GP_HDR_NUM_SORTED] = over ? 0 : (int)R;
-    }
-  }
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < tiles; i += gridDim.x * blockDim.x) ranges[i] = make_uint2(0u, 0u);
 }
 
 extern "C" int gp_raster_render(const gp_raster_cfg* cfg, const float* bg, const float* colors_precomp, void* geom_ws,
@@ -595,16 +596,16 @@ extern "C" int gp_raster_render(const gp_raster_cfg* cfg, const float* bg, const
   const int nb = (P + GP_SCAN_BLOCK - 1) / GP_SCAN_BLOCK;
 
   const int bits = gp_tile_bits(W, H);
-  GP_KERNEL("gp_set_capacity_kernel", stream,
-            gp_set_capacity_kernel<<<8, 256, 0, stream>>>(g.hdr, capacity, im.ranges, (int)(gx * gy), b.radix));
-  GP_LAUNCH_CHECK();
+  b.radix.hist = g.tile_hist;        // counters of the tile sort live in the geometry workspace (zeroed by the
+  b.radix.tickets = g.tile_tickets;  // preprocess stage); the status words are the binning workspace's own
   GP_KERNEL("gp_duplicate_kernel", stream, gp_duplicate_kernel<<<nb, GP_SCAN_BLOCK, 0, stream>>>(P, g.dvals[0], g.tiles_touched, g.xy_depth, radii, g.block_sums,
-                                                        g.hdr, gx, gy, b.tkeys[0], b.tvals[0], b.radix, (bits + 7) / 8));
+                                                        g.hdr, gx, gy, b.tkeys[0], b.tvals[0], b.radix, (bits + 7) / 8,
+                                                        g.hdr, capacity, im.ranges, (int)(gx * gy)));
   GP_LAUNCH_CHECK();
   const int sel = gp_radix_sort_pairs(b.tkeys, b.tvals, g.hdr + GP_HDR_NUM_SORTED, 0, bits, b.radix, stream, /*reset=*/false,
                                       /*prepared=*/true);
   GP_LAUNCH_CHECK();
-  GP_KERNEL("gp_tile_ranges_kernel", stream, gp_tile_ranges_kernel<<<148 * 4, 256, 0, stream>>>(g.hdr, b.tkeys[sel], im.ranges));
+  GP_KERNEL("gp_tile_ranges_kernel", stream, gp_tile_ranges_kernel<<<148 * 4, 256, 0, stream>>>(g.hdr, b.tkeys[sel], im.ranges, b.radix));
   GP_LAUNCH_CHECK();
   GP_KERNEL("gp_render_fwd_kernel", stream, gp_render_fwd_kernel<<<gx * gy, GP_TILE_PIX, 0, stream>>>(im.ranges, b.tvals[sel], W, H, gx, g.xy_depth,
                                                            g.conic_opacity, g.rgb, colors_precomp, bg, g.hdr,

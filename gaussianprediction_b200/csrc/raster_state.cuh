@@ -22,6 +22,8 @@ struct GpGeom {
   uint32_t* dkeys[2];       // [P] depth bits (0xFFFFFFFF for culled), ping-pong
   uint32_t* dvals[2];       // [P] Gaussian index, ping-pong
   uint32_t* block_sums;     // [ceil(P/GP_SCAN_BLOCK)] tiles touched per block of sorted Gaussians (then exclusive)
+  uint32_t* tile_hist;      // digit histograms + tickets of the TILE sort: kept here (not in the binning workspace) so
+  uint32_t* tile_tickets;   // that a kernel of the preprocess stage can zero them before the binning buffers exist
   GpRadixTemp radix;
   size_t bytes;
 };
@@ -56,6 +58,8 @@ static inline GpGeom gp_carve_geom(void* ws, int P) {
   g.dvals[0] = c.take<uint32_t>(n);
   g.dvals[1] = c.take<uint32_t>(n);
   g.block_sums = c.take<uint32_t>((n + GP_SCAN_BLOCK - 1) / GP_SCAN_BLOCK + 1);
+  g.tile_hist = c.take<uint32_t>((size_t)GP_RS_MAX_PASSES * GP_RS_RADIX);
+  g.tile_tickets = c.take<uint32_t>(GP_RS_MAX_PASSES);
   g.radix = gp_radix_carve(c, (long long)n);
   g.bytes = c.used();
   return g;

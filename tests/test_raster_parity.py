@@ -269,6 +269,20 @@ def test_capacity_mode_and_overflow(gplib):
     *_, st2 = R.raster_forward(*args, capacity=Rn // 2)
     s2 = R.export_state(st2)
     assert s2["overflow"] == 1 and s2["num_rendered"] == Rn
+    # the second stage can be run again on the same preprocessed frame: after the overflow with enough room, and once
+    # more after a successful render (the tile sort leaves its counters clean) -- both give the exact-mode image
+    import ctypes
+    from gaussianprediction_b200 import _lib
+    L = _lib.lib()
+    _, bbytes, _ = R.workspace_sizes(st2.cfg.P, c["W"], c["H"], Rn + 5)
+    for _ in range(2):
+        binning = torch.empty(bbytes, dtype=torch.uint8, device="cuda")
+        color, depth = torch.empty_like(color0), torch.empty_like(depth0)
+        tidx = torch.empty_like(tidx0)
+        _lib.check(L.gp_raster_render(ctypes.byref(st2.cfg), _lib.ptr(c["bg"]), None, _lib.ptr(st2.geom), _lib.ptr(binning),
+                                      Rn + 5, _lib.ptr(st2.image), _lib.ptr(st2.radii), _lib.ptr(color), _lib.ptr(depth),
+                                      _lib.ptr(tidx), _lib.stream_ptr()), "gp_raster_render")
+        assert count_diff(color, color0) == 0 and count_diff(depth, depth0) == 0 and count_diff(tidx, tidx0) == 0
 
 
 def test_full_size_invariants_1m(gplib):
