@@ -210,8 +210,15 @@ gp_knn_kernel(int N, int Kp, int Drt, int K, const float* __restrict__ q_points,
         bmin[a] = lo;
         bmax[a] = hi;
       }
-      // (b) per keypoint: squared distance from the box in the leading dimensions, shrunk a little so that it stays a
-      //     lower bound of the fma-accumulated distance of every query in the box
+      // (b) per keypoint: squared distance from the box in the leading dimensions, shrunk so that it PROVABLY stays a
+      //     lower bound of the fma-accumulated distance every query in the box computes (u = 2^-24):
+      //       * lb as computed here: <= 3 squares of exact-input differences summed -> lb_c <= LB (1 + 6u);
+      //       * LB <= exact partial distance of any query in the box <= exact full distance DIST;
+      //       * the query's chain of D fused multiply-adds computes dist_c >= DIST (1 - (D + 1) u);
+      //       so dist_c >= lb_c (1 - (D + 7) u - ...) > lb_c (1 - (D + 8) * 2u) = the value stored below, for any D the
+      //       entry points accept.  A keypoint is dropped only when this value is STRICTLY greater than U, itself a
+      //       distance computed with the query's own chain, so no neighbour (and no tie) can be lost.
+      const float shrink = 1.0f - (float)(Dn + 8) * 1.1920929e-7f;
       for (int j = lane; j < cnt; j += 32) {
         float lb = 0.f;
 #pragma unroll
@@ -220,7 +227,7 @@ gp_knn_kernel(int N, int Kp, int Drt, int K, const float* __restrict__ q_points,
           const float dd = fmaxf(0.f, fmaxf(bmin[a] - kx, kx - bmax[a]));
           lb += dd * dd;
         }
-        s_lb[j] = lb * (1.0f - 1e-5f);
+        s_lb[j] = lb * shrink;
       }
       __syncwarp();
       // (c) the K keypoints closest to the box -> an upper bound U of every query's K-th distance

@@ -7,11 +7,24 @@
 //
 // A pair (pixel, Gaussian) is skipped by the blend loops unless power <= 0 and opacity * exp(power) >= 1/255
 // (reference forward.cu:345-352, backward.cu:497-504), i.e. unless the pixel lies in the ellipse
-// d^T Q d <= 2 ln(255 opacity) around the projected centre (Q = conic).  Its axis-aligned bounding box is
-// |dx| <= sqrt(2 tau cov_xx), |dy| <= sqrt(2 tau cov_yy) with cov = Q^-1.  Bit w of the result is set when that
-// box (inflated by 0.1 % + 0.01 px against rounding) meets patch w = 2 * row + col.  Patches whose bit is clear
-// would be skipped pixel by pixel anyway, so dropping them changes no result; it only removes work.  The
-// reference's tile list is built from a circle of radius 3 sigma_max and therefore holds many such pairs.
+// d^T Q d <= 2 tau, tau = ln(255 opacity), around the projected centre (Q = conic).  Its axis-aligned bounding box is
+// |dx| <= sqrt(2 tau c / det), |dy| <= sqrt(2 tau a / det).  Bit w of the result is set when that box meets patch
+// w = 2 * row + col.  Patches whose bit is clear would be skipped pixel by pixel anyway, so dropping them changes no
+// result; it only removes work (the reference's tile list comes from a circle of radius 3 sigma_max and holds many
+// such pairs).
+//
+// The box must contain every pixel the blend loops ACCEPT IN FLOATING POINT, so it is inflated by bounds on their
+// rounding (u = 2^-24), not by a guess:
+//   * acceptance means fl(o * fl(exp(power_c))) >= 1/255 with expf good to 2 ulp: power_c >= -(tau + 5u');
+//     logf(255 o) is off by at most 2u(1 + tau): tau is replaced by tau + 1e-6 (covers both, tau <= 5.6).
+//   * power_c = fma(fma(a dx, dx, (c dy) dy), -0.5, -((b dx) dy)) carries <= 4 roundings on terms whose absolute sum is
+//     <= a dx^2 + c dy^2 <= 2 rho * |power| with rho = (a c + b^2) / det (largest generalised eigenvalue of diag(a, c)
+//     against Q): |power_c - power| <= 16 u rho |power|.
+//   * det_c = fl(a c - b^2) is off by <= 3 u rho relative (cancellation of two rounded products).
+//   Both relative errors enter the squared half-extents once: factor (1 + 32 u rho) <= 1 + 2e-6 rho, plus 1e-5 for
+//   the divisions, square roots and the products below.  rho is itself computed from det_c, so a Gaussian whose
+//   rho_c exceeds 1e5 (relative bound 0.2: an extremely elongated, strongly rotated splat) is not culled at all.
+//   * centre +- half-extent minus the tile origin: three roundings at magnitude <= 2^13 px -> 0.002 px added.
 __device__ __forceinline__ unsigned gp_patch_mask(const float4 co, const float cx, const float cy, const float tile_x0,
                                                   const float tile_y0) {
   const float o = co.w;
@@ -19,10 +32,12 @@ __device__ __forceinline__ unsigned gp_patch_mask(const float4 co, const float c
   const float a = co.x, b = co.y, c = co.z;
   const float det = a * c - b * b;
   if (!(det > 0.f) || !(a > 0.f) || !(c > 0.f)) return 0xFFu;  // not a proper ellipse: no culling
-  const float k = 2.0f * logf(255.0f * o) / det;
-  const float hx = sqrtf(k * c) * 1.001f + 0.01f;
-  const float hy = sqrtf(k * a) * 1.001f + 0.01f;
-  if (!(hx < 1e30f) || !(hy < 1e30f)) return 0xFFu;
+  const float rho = (a * c + b * b) / det;
+  if (!(rho < 1e5f)) return 0xFFu;
+  const float k = 2.0f * (logf(255.0f * o) + 1e-6f) / det * (1.0f + 1e-5f + 2e-6f * rho);
+  const float hx = sqrtf(k * c) + 0.002f;
+  const float hy = sqrtf(k * a) + 0.002f;
+  if (!(hx < 1e30f) || !(hy < 1e30f) || !(fabsf(cx) < 8192.f) || !(fabsf(cy) < 8192.f)) return 0xFFu;
   const float xlo = cx - hx - tile_x0, xhi = cx + hx - tile_x0;  // relative to the tile origin
   const float ylo = cy - hy - tile_y0, yhi = cy + hy - tile_y0;
   unsigned colm = 0u, rowm = 0u;

@@ -405,9 +405,10 @@ class KeypointDeformation(nn.Module):
             s, opacity = self.get_scaling, self.get_opacity
         else:
             # second stage (:251-273, :285-287): keypoints
-            factor = 0.1 * (1 - min(1, (iteration - self.second_stage_iter) / args.xyz_noise_iteration))
+            factor = 1 - min(1, (iteration - self.second_stage_iter) / args.xyz_noise_iteration)
             noise = torch.randn_like(self.super_gaussians)  # RNG consumed even when the factor is 0 (:254)
-            kp_in = self.super_gaussians + noise * factor if factor != 0 else self.super_gaussians   # + 0 * noise == itself
+            # same product order as the reference (randn * 0.1 * factor); + 0 * noise == the keypoints themselves
+            kp_in = self.super_gaussians + noise * 0.1 * factor if factor != 0 else self.super_gaussians
             logits = self.weights_model(self._xyz.detach())
             if not (self.knn_cache and self._idx32 is not None):
                 self.get_nearest_mask(keepshape=True)

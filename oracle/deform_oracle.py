@@ -7,9 +7,13 @@ Parity status: PINNED for ``positional_encoding`` and ``Deformable_Field`` again
 modules (loaded by file path from /root/reference/scene/deformable_field.py by tests/golden/make_golden.py,
 vectors in tests/golden/deform_*.npz) and for the kNN against the reference's CUDA kernels
 (oracle/_ref/ref_frnn.so, same script, run on a B200) and its CPU brute force ``frnn_bf_cpu``.
-The blend / quaternion chain follows scene/gaussian_model.py line by line but cannot be executed from the
-reference (``scene.gaussian_model`` needs tinycudann, pytorch3d, ... which are absent): that part is
-"parity unpinned" and is checked against torch autograd instead.
+The blend / quaternion chain (``fill_nearest``, ``quat_mul``, ``keypoint_forward``, ``model_forward``,
+``extrapolate_frame``) is PINNED too: ``scene.gaussian_model`` cannot be imported (tinycudann, pytorch3d, ... are
+absent), so tests/golden/make_golden.py cuts ``GaussianModel.forward / fill_nearest / get_motion_delta / get_rotation_ /
+get_nearest_mask``, ``quat_mul`` and the two extrapolation statements of ``render_kpts`` out of the reference files as
+text, executes them against a stub ``self`` and stores outputs + autograd gradients in tests/golden/blend_chain.npz
+(all three stages, both step-opacity types, keypoint noise, ``return_weights``); tests/test_oracle_golden.py checks
+this file against it.  Only the tinycudann hash-grid network stays unpinned (its source is not in the tree).
 """
 import numpy as np
 import torch
@@ -123,6 +127,59 @@ def keypoint_forward(t, xyz, rotation, scaling, opacity, super_gaussians, super_
     xyz_t = xyz + dx                                                             # :285
     q_t = normalize(quat_mul(normalize(dq), rotation))                           # :286, :314-315
     return xyz_t, q_t, torch.exp(scaling), torch.sigmoid(opacity), delta_xyz, delta_q
+
+
+def model_forward(t, iteration, p, df_state, args, nearest_mask=None, noise=None, return_weights=False):
+    """All branches of ``GaussianModel.forward`` (scene/gaussian_model.py:231-304).  ``p``: dict with xyz, rotation,
+    scaling, opacity, motion_feature, kp, kf, logits and (step opacity) thres; ``args``: the reference's flag object;
+    ``noise``: the ``randn_like`` draw of :240 / :254 (None = zeros).  Returns what the reference returns, plus a dict
+    of the side-effect attributes (kpts_xyz_motion, kpts_rotation_motion, weights_sum, lifecycle_opacity)."""
+    normalize = torch.nn.functional.normalize
+    side = {}
+    t_input = t
+    t_enc = positional_encoding(t, args.time_freq).unsqueeze(0)                              # :233
+    get_opacity, get_scaling = torch.sigmoid(p["opacity"]), torch.exp(p["scaling"])
+    if iteration < args.jointly_iteration:                                                   # :237-238
+        return (p["xyz"], normalize(p["rotation"]), get_scaling, get_opacity), side
+    second = iteration > args.second_stage_iteration
+    d = getattr(args, "d", 4)
+
+    def motion_delta(xyz_embed, feat):                                                       # :180-189
+        tt = t_enc.repeat((feat.shape[0], 1))
+        delta = mlp_forward(df_state, torch.cat([feat, xyz_embed, tt], dim=-1), d)
+        return delta[..., 0:3], delta[..., 3:7], (delta[..., 7:8] if args.step_opacity else None)
+
+    if not second:                                                                           # :240-244
+        f = 1 - min(1, iteration / args.xyz_noise_iteration)
+        x = p["xyz"].detach() + (0 if noise is None else noise * 0.1 * f)    # same product order as :240
+        xyz_embed, feat = positional_encoding(x, args.xyz_freq), p["motion_feature"]
+    else:                                                                                    # :251-263
+        f = 1 - min(1, (iteration - args.second_stage_iteration) / args.xyz_noise_iteration)
+        xyz_embed = positional_encoding(p["kp"] + (0 if noise is None else noise * 0.1 * f), args.xyz_freq)   # :254-255
+        feat = p["kf"]
+        K, Kp = args.nearest_num, p["kp"].shape[0]
+        weights_xyz, weights_r = fill_nearest(p["logits"], nearest_mask, Kp, K)
+        side["weights_sum"] = torch.abs(weights_xyz) + torch.abs(weights_r)
+    delta_xyz, delta_q, _ = motion_delta(xyz_embed, feat)                                    # :265
+    if args.norm_rotation:
+        delta_q = normalize(delta_q)                                                         # :266-267
+    side["kpts_xyz_motion"], side["kpts_rotation_motion"] = delta_xyz, delta_q               # :269-270
+    if second:
+        delta_q = weights_r @ delta_q                                                        # :272
+        delta_xyz = weights_xyz @ delta_xyz                                                  # :273
+    xyz = p["xyz"] + delta_xyz                                                               # :285
+    q = normalize(quat_mul(normalize(delta_q), p["rotation"]))                               # :286, :314-315
+    opacity = get_opacity
+    if args.step_opacity and iteration > args.step_opacity_iteration:                        # :291-301
+        _, _, delta_o = motion_delta(positional_encoding(p["xyz"], args.xyz_freq), p["motion_feature"])
+        if args.opacity_type == "explicit":
+            opacity = get_opacity * (1 / (1 + torch.exp(-(t_input - p["thres"]) / args.beta)))   # :50
+        else:
+            opacity = get_opacity * (1 / (1 + torch.exp(-delta_o / args.beta)))                  # :51
+        side["lifecycle_opacity"] = opacity
+    if return_weights and second:
+        return (xyz, q, get_scaling, get_opacity, weights_xyz, weights_r), side              # :299-300, :302-303
+    return (xyz, q, get_scaling, opacity), side
 
 
 def extrapolate_frame(xyz, rotation, weights_xyz, weights_r, kpts_i, kpts, kpts_rotation_i):

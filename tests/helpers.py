@@ -50,3 +50,31 @@ def count_diff(a, b):
     if a.dtype == np.float32:
         return int((a.view(np.uint32) != b.view(np.uint32)).sum())
     return int((a != b).sum())
+
+
+# ---- the reference's own GaussianModel.forward chain (tests/golden/blend_chain.npz, see make_golden.py:make_chain) ----
+
+CHAIN_CASES = {   # tag -> (iteration, flags) exactly as make_chain ran the reference source
+    "A": (50000, dict(norm_rotation=True)),
+    "A2": (50000, dict(norm_rotation=False, knn_type="3D")),
+    "B": (50000, dict(norm_rotation=False, step_opacity=True, opacity_type="implicit")),
+    "C": (50000, dict(norm_rotation=True, step_opacity=True, opacity_type="explicit")),
+    "D": (20000, dict(norm_rotation=True)),
+    "D2": (20000, dict(norm_rotation=False, step_opacity=True)),
+    "E": (500, dict()),
+    "F": (32000, dict(norm_rotation=True)),
+    "W": (50000, dict(norm_rotation=True)),
+}
+CHAIN_LEAVES = ("xyz", "rotation", "scaling", "opacity", "motion_feature", "kp", "kf", "logits", "thres")
+
+
+def chain_args(flags):
+    from gaussianprediction_b200.deform import default_args
+    a = dict(feature_amplify=0.5, w=64, d=4, feature_dim=32)
+    a.update(flags)
+    return default_args(**a)
+
+
+def chain_state_dict(gold, out_dim):
+    pre = f"sd{out_dim}_"
+    return {k[len(pre):]: torch.tensor(gold[k]) for k in gold.files if k.startswith(pre)}

@@ -457,3 +457,119 @@ def test_full_size_deformation_properties_1m(gplib):
     assert float((q1.norm(dim=1) - 1).abs().max()) <= 1e-6 and count_diff(q1, q2) == 0
     assert float((s1 - gs.scaling.to(dev).exp()).abs().max()) <= 1e-6 * float(s1.max())
     assert float((o1 - torch.sigmoid(gs.opacity.to(dev))).abs().max()) <= 1e-6
+
+
+@pytest.mark.parametrize("tag", ["A", "A2", "B", "C", "D", "D2", "E", "F", "W"])
+def test_model_forward_vs_reference_source(gplib, tag, monkeypatch):
+    """KeypointDeformation on the GPU == the reference's own ``GaussianModel.forward`` source, executed on the CPU by
+    tests/golden/make_golden.py:make_chain (blend_chain.npz): all three stages, both step-opacity types, keypoint noise,
+    ``return_weights``, the side-effect attributes, the search result, and every autograd gradient.
+    Tolerances (north_star): outputs 1e-5 abs (fp32, different summation order), gradients 1e-3 relative."""
+    from helpers import CHAIN_CASES, CHAIN_LEAVES, chain_args, chain_state_dict
+    from gaussianprediction_b200.deform import KeypointDeformation
+    g = np.load(os.path.join(GOLD, "blend_chain.npz"))
+    it, flags = CHAIN_CASES[tag]
+    args = chain_args(flags)
+    leaf = {k: torch.tensor(g[k]) for k in CHAIN_LEAVES}
+    model = KeypointDeformation(args, leaf["xyz"], leaf["rotation"], leaf["scaling"], leaf["opacity"], leaf["motion_feature"],
+                                leaf["kp"], leaf["kf"], logits=leaf["logits"])
+    if args.step_opacity:
+        model.opacity_thres.data.copy_(leaf["thres"])
+    model.df_model.load_state_dict(chain_state_dict(g, 8 if args.step_opacity else 7))
+    model = model.cuda()
+    if (tag + "_noise") in g.files:      # the reference's randn draw (CPU generator) injected in place of the CUDA one
+        noise = torch.tensor(g[tag + "_noise"]).cuda()
+        monkeypatch.setattr(torch, "randn_like", lambda x, *a, **k: noise)
+    t = torch.tensor([float(g["t"])], device="cuda")
+    res = model(t, it, return_weights=(tag == "W"))
+    for n, v in zip(("xyz_t", "q_t", "s_t", "o_t", "weights_xyz", "weights_r"), res):
+        assert float(np.abs(to_np(v) - g[f"{tag}_{n}"]).max()) <= 1e-5, n
+    if it > 30000:
+        assert np.array_equal(to_np(model.nearest_mask), g[tag + "_nearest_mask"])
+        assert float(np.abs(to_np(model.weights_sum) - g[tag + "_weights_sum"]).max()) <= 1e-5
+    if it >= 1000:
+        assert float(np.abs(to_np(model.kpts_xyz_motion) - g[tag + "_kpts_xyz_motion"]).max()) <= 1e-5
+        assert float(np.abs(to_np(model.kpts_rotation_motion) - g[tag + "_kpts_rotation_motion"]).max()) <= 1e-5
+    if (tag + "_lifecycle_opacity") in g.files:
+        assert float(np.abs(to_np(model.lifecycle_opacity) - g[tag + "_lifecycle_opacity"]).max()) <= 1e-5
+    else:
+        assert model.lifecycle_opacity is None
+    cot = [torch.tensor(g[k]).cuda() for k in ("cot_xyz", "cot_q", "cot_s", "cot_o")]
+    sum((a * b).sum() for a, b in zip(res[:4], cot)).backward()
+    names = dict(xyz=model._xyz, rotation=model._rotation, scaling=model._scaling, opacity=model._opacity,
+                 motion_feature=model.motion_feature, kp=model.super_gaussians, kf=model.super_gaussians_feature,
+                 logits=model.weights_model.logits)
+    if args.step_opacity:
+        names["thres"] = model.opacity_thres
+    names.update({"net_" + k: p for k, p in model.df_model.named_parameters()})
+    for n, p in names.items():
+        key = f"{tag}_g_{n}"
+        if key in g.files:
+            assert p.grad is not None, n
+            assert rel_err(p.grad, g[key]) <= 1e-3, (n, rel_err(p.grad, g[key]))
+        else:
+            assert p.grad is None or float(p.grad.abs().max()) == 0.0, n
+
+
+def test_knn_c2_size_with_order_and_hint_vs_reference(gplib):
+    """The benchmarked configuration of the search -- 100k x 512, D = 35, Morton order + previous-frame hint, i.e. the
+    pruned path bench.py times -- against the reference's CUDA FRNN (bit-exact indices and squared distances)."""
+    from gaussianprediction_b200.deform import knn_keypoints, spatial_order
+    from oracle import deform_oracle as do
+    from oracle import ref_cuda
+    if not (ref_cuda.available("ref_frnn") and ref_cuda.available("ref_prefix_sum")):
+        pytest.skip("oracle/_ref/ref_frnn.so not built")
+    gs, kp, kf, _ = scene(100_000, 512, seed=2024)
+    amplify = 0.5
+    p1, p2 = do.hybrid_points(gs.xyz, gs.motion_feature, kp, kf, amplify)
+    rd, ri = ref_cuda.frnn_grid_points(p1[None].cuda().contiguous(), p2[None].cuda().contiguous(), 6, 1e8)
+    rd, ri = to_np(rd[0]), to_np(ri[0])
+    xyz, mf, kpc, kfc = gs.xyz.cuda(), gs.motion_feature.cuda(), kp.cuda(), kf.cuda()
+    order = spatial_order(xyz)
+    # first call: no hint; second call: the first result as hint (the steady state of the frame loop); third: a hint
+    # that is valid but useless (neighbours of a shifted cloud), which must not change the result either
+    _, idx_a, d_a = knn_keypoints(xyz, mf, kpc, kfc, 6, "hybird", amplify, return_dists=True, order=order)
+    hint = idx_a.clone()
+    _, idx_b, d_b = knn_keypoints(xyz, mf, kpc, kfc, 6, "hybird", amplify, return_dists=True, order=order, hint=hint)
+    bad = torch.roll(idx_a, 7919, 0).contiguous()
+    _, idx_c, d_c = knn_keypoints(xyz, mf, kpc, kfc, 6, "hybird", amplify, return_dists=True, order=order, hint=bad)
+    # tie policy (SURVEY.md par. 8c): rows whose K+1 nearest are closer than 1e-6 relative are compared as sets
+    for idx, d in ((idx_a, d_a), (idx_b, d_b), (idx_c, d_c)):
+        idx, d = to_np(idx), to_np(d)
+        assert count_diff(np.sort(d, 1), np.sort(rd, 1)) == 0            # distances: bit-identical multiset per row
+        rows = (idx.astype(np.int64) != ri).any(1)
+        assert rows.mean() < 1e-4                                         # index order may differ only on near-ties
+        for r in np.nonzero(rows)[0]:
+            gap = np.diff(rd[r]) / np.maximum(rd[r][1:], 1e-30)
+            assert gap.min() < 1e-6, "index mismatch on a tie-free row"
+
+
+def test_knn_pruning_adversarial_lattice(gplib):
+    """Queries and keypoints on lattices: keypoints sit exactly ON the faces of the warps' query bounding boxes and
+    exact distance ties are everywhere -- the worst case for the box-bound pruning (csrc/knn.cu step (b): a keypoint is
+    dropped only if its shrunk box distance is strictly greater than the K-th bound).  Must equal the exhaustive
+    oracle, ties resolved to the smaller index, with and without order / hint."""
+    from gaussianprediction_b200.deform import knn_keypoints, spatial_order
+    from oracle import deform_oracle as do
+    ax = torch.arange(17, dtype=torch.float32) / 16.0
+    q = torch.stack(torch.meshgrid(ax, ax, ax, indexing="ij"), -1).reshape(-1, 3)            # 4913 lattice queries
+    bx = torch.arange(5, dtype=torch.float32) / 4.0
+    k = torch.stack(torch.meshgrid(bx, bx, bx, indexing="ij"), -1).reshape(-1, 3)            # 125 lattice keypoints
+    g = torch.Generator().manual_seed(3)
+    q = q[torch.randperm(q.shape[0], generator=g)].contiguous()
+    for D_feat in (0, 32):
+        mf = torch.zeros(q.shape[0], 32)
+        kf = torch.zeros(k.shape[0], 32)
+        mode = "3D" if D_feat == 0 else "hybird"
+        p1 = q if D_feat == 0 else torch.cat([q, mf], 1)
+        p2 = k if D_feat == 0 else torch.cat([k, kf], 1)
+        od, oi = do.knn(p1.numpy(), p2.numpy(), 6, r=1e3 if D_feat == 0 else 1e8, fma=True)
+        qc, kc = q.cuda(), k.cuda()
+        order = spatial_order(qc)
+        for o, h in ((None, None), (order, None), (order, "self")):
+            hint = None
+            if h == "self":
+                hint = knn_keypoints(qc, mf.cuda(), kc, kf.cuda(), 6, mode, 1.0, order=order)[1].clone()
+            i64, _, d = knn_keypoints(qc, mf.cuda(), kc, kf.cuda(), 6, mode, 1.0, return_dists=True, order=o, hint=hint)
+            assert count_diff(to_np(d), od) == 0, (mode, o is not None, h)
+            assert count_diff(to_np(i64), oi) == 0, (mode, o is not None, h)

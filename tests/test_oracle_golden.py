@@ -195,3 +195,63 @@ def test_densification_stats_oracle_vs_reference_expressions():
     amax[vis] = torch.where(grad > amax[vis], grad, amax[vis])
     for a, b in zip(o, (max_r, accum, denom, amax)):
         assert np.allclose(a, b.numpy(), rtol=1e-6, atol=0)
+
+
+# ---- blend / quaternion chain: the oracle against the reference's OWN source (blend_chain.npz) ----
+
+@pytest.fixture(scope="module")
+def chain_gold():
+    return np.load(os.path.join(GOLD, "blend_chain.npz"))
+
+
+def test_quat_mul_and_fill_nearest_vs_reference_source(chain_gold):
+    from oracle import deform_oracle as do
+    g = chain_gold
+    assert np.array_equal(do.quat_mul(torch.tensor(g["Q_a"]), torch.tensor(g["Q_b"])).numpy(), g["Q_ab"])
+    wx, wr = do.fill_nearest(torch.tensor(g["logits"]), torch.tensor(g["W_nearest_mask"]), g["kp"].shape[0], 6)
+    assert np.array_equal(wx.numpy(), g["W_weights_xyz"]) and np.array_equal(wr.numpy(), g["W_weights_r"])
+
+
+@pytest.mark.parametrize("tag", ["A", "A2", "B", "C", "D", "D2", "E", "F", "W"])
+def test_model_forward_oracle_vs_reference_source(chain_gold, tag):
+    """oracle.model_forward == the reference's GaussianModel.forward executed from its own source text: outputs,
+    side-effect attributes and every autograd gradient."""
+    from helpers import CHAIN_CASES, CHAIN_LEAVES, chain_args, chain_state_dict
+    from oracle import deform_oracle as do
+    g = chain_gold
+    it, flags = CHAIN_CASES[tag]
+    args = chain_args(flags)
+    leaf = {k: torch.tensor(g[k]).requires_grad_(True) for k in CHAIN_LEAVES}
+    sd = {k: v.requires_grad_(True) for k, v in chain_state_dict(g, 8 if args.step_opacity else 7).items()}
+    mask = torch.tensor(g[tag + "_nearest_mask"]) if it > 30000 else None
+    if mask is not None:      # the search itself: oracle kNN == the reference's get_nearest_mask (on its CPU brute force)
+        p1, p2 = (leaf["xyz"].detach(), leaf["kp"].detach()) if args.knn_type == "3D" else \
+            do.hybrid_points(leaf["xyz"].detach(), leaf["motion_feature"].detach(), leaf["kp"].detach(), leaf["kf"].detach(), 0.5)
+        _, idx = do.knn(p1.numpy(), p2.numpy(), 6, fma=False)
+        assert np.array_equal(idx, g[tag + "_nearest_mask"])
+    noise = torch.tensor(g[tag + "_noise"]) if (tag + "_noise") in g.files else None
+    res, side = do.model_forward(torch.tensor([float(g["t"])]), it, leaf, sd, args, nearest_mask=mask, noise=noise,
+                                 return_weights=(tag == "W"))
+    for n, v in zip(("xyz_t", "q_t", "s_t", "o_t", "weights_xyz", "weights_r"), res):
+        assert np.abs(v.detach().numpy() - g[f"{tag}_{n}"]).max() <= 1e-6, n
+    for n, v in side.items():
+        assert np.abs(v.detach().numpy() - g[f"{tag}_{n}"]).max() <= 1e-6, n
+    cot = [torch.tensor(g[k]) for k in ("cot_xyz", "cot_q", "cot_s", "cot_o")]
+    loss = sum((a * b).sum() for a, b in zip(res[:4], cot))
+    names = list(leaf) + ["net_" + k for k in sd]
+    grads = torch.autograd.grad(loss, list(leaf.values()) + list(sd.values()), allow_unused=True)
+    for n, gr in zip(names, grads):
+        key = f"{tag}_g_{n}"
+        assert (gr is not None) == (key in g.files), n
+        if gr is not None:
+            assert rel(gr.numpy(), g[key]) <= 1e-5, (n, rel(gr.numpy(), g[key]))
+
+
+def test_extrapolate_frame_oracle_vs_reference_source(chain_gold):
+    from oracle import deform_oracle as do
+    g = chain_gold
+    wx, wr = torch.tensor(g["W_weights_xyz"]), torch.tensor(g["W_weights_r"])
+    for i in range(3):
+        xf, dr = do.extrapolate_frame(torch.tensor(g["xyz"]), torch.tensor(g["rotation"]), wx, wr, torch.tensor(g["X_kpts"][i]),
+                                      torch.tensor(g["kp"]), torch.tensor(g["X_kpts_rotation"][i]))
+        assert np.abs(xf.numpy() - g[f"X_xyz_{i}"]).max() <= 1e-6 and np.abs(dr.numpy() - g[f"X_r_{i}"]).max() <= 1e-6

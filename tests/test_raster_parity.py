@@ -326,3 +326,29 @@ def test_full_size_invariants_1m(gplib):
         assert count_diff(a["radii"], ref["fwd"]["radii"]) == 0
         for k in ("means2D", "opacity", "means3D", "sh", "scales", "rotations"):
             assert rel_err(a["grads"][k], ref["grads"][k]) <= GRAD_TOL, k
+
+
+def test_patch_culling_adversarial_vs_reference(gplib):
+    """Worst cases for the patch mask (csrc/raster_common.cuh:gp_patch_mask, which decides per 8x4-pixel patch whether
+    a Gaussian can reach alpha >= 1/255 there): opacities within a few ulp of 1/255 (the alpha >= 1/255 region shrinks
+    to the pixels where exp() rounds to 1), extremely elongated and strongly rotated splats (ill-conditioned conics,
+    where det = ac - b^2 cancels), centres exactly on pixel centres and on patch borders, and huge splats.  Every
+    forward quantity must stay bit-identical to the reference CUDA build and the gradients within tolerance."""
+    need_ref()
+    case = raster_case(N=6000, W=160, H=128, seed=31)
+    op = case["opacities"].clone()
+    thr = np.float32(1.0 / 255.0)
+    near = thr * (1.0 + np.arange(-3, 13, dtype=np.float32) * np.float32(2.0 ** -23))
+    op[:2000, 0] = torch.tensor(near[np.arange(2000) % near.size])
+    sc = case["scales"].clone()
+    sc[1000:3000, 0] *= 60.0                       # needles: 60 : 1 and beyond
+    sc[1000:3000, 1] *= 0.05
+    sc[3000:3200] *= 25.0                          # huge splats: hundreds of pixels
+    case["opacities"], case["scales"] = op, sc
+    mine, ref = run_mine(case, seeded_grad(case)), run_ref(case, seeded_grad(case))
+    for k in ("color", "depth", "tidx"):
+        assert count_diff(mine[k], ref["fwd"][k]) == 0, k
+    assert count_diff(mine["state"]["n_contrib"], ref["state"]["n_contrib"]) == 0
+    assert count_diff(mine["state"]["final_T"], ref["state"]["final_T"]) == 0
+    for k in ("means2D", "opacity", "means3D", "sh", "scales", "rotations"):
+        assert rel_err(mine["grads"][k], ref["grads"][k]) <= GRAD_TOL, (k, rel_err(mine["grads"][k], ref["grads"][k]))
