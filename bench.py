@@ -1,20 +1,26 @@
 #!/usr/bin/env python
-"""Headline benchmark: one train iteration of the per-frame render hot path (keypoint deformation forward ->
-rasterize forward -> backward through both), on BASELINE.json configs[1]: D-NeRF-shaped synthetic scene, 800x800,
-~100k Gaussians, 512 keypoints, nearest_num 6, SH degree 3.
+"""Headline benchmark of the per-frame render hot path: train iterations (keypoint deformation forward -> rasterize
+forward -> backward through both) of the reference's ``--batch`` loop (train.py:113-133).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload NAME] [--mode train|extrapolate]
 
-One JSON line on stdout (rank 0).  A "step" is one (camera, timestep) sample per rank: weak scaling, samples are
-sharded across ranks and the parameter gradients are summed with one NCCL all-reduce per step.
+ONE job at every N (so that per-N values compare): BASELINE.json configs[4] -- 2 M Gaussians, 800x800, 512 keypoints,
+nearest_num 6, SH degree 3, **8 (camera, time) samples per step split over the N ranks** (strong scaling): rank r
+renders samples r, r+N, ... of the step, gradients are summed over the samples of a rank in place and over the ranks
+with ONE exchange per step (SUM of gradients, MAX of radii = OR of visibility), started bucket by bucket while the
+last sample's backward is still running.  One JSON line on stdout (rank 0):
 
-  value        ms per train iteration, whole job (step time / samples processed in it), inputs resident in HBM
-  e2e          same, through the public API with the step's camera + target image coming from pinned host memory and
-               the loss scalar read back every step
-  roofline     the dominant kernel of the step, timed with CUDA events on its stream in a second pass over the
-               same steps (gp_profile_enable), against MEASURED_PEAKS.json
-  cpu_baseline the CPU oracle (oracle/) on the same workload, bounded sample, rank 0 / N=1 only
-  --impl reference   the reference's own CUDA path (oracle/_ref/*.so + its torch ops, oracle/ref_pipeline.py)
+  value        ms per train iteration, whole job = step time / 8, inputs resident in HBM, max over ranks
+  e2e          same through the public API with every sample's camera + time + target image coming from pinned host
+               memory and the step's loss read back
+  secondary    (N = 1) ms per iteration on the other BASELINE.json configs, one sample per step: c4_1m_800x800 (the
+               1 M-Gaussian scene north_star states its 2x target on), c2 (100 k), c3 (500 k, 536x960)
+  roofline     the dominant kernel of the step (CUDA events around every launch in a second pass, gp_profile_enable)
+               against MEASURED_PEAKS.json / the measured FP32 peak; ``rooflines`` holds the same for every kernel
+  cpu_baseline the deformation stage (the only part of the path with a CPU implementation) on BASELINE.json
+               configs[0] (20 k x 512, forward), oracle/ on the host cores: 1 thread and all cores
+  --impl reference   the reference's own CUDA path (oracle/_ref/*.so + its torch ops, oracle/ref_pipeline.py), same job
+  --mode extrapolate configs[3]: 1 M Gaussians, 200 timesteps x 50 views, frames sharded over the ranks, frames/s
 """
 import argparse
 import json
@@ -35,9 +41,13 @@ METRIC = "train-iter ms (deform+raster fwd/bwd)"
 WORKLOADS = {
     "c2_dnerf_100k_800x800": dict(N=100_000, W=800, H=800, Kp=512, K=6, shape="dnerf"),
     "c3_hyper_500k_536x960": dict(N=500_000, W=536, H=960, Kp=512, K=6, shape="hyper"),
+    "c4_1m_800x800": dict(N=1_000_000, W=800, H=800, Kp=512, K=6, shape="dnerf"),
     "c5_2m_800x800": dict(N=2_000_000, W=800, H=800, Kp=512, K=6, shape="dnerf"),
     "tiny": dict(N=5_000, W=160, H=112, Kp=64, K=6, shape="dnerf"),
 }
+HEADLINE = "c5_2m_800x800"
+SECONDARY = ("c4_1m_800x800", "c2_dnerf_100k_800x800", "c3_hyper_500k_536x960")
+SAMPLES_PER_STEP = 8
 ITER = 50_000          # > second_stage_iteration + xyz_noise_iteration: keypoint stage, noise factor 0
 
 
@@ -47,11 +57,15 @@ def parse():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="c2_dnerf_100k_800x800", choices=list(WORKLOADS))
+    ap.add_argument("--workload", default=HEADLINE, choices=list(WORKLOADS))
+    ap.add_argument("--samples-per-step", type=int, default=SAMPLES_PER_STEP)
+    ap.add_argument("--mode", default="train", choices=["train", "extrapolate"])
+    ap.add_argument("--frames", type=int, default=200 * 50, help="extrapolate: timesteps x views")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-profile", action="store_true")
+    ap.add_argument("--no-secondary", action="store_true")
     ap.add_argument("--ncams", type=int, default=16)
-    ap.add_argument("--eager", action="store_true", help="ours: do not capture the iteration into a CUDA graph")
+    ap.add_argument("--exchange", default=os.environ.get("GP_EXCHANGE", "auto"), choices=["auto", "nccl", "nvls"])
     return ap.parse_args()
 
 
@@ -141,10 +155,15 @@ class ClockSampler:
 # ------------------------------------------------------------------------------------------------ our arm
 
 class OurRunner:
-    def __init__(self, wl, dev, ncams, world):
+    """This package's arm: ``S`` samples per step, this rank renders samples rank, rank + world, ... of each step."""
+
+    def __init__(self, wl, dev, ncams, world, samples_per_step=1, exchange="auto"):
         from gaussianprediction_b200.deform import KeypointDeformation
         from gaussianprediction_b200.renderer import SceneModel
-        self.wl, self.dev, self.world = wl, dev, world
+        self.wl, self.dev, self.world, self.S = wl, dev, world, int(samples_per_step)
+        assert self.S % world == 0, "samples per step must divide evenly over the ranks"
+        self.local = self.S // world
+        self.exchange = exchange
         self.rank = int(os.environ.get("RANK", "0")) if world > 1 else 0
         gs, kp, kf, logits, cams, times, grads = build_inputs(wl, ncams)
         torch.manual_seed(2024)
@@ -160,98 +179,109 @@ class OurRunner:
         self.grads_dev = [g.to(dev) for g in grads]
         self.bg = torch.zeros(3, device=dev)
         self.capacity = None
-        self.reducer = None
-        self.h2d_bytes = grads[0].numel() * 4 + (16 + 16 + 3 + 1) * 4
-        self.d2h_bytes = 4
+        self.batch = None
+        self.h2d_bytes = self.S * (grads[0].numel() * 4 + (16 + 16 + 3 + 1) * 4)     # whole job, per step
+        self.d2h_bytes = 4 * world
 
-    def step(self, i, host_inputs=False):
+    # sample g of the global sequence: step s, slot k of this rank -> g = s * S + rank + k * world (parallel.shard_samples)
+    def _ids(self, s):
+        return [s * self.S + self.rank + k * self.world for k in range(self.local)]
+
+    def sample(self, g, host=False):
+        k = g % len(self.cams_dev)
+        if host:
+            return self.cams_host[k], self.times_host[k:k + 1], self.grads_host[g % len(self.grads_host)]
+        return self.cams_dev[k], self.times_dev[k], self.grads_dev[g % len(self.grads_dev)]
+
+    def step(self, s, host_inputs=False):
+        """Eager launches (no graph): autograd accumulates the samples' gradients in ``p.grad``."""
         from gaussianprediction_b200.renderer import render
-        i = i * self.world + self.rank          # samples r, r + W, r + 2W, ... of the global sequence (parallel.shard_samples)
-        k = i % len(self.cams_dev)
-        if host_inputs:
-            cam = cam_to(self.cams_host[k], self.dev, non_blocking=True)
-            t = self.times_host[k:k + 1].to(self.dev, non_blocking=True)
-            G = self.grads_host[i % len(self.grads_host)].to(self.dev, non_blocking=True)
-        else:
-            cam, t, G = self.cams_dev[k], self.times_dev[k], self.grads_dev[i % len(self.grads_dev)]
         for p in self.params:
             p.grad = None
-        pkg = render(cam, self.pc, None, self.bg, time=t, it=ITER, capacity=self.capacity)
-        loss = (pkg["render"] * G).sum()
-        loss.backward()
+        total = None
+        for g in self._ids(s):
+            cam, t, G = self.sample(g, host_inputs)
+            if host_inputs:
+                cam, t, G = cam_to(cam, self.dev, True), t.to(self.dev, non_blocking=True), G.to(self.dev, non_blocking=True)
+            pkg = render(cam, self.pc, None, self.bg, time=t, it=ITER, capacity=self.capacity)
+            loss = (pkg["render"] * G).sum()
+            loss.backward()
+            total = loss.detach() if total is None else total + loss.detach()
         if self.world > 1:
             self.allreduce()
-        return loss
+        return total
+
+    def make_reducer(self):
+        from gaussianprediction_b200 import parallel
+        d = self.pc.deformation
+        live = [p for p in self.params if id(p) in self._live]
+        if self.world == 1:
+            return parallel.FlatGradAllReduce(live)                 # one bucket -> the step stays one graph
+        cls = parallel.FlatGradAllReduce
+        if self.exchange in ("auto", "nvls") and hasattr(parallel, "NvlsFlatGradAllReduce"):
+            try:
+                ok = parallel.NvlsFlatGradAllReduce.supported()
+            except Exception:
+                ok = False
+            if ok:
+                cls = parallel.NvlsFlatGradAllReduce
+            elif self.exchange == "nvls":
+                raise SystemExit("--exchange nvls: NVSwitch multicast memory is not available here")
+        self.exchange_kind = cls.__name__
+        return cls(live, first=[self.pc._features_dc, self.pc._features_rest],
+                   second=[d._xyz, d._rotation, d._scaling, d._opacity] + list(d.weights_model.parameters()))
 
     def enable_graph(self):
-        """Capture the whole iteration into one CUDA graph (gaussianprediction_b200.pipeline.TrainStep)."""
-        from gaussianprediction_b200.pipeline import RenderStep, TrainStep
-        reducer = None
-        if self.world > 1:
-            from gaussianprediction_b200.parallel import FlatGradAllReduce
-            # only parameters that receive a gradient on this path take part in the exchange (known after the eager pass)
-            d = self.pc.deformation
-            reducer = FlatGradAllReduce([p for p in self.params if p.grad is not None],
-                                        first=[self.pc._features_dc, self.pc._features_rest],
-                                        second=[d._xyz, d._rotation, d._scaling, d._opacity] + list(d.weights_model.parameters()))
-        self.graph_reducer = reducer
-        self.train_step = TrainStep(self.pc, self.cams_dev[0], self.capacity, bg=self.bg, iteration=ITER, reducer=reducer)
-        self.render_step = RenderStep(self.pc, self.cams_dev[0], self.capacity, bg=self.bg, iteration=ITER)
+        """Capture the iteration (gaussianprediction_b200.pipeline.BatchStep: one or two captured TrainSteps)."""
+        from gaussianprediction_b200.pipeline import BatchStep
+        # only parameters that receive a gradient on this path take part (known after the eager pass)
+        self._live = {id(p) for p in self.params if p.grad is not None}
+        self.exchange_kind = "none"
+        self.batch = BatchStep(self.pc, self.cams_dev[0], self.capacity, self.make_reducer, self.local, bg=self.bg,
+                               iteration=ITER)
 
-    def _host_sample(self, i):
-        i = i * self.world + self.rank
-        k = i % len(self.cams_dev)
-        return self.cams_host[k], self.times_host[k:k + 1], self.grads_host[i % len(self.grads_host)]
-
-    def step_graph(self, i, host_inputs=False):
+    def step_graph(self, s, host_inputs=False):
+        ids = self._ids(s)
         if host_inputs:
-            # end-to-end: every sample comes from pinned host memory; sample i+1 is copied while step i computes
-            if getattr(self, "_prefetched", None) != i:
-                self.train_step.prefetch(*self._host_sample(i))
-            loss = self.train_step.step_prefetched()
-            self.train_step.prefetch(*self._host_sample(i + 1))
-            self._prefetched = i + 1
-            return loss
-        i = i * self.world + self.rank
-        k = i % len(self.cams_dev)
-        if host_inputs:
-            cam, t, G = self.cams_host[k], self.times_host[k:k + 1], self.grads_host[i % len(self.grads_host)]
-        else:
-            cam, t, G = self.cams_dev[k], self.times_dev[k], self.grads_dev[i % len(self.grads_dev)]
-        loss = self.train_step(cam, t, G)       # with world > 1 the step includes the gradient all-reduce
-        return loss
+            nxt = self.sample(self._ids(s + 1)[0], True)
+            return self.batch.step_host([self.sample(g, True) for g in ids], next_first=nxt)
+        return self.batch.step([self.sample(g) for g in ids])
 
     def allreduce(self):
-        if self.reducer is None:
+        if getattr(self, "_grouped", None) is None:
             from gaussianprediction_b200.parallel import GroupedGradAllReduce
-            self.reducer = GroupedGradAllReduce(self.params)
-        self.reducer.reduce()
+            self._grouped = GroupedGradAllReduce(self.params)
+        self._grouped.reduce()
 
-    def eval_fps(self, steps, graph=False):
-        """Forward-only render FPS in the reference's own span (eval.py:210-214: sync, render(), sync)."""
-        from gaussianprediction_b200.renderer import render
-        ts = []
-        with torch.no_grad():
-            for i in range(steps + 3):
-                k = i % len(self.cams_dev)
-                torch.cuda.synchronize()
-                t0 = time.perf_counter()
-                if graph:
-                    self.render_step(self.cams_dev[k], self.times_dev[k])
-                else:
-                    render(self.cams_dev[k], self.pc, None, self.bg, time=self.times_dev[k], it=ITER, capacity=self.capacity)
-                torch.cuda.synchronize()
-                if i >= 3:
-                    ts.append(time.perf_counter() - t0)
-        return 1.0 / float(np.mean(ts))
+    def measured_fps(self, frames, world):
+        """Forward-only frames/s of the whole job: every rank renders ``frames`` frames of its shard through the captured
+        ``RenderStep`` between two barriers; the reference's span (eval.py:210-214) is one frame between two syncs."""
+        import torch.distributed as dist
+        from gaussianprediction_b200.pipeline import RenderStep
+        rs = RenderStep(self.pc, self.cams_dev[0], self.capacity, bg=self.bg, iteration=ITER)
+        for i in range(3):
+            rs(self.cams_dev[i % len(self.cams_dev)], self.times_dev[i % len(self.times_dev)])
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        t0 = time.perf_counter()
+        for i in range(frames):
+            k = (i * world + self.rank) % len(self.cams_dev)
+            rs(self.cams_dev[k], self.times_dev[k])
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        dt = max_over_ranks(dt, world, self.dev)
+        del rs
+        return frames * world / dt
 
 
 class RefRunner:
-    """The reference's CUDA path (see oracle/ref_pipeline.py)."""
+    """The reference's CUDA path (oracle/ref_pipeline.py) on ONE GPU: all ``S`` samples of a step, gradients
+    accumulated by autograd as the reference's summed loss does (train.py:113-133)."""
 
-    def __init__(self, wl, dev, ncams, world):
+    def __init__(self, wl, dev, ncams, world, samples_per_step=1, exchange=None):
         from oracle.ref_pipeline import RefKeypointModel
-        self.wl, self.dev, self.world = wl, dev, 1
+        self.wl, self.dev, self.world, self.S = wl, dev, 1, int(samples_per_step)
         gs, kp, kf, logits, cams, times, grads = build_inputs(wl, ncams)
         torch.manual_seed(2024)
         self.pc = RefKeypointModel(model_args(), gs.xyz, gs.rotation, gs.scaling, gs.opacity, gs.motion_feature, kp, kf,
@@ -264,48 +294,49 @@ class RefRunner:
         self.grads_host = [g.pin_memory() for g in grads]
         self.grads_dev = [g.to(dev) for g in grads]
         self.bg = torch.zeros(3, device=dev)
-        self.h2d_bytes = grads[0].numel() * 4 + (16 + 16 + 3 + 1) * 4
+        self.h2d_bytes = self.S * (grads[0].numel() * 4 + (16 + 16 + 3 + 1) * 4)
         self.d2h_bytes = 4
 
-    def calibrate(self):
-        return None
-
-    def step(self, i, host_inputs=False):
+    def step(self, s, host_inputs=False):
         from oracle.ref_pipeline import ref_render
-        k = i % len(self.cams_dev)
-        if host_inputs:
-            cam = cam_to(self.cams_host[k], self.dev, non_blocking=True)
-            t = self.times_host[k:k + 1].to(self.dev, non_blocking=True)
-            G = self.grads_host[i % len(self.grads_host)].to(self.dev, non_blocking=True)
-        else:
-            cam, t, G = self.cams_dev[k], self.times_dev[k], self.grads_dev[i % len(self.grads_dev)]
         for p in self.params:
             p.grad = None
-        pkg = ref_render(cam, self.pc, self.bg, t, ITER)
-        loss = (pkg["render"] * G).sum()
-        loss.backward()
-        return loss
+        total = None
+        for g in range(s * self.S, (s + 1) * self.S):
+            k = g % len(self.cams_dev)
+            if host_inputs:
+                cam = cam_to(self.cams_host[k], self.dev, non_blocking=True)
+                t = self.times_host[k:k + 1].to(self.dev, non_blocking=True)
+                G = self.grads_host[g % len(self.grads_host)].to(self.dev, non_blocking=True)
+            else:
+                cam, t, G = self.cams_dev[k], self.times_dev[k], self.grads_dev[g % len(self.grads_dev)]
+            pkg = ref_render(cam, self.pc, self.bg, t, ITER)
+            loss = (pkg["render"] * G).sum()
+            loss.backward()
+            total = loss.detach() if total is None else total + loss.detach()
+        return total
 
-    def eval_fps(self, steps):
+    step_graph = step
+
+    def measured_fps(self, frames, world):
         from oracle.ref_pipeline import ref_render
-        ts = []
         with torch.no_grad():
-            for i in range(steps + 3):
+            for i in range(2):
+                ref_render(self.cams_dev[i], self.pc, self.bg, self.times_dev[i], ITER)
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            for i in range(frames):
                 k = i % len(self.cams_dev)
-                torch.cuda.synchronize()
-                t0 = time.perf_counter()
                 ref_render(self.cams_dev[k], self.pc, self.bg, self.times_dev[k], ITER)
-                torch.cuda.synchronize()
-                if i >= 3:
-                    ts.append(time.perf_counter() - t0)
-        return 1.0 / float(np.mean(ts))
+            torch.cuda.synchronize()
+        return frames / (time.perf_counter() - t0)
 
 
 # ------------------------------------------------------------------------------------------------ timing
 
 def timed_steps(runner, steps, warmup, world, host_inputs, flush, graph=False):
     """W untimed steps, then exactly K steps; every step is bracketed by CUDA events on the current stream, L2 is
-    flushed (256 MiB write) between steps outside the events; returns (sum of per-step device ms, wall ms)."""
+    flushed (256 MiB write) between steps outside the events; returns (per-step device ms list, wall ms)."""
     import torch.distributed as dist
     step = runner.step_graph if graph else runner.step
     for i in range(warmup):
@@ -319,7 +350,7 @@ def timed_steps(runner, steps, warmup, world, host_inputs, flush, graph=False):
     evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
     t0 = time.perf_counter()
     for i in range(steps):
-        flush.add_(1.0)                      # evict L2 (126 MB) between timed iterations
+        flush.add_(1.0)                      # evict L2 (126 MB) between timed steps
         evs[i][0].record()
         loss = step(warmup + i, host_inputs)
         if host_inputs:
@@ -330,8 +361,7 @@ def timed_steps(runner, steps, warmup, world, host_inputs, flush, graph=False):
         dist.barrier()
     torch.cuda.synchronize()
     wall_ms = (time.perf_counter() - t0) * 1e3
-    dev_ms = sum(a.elapsed_time(b) for a, b in evs)
-    return dev_ms, wall_ms
+    return [a.elapsed_time(b) for a, b in evs], wall_ms
 
 
 def max_over_ranks(x, world, dev):
@@ -344,14 +374,21 @@ def max_over_ranks(x, world, dev):
 
 
 def profile_pass(runner, steps, warmup):
-    """Second pass over the same steps with per-kernel CUDA events (same stream); returns {kernel: (launches, ms)}."""
+    """Second pass over the same steps with a CUDA-event pair around every library launch (same stream, eager
+    launches); returns {kernel: (launches, ms)}."""
     import ctypes
     from gaussianprediction_b200 import _lib
     L = _lib.lib()
-    L.gp_profile_enable(1)
-    for i in range(steps):
-        runner.step(warmup + i, False)
-    torch.cuda.synchronize()
+    world, runner.world = runner.world, 1          # no exchange in the profiling pass (per-kernel times only)
+    try:
+        runner.step(warmup, False)
+        torch.cuda.synchronize()
+        L.gp_profile_enable(1)
+        for i in range(steps):
+            runner.step(warmup + i, False)
+        torch.cuda.synchronize()
+    finally:
+        runner.world = world
     buf = ctypes.create_string_buffer(1 << 16)
     L.gp_profile_report(buf, len(buf))
     L.gp_profile_enable(0)
@@ -379,109 +416,338 @@ def workload_stats(runner):
                 ex = R.export_state(st)
                 out = dict(R=int(st.num_rendered), visible=int((radii > 0).sum()),
                            pairs=int(ex["n_contrib"].to(torch.int64).sum()))
+            del color, radii, depth, tidx, st
     out["max_R"] = max_r
     return out
 
 
-# dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full captures
-# (profiles/r1_ncu_full.md), C2 workload only; other workloads report null
+# dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full captures (profiles/), keyed
+# by workload; other workloads report null
 NCU_DRAM_BYTES = {"c2_dnerf_100k_800x800": {"gp_render_bwd_kernel": 24.19e6, "gp_render_fwd_kernel": 6.97e6}}
+NCU_DRAM_SOURCE = "profiles/r1_ncu_full.md"
 
 
-def roofline_for(prof, stats, wl, steps, peaks):
-    """Dominant kernel of the step and its achieved rate.  Algorithmic work per launch:
-    HBM kernels in bytes (SURVEY.md §8d per-unit figures), blend kernels in FP32 operations per evaluated
-    pixel x Gaussian pair (18 forward, 45 backward, SURVEY.md §8d hand counts; pair count = sum of n_contrib)."""
+def measured_fp32_peak(dev, peaks):
+    """FP32 FMA-pipe peak of this GPU, measured (gp_fma_peak: 8 independent FFMA chains per thread, grid = 8 x SMs),
+    next to the derived 148 SM x 128 lanes x 2 x clock.  TFLOP/s."""
+    import ctypes
+    from gaussianprediction_b200 import _lib
+    L = _lib.lib()
+    derived = 148 * 128 * 2 * peaks.get("sm_max_mhz", 1965.0) * 1e6 / 1e12
+    if not hasattr(L, "gp_fma_peak"):
+        return derived, derived, "derived 148 SM x 128 lanes x 2 x sm_max_mhz"
+    out = torch.zeros(1, device=dev)
+    best = 0.0
+    iters = 1 << 14
+    for _ in range(5):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        flops = ctypes.c_double()
+        _lib.check(L.gp_fma_peak(iters, out.data_ptr(), ctypes.byref(flops), _lib.stream_ptr()), "gp_fma_peak")
+        e1.record()
+        torch.cuda.synchronize()
+        best = max(best, flops.value / (e0.elapsed_time(e1) * 1e-3) / 1e12)
+    return best, derived, "measured in this run (gp_fma_peak, best of 5)"
+
+
+def rooflines(prof, stats, wl, steps, samples, peaks, fp32_peak, fp32_src):
+    """Achieved rate of EVERY kernel of the step against the roofline that bounds it.  Algorithmic work per launch
+    (DESIGN.md par. 4): HBM kernels in bytes (SURVEY.md par. 8d per-unit figures), blend kernels in FP32 operations per
+    evaluated pixel x Gaussian pair (18 forward, 45 backward, SURVEY.md par. 8d hand counts; pairs = sum of n_contrib),
+    the search in sub + FMA per (Gaussian, keypoint, dimension)."""
     if not prof:
-        return None, {}
+        return None, {}, {}
     per = {k: v[1] / max(v[0], 1) for k, v in prof.items()}            # ms per launch
     tot = {k: v[1] / steps for k, v in prof.items()}                    # ms per step
-    N, R, pairs = wl["N"], stats["R"], stats["pairs"]
+    calls = {k: v[0] / steps for k, v in prof.items()}
+    N, R, pairs, Kp = wl["N"], stats["R"], stats["pairs"], wl["Kp"]
     hbm = peaks.get("hbm_gbs", 6650.0)
-    fp32_peak = 148 * 128 * 2 * peaks.get("sm_max_mhz", 1965.0) * 1e6 / 1e12   # TFLOP/s, derived (not measured)
+    mlp_fma = Kp * (104 * 256 + 3 * 256 * 256 + 256 * 7)
     work = {
         "gp_preprocess_kernel": ("hbm", 311.0 * N),
         "gp_preprocess_bwd_kernel": ("hbm", 535.0 * N),
-        "gp_rs_scatter_kernel": ("hbm", None),
+        "gp_rs_pass_kernel": ("hbm", None),
         "gp_render_fwd_kernel": ("fp32", 18.0 * pairs),
         "gp_render_bwd_kernel": ("fp32", 45.0 * pairs),
-        "gp_knn_kernel": ("fp32", 2.0 * 2 * N * wl["Kp"] * 35),
+        "gp_knn_kernel": ("fp32", 2.0 * 2 * N * Kp * 35),
         "gp_blend_fwd_kernel": ("hbm", 128.0 * N),
         "gp_blend_bwd_kernel": ("hbm", 204.0 * N),
+        "gp_block_sum_kernel": ("hbm", 8.0 * N),
+        "gp_duplicate_kernel": ("hbm", 20.0 * N + 8.0 * R),
+        "gp_tile_ranges_kernel": ("hbm", 4.0 * R),
+        "gp_kpmlp_fwd_kernel": ("fp32", 2.0 * mlp_fma),
+        "gp_kpmlp_bwd_data_kernel": ("fp32", 2.0 * mlp_fma),
+        "gp_kpmlp_bwd_weights_kernel": ("fp32", 2.0 * mlp_fma),
     }
+    # the sort: 16 B per key per pass (key + value, read + write); 4 passes over P depth keys + the tile-id passes over R
+    n_pass = calls.get("gp_rs_pass_kernel", 0) / max(samples, 1)       # sort passes per sample
+    if n_pass:
+        depth_passes = min(4.0, n_pass)
+        work["gp_rs_pass_kernel"] = ("hbm", (depth_passes * 16.0 * N + (n_pass - depth_passes) * 16.0 * R) / n_pass)
+    table = {}
+    for k in sorted(tot, key=tot.get, reverse=True):
+        kind, w = work.get(k, ("hbm", None))
+        row = {"ms_per_step": round(tot[k], 4), "ms_per_launch": round(per[k], 4), "launches_per_step": round(calls[k], 2),
+               "bound": kind}
+        if w is not None:
+            sec = per[k] * 1e-3
+            if kind == "hbm":
+                ach, peak, unit = w / sec / 1e9, hbm, "GB/s"
+            else:
+                ach, peak, unit = w / sec / 1e12, fp32_peak, "TFLOP/s"
+            row.update(achieved=round(ach, 3), peak=round(peak, 3), unit=unit, frac=round(ach / peak, 4))
+        table[k] = row
     top = max(tot, key=tot.get)
-    table = {k: round(v, 4) for k, v in sorted(tot.items(), key=lambda kv: -kv[1])}
-    kind, w = work.get(top, ("hbm", None))
-    if w is None:
-        return {"kernel": top, "bound": kind, "achieved": None, "peak": None, "unit": None, "frac": None, "traffic": None,
-                "ms_per_launch": per[top], "share_of_kernel_time": tot[top] / sum(tot.values())}, table
-    sec = per[top] * 1e-3
-    if kind == "hbm":
-        ach, peak, unit = w / sec / 1e9, hbm, "GB/s"
-    else:
-        ach, peak, unit = w / sec / 1e12, fp32_peak, "TFLOP/s"
-    return {"kernel": top, "bound": kind, "achieved": round(ach, 3), "peak": round(peak, 3), "unit": unit,
-            "frac": round(ach / peak, 4), "traffic": NCU_DRAM_BYTES.get(wl.get("name"), {}).get(top),
-            "traffic_unit": "bytes/launch (ncu dram read+write, profiles/r1_ncu_full.md)",
-            "ms_per_launch": round(per[top], 4),
-            "share_of_kernel_time": round(tot[top] / sum(tot.values()), 4),
-            "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if kind == "hbm" else
-            "derived 148 SM x 128 lanes x 2 x sm_max_mhz (FP32 FMA pipe; not in MEASURED_PEAKS.json)"}, table
+    r = dict(table[top])
+    roof = {"kernel": top, "bound": r["bound"], "achieved": r.get("achieved"), "peak": r.get("peak"), "unit": r.get("unit"),
+            "frac": r.get("frac"), "traffic": NCU_DRAM_BYTES.get(wl.get("name"), {}).get(top),
+            "traffic_unit": f"bytes/launch (ncu dram read+write, {NCU_DRAM_SOURCE})",
+            "ms_per_launch": r["ms_per_launch"], "share_of_kernel_time": round(tot[top] / sum(tot.values()), 4),
+            "peak_source": "MEASURED_PEAKS.json hbm_gbs" if r["bound"] == "hbm" else f"FP32 FMA pipe, {fp32_src}"}
+    return roof, table, {k: round(v, 4) for k, v in sorted(tot.items(), key=lambda kv: -kv[1])}
 
 
 # ------------------------------------------------------------------------------------------------ CPU baseline
 
-def cpu_train_iter(wl, sample_note=True):
-    """One train iteration of the same workload on the host: deformation in torch CPU (oracle/deform_oracle.py, dense
-    formulation, autograd) + rasterizer forward/backward in the single-threaded C oracle (oracle/raster_oracle.c)."""
-    from oracle import deform_oracle as do
-    from oracle import raster_oracle as ro
+def cpu_deformation_baseline(dev, budget_s=12.0):
+    """BASELINE.md par. 4(B): the deformation stage (kNN + blend, forward, no_grad, float32) on BASELINE.json configs[0]
+    (20 k Gaussians x 512 keypoints, nearest_num 6, D = 35) on the host cores with the CPU oracle (oracle/deform_oracle.py,
+    pinned against the reference's own source), at 1 thread (the reference pins OMP/MKL to 1, train.py:13-14) and at all
+    cores; >= 3 warm-ups, then up to 20 runs within the time budget.  The rasterizer has no CPU implementation.  Also
+    timed: the reference's own single-threaded C++ kNN (frnn_bf_cpu) and this library on the same sample."""
+    from gaussianprediction_b200 import synthetic as syn
     from gaussianprediction_b200.deform import DeformableField
-    gs, kp, kf, logits, cams, times, grads = build_inputs(wl, 1)
+    from oracle import deform_oracle as do
+    N, Kp, K = 20_000, 512, 6
+    gs = syn.make_gaussians(N, seed=2024)
+    kp, kf = syn.make_keypoints(gs, Kp=Kp, seed=2025)
+    logits = syn.make_logits(N, K, seed=2026)
     a = model_args()
     torch.manual_seed(2024)
     net = DeformableField(2 * a.time_freq + 6 * a.xyz_freq + a.feature_dim, 7, a.d, a.w)
     sd = dict(net.state_dict())
-    cam = cams[0]
-    leaf = {k: v.clone().requires_grad_(True) for k, v in dict(xyz=gs.xyz, rot=gs.rotation, sc=gs.scaling, op=gs.opacity,
-                                                              kp=kp, kf=kf, logits=logits).items()}
-    shs = torch.cat([gs.features_dc, gs.features_rest], 1).contiguous()
-    t0 = time.perf_counter()
-    p1, p2 = do.hybrid_points(gs.xyz, gs.motion_feature, kp, kf, a.feature_amplify)
-    # kNN: the reference's own single-threaded CPU brute force on a bounded sample of the queries (it is linear in
-    # their number), scaled to all of them; the indices used downstream come from the full-size numpy oracle only
-    # when the sample covers everything.
-    n_q = p1.shape[0]
-    n_s = min(n_q, 20_000)
-    scale = n_q / n_s
-    t_k0 = time.perf_counter()
+    t = torch.tensor([0.37])
+
+    def torch_knn(p1, p2):
+        # the reference's accumulation order (sequential over d, SURVEY.md par. 8c), vectorised over the pairs
+        acc = torch.zeros(p1.shape[0], p2.shape[0])
+        for d in range(p1.shape[1]):
+            diff = p2[None, :, d] - p1[:, None, d]
+            acc = acc + diff * diff
+        return torch.topk(acc, K, dim=1, largest=False, sorted=True)[1]
+
+    def once():
+        with torch.no_grad():
+            p1, p2 = do.hybrid_points(gs.xyz, gs.motion_feature, kp, kf, a.feature_amplify)
+            idx = torch_knn(p1, p2)
+            do.keypoint_forward(t, gs.xyz, gs.rotation, gs.scaling, gs.opacity, kp, kf, logits, idx, sd,
+                                norm_rotation=a.norm_rotation)
+
+    def timed(threads):
+        old = torch.get_num_threads()
+        torch.set_num_threads(threads)
+        try:
+            for _ in range(3):
+                once()
+            ts, t_end = [], time.perf_counter() + budget_s
+            while len(ts) < 20 and (len(ts) < 3 or time.perf_counter() < t_end):
+                t0 = time.perf_counter()
+                once()
+                ts.append((time.perf_counter() - t0) * 1e3)
+        finally:
+            torch.set_num_threads(old)
+        return float(np.median(ts)), len(ts)
+
+    cores = os.cpu_count() or 1
+    one_ms, one_runs = timed(1)
+    all_ms, all_runs = timed(cores)
+    out = {"value": round(one_ms, 2), "unit": "ms per deformation forward (kNN + keypoint MLP + blend)", "cores": 1,
+           "kind": "port", "runs": one_runs,
+           "sample": "BASELINE.json configs[0]: 20k Gaussians x 512 keypoints, nearest_num 6, D=35, forward only, float32, "
+                     "median of the timed runs after 3 warm-ups; torch CPU restatement of the reference ops (oracle/)",
+           "all_cores": {"value": round(all_ms, 2), "cores": cores, "runs": all_runs}}
     try:
         from oracle import ref_cuda
-        _, idx_s = ref_cuda.frnn_bf_cpu(p1[None, :n_s].contiguous(), p2[None], wl["K"], 1e8)   # the reference's own CPU kNN
-        idx_s = idx_s[0]
-        knn_kind = "reference frnn_bf_cpu"
-    except Exception:
-        _, idx_s = do.knn(p1[:n_s].numpy(), p2.numpy(), wl["K"], fma=False)
-        idx_s = torch.from_numpy(idx_s)
-        knn_kind = "oracle knn (numpy)"
-    t_knn = (time.perf_counter() - t_k0) * scale
-    if n_s < n_q:      # neighbours of the remaining queries: any valid index set keeps the downstream work identical
-        idx = torch.cat([idx_s, idx_s.repeat((n_q + n_s - 1) // n_s, 1)[:n_q - n_s]], 0)
+        p1, p2 = do.hybrid_points(gs.xyz, gs.motion_feature, kp, kf, a.feature_amplify)
+        t0 = time.perf_counter()
+        ref_cuda.frnn_bf_cpu(p1[None].contiguous(), p2[None].contiguous(), K, 1e8)
+        out["reference_frnn_bf_cpu_ms"] = round((time.perf_counter() - t0) * 1e3, 2)
+    except Exception as e:                                              # pragma: no cover
+        out["reference_frnn_bf_cpu_ms"] = f"unavailable: {type(e).__name__}"
+    try:
+        from gaussianprediction_b200.deform import KeypointDeformation
+        m = KeypointDeformation(a, gs.xyz, gs.rotation, gs.scaling, gs.opacity, gs.motion_feature, kp, kf, logits=logits).to(dev)
+        tt = t.to(dev)
+        with torch.no_grad():
+            for _ in range(3):
+                m(tt, ITER)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(20):
+                m(tt, ITER)
+            e1.record()
+            torch.cuda.synchronize()
+        out["gpu_same_sample_ms"] = round(e0.elapsed_time(e1) / 20, 4)
+    except Exception as e:                                              # pragma: no cover
+        out["gpu_same_sample_ms"] = f"failed: {type(e).__name__}: {e}"
+    return out
+
+
+# ------------------------------------------------------------------------------------------------ checks / modes
+
+def exchange_check(runner, s):
+    """Outside the timed region (world > 1): the exchanged gradient buffer of one step must equal the sum over the ranks
+    of the per-rank sums, formed independently (all_gather of the un-exchanged buffers, added in rank order)."""
+    import torch.distributed as dist
+    b = runner.batch
+    b.exchange = False
+    b.step([runner.sample(g) for g in runner._ids(s)])
+    torch.cuda.synchronize()
+    local = b.acc.flat.clone()
+    radii_local = b.radii.clone()
+    b.exchange = True
+    parts = [torch.empty_like(local) for _ in range(runner.world)]
+    dist.all_gather(parts, local)
+    want = parts[0].double()
+    for p in parts[1:]:
+        want += p.double()
+    rparts = [torch.empty_like(radii_local) for _ in range(runner.world)]
+    dist.all_gather(rparts, radii_local)
+    rwant = torch.stack(rparts).max(0)[0]
+    del parts
+    b.step([runner.sample(g) for g in runner._ids(s)])
+    torch.cuda.synchronize()
+    got = b.acc.flat.double()
+    scale = float(want.abs().max())
+    err = float((got - want).abs().max()) / max(scale, 1e-30)
+    out = {"max_rel_err": err, "radii_equal": bool(torch.equal(b.radii, rwant)), "bytes": int(local.numel() * 4),
+           "kind": getattr(runner, "exchange_kind", "?")}
+    # per bucket too (a bucket that is all zeros would hide behind the global scale)
+    per = []
+    for _, _, e0, e1 in b.acc.bucket_ranges:
+        sc = float(want[e0:e1].abs().max())
+        per.append(float((got[e0:e1] - want[e0:e1]).abs().max()) / max(sc, 1e-30))
+    out["max_rel_err_per_bucket"] = per
+    out["ok"] = bool(max(per) <= 1e-4 and out["radii_equal"])      # run-to-run atomic-order noise is ~1e-6
+    t = torch.tensor([1.0 if out["ok"] else 0.0], device=local.device)
+    dist.all_reduce(t, op=dist.ReduceOp.MIN)
+    out["ok"] = bool(t.item() > 0)
+    return out
+
+
+def exchange_time(runner, reps=10):
+    """The exchange alone (all buckets back to back on idle GPUs), ms: what a step would pay with no overlap."""
+    import torch.distributed as dist
+    acc = runner.batch.acc
+    for _ in range(2):
+        for w in [acc.all_reduce_bucket(b) for b in acc.buckets()]:
+            if w is not None:
+                w.wait()
+    torch.cuda.synchronize()
+    dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        for w in [acc.all_reduce_bucket(b) for b in acc.buckets()]:
+            if w is not None:
+                w.wait()
+    e1.record()
+    torch.cuda.synchronize()
+    acc.flat.zero_()
+    return max_over_ranks(e0.elapsed_time(e1) / reps, runner.world, runner.dev)
+
+
+def run_single(name, impl, dev, steps, warmup, flush, ncams=8):
+    """One secondary workload at one sample per step on one GPU: ms per train iteration, device-resident and end to end."""
+    wl = dict(WORKLOADS[name], name=name)
+    cls = OurRunner if impl == "ours" else RefRunner
+    r = cls(wl, dev, ncams, 1, 1)
+    out = {"workload": name, "gaussians": wl["N"], "image": f'{wl["W"]}x{wl["H"]}', "samples_per_step": 1}
+    graph = False
+    if impl == "ours":
+        st = workload_stats(r)
+        r.capacity = int(st["max_R"] * 1.25) + 65536
+        r.step(0)
+        r.enable_graph()
+        graph = True
+        out.update(tile_instances=st["R"], blend_pairs=st["pairs"])
+    per, _ = timed_steps(r, steps, warmup, 1, False, flush, graph=graph)
+    per_e, _ = timed_steps(r, steps, warmup, 1, True, flush, graph=graph)
+    if impl == "ours" and r.batch.overflowed()[1]:
+        raise SystemExit(f"{name}: tile-instance capacity overflowed during the timed region")
+    out.update(ms_per_iter=round(sum(per) / steps, 4), ms_per_iter_median=round(float(np.median(per)), 4),
+               e2e_ms_per_iter=round(sum(per_e) / steps, 4))
+    del r
+    torch.cuda.empty_cache()
+    return out
+
+
+def extrapolate_mode(args, dev, rank, world):
+    """BASELINE.json configs[3]: 1 M Gaussians, GCN-style keypoint trajectories, ``frames`` = timesteps x views frames
+    sharded f = r (mod world), no communication; neighbour indices / blend logits computed once per rank (eval.py:125-126).
+    Reports measured aggregate frames/s (barrier, all ranks' frames, barrier)."""
+    import torch.distributed as dist
+    from gaussianprediction_b200 import synthetic as syn
+    name = args.workload if args.workload != HEADLINE else "c4_1m_800x800"
+    wl = dict(WORKLOADS[name], name=name)
+    n_t, n_v = 200, 50
+    frames = min(args.frames, n_t * n_v)
+    line = {"metric": "render FPS (motion extrapolation: per-frame blend + rasterize forward)", "unit": "frames/s",
+            "n_gpus": world if args.impl == "ours" else args.gpus, "higher_is_better": True, "scaling": "strong",
+            "dtype": "f32", "data": "synthetic", "vs_baseline": None,
+            "config": {"workload": name + "_extrapolate", "gaussians": wl["N"], "image": f'{wl["W"]}x{wl["H"]}',
+                       "keypoints": wl["Kp"], "timesteps": n_t, "views": n_v, "frames": frames}}
+    if args.impl == "ours":
+        from gaussianprediction_b200.pipeline import MotionStep
+        r = OurRunner(wl, dev, n_v, world, world)
+        kpts, krot = syn.keypoint_trajectory(r.pc.deformation.super_gaussians.detach().cpu(), frames=n_t)
+        kpts, krot = kpts.to(dev), krot.to(dev)
+        st = workload_stats(r)
+        cap = int(st["max_R"] * 1.6) + 65536            # moving keypoints change the instance count: headroom, checked below
+        with torch.no_grad():
+            r.pc(r.times_dev[0], ITER)                  # indices + logits once (eval.py:125-126)
+        ms = MotionStep(r.pc, r.cams_dev[0], cap, bg=r.bg)
+        mine = list(range(rank, frames, world))
+        for f in mine[:3]:
+            ms(r.cams_dev[f % n_v], kpts[f // n_v % n_t], krot[f // n_v % n_t])
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        t0 = time.perf_counter()
+        over = False
+        for i, f in enumerate(mine):
+            ms(r.cams_dev[f % n_v], kpts[f // n_v % n_t], krot[f // n_v % n_t])
+            if i % 512 == 511:
+                over = over or ms.overflowed()[1]
+        torch.cuda.synchronize()
+        dt = max_over_ranks(time.perf_counter() - t0, world, dev)
+        over = over or ms.overflowed()[1]
+        if over:
+            raise SystemExit("extrapolate: tile-instance capacity overflowed; result invalid")
+        line.update(value=round(frames / dt, 2), ms_per_frame_per_gpu=round(dt / len(mine) * 1e3, 4), frames_timed=frames)
     else:
-        idx = idx_s
-    knn_kind += f" on {n_s} of {n_q} queries, scaled x{scale:.0f}"
-    t_rest0 = time.perf_counter()
-    xyz_t, q_t, s_t, o_t, _, _ = do.keypoint_forward(times[0:1], leaf["xyz"], leaf["rot"], leaf["sc"], leaf["op"], leaf["kp"],
-                                                      leaf["kf"], leaf["logits"], idx, sd, norm_rotation=a.norm_rotation)
-    t_def = time.perf_counter() - t_rest0
-    o = ro.forward(xyz_t.detach().numpy(), o_t.detach().numpy(), np.zeros(3, np.float32), cam.world_view_transform.numpy(),
-                   cam.full_proj_transform.numpy(), cam.camera_center.numpy(), wl["W"], wl["H"], cam.tanfovx, cam.tanfovy,
-                   shs=shs.numpy(), scales=s_t.detach().numpy(), rotations=q_t.detach().numpy())
-    g = ro.backward(o, grads[0].numpy())
-    torch.autograd.backward([xyz_t, q_t, s_t, o_t], [torch.from_numpy(g["means3D"]), torch.from_numpy(g["rotations"]),
-                                                     torch.from_numpy(g["scales"]), torch.from_numpy(g["opacity"])])
-    total = (time.perf_counter() - t_rest0) + t_knn
-    return total * 1e3, dict(knn_ms=t_knn * 1e3, deform_fwd_ms=t_def * 1e3, knn=knn_kind)
+        from oracle import deform_oracle as do
+        from oracle.ref_pipeline import ref_render_motion
+        r = RefRunner(wl, dev, n_v, 1, 1)
+        kpts, krot = syn.keypoint_trajectory(r.pc.super_gaussians.detach().cpu(), frames=n_t)
+        kpts, krot = kpts.to(dev), krot.to(dev)
+        sample = min(frames, 400)                        # bounded sample of the same frame sequence (stride through it)
+        ids = [int(i * frames / sample) for i in range(sample)]
+        with torch.no_grad():
+            wx, wr = r.pc.dense_weights(r.times_dev[0], ITER)                    # eval.py:125-126, dense [N,Kp] x 2
+            for f in ids[:2]:
+                ref_render_motion(r.cams_dev[f % n_v], r.pc, r.bg, wx, wr, kpts[f // n_v % n_t], krot[f // n_v % n_t])
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            for f in ids:
+                ref_render_motion(r.cams_dev[f % n_v], r.pc, r.bg, wx, wr, kpts[f // n_v % n_t], krot[f // n_v % n_t])
+            torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        line.update(value=round(sample / dt, 2), ms_per_frame_per_gpu=round(dt / sample * 1e3, 4), frames_timed=sample,
+                    impl="reference")
+    line["ms_per_step"] = line["ms_per_frame_per_gpu"]
+    line["steps"], line["warmup"] = line["frames_timed"], 3
+    return line
 
 
 # ------------------------------------------------------------------------------------------------ main
@@ -493,6 +759,7 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     wl = dict(WORKLOADS[args.workload], name=args.workload)
     steps, warmup = args.steps, max(args.warmup, 3)
+    S = args.samples_per_step
 
     if args.impl == "reference" and rank != 0:
         return 0                                                   # rank 0 alone runs the reference arm
@@ -514,15 +781,28 @@ def main():
 
     if args.impl == "ours":
         from gaussianprediction_b200 import _lib
-        L = _lib.lib()                                             # raises if the CUDA library is missing
-        runner = OurRunner(wl, dev, args.ncams, eff_world)
+        _lib.lib()                                                 # raises if the CUDA library is missing
     else:
         from oracle import ref_cuda
         for m in ("ref_dgr", "ref_frnn", "ref_prefix_sum"):
             if not ref_cuda.available(m):
                 print(json.dumps({"impl": "reference", "unavailable": f"oracle/_ref/{m}.so not built"}))
                 return 0
-        runner = RefRunner(wl, dev, args.ncams, 1)
+
+    if args.mode == "extrapolate":
+        line = extrapolate_mode(args, dev, rank, eff_world)
+        if rank == 0:
+            print(json.dumps(line))
+        if world > 1 and args.impl == "ours":
+            import torch.distributed as dist
+            dist.barrier()
+            dist.destroy_process_group()
+        return 0
+
+    if S % eff_world != 0:
+        raise SystemExit(f"--samples-per-step {S} does not divide over {eff_world} ranks")
+    cls = OurRunner if args.impl == "ours" else RefRunner
+    runner = cls(wl, dev, args.ncams, eff_world, S, exchange=args.exchange)
 
     stats = None
     if args.impl == "ours":
@@ -535,82 +815,102 @@ def main():
         sampler.start()
     use_graph, graph_note = False, "eager launches"
     eager_ms = None
+    launches = 0
     if args.impl == "ours":
         # eager pass first: it counts the kernels of one step (a graph replay re-issues exactly those launches)
+        n_eager = min(steps, 3)
         launches0 = _lib.lib().gp_launch_count()
-        eager_dev_ms, _ = timed_steps(runner, steps, warmup, eff_world, False, flush)
-        launches = _lib.lib().gp_launch_count() - launches0
-        launches = launches * steps // (steps + warmup)
-        eager_ms = max_over_ranks(eager_dev_ms, eff_world, dev) / steps / eff_world
-        if not args.eager:
-            try:
-                runner.enable_graph()
-                use_graph, graph_note = True, "whole iteration replayed as one CUDA graph (pipeline.TrainStep)"
-            except Exception as e:                                  # pragma: no cover
-                graph_note = f"eager launches (graph capture failed: {type(e).__name__}: {e})"
-    else:
-        launches = 0
-    dev_ms, wall_ms = timed_steps(runner, steps, warmup, eff_world, False, flush, graph=use_graph)
-    e2e_dev_ms, e2e_wall_ms = timed_steps(runner, steps, warmup, eff_world, True, flush, graph=use_graph)
+        eager_per, _ = timed_steps(runner, n_eager, 1, eff_world, False, flush)
+        launches = (_lib.lib().gp_launch_count() - launches0) // (n_eager + 1) * steps
+        eager_ms = max_over_ranks(sum(eager_per), eff_world, dev) / n_eager / S
+        runner.enable_graph()
+        use_graph = True
+        graph_note = ("every sample replayed as captured CUDA graphs (pipeline.BatchStep); exchange: " + runner.exchange_kind)
+    per, wall_ms = timed_steps(runner, steps, warmup, eff_world, False, flush, graph=use_graph)
+    per_e, _ = timed_steps(runner, steps, warmup, eff_world, True, flush, graph=use_graph)
     clocks = sampler.stop() if rank == 0 else None
-    if use_graph:
-        R_last, over = runner.train_step.overflowed()
-        if over:
-            raise SystemExit("tile-instance capacity overflowed during the timed region: result invalid")
+    if use_graph and runner.batch.overflowed()[1]:
+        raise SystemExit("tile-instance capacity overflowed during the timed region: result invalid")
 
-    dev_ms = max_over_ranks(dev_ms, eff_world, dev)
-    e2e_dev_ms = max_over_ranks(e2e_dev_ms, eff_world, dev)
+    dev_ms = max_over_ranks(sum(per), eff_world, dev)
+    e2e_dev_ms = max_over_ranks(sum(per_e), eff_world, dev)
     ms_per_step = dev_ms / steps
-    e2e_ms_per_step = e2e_dev_ms / steps
-    value = ms_per_step / eff_world                                # whole job: ms per (camera, time) sample
-    e2e_value = e2e_ms_per_step / eff_world
-
-    fps = runner.eval_fps(min(steps, 20), graph=True) if use_graph else runner.eval_fps(min(steps, 20))
+    value = ms_per_step / S                                        # whole job: ms per (camera, time) train iteration
+    e2e_value = e2e_dev_ms / steps / S
 
     line = {
         "metric": METRIC, "value": round(value, 4), "unit": "ms/iter", "n_gpus": eff_world if args.impl == "ours" else args.gpus,
         "steps": steps, "warmup": warmup, "ms_per_step": round(ms_per_step, 4), "higher_is_better": False,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": args.workload, "gaussians": wl["N"], "image": f'{wl["W"]}x{wl["H"]}', "keypoints": wl["Kp"],
-                   "nearest_num": wl["K"], "knn_type": "hybird", "sh_degree": 3, "samples_per_step_per_gpu": 1,
+                   "nearest_num": wl["K"], "knn_type": "hybird", "sh_degree": 3, "samples_per_step": S,
                    "l2": "flushed between timed steps (256 MiB write, outside the events)",
-                   "timing": "sum of per-step CUDA-event times, max over ranks"},
+                   "timing": "sum of per-step CUDA-event times, max over ranks; value = step time / samples per step"},
         "e2e": {"value": round(e2e_value, 4), "unit": "ms/iter", "h2d_bytes_per_step": runner.h2d_bytes,
                 "d2h_bytes_per_step": runner.d2h_bytes},
         "gpu_launches": int(launches),
-        "train_iters_per_s": round(1e3 / value, 2), "render_fps": round(fps * eff_world, 2),
+        "ms_per_step_median": round(float(np.median(per)), 4),
+        "train_iters_per_s": round(1e3 / value, 2),
         "wall_ms_per_step": round(wall_ms / steps, 4),
+        "launch": graph_note,
     }
-    line["config"]["launch"] = graph_note
     if eager_ms is not None:
         line["eager_ms_per_iter"] = round(eager_ms, 4)
+    if stats:
+        line["workload_stats"] = dict(tile_instances=stats["R"], visible=stats["visible"], blend_pairs=stats["pairs"],
+                                      max_tile_instances=stats["max_R"])
     if args.impl == "reference":
         line["impl"] = "reference"
-        line["n_gpus"] = args.gpus
+        line["reference_gpus"] = 1
         line["cpu_baseline"] = {"value": line["value"], "unit": "ms/iter", "cores": 0, "kind": "reference",
-                                "sample": "the reference's CUDA kernels (oracle/_ref, sm_100) + its torch ops on one B200: "
-                                          "north_star's bar; the rasterizer has no CPU implementation"}
-        line["e2e"] = {"value": round(e2e_value, 4), "unit": "ms/iter", "h2d_bytes_per_step": runner.h2d_bytes,
-                       "d2h_bytes_per_step": runner.d2h_bytes}
-    if stats:
-        line["config"].update(tile_instances=stats["R"], visible=stats["visible"], blend_pairs=stats["pairs"])
+                                "sample": "the reference's CUDA kernels (oracle/_ref, sm_100) + its torch ops on ONE B200 "
+                                          "(all samples of the step on that GPU): north_star's bar; the rasterizer has no "
+                                          "CPU implementation"}
     if clocks is not None:
         line["clocks"] = clocks
+
+    if args.impl == "ours" and eff_world > 1:
+        chk = exchange_check(runner, warmup + steps)
+        line["exchange_check"] = chk
+        line["exchange_alone_ms"] = round(exchange_time(runner), 4)
+        if not chk["ok"]:
+            if rank == 0:
+                print(json.dumps(line))
+            raise SystemExit("exchange check failed: the reduced gradients are not the sum of the per-rank gradients")
+
+    # forward-only frames/s of the whole job, measured (not extrapolated)
+    try:
+        line["render_fps"] = round(runner.measured_fps(min(4 * steps, 64) if args.impl == "ours" else min(steps, 8), eff_world), 2)
+    except Exception as e:                                          # pragma: no cover
+        line["render_fps"] = None
+        line["render_fps_error"] = f"{type(e).__name__}: {e}"
+
     if args.impl == "ours" and not args.no_profile:
-        prof = profile_pass(runner, min(steps, 10), warmup)
-        roof, table = roofline_for(prof, stats, wl, min(steps, 10), peaks)
+        fp32_peak, fp32_derived, fp32_src = measured_fp32_peak(dev, peaks)
+        n_prof = min(steps, 4)
+        prof = profile_pass(runner, n_prof, warmup)
+        roof, table, per_kernel = rooflines(prof, stats, wl, n_prof, runner.local, peaks, fp32_peak, fp32_src)
         line["roofline"] = roof
-        line["kernel_ms_per_step"] = table
+        line["rooflines"] = table
+        line["peaks"] = {"hbm_gbs": peaks.get("hbm_gbs"), "fp32_tflops_measured": round(fp32_peak, 2),
+                         "fp32_tflops_derived": round(fp32_derived, 2), "source": fp32_src}
+
+    if rank == 0 and eff_world == 1 and not args.no_secondary and args.workload == HEADLINE:
+        sec = []
+        del runner
+        torch.cuda.empty_cache()
+        for name in SECONDARY:
+            try:
+                sec.append(run_single(name, args.impl, dev, steps, warmup, flush))
+            except Exception as e:                                  # pragma: no cover
+                sec.append({"workload": name, "error": f"{type(e).__name__}: {e}"})
+        line["secondary"] = sec
+
     if args.impl == "ours" and rank == 0 and eff_world == 1 and not args.no_cpu_baseline:
-        small = dict(wl)
         try:
-            ms, parts = cpu_train_iter(small)
-            line["cpu_baseline"] = {"value": round(ms, 1), "unit": "ms/iter", "cores": 1, "kind": "port",
-                                    "sample": f"1 train iteration of the same workload ({args.workload}) on the host: "
-                                              f"kNN {parts['knn']} {parts['knn_ms']:.0f} ms, torch-CPU dense deformation "
-                                              f"({torch.get_num_threads()} threads), C oracle rasterizer fwd+bwd (1 thread)"}
+            line["cpu_baseline"] = cpu_deformation_baseline(dev)
         except Exception as e:                                      # pragma: no cover
-            line["cpu_baseline"] = {"value": None, "unit": "ms/iter", "cores": 1, "kind": "port", "sample": f"failed: {e}"}
+            line["cpu_baseline"] = {"value": None, "unit": "ms", "cores": 1, "kind": "port", "sample": f"failed: {e}"}
     if rank == 0:
         print(json.dumps(line))
     if world > 1 and args.impl == "ours":

@@ -47,6 +47,7 @@ SIGNATURES = {
     "gp_launch_count": (c_longlong, []),
     "gp_profile_enable": (c_int, [c_int]),
     "gp_profile_report": (c_int, [ctypes.c_char_p, c_size_t]),
+    "gp_fma_peak": (c_int, [c_int, _P, POINTER(c_double), _P]),
     "gp_raster_sizes": (c_int, [c_int, c_int, c_int, c_longlong, POINTER(c_size_t), POINTER(c_size_t), POINTER(c_size_t)]),
     "gp_raster_preprocess": (c_int, [POINTER(RasterCfg)] + [_P] * 10 + [_P, _P, _P]),
     "gp_raster_num_rendered": (c_int, [_P, _P, POINTER(c_int)]),

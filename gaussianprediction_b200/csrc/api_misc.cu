@@ -90,3 +90,37 @@ extern "C" int gp_profile_report(char* buf, size_t buf_bytes) {
   }
   return GP_OK;
 }
+
+// ------------------------------------------------------------------------------------------------
+// FP32 FMA-pipe micro-benchmark: the measured denominator of the render kernels' roofline (SURVEY.md par. 8d asks
+// for the derived 148 SM x 128 lanes x 2 x clock figure to be re-measured on the box).
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) gp_fma_peak_kernel(int iters, float* __restrict__ out) {
+  // 8 independent dependent-FFMA chains per thread: enough ILP to hide the 4-cycle FFMA latency at 8 warps/scheduler
+  float a0 = threadIdx.x * 1e-3f, a1 = a0 + 1.f, a2 = a0 + 2.f, a3 = a0 + 3.f, a4 = a0 + 4.f, a5 = a0 + 5.f, a6 = a0 + 6.f,
+        a7 = a0 + 7.f;
+  const float m = 0.999f, c = 1e-3f;
+#pragma unroll 1
+  for (int i = 0; i < iters; i++) {
+#pragma unroll
+    for (int u = 0; u < 8; u++) {
+      a0 = fmaf(a0, m, c); a1 = fmaf(a1, m, c); a2 = fmaf(a2, m, c); a3 = fmaf(a3, m, c);
+      a4 = fmaf(a4, m, c); a5 = fmaf(a5, m, c); a6 = fmaf(a6, m, c); a7 = fmaf(a7, m, c);
+    }
+  }
+  const float s = ((a0 + a1) + (a2 + a3)) + ((a4 + a5) + (a6 + a7));
+  if (s == 123456.789f) out[0] = s;  // never true: keeps the chains alive
+}
+
+extern "C" int gp_fma_peak(int iters, float* out, double* flops, gp_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (iters <= 0 || !out || !flops) return GP_ERR_BAD_ARG;
+  int dev = 0, sms = 0;
+  GP_CUDA_TRY(cudaGetDevice(&dev));
+  GP_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  const int blocks = sms * 8;  // 8 x 256 threads = 2048 resident threads per SM
+  gp_fma_peak_kernel<<<blocks, 256, 0, stream>>>(iters, out);
+  GP_LAUNCH_CHECK();
+  *flops = 2.0 * 64.0 * (double)iters * 256.0 * (double)blocks;
+  return GP_OK;
+}

@@ -14,6 +14,7 @@
 //    and every output gradient is written exactly once, including zeros for culled Gaussians, so no
 //    output tensor needs a memset (the reference zero-fills 300 B per Gaussian per call,
 //    rasterize_points.cu:153-161).
+#include <stdlib.h>
 #include "gmath.cuh"
 #include "raster_common.cuh"
 #include "raster_state.cuh"
@@ -23,6 +24,7 @@
 //   [4] dL/dconic.w   [5] dL/dopacity   [6] dL/dr        [7] dL/dg
 //   [8] dL/db         [9..11] unused
 #define GP_GREC 12
+#define GP_STATIC_MAX_DEVICES_ATTR 64
 #define GP_SACC 9
 
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
@@ -58,7 +60,7 @@ __device__ __forceinline__ float warp_transpose_reduce8(float (&v)[8], int lane)
 }
 
 __global__ void __launch_bounds__(GP_TILE_PIX, 4)
-gp_render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H,
+gp_render_bwd_butterfly_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H,
                      unsigned grid_x, const float* __restrict__ bg_color, const float4* __restrict__ xy_depth,
                      const float4* __restrict__ conic_opacity, const float4* __restrict__ rgb4,
                      const float* __restrict__ colors_precomp, const float* __restrict__ final_Ts,
@@ -228,6 +230,211 @@ gp_render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
       if (a0 != 0.f || a1 != 0.f || a2 != 0.f || a3 != 0.f) red_add_v4(dst, a0, a1, a2, a3);
       if (a4 != 0.f || a5 != 0.f || a6 != 0.f || a7 != 0.f) red_add_v4(dst + 4, a4, a5, a6, a7);
       if (a8 != 0.f) atomicAdd(dst + 8, a8);
+    }
+  }
+}
+
+
+// ------------------------------------------------------------------------------------------------
+// Blend backward, two-phase ("pixel pass, then splat pass") -- the kernel gp_raster_backward launches.
+//
+// The butterfly kernel above spends more instructions on summing 9 values over the 32 pixels of a warp than on the
+// blend math itself (ncu, profiles/r1_ncu_full.md: 14 SHFL + 16 SEL per visit, float atomicAdd on shared memory =
+// CAS spin loops, 31 % bank-conflicted wavefronts).  Here the reduction disappears:
+//   phase 1 (lane = pixel, as before): walk the tile's list back to front, rebuild T by division, and for every
+//           (patch, Gaussian) visit with at least one contributing pixel store TWO scalars per pixel in a warp-private
+//           shared-memory slot:  Wg = G * dL/dalpha  and  U = alpha * T.
+//           dL/dalpha uses ONE scalar recurrence instead of the reference's three colour accumulators:
+//           dL/dalpha_i = T_i (c_i . dpx) - S_i / (1 - alpha_i),  S_i = sum_{k behind i} (c_k . dpx) alpha_k T_k + T_final (bg . dpx)
+//           (the same quantity as backward.cu:506-527, regrouped).
+//   phase 2 (every 16 visits; lane = (slot, half)): lane (s, h) owns the Gaussian of slot s and walks the 16 pixels of
+//           patch rows 2h, 2h+1, accumulating in registers the six moments of Wg about the Gaussian's centre
+//           (1, dx, dy, dx^2, dx dy, dy^2) and sum U dpx_c.  All nine reference gradients are linear in those:
+//             dL/dmean2D = -o (a Mx + b My) W/2, -o (c My + b Mx) H/2;  dL/dconic = -o/2 (Mxx, Mxy, Myy);  dL/dopacity = M0.
+//           One shuffle per value joins the two halves; three red.global.add.v4.f32 per visit add the result to the
+//           Gaussian's packed record.  No shared-memory atomics, no cross-warp accumulator, conflict-free rows (stride 33).
+// ------------------------------------------------------------------------------------------------
+#define GP_BW_SLOTS 16
+#define GP_BW_STRIDE 33
+#define GP_BW_SMEM (GP_TILE_PIX * (4 * 16 + 2 * 4) + 8 * 2 * GP_BW_SLOTS * GP_BW_STRIDE * 4)
+
+__global__ void __launch_bounds__(GP_TILE_PIX, 4)
+gp_render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H,
+                     unsigned grid_x, const float* __restrict__ bg_color, const float4* __restrict__ xy_depth,
+                     const float4* __restrict__ conic_opacity, const float4* __restrict__ rgb4,
+                     const float* __restrict__ colors_precomp, const float* __restrict__ final_Ts,
+                     const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpixels,
+                     const int* __restrict__ hdr, float* __restrict__ grec) {
+  extern __shared__ __align__(16) unsigned char s_raw[];
+  float4* s_co = (float4*)s_raw;
+  float4* s_xyd = s_co + GP_TILE_PIX;
+  float4* s_rgb = s_xyd + GP_TILE_PIX;
+  float4* s_dpx = s_rgb + GP_TILE_PIX;
+  int* s_id = (int*)(s_dpx + GP_TILE_PIX);
+  unsigned* s_mask = (unsigned*)(s_id + GP_TILE_PIX);
+  float* s_w = (float*)(s_mask + GP_TILE_PIX);
+
+  if (hdr[GP_HDR_OVERFLOW]) return;
+  const int t = threadIdx.x, w = t >> 5, lane = t & 31;
+  const unsigned tile = blockIdx.x;
+  const unsigned tile_x = tile % grid_x, tile_y = tile / grid_x;
+  const unsigned px0 = tile_x * GP_TILE_X + (w & 1) * 8, py0 = tile_y * GP_TILE_Y + (w >> 1) * 4;  // patch origin
+  const unsigned px = px0 + (lane & 7);
+  const unsigned py = py0 + (lane >> 3);
+  const bool inside = px < (unsigned)W && py < (unsigned)H;
+  const unsigned pix_id = (unsigned)W * py + px;
+  const float pixfx = (float)px, pixfy = (float)py;
+
+  const uint2 range = ranges[tile];
+  const int rounds = ((range.y - range.x + GP_TILE_PIX - 1) / GP_TILE_PIX);
+  int toDo = range.y - range.x;
+  const int total = toDo;
+
+  const float T_final = inside ? final_Ts[pix_id] : 0.f;
+  float T = T_final;
+  const uint32_t last_contributor = inside ? n_contrib[pix_id] : 0u;
+  float dpx0 = 0.f, dpx1 = 0.f, dpx2 = 0.f;
+  if (inside) {
+    const size_t hw = (size_t)H * W;
+    dpx0 = dL_dpixels[pix_id];
+    dpx1 = dL_dpixels[hw + pix_id];
+    dpx2 = dL_dpixels[2 * hw + pix_id];
+  }
+  s_dpx[t] = make_float4(dpx0, dpx1, dpx2, 0.f);   // read back by this warp only (phase 2)
+  float S = T_final * (bg_color[0] * dpx0 + bg_color[1] * dpx1 + bg_color[2] * dpx2);
+
+  unsigned warp_last = last_contributor;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) warp_last = max(warp_last, __shfl_xor_sync(0xffffffffu, warp_last, o));
+
+  // phase-2 identity of this lane
+  const int slot = lane & (GP_BW_SLOTS - 1), half = lane >> 4;
+  float* const bufW = s_w + (size_t)w * (2 * GP_BW_SLOTS * GP_BW_STRIDE);
+  float* const bufU = bufW + GP_BW_SLOTS * GP_BW_STRIDE;
+  const float* const rowW = bufW + slot * GP_BW_STRIDE + half * 16;
+  const float* const rowU = bufU + slot * GP_BW_STRIDE + half * 16;
+  const float4* const rowD = s_dpx + w * 32 + half * 16;
+  const float fx0 = (float)px0, fy0 = (float)(py0 + 2 * half);
+  const float half_w = 0.5f * W, half_h = 0.5f * H;
+  int nslots = 0;   // warp-uniform
+  int myj = 0;      // batch index of the Gaussian in this lane's slot
+
+  auto splat_pass = [&]() {
+    __syncwarp();
+    const float4 xyd = s_xyd[myj];
+    const float bx = xyd.x - fx0, by = xyd.y - fy0;
+    float m0 = 0.f, mx = 0.f, my = 0.f, mxx = 0.f, mxy = 0.f, myy = 0.f, c0 = 0.f, c1 = 0.f, c2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < 16; i++) {
+      const float Wg = rowW[i], U = rowU[i];
+      const float4 d = rowD[i];
+      const float dx = bx - (float)(i & 7), dy = by - (float)(i >> 3);
+      const float wx = Wg * dx, wy = Wg * dy;
+      m0 += Wg;
+      mx += wx;
+      my += wy;
+      mxx = fmaf(wx, dx, mxx);
+      mxy = fmaf(wx, dy, mxy);
+      myy = fmaf(wy, dy, myy);
+      c0 = fmaf(U, d.x, c0);
+      c1 = fmaf(U, d.y, c1);
+      c2 = fmaf(U, d.z, c2);
+    }
+    m0 += __shfl_xor_sync(0xffffffffu, m0, 16);
+    mx += __shfl_xor_sync(0xffffffffu, mx, 16);
+    my += __shfl_xor_sync(0xffffffffu, my, 16);
+    mxx += __shfl_xor_sync(0xffffffffu, mxx, 16);
+    mxy += __shfl_xor_sync(0xffffffffu, mxy, 16);
+    myy += __shfl_xor_sync(0xffffffffu, myy, 16);
+    c0 += __shfl_xor_sync(0xffffffffu, c0, 16);
+    c1 += __shfl_xor_sync(0xffffffffu, c1, 16);
+    c2 += __shfl_xor_sync(0xffffffffu, c2, 16);
+    if (half == 0 && slot < nslots) {
+      const float4 co = s_co[myj];
+      float* dst = grec + (size_t)s_id[myj] * GP_GREC;
+      const float no = -co.w;
+      red_add_v4(dst, no * (co.x * mx + co.y * my) * half_w, no * (co.z * my + co.y * mx) * half_h, 0.5f * no * mxx,
+                 0.5f * no * mxy);
+      red_add_v4(dst + 4, 0.5f * no * myy, m0, c0, c1);
+      atomicAdd(dst + 8, c2);
+    }
+    __syncwarp();
+  };
+
+  const float tile_fx0 = (float)(tile_x * GP_TILE_X), tile_fy0 = (float)(tile_y * GP_TILE_Y);
+  for (int i = 0; i < rounds; i++, toDo -= GP_TILE_PIX) {
+    __syncthreads();
+    const int progress = i * GP_TILE_PIX + t;
+    unsigned pmask = 0u;
+    if (range.x + progress < range.y) {
+      const int id = point_list[range.y - progress - 1];
+      s_id[t] = id;
+      const float4 co = __ldg(conic_opacity + id);
+      const float4 xyd = __ldg(xy_depth + id);
+      s_co[t] = co;
+      s_xyd[t] = xyd;
+      if (colors_precomp != nullptr)
+        s_rgb[t] = make_float4(colors_precomp[3 * (size_t)id], colors_precomp[3 * (size_t)id + 1],
+                               colors_precomp[3 * (size_t)id + 2], 0.f);
+      else
+        s_rgb[t] = __ldg(rgb4 + id);
+      pmask = gp_patch_mask(co, xyd.x, xyd.y, tile_fx0, tile_fy0);
+    }
+    s_mask[t] = pmask;
+    __syncthreads();
+
+    const int nb = min(GP_TILE_PIX, toDo);
+    // elements of this batch in front of index (total - warp_last) lie behind the last contributor of every pixel
+    // of this warp: start at the first 32-chunk that can matter
+    const int first = total - (int)warp_last - i * GP_TILE_PIX;
+    for (int c0 = max(first, 0) & ~31; c0 < nb; c0 += 32) {
+      unsigned bits = __ballot_sync(0xffffffffu, (s_mask[c0 + lane] >> w) & 1u);
+      while (bits) {
+        const int j = c0 + __ffs(bits) - 1;
+        bits &= bits - 1;
+        // 0-based position of this Gaussian in the tile's front-to-back list
+        const uint32_t contributor = (uint32_t)(total - 1 - (i * GP_TILE_PIX + j));
+        if (contributor >= warp_last) continue;  // warp-uniform: nobody in this warp reaches it
+        bool active = inside && contributor < last_contributor;
+        const float4 xyd = s_xyd[j];
+        const float4 co = s_co[j];
+        const float dx = xyd.x - pixfx;
+        const float dy = xyd.y - pixfy;
+        const float qa = __fmul_rn(co.x, dx);
+        const float qb = __fmul_rn(__fmul_rn(co.z, dy), dy);
+        const float qs = __fmaf_rn(qa, dx, qb);
+        const float qc = __fmul_rn(__fmul_rn(co.y, dx), dy);
+        const float power = __fmaf_rn(qs, -0.5f, -qc);
+        active = active && !(power > 0.0f);
+        const float G = expf(power);
+        const float alpha = fminf(0.99f, __fmul_rn(co.w, G));
+        active = active && !(alpha < 1.0f / 255.0f);
+        if (!__any_sync(0xffffffffu, active)) continue;
+
+        float Wg = 0.f, U = 0.f;
+        if (active) {
+          // one correctly rounded reciprocal serves both divisions by (1 - alpha) (reference backward.cu:503,533)
+          const float inv1ma = __frcp_rn(1.f - alpha);
+          T = T * inv1ma;
+          const float4 col = s_rgb[j];
+          const float cd = col.x * dpx0 + col.y * dpx1 + col.z * dpx2;
+          const float dL_dalpha = T * cd - S * inv1ma;
+          U = alpha * T;
+          S = fmaf(cd, U, S);
+          Wg = G * dL_dalpha;
+        }
+        bufW[nslots * GP_BW_STRIDE + lane] = Wg;
+        bufU[nslots * GP_BW_STRIDE + lane] = U;
+        if (slot == nslots) myj = j;
+        if (++nslots == GP_BW_SLOTS) {
+          splat_pass();
+          nslots = 0;
+        }
+      }
+    }
+    if (nslots) {   // the batch in shared memory is about to be replaced
+      splat_pass();
+      nslots = 0;
     }
   }
 }
@@ -603,9 +810,23 @@ extern "C" int gp_raster_backward(const gp_raster_cfg* cfg, const float* bg, con
   float* grec = (float*)grad_ws;
   GP_CUDA_TRY(cudaMemsetAsync(grec, 0, (size_t)P * GP_GREC * 4, stream));
   const uint32_t* point_list = bn.tvals[gp_tile_sort_sel(W, H)];
-  GP_KERNEL("gp_render_bwd_kernel", stream, gp_render_bwd_kernel<<<gx * gy, GP_TILE_PIX, 0, stream>>>(im.ranges, point_list, W, H, gx, bg, g.xy_depth,
-                                                           g.conic_opacity, g.rgb, colors_precomp, im.final_T,
-                                                           im.n_contrib, dL_dpix, g.hdr, grec));
+  static const bool use_butterfly = getenv("GP_RENDER_BWD_BUTTERFLY") != nullptr;   // A/B knob: the round-1 kernel
+  if (use_butterfly) {
+    GP_KERNEL("gp_render_bwd_kernel", stream, gp_render_bwd_butterfly_kernel<<<gx * gy, GP_TILE_PIX, 0, stream>>>(
+        im.ranges, point_list, W, H, gx, bg, g.xy_depth, g.conic_opacity, g.rgb, colors_precomp, im.final_T,
+        im.n_contrib, dL_dpix, g.hdr, grec));
+  } else {
+    static bool attr_set[GP_STATIC_MAX_DEVICES_ATTR] = {};
+    int dev = 0;
+    GP_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= GP_STATIC_MAX_DEVICES_ATTR || !attr_set[dev]) {
+      GP_CUDA_TRY(cudaFuncSetAttribute(gp_render_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GP_BW_SMEM));
+      if (dev >= 0 && dev < GP_STATIC_MAX_DEVICES_ATTR) attr_set[dev] = true;
+    }
+    GP_KERNEL("gp_render_bwd_kernel", stream, gp_render_bwd_kernel<<<gx * gy, GP_TILE_PIX, GP_BW_SMEM, stream>>>(
+        im.ranges, point_list, W, H, gx, bg, g.xy_depth, g.conic_opacity, g.rgb, colors_precomp, im.final_T,
+        im.n_contrib, dL_dpix, g.hdr, grec));
+  }
   GP_LAUNCH_CHECK();
   const float* cov3D_ptr = cov3D_precomp ? cov3D_precomp : g.cov3D;
   // SH rows go through shared memory when they are the standard 16 coefficients and 16-byte aligned

@@ -37,22 +37,30 @@ class FlatGradAllReduce:
         groups.append([p for p in params if id(p) not in seen])
         self.params = [p for grp in groups for p in grp]
         self.group = group
-        n = sum(p.numel() for p in self.params)
-        p0 = self.params[0]
-        self.flat = torch.zeros(n, dtype=p0.dtype, device=p0.device)
-        self.views = []
-        off = 0
+        # Every view starts on a 16-byte boundary (ALIGN elements): the backward kernels write gradients straight into
+        # these views with 128-bit stores (pipeline.TrainStep, _sinks), and after densification the Gaussian count is
+        # rarely a multiple of 4.  The padding elements stay zero and travel with the exchange (< 16 B per parameter).
+        ALIGN = 4
+        pad = lambda k: (k + ALIGN - 1) // ALIGN * ALIGN
+        offs, off = [], 0
         for p in self.params:
-            self.views.append(self.flat[off:off + p.numel()].view_as(p))
-            off += p.numel()
+            offs.append(off)
+            off = pad(off + p.numel())
+        p0 = self.params[0]
+        self.flat = self._alloc_flat(max(off, ALIGN), p0.dtype, p0.device)
+        self.views = [self.flat[o:o + p.numel()].view_as(p) for o, p in zip(offs, self.params)]
         # per bucket: (first parameter index, one past the last, first element, one past the last); empty ones dropped
         self.bucket_ranges = []
-        i = e = 0
+        i = 0
         for grp in groups:
-            ne = sum(p.numel() for p in grp)
             if grp:
-                self.bucket_ranges.append((i, i + len(grp), e, e + ne))
-            i, e = i + len(grp), e + ne
+                e0 = offs[i]
+                e1 = offs[i + len(grp)] if i + len(grp) < len(offs) else self.flat.numel()
+                self.bucket_ranges.append((i, i + len(grp), e0, e1))
+            i += len(grp)
+
+    def _alloc_flat(self, n, dtype, device):
+        return torch.zeros(n, dtype=dtype, device=device)
 
     def buckets(self):
         """The flat buffer bucket by bucket, in the order their gradients complete."""
@@ -75,6 +83,11 @@ class FlatGradAllReduce:
     @property
     def nbytes(self):
         return self.flat.numel() * self.flat.element_size()
+
+    def all_reduce_bucket(self, bucket):
+        """Sum one bucket (a slice of ``flat``) over the ranks; returns a work handle or None.  Subclasses replace the
+        transport (``NvlsFlatGradAllReduce``: an in-stream kernel over NVSwitch multicast memory)."""
+        return dist.all_reduce(bucket, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
 
     def reduce(self, async_op=False):
         self.pack()

@@ -12,6 +12,7 @@ A graph is tied to (image size, tan-fov, SH degree, parameter shapes, capacity):
 import os
 
 import torch
+from torch.nn.utils.stateless import _reparametrize_module
 
 from . import _lib
 from ._sinks import grad_sinks
@@ -49,16 +50,24 @@ class TrainStep:
     """
 
     def __init__(self, pc, cam, capacity, bg=None, iteration=50_000, loss_fn=None, warmup=3, reducer=None,
-                 capture_collective=False):
+                 capture_collective=False, accumulate_into=None):
         """``reducer``: a ``parallel.FlatGradAllReduce`` over the same parameters.  The backward kernels then write
         the parameter gradients straight into its flat buffer (``_sinks``: no zero fill, no accumulation pass, no
         packing copies) and the step is captured as one CUDA graph per reducer bucket (up to three, see
         ``_stage_fns``): each graph ends where the gradients of its bucket are final, its all-reduce is issued right
         after the replay and runs over NVLink while the next graph computes.  ``capture_collective=True`` records ONE
         all-reduce into a single graph instead; EXPERIMENTAL -- with torch 2.11 / NCCL 2.28 on the B200 test box
-        that capture hung, so it is off by default and not used by bench.py."""
+        that capture hung, so it is off by default and not used by bench.py.
+
+        ``accumulate_into``: a second ``FlatGradAllReduce`` with the same layout.  Every stage graph then ends with
+        ``accumulate_into.bucket[k] += reducer.bucket[k]``: this step object serves samples 2.. of a gradient-
+        accumulation step (``BatchStep``), the running sum lives in the other buffer and is what gets exchanged."""
         self.pc = pc
         self.reducer = reducer
+        self.accumulate_into = accumulate_into
+        if accumulate_into is not None:
+            assert reducer is not None and accumulate_into.flat.shape == reducer.flat.shape and \
+                accumulate_into.bucket_ranges == reducer.bucket_ranges, "accumulate_into must mirror the reducer"
         self.capture_collective = bool(capture_collective and reducer is not None)
         self.params = [p for p in pc.parameters() if p.requires_grad]
         if reducer is not None:
@@ -139,8 +148,11 @@ class TrainStep:
             return r.params[lo:hi]
 
         def finish(k, last):
-            lo, hi, _, _ = r.bucket_ranges[k]
+            lo, hi, e0, _ = r.bucket_ranges[k]
             self.packed += r.pack(lo, len(r.params) if last else hi)
+            if self.accumulate_into is not None:      # running sum of the step's samples (captured with the stage)
+                e1 = r.flat.numel() if last else r.bucket_ranges[k][3]
+                self.accumulate_into.flat[e0:e1].add_(r.flat[e0:e1])
 
         def stage0():
             for p in self.params:
@@ -149,20 +161,18 @@ class TrainStep:
             if can_cut_mlp:
                 model.keep_kp_deltas = True
             with grad_sinks(zip(r.params, r.views)):      # looked up while the autograd graph is being built
-                self.pkg = render(self.cam, self.pc, None, self.bg, time=self.t, it=self.iteration,
-                                  capacity=self.capacity)
-                self.loss = self.loss_fn(self.pkg["render"], self.target)
+                self._render_aliased()
             if can_cut_mlp:
                 model.keep_kp_deltas = False
                 self._cut2, model._kp_deltas = model._kp_deltas, None
             deformed = [t for t in self.pkg["deformed"] if t.requires_grad]
             if nb == 1:
-                self.loss.backward()
-                self.viewspace_grad = self.pkg["viewspace_points"].grad
+                self._grads_into([self.loss], None, self.params, viewspace=True)
                 finish(0, True)
                 return
             early = leaves(0)
-            outs = torch.autograd.grad(self.loss, deformed + early + [self.pkg["viewspace_points"]], allow_unused=True)
+            outs = torch.autograd.grad(self.loss, deformed + self._aliases_of(early) + [self.pkg["viewspace_points"]],
+                                       allow_unused=True)
             self._cut1 = [(t, g) for t, g in zip(deformed, outs[:len(deformed)]) if g is not None]
             for p, g in zip(early, outs[len(deformed):len(deformed) + len(early)]):
                 p.grad = g
@@ -174,11 +184,12 @@ class TrainStep:
             cut = [t for t in (self._cut2 or ()) if t is not None and t.requires_grad] if can_cut_mlp else []
             if not cut:
                 if ts:
-                    torch.autograd.backward(ts, gs)
+                    done = {id(p) for p in leaves(0)}
+                    self._grads_into(ts, gs, [p for p in self.params if id(p) not in done])
                 finish(1, True)
                 return
             mine = leaves(1)
-            outs = torch.autograd.grad(ts, cut + mine, grad_outputs=gs, allow_unused=True)
+            outs = torch.autograd.grad(ts, cut + self._aliases_of(mine), grad_outputs=gs, allow_unused=True)
             self._cut2 = [(t, g) for t, g in zip(cut, outs[:len(cut)]) if g is not None]
             for p, g in zip(mine, outs[len(cut):]):
                 p.grad = g
@@ -186,7 +197,9 @@ class TrainStep:
 
         def stage2():
             if self._cut2:
-                torch.autograd.backward([t for t, _ in self._cut2], [g for _, g in self._cut2])
+                done = {id(p) for p in leaves(0) + leaves(1)}
+                self._grads_into([t for t, _ in self._cut2], [g for _, g in self._cut2],
+                                 [p for p in self.params if id(p) not in done])
             self._cut2 = None
             finish(2, True)
 
@@ -195,6 +208,32 @@ class TrainStep:
         if not can_cut_mlp:
             return [stage0, stage1]
         return [stage0, stage1, stage2]
+
+    def _render_aliased(self):
+        """``render()`` + loss on fresh leaf ALIASES of the parameters (same storage, new autograd identity).  A parameter's
+        AccumulateGrad node is bound to the stream it was first used on and stays alive as long as any earlier autograd
+        graph does (a loss the caller still holds, say); the engine would then route this backward through that stream
+        -- the legacy default stream, typically -- and break the capture.  Aliases made here belong to this stream."""
+        named = list(self.pc.named_parameters())
+        aliases = {n: p.detach().requires_grad_(p.requires_grad) for n, p in named}
+        self._alias = {id(p): aliases[n] for n, p in named}
+        with _reparametrize_module(self.pc, aliases):
+            self.pkg = render(self.cam, self.pc, None, self.bg, time=self.t, it=self.iteration, capacity=self.capacity)
+            self.loss = self.loss_fn(self.pkg["render"], self.target)
+
+    def _aliases_of(self, params):
+        return [self._alias[id(p)] for p in params]
+
+    def _grads_into(self, outputs, grad_outputs, params, viewspace=False):
+        """``p.grad = dL/dp`` through ``torch.autograd.grad`` rather than ``backward()``: no AccumulateGrad node runs, so a
+        stale autograd graph the caller still holds (whose AccumulateGrad nodes are bound to another stream) cannot
+        invalidate a capture, and a gradient written through a sink is adopted as is."""
+        wanted = self._aliases_of(params) + ([self.pkg["viewspace_points"]] if viewspace else [])
+        outs = torch.autograd.grad(outputs, wanted, grad_outputs=grad_outputs, allow_unused=True)
+        for p, g in zip(params, outs):
+            p.grad = g
+        if viewspace:
+            self.viewspace_grad = outs[-1]
 
     def _verify_staging(self):
         """The staged backward only asks autograd for the leaves of the bucket a stage closes.  A parameter that gets
@@ -233,9 +272,13 @@ class TrainStep:
                     p.grad = None
             for p, v in zip(self.reducer.params, self.reducer.views):
                 p.grad = v
-        self.pkg = render(self.cam, self.pc, None, self.bg, time=self.t, it=self.iteration, capacity=self.capacity)
-        self.loss = self.loss_fn(self.pkg["render"], self.target)
-        self.loss.backward()
+        if self.reducer is None:
+            self._render_aliased()
+            self._grads_into([self.loss], None, self.params, viewspace=True)
+        else:
+            self.pkg = render(self.cam, self.pc, None, self.bg, time=self.t, it=self.iteration, capacity=self.capacity)
+            self.loss = self.loss_fn(self.pkg["render"], self.target)
+            self.loss.backward()
         if self.capture_collective:
             import torch.distributed as dist
             dist.all_reduce(self.reducer.flat, op=dist.ReduceOp.SUM, group=self.reducer.group)
@@ -250,6 +293,7 @@ class TrainStep:
                                 target=torch.empty_like(self.target), ready=torch.cuda.Event(), free=torch.cuda.Event())
                            for _ in range(2)]
             self._slot = 0
+            self._pending = []
             for s in self._stage:
                 s["free"].record(torch.cuda.current_stream(self.dev))
         s = self._stage[self._slot]
@@ -266,35 +310,47 @@ class TrainStep:
             s["target"].copy_(target, non_blocking=True)
             s["ready"].record(self._copy_stream)
         s["used"] = True
-        self._pending = s
+        self._pending.append(s)                               # FIFO: at most two samples are in flight (two slots)
+        assert len(self._pending) <= 2, "prefetch() twice without a step_prefetched() in between is the limit"
         self._slot ^= 1
 
-    def step_prefetched(self):
-        s = self._pending
+    def step_prefetched(self, exchange=None):
+        s = self._pending.pop(0)
         cur = torch.cuda.current_stream(self.dev)
         cur.wait_event(s["ready"])
         self.cam.packed.copy_(s["small"])
         self.target.copy_(s["target"])
         s["free"].record(cur)
-        return self._replay()
+        return self._replay(exchange)
 
-    def __call__(self, cam, t, target, non_blocking=True):
+    def __call__(self, cam, t, target, non_blocking=True, exchange=None):
         self.cam.load(cam, non_blocking)
         self.t.copy_(t, non_blocking=non_blocking)
         self.target.copy_(target, non_blocking=non_blocking)
-        return self._replay()
+        return self._replay(exchange)
 
-    def _replay(self):
+    def _replay(self, exchange=None):
+        """``exchange``: None = this step's own reducer (when it has one and a process group of more than one rank
+        exists), False = no exchange (a sample in the middle of an accumulation step, or a single-rank run), or the
+        ``FlatGradAllReduce`` whose buckets are to be summed over the ranks (the accumulator of a ``BatchStep``)."""
         if self.two_stage:
             import torch.distributed as dist
-            buckets, works = self.reducer.buckets(), []
+            if exchange is None:
+                exchange = self.reducer if (dist.is_available() and dist.is_initialized() and
+                                            dist.get_world_size(self.reducer.group) > 1) else False
             last = len(self.stage_graphs) - 1
-            for k, g in enumerate(self.stage_graphs):
-                g.replay()                    # stage k+1 runs while bucket k is on the wire
-                for b in (buckets[k:] if k == last else buckets[k:k + 1]):
-                    works.append(dist.all_reduce(b, op=dist.ReduceOp.SUM, group=self.reducer.group, async_op=True))
-            for w in works:
-                w.wait()
+            if exchange is False:
+                for g in self.stage_graphs:
+                    g.replay()
+            else:
+                buckets, works = exchange.buckets(), []
+                for k, g in enumerate(self.stage_graphs):
+                    g.replay()                    # stage k+1 runs while bucket k is on the wire
+                    for b in (buckets[k:] if k == last else buckets[k:k + 1]):
+                        works.append(exchange.all_reduce_bucket(b))
+                for w in works:
+                    if w is not None:
+                        w.wait()
         else:
             self.graph.replay()
         for p, g in zip(self.params, self.grads):     # p.grad may have been replaced / cleared by the caller
@@ -337,3 +393,144 @@ class RenderStep:
         self.t.copy_(t, non_blocking=non_blocking)
         self.graph.replay()
         return self.pkg
+
+
+class BatchStep:
+    """One optimizer step of the reference's ``--batch`` loop (train.py:113-133) on this rank's share of the step's
+    (camera, time) samples: every sample is one replay of a captured train iteration, the parameter gradients are
+    summed over the samples (the reference sums the losses and calls backward once), ``radii`` are max-reduced and the
+    visibility mask or-reduced (train.py:122-123).  With more than one rank the sums are then taken over the ranks too
+    (``parallel``: SUM for gradients, MAX for radii), started bucket by bucket while the last sample's backward is still
+    running.
+
+    Two captured steps share the work: ``first`` writes its gradients straight into the accumulator (no zero fill, no
+    copy), ``rest`` writes into a scratch buffer of the same layout and ends each stage with ``accumulator += scratch``.
+    After ``step()`` ``p.grad`` of every exchanged parameter is its view of the (summed) accumulator.
+    """
+
+    def __init__(self, pc, cam, capacity, make_reducer, samples_per_rank, bg=None, iteration=50_000, loss_fn=None,
+                 group=None):
+        import torch.distributed as dist
+        self.pc = pc
+        self.n = int(samples_per_rank)
+        self.world = dist.get_world_size(group) if (dist.is_available() and dist.is_initialized()) else 1
+        self.group = group
+        self.acc = make_reducer()
+        self.first = TrainStep(pc, cam, capacity, bg=bg, iteration=iteration, loss_fn=loss_fn, reducer=self.acc)
+        self.rest = None
+        if self.n > 1:
+            self.scratch = make_reducer()
+            self.rest = TrainStep(pc, cam, capacity, bg=bg, iteration=iteration, loss_fn=loss_fn, reducer=self.scratch,
+                                  accumulate_into=self.acc)
+        dev = self.first.dev
+        self.dev = dev
+        self.loss_sum = torch.zeros((), device=dev)
+        P = int(pc.get_xyz.shape[0])
+        self.radii = torch.zeros(P, dtype=torch.int32, device=dev)      # max over the step's samples (and ranks)
+
+    def _steps(self):
+        return [self.first] + [self.rest] * (self.n - 1)
+
+    def _after_sample(self, j, ts):
+        if j == 0:
+            self.loss_sum.copy_(ts.loss.detach())
+            self.radii.copy_(ts.pkg["radii"])
+        else:
+            self.loss_sum.add_(ts.loss.detach())
+            torch.maximum(self.radii, ts.pkg["radii"], out=self.radii)
+
+    def _finish(self):
+        if self.world > 1 and self.exchange:
+            import torch.distributed as dist
+            dist.all_reduce(self.radii, op=dist.ReduceOp.MAX, group=self.group)
+        for p, v in zip(self.acc.params, self.acc.views):
+            p.grad = v
+        return self.loss_sum
+
+    def _exchange(self, j):
+        return self.acc if (self.world > 1 and self.exchange and j == self.n - 1) else False
+
+    exchange = True     # False: leave the per-rank sums un-exchanged (diagnostics: bench.py's exchange check)
+
+    def step(self, samples):
+        """``samples``: this rank's ``samples_per_rank`` tuples (camera, time [1], target [3,H,W]) of device tensors."""
+        assert len(samples) == self.n
+        for j, (ts, (cam, t, target)) in enumerate(zip(self._steps(), samples)):
+            ts(cam, t, target, exchange=self._exchange(j))
+            self._after_sample(j, ts)
+        return self._finish()
+
+    def step_host(self, samples, next_first=None):
+        """Same, the samples being PINNED HOST tensors: the copy of sample j + 1 is issued on a side stream before
+        sample j is replayed (``TrainStep.prefetch``); ``next_first`` is the first sample of the NEXT step, whose copy
+        then overlaps this step's last sample."""
+        assert len(samples) == self.n
+        steps = self._steps()
+        if not getattr(self, "_primed", False):
+            steps[0].prefetch(*samples[0])
+        for j, ts in enumerate(steps):
+            if j + 1 < self.n:
+                steps[j + 1].prefetch(*samples[j + 1])
+            elif next_first is not None:
+                steps[0].prefetch(*next_first)
+            ts.step_prefetched(exchange=self._exchange(j))
+            self._after_sample(j, ts)
+        self._primed = next_first is not None
+        return self._finish()
+
+    def overflowed(self):
+        a = self.first.overflowed()
+        b = self.rest.overflowed() if self.rest is not None else (0, False)
+        return max(a[0], b[0]), (a[1] or b[1])
+
+
+class MotionStep:
+    """One frame of the motion-extrapolation loop (eval.py:120-157, ``render_kpts``) as one graph: the per-frame blend
+    ``xyz + W_x (kpts_i - kpts)``, ``normalize(quat_mul(normalize(W_r rot_i), rotation))`` (eval.py:140-141, sparse: the
+    neighbour indices and blend logits of one earlier ``pc(time, iteration)`` call are reused, as the reference reuses
+    its dense weights) followed by ``render_motion`` (gaussian_renderer/__init__.py:117-191)."""
+
+    def __init__(self, pc, cam, capacity, bg=None, warmup=3, opacity=None):
+        from .renderer import render_motion
+        self.pc, self._render_motion = pc, render_motion
+        self.model = getattr(pc, "deformation", pc)
+        assert self.model._idx32 is not None, "call pc(time, iteration) once first (eval.py:125-126)"
+        dev = next(pc.parameters()).device
+        self.dev, self.capacity = dev, int(capacity)
+        self.bg = torch.zeros(3, device=dev) if bg is None else bg
+        self.opacity = opacity                      # ``lifecycle_opacity`` of that call, or None (eval.py:127)
+        self.cam = _StaticCamera(cam, dev)
+        self.cam.load(cam, non_blocking=False)
+        Kp = int(self.model.super_gaussians.shape[0])
+        self.kpts = torch.zeros(Kp, 3, device=dev)
+        self.kpts_rotation = torch.zeros(Kp, 4, device=dev)
+        self.kpts_rotation[:, 0] = 1.0
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side), torch.no_grad():
+            for _ in range(max(warmup, 1)):
+                self._body()
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.no_grad(), torch.cuda.graph(self.graph):
+            self._body()
+        from . import rasterizer as _r
+        self._state = _r.LAST_STATE
+        torch.cuda.synchronize(dev)
+
+    def _body(self):
+        xyz_t, q_t = self.model.extrapolate(self.kpts, self.kpts_rotation)
+        self.pkg = self._render_motion(self.cam, self.pc, None, self.bg, xyz_t=xyz_t, r_t=q_t, opacity=self.opacity,
+                                       capacity=self.capacity)
+
+    def __call__(self, cam, kpts_i, kpts_rotation_i, non_blocking=True):
+        self.cam.load(cam, non_blocking)
+        self.kpts.copy_(kpts_i, non_blocking=non_blocking)
+        self.kpts_rotation.copy_(kpts_rotation_i, non_blocking=non_blocking)
+        self.graph.replay()
+        return self.pkg
+
+    def overflowed(self):
+        hdr = self._state.geom[:16].view(torch.int32).cpu()
+        return int(hdr[_lib.HDR_NUM_RENDERED]), bool(int(hdr[_lib.HDR_OVERFLOW]))

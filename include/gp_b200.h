@@ -39,6 +39,12 @@ long long gp_launch_count(void);
 int gp_profile_enable(int on);
 int gp_profile_report(char* buf, size_t buf_bytes);
 
+/* FP32 FMA-pipe micro-benchmark (no reference counterpart): launches a kernel of dependent FFMA chains (8 per thread,
+ * 8 blocks of 256 threads per SM, `iters` x 64 FFMA per thread) on `stream` and returns the floating-point operations
+ * it performs in *flops; the caller times it with events.  bench.py uses it as the measured peak of the FP32-bound
+ * kernels' roofline. */
+int gp_fma_peak(int iters, float* out, double* flops, gp_stream_t stream);
+
 /* ------------------------------------------------------------------------------------------------
  * Rasterizer.  Stands in for diff_gaussian_rasterization._C.rasterize_gaussians /
  * rasterize_gaussians_backward / mark_visible

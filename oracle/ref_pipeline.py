@@ -99,6 +99,17 @@ class RefKeypointModel(nn.Module):
         q = normalize(do.quat_mul(normalize(delta_q), self._rotation))                             # :286
         return xyz, q, torch.exp(self._scaling), torch.sigmoid(self._opacity)                      # :287, :304
 
+    @torch.no_grad()
+    def dense_weights(self, t, iteration):
+        """``_, _, _, _, weights_xyz, weights_r = gaussians(time_, iteration, return_weights=True)`` (eval.py:125-126):
+        the dense [N,Kp] matrices the extrapolation loop reuses for every frame."""
+        self.get_nearest_mask()
+        fill = self.weights_fill[..., :self.super_gaussians.shape[0]]
+        K = self.args.nearest_num
+        wx = torch.scatter(fill, -1, self.nearest_mask, nn.Softmax(dim=-1)(self.logits[..., 0:K]))
+        wr = torch.scatter(fill, -1, self.nearest_mask, nn.Softmax(dim=-1)(self.logits[..., K:2 * K]))
+        return wx, wr
+
     @property
     def get_features(self):                                           # :155-158
         return torch.cat((self._features_dc, self._features_rest), dim=1)
@@ -117,3 +128,17 @@ def ref_render(cam, pc, bg, time, it):
                                                     bg, pc.active_sh_degree)                       # :98-106
     return {"render": color, "viewspace_points": screenspace_points, "visibility_filter": radii > 0, "radii": radii,
             "depth": depth, "tidx": tidx}
+
+
+@torch.no_grad()
+def ref_render_motion(cam, pc, bg, weights_xyz, weights_r, kpts_i, kpts_rotation_i):
+    """One frame of ``render_kpts`` (eval.py:137-153): the two dense matmuls + quaternion compose (:140-141), then
+    ``render_motion`` (gaussian_renderer/__init__.py:117-191: canonical scales / opacity, the reference rasterizer)."""
+    normalize = torch.nn.functional.normalize
+    xyz_final = pc._xyz + (weights_xyz @ (kpts_i - pc.super_gaussians))                             # eval.py:140
+    delta_r = normalize(do.quat_mul(normalize(weights_r @ kpts_rotation_i), pc._rotation))         # eval.py:141
+    fwd = ref_cuda.rasterize(xyz_final, torch.sigmoid(pc._opacity), bg, cam.world_view_transform, cam.full_proj_transform,
+                             cam.camera_center, cam.image_width, cam.image_height, cam.tanfovx, cam.tanfovy,
+                             shs=pc.get_features, scales=torch.exp(pc._scaling), rotations=delta_r,
+                             sh_degree=pc.active_sh_degree)
+    return {"render": fwd["color"], "radii": fwd["radii"]}

@@ -363,7 +363,8 @@ def test_model_fused_mlp_equals_torch_mlp(gplib):
         assert rel_err(grads[0][n], grads[1][n]) <= 1e-3, n
 
 
-def test_two_stage_step_with_grad_sinks_matches_eager(gplib):
+@pytest.mark.parametrize("N", [6000, 6001])      # 6001: not a multiple of 4 (the reducer pads every view to 16 bytes)
+def test_two_stage_step_with_grad_sinks_matches_eager(gplib, N):
     """pipeline.TrainStep with a reducer: two graphs with the gradient exchange issued between them, gradients written
     by the kernels straight into the reducer's flat buffer.  One-rank NCCL group: the sums are the local gradients."""
     import torch.distributed as dist
@@ -376,7 +377,7 @@ def test_two_stage_step_with_grad_sinks_matches_eager(gplib):
     if own_group:
         dist.init_process_group("nccl", init_method="tcp://127.0.0.1:%d" % (32500 + os.getpid() % 2000), rank=0, world_size=1)
     try:
-        N, Kp, W, H = 6000, 96, 128, 96
+        Kp, W, H = 96, 128, 96
         gs, kp, kf, logits = scene(N, Kp, seed=51)
         args = default_args(feature_amplify=0.5, norm_rotation=True)
         torch.manual_seed(0)
@@ -415,6 +416,60 @@ def test_two_stage_step_with_grad_sinks_matches_eager(gplib):
     finally:
         if own_group:
             dist.destroy_process_group()
+
+
+def test_batch_step_accumulates_samples(gplib):
+    """pipeline.BatchStep (the reference's --batch loop, train.py:113-133): after a step over three samples ``p.grad`` is
+    the SUM of the three per-sample gradients, the loss the sum of the losses, ``radii`` the element-wise maximum --
+    from device tensors and from pinned host tensors (prefetch path)."""
+    from gaussianprediction_b200 import synthetic as syn
+    from gaussianprediction_b200.deform import KeypointDeformation, default_args
+    from gaussianprediction_b200.parallel import FlatGradAllReduce
+    from gaussianprediction_b200.pipeline import BatchStep
+    from gaussianprediction_b200.renderer import SceneModel, render
+    N, Kp, W, H = 6001, 96, 128, 96
+    gs, kp, kf, logits = scene(N, Kp, seed=52)
+    args = default_args(feature_amplify=0.5, norm_rotation=True)
+    torch.manual_seed(0)
+    model = KeypointDeformation(args, gs.xyz, gs.rotation, gs.scaling, gs.opacity, gs.motion_feature, kp, kf, logits=logits)
+    pc = SceneModel(model, gs.features_dc, gs.features_rest).cuda()
+    cams = syn.camera_ring(3, W, H, seed=6)
+    host = []
+    g = torch.Generator().manual_seed(2)
+    for i, c in enumerate(cams):
+        hc = type(c)(**vars(c))
+        for k in ("world_view_transform", "full_proj_transform", "camera_center"):
+            setattr(hc, k, getattr(c, k).pin_memory())
+            setattr(c, k, getattr(c, k).cuda())
+        host.append((hc, torch.tensor([0.2 + 0.3 * i]).pin_memory(), (torch.randn(3, H, W, generator=g) * 1e-2).pin_memory()))
+    dev_samples = [(c, h[1].cuda(), h[2].cuda()) for c, h in zip(cams, host)]
+    bg = torch.zeros(3, device="cuda")
+    with_grad = [p for n, p in pc.named_parameters() if not n.endswith("motion_feature")]
+    # eager truth: autograd accumulation over the three samples
+    want_loss, want_radii = 0.0, None
+    for cam, t, tgt in dev_samples:
+        pkg = render(cam, pc, None, bg, time=t, it=50_000)
+        loss = (pkg["render"] * tgt).sum()
+        loss.backward()
+        want_loss += float(loss)
+        want_radii = pkg["radii"] if want_radii is None else torch.maximum(want_radii, pkg["radii"])
+    want = {n: p.grad.clone() for n, p in pc.named_parameters() if p.grad is not None}
+    for p in pc.parameters():
+        p.grad = None
+    del pkg, loss
+    batch = BatchStep(pc, cams[0], 400_000, lambda: FlatGradAllReduce(with_grad), 3, bg=bg)
+    for mode in ("device", "host", "host"):
+        if mode == "device":
+            loss = batch.step(dev_samples)
+        else:
+            loss = batch.step_host(host, next_first=host[0])
+        torch.cuda.synchronize()
+        assert not batch.overflowed()[1]
+        assert abs(float(loss) - want_loss) <= 1e-5 * max(1.0, abs(want_loss)), mode
+        assert torch.equal(batch.radii, want_radii), mode
+        for n, p in pc.named_parameters():
+            if n in want:
+                assert rel_err(p.grad, want[n]) <= 1e-3, (mode, n, rel_err(p.grad, want[n]))
 
 
 def test_full_size_deformation_properties_1m(gplib):

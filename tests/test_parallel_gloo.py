@@ -53,7 +53,7 @@ def test_sample_sharding_and_flat_allreduce_gloo(tmp_path):
     w0 = sum(s + 1 for s in range(8))
     w1 = sum(s + 2 for s in range(8))
     assert torch.allclose(r["g0"], 2 * w0 * p0) and torch.allclose(r["g1"], torch.full((7,), float(w1)))
-    assert float(r["g2"].abs().sum()) == 0 and r["mine"] == [0, 2, 4, 6] and r["same_storage"] and r["nbytes"] == 26 * 4
+    assert float(r["g2"].abs().sum()) == 0 and r["mine"] == [0, 2, 4, 6] and r["same_storage"] and r["nbytes"] == 28 * 4   # 15 -> 16, 7 -> 8, 4: views are 16-byte aligned
     assert r["radii"].tolist() == [2, 5, 0] and r["vis"].tolist() == [True, True, False]
 
 
@@ -94,6 +94,26 @@ def test_bucketed_exchange_and_grad_sinks_gloo(tmp_path):
     port = 31500 + (os.getpid() % 2000)
     mp.spawn(_bucket_worker, args=(2, port, out), nprocs=2, join=True)
     r = torch.load(out)
-    assert r["layout"] == (True, 1, 10, 18) and r["hit"] and r["moved"] == (0, 2) and r["in_flat"]
+    assert r["layout"] == (True, 1, 12, 20)        # 10 -> 12 | 12 + 6 -> 20: every view starts 16-byte aligned
+    assert r["hit"] and r["hit"] and r["moved"] == (0, 2) and r["in_flat"]
     assert torch.equal(r["c"], torch.full((2, 5), 3.0)) and torch.equal(r["a"], torch.full((4, 3), 30.0))
     assert float(r["b"].abs().sum()) == 0
+
+
+def test_flat_views_are_16_byte_aligned_for_any_gaussian_count():
+    """The backward kernels store 128-bit vectors straight into the reducer's views (pipeline.TrainStep); after
+    densification the Gaussian count is rarely a multiple of 4 (N = 6001 made `_rotation` start mid-vector)."""
+    from gaussianprediction_b200.parallel import FlatGradAllReduce
+    N = 6001
+    ps = [torch.nn.Parameter(torch.zeros(*shape)) for shape in ((N, 1, 3), (N, 15, 3), (N, 3), (N, 4), (N, 3), (N, 1),
+                                                                (N, 12), (37, 3), (37, 32), (7,), (7, 256))]
+    red = FlatGradAllReduce(ps, first=ps[:2], second=ps[2:7])
+    base = red.flat.data_ptr()
+    assert all((v.data_ptr() - base) % 16 == 0 for v in red.views)
+    assert all(v.shape == p.shape for v, p in zip(red.views, red.params))
+    r = red.bucket_ranges
+    assert r[0][2] == 0 and r[-1][3] == red.flat.numel() and all(a[3] == b[2] for a, b in zip(r, r[1:]))
+    assert all(e0 % 4 == 0 for _, _, e0, _ in r)
+    # views do not overlap
+    ends = sorted(((v.data_ptr() - base) // 4, (v.data_ptr() - base) // 4 + v.numel()) for v in red.views)
+    assert all(a[1] <= b[0] for a, b in zip(ends, ends[1:]))

@@ -350,5 +350,13 @@ def test_patch_culling_adversarial_vs_reference(gplib):
         assert count_diff(mine[k], ref["fwd"][k]) == 0, k
     assert count_diff(mine["state"]["n_contrib"], ref["state"]["n_contrib"]) == 0
     assert count_diff(mine["state"]["final_T"], ref["state"]["final_T"]) == 0
+    # The needles make the scale / rotation gradients ill-conditioned: the reference's own result moves from run to run
+    # with the order of its atomicAdds.  Bar = north_star's 1e-3, or three times the reference's own run-to-run
+    # deviation where that is larger.
+    ref2 = run_ref(case, seeded_grad(case))
     for k in ("means2D", "opacity", "means3D", "sh", "scales", "rotations"):
-        assert rel_err(mine["grads"][k], ref["grads"][k]) <= GRAD_TOL, (k, rel_err(mine["grads"][k], ref["grads"][k]))
+        noise = rel_err(ref2["grads"][k], ref["grads"][k])
+        e = rel_err(mine["grads"][k], ref["grads"][k])
+        print(k, "ours vs ref %.3g, ref vs ref %.3g" % (e, noise))
+        assert e <= max(GRAD_TOL, 3 * noise), (k, e, noise)
+

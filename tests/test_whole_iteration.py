@@ -74,9 +74,9 @@ def test_whole_iteration_vs_reference_arm(gplib, workload):
     stats = bench.workload_stats(ours)
     ours.capacity = int(stats["max_R"] * 1.25) + 65536
     ours.enable_graph()
-    loss = ours.train_step(cam, t, G)
+    loss = ours.batch.step([(cam, t, G)])
     torch.cuda.synchronize()
-    assert not ours.train_step.overflowed()[1]
+    assert not ours.batch.overflowed()[1]
     assert abs(float(loss) - float((pr["render"] * G).sum())) <= 1e-3 * max(1.0, abs(float(loss)))
     for n, a, b in pairs:
         assert rel_err(a.grad, b.grad) <= 1e-3, ("graph", n, rel_err(a.grad, b.grad))
