@@ -256,7 +256,38 @@ gp_render_bwd_butterfly_kernel(const uint2* __restrict__ ranges, const uint32_t*
 // ------------------------------------------------------------------------------------------------
 #define GP_BW_SLOTS 16
 #define GP_BW_STRIDE 33
-#define GP_BW_SMEM (GP_TILE_PIX * (4 * 16 + 2 * 4) + 8 * 2 * GP_BW_SLOTS * GP_BW_STRIDE * 4)
+// dynamic shared memory, byte offsets (explicit shared-space addressing: a generic pointer into dynamic shared memory
+// costs S2R CgaCtaId + LEA at every access, ~8 % of the round-1 kernel's instructions)
+#define GP_BW_CO 0
+#define GP_BW_XYD (GP_TILE_PIX * 16)
+#define GP_BW_RGB (2 * GP_TILE_PIX * 16)
+#define GP_BW_DPX (3 * GP_TILE_PIX * 16)
+#define GP_BW_ID (4 * GP_TILE_PIX * 16)
+#define GP_BW_MASK (GP_BW_ID + GP_TILE_PIX * 4)
+#define GP_BW_W (GP_BW_MASK + GP_TILE_PIX * 4)
+#define GP_BW_WARP_BYTES (2 * GP_BW_SLOTS * GP_BW_STRIDE * 4)
+#define GP_BW_SMEM (GP_BW_W + 8 * GP_BW_WARP_BYTES)
+
+__device__ __forceinline__ float4 gp_lds128(uint32_t a) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ float gp_lds32(uint32_t a) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ uint32_t gp_lds32u(uint32_t a) {
+  uint32_t v;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ void gp_sts32(uint32_t a, float v) { asm volatile("st.shared.f32 [%0], %1;" ::"r"(a), "f"(v) : "memory"); }
+__device__ __forceinline__ void gp_sts32u(uint32_t a, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
+__device__ __forceinline__ void gp_sts128(uint32_t a, float4 v) {
+  asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(a), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
 
 __global__ void __launch_bounds__(GP_TILE_PIX, 4)
 gp_render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H,
@@ -266,13 +297,8 @@ gp_render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
                      const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpixels,
                      const int* __restrict__ hdr, float* __restrict__ grec) {
   extern __shared__ __align__(16) unsigned char s_raw[];
-  float4* s_co = (float4*)s_raw;
-  float4* s_xyd = s_co + GP_TILE_PIX;
-  float4* s_rgb = s_xyd + GP_TILE_PIX;
-  float4* s_dpx = s_rgb + GP_TILE_PIX;
-  int* s_id = (int*)(s_dpx + GP_TILE_PIX);
-  unsigned* s_mask = (unsigned*)(s_id + GP_TILE_PIX);
-  float* s_w = (float*)(s_mask + GP_TILE_PIX);
+  uint32_t sb = (uint32_t)__cvta_generic_to_shared(s_raw);
+  asm volatile("" : "+r"(sb));   // opaque: kept in a register instead of being rebuilt (S2R CgaCtaId + LEA) at every use
 
   if (hdr[GP_HDR_OVERFLOW]) return;
   const int t = threadIdx.x, w = t >> 5, lane = t & 31;
@@ -300,7 +326,7 @@ gp_render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
     dpx1 = dL_dpixels[hw + pix_id];
     dpx2 = dL_dpixels[2 * hw + pix_id];
   }
-  s_dpx[t] = make_float4(dpx0, dpx1, dpx2, 0.f);   // read back by this warp only (phase 2)
+  gp_sts128(sb + GP_BW_DPX + t * 16, make_float4(dpx0, dpx1, dpx2, 0.f));   // read back by this warp only (phase 2)
   float S = T_final * (bg_color[0] * dpx0 + bg_color[1] * dpx1 + bg_color[2] * dpx2);
 
   unsigned warp_last = last_contributor;
@@ -309,25 +335,24 @@ gp_render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
 
   // phase-2 identity of this lane
   const int slot = lane & (GP_BW_SLOTS - 1), half = lane >> 4;
-  float* const bufW = s_w + (size_t)w * (2 * GP_BW_SLOTS * GP_BW_STRIDE);
-  float* const bufU = bufW + GP_BW_SLOTS * GP_BW_STRIDE;
-  const float* const rowW = bufW + slot * GP_BW_STRIDE + half * 16;
-  const float* const rowU = bufU + slot * GP_BW_STRIDE + half * 16;
-  const float4* const rowD = s_dpx + w * 32 + half * 16;
+  const uint32_t bufW = sb + GP_BW_W + w * GP_BW_WARP_BYTES;                       // [slot][33] Wg, then [slot][33] U
+  const uint32_t rowW = bufW + (slot * GP_BW_STRIDE + half * 16) * 4;
+  const uint32_t rowD = sb + GP_BW_DPX + (w * 32 + half * 16) * 16;
   const float fx0 = (float)px0, fy0 = (float)(py0 + 2 * half);
   const float half_w = 0.5f * W, half_h = 0.5f * H;
-  int nslots = 0;   // warp-uniform
-  int myj = 0;      // batch index of the Gaussian in this lane's slot
+  int nslots = 0;                    // warp-uniform
+  uint32_t wr = bufW + lane * 4;     // where this lane's (Wg, U) of the next visit go
+  int myj = 0;                       // batch index of the Gaussian in this lane's slot
 
   auto splat_pass = [&]() {
     __syncwarp();
-    const float4 xyd = s_xyd[myj];
+    const float4 xyd = gp_lds128(sb + GP_BW_XYD + myj * 16);
     const float bx = xyd.x - fx0, by = xyd.y - fy0;
     float m0 = 0.f, mx = 0.f, my = 0.f, mxx = 0.f, mxy = 0.f, myy = 0.f, c0 = 0.f, c1 = 0.f, c2 = 0.f;
 #pragma unroll
     for (int i = 0; i < 16; i++) {
-      const float Wg = rowW[i], U = rowU[i];
-      const float4 d = rowD[i];
+      const float Wg = gp_lds32(rowW + i * 4), U = gp_lds32(rowW + GP_BW_SLOTS * GP_BW_STRIDE * 4 + i * 4);
+      const float4 d = gp_lds128(rowD + i * 16);
       const float dx = bx - (float)(i & 7), dy = by - (float)(i >> 3);
       const float wx = Wg * dx, wy = Wg * dy;
       m0 += Wg;
@@ -350,8 +375,8 @@ gp_render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
     c1 += __shfl_xor_sync(0xffffffffu, c1, 16);
     c2 += __shfl_xor_sync(0xffffffffu, c2, 16);
     if (half == 0 && slot < nslots) {
-      const float4 co = s_co[myj];
-      float* dst = grec + (size_t)s_id[myj] * GP_GREC;
+      const float4 co = gp_lds128(sb + GP_BW_CO + myj * 16);
+      float* dst = grec + (size_t)gp_lds32u(sb + GP_BW_ID + myj * 4) * GP_GREC;
       const float no = -co.w;
       red_add_v4(dst, no * (co.x * mx + co.y * my) * half_w, no * (co.z * my + co.y * mx) * half_h, 0.5f * no * mxx,
                  0.5f * no * mxy);
@@ -359,6 +384,8 @@ gp_render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
       atomicAdd(dst + 8, c2);
     }
     __syncwarp();
+    nslots = 0;
+    wr = bufW + lane * 4;
   };
 
   const float tile_fx0 = (float)(tile_x * GP_TILE_X), tile_fy0 = (float)(tile_y * GP_TILE_Y);
@@ -368,36 +395,40 @@ gp_render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
     unsigned pmask = 0u;
     if (range.x + progress < range.y) {
       const int id = point_list[range.y - progress - 1];
-      s_id[t] = id;
+      gp_sts32u(sb + GP_BW_ID + t * 4, (uint32_t)id);
       const float4 co = __ldg(conic_opacity + id);
       const float4 xyd = __ldg(xy_depth + id);
-      s_co[t] = co;
-      s_xyd[t] = xyd;
+      gp_sts128(sb + GP_BW_CO + t * 16, co);
+      gp_sts128(sb + GP_BW_XYD + t * 16, xyd);
+      float4 col;
       if (colors_precomp != nullptr)
-        s_rgb[t] = make_float4(colors_precomp[3 * (size_t)id], colors_precomp[3 * (size_t)id + 1],
-                               colors_precomp[3 * (size_t)id + 2], 0.f);
+        col = make_float4(colors_precomp[3 * (size_t)id], colors_precomp[3 * (size_t)id + 1],
+                          colors_precomp[3 * (size_t)id + 2], 0.f);
       else
-        s_rgb[t] = __ldg(rgb4 + id);
+        col = __ldg(rgb4 + id);
+      gp_sts128(sb + GP_BW_RGB + t * 16, col);
       pmask = gp_patch_mask(co, xyd.x, xyd.y, tile_fx0, tile_fy0);
     }
-    s_mask[t] = pmask;
+    gp_sts32u(sb + GP_BW_MASK + t * 4, pmask);
     __syncthreads();
 
     const int nb = min(GP_TILE_PIX, toDo);
+    // list position (0-based, front to back) of batch element j is base - j
+    const int base = total - 1 - i * GP_TILE_PIX;
     // elements of this batch in front of index (total - warp_last) lie behind the last contributor of every pixel
     // of this warp: start at the first 32-chunk that can matter
     const int first = total - (int)warp_last - i * GP_TILE_PIX;
     for (int c0 = max(first, 0) & ~31; c0 < nb; c0 += 32) {
-      unsigned bits = __ballot_sync(0xffffffffu, (s_mask[c0 + lane] >> w) & 1u);
+      unsigned bits = __ballot_sync(0xffffffffu, (gp_lds32u(sb + GP_BW_MASK + (c0 + lane) * 4) >> w) & 1u);
       while (bits) {
         const int j = c0 + __ffs(bits) - 1;
         bits &= bits - 1;
-        // 0-based position of this Gaussian in the tile's front-to-back list
-        const uint32_t contributor = (uint32_t)(total - 1 - (i * GP_TILE_PIX + j));
+        const uint32_t contributor = (uint32_t)(base - j);
         if (contributor >= warp_last) continue;  // warp-uniform: nobody in this warp reaches it
         bool active = inside && contributor < last_contributor;
-        const float4 xyd = s_xyd[j];
-        const float4 co = s_co[j];
+        const uint32_t aj = sb + j * 16;
+        const float4 xyd = gp_lds128(aj + GP_BW_XYD);
+        const float4 co = gp_lds128(aj + GP_BW_CO);
         const float dx = xyd.x - pixfx;
         const float dy = xyd.y - pixfy;
         const float qa = __fmul_rn(co.x, dx);
@@ -406,36 +437,35 @@ gp_render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
         const float qc = __fmul_rn(__fmul_rn(co.y, dx), dy);
         const float power = __fmaf_rn(qs, -0.5f, -qc);
         active = active && !(power > 0.0f);
-        const float G = expf(power);
+        // exp() through ex2.approx (2 ulp, 6 instructions fewer than expf): the gradients' bar is 1e-3 relative; a
+        // pair within 3e-7 relative of the alpha >= 1/255 threshold may be classified differently from the forward
+        // pass, which changes that pixel's chain by <= 0.4 % -- far below the bar (tests/test_raster_parity.py).
+        float G;
+        asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(G) : "f"(power * 1.4426950408889634f));
         const float alpha = fminf(0.99f, __fmul_rn(co.w, G));
         active = active && !(alpha < 1.0f / 255.0f);
         if (!__any_sync(0xffffffffu, active)) continue;
 
-        float Wg = 0.f, U = 0.f;
-        if (active) {
-          // one correctly rounded reciprocal serves both divisions by (1 - alpha) (reference backward.cu:503,533)
-          const float inv1ma = __frcp_rn(1.f - alpha);
-          T = T * inv1ma;
-          const float4 col = s_rgb[j];
-          const float cd = col.x * dpx0 + col.y * dpx1 + col.z * dpx2;
-          const float dL_dalpha = T * cd - S * inv1ma;
-          U = alpha * T;
-          S = fmaf(cd, U, S);
-          Wg = G * dL_dalpha;
-        }
-        bufW[nslots * GP_BW_STRIDE + lane] = Wg;
-        bufU[nslots * GP_BW_STRIDE + lane] = U;
+        // Branch-free: every lane computes, inactive lanes keep their state and store zeros.  One reciprocal serves
+        // both divisions by (1 - alpha) (reference backward.cu:503,533); 1 - alpha >= 0.01, so the approximate
+        // reciprocal (2 ulp) needs no special cases.
+        float inv1ma;
+        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv1ma) : "f"(1.f - alpha));
+        const float Tn = T * inv1ma;
+        const float4 col = gp_lds128(aj + GP_BW_RGB);
+        const float cd = col.x * dpx0 + col.y * dpx1 + col.z * dpx2;
+        const float dL_dalpha = Tn * cd - S * inv1ma;
+        const float Un = alpha * Tn;
+        T = active ? Tn : T;
+        S = active ? fmaf(cd, Un, S) : S;
+        gp_sts32(wr, active ? G * dL_dalpha : 0.f);
+        gp_sts32(wr + GP_BW_SLOTS * GP_BW_STRIDE * 4, active ? Un : 0.f);
+        wr += GP_BW_STRIDE * 4;
         if (slot == nslots) myj = j;
-        if (++nslots == GP_BW_SLOTS) {
-          splat_pass();
-          nslots = 0;
-        }
+        if (++nslots == GP_BW_SLOTS) splat_pass();
       }
     }
-    if (nslots) {   // the batch in shared memory is about to be replaced
-      splat_pass();
-      nslots = 0;
-    }
+    if (nslots) splat_pass();   // the batch in shared memory is about to be replaced
   }
 }
 
