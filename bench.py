@@ -218,18 +218,25 @@ class OurRunner:
         if self.world == 1:
             return parallel.FlatGradAllReduce(live)                 # one bucket -> the step stays one graph
         cls = parallel.FlatGradAllReduce
-        if self.exchange in ("auto", "nvls") and hasattr(parallel, "NvlsFlatGradAllReduce"):
-            try:
-                ok = parallel.NvlsFlatGradAllReduce.supported()
-            except Exception:
-                ok = False
-            if ok:
+        first_call = not getattr(self, "_have_acc", False)       # the accumulator is exchanged, the scratch buffer is not
+        self._have_acc = True
+        if first_call and self.exchange in ("auto", "nvls"):
+            if getattr(self, "_nvls_ok", None) is None:
+                try:
+                    self._nvls_ok = parallel.NvlsFlatGradAllReduce.supported()
+                except Exception:
+                    self._nvls_ok = False
+            if self._nvls_ok:
                 cls = parallel.NvlsFlatGradAllReduce
             elif self.exchange == "nvls":
-                raise SystemExit("--exchange nvls: NVSwitch multicast memory is not available here")
-        self.exchange_kind = cls.__name__
-        return cls(live, first=[self.pc._features_dc, self.pc._features_rest],
-                   second=[d._xyz, d._rotation, d._scaling, d._opacity] + list(d.weights_model.parameters()))
+                raise SystemExit("--exchange nvls: no symmetric memory between the ranks here")
+        red = cls(live, first=[self.pc._features_dc, self.pc._features_rest],
+                  second=[d._xyz, d._rotation, d._scaling, d._opacity] + list(d.weights_model.parameters()))
+        if first_call:
+            self.exchange_kind = ("gp_allreduce_sum_kernel over symmetric memory (" +
+                                  ("NVSwitch multicast, multimem.ld_reduce" if red.multicast else "peer loads/stores") + ")") \
+                if cls is not parallel.FlatGradAllReduce else "NCCL all_reduce per bucket"
+        return red
 
     def enable_graph(self):
         """Capture the iteration (gaussianprediction_b200.pipeline.BatchStep: one or two captured TrainSteps)."""
@@ -353,6 +360,8 @@ def timed_steps(runner, steps, warmup, world, host_inputs, flush, graph=False):
         flush.add_(1.0)                      # evict L2 (126 MB) between timed steps
         evs[i][0].record()
         loss = step(warmup + i, host_inputs)
+        if i == steps - 1 and graph and getattr(runner, "batch", None) is not None:
+            runner.batch.flush()             # pipelined exchange: the last step's SH bucket is joined inside its bracket
         if host_inputs:
             loss.item()                      # D2H read of the step's result inside the timed region
         evs[i][1].record()
@@ -600,6 +609,7 @@ def exchange_check(runner, s):
     of the per-rank sums, formed independently (all_gather of the un-exchanged buffers, added in rank order)."""
     import torch.distributed as dist
     b = runner.batch
+    b.flush()
     b.exchange = False
     b.step([runner.sample(g) for g in runner._ids(s)])
     torch.cuda.synchronize()
@@ -616,6 +626,7 @@ def exchange_check(runner, s):
     rwant = torch.stack(rparts).max(0)[0]
     del parts
     b.step([runner.sample(g) for g in runner._ids(s)])
+    b.flush()
     torch.cuda.synchronize()
     got = b.acc.flat.double()
     scale = float(want.abs().max())

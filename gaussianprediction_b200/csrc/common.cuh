@@ -6,6 +6,7 @@
 #define GP_TILE_X 16
 #define GP_TILE_Y 16
 #define GP_TILE_PIX (GP_TILE_X * GP_TILE_Y)
+#define GP_MAX_INSTANCES (1ll << 30)   // sort keys per frame (and Gaussians): the radix sort packs 30-bit counts
 
 // Error codes returned across the C ABI (0 = ok, >0 = cudaError_t, <0 = ours).
 #define GP_OK 0

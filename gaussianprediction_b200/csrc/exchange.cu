@@ -1,0 +1,139 @@
+// Gradient exchange of the data-parallel frame loop over NVLink 5 / NVSwitch peer memory (sm_100a).
+//
+// The reference is single-GPU; the seam is its --batch accumulation (train.py:113-133): the gradients of the step's
+// (camera, time) samples are SUMMED.  With one process per GPU every rank holds the sum of its own samples in one flat
+// buffer (parallel.FlatGradAllReduce) and the step needs the sum over the ranks in every copy.
+//
+// One kernel does the whole all-reduce in place on a SYMMETRIC allocation (the same virtual layout on every rank,
+// mapped into every process: torch.distributed._symmetric_memory supplies the allocation and the address exchange):
+//   1. flag barrier: block b of every rank tells block b of every peer that it has started -- its predecessors on the
+//      stream, the kernels that wrote the gradients, are therefore complete;
+//   2. rank r owns slice r of the range.  With an NVSwitch multicast mapping, one `multimem.ld_reduce.add.v4.f32` per
+//      16 bytes makes the SWITCH read the word from all ranks and add them (NVLS), and one `multimem.st.v4.f32` writes
+//      the sum back to all ranks: every byte crosses this GPU's links once in and once out, instead of 2 (n - 1) / n
+//      times for a ring.  Without multicast (peer mapping only) the owner loads the word from every peer in rank
+//      order, adds, and stores it to every peer;
+//   3. flag barrier: all slices are written everywhere.
+// No host synchronisation, no NCCL launch: the kernel is stream-ordered (capturable), uses a few dozen CTAs and runs
+// next to the backward kernels of the following stage.  Each owner computes a word once and broadcasts it, so all
+// replicas receive bit-identical sums.
+#include "../../include/gp_b200.h"
+#include "common.cuh"
+
+#define GP_AR_MAX_WORLD 16
+#define GP_AR_THREADS 512
+#define GP_AR_FLAG_WORDS (GP_AR_MAX_WORLD + 1)   // per block: one arrival word per peer + this block's epoch
+
+struct GpPeers {
+  char* p[GP_AR_MAX_WORLD];
+};
+
+__device__ __forceinline__ void gp_st_release_sys(uint32_t* a, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(a), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t gp_ld_acquire_sys(const uint32_t* a) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(a) : "memory");
+  return v;
+}
+
+// Block b of this rank <-> block b of every peer.  Epochs only grow, so no flag is ever reset and a fast peer that is
+// already one call ahead cannot be mistaken for the current one (the comparison is on the signed difference).
+__device__ __forceinline__ void gp_peer_barrier(const GpPeers& peers, size_t flags_off, int rank, int world, uint32_t epoch) {
+  __syncthreads();
+  if (threadIdx.x < (unsigned)world) {
+    const int q = threadIdx.x;
+    __threadfence_system();
+    uint32_t* theirs = (uint32_t*)(peers.p[q] + flags_off) + (size_t)blockIdx.x * GP_AR_FLAG_WORDS + rank;
+    gp_st_release_sys(theirs, epoch);
+    const uint32_t* mine = (const uint32_t*)(peers.p[rank] + flags_off) + (size_t)blockIdx.x * GP_AR_FLAG_WORDS + q;
+    while ((int)(gp_ld_acquire_sys(mine) - epoch) < 0) {
+    }
+  }
+  __syncthreads();
+}
+
+template <bool MULTICAST>
+__global__ void __launch_bounds__(GP_AR_THREADS)
+gp_allreduce_sum_kernel(GpPeers peers, char* mc_base, int rank, int world, size_t byte_off, size_t n4, size_t flags_off) {
+  __shared__ uint32_t s_epoch;
+  uint32_t* my_epoch = (uint32_t*)(peers.p[rank] + flags_off) + (size_t)blockIdx.x * GP_AR_FLAG_WORDS + GP_AR_MAX_WORLD;
+  if (threadIdx.x == 0) s_epoch = *my_epoch;
+  __syncthreads();
+  const uint32_t e = s_epoch;
+  gp_peer_barrier(peers, flags_off, rank, world, e + 1);
+
+  const size_t per = (n4 + world - 1) / world;
+  const size_t lo = min(n4, per * rank), hi = min(n4, lo + per);
+  const size_t stride = (size_t)gridDim.x * GP_AR_THREADS;
+  if (MULTICAST) {
+    char* base = mc_base + byte_off;
+    size_t i = lo + (size_t)blockIdx.x * GP_AR_THREADS + threadIdx.x;
+    // four independent 16-byte reductions in flight per thread: the round trip through the switch is microseconds
+    for (; i + 3 * stride < hi; i += 4 * stride) {
+      float4 v[4];
+#pragma unroll
+      for (int u = 0; u < 4; u++)
+        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                     : "=f"(v[u].x), "=f"(v[u].y), "=f"(v[u].z), "=f"(v[u].w)
+                     : "l"(base + (i + u * stride) * 16)
+                     : "memory");
+#pragma unroll
+      for (int u = 0; u < 4; u++)
+        asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(base + (i + u * stride) * 16),
+                     "f"(v[u].x), "f"(v[u].y), "f"(v[u].z), "f"(v[u].w)
+                     : "memory");
+    }
+    for (; i < hi; i += stride) {
+      float4 v;
+      asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                   : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                   : "l"(base + i * 16)
+                   : "memory");
+      asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(base + i * 16), "f"(v.x), "f"(v.y),
+                   "f"(v.z), "f"(v.w)
+                   : "memory");
+    }
+  } else {
+    for (size_t i = lo + (size_t)blockIdx.x * GP_AR_THREADS + threadIdx.x; i < hi; i += stride) {
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int q = 0; q < world; q++) {   // rank order: every owner adds in the same order
+        float4 v;   // bypass L1: the peers wrote this memory
+        asm volatile("ld.global.relaxed.sys.v4.f32 {%0, %1, %2, %3}, [%4];"
+                     : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                     : "l"(peers.p[q] + byte_off + i * 16)
+                     : "memory");
+        acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+      }
+      for (int q = 0; q < world; q++) *(float4*)(peers.p[q] + byte_off + i * 16) = acc;
+    }
+  }
+  gp_peer_barrier(peers, flags_off, rank, world, e + 2);
+  if (threadIdx.x == 0) *my_epoch = e + 2;
+}
+
+extern "C" size_t gp_allreduce_flag_bytes(int blocks) {
+  return gp_align_up((size_t)(blocks > 0 ? blocks : 1) * GP_AR_FLAG_WORDS * sizeof(uint32_t), 256);
+}
+
+extern "C" int gp_allreduce_sum_f32(int rank, int world, void* multicast_base, void* const* peer_bases, size_t byte_offset,
+                                    size_t n_floats, size_t flags_byte_offset, int blocks, gp_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (world < 1 || world > GP_AR_MAX_WORLD || rank < 0 || rank >= world || !peer_bases || blocks < 1) return GP_ERR_BAD_ARG;
+  if ((byte_offset & 15) || (n_floats & 3) || (flags_byte_offset & 15)) return GP_ERR_BAD_ARG;   // 16-byte granules
+  if (n_floats == 0) return GP_OK;
+  GpPeers peers;
+  for (int q = 0; q < GP_AR_MAX_WORLD; q++) peers.p[q] = q < world ? (char*)peer_bases[q] : nullptr;
+  for (int q = 0; q < world; q++)
+    if (!peers.p[q]) return GP_ERR_BAD_ARG;
+  const size_t n4 = n_floats / 4;
+  if (multicast_base) {
+    GP_KERNEL("gp_allreduce_sum_kernel", stream, gp_allreduce_sum_kernel<true><<<blocks, GP_AR_THREADS, 0, stream>>>(
+        peers, (char*)multicast_base, rank, world, byte_offset, n4, flags_byte_offset));
+  } else {
+    GP_KERNEL("gp_allreduce_sum_kernel", stream, gp_allreduce_sum_kernel<false><<<blocks, GP_AR_THREADS, 0, stream>>>(
+        peers, nullptr, rank, world, byte_offset, n4, flags_byte_offset));
+  }
+  GP_LAUNCH_CHECK();
+  return GP_OK;
+}

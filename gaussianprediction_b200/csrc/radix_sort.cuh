@@ -205,7 +205,9 @@ gp_rs_pass_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restri
         unsigned polls = 0;
         while ((s & (GP_RS_FLAG_AGG | GP_RS_FLAG_PREFIX)) == 0u) {
           s = status[(size_t)(t0 - j) * GP_RS_RADIX + tid];
-          if (++polls > (1u << 26)) __trap();  // an earlier tile never published: fail loudly instead of hanging
+          // an earlier tile never published: after ~2^30 polls (minutes -- far beyond any time-slicing or debugger pause)
+          // fail loudly instead of hanging the device forever
+          if (++polls > (1u << 30)) __trap();
         }
         excl += s & GP_RS_COUNT_MASK;
         if (s & GP_RS_FLAG_PREFIX) done = true;

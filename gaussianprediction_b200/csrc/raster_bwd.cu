@@ -15,6 +15,8 @@
 //    output tensor needs a memset (the reference zero-fills 300 B per Gaussian per call,
 //    rasterize_points.cu:153-161).
 #include <stdlib.h>
+#include <atomic>
+#include <mutex>
 #include "gmath.cuh"
 #include "raster_common.cuh"
 #include "raster_state.cuh"
@@ -268,27 +270,6 @@ gp_render_bwd_butterfly_kernel(const uint2* __restrict__ ranges, const uint32_t*
 #define GP_BW_WARP_BYTES (2 * GP_BW_SLOTS * GP_BW_STRIDE * 4)
 #define GP_BW_SMEM (GP_BW_W + 8 * GP_BW_WARP_BYTES)
 
-__device__ __forceinline__ float4 gp_lds128(uint32_t a) {
-  float4 v;
-  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a));
-  return v;
-}
-__device__ __forceinline__ float gp_lds32(uint32_t a) {
-  float v;
-  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a));
-  return v;
-}
-__device__ __forceinline__ uint32_t gp_lds32u(uint32_t a) {
-  uint32_t v;
-  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a));
-  return v;
-}
-__device__ __forceinline__ void gp_sts32(uint32_t a, float v) { asm volatile("st.shared.f32 [%0], %1;" ::"r"(a), "f"(v) : "memory"); }
-__device__ __forceinline__ void gp_sts32u(uint32_t a, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
-__device__ __forceinline__ void gp_sts128(uint32_t a, float4 v) {
-  asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(a), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
-}
-
 __global__ void __launch_bounds__(GP_TILE_PIX, 4)
 gp_render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H,
                      unsigned grid_x, const float* __restrict__ bg_color, const float4* __restrict__ xy_depth,
@@ -297,8 +278,7 @@ gp_render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
                      const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpixels,
                      const int* __restrict__ hdr, float* __restrict__ grec) {
   extern __shared__ __align__(16) unsigned char s_raw[];
-  uint32_t sb = (uint32_t)__cvta_generic_to_shared(s_raw);
-  asm volatile("" : "+r"(sb));   // opaque: kept in a register instead of being rebuilt (S2R CgaCtaId + LEA) at every use
+  const uint32_t sb = gp_smem_base(s_raw);
 
   if (hdr[GP_HDR_OVERFLOW]) return;
   const int t = threadIdx.x, w = t >> 5, lane = t & 31;
@@ -893,8 +873,11 @@ extern "C" int gp_raster_backward(const gp_raster_cfg* cfg, const float* bg, con
 static __device__ __align__(256) float gp_static_grad_scratch[(size_t)GP_STATIC_MAX_GAUSSIANS * GP_GREC];
 
 #define GP_STATIC_MAX_DEVICES 64
-static float* gp_static_scratch_ptr[GP_STATIC_MAX_DEVICES];  // device address of the array, per device
-static bool gp_static_scratch_ready[GP_STATIC_MAX_DEVICES];
+// Device address of the array per device ordinal, filled once per device under a lock (two host threads may make
+// their first call at the same time); the atomic flag lets later calls skip the lock.
+static float* gp_static_scratch_ptr[GP_STATIC_MAX_DEVICES];
+static std::atomic<bool> gp_static_scratch_ready[GP_STATIC_MAX_DEVICES];
+static std::mutex gp_static_scratch_mu;
 
 extern "C" int gp_raster_backward_static_max_gaussians(void) { return GP_STATIC_MAX_GAUSSIANS; }
 
@@ -909,6 +892,8 @@ extern "C" int gp_raster_backward_static_max_gaussians(void) { return GP_STATIC_
 //   call uses is cleared on `stream` before the kernels run.  Two calls that can overlap on the same
 //   GPU (different streams, or threads) would sum into the same memory and corrupt each other --
 //   serialise them, or use gp_raster_backward with separate workspaces.
+// * The resolved address is cached per device for the life of the process; host threads may race on the first call
+//   (it is locked).  After cudaDeviceReset() the cache would be stale: do not reset a device this library has used.
 extern "C" int gp_raster_backward_static(const gp_raster_cfg* cfg, const float* bg, const float* means3D,
                                          const float* shs, const float* colors_precomp, const float* scales,
                                          const float* rotations, const float* cov3D_precomp, const float* viewmatrix,
@@ -922,13 +907,16 @@ extern "C" int gp_raster_backward_static(const gp_raster_cfg* cfg, const float* 
   int dev = -1;
   GP_CUDA_TRY(cudaGetDevice(&dev));
   if (dev < 0 || dev >= GP_STATIC_MAX_DEVICES) return GP_ERR_UNSUPPORTED;
-  if (!gp_static_scratch_ready[dev]) {
-    // In host code the array's name is only a handle for the runtime, not an address a kernel can use.
-    float* p = nullptr;
-    GP_CUDA_TRY(cudaGetSymbolAddress((void**)&p, gp_static_grad_scratch));
-    if (!p) return GP_ERR_UNSUPPORTED;
-    gp_static_scratch_ptr[dev] = p;
-    gp_static_scratch_ready[dev] = true;
+  if (!gp_static_scratch_ready[dev].load(std::memory_order_acquire)) {
+    std::lock_guard<std::mutex> lk(gp_static_scratch_mu);
+    if (!gp_static_scratch_ready[dev].load(std::memory_order_relaxed)) {
+      // In host code the array's name is only a handle for the runtime, not an address a kernel can use.
+      float* p = nullptr;
+      GP_CUDA_TRY(cudaGetSymbolAddress((void**)&p, gp_static_grad_scratch));
+      if (!p) return GP_ERR_UNSUPPORTED;
+      gp_static_scratch_ptr[dev] = p;
+      gp_static_scratch_ready[dev].store(true, std::memory_order_release);
+    }
   }
   // gp_raster_backward clears the first P records of the scratch on `stream` before accumulating.
   return gp_raster_backward(cfg, bg, means3D, shs, colors_precomp, scales, rotations, cov3D_precomp, viewmatrix,

@@ -54,6 +54,37 @@ __device__ __forceinline__ unsigned gp_patch_mask(const float4 co, const float c
 }
 
 // ------------------------------------------------------------------------------------------------
+// Explicit shared-space accesses (32-bit shared addresses).  A generic pointer into shared memory makes the compiler
+// rebuild the window base (S2R CgaCtaId + LEA) at the uses; the blend kernels keep one opaque base register instead.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ float4 gp_lds128(uint32_t a) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ float gp_lds32(uint32_t a) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ uint32_t gp_lds32u(uint32_t a) {
+  uint32_t v;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ void gp_sts32(uint32_t a, float v) { asm volatile("st.shared.f32 [%0], %1;" ::"r"(a), "f"(v) : "memory"); }
+__device__ __forceinline__ void gp_sts32u(uint32_t a, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
+__device__ __forceinline__ void gp_sts128(uint32_t a, float4 v) {
+  asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(a), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
+__device__ __forceinline__ uint32_t gp_smem_base(const void* p) {
+  uint32_t sb = (uint32_t)__cvta_generic_to_shared(p);
+  asm volatile("" : "+r"(sb));   // opaque to the optimiser: stays in a register
+  return sb;
+}
+
+// ------------------------------------------------------------------------------------------------
 // SH rows staged through shared memory (preprocess forward and backward)
 // ------------------------------------------------------------------------------------------------
 #define GP_SH_ROW 52  // floats per staged SH row in shared memory: 48 + 4 pad (16-byte aligned rows, conflict-free LDS.128)

@@ -295,9 +295,9 @@ gp_block_sum_kernel(int P, const uint32_t* __restrict__ sorted_idx, const uint32
 __global__ void __launch_bounds__(GP_SCAN_BLOCK)
 gp_duplicate_kernel(int P, const uint32_t* __restrict__ sorted_idx, const uint32_t* __restrict__ tiles_touched,
                     const float4* __restrict__ xy_depth, const int* __restrict__ radii,
-                    const uint32_t* __restrict__ block_excl, const int* __restrict__ hdr, unsigned grid_x,
+                    const uint32_t* __restrict__ block_excl, int* hdr, unsigned grid_x,
                     unsigned grid_y, uint32_t* __restrict__ tkeys, uint32_t* __restrict__ tvals, GpRadixTemp tile_radix,
-                    int passes, int* __restrict__ hdr_out, long long capacity, uint2* __restrict__ ranges, int tiles) {
+                    int passes, long long capacity, uint2* __restrict__ ranges, int tiles) {
   __shared__ uint32_t s_hist[GP_RS_MAX_PASSES][GP_RS_RADIX];  // digit counts of the tile ids this block emits
   __shared__ uint32_t s_off[GP_SCAN_BLOCK + 1];  // exclusive offsets inside the block
   __shared__ uint32_t s_g[GP_SCAN_BLOCK];
@@ -307,10 +307,12 @@ gp_duplicate_kernel(int P, const uint32_t* __restrict__ sorted_idx, const uint32
   // does the frame fit the binning buffers?  Every block decides for itself from R (no block reads the flag another
   // one writes); block 0 publishes the decision for the kernels that follow.  Tiles without instances keep range (0,0).
   const long long R = hdr[GP_HDR_NUM_RENDERED];
-  const bool over = R > capacity || R >= 0x7FFFFFFFll;
+  // (one plain pointer for the header: block 0 writes two of its words while every block reads a third)
+  // R >= 2^30 is refused: the radix sort's look-back words keep a 30-bit count next to 2 flag bits (radix_sort.cuh)
+  const bool over = R > capacity || R >= GP_MAX_INSTANCES;
   if (blockIdx.x == 0 && t == 0) {
-    hdr_out[GP_HDR_OVERFLOW] = over ? 1 : 0;
-    hdr_out[GP_HDR_NUM_SORTED] = over ? 0 : (int)R;
+    hdr[GP_HDR_OVERFLOW] = over ? 1 : 0;
+    hdr[GP_HDR_NUM_SORTED] = over ? 0 : (int)R;
   }
   for (int i = blockIdx.x * GP_SCAN_BLOCK + t; i < tiles; i += gridDim.x * GP_SCAN_BLOCK) ranges[i] = make_uint2(0u, 0u);
   if (over) return;
@@ -408,13 +410,12 @@ gp_render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
                      const float* __restrict__ bg_color, const int* __restrict__ hdr, float* __restrict__ final_T,
                      uint32_t* __restrict__ n_contrib, float* __restrict__ out_color, float* __restrict__ out_depth,
                      int* __restrict__ out_tidx) {
-  __shared__ float4 s_co[GP_TILE_PIX];
-  __shared__ float4 s_xyd[GP_TILE_PIX];
-  __shared__ float4 s_rgb[GP_TILE_PIX];
-  __shared__ int s_id[GP_TILE_PIX];
-  __shared__ unsigned s_mask[GP_TILE_PIX];
+  // one shared block addressed through an opaque 32-bit base (raster_common.cuh): [co | xyd | rgb | id | mask]
+  __shared__ __align__(16) unsigned char s_raw[GP_TILE_PIX * (3 * 16 + 2 * 4)];
+  const uint32_t sb = gp_smem_base(s_raw);
+  constexpr uint32_t S_CO = 0, S_XYD = GP_TILE_PIX * 16, S_RGB = 2 * GP_TILE_PIX * 16, S_ID = 3 * GP_TILE_PIX * 16,
+                     S_MASK = S_ID + GP_TILE_PIX * 4;
 
-  if (hdr[GP_HDR_OVERFLOW]) return;
   const int t = threadIdx.x, w = t >> 5, lane = t & 31;
   const unsigned tile = blockIdx.x;
   const unsigned tile_x = tile % grid_x, tile_y = tile / grid_x;
@@ -424,7 +425,10 @@ gp_render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
   const unsigned pix_id = (unsigned)W * py + px;
   const float pixfx = (float)px, pixfy = (float)py;
 
-  const uint2 range = ranges[tile];
+  // A frame that did not fit the caller's capacity is not rendered, but its outputs are DEFINED: the empty image
+  // (background, depth sentinel, no Gaussian), so a caller that misses the overflow flag never reads stale memory.
+  // Tile ranges are all (0,0) in that case (gp_duplicate_kernel), so the loop below simply does not run.
+  const uint2 range = hdr[GP_HDR_OVERFLOW] ? make_uint2(0u, 0u) : ranges[tile];
   const int rounds = ((range.y - range.x + GP_TILE_PIX - 1) / GP_TILE_PIX);
   int toDo = range.y - range.x;
   bool done = !inside;
@@ -443,30 +447,33 @@ gp_render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
     unsigned pmask = 0u;
     if (range.x + progress < range.y) {
       const int id = point_list[range.x + progress];
-      s_id[t] = id;
+      gp_sts32u(sb + S_ID + t * 4, (uint32_t)id);
       const float4 co = __ldg(conic_opacity + id);
       const float4 xyd = __ldg(xy_depth + id);
-      s_co[t] = co;
-      s_xyd[t] = xyd;
+      gp_sts128(sb + S_CO + t * 16, co);
+      gp_sts128(sb + S_XYD + t * 16, xyd);
+      float4 col;
       if (colors_precomp != nullptr)
-        s_rgb[t] = make_float4(colors_precomp[3 * (size_t)id], colors_precomp[3 * (size_t)id + 1],
-                               colors_precomp[3 * (size_t)id + 2], 0.f);
+        col = make_float4(colors_precomp[3 * (size_t)id], colors_precomp[3 * (size_t)id + 1],
+                          colors_precomp[3 * (size_t)id + 2], 0.f);
       else
-        s_rgb[t] = __ldg(rgb4 + id);
+        col = __ldg(rgb4 + id);
+      gp_sts128(sb + S_RGB + t * 16, col);
       pmask = gp_patch_mask(co, xyd.x, xyd.y, tile_fx0, tile_fy0);
     }
-    s_mask[t] = pmask;
+    gp_sts32u(sb + S_MASK + t * 4, pmask);
     __syncthreads();
     const int nb = min(GP_TILE_PIX, toDo);
     for (int c0 = 0; c0 < nb; c0 += 32) {
       if (__all_sync(0xffffffffu, done)) break;
-      unsigned bits = __ballot_sync(0xffffffffu, (s_mask[c0 + lane] >> w) & 1u);
+      unsigned bits = __ballot_sync(0xffffffffu, (gp_lds32u(sb + S_MASK + (c0 + lane) * 4) >> w) & 1u);
       while (bits) {
         const int j = c0 + __ffs(bits) - 1;
         bits &= bits - 1;
         if (done) continue;
-        const float4 xyd = s_xyd[j];
-        const float4 co = s_co[j];
+        const uint32_t aj = sb + j * 16;
+        const float4 xyd = gp_lds128(aj + S_XYD);
+        const float4 co = gp_lds128(aj + S_CO);
         const float dx = xyd.x - pixfx;
         const float dy = xyd.y - pixfy;
         const float qa = __fmul_rn(co.x, dx);
@@ -482,13 +489,13 @@ gp_render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
           done = true;
           continue;
         }
-        const float4 col = s_rgb[j];
+        const float4 col = gp_lds128(aj + S_RGB);
         C0 = __fmaf_rn(T, __fmul_rn(alpha, col.x), C0);
         C1 = __fmaf_rn(T, __fmul_rn(alpha, col.y), C1);
         C2 = __fmaf_rn(T, __fmul_rn(alpha, col.z), C2);
         if (T > 0.5f && test_T < 0.5f) {
           Dm = xyd.z;
-          tid = s_id[j];
+          tid = (int)gp_lds32u(sb + S_ID + j * 4);
         }
         T = test_T;
         last_contributor = (uint32_t)(i * GP_TILE_PIX + j + 1);  // position in the tile list, 1-based
@@ -523,6 +530,7 @@ __global__ void gp_check_frustum_kernel(int P, const float* __restrict__ means3D
 extern "C" int gp_raster_sizes(int P, int width, int height, long long capacity, size_t* geom_bytes,
                                size_t* binning_bytes, size_t* image_bytes) {
   if (P < 0 || width < 0 || height < 0 || capacity < 0) return GP_ERR_BAD_ARG;
+  if (capacity >= GP_MAX_INSTANCES || P >= GP_MAX_INSTANCES) return GP_ERR_LIMIT;   // 30-bit counts in the sort's look-back words
   if (geom_bytes) *geom_bytes = gp_carve_geom(nullptr, P).bytes;
   if (binning_bytes) *binning_bytes = gp_carve_binning(nullptr, capacity).bytes;
   if (image_bytes) *image_bytes = gp_carve_image(nullptr, width, height).bytes;
@@ -589,6 +597,7 @@ extern "C" int gp_raster_render(const gp_raster_cfg* cfg, const float* bg, const
     return GP_ERR_BAD_ARG;
   const int P = cfg->P, W = cfg->width, H = cfg->height;
   if (P <= 0 || W <= 0 || H <= 0 || capacity < 0) return GP_ERR_BAD_ARG;
+  if (capacity >= GP_MAX_INSTANCES || P >= GP_MAX_INSTANCES) return GP_ERR_LIMIT;
   GpGeom g = gp_carve_geom(geom_ws, P);
   GpBinning b = gp_carve_binning(binning_ws, capacity);
   GpImage im = gp_carve_image(image_ws, W, H);
@@ -600,7 +609,7 @@ extern "C" int gp_raster_render(const gp_raster_cfg* cfg, const float* bg, const
   b.radix.tickets = g.tile_tickets;  // preprocess stage); the status words are the binning workspace's own
   GP_KERNEL("gp_duplicate_kernel", stream, gp_duplicate_kernel<<<nb, GP_SCAN_BLOCK, 0, stream>>>(P, g.dvals[0], g.tiles_touched, g.xy_depth, radii, g.block_sums,
                                                         g.hdr, gx, gy, b.tkeys[0], b.tvals[0], b.radix, (bits + 7) / 8,
-                                                        g.hdr, capacity, im.ranges, (int)(gx * gy)));
+                                                        capacity, im.ranges, (int)(gx * gy)));
   GP_LAUNCH_CHECK();
   const int sel = gp_radix_sort_pairs(b.tkeys, b.tvals, g.hdr + GP_HDR_NUM_SORTED, 0, bits, b.radix, stream, /*reset=*/false,
                                       /*prepared=*/true);

@@ -136,3 +136,87 @@ def reduce_densification_stats(radii, visibility_filter, group=None):
     vis = visibility_filter.to(torch.int32)
     dist.all_reduce(vis, op=dist.ReduceOp.MAX, group=group)
     return radii, vis.bool()
+
+
+class NvlsFlatGradAllReduce(FlatGradAllReduce):
+    """``FlatGradAllReduce`` whose exchange is this library's own kernel (csrc/exchange.cu) instead of NCCL: the flat
+    buffer lives in a symmetric allocation (``torch.distributed._symmetric_memory`` provides the allocation and the
+    address exchange -- plumbing), every bucket is summed in place by ONE kernel per rank that reduces through the
+    NVSwitch multicast mapping (``multimem.ld_reduce`` / ``multimem.st``: in-switch reduction, NVLS) or, where no
+    multicast mapping exists, through plain peer loads and stores.  The kernel runs on a side stream next to the
+    backward kernels of the following stage; ``all_reduce_bucket`` returns a handle whose ``wait()`` joins it to the
+    current stream.  Results are bit-identical on every rank (each word is summed once by its owner and broadcast)."""
+
+    BLOCKS = int(__import__("os").environ.get("GP_EXCHANGE_BLOCKS", "48"))
+    MAX_BUCKETS = 4
+
+    @staticmethod
+    def supported(group=None):
+        """Collective: True on every rank iff a symmetric allocation can be set up on all of them."""
+        if not (dist.is_available() and dist.is_initialized()) or dist.get_backend(group) != "nccl":
+            return False
+        ok = 1
+        try:
+            import torch.distributed._symmetric_memory as symm
+            t = symm.empty(1024, dtype=torch.float32, device=torch.device("cuda", torch.cuda.current_device()))
+            symm.rendezvous(t, group if group is not None else dist.group.WORLD)
+        except Exception:
+            ok = 0
+        flag = torch.tensor([ok], device="cuda")
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+        return bool(flag.item())
+
+    def _alloc_flat(self, n, dtype, device):
+        import torch.distributed._symmetric_memory as symm
+        from . import _lib
+        assert dtype == torch.float32
+        L = _lib.lib()
+        self._flag_bytes = int(L.gp_allreduce_flag_bytes(self.BLOCKS))
+        data_bytes = (n * 4 + 255) // 256 * 256
+        self._flags_off = data_bytes
+        total = data_bytes + self.MAX_BUCKETS * self._flag_bytes
+        self._symm = symm.empty(total // 4, dtype=torch.float32, device=device)
+        self._symm.zero_()
+        self._hdl = symm.rendezvous(self._symm, self.group if self.group is not None else dist.group.WORLD)
+        torch.cuda.synchronize(device)
+        dist.barrier(group=self.group)              # every rank's flags are zero before anybody signals
+        self._rank, self._world = int(self._hdl.rank), int(self._hdl.world_size)
+        import ctypes
+        self._peers = (ctypes.c_void_p * self._world)(*[int(p) for p in self._hdl.buffer_ptrs])
+        mc = int(getattr(self._hdl, "multicast_ptr", 0) or 0)
+        self.multicast = mc != 0 and __import__("os").environ.get("GP_EXCHANGE_NO_MULTICAST") is None
+        self._mc = mc if self.multicast else None
+        self._side = torch.cuda.Stream(device=device)
+        self._evs = {}
+        return self._symm[:n]
+
+    def all_reduce_bucket(self, bucket):
+        from . import _lib
+        k = next(i for i, (_, _, e0, _) in enumerate(self.bucket_ranges) if self.flat[e0:].data_ptr() == bucket.data_ptr())
+        assert k < self.MAX_BUCKETS
+        off = bucket.data_ptr() - self._symm.data_ptr()
+        n = (bucket.numel() + 3) // 4 * 4           # buckets are padded to 16 bytes (FlatGradAllReduce layout)
+        cur = torch.cuda.current_stream(self.flat.device)
+        ready, done = self._evs.setdefault(k, (torch.cuda.Event(), torch.cuda.Event()))
+        ready.record(cur)
+        self._side.wait_event(ready)
+        _lib.check(_lib.lib().gp_allreduce_sum_f32(self._rank, self._world, self._mc, self._peers, off, n,
+                                                   self._flags_off + k * self._flag_bytes, self.BLOCKS,
+                                                   self._side.cuda_stream), "gp_allreduce_sum_f32")
+        done.record(self._side)
+        return _StreamJoin(done, self.flat.device)
+
+    def reduce(self, async_op=False):
+        self.pack()
+        works = [self.all_reduce_bucket(b) for b in self.buckets()]
+        for w in works:
+            w.wait()
+        return None
+
+
+class _StreamJoin:
+    def __init__(self, event, device):
+        self.event, self.device = event, device
+
+    def wait(self):
+        torch.cuda.current_stream(self.device).wait_event(self.event)

@@ -50,7 +50,7 @@ class TrainStep:
     """
 
     def __init__(self, pc, cam, capacity, bg=None, iteration=50_000, loss_fn=None, warmup=3, reducer=None,
-                 capture_collective=False, accumulate_into=None):
+                 capture_collective=False, accumulate_into=None, split_forward=False):
         """``reducer``: a ``parallel.FlatGradAllReduce`` over the same parameters.  The backward kernels then write
         the parameter gradients straight into its flat buffer (``_sinks``: no zero fill, no accumulation pass, no
         packing copies) and the step is captured as one CUDA graph per reducer bucket (up to three, see
@@ -59,9 +59,18 @@ class TrainStep:
         all-reduce into a single graph instead; EXPERIMENTAL -- with torch 2.11 / NCCL 2.28 on the B200 test box
         that capture hung, so it is off by default and not used by bench.py.
 
+        ``split_forward``: the deformation forward (neighbour search, keypoint MLP, blend) becomes a graph of its own in
+        front of the others.  It reads no SH coefficient, so ``_replay(wait_before_raster=...)`` can let the PREVIOUS
+        step's SH-gradient exchange (and the optimizer update that depends on it) run underneath it.
+
         ``accumulate_into``: a second ``FlatGradAllReduce`` with the same layout.  Every stage graph then ends with
         ``accumulate_into.bucket[k] += reducer.bucket[k]``: this step object serves samples 2.. of a gradient-
         accumulation step (``BatchStep``), the running sum lives in the other buffer and is what gets exchanged."""
+        self._ctor = dict(pc=pc, cam=cam, bg=bg, iteration=iteration, loss_fn=loss_fn, warmup=warmup, reducer=reducer,
+                          capture_collective=capture_collective, accumulate_into=accumulate_into,
+                          split_forward=split_forward)
+        self.split_forward = bool(split_forward)
+        self.deferred = None
         self.pc = pc
         self.reducer = reducer
         self.accumulate_into = accumulate_into
@@ -154,17 +163,26 @@ class TrainStep:
                 e1 = r.flat.numel() if last else r.bucket_ranges[k][3]
                 self.accumulate_into.flat[e0:e1].add_(r.flat[e0:e1])
 
-        def stage0():
-            for p in self.params:
-                p.grad = None
-            self.packed = 0                   # diagnostics: gradients that did NOT arrive through a sink
-            if can_cut_mlp:
-                model.keep_kp_deltas = True
+        split = self.split_forward and nb > 1
+
+        def forward(phase):
+            if phase != "raster":
+                for p in self.params:
+                    p.grad = None
+                self.packed = 0               # diagnostics: gradients that did NOT arrive through a sink
+                if can_cut_mlp:
+                    model.keep_kp_deltas = True
             with grad_sinks(zip(r.params, r.views)):      # looked up while the autograd graph is being built
-                self._render_aliased()
-            if can_cut_mlp:
+                self._render_aliased(phase)
+            if phase != "raster" and can_cut_mlp:
                 model.keep_kp_deltas = False
                 self._cut2, model._kp_deltas = model._kp_deltas, None
+
+        def stage_pre():
+            forward("deform")
+
+        def stage0():
+            forward("raster" if split else "all")
             deformed = [t for t in self.pkg["deformed"] if t.requires_grad]
             if nb == 1:
                 self._grads_into([self.loss], None, self.params, viewspace=True)
@@ -203,23 +221,55 @@ class TrainStep:
             self._cut2 = None
             finish(2, True)
 
+        self._n_pre = 1 if split else 0
+        pre = [stage_pre] if split else []
         if nb == 1:
             return [stage0]
         if not can_cut_mlp:
-            return [stage0, stage1]
-        return [stage0, stage1, stage2]
+            return pre + [stage0, stage1]
+        return pre + [stage0, stage1, stage2]
 
-    def _render_aliased(self):
+    def _render_aliased(self, phase="all"):
         """``render()`` + loss on fresh leaf ALIASES of the parameters (same storage, new autograd identity).  A parameter's
         AccumulateGrad node is bound to the stream it was first used on and stays alive as long as any earlier autograd
         graph does (a loss the caller still holds, say); the engine would then route this backward through that stream
         -- the legacy default stream, typically -- and break the capture.  Aliases made here belong to this stream."""
-        named = list(self.pc.named_parameters())
-        aliases = {n: p.detach().requires_grad_(p.requires_grad) for n, p in named}
-        self._alias = {id(p): aliases[n] for n, p in named}
-        with _reparametrize_module(self.pc, aliases):
-            self.pkg = render(self.cam, self.pc, None, self.bg, time=self.t, it=self.iteration, capacity=self.capacity)
-            self.loss = self.loss_fn(self.pkg["render"], self.target)
+        if phase != "raster":
+            named = list(self.pc.named_parameters())
+            self._aliases = {n: p.detach().requires_grad_(p.requires_grad) for n, p in named}
+            self._alias = {id(p): self._aliases[n] for n, p in named}
+        with _reparametrize_module(self.pc, self._aliases):
+            if phase == "deform":             # the deformation forward alone (``split_forward``)
+                self._deformed = tuple(self.pc(self.t, self.iteration))
+                return
+            self.pkg = render(self.cam, self.pc, None, self.bg, time=self.t, it=self.iteration, capacity=self.capacity,
+                              deformed=self._deformed if phase == "raster" else None)
+            self.loss = self._flag_overflow(self.loss_fn(self.pkg["render"], self.target))
+        self._deformed = None
+
+    def _flag_overflow(self, loss):
+        """Overflow policy, device side: a frame whose tile instances exceed ``capacity`` is not rendered (the image is
+        the empty one, every gradient zero) and its loss becomes NaN -- the caller, who reads the loss anyway
+        (train.py:139), sees it without an extra synchronisation and calls ``grow()``."""
+        from . import rasterizer as _r
+        hdr = _r.LAST_STATE.geom[:16].view(torch.int32)
+        if not hasattr(self, "_nan"):
+            self._nan = torch.full((), float("nan"), device=self.dev)
+        return torch.where(hdr[_lib.HDR_OVERFLOW] != 0, self._nan, loss)
+
+    def grow(self, capacity=None):
+        """Re-capture the step with room for more tile instances (default: 1.5 x the instance count of the frame that
+        overflowed); returns the new capacity.  The static inputs (camera, time, target) are kept."""
+        R, _ = self.overflowed()
+        new = int(capacity) if capacity is not None else int(max(R, self.capacity) * 1.5) + 65536
+        packed, target = self.cam.packed.clone(), self.target.clone()
+        stage = getattr(self, "_stage", None)
+        self.__init__(capacity=new, **self._ctor)
+        self.cam.packed.copy_(packed)
+        self.target.copy_(target)
+        if stage is not None:
+            del self._stage                     # staging slots are rebuilt against the new static tensors on next use
+        return new
 
     def _aliases_of(self, params):
         return [self._alias[id(p)] for p in params]
@@ -277,7 +327,7 @@ class TrainStep:
             self._grads_into([self.loss], None, self.params, viewspace=True)
         else:
             self.pkg = render(self.cam, self.pc, None, self.bg, time=self.t, it=self.iteration, capacity=self.capacity)
-            self.loss = self.loss_fn(self.pkg["render"], self.target)
+            self.loss = self._flag_overflow(self.loss_fn(self.pkg["render"], self.target))
             self.loss.backward()
         if self.capture_collective:
             import torch.distributed as dist
@@ -314,22 +364,22 @@ class TrainStep:
         assert len(self._pending) <= 2, "prefetch() twice without a step_prefetched() in between is the limit"
         self._slot ^= 1
 
-    def step_prefetched(self, exchange=None):
+    def step_prefetched(self, exchange=None, **kw):
         s = self._pending.pop(0)
         cur = torch.cuda.current_stream(self.dev)
         cur.wait_event(s["ready"])
         self.cam.packed.copy_(s["small"])
         self.target.copy_(s["target"])
         s["free"].record(cur)
-        return self._replay(exchange)
+        return self._replay(exchange, **kw)
 
-    def __call__(self, cam, t, target, non_blocking=True, exchange=None):
+    def __call__(self, cam, t, target, non_blocking=True, exchange=None, **kw):
         self.cam.load(cam, non_blocking)
         self.t.copy_(t, non_blocking=non_blocking)
         self.target.copy_(target, non_blocking=non_blocking)
-        return self._replay(exchange)
+        return self._replay(exchange, **kw)
 
-    def _replay(self, exchange=None):
+    def _replay(self, exchange=None, wait_before_raster=None, defer_first=False):
         """``exchange``: None = this step's own reducer (when it has one and a process group of more than one rank
         exists), False = no exchange (a sample in the middle of an accumulation step, or a single-rank run), or the
         ``FlatGradAllReduce`` whose buckets are to be summed over the ranks (the accumulator of a ``BatchStep``)."""
@@ -338,16 +388,25 @@ class TrainStep:
             if exchange is None:
                 exchange = self.reducer if (dist.is_available() and dist.is_initialized() and
                                             dist.get_world_size(self.reducer.group) > 1) else False
-            last = len(self.stage_graphs) - 1
+            npre = getattr(self, "_n_pre", 0)
+            for g in self.stage_graphs[:npre]:    # deformation forward: reads no SH coefficient
+                g.replay()
+            if wait_before_raster is not None:    # the previous step's SH exchange ran underneath it
+                wait_before_raster.wait()
+            stages = self.stage_graphs[npre:]
+            last = len(stages) - 1
+            self.deferred = None
             if exchange is False:
-                for g in self.stage_graphs:
+                for g in stages:
                     g.replay()
             else:
                 buckets, works = exchange.buckets(), []
-                for k, g in enumerate(self.stage_graphs):
+                for k, g in enumerate(stages):
                     g.replay()                    # stage k+1 runs while bucket k is on the wire
                     for b in (buckets[k:] if k == last else buckets[k:k + 1]):
                         works.append(exchange.all_reduce_bucket(b))
+                if defer_first and len(works) > 1:
+                    self.deferred, works = works[0], works[1:]    # bucket 0 (SH): joined by the NEXT step
                 for w in works:
                     if w is not None:
                         w.wait()
@@ -416,7 +475,13 @@ class BatchStep:
         self.world = dist.get_world_size(group) if (dist.is_available() and dist.is_initialized()) else 1
         self.group = group
         self.acc = make_reducer()
-        self.first = TrainStep(pc, cam, capacity, bg=bg, iteration=iteration, loss_fn=loss_fn, reducer=self.acc)
+        # Pipelined exchange (more than one rank): the SH bucket -- three quarters of the bytes -- is not joined at the end
+        # of the step but in front of the NEXT step's rasterizer, the first reader of the SH coefficients; it (and the
+        # optimizer update of that group) runs underneath the tail of this backward and the head of the next forward.
+        self.pipelined = self.world > 1 and os.environ.get("GP_PIPELINE_EXCHANGE", "1") != "0"
+        self._sh_pending = None
+        self.first = TrainStep(pc, cam, capacity, bg=bg, iteration=iteration, loss_fn=loss_fn, reducer=self.acc,
+                               split_forward=self.pipelined)
         self.rest = None
         if self.n > 1:
             self.scratch = make_reducer()
@@ -433,6 +498,7 @@ class BatchStep:
 
     def _after_sample(self, j, ts):
         if j == 0:
+            self._join_radii()                # the previous step's MAX reduction owns self.radii until it is done
             self.loss_sum.copy_(ts.loss.detach())
             self.radii.copy_(ts.pkg["radii"])
         else:
@@ -442,7 +508,11 @@ class BatchStep:
     def _finish(self):
         if self.world > 1 and self.exchange:
             import torch.distributed as dist
-            dist.all_reduce(self.radii, op=dist.ReduceOp.MAX, group=self.group)
+            w = dist.all_reduce(self.radii, op=dist.ReduceOp.MAX, group=self.group, async_op=True)
+            if self.pipelined:
+                self._radii_pending = w       # 4 B per Gaussian: joined by flush() / the next step, like the SH bucket
+            else:
+                w.wait()
         for p, v in zip(self.acc.params, self.acc.views):
             p.grad = v
         return self.loss_sum
@@ -452,11 +522,39 @@ class BatchStep:
 
     exchange = True     # False: leave the per-rank sums un-exchanged (diagnostics: bench.py's exchange check)
 
+    def _kw(self, j):
+        kw = {}
+        if j == 0 and self._sh_pending is not None:
+            kw["wait_before_raster"], self._sh_pending = self._sh_pending, None
+        if self.pipelined and self._exchange(j) is not False:
+            kw["defer_first"] = True
+        return kw
+
+    def _keep_deferred(self, ts):
+        if ts.deferred is not None:
+            self._sh_pending, ts.deferred = ts.deferred, None
+
+    def flush(self):
+        """Join the SH-gradient exchange of the last step to the current stream (pipelined mode): call it before reading
+        those gradients, e.g. in front of the optimizer update of the SH group.  The next ``step()`` does it by itself."""
+        if self._sh_pending is not None:
+            self._sh_pending.wait()
+            self._sh_pending = None
+        self._join_radii()
+
+    def _join_radii(self):
+        w, self._radii_pending = getattr(self, "_radii_pending", None), None
+        if w is not None:
+            w.wait()
+
     def step(self, samples):
         """``samples``: this rank's ``samples_per_rank`` tuples (camera, time [1], target [3,H,W]) of device tensors."""
         assert len(samples) == self.n
         for j, (ts, (cam, t, target)) in enumerate(zip(self._steps(), samples)):
-            ts(cam, t, target, exchange=self._exchange(j))
+            if j == 0 and not ts.split_forward:
+                self.flush()
+            ts(cam, t, target, exchange=self._exchange(j), **self._kw(j))
+            self._keep_deferred(ts)
             self._after_sample(j, ts)
         return self._finish()
 
@@ -473,7 +571,10 @@ class BatchStep:
                 steps[j + 1].prefetch(*samples[j + 1])
             elif next_first is not None:
                 steps[0].prefetch(*next_first)
-            ts.step_prefetched(exchange=self._exchange(j))
+            if j == 0 and not ts.split_forward:
+                self.flush()
+            ts.step_prefetched(exchange=self._exchange(j), **self._kw(j))
+            self._keep_deferred(ts)
             self._after_sample(j, ts)
         self._primed = next_first is not None
         return self._finish()
@@ -482,6 +583,27 @@ class BatchStep:
         a = self.first.overflowed()
         b = self.rest.overflowed() if self.rest is not None else (0, False)
         return max(a[0], b[0]), (a[1] or b[1])
+
+    def grow(self, capacity=None):
+        """Both captured steps re-captured with the same, larger capacity (see ``TrainStep.grow``)."""
+        self.flush()
+        R, _ = self.overflowed()
+        new = int(capacity) if capacity is not None else int(max(R, self.first.capacity) * 1.5) + 65536
+        self.first.grow(new)
+        if self.rest is not None:
+            self.rest.grow(new)
+        self._primed = False
+        return new
+
+    def step_checked(self, samples):
+        """``step()`` with the overflow policy applied: the loss of an overflowing frame is NaN (device side); if the
+        summed loss comes back NaN and a frame did overflow, the steps are re-captured with more room and the step is
+        run again.  One host read of the loss per step -- the read the training loop does anyway (train.py:139)."""
+        loss = self.step(samples)
+        if torch.isnan(loss).item() and self.overflowed()[1]:
+            self.grow()
+            loss = self.step(samples)
+        return loss
 
 
 class MotionStep:

@@ -37,7 +37,9 @@ def _sh_inputs(pc, override_color):
 
 
 def render(viewpoint_camera, pc, pipe=None, bg_color=None, scaling_modifier=1.0, override_color=None, delta=None,
-           time=None, it=1, capacity=None):
+           time=None, it=1, capacity=None, deformed=None):
+    """``deformed`` (extra, keyword only): the result of an earlier ``pc(time, it)`` call to use instead of calling it
+    here -- lets a captured step put the deformation forward and the rasterizer into different CUDA graphs."""
     screenspace_points = torch.zeros_like(pc.get_xyz, dtype=pc.get_xyz.dtype, requires_grad=True, device="cuda") + 0
     try:
         screenspace_points.retain_grad()
@@ -48,6 +50,8 @@ def render(viewpoint_camera, pc, pipe=None, bg_color=None, scaling_modifier=1.0,
     if time is None:
         means3D = pc.get_xyz + delta if delta is not None else pc.get_xyz
         scales, rotations = pc.get_scaling, pc.get_rotation
+    elif deformed is not None:
+        means3D, rotations, scales, opacity = deformed
     else:
         means3D, rotations, scales, opacity = pc(time, it)
     shs, shs_rest, colors_precomp = _sh_inputs(pc, override_color)

@@ -71,7 +71,7 @@ typedef struct {
 
 /* Header words at the start of the geometry workspace (int32 each); readable by the host. */
 #define GP_HDR_NUM_RENDERED 0 /* R = sum of tiles touched (may exceed the binning capacity) */
-#define GP_HDR_OVERFLOW 1     /* 1 if R > capacity: the frame was NOT rendered, retry with more */
+#define GP_HDR_OVERFLOW 1     /* 1 if R > capacity: the frame was NOT rendered (outputs = the empty image), retry with more */
 #define GP_HDR_NUM_POINTS 2   /* P */
 #define GP_HDR_NUM_SORTED 3   /* min(R, capacity) */
 #define GP_HDR_SCAN_TICKET 4  /* internal: blocks of the tiles-touched scan that have finished */
@@ -79,7 +79,8 @@ typedef struct {
 
 /* Workspace sizes in bytes for P Gaussians, a width x height image and room for `capacity` tile
  * instances.  (The reference grows three torch byte tensors through callbacks instead,
- * rasterize_points.cu:27-33,72-79.) */
+ * rasterize_points.cu:27-33,72-79.)  P and capacity must be below 2^30 (GP_ERR_LIMIT): the tile sort keeps 30-bit
+ * counts in its look-back words. */
 int gp_raster_sizes(int P, int width, int height, long long capacity, size_t* geom_bytes, size_t* binning_bytes,
                     size_t* image_bytes);
 
@@ -97,8 +98,9 @@ int gp_raster_num_rendered(const void* geom_ws, gp_stream_t stream, int* num_ren
 
 /* Stage 2 of the forward: duplicate-with-keys, tile sort, tile ranges, alpha/median-depth blending.
  * Reference: rasterizer_impl.cu:286-339, forward.cu:261-398.  `capacity` is the number of tile
- * instances binning_ws was sized for; if R > capacity nothing is rendered and GP_HDR_OVERFLOW is set
- * (no host sync is needed to launch this stage). */
+ * instances binning_ws was sized for; if R > capacity nothing is rendered, GP_HDR_OVERFLOW is set and the outputs
+ * hold the EMPTY image (background colour, depth 15, tidx -1; the backward then yields zero gradients) -- never
+ * uninitialised memory.  No host sync is needed to launch this stage. */
 int gp_raster_render(const gp_raster_cfg* cfg, const float* bg, const float* colors_precomp, void* geom_ws,
                      void* binning_ws, long long capacity, void* image_ws, const int* radii, float* out_color,
                      float* out_depth, int* out_tidx, gp_stream_t stream);
@@ -291,6 +293,21 @@ int gp_adam_step(int count, const gp_adam_tensor* tensors, double beta1, double 
 int gp_densification_stats(int P, const float* viewspace_grad /*[P,3]*/, const int* radii /*[P]*/,
                            float* max_radii2D /*[P]*/, float* xyz_gradient_accum /*[P,1]*/, float* denom /*[P,1]*/,
                            float* xyz_gradient_accum_max /*[P,1]*/, gp_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Gradient exchange of the data-parallel frame loop.  No reference counterpart: the reference is single-GPU; the
+ * seam is its --batch accumulation (train.py:113-133), which SUMS the gradients of the step's samples.
+ *
+ * gp_allreduce_sum_f32 sums `n_floats` floats at `byte_offset` of a SYMMETRIC allocation over `world` ranks, in
+ * place, in one kernel on `stream` (csrc/exchange.cu): peer_bases[q] is rank q's copy of the allocation as mapped into
+ * this process (host array of `world` device addresses), multicast_base the NVSwitch multicast mapping of the same
+ * allocation or NULL (then plain peer loads/stores are used).  The allocation also holds gp_allreduce_flag_bytes(blocks)
+ * bytes of zero-initialised flags at `flags_byte_offset`; calls that may overlap in time must use different flag
+ * regions.  Every rank must issue the same call (same sizes, same `blocks`, <= the number of co-resident CTAs).
+ * byte_offset, flags_byte_offset: multiples of 16; n_floats: multiple of 4; world <= 16. */
+size_t gp_allreduce_flag_bytes(int blocks);
+int gp_allreduce_sum_f32(int rank, int world, void* multicast_base, void* const* peer_bases, size_t byte_offset,
+                         size_t n_floats, size_t flags_byte_offset, int blocks, gp_stream_t stream);
 
 #ifdef __cplusplus
 }

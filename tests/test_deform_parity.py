@@ -472,6 +472,45 @@ def test_batch_step_accumulates_samples(gplib):
                 assert rel_err(p.grad, want[n]) <= 1e-3, (mode, n, rel_err(p.grad, want[n]))
 
 
+def test_overflow_policy_nan_loss_then_grow(gplib):
+    """A frame with more tile instances than the captured capacity: defined outputs (empty image, zero gradients), NaN
+    loss on the device (no extra sync), and ``step_checked`` re-captures with more room and reruns the step."""
+    from gaussianprediction_b200 import synthetic as syn
+    from gaussianprediction_b200.deform import KeypointDeformation, default_args
+    from gaussianprediction_b200.parallel import FlatGradAllReduce
+    from gaussianprediction_b200.pipeline import BatchStep
+    from gaussianprediction_b200.renderer import SceneModel, render
+    N, Kp, W, H = 6000, 96, 128, 96
+    gs, kp, kf, logits = scene(N, Kp, seed=53)
+    args = default_args(feature_amplify=0.5, norm_rotation=True)
+    torch.manual_seed(0)
+    model = KeypointDeformation(args, gs.xyz, gs.rotation, gs.scaling, gs.opacity, gs.motion_feature, kp, kf, logits=logits)
+    pc = SceneModel(model, gs.features_dc, gs.features_rest).cuda()
+    cam = syn.camera_ring(1, W, H, seed=7)[0]
+    for k in ("world_view_transform", "full_proj_transform", "camera_center"):
+        setattr(cam, k, getattr(cam, k).cuda())
+    bg = torch.tensor([0.25, 0.5, 0.75], device="cuda")
+    t = torch.tensor([0.4], device="cuda")
+    tgt = (torch.randn(3, H, W, generator=torch.Generator().manual_seed(3)) * 1e-2).cuda()
+    pkg = render(cam, pc, None, bg, time=t, it=50_000)
+    want = float((pkg["render"] * tgt).sum())
+    del pkg
+    with_grad = [p for n, p in pc.named_parameters() if not n.endswith("motion_feature")]
+    batch = BatchStep(pc, cam, 1000, lambda: FlatGradAllReduce(with_grad), 1, bg=bg)      # far too small on purpose
+    loss = batch.step([(cam, t, tgt)])
+    torch.cuda.synchronize()
+    R, over = batch.overflowed()
+    assert over and R > 1000 and bool(torch.isnan(loss))
+    img = batch.first.pkg["render"]
+    assert float((img - bg.view(3, 1, 1)).abs().max()) == 0.0                # the empty image, not stale memory
+    assert int((batch.first.pkg["tidx"] != -1).sum()) == 0 and float((batch.first.pkg["depth"] - 15.0).abs().max()) == 0.0
+    assert all(float(p.grad.abs().max()) == 0.0 for p in with_grad if p.grad is not None)
+    loss = batch.step_checked([(cam, t, tgt)])
+    torch.cuda.synchronize()
+    assert not batch.overflowed()[1] and batch.first.capacity >= R
+    assert abs(float(loss) - want) <= 1e-5 * max(1.0, abs(want))
+
+
 def test_full_size_deformation_properties_1m(gplib):
     """BASELINE.json's large configs (C4/C5: 1-2 M Gaussians) are too big for the brute-force oracle, so the
     deformation stage is checked there through size-independent properties: the neighbour lists are sorted, unique and

@@ -45,7 +45,15 @@ def _backward(c, st, grad, static):
     tail = (ptr(out["means2D"]), None, ptr(out["opacity"]), ptr(out["means3D"]), None, ptr(out["sh"]),
             ptr(out["scales"]), ptr(out["rotations"]), _lib.stream_ptr())
     if static:
+        torch.cuda.synchronize()
+        free0 = torch.cuda.mem_get_info()[0]
         check(L.gp_raster_backward_static(*head, *tail), "gp_raster_backward_static")
+        torch.cuda.synchronize()
+        # the property the entry point exists for: the device's free memory is the same before and after the call
+        # (cudaMemGetInfo; the first call on a device has already resolved the scratch address in the warm-up below)
+        if getattr(_backward, "warmed", False):
+            assert torch.cuda.mem_get_info()[0] == free0, "gp_raster_backward_static changed the device's free memory"
+        _backward.warmed = True
     else:
         ws = torch.empty((L.gp_raster_backward_ws_bytes(P),), dtype=torch.uint8, device="cuda")
         check(L.gp_raster_backward(*head, ptr(ws), *tail), "gp_raster_backward")
@@ -64,6 +72,20 @@ def test_static_backward_matches_workspace_backward_twice(gplib):
         for k in ref:
             assert torch.isfinite(got[k]).all(), (call, k)
             assert rel_err(got[k], ref[k]) <= GRAD_TOL, (call, k, rel_err(got[k], ref[k]))
+
+
+def test_static_backward_at_its_limit(gplib):
+    """Exactly gp_raster_backward_static_max_gaussians() Gaussians: the whole static array is in use."""
+    from gaussianprediction_b200 import _lib
+    limit = _lib.lib().gp_raster_backward_static_max_gaussians()
+    case = raster_case(N=limit, W=192, H=128, seed=5)
+    c, rs, st = _forward(case)
+    grad = (torch.randn(3, c["H"], c["W"], generator=torch.Generator().manual_seed(33)) * 1e-2).cuda().contiguous()
+    ref = _backward(c, st, grad, static=False)
+    got = _backward(c, st, grad, static=True)
+    for k in ref:
+        assert torch.isfinite(got[k]).all(), k
+        assert rel_err(got[k], ref[k]) <= GRAD_TOL, (k, rel_err(got[k], ref[k]))
 
 
 def test_static_backward_rejects_sizes_beyond_its_limit(gplib):
