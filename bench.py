@@ -231,7 +231,10 @@ class OurRunner:
             elif self.exchange == "nvls":
                 raise SystemExit("--exchange nvls: no symmetric memory between the ranks here")
         red = cls(live, first=[self.pc._features_dc, self.pc._features_rest],
-                  second=[d._xyz, d._rotation, d._scaling, d._opacity] + list(d.weights_model.parameters()))
+                  # xyz goes with the keypoints and MLP weights into the LAST bucket: the next step's neighbour search needs
+                  # it first, so that bucket is the one joined at the end of the step; the others are joined later
+                  second=[d._rotation, d._scaling, d._opacity] + list(d.weights_model.parameters()),
+                  aux_int32=self.wl["N"] if first_call else 0)       # the radii ride the same exchange (MAX)
         if first_call:
             self.exchange_kind = ("gp_allreduce_sum_kernel over symmetric memory (" +
                                   ("NVSwitch multicast, multimem.ld_reduce" if red.multicast else "peer loads/stores") + ")") \
@@ -246,13 +249,21 @@ class OurRunner:
         self.exchange_kind = "none"
         self.batch = BatchStep(self.pc, self.cams_dev[0], self.capacity, self.make_reducer, self.local, bg=self.bg,
                                iteration=ITER)
+        if os.environ.get("GP_BENCH_NO_EXCHANGE"):       # DIAGNOSTIC ONLY: the compute of a step without its exchange
+            self.batch.exchange = False
+            self.exchange_kind += " -- DISABLED (GP_BENCH_NO_EXCHANGE): not a valid result"
+        # device-resident samples in the packed form the captured step keeps its camera in (view | proj | centre | time)
+        self.packed_dev = [torch.cat([c.world_view_transform.reshape(-1), c.full_proj_transform.reshape(-1),
+                                      c.camera_center.reshape(-1), t.reshape(-1)]).contiguous()
+                           for c, t in zip(self.cams_dev, self.times_dev)]
 
     def step_graph(self, s, host_inputs=False):
         ids = self._ids(s)
         if host_inputs:
             nxt = self.sample(self._ids(s + 1)[0], True)
             return self.batch.step_host([self.sample(g, True) for g in ids], next_first=nxt)
-        return self.batch.step([self.sample(g) for g in ids])
+        return self.batch.step([(self.packed_dev[g % len(self.packed_dev)], self.grads_dev[g % len(self.grads_dev)])
+                                for g in ids])
 
     def allreduce(self):
         if getattr(self, "_grouped", None) is None:
@@ -346,6 +357,11 @@ def timed_steps(runner, steps, warmup, world, host_inputs, flush, graph=False):
     flushed (256 MiB write) between steps outside the events; returns (per-step device ms list, wall ms)."""
     import torch.distributed as dist
     step = runner.step_graph if graph else runner.step
+    # End to end: the loss of every step is copied to pinned host memory inside the timed region and read by the host
+    # ONE STEP LATER (the reference reads it for its progress bar only, train.py:139-147), so the host keeps enqueueing
+    # while the GPU computes; the last step's loss is read before its closing event.
+    pinned = [torch.zeros((), dtype=torch.float32).pin_memory() for _ in range(2)] if host_inputs else None
+    copied = [torch.cuda.Event(), torch.cuda.Event()] if host_inputs else None
     for i in range(warmup):
         loss = step(i, host_inputs)
         if host_inputs:
@@ -355,21 +371,31 @@ def timed_steps(runner, steps, warmup, world, host_inputs, flush, graph=False):
         dist.barrier()
     torch.cuda.synchronize()
     evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    losses = []
     t0 = time.perf_counter()
     for i in range(steps):
         flush.add_(1.0)                      # evict L2 (126 MB) between timed steps
         evs[i][0].record()
         loss = step(warmup + i, host_inputs)
         if i == steps - 1 and graph and getattr(runner, "batch", None) is not None:
-            runner.batch.flush()             # pipelined exchange: the last step's SH bucket is joined inside its bracket
-        if host_inputs:
-            loss.item()                      # D2H read of the step's result inside the timed region
+            runner.batch.flush()             # pipelined exchange: the last step's buckets are joined inside its bracket
+        if host_inputs:                      # D2H read of every step's result inside the timed region
+            pinned[i & 1].copy_(loss.detach(), non_blocking=True)
+            copied[i & 1].record()
+            if i > 0:
+                copied[(i - 1) & 1].synchronize()
+                losses.append(float(pinned[(i - 1) & 1]))
+            if i == steps - 1:
+                copied[i & 1].synchronize()
+                losses.append(float(pinned[i & 1]))
         evs[i][1].record()
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
     wall_ms = (time.perf_counter() - t0) * 1e3
+    if host_inputs:
+        assert len(losses) == steps and all(math.isfinite(x) for x in losses), "a step's loss did not reach the host"
     return [a.elapsed_time(b) for a, b in evs], wall_ms
 
 
@@ -880,7 +906,7 @@ def main():
     if clocks is not None:
         line["clocks"] = clocks
 
-    if args.impl == "ours" and eff_world > 1:
+    if args.impl == "ours" and eff_world > 1 and not os.environ.get("GP_BENCH_NO_EXCHANGE"):
         chk = exchange_check(runner, warmup + steps)
         line["exchange_check"] = chk
         line["exchange_alone_ms"] = round(exchange_time(runner), 4)

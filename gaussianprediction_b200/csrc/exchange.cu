@@ -19,6 +19,7 @@
 // replicas receive bit-identical sums.
 #include "../../include/gp_b200.h"
 #include "common.cuh"
+#include <limits.h>
 
 #define GP_AR_MAX_WORLD 16
 #define GP_AR_THREADS 512
@@ -112,6 +113,39 @@ gp_allreduce_sum_kernel(GpPeers peers, char* mc_base, int rank, int world, size_
   if (threadIdx.x == 0) *my_epoch = e + 2;
 }
 
+// Element-wise MAX of int32 (the radii of the step's samples: max over samples and ranks, train.py:122; visibility is
+// radii > 0).  Same protocol; 4-byte granules (the integer forms of multimem.ld_reduce are scalar).
+template <bool MULTICAST>
+__global__ void __launch_bounds__(GP_AR_THREADS)
+gp_allreduce_max_kernel(GpPeers peers, char* mc_base, int rank, int world, size_t byte_off, size_t n, size_t flags_off) {
+  __shared__ uint32_t s_epoch;
+  uint32_t* my_epoch = (uint32_t*)(peers.p[rank] + flags_off) + (size_t)blockIdx.x * GP_AR_FLAG_WORDS + GP_AR_MAX_WORLD;
+  if (threadIdx.x == 0) s_epoch = *my_epoch;
+  __syncthreads();
+  const uint32_t e = s_epoch;
+  gp_peer_barrier(peers, flags_off, rank, world, e + 1);
+  const size_t per = (n + world - 1) / world;
+  const size_t lo = min(n, per * rank), hi = min(n, lo + per);
+  const size_t stride = (size_t)gridDim.x * GP_AR_THREADS;
+  for (size_t i = lo + (size_t)blockIdx.x * GP_AR_THREADS + threadIdx.x; i < hi; i += stride) {
+    if (MULTICAST) {
+      int v;
+      asm volatile("multimem.ld_reduce.relaxed.sys.global.max.s32 %0, [%1];" : "=r"(v) : "l"(mc_base + byte_off + i * 4) : "memory");
+      asm volatile("multimem.st.relaxed.sys.global.b32 [%0], %1;" ::"l"(mc_base + byte_off + i * 4), "r"(v) : "memory");
+    } else {
+      int m = INT_MIN;
+      for (int q = 0; q < world; q++) {
+        int v;
+        asm volatile("ld.global.relaxed.sys.s32 %0, [%1];" : "=r"(v) : "l"(peers.p[q] + byte_off + i * 4) : "memory");
+        m = max(m, v);
+      }
+      for (int q = 0; q < world; q++) *(int*)(peers.p[q] + byte_off + i * 4) = m;
+    }
+  }
+  gp_peer_barrier(peers, flags_off, rank, world, e + 2);
+  if (threadIdx.x == 0) *my_epoch = e + 2;
+}
+
 extern "C" size_t gp_allreduce_flag_bytes(int blocks) {
   return gp_align_up((size_t)(blocks > 0 ? blocks : 1) * GP_AR_FLAG_WORDS * sizeof(uint32_t), 256);
 }
@@ -133,6 +167,27 @@ extern "C" int gp_allreduce_sum_f32(int rank, int world, void* multicast_base, v
   } else {
     GP_KERNEL("gp_allreduce_sum_kernel", stream, gp_allreduce_sum_kernel<false><<<blocks, GP_AR_THREADS, 0, stream>>>(
         peers, nullptr, rank, world, byte_offset, n4, flags_byte_offset));
+  }
+  GP_LAUNCH_CHECK();
+  return GP_OK;
+}
+
+extern "C" int gp_allreduce_max_s32(int rank, int world, void* multicast_base, void* const* peer_bases, size_t byte_offset,
+                                    size_t n_ints, size_t flags_byte_offset, int blocks, gp_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (world < 1 || world > GP_AR_MAX_WORLD || rank < 0 || rank >= world || !peer_bases || blocks < 1) return GP_ERR_BAD_ARG;
+  if ((byte_offset & 3) || (flags_byte_offset & 15)) return GP_ERR_BAD_ARG;
+  if (n_ints == 0) return GP_OK;
+  GpPeers peers;
+  for (int q = 0; q < GP_AR_MAX_WORLD; q++) peers.p[q] = q < world ? (char*)peer_bases[q] : nullptr;
+  for (int q = 0; q < world; q++)
+    if (!peers.p[q]) return GP_ERR_BAD_ARG;
+  if (multicast_base) {
+    GP_KERNEL("gp_allreduce_max_kernel", stream, gp_allreduce_max_kernel<true><<<blocks, GP_AR_THREADS, 0, stream>>>(
+        peers, (char*)multicast_base, rank, world, byte_offset, n_ints, flags_byte_offset));
+  } else {
+    GP_KERNEL("gp_allreduce_max_kernel", stream, gp_allreduce_max_kernel<false><<<blocks, GP_AR_THREADS, 0, stream>>>(
+        peers, nullptr, rank, world, byte_offset, n_ints, flags_byte_offset));
   }
   GP_LAUNCH_CHECK();
   return GP_OK;

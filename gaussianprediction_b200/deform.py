@@ -336,6 +336,7 @@ class KeypointDeformation(nn.Module):
         self._idx32 = None
         self._last_logits = None
         self.keep_kp_deltas, self._kp_deltas = False, None
+        self._pre_blend_hook = None
         self.fused_mlp = True   # keypoint MLP through gp_kpmlp_* (False: the torch modules, e.g. to compare)
         self.knn_cache = False  # eval: the search inputs are parameters only, so it can be hoisted out of the frame loop
         # Morton order of the Gaussians, a speed hint for the search (results do not depend on it).  Built on first use
@@ -429,6 +430,8 @@ class KeypointDeformation(nn.Module):
             self.kpts_xyz_motion, self.kpts_rotation_motion = delta_xyz.detach(), delta_q.detach()
             if self.keep_kp_deltas:          # pipeline.TrainStep cuts the backward here (and drops the reference again)
                 self._kp_deltas = (delta_xyz, delta_q)
+            if self._pre_blend_hook is not None:      # pipeline.TrainStep ends one captured graph here and starts the next:
+                self._pre_blend_hook()                # what precedes reads only xyz / keypoints / MLP, what follows the rest
             xyz, q, s, opacity = keypoint_blend(logits, self._idx32, delta_xyz, delta_q, self._xyz, self._rotation,
                                                 self._scaling, self._opacity)
         self.lifecycle_opacity = None

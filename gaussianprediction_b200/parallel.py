@@ -22,13 +22,14 @@ class FlatGradAllReduce:
     this rank), sums it over the process group and points ``p.grad`` at views of the reduced buffer, so every rank
     ends the step with identical gradients (and, with identical optimizer state, identical parameters)."""
 
-    def __init__(self, params, group=None, first=(), second=()):
+    def __init__(self, params, group=None, first=(), second=(), aux_int32=0):
         """``first`` / ``second``: parameters whose gradients are complete early in the backward, in that order -- the
         SH coefficients (written by the rasterizer backward), then the per-Gaussian deformation parameters (written
         by the blend backward).  Each group becomes its own bucket at the front of the buffer so that
         ``pipeline.TrainStep`` can start its all-reduce while the rest of the backward is still running; everything
         else forms the last bucket.  ``reduce()`` itself always exchanges the whole buffer."""
         params = [p for p in params if p.requires_grad]
+        self._aux_n = int(aux_int32)      # optional int32 side buffer exchanged with MAX (radii, train.py:122)
         groups, seen = [], set()
         for grp in (first, second):
             ids = {id(p) for p in grp}
@@ -60,7 +61,12 @@ class FlatGradAllReduce:
             i += len(grp)
 
     def _alloc_flat(self, n, dtype, device):
+        self.aux = torch.zeros(self._aux_n, dtype=torch.int32, device=device) if self._aux_n else None
         return torch.zeros(n, dtype=dtype, device=device)
+
+    def all_reduce_max_aux(self):
+        """Element-wise MAX of ``aux`` over the ranks; returns a handle with ``wait()``."""
+        return dist.all_reduce(self.aux, op=dist.ReduceOp.MAX, group=self.group, async_op=True)
 
     def buckets(self):
         """The flat buffer bucket by bucket, in the order their gradients complete."""
@@ -147,8 +153,7 @@ class NvlsFlatGradAllReduce(FlatGradAllReduce):
     backward kernels of the following stage; ``all_reduce_bucket`` returns a handle whose ``wait()`` joins it to the
     current stream.  Results are bit-identical on every rank (each word is summed once by its owner and broadcast)."""
 
-    BLOCKS = int(__import__("os").environ.get("GP_EXCHANGE_BLOCKS", "48"))
-    MAX_BUCKETS = 4
+    BLOCKS = int(__import__("os").environ.get("GP_EXCHANGE_BLOCKS", "24"))   # CTAs of the exchange kernel (tools/exchange_probe.py)
 
     @staticmethod
     def supported(group=None):
@@ -167,44 +172,64 @@ class NvlsFlatGradAllReduce(FlatGradAllReduce):
         return bool(flag.item())
 
     def _alloc_flat(self, n, dtype, device):
+        import ctypes
+        import os
         import torch.distributed._symmetric_memory as symm
         from . import _lib
         assert dtype == torch.float32
         L = _lib.lib()
-        self._flag_bytes = int(L.gp_allreduce_flag_bytes(self.BLOCKS))
+        self._flag_bytes = int(L.gp_allreduce_flag_bytes(max(self.BLOCKS, 148)))
         data_bytes = (n * 4 + 255) // 256 * 256
+        self._aux_off = data_bytes
+        data_bytes += (self._aux_n * 4 + 255) // 256 * 256
         self._flags_off = data_bytes
-        total = data_bytes + self.MAX_BUCKETS * self._flag_bytes
+        total = data_bytes + self._flag_bytes
         self._symm = symm.empty(total // 4, dtype=torch.float32, device=device)
         self._symm.zero_()
         self._hdl = symm.rendezvous(self._symm, self.group if self.group is not None else dist.group.WORLD)
         torch.cuda.synchronize(device)
         dist.barrier(group=self.group)              # every rank's flags are zero before anybody signals
         self._rank, self._world = int(self._hdl.rank), int(self._hdl.world_size)
-        import ctypes
         self._peers = (ctypes.c_void_p * self._world)(*[int(p) for p in self._hdl.buffer_ptrs])
         mc = int(getattr(self._hdl, "multicast_ptr", 0) or 0)
-        self.multicast = mc != 0 and __import__("os").environ.get("GP_EXCHANGE_NO_MULTICAST") is None
+        # measured (tools/exchange_probe.py, B200 NVSwitch box, 512 MiB): 8 ranks multimem 1.13 ms on 24 CTAs vs NCCL 1.34,
+        # peer ld/st 1.51; 2 ranks peer ld/st 0.81 ms on 148 CTAs vs NCCL 1.00, multimem 1.33 -- the in-switch reduction
+        # pays from 3 ranks up
+        self.multicast = mc != 0 and os.environ.get("GP_EXCHANGE_NO_MULTICAST") is None and self._world > 2
         self._mc = mc if self.multicast else None
+        if "GP_EXCHANGE_BLOCKS" not in os.environ:
+            self.BLOCKS = 24 if self.multicast else 148
         self._side = torch.cuda.Stream(device=device)
-        self._evs = {}
+        self.aux = self._symm[self._aux_off // 4:self._aux_off // 4 + self._aux_n].view(torch.int32) if self._aux_n else None
         return self._symm[:n]
 
-    def all_reduce_bucket(self, bucket):
+    def _launch(self, fn, what, byte_off, n):
         from . import _lib
-        k = next(i for i, (_, _, e0, _) in enumerate(self.bucket_ranges) if self.flat[e0:].data_ptr() == bucket.data_ptr())
-        assert k < self.MAX_BUCKETS
-        off = bucket.data_ptr() - self._symm.data_ptr()
-        n = (bucket.numel() + 3) // 4 * 4           # buckets are padded to 16 bytes (FlatGradAllReduce layout)
+        from . import pipeline as _p
         cur = torch.cuda.current_stream(self.flat.device)
-        ready, done = self._evs.setdefault(k, (torch.cuda.Event(), torch.cuda.Event()))
+        ready, done = torch.cuda.Event(), torch.cuda.Event()
         ready.record(cur)
         self._side.wait_event(ready)
-        _lib.check(_lib.lib().gp_allreduce_sum_f32(self._rank, self._world, self._mc, self._peers, off, n,
-                                                   self._flags_off + k * self._flag_bytes, self.BLOCKS,
-                                                   self._side.cuda_stream), "gp_allreduce_sum_f32")
+        _p._mark(f"{what} {n * 4 >> 20} MiB start", self._side)
+        _lib.check(fn(self._rank, self._world, self._mc, self._peers, byte_off, n, self._flags_off, self.BLOCKS,
+                      self._side.cuda_stream), what)
+        _p._mark(f"{what} {n * 4 >> 20} MiB end", self._side)
         done.record(self._side)
         return _StreamJoin(done, self.flat.device)
+
+    def all_reduce_bucket(self, bucket):
+        """Sum any 16-byte aligned slice of ``flat`` over the ranks on the side stream.  The calls of one reducer run
+        one after the other (same stream), so they share one flag region: epochs only grow, and a rank that is already
+        in the next call cannot release a peer that still waits in this one before that peer's own data is complete."""
+        from . import _lib
+        off = bucket.data_ptr() - self._symm.data_ptr()
+        n = bucket.numel()
+        assert off % 16 == 0 and n % 4 == 0 and 0 <= off and off + 4 * n <= self._aux_off
+        return self._launch(_lib.lib().gp_allreduce_sum_f32, "gp_allreduce_sum_f32", off, n)
+
+    def all_reduce_max_aux(self):
+        from . import _lib
+        return self._launch(_lib.lib().gp_allreduce_max_s32, "gp_allreduce_max_s32", self._aux_off, self._aux_n)
 
     def reduce(self, async_op=False):
         self.pack()

@@ -20,6 +20,22 @@ from .rasterizer import export_state  # noqa: F401  (kept importable for diagnos
 from .renderer import render
 
 
+# share of the SH bucket exchanged right after the rasterizer backward in pipelined mode (the rest follows the small
+# buckets).  Measured on the 2 M-Gaussian job at 8 ranks: 0 is best (3.65 vs 3.80 ms per step with 0.25) -- under the
+# blend backward the head runs at a third of its speed and delays the buckets the next step needs first
+EARLY_FRACTION = float(os.environ.get("GP_EXCHANGE_EARLY_FRACTION", "0"))
+
+TRACE = None     # diagnostics (tools/timeline_probe.py): a list that receives (label, timing event, host time) marks
+
+
+def _mark(label, stream=None):
+    if TRACE is not None:
+        import time
+        e = torch.cuda.Event(enable_timing=True)
+        e.record(stream if stream is not None else torch.cuda.current_stream())
+        TRACE.append((label, e, time.perf_counter()))
+
+
 class _StaticCamera:
     def __init__(self, cam, device):
         self.image_width, self.image_height = int(cam.image_width), int(cam.image_height)
@@ -50,7 +66,7 @@ class TrainStep:
     """
 
     def __init__(self, pc, cam, capacity, bg=None, iteration=50_000, loss_fn=None, warmup=3, reducer=None,
-                 capture_collective=False, accumulate_into=None, split_forward=False):
+                 capture_collective=False, accumulate_into=None, split_forward=False, stats=None):
         """``reducer``: a ``parallel.FlatGradAllReduce`` over the same parameters.  The backward kernels then write
         the parameter gradients straight into its flat buffer (``_sinks``: no zero fill, no accumulation pass, no
         packing copies) and the step is captured as one CUDA graph per reducer bucket (up to three, see
@@ -59,18 +75,22 @@ class TrainStep:
         all-reduce into a single graph instead; EXPERIMENTAL -- with torch 2.11 / NCCL 2.28 on the B200 test box
         that capture hung, so it is off by default and not used by bench.py.
 
-        ``split_forward``: the deformation forward (neighbour search, keypoint MLP, blend) becomes a graph of its own in
-        front of the others.  It reads no SH coefficient, so ``_replay(wait_before_raster=...)`` can let the PREVIOUS
-        step's SH-gradient exchange (and the optimizer update that depends on it) run underneath it.
+        ``split_forward``: the deformation forward becomes two graphs of its own in front of the others, [neighbour
+        search + keypoint MLP] and [blend].  The first reads only xyz / keypoints / MLP weights, the second the other
+        per-Gaussian parameters and the blend logits, and neither reads an SH coefficient -- so
+        ``_replay(wait_before_blend=..., wait_before_raster=...)`` can let the PREVIOUS step's exchange of those
+        groups (and the optimizer updates that depend on it) run underneath them.
 
         ``accumulate_into``: a second ``FlatGradAllReduce`` with the same layout.  Every stage graph then ends with
         ``accumulate_into.bucket[k] += reducer.bucket[k]``: this step object serves samples 2.. of a gradient-
         accumulation step (``BatchStep``), the running sum lives in the other buffer and is what gets exchanged."""
         self._ctor = dict(pc=pc, cam=cam, bg=bg, iteration=iteration, loss_fn=loss_fn, warmup=warmup, reducer=reducer,
                           capture_collective=capture_collective, accumulate_into=accumulate_into,
-                          split_forward=split_forward)
+                          split_forward=split_forward, stats=stats)
+        self._stats = stats      # (loss_sum, radii, first): running loss sum / radii max of a BatchStep, updated in-graph
+        self.exchange_radii = False
         self.split_forward = bool(split_forward)
-        self.deferred = None
+        self.deferred_blend = self.deferred_raster = None
         self.pc = pc
         self.reducer = reducer
         self.accumulate_into = accumulate_into
@@ -121,6 +141,11 @@ class TrainStep:
             self.stage_graphs = []
             for k, fn in enumerate(self._stages):
                 g = self.graph if k == 0 else torch.cuda.CUDAGraph()
+                if k == 0 and getattr(self, "_n_pre", 0) == 2:
+                    g2 = torch.cuda.CUDAGraph()
+                    self._capture_split_at_blend(g, g2, fn)
+                    self.stage_graphs += [g, g2]
+                    continue
                 with torch.cuda.graph(g, **({} if k == 0 else dict(pool=self.graph.pool()))):
                     fn()
                 self.stage_graphs.append(g)
@@ -131,6 +156,36 @@ class TrainStep:
         self._state = _r.LAST_STATE          # workspaces of the captured frame (static addresses)
         self.grads = [p.grad for p in self.params]   # the tensors the graph writes; re-attached after every replay
         torch.cuda.synchronize(dev)
+
+    def _capture_split_at_blend(self, g_a, g_b, fn):
+        """Capture ``fn`` (the deformation forward) into TWO graphs cut right before the blend kernel: the neighbour search
+        and the keypoint MLP read only xyz / keypoints / MLP weights, the blend reads the other per-Gaussian parameters and
+        the blend logits -- so the exchange (and optimizer update) of those may still be running during the first graph."""
+        import gc
+        model = getattr(self.pc, "deformation", self.pc)
+        gc.collect()
+        torch.cuda.synchronize(self.dev)
+        cs = torch.cuda.Stream(device=self.dev)
+        cs.wait_stream(torch.cuda.current_stream(self.dev))
+        state = {"cut": False}
+
+        def hook():
+            g_a.capture_end()
+            g_b.capture_begin(pool=g_a.pool())
+            state["cut"] = True
+
+        with torch.cuda.stream(cs):
+            g_a.capture_begin()
+            model._pre_blend_hook = hook
+            try:
+                fn()
+            finally:
+                model._pre_blend_hook = None
+            (g_b if state["cut"] else g_a).capture_end()
+            if not state["cut"]:                  # a model without the hook: the second graph stays empty
+                g_b.capture_begin(pool=g_a.pool())
+                g_b.capture_end()
+        torch.cuda.current_stream(self.dev).wait_stream(cs)
 
     def overflowed(self):
         """(R, flag) of the last replay, read from the device header; if flag is set the frame was not rendered."""
@@ -183,6 +238,14 @@ class TrainStep:
 
         def stage0():
             forward("raster" if split else "all")
+            if self._stats is not None:           # the accumulation step's running sums, captured with the stage
+                loss_sum, radii, first = self._stats
+                if first:
+                    loss_sum.copy_(self.loss.detach())
+                    radii.copy_(self.pkg["radii"])
+                else:
+                    loss_sum.add_(self.loss.detach())
+                    torch.maximum(radii, self.pkg["radii"], out=radii)
             deformed = [t for t in self.pkg["deformed"] if t.requires_grad]
             if nb == 1:
                 self._grads_into([self.loss], None, self.params, viewspace=True)
@@ -206,7 +269,9 @@ class TrainStep:
                     self._grads_into(ts, gs, [p for p in self.params if id(p) not in done])
                 finish(1, True)
                 return
-            mine = leaves(1)
+            # leaves of the LAST bucket whose gradient is already produced here (e.g. xyz, when the caller put it there
+            # because the next step needs it first) are taken now; stage 2 asks only for what is still missing
+            mine = leaves(1) + leaves(2)
             outs = torch.autograd.grad(ts, cut + self._aliases_of(mine), grad_outputs=gs, allow_unused=True)
             self._cut2 = [(t, g) for t, g in zip(cut, outs[:len(cut)]) if g is not None]
             for p, g in zip(mine, outs[len(cut):]):
@@ -215,13 +280,13 @@ class TrainStep:
 
         def stage2():
             if self._cut2:
-                done = {id(p) for p in leaves(0) + leaves(1)}
+                done = {id(p) for p in leaves(0) + leaves(1)} | {id(p) for p in leaves(2) if p.grad is not None}
                 self._grads_into([t for t, _ in self._cut2], [g for _, g in self._cut2],
                                  [p for p in self.params if id(p) not in done])
             self._cut2 = None
             finish(2, True)
 
-        self._n_pre = 1 if split else 0
+        self._n_pre = 2 if split else 0          # [search + keypoint MLP | blend] in front of the rasterizer stages
         pre = [stage_pre] if split else []
         if nb == 1:
             return [stage0]
@@ -373,43 +438,81 @@ class TrainStep:
         s["free"].record(cur)
         return self._replay(exchange, **kw)
 
+    def step_packed(self, packed, target, exchange=None, **kw):
+        """Device-resident sample in the packed form of ``_StaticCamera`` (view 16 | proj 16 | centre 3 | time 1, float32
+        [36]): two copies into the static inputs instead of five."""
+        self.cam.packed.copy_(packed, non_blocking=True)
+        self.target.copy_(target, non_blocking=True)
+        return self._replay(exchange, **kw)
+
     def __call__(self, cam, t, target, non_blocking=True, exchange=None, **kw):
         self.cam.load(cam, non_blocking)
         self.t.copy_(t, non_blocking=non_blocking)
         self.target.copy_(target, non_blocking=non_blocking)
         return self._replay(exchange, **kw)
 
-    def _replay(self, exchange=None, wait_before_raster=None, defer_first=False):
+    def _replay(self, exchange=None, wait_before_blend=None, wait_before_raster=None, defer=False):
         """``exchange``: None = this step's own reducer (when it has one and a process group of more than one rank
         exists), False = no exchange (a sample in the middle of an accumulation step, or a single-rank run), or the
-        ``FlatGradAllReduce`` whose buckets are to be summed over the ranks (the accumulator of a ``BatchStep``)."""
+        ``FlatGradAllReduce`` whose buckets are to be summed over the ranks (the accumulator of a ``BatchStep``).
+
+        Pipelined exchange (``defer=True``, ``split_forward`` steps): only the LAST bucket (what the next step's
+        neighbour search and keypoint MLP read: xyz, keypoints, MLP weights) is joined before this call returns; the
+        per-Gaussian bucket is handed back in ``deferred_blend`` and the SH bucket in ``deferred_raster`` -- the next
+        step joins them through ``wait_before_blend`` / ``wait_before_raster``, right in front of their first reader.
+        Exchanges execute in issue order (one NCCL / side stream): last bucket, radii, per-Gaussian bucket, SH bucket
+        (optionally a head of the SH bucket first, ``EARLY_FRACTION``)."""
+        self.deferred_blend = self.deferred_raster = None
         if self.two_stage:
             import torch.distributed as dist
             if exchange is None:
                 exchange = self.reducer if (dist.is_available() and dist.is_initialized() and
                                             dist.get_world_size(self.reducer.group) > 1) else False
             npre = getattr(self, "_n_pre", 0)
-            for g in self.stage_graphs[:npre]:    # deformation forward: reads no SH coefficient
-                g.replay()
-            if wait_before_raster is not None:    # the previous step's SH exchange ran underneath it
+            _mark("begin")
+            if npre:
+                self.stage_graphs[0].replay()     # neighbour search + keypoint MLP
+                _mark("search + mlp done")
+                if wait_before_blend is not None:
+                    wait_before_blend.wait()
+                self.stage_graphs[1].replay()     # blend
+                _mark("blend done")
+            if wait_before_raster is not None:    # the previous step's SH exchange ran underneath all of that
                 wait_before_raster.wait()
+                _mark("joined previous SH")
             stages = self.stage_graphs[npre:]
             last = len(stages) - 1
-            self.deferred = None
             if exchange is False:
                 for g in stages:
                     g.replay()
             else:
                 buckets, works = exchange.buckets(), []
-                for k, g in enumerate(stages):
-                    g.replay()                    # stage k+1 runs while bucket k is on the wire
-                    for b in (buckets[k:] if k == last else buckets[k:k + 1]):
-                        works.append(exchange.all_reduce_bucket(b))
-                if defer_first and len(works) > 1:
-                    self.deferred, works = works[0], works[1:]    # bucket 0 (SH): joined by the NEXT step
+                pipelined = defer and len(stages) == 3 and len(buckets) == 3
+                if not pipelined:
+                    for k, g in enumerate(stages):
+                        g.replay()                # stage k+1 runs while bucket k is on the wire
+                        for b in (buckets[k:] if k == last else buckets[k:k + 1]):
+                            works.append(exchange.all_reduce_bucket(b))
+                else:
+                    sh = buckets[0]
+                    cut = int(sh.numel() * EARLY_FRACTION) // 4 * 4
+                    stages[0].replay()
+                    _mark("stage 0 done")
+                    if cut:
+                        works.append(exchange.all_reduce_bucket(sh[:cut]))
+                    stages[1].replay()
+                    _mark("stage 1 done")
+                    stages[2].replay()
+                    _mark("stage 2 done")
+                    works.append(exchange.all_reduce_bucket(buckets[2]))
+                    if self.exchange_radii:       # MAX of the radii: in front of the per-Gaussian bucket, joined with it
+                        exchange.all_reduce_max_aux()
+                    self.deferred_blend = exchange.all_reduce_bucket(buckets[1])
+                    self.deferred_raster = exchange.all_reduce_bucket(sh[cut:]) if cut < sh.numel() else self.deferred_blend
                 for w in works:
                     if w is not None:
                         w.wait()
+                _mark("joined exchanges")
         else:
             self.graph.replay()
         for p, g in zip(self.params, self.grads):     # p.grad may have been replaced / cleared by the caller
@@ -475,42 +578,43 @@ class BatchStep:
         self.world = dist.get_world_size(group) if (dist.is_available() and dist.is_initialized()) else 1
         self.group = group
         self.acc = make_reducer()
-        # Pipelined exchange (more than one rank): the SH bucket -- three quarters of the bytes -- is not joined at the end
-        # of the step but in front of the NEXT step's rasterizer, the first reader of the SH coefficients; it (and the
-        # optimizer update of that group) runs underneath the tail of this backward and the head of the next forward.
+        # Pipelined exchange (more than one rank): only the bucket the next step reads FIRST (xyz, keypoints, MLP weights)
+        # is joined at the end of a step.  The per-Gaussian bucket is joined in front of the next step's blend kernel and
+        # the SH bucket -- three quarters of the bytes -- in front of its rasterizer, their first readers: they (and the
+        # optimizer updates of those groups) run underneath the next step's neighbour search, MLP and blend.
         self.pipelined = self.world > 1 and os.environ.get("GP_PIPELINE_EXCHANGE", "1") != "0"
-        self._sh_pending = None
+        self._sh_pending = self._blend_pending = None
+        dev = next(pc.parameters()).device
+        self.dev = dev
+        self.loss_sum = torch.zeros((), device=dev)
+        P = int(pc.get_xyz.shape[0])
+        aux = getattr(self.acc, "aux", None)          # the reducer's own MAX-exchanged buffer, when it was given one
+        self._radii_in_acc = aux is not None and aux.numel() == P
+        self.radii = aux if self._radii_in_acc else torch.zeros(P, dtype=torch.int32, device=dev)   # max over samples (and ranks)
+        # the running loss sum and radii max are updated inside the captured stage 0 of every sample (TrainStep ``stats``)
         self.first = TrainStep(pc, cam, capacity, bg=bg, iteration=iteration, loss_fn=loss_fn, reducer=self.acc,
-                               split_forward=self.pipelined)
+                               split_forward=self.pipelined, stats=(self.loss_sum, self.radii, True))
         self.rest = None
         if self.n > 1:
             self.scratch = make_reducer()
             self.rest = TrainStep(pc, cam, capacity, bg=bg, iteration=iteration, loss_fn=loss_fn, reducer=self.scratch,
-                                  accumulate_into=self.acc)
-        dev = self.first.dev
-        self.dev = dev
-        self.loss_sum = torch.zeros((), device=dev)
-        P = int(pc.get_xyz.shape[0])
-        self.radii = torch.zeros(P, dtype=torch.int32, device=dev)      # max over the step's samples (and ranks)
+                                  accumulate_into=self.acc, stats=(self.loss_sum, self.radii, False))
+        # pipelined + the radii live in the reducer: their MAX exchange is issued inside the last sample's replay, in
+        # front of the per-Gaussian bucket, and is joined with it (next step, in front of the blend)
+        self._radii_inline = self.pipelined and self._radii_in_acc
+        (self.rest if self.rest is not None else self.first).exchange_radii = self._radii_inline
 
     def _steps(self):
         return [self.first] + [self.rest] * (self.n - 1)
 
-    def _after_sample(self, j, ts):
-        if j == 0:
-            self._join_radii()                # the previous step's MAX reduction owns self.radii until it is done
-            self.loss_sum.copy_(ts.loss.detach())
-            self.radii.copy_(ts.pkg["radii"])
-        else:
-            self.loss_sum.add_(ts.loss.detach())
-            torch.maximum(self.radii, ts.pkg["radii"], out=self.radii)
-
     def _finish(self):
-        if self.world > 1 and self.exchange:
+        _mark("finish")
+        if self.world > 1 and self.exchange and not self._radii_inline:
             import torch.distributed as dist
-            w = dist.all_reduce(self.radii, op=dist.ReduceOp.MAX, group=self.group, async_op=True)
+            w = self.acc.all_reduce_max_aux() if self._radii_in_acc else \
+                dist.all_reduce(self.radii, op=dist.ReduceOp.MAX, group=self.group, async_op=True)
             if self.pipelined:
-                self._radii_pending = w       # 4 B per Gaussian: joined by flush() / the next step, like the SH bucket
+                self._radii_pending = w       # 4 B per Gaussian: joined by flush() / the next step
             else:
                 w.wait()
         for p, v in zip(self.acc.params, self.acc.views):
@@ -526,20 +630,27 @@ class BatchStep:
         kw = {}
         if j == 0 and self._sh_pending is not None:
             kw["wait_before_raster"], self._sh_pending = self._sh_pending, None
+        if j == 0 and self._blend_pending is not None:
+            kw["wait_before_blend"], self._blend_pending = self._blend_pending, None
         if self.pipelined and self._exchange(j) is not False:
-            kw["defer_first"] = True
+            kw["defer"] = True
         return kw
 
     def _keep_deferred(self, ts):
-        if ts.deferred is not None:
-            self._sh_pending, ts.deferred = ts.deferred, None
+        if ts.deferred_raster is not None:
+            self._sh_pending, ts.deferred_raster = ts.deferred_raster, None
+        if ts.deferred_blend is not None:
+            self._blend_pending, ts.deferred_blend = ts.deferred_blend, None
 
     def flush(self):
-        """Join the SH-gradient exchange of the last step to the current stream (pipelined mode): call it before reading
-        those gradients, e.g. in front of the optimizer update of the SH group.  The next ``step()`` does it by itself."""
-        if self._sh_pending is not None:
-            self._sh_pending.wait()
-            self._sh_pending = None
+        """Join what the last step left on the wire (pipelined mode) to the current stream: call it before reading
+        those gradients (or the radii), e.g. in front of the optimizer update of the per-Gaussian and SH groups.  The
+        next ``step()`` joins them by itself, each in front of its first reader."""
+        for name in ("_blend_pending", "_sh_pending"):
+            w = getattr(self, name)
+            if w is not None:
+                w.wait()
+                setattr(self, name, None)
         self._join_radii()
 
     def _join_radii(self):
@@ -547,15 +658,27 @@ class BatchStep:
         if w is not None:
             w.wait()
 
+    def _before_first(self, ts):
+        # stage 0 of sample 0 overwrites the radii: a MAX exchange of the previous step that is still pending must be
+        # done (inline mode: it sits in front of the per-Gaussian bucket on the side stream, which is joined before the
+        # blend, i.e. before stage 0)
+        if not ts.split_forward:
+            self.flush()
+        else:
+            self._join_radii()
+
     def step(self, samples):
-        """``samples``: this rank's ``samples_per_rank`` tuples (camera, time [1], target [3,H,W]) of device tensors."""
+        """``samples``: this rank's ``samples_per_rank`` samples, device tensors: tuples (camera, time [1], target
+        [3,H,W]) or, cheaper, (packed camera + time [36], target) -- see ``TrainStep.step_packed``."""
         assert len(samples) == self.n
-        for j, (ts, (cam, t, target)) in enumerate(zip(self._steps(), samples)):
-            if j == 0 and not ts.split_forward:
-                self.flush()
-            ts(cam, t, target, exchange=self._exchange(j), **self._kw(j))
+        for j, (ts, sample) in enumerate(zip(self._steps(), samples)):
+            if j == 0:
+                self._before_first(ts)
+            if len(sample) == 2:
+                ts.step_packed(sample[0], sample[1], exchange=self._exchange(j), **self._kw(j))
+            else:
+                ts(sample[0], sample[1], sample[2], exchange=self._exchange(j), **self._kw(j))
             self._keep_deferred(ts)
-            self._after_sample(j, ts)
         return self._finish()
 
     def step_host(self, samples, next_first=None):
@@ -571,11 +694,10 @@ class BatchStep:
                 steps[j + 1].prefetch(*samples[j + 1])
             elif next_first is not None:
                 steps[0].prefetch(*next_first)
-            if j == 0 and not ts.split_forward:
-                self.flush()
+            if j == 0:
+                self._before_first(ts)
             ts.step_prefetched(exchange=self._exchange(j), **self._kw(j))
             self._keep_deferred(ts)
-            self._after_sample(j, ts)
         self._primed = next_first is not None
         return self._finish()
 

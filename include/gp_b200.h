@@ -303,11 +303,15 @@ int gp_densification_stats(int P, const float* viewspace_grad /*[P,3]*/, const i
  * this process (host array of `world` device addresses), multicast_base the NVSwitch multicast mapping of the same
  * allocation or NULL (then plain peer loads/stores are used).  The allocation also holds gp_allreduce_flag_bytes(blocks)
  * bytes of zero-initialised flags at `flags_byte_offset`; calls that may overlap in time must use different flag
- * regions.  Every rank must issue the same call (same sizes, same `blocks`, <= the number of co-resident CTAs).
+ * regions (calls issued one after the other on one stream may share one).  Every rank must issue the same call (same sizes, same `blocks`, <= the number of co-resident CTAs).
  * byte_offset, flags_byte_offset: multiples of 16; n_floats: multiple of 4; world <= 16. */
 size_t gp_allreduce_flag_bytes(int blocks);
 int gp_allreduce_sum_f32(int rank, int world, void* multicast_base, void* const* peer_bases, size_t byte_offset,
                          size_t n_floats, size_t flags_byte_offset, int blocks, gp_stream_t stream);
+/* Same protocol, element-wise MAX of int32: the radii of the step's samples ("radii = max", "visibility = or" =
+ * radii > 0, train.py:122-123).  byte_offset: multiple of 4. */
+int gp_allreduce_max_s32(int rank, int world, void* multicast_base, void* const* peer_bases, size_t byte_offset,
+                         size_t n_ints, size_t flags_byte_offset, int blocks, gp_stream_t stream);
 
 #ifdef __cplusplus
 }
