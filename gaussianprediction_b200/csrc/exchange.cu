@@ -54,16 +54,9 @@ __device__ __forceinline__ void gp_peer_barrier(const GpPeers& peers, size_t fla
   __syncthreads();
 }
 
+// This rank's slice of an n4 x 16-byte range: sum over the ranks, result to every rank.
 template <bool MULTICAST>
-__global__ void __launch_bounds__(GP_AR_THREADS)
-gp_allreduce_sum_kernel(GpPeers peers, char* mc_base, int rank, int world, size_t byte_off, size_t n4, size_t flags_off) {
-  __shared__ uint32_t s_epoch;
-  uint32_t* my_epoch = (uint32_t*)(peers.p[rank] + flags_off) + (size_t)blockIdx.x * GP_AR_FLAG_WORDS + GP_AR_MAX_WORLD;
-  if (threadIdx.x == 0) s_epoch = *my_epoch;
-  __syncthreads();
-  const uint32_t e = s_epoch;
-  gp_peer_barrier(peers, flags_off, rank, world, e + 1);
-
+__device__ __forceinline__ void gp_sum_slice(const GpPeers& peers, char* mc_base, int rank, int world, size_t byte_off, size_t n4) {
   const size_t per = (n4 + world - 1) / world;
   const size_t lo = min(n4, per * rank), hi = min(n4, lo + per);
   const size_t stride = (size_t)gridDim.x * GP_AR_THREADS;
@@ -109,21 +102,12 @@ gp_allreduce_sum_kernel(GpPeers peers, char* mc_base, int rank, int world, size_
       for (int q = 0; q < world; q++) *(float4*)(peers.p[q] + byte_off + i * 16) = acc;
     }
   }
-  gp_peer_barrier(peers, flags_off, rank, world, e + 2);
-  if (threadIdx.x == 0) *my_epoch = e + 2;
 }
 
 // Element-wise MAX of int32 (the radii of the step's samples: max over samples and ranks, train.py:122; visibility is
-// radii > 0).  Same protocol; 4-byte granules (the integer forms of multimem.ld_reduce are scalar).
+// radii > 0).  4-byte granules (the integer forms of multimem.ld_reduce are scalar).
 template <bool MULTICAST>
-__global__ void __launch_bounds__(GP_AR_THREADS)
-gp_allreduce_max_kernel(GpPeers peers, char* mc_base, int rank, int world, size_t byte_off, size_t n, size_t flags_off) {
-  __shared__ uint32_t s_epoch;
-  uint32_t* my_epoch = (uint32_t*)(peers.p[rank] + flags_off) + (size_t)blockIdx.x * GP_AR_FLAG_WORDS + GP_AR_MAX_WORLD;
-  if (threadIdx.x == 0) s_epoch = *my_epoch;
-  __syncthreads();
-  const uint32_t e = s_epoch;
-  gp_peer_barrier(peers, flags_off, rank, world, e + 1);
+__device__ __forceinline__ void gp_max_slice(const GpPeers& peers, char* mc_base, int rank, int world, size_t byte_off, size_t n) {
   const size_t per = (n + world - 1) / world;
   const size_t lo = min(n, per * rank), hi = min(n, lo + per);
   const size_t stride = (size_t)gridDim.x * GP_AR_THREADS;
@@ -142,8 +126,90 @@ gp_allreduce_max_kernel(GpPeers peers, char* mc_base, int rank, int world, size_
       for (int q = 0; q < world; q++) *(int*)(peers.p[q] + byte_off + i * 4) = m;
     }
   }
+}
+
+template <bool MULTICAST>
+__global__ void __launch_bounds__(GP_AR_THREADS)
+gp_allreduce_sum_kernel(GpPeers peers, char* mc_base, int rank, int world, size_t byte_off, size_t n4, size_t flags_off) {
+  __shared__ uint32_t s_epoch;
+  uint32_t* my_epoch = (uint32_t*)(peers.p[rank] + flags_off) + (size_t)blockIdx.x * GP_AR_FLAG_WORDS + GP_AR_MAX_WORLD;
+  if (threadIdx.x == 0) s_epoch = *my_epoch;
+  __syncthreads();
+  const uint32_t e = s_epoch;
+  gp_peer_barrier(peers, flags_off, rank, world, e + 1);
+  gp_sum_slice<MULTICAST>(peers, mc_base, rank, world, byte_off, n4);
   gp_peer_barrier(peers, flags_off, rank, world, e + 2);
   if (threadIdx.x == 0) *my_epoch = e + 2;
+}
+
+template <bool MULTICAST>
+__global__ void __launch_bounds__(GP_AR_THREADS)
+gp_allreduce_max_kernel(GpPeers peers, char* mc_base, int rank, int world, size_t byte_off, size_t n, size_t flags_off) {
+  __shared__ uint32_t s_epoch;
+  uint32_t* my_epoch = (uint32_t*)(peers.p[rank] + flags_off) + (size_t)blockIdx.x * GP_AR_FLAG_WORDS + GP_AR_MAX_WORLD;
+  if (threadIdx.x == 0) s_epoch = *my_epoch;
+  __syncthreads();
+  const uint32_t e = s_epoch;
+  gp_peer_barrier(peers, flags_off, rank, world, e + 1);
+  gp_max_slice<MULTICAST>(peers, mc_base, rank, world, byte_off, n);
+  gp_peer_barrier(peers, flags_off, rank, world, e + 2);
+  if (threadIdx.x == 0) *my_epoch = e + 2;
+}
+
+// Several ranges in ONE resident kernel.  A kernel launched while the GPU is full waits for free SM slots; kernels with
+// persistent blocks (the neighbour search) hold theirs for their whole run, so an exchange launched after them starts
+// late however its stream is prioritised.  This kernel is launched ONCE, when the last gradients of the step are final,
+// takes its few CTAs, and then works through the ranges in the order the next step needs them while that step's
+// kernels fill the rest of the machine.  After each range (all ranks have written it: one flag barrier per range) the
+// last CTA to finish publishes `call_id` in sync[GP_XS_MAX + s]; the consumer stream waits for that word with
+// gp_stream_wait_word just in front of the first reader.  sync[s] (s < GP_XS_MAX) are CTA counters (zero between calls).
+#define GP_XS_MAX 8
+struct GpSegments {
+  size_t byte_off[GP_XS_MAX];
+  size_t count[GP_XS_MAX];   // floats (sum, multiple of 4) or ints (max)
+  int op[GP_XS_MAX];         // 0: sum f32, 1: max s32
+  int n;
+};
+
+template <bool MULTICAST>
+__global__ void __launch_bounds__(GP_AR_THREADS)
+gp_exchange_segments_kernel(GpPeers peers, char* mc_base, int rank, int world, size_t flags_off, GpSegments segs,
+                            unsigned* sync, unsigned call_id) {
+  __shared__ uint32_t s_epoch;
+  uint32_t* my_epoch = (uint32_t*)(peers.p[rank] + flags_off) + (size_t)blockIdx.x * GP_AR_FLAG_WORDS + GP_AR_MAX_WORLD;
+  if (threadIdx.x == 0) s_epoch = *my_epoch;
+  __syncthreads();
+  const uint32_t e = s_epoch;
+  gp_peer_barrier(peers, flags_off, rank, world, e + 1);   // every rank's gradients are final (all ranges)
+  for (int s = 0; s < segs.n; s++) {
+    if (segs.op[s] == 0)
+      gp_sum_slice<MULTICAST>(peers, mc_base, rank, world, segs.byte_off[s], segs.count[s] / 4);
+    else
+      gp_max_slice<MULTICAST>(peers, mc_base, rank, world, segs.byte_off[s], segs.count[s]);
+    gp_peer_barrier(peers, flags_off, rank, world, e + 2 + s);   // every rank's slice of this range is written everywhere
+    if (threadIdx.x == 0) {
+      __threadfence();
+      if (atomicAdd(&sync[s], 1u) == gridDim.x - 1) {
+        sync[s] = 0u;
+        __threadfence();
+        asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(sync + GP_XS_MAX + s), "r"(call_id) : "memory");
+      }
+    }
+  }
+  if (threadIdx.x == 0) *my_epoch = e + 1 + segs.n;
+}
+
+// Stream-ordered wait for a word to reach a value (signed distance: ids only grow).  One thread; sleeps between polls;
+// gives up with a trap after ~1 minute instead of hanging the device if the producer never comes.
+__global__ void gp_wait_word_kernel(const unsigned* word, unsigned value) {
+  unsigned v;
+  unsigned long long polls = 0;
+  for (;;) {
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(word) : "memory");
+    if ((int)(v - value) >= 0) break;
+    __nanosleep(500);
+    if (++polls > (1ull << 27)) __trap();
+  }
 }
 
 extern "C" size_t gp_allreduce_flag_bytes(int blocks) {
@@ -189,6 +255,50 @@ extern "C" int gp_allreduce_max_s32(int rank, int world, void* multicast_base, v
     GP_KERNEL("gp_allreduce_max_kernel", stream, gp_allreduce_max_kernel<false><<<blocks, GP_AR_THREADS, 0, stream>>>(
         peers, nullptr, rank, world, byte_offset, n_ints, flags_byte_offset));
   }
+  GP_LAUNCH_CHECK();
+  return GP_OK;
+}
+
+extern "C" int gp_exchange_segments(int rank, int world, void* multicast_base, void* const* peer_bases,
+                                    size_t flags_byte_offset, int blocks, int n_segments, const size_t* byte_offsets,
+                                    const size_t* counts, const int* ops, unsigned* sync_words, unsigned call_id,
+                                    gp_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (world < 1 || world > GP_AR_MAX_WORLD || rank < 0 || rank >= world || !peer_bases || blocks < 1) return GP_ERR_BAD_ARG;
+  if (n_segments < 1 || n_segments > GP_XS_MAX || !byte_offsets || !counts || !ops || !sync_words) return GP_ERR_BAD_ARG;
+  if (flags_byte_offset & 15) return GP_ERR_BAD_ARG;
+  GpSegments segs;
+  segs.n = n_segments;
+  for (int s = 0; s < GP_XS_MAX; s++) {
+    segs.byte_off[s] = s < n_segments ? byte_offsets[s] : 0;
+    segs.count[s] = s < n_segments ? counts[s] : 0;
+    segs.op[s] = s < n_segments ? ops[s] : 0;
+    if (s < n_segments) {
+      if (ops[s] == 0 && ((byte_offsets[s] & 15) || (counts[s] & 3))) return GP_ERR_BAD_ARG;
+      if (ops[s] == 1 && (byte_offsets[s] & 3)) return GP_ERR_BAD_ARG;
+      if (ops[s] != 0 && ops[s] != 1) return GP_ERR_BAD_ARG;
+    }
+  }
+  GpPeers peers;
+  for (int q = 0; q < GP_AR_MAX_WORLD; q++) peers.p[q] = q < world ? (char*)peer_bases[q] : nullptr;
+  for (int q = 0; q < world; q++)
+    if (!peers.p[q]) return GP_ERR_BAD_ARG;
+  if (multicast_base) {
+    GP_KERNEL("gp_exchange_segments_kernel", stream, gp_exchange_segments_kernel<true><<<blocks, GP_AR_THREADS, 0, stream>>>(
+        peers, (char*)multicast_base, rank, world, flags_byte_offset, segs, sync_words, call_id));
+  } else {
+    GP_KERNEL("gp_exchange_segments_kernel", stream, gp_exchange_segments_kernel<false><<<blocks, GP_AR_THREADS, 0, stream>>>(
+        peers, nullptr, rank, world, flags_byte_offset, segs, sync_words, call_id));
+  }
+  GP_LAUNCH_CHECK();
+  return GP_OK;
+}
+
+extern "C" int gp_exchange_sync_words(void) { return 2 * GP_XS_MAX; }
+
+extern "C" int gp_stream_wait_word(const unsigned* word, unsigned value, gp_stream_t stream_) {
+  if (!word) return GP_ERR_BAD_ARG;
+  gp_wait_word_kernel<<<1, 1, 0, (cudaStream_t)stream_>>>(word, value);
   GP_LAUNCH_CHECK();
   return GP_OK;
 }

@@ -13,11 +13,14 @@
 // (diff = ref - query; acc = fma(diff, diff, acc), d = 0..D-1 in order), so the distances are
 // bit-identical and on tie-free inputs the indices are too.  Exact ties are broken by the smaller
 // keypoint index (the reference's tie order depends on an atomicAdd race).
+#include <atomic>
 #include "../../include/gp_b200.h"
 #include "common.cuh"
 #include "radix_sort.cuh"
 
 #define GP_KNN_THREADS 256
+#define GP_KNN_TICKET_SLOTS 64
+static __device__ unsigned gp_knn_tickets[2 * GP_KNN_TICKET_SLOTS];
 
 // Top-K in registers.  KT > 0: K is the compile-time constant KT (the repo's nearest_num <= 8 cases: every index is
 // static, nothing spills).  KT == 0: runtime K <= 32 with predicated indexing.
@@ -77,15 +80,35 @@ __global__ void __launch_bounds__(GP_KNN_THREADS, 2)
 gp_knn_kernel(int N, int Kp, int Drt, int K, const float* __restrict__ q_points, const float* __restrict__ q_feat,
               const float* __restrict__ r_points, const float* __restrict__ r_feat, int F, float amplify, float r2,
               int kp_chunk, const int* __restrict__ order, const int* hint, long long* __restrict__ idx64,
-              int* idx32, float* __restrict__ dists) {
+              int* idx32, float* __restrict__ dists, unsigned* ticket) {
   extern __shared__ __align__(16) float s_ref[];  // [kp_chunk][DP]
   constexpr int DD = D > 0 ? D : 1;
   const int Dn = D > 0 ? D : Drt;
   const int DP = (Dn + 3) & ~3;
-  const int n_groups = (N + GP_KNN_THREADS - 1) / GP_KNN_THREADS;
   const bool single_chunk = kp_chunk >= Kp;
-  for (int group = blockIdx.x; group < n_groups; group += gridDim.x) {
-  const int slot = group * GP_KNN_THREADS + threadIdx.x;
+  // Work is handed out by ticket, not by block index: a block or warp that starts late (the GPU shared with another
+  // resident kernel, or simply the last wave) takes fewer queries instead of leaving a tail.  Unit = 32 queries.  The
+  // first round of a block is block-wide (8 units, with the barriers the keypoint staging needs); after that, when the
+  // keypoints stay resident (one chunk), every WARP draws its own units and never waits for its neighbours again --
+  // pruning makes the cost of a unit very uneven.
+  __shared__ int s_unit;
+  const int n_units = (N + 31) / 32;
+  bool first_group = true;
+  for (;;) {
+  int unit;
+  if (first_group || !single_chunk) {
+    __syncthreads();
+    if (threadIdx.x == 0) s_unit = (int)atomicAdd(&ticket[0], (unsigned)(GP_KNN_THREADS / 32));
+    __syncthreads();
+    if (s_unit >= n_units) break;       // block-uniform
+    unit = s_unit + (threadIdx.x >> 5);
+  } else {
+    unsigned u = 0;
+    if ((threadIdx.x & 31) == 0) u = atomicAdd(&ticket[0], 1u);
+    unit = (int)__shfl_sync(0xffffffffu, u, 0);
+    if (unit >= n_units) break;         // warp-uniform
+  }
+  const int slot = unit * 32 + (threadIdx.x & 31);
   const bool valid = slot < N;
   // `order` (optional) is a permutation of the queries that puts spatial neighbours in the same warp, which makes
   // the warp-wide early exit below fire for most keypoints.  It only changes which thread serves which query.
@@ -127,7 +150,7 @@ gp_knn_kernel(int N, int Kp, int Drt, int K, const float* __restrict__ q_points,
     const int cnt = min(kp_chunk, Kp - base);
     // ---- stage the keypoints of this chunk (zero padded to DP floats per row); a block whose keypoints fit in one
     //      chunk stages them once and keeps them for all its query groups ----
-    const bool stage = !single_chunk || group == (int)blockIdx.x;
+    const bool stage = !single_chunk || first_group;
     if (stage) __syncthreads();
     if (!stage) {
     } else if (r_feat != nullptr) {
@@ -379,7 +402,17 @@ gp_knn_kernel(int N, int Kp, int Drt, int K, const float* __restrict__ q_points,
       }
     }
   }
+  first_group = false;
   }  // query groups
+  // the last block out re-arms the ticket pair for the next launch that uses it
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    if (atomicAdd(&ticket[1], 1u) == gridDim.x - 1) {
+      ticket[0] = 0u;
+      ticket[1] = 0u;
+    }
+  }
 }
 
 template <int D, int KT>
@@ -401,8 +434,21 @@ static int launch_knn(int N, int Kp, int Drt, int K, const float* q_points, cons
   // persistent grid: two blocks per SM (register-limited), each looping over groups of 256 queries
   const int n_groups = (N + GP_KNN_THREADS - 1) / GP_KNN_THREADS;
   const int grid = n_groups < 148 * 2 ? n_groups : 148 * 2;
+  // ticket pair (next group, blocks finished) of this launch: rotating slots, so that launches on different streams do
+  // not share one (64 in flight at most); a slot is zero whenever no launch is using it
+  static std::atomic<unsigned> next_slot{0};
+  static std::atomic<unsigned*> ticket_base[64];          // per device ordinal, resolved on the first launch there
+  int dev = 0;
+  GP_CUDA_TRY(cudaGetDevice(&dev));
+  unsigned* tickets = (dev >= 0 && dev < 64) ? ticket_base[dev].load(std::memory_order_acquire) : nullptr;
+  if (!tickets) {
+    GP_CUDA_TRY(cudaGetSymbolAddress((void**)&tickets, gp_knn_tickets));
+    if (dev >= 0 && dev < 64) ticket_base[dev].store(tickets, std::memory_order_release);
+  }
+  unsigned* ticket = tickets + 2 * (next_slot.fetch_add(1) % GP_KNN_TICKET_SLOTS);
   GP_KERNEL("gp_knn_kernel", stream, kern<<<grid, GP_KNN_THREADS, smem, stream>>>(
-      N, Kp, Drt, K, q_points, q_feat, r_points, r_feat, F, amplify, r2, kp_chunk, order, hint, idx64, idx32, dists));
+      N, Kp, Drt, K, q_points, q_feat, r_points, r_feat, F, amplify, r2, kp_chunk, order, hint, idx64, idx32, dists,
+      ticket));
   GP_LAUNCH_CHECK();
   return GP_OK;
 }

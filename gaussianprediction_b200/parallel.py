@@ -231,6 +231,40 @@ class NvlsFlatGradAllReduce(FlatGradAllReduce):
         from . import _lib
         return self._launch(_lib.lib().gp_allreduce_max_s32, "gp_allreduce_max_s32", self._aux_off, self._aux_n)
 
+    def exchange_segments(self, segments):
+        """``segments``: slices of ``flat`` (summed) and/or the string "aux" (the int32 side buffer, MAX), in the order
+        their readers come.  ONE resident kernel on the side stream works through them (csrc/exchange.cu,
+        gp_exchange_segments_kernel); returns one handle per segment whose ``wait()`` makes the current stream wait (a
+        one-thread kernel polling a device word) until that segment is complete on every rank."""
+        import ctypes
+        from . import _lib
+        from . import pipeline as _p
+        L = _lib.lib()
+        if not hasattr(self, "_sync"):
+            self._sync = torch.zeros(int(L.gp_exchange_sync_words()), dtype=torch.int32, device=self.flat.device)
+            self._call_id = 0
+        offs, counts, ops = [], [], []
+        for sgm in segments:
+            if isinstance(sgm, str):
+                offs.append(self._aux_off); counts.append(self._aux_n); ops.append(1)
+            else:
+                off = sgm.data_ptr() - self._symm.data_ptr()
+                assert off % 16 == 0 and sgm.numel() % 4 == 0 and 0 <= off and off + 4 * sgm.numel() <= self._aux_off
+                offs.append(off); counts.append(sgm.numel()); ops.append(0)
+        n = len(offs)
+        self._call_id += 1
+        cur = torch.cuda.current_stream(self.flat.device)
+        ready = torch.cuda.Event()
+        ready.record(cur)
+        self._side.wait_event(ready)
+        _p._mark(f"resident exchange ({n} ranges) start", self._side)
+        _lib.check(L.gp_exchange_segments(self._rank, self._world, self._mc, self._peers, self._flags_off, self.BLOCKS, n,
+                                          (ctypes.c_size_t * n)(*offs), (ctypes.c_size_t * n)(*counts), (ctypes.c_int * n)(*ops),
+                                          self._sync.data_ptr(), self._call_id, self._side.cuda_stream), "gp_exchange_segments")
+        _p._mark("resident exchange end", self._side)
+        half = self._sync.numel() // 2
+        return [_WordJoin(self._sync.data_ptr() + 4 * (half + k), self._call_id, self.flat.device) for k in range(n)]
+
     def reduce(self, async_op=False):
         self.pack()
         works = [self.all_reduce_bucket(b) for b in self.buckets()]
@@ -245,3 +279,15 @@ class _StreamJoin:
 
     def wait(self):
         torch.cuda.current_stream(self.device).wait_event(self.event)
+
+
+class _WordJoin:
+    """``wait()``: the current stream waits until a device word reaches ``value`` (gp_stream_wait_word)."""
+
+    def __init__(self, word_ptr, value, device):
+        self.word_ptr, self.value, self.device = word_ptr, value, device
+
+    def wait(self):
+        from . import _lib
+        _lib.check(_lib.lib().gp_stream_wait_word(self.word_ptr, self.value,
+                                                  torch.cuda.current_stream(self.device).cuda_stream), "gp_stream_wait_word")

@@ -25,6 +25,8 @@ from .renderer import render
 # blend backward the head runs at a third of its speed and delays the buckets the next step needs first
 EARLY_FRACTION = float(os.environ.get("GP_EXCHANGE_EARLY_FRACTION", "0"))
 
+RESIDENT_EXCHANGE = os.environ.get("GP_EXCHANGE_RESIDENT", "1") != "0"   # A/B knob (see TrainStep._replay)
+
 TRACE = None     # diagnostics (tools/timeline_probe.py): a list that receives (label, timing event, host time) marks
 
 
@@ -504,11 +506,21 @@ class TrainStep:
                     _mark("stage 1 done")
                     stages[2].replay()
                     _mark("stage 2 done")
-                    works.append(exchange.all_reduce_bucket(buckets[2]))
-                    if self.exchange_radii:       # MAX of the radii: in front of the per-Gaussian bucket, joined with it
-                        exchange.all_reduce_max_aux()
-                    self.deferred_blend = exchange.all_reduce_bucket(buckets[1])
-                    self.deferred_raster = exchange.all_reduce_bucket(sh[cut:]) if cut < sh.numel() else self.deferred_blend
+                    if hasattr(exchange, "exchange_segments") and RESIDENT_EXCHANGE:
+                        # one resident kernel: it takes its CTAs now, while the GPU is between steps, and is not locked
+                        # out by the persistent blocks of the next step's neighbour search
+                        segs = [buckets[2], buckets[1]] + (["aux"] if self.exchange_radii else []) + \
+                            ([sh[cut:]] if cut < sh.numel() else [])
+                        hs = exchange.exchange_segments(segs)
+                        works.append(hs[0])
+                        self.deferred_blend = hs[2] if self.exchange_radii else hs[1]
+                        self.deferred_raster = hs[-1]
+                    else:
+                        works.append(exchange.all_reduce_bucket(buckets[2]))
+                        if self.exchange_radii:   # MAX of the radii: in front of the per-Gaussian bucket, joined with it
+                            exchange.all_reduce_max_aux()
+                        self.deferred_blend = exchange.all_reduce_bucket(buckets[1])
+                        self.deferred_raster = exchange.all_reduce_bucket(sh[cut:]) if cut < sh.numel() else self.deferred_blend
                 for w in works:
                     if w is not None:
                         w.wait()

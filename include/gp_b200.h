@@ -312,6 +312,18 @@ int gp_allreduce_sum_f32(int rank, int world, void* multicast_base, void* const*
  * radii > 0, train.py:122-123).  byte_offset: multiple of 4. */
 int gp_allreduce_max_s32(int rank, int world, void* multicast_base, void* const* peer_bases, size_t byte_offset,
                          size_t n_ints, size_t flags_byte_offset, int blocks, gp_stream_t stream);
+/* Up to 8 ranges of the same allocation in ONE kernel that stays resident and works through them in order (ops[s]: 0 =
+ * sum of counts[s] floats, 1 = max of counts[s] int32).  Launched when the step's last gradients are final, it holds
+ * its few CTAs while the next step's kernels fill the rest of the GPU -- an exchange launched later would wait behind
+ * kernels with persistent blocks.  After range s is complete on every rank the kernel stores `call_id` (ids must grow
+ * from call to call) to sync_words[8 + s]; sync_words: gp_exchange_sync_words() zero-initialised device words owned by
+ * the caller.  gp_stream_wait_word makes `stream` wait (a one-thread kernel) until *word >= value: put it in front of
+ * the first reader of the range. */
+int gp_exchange_sync_words(void);
+int gp_exchange_segments(int rank, int world, void* multicast_base, void* const* peer_bases, size_t flags_byte_offset,
+                         int blocks, int n_segments, const size_t* byte_offsets, const size_t* counts, const int* ops,
+                         unsigned* sync_words, unsigned call_id, gp_stream_t stream);
+int gp_stream_wait_word(const unsigned* word, unsigned value, gp_stream_t stream);
 
 #ifdef __cplusplus
 }
