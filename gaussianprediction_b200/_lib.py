@@ -82,6 +82,7 @@ SIGNATURES = {
     "gp_exchange_segments": (c_int, [c_int, c_int, _P, POINTER(c_void_p), c_size_t, c_int, c_int, POINTER(c_size_t),
                                      POINTER(c_size_t), POINTER(c_int), _P, ctypes.c_uint, _P]),
     "gp_stream_wait_word": (c_int, [_P, ctypes.c_uint, _P]),
+    "gp_linear_forward": (c_int, [c_int, c_int, c_int, _P, c_int, _P, c_int, _P, _P, c_int, _P, c_int, _P]),
     "gp_raster_export_binning": (c_int, [POINTER(RasterCfg), _P, _P, c_longlong, _P, _P, _P]),
 }
 

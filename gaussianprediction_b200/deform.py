@@ -244,6 +244,20 @@ class _KeypointMLP(torch.autograd.Function):
         return (None, g_xyz, g_feat, None) + tuple(gw) + tuple(gb)
 
 
+_WARNED = set()
+
+
+def _warn_torch_mlp(df_model, x):
+    """There is no silent torch fallback: when the MLP cannot run on this library's kernels it says so (once per cause)."""
+    import warnings
+    why = "fused_mlp disabled / not a CUDA float32 [rows, dim] input" if (hasattr(df_model, "linears") and df_model.linears()) \
+        else "df_model is not a plain Linear/ReLU stack"
+    if why not in _WARNED:
+        _WARNED.add(why)
+        warnings.warn(f"gaussianprediction_b200: Deformable_Field runs through torch modules ({why}); "
+                      "this is off the accelerated path", RuntimeWarning, stacklevel=3)
+
+
 def keypoint_mlp_supported(df_model, feature_dim, xyz_freq, time_freq):
     """Shapes the fused kernels take (include/gp_b200.h, gp_kpmlp_*); anything else goes through the torch modules."""
     lin = df_model.linears() if hasattr(df_model, "linears") else None
@@ -265,6 +279,64 @@ def keypoint_mlp(df_model, kp_xyz, kp_feat, t, xyz_freq, time_freq, normalize_q=
     dims = (int(xyz_freq), int(time_freq), len(lin) - 1, lin[0].out_features, lin[-1].out_features, bool(normalize_q))
     out = _KeypointMLP.apply(dims, kp_xyz, kp_feat, t, *[l.weight for l in lin], *[l.bias for l in lin])
     return out if len(out) == 3 else (out[0], out[1], None)
+
+
+def _linear_tc(a, w, bias, relu, mask=None):
+    """act(a @ w.T + bias) [* (mask > 0)] through gp_linear_forward (tcgen05, error-compensated TF32)."""
+    M, K = int(a.shape[0]), int(a.shape[1])
+    n_out = int(w.shape[0])
+    out = torch.empty((M, n_out), dtype=torch.float32, device=a.device)
+    check(_lib.lib().gp_linear_forward(M, K, n_out, ptr(a), K, ptr(mask), n_out if mask is not None else 0, ptr(w),
+                                       ptr(bias), int(bool(relu)), ptr(out), n_out, _lib.stream_ptr()), "gp_linear_forward")
+    return out
+
+
+class _GaussianMLP(torch.autograd.Function):
+    """``Deformable_Field`` (d x (Linear + ReLU), Linear) over ALL rows of x -- the per-Gaussian MLP of the first stage
+    and of the step-opacity pass (scene/gaussian_model.py:240-244,265,291-298).  Forward and the data gradients run
+    layer by layer on the tensor cores (csrc/linear_tc.cu); the weight gradients dZ^T H are plain library GEMMs
+    (torch.mm) and the bias gradients column sums."""
+
+    @staticmethod
+    def forward(ctx, x, n_layers, *params):
+        weights, biases = [_c(w) for w in params[:n_layers]], [_c(b) for b in params[n_layers:]]
+        hs = [_c(x)]
+        for i, (w, b) in enumerate(zip(weights, biases)):
+            hs.append(_linear_tc(hs[-1], w, b, relu=i < n_layers - 1))
+        ctx.save_for_backward(*hs[:-1], *weights)
+        ctx.n_layers = n_layers
+        return hs[-1]
+
+    @staticmethod
+    def backward(ctx, g_out):
+        n = ctx.n_layers
+        saved = ctx.saved_tensors
+        hs, weights = saved[:n], saved[n:]
+        need = ctx.needs_input_grad
+        dz = _c(g_out)
+        gw, gb = [None] * n, [None] * n
+        gx = None
+        for i in range(n - 1, -1, -1):
+            if need[2 + i]:
+                gw[i] = dz.t().mm(hs[i])
+            if need[2 + n + i]:
+                gb[i] = dz.sum(0)
+            if i > 0:        # through the ReLU that produced hs[i]
+                dz = _linear_tc(dz, weights[i].t().contiguous(), None, relu=False, mask=hs[i])
+            elif need[0]:
+                gx = _linear_tc(dz, weights[0].t().contiguous(), None, relu=False)
+        return (gx, None) + tuple(gw) + tuple(gb)
+
+
+def gaussian_mlp_supported(df_model, x):
+    lin = df_model.linears() if hasattr(df_model, "linears") else None
+    return lin is not None and x.is_cuda and x.dtype == torch.float32 and x.dim() == 2 and \
+        all(l.bias is not None and l.out_features <= 256 and l.weight.dtype == torch.float32 and l.weight.is_cuda for l in lin)
+
+
+def gaussian_mlp(df_model, x):
+    lin = df_model.linears()
+    return _GaussianMLP.apply(x, len(lin), *[l.weight for l in lin], *[l.bias for l in lin])
 
 
 @torch.no_grad()
@@ -380,7 +452,12 @@ class KeypointDeformation(nn.Module):
 
     def get_motion_delta(self, xyz_embed, motion_feature, t):
         t = t.repeat((motion_feature.shape[0], 1))
-        delta = self.df_model(torch.cat([motion_feature, xyz_embed, t], dim=-1))
+        x = torch.cat([motion_feature, xyz_embed, t], dim=-1)
+        if self.fused_mlp and gaussian_mlp_supported(self.df_model, x):
+            delta = gaussian_mlp(self.df_model, x)           # tensor-core path (csrc/linear_tc.cu)
+        else:
+            _warn_torch_mlp(self.df_model, x)
+            delta = self.df_model(x)
         delta_o = delta[..., 7:8] if self.args.step_opacity else None
         return delta[..., 0:3], delta[..., 3:7], delta_o
 
@@ -421,6 +498,8 @@ class KeypointDeformation(nn.Module):
                                                      self.super_gaussians_feature, t_input, xf, tf,
                                                      normalize_q=args.norm_rotation)
             else:
+                # shapes outside the fused keypoint kernel's limits (include/gp_b200.h, gp_kpmlp_*): layer by layer
+                # through gp_linear_forward; only a model that is not a plain Linear/ReLU stack reaches torch (warned)
                 xyz_embed = positional_encoding(kp_in, xf)
                 delta_xyz, delta_q, _ = self.get_motion_delta(xyz_embed, self.super_gaussians_feature, t_embed())
                 if args.norm_rotation:

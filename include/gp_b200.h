@@ -295,6 +295,18 @@ int gp_densification_stats(int P, const float* viewspace_grad /*[P,3]*/, const i
                            float* xyz_gradient_accum_max /*[P,1]*/, gp_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------------
+ * Dense layer on the tensor cores: C[M,Nout] = act(A[M,K] W[Nout,K]^T + bias), fp32 in and out, error-compensated
+ * TF32 (three tcgen05.mma per K step, fp32 accumulation in tensor memory; ~1e-6 relative, csrc/linear_tc.cu).
+ * Stands in for the cuBLAS SGEMM + elementwise kernels behind the per-Gaussian `Deformable_Field` calls of
+ * GaussianModel.forward -- first-stage deformation (scene/gaussian_model.py:240-244,265) and step-opacity pass
+ * (:291-298; scene/deformable_field.py:112-127): [N,104] -> 4 x (Linear 256 + ReLU) -> Linear 8 over all N Gaussians.
+ * W is in nn.Linear layout.  relu != 0 applies max(0, .).  mask (optional, [M,Nout], leading dimension ldm) zeroes C
+ * where mask <= 0: with W passed transposed the same call is the backward of a layer through the ReLU below it,
+ * dZ_below = (dZ W) * [h > 0].  Nout <= 256; lda >= K, ldc >= Nout (elements). */
+int gp_linear_forward(int M, int K, int Nout, const float* A, int lda, const float* mask, int ldm, const float* W,
+                      const float* bias, int relu, float* C, int ldc, gp_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------
  * Gradient exchange of the data-parallel frame loop.  No reference counterpart: the reference is single-GPU; the
  * seam is its --batch accumulation (train.py:113-133), which SUMS the gradients of the step's samples.
  *
