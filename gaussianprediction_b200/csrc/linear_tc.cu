@@ -30,7 +30,7 @@
 
 #define GP_LT_THREADS 256
 #define GP_LT_ROWS 128
-#define GP_LT_KC 32                                    // K chunk per stage (floats)
+#define GP_LT_KC 16                                    // K chunk per stage (floats)
 #define GP_LT_SLABS (GP_LT_KC / 4)                      // 16-byte K slabs per chunk
 
 __device__ __forceinline__ uint32_t gp_lt_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -91,7 +91,7 @@ __device__ __forceinline__ void gp_lt_split(const float4 v, float4& hi, float4& 
 
 // NP = Nout padded to a multiple of 16 (UMMA N); TMEM columns = max(32, pow2 >= NP)
 template <int NP>
-__global__ void __launch_bounds__(GP_LT_THREADS, 1)
+__global__ void __launch_bounds__(GP_LT_THREADS, 2)
 gp_linear_tc_kernel(int M, int K, int Nout, const float* __restrict__ A, int lda, const float* __restrict__ mask, int ldm,
                     const float* __restrict__ W, const float* __restrict__ bias, int relu, float* __restrict__ C, int ldc) {
   constexpr int TMEM_COLS = NP <= 32 ? 32 : NP <= 64 ? 64 : NP <= 128 ? 128 : 256;
@@ -130,13 +130,16 @@ gp_linear_tc_kernel(int M, int K, int Nout, const float* __restrict__ A, int lda
   const bool vec_a = ((lda & 3) == 0) && ((((size_t)A) & 15) == 0);
   const bool vec_w = ((K & 3) == 0) && ((((size_t)W) & 15) == 0);
 
-  for (int c = 0; c < n_chunks; c++) {
-    const int s = c & 1;
-    if (c >= 2) gp_lt_mbar_wait(&bar_free[s], ((c >> 1) - 1) & 1);   // the MMAs of chunk c - 2 have read this stage
-    unsigned char* st = smem + (size_t)s * STAGE;
+  // Global loads of chunk c + 1 are issued (into registers) before the MMAs of chunk c are launched, so their latency
+  // hides behind the tensor-core work and the barrier wait; element e = r * 8 + j (row, 16-byte K slab), j fastest.
+  constexpr int A_IT = GP_LT_ROWS * GP_LT_SLABS / GP_LT_THREADS;   // 4
+  constexpr int W_IT = (NP * GP_LT_SLABS + GP_LT_THREADS - 1) / GP_LT_THREADS;
+  float4 ra[A_IT], rw[W_IT];
+  auto load_chunk = [&](int c) {
     const int k0 = c * GP_LT_KC;
-    // ---- A: 128 rows x 8 slabs; a thread takes (row, slab) pairs with the slab index fastest (coalesced rows) ----
-    for (int e = tid; e < GP_LT_ROWS * GP_LT_SLABS; e += GP_LT_THREADS) {
+#pragma unroll
+    for (int it = 0; it < A_IT; it++) {
+      const int e = tid + it * GP_LT_THREADS;
       const int r = e / GP_LT_SLABS, j = e % GP_LT_SLABS;
       const int gr = row0 + r, k = k0 + 4 * j;
       float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -149,13 +152,11 @@ gp_linear_tc_kernel(int M, int K, int Nout, const float* __restrict__ A, int lda
           v = make_float4(t[0], t[1], t[2], t[3]);
         }
       }
-      float4 hi, lo;
-      gp_lt_split(v, hi, lo);
-      *(float4*)(st + j * A_SLAB + r * 16) = hi;
-      *(float4*)(st + A_BYTES + j * A_SLAB + r * 16) = lo;
+      ra[it] = v;
     }
-    // ---- W: NP rows (output units) x 8 slabs ----
-    for (int e = tid; e < NP * GP_LT_SLABS; e += GP_LT_THREADS) {
+#pragma unroll
+    for (int it = 0; it < W_IT; it++) {
+      const int e = tid + it * GP_LT_THREADS;
       const int r = e / GP_LT_SLABS, j = e % GP_LT_SLABS;
       const int k = k0 + 4 * j;
       float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -168,11 +169,37 @@ gp_linear_tc_kernel(int M, int K, int Nout, const float* __restrict__ A, int lda
           v = make_float4(t[0], t[1], t[2], t[3]);
         }
       }
-      float4 hi, lo;
-      gp_lt_split(v, hi, lo);
-      *(float4*)(st + 2 * A_BYTES + j * B_SLAB + r * 16) = hi;
-      *(float4*)(st + 2 * A_BYTES + B_BYTES + j * B_SLAB + r * 16) = lo;
+      rw[it] = v;
     }
+  };
+  load_chunk(0);
+
+  for (int c = 0; c < n_chunks; c++) {
+    const int s = c & 1;
+    if (c >= 2) gp_lt_mbar_wait(&bar_free[s], ((c >> 1) - 1) & 1);   // the MMAs of chunk c - 2 have read this stage
+    unsigned char* st = smem + (size_t)s * STAGE;
+    const int k0 = c * GP_LT_KC;
+#pragma unroll
+    for (int it = 0; it < A_IT; it++) {
+      const int e = tid + it * GP_LT_THREADS;
+      const int r = e / GP_LT_SLABS, j = e % GP_LT_SLABS;
+      float4 hi, lo;
+      gp_lt_split(ra[it], hi, lo);
+      *(float4*)(st + j * A_SLAB + r * 16) = hi;
+      *(float4*)(st + A_BYTES + j * A_SLAB + r * 16) = lo;
+    }
+#pragma unroll
+    for (int it = 0; it < W_IT; it++) {
+      const int e = tid + it * GP_LT_THREADS;
+      const int r = e / GP_LT_SLABS, j = e % GP_LT_SLABS;
+      if (r < NP) {
+        float4 hi, lo;
+        gp_lt_split(rw[it], hi, lo);
+        *(float4*)(st + 2 * A_BYTES + j * B_SLAB + r * 16) = hi;
+        *(float4*)(st + 2 * A_BYTES + B_BYTES + j * B_SLAB + r * 16) = lo;
+      }
+    }
+    if (c + 1 < n_chunks) load_chunk(c + 1);
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy stores -> visible to the tensor core
     __syncthreads();
     if (tid == 0) {
