@@ -83,6 +83,9 @@ SIGNATURES = {
                                      POINTER(c_size_t), POINTER(c_int), _P, ctypes.c_uint, _P]),
     "gp_stream_wait_word": (c_int, [_P, ctypes.c_uint, _P]),
     "gp_linear_forward": (c_int, [c_int, c_int, c_int, _P, c_int, _P, c_int, _P, _P, c_int, _P, c_int, _P]),
+    "gp_hashgrid_entries": (c_longlong, [c_int, c_int, c_float, c_int]),
+    "gp_hashgrid_forward": (c_int, [c_int, c_int, c_int, c_float, c_int, _P, _P, _P, _P, _P]),
+    "gp_hashgrid_backward": (c_int, [c_int, c_int, c_int, c_float, c_int, _P, _P, _P, _P, _P]),
     "gp_raster_export_binning": (c_int, [POINTER(RasterCfg), _P, _P, c_longlong, _P, _P, _P]),
 }
 

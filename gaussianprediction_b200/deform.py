@@ -299,7 +299,8 @@ class _GaussianMLP(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x, n_layers, *params):
-        weights, biases = [_c(w) for w in params[:n_layers]], [_c(b) for b in params[n_layers:]]
+        weights = [_c(w) for w in params[:n_layers]]
+        biases = [None if b is None else _c(b) for b in params[n_layers:]]      # the hash-grid MLP has no biases
         hs = [_c(x)]
         for i, (w, b) in enumerate(zip(weights, biases)):
             hs.append(_linear_tc(hs[-1], w, b, relu=i < n_layers - 1))
@@ -319,7 +320,7 @@ class _GaussianMLP(torch.autograd.Function):
         for i in range(n - 1, -1, -1):
             if need[2 + i]:
                 gw[i] = dz.t().mm(hs[i])
-            if need[2 + n + i]:
+            if len(need) > 2 + n + i and need[2 + n + i]:
                 gb[i] = dz.sum(0)
             if i > 0:        # through the ReLU that produced hs[i]
                 dz = _linear_tc(dz, weights[i].t().contiguous(), None, relu=False, mask=hs[i])

@@ -295,6 +295,21 @@ int gp_densification_stats(int P, const float* viewspace_grad /*[P,3]*/, const i
                            float* xyz_gradient_accum_max /*[P,1]*/, gp_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------------
+ * Multiresolution hash-grid encoding of the blend-weight network.  Stands in for the encoding half of the tinycudann
+ * `NetworkWithInputEncoding` the reference builds at scene/gaussian_model.py:370-392 and calls every keypoint-stage
+ * frame at :257 (`weights_model(get_xyz.detach())`): Grid/Hash, linear interpolation; the reference's values are
+ * n_levels 16, base_resolution 16, per_level_scale exp(ln(2048/16)/15), log2_hashmap_size 19, 4 features per level
+ * (fixed here).  tinycudann is not part of the reference tree: this follows the published algorithm (parity unpinned,
+ * oracle/hashgrid_oracle.py).  table: float[entries][4], entries = gp_hashgrid_entries(...); enc: float[N][4 * n_levels];
+ * order: optional permutation of the points (e.g. gp_spatial_order) that only changes which thread serves which point.
+ * gp_hashgrid_backward ADDS dL/dtable into d_table (zero it first); the points get no gradient (the reference detaches). */
+long long gp_hashgrid_entries(int n_levels, int base_resolution, float per_level_scale, int log2_hashmap_size);
+int gp_hashgrid_forward(int N, int n_levels, int base_resolution, float per_level_scale, int log2_hashmap_size,
+                        const float* xyz, const int* order, const float* table, float* enc, gp_stream_t stream);
+int gp_hashgrid_backward(int N, int n_levels, int base_resolution, float per_level_scale, int log2_hashmap_size,
+                         const float* xyz, const int* order, const float* d_enc, float* d_table, gp_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------
  * Dense layer on the tensor cores: C[M,Nout] = act(A[M,K] W[Nout,K]^T + bias), fp32 in and out, error-compensated
  * TF32 (three tcgen05.mma per K step, fp32 accumulation in tensor memory; ~1e-6 relative, csrc/linear_tc.cu).
  * Stands in for the cuBLAS SGEMM + elementwise kernels behind the per-Gaussian `Deformable_Field` calls of

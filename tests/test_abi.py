@@ -119,3 +119,13 @@ def test_header_is_plain_c_and_struct_layouts_match_ctypes(tmp_path):
     assert rows[0] == [ctypes.sizeof(R), R.tanfovx.offset, R.sh_rest.offset, R.dL_dsh_rest.offset]
     assert rows[1] == [ctypes.sizeof(M), M.normalize_q.offset]
     assert rows[2] == [ctypes.sizeof(A), A.n.offset, A.lr.offset, A.step.offset]
+
+
+def test_hashgrid_level_table_matches_oracle(gplib):
+    """Host-side level geometry of the hash grid (entries per level: dense below 2^log2_T, aligned to 8) -- no GPU needed."""
+    import numpy as np
+    from oracle import hashgrid_oracle as ho
+    for log2_t in (12, 19):
+        _, total = ho.levels(log2_hashmap_size=log2_t)
+        assert gplib.gp_hashgrid_entries(16, 16, float(np.exp(np.log(2048 / 16) / 15)), log2_t) == total
+    assert gplib.gp_hashgrid_entries(0, 16, 1.5, 19) == -1
