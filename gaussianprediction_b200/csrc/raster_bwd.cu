@@ -369,12 +369,18 @@ gp_render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
   };
 
   const float tile_fx0 = (float)(tile_x * GP_TILE_X), tile_fy0 = (float)(tile_y * GP_TILE_Y);
+  // The per-Gaussian records of a batch are gathered from all over the geometry arrays (DRAM at 2 M Gaussians).  The
+  // list entry of batch i + 1 is read one batch ahead and its three records are prefetched into L2 while batch i is
+  // being processed, so the gather at the top of the next round is served by L2 instead of HBM.
+  int id_cur = (range.x + (unsigned)t < range.y) ? (int)point_list[range.y - t - 1] : -1;
   for (int i = 0; i < rounds; i++, toDo -= GP_TILE_PIX) {
     __syncthreads();
     const int progress = i * GP_TILE_PIX + t;
+    const int progress_next = progress + GP_TILE_PIX;
+    const int id_next = (range.x + (unsigned)progress_next < range.y) ? (int)point_list[range.y - progress_next - 1] : -1;
     unsigned pmask = 0u;
     if (range.x + progress < range.y) {
-      const int id = point_list[range.y - progress - 1];
+      const int id = id_cur;
       gp_sts32u(sb + GP_BW_ID + t * 4, (uint32_t)id);
       const float4 co = __ldg(conic_opacity + id);
       const float4 xyd = __ldg(xy_depth + id);
@@ -391,6 +397,12 @@ gp_render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
     }
     gp_sts32u(sb + GP_BW_MASK + t * 4, pmask);
     __syncthreads();
+    if (id_next >= 0) {
+      asm volatile("prefetch.global.L2 [%0];" ::"l"(conic_opacity + id_next));
+      asm volatile("prefetch.global.L2 [%0];" ::"l"(xy_depth + id_next));
+      if (colors_precomp == nullptr) asm volatile("prefetch.global.L2 [%0];" ::"l"(rgb4 + id_next));
+    }
+    id_cur = id_next;
 
     const int nb = min(GP_TILE_PIX, toDo);
     // list position (0-based, front to back) of batch element j is base - j

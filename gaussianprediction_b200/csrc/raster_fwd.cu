@@ -440,13 +440,17 @@ gp_render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
   int tid = -1;
 
   const float tile_fx0 = (float)(tile_x * GP_TILE_X), tile_fy0 = (float)(tile_y * GP_TILE_Y);
+  // list entries are read one batch ahead and the records of the next batch prefetched into L2 (see the backward kernel)
+  int id_cur = (range.x + (unsigned)t < range.y) ? (int)point_list[range.x + t] : -1;
   for (int i = 0; i < rounds; i++, toDo -= GP_TILE_PIX) {
     const int num_done = __syncthreads_count(done);
     if (num_done == GP_TILE_PIX) break;
     const int progress = i * GP_TILE_PIX + t;
+    const int progress_next = progress + GP_TILE_PIX;
+    const int id_next = (range.x + (unsigned)progress_next < range.y) ? (int)point_list[range.x + progress_next] : -1;
     unsigned pmask = 0u;
     if (range.x + progress < range.y) {
-      const int id = point_list[range.x + progress];
+      const int id = id_cur;
       gp_sts32u(sb + S_ID + t * 4, (uint32_t)id);
       const float4 co = __ldg(conic_opacity + id);
       const float4 xyd = __ldg(xy_depth + id);
@@ -463,6 +467,12 @@ gp_render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
     }
     gp_sts32u(sb + S_MASK + t * 4, pmask);
     __syncthreads();
+    if (id_next >= 0) {
+      asm volatile("prefetch.global.L2 [%0];" ::"l"(conic_opacity + id_next));
+      asm volatile("prefetch.global.L2 [%0];" ::"l"(xy_depth + id_next));
+      if (colors_precomp == nullptr) asm volatile("prefetch.global.L2 [%0];" ::"l"(rgb4 + id_next));
+    }
+    id_cur = id_next;
     const int nb = min(GP_TILE_PIX, toDo);
     for (int c0 = 0; c0 < nb; c0 += 32) {
       if (__all_sync(0xffffffffu, done)) break;
