@@ -48,7 +48,11 @@ __device__ __forceinline__ void gp_peer_barrier(const GpPeers& peers, size_t fla
     uint32_t* theirs = (uint32_t*)(peers.p[q] + flags_off) + (size_t)blockIdx.x * GP_AR_FLAG_WORDS + rank;
     gp_st_release_sys(theirs, epoch);
     const uint32_t* mine = (const uint32_t*)(peers.p[rank] + flags_off) + (size_t)blockIdx.x * GP_AR_FLAG_WORDS + q;
+    // bounded: a peer that never arrives (a rank that died, mismatched calls) ends in a trap after ~half a minute
+    // instead of a kernel that spins for ever
+    unsigned long long polls = 0;
     while ((int)(gp_ld_acquire_sys(mine) - epoch) < 0) {
+      if (++polls > (1ull << 26)) __trap();
     }
   }
   __syncthreads();

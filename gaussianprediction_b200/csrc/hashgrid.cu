@@ -17,9 +17,8 @@
 // Layout: the table is float4 per entry (F = 4), levels back to back (offsets in entries).  One WARP works on one level
 // of 32 consecutive points: with the points in Morton order (the same permutation the neighbour search uses) the 32
 // lanes touch neighbouring cells, so the coarse and middle levels are served by L1/L2.  Backward: each lane adds its
-// 8 weighted gradients with one red.global.add.v4.f32 per corner; lanes of a warp that hit the SAME entry (the common
-// case on coarse levels, where a whole warp sits in one cell) are merged first with __match_any_sync so that the
-// atomic unit sees one add instead of 32.
+// 8 weighted gradients with one red.global.add.v4.f32 per corner; when the whole warp hits the SAME entry (coarse levels,
+// Morton-ordered points) the 32 contributions are summed with a butterfly first and one lane adds.
 #include "../../include/gp_b200.h"
 #include "common.cuh"
 
@@ -123,21 +122,20 @@ gp_hashgrid_bwd_kernel(int N, const float* __restrict__ xyz, const int* __restri
       // merge the lanes that hit the same entry: the lowest lane of each group adds the group's sum
       const unsigned peers = __match_any_sync(0xffffffffu, idx);
       const int leader = __ffs(peers) - 1;
-      if (peers != (1u << lane)) {
-        // sum over the group in lane order (deterministic within the warp)
-        float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
-        unsigned m = peers;
-        while (m) {
-          const int src = __ffs(m) - 1;
-          m &= m - 1;
-          s.x += __shfl_sync(peers, v.x, src);
-          s.y += __shfl_sync(peers, v.y, src);
-          s.z += __shfl_sync(peers, v.z, src);
-          s.w += __shfl_sync(peers, v.w, src);
+      if (peers == 0xffffffffu) {
+        // the whole warp sits on one entry (coarse levels, Morton-ordered points): plain butterfly
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+          v.x += __shfl_xor_sync(0xffffffffu, v.x, o);
+          v.y += __shfl_xor_sync(0xffffffffu, v.y, o);
+          v.z += __shfl_xor_sync(0xffffffffu, v.z, o);
+          v.w += __shfl_xor_sync(0xffffffffu, v.w, o);
         }
-        v = s;
       }
-      if (valid && lane == leader)
+      // Partial groups are NOT merged: walking a group with shuffles costs more than the few extra atomics it saves
+      // (measured at 2 M points: 4.1 ms with the walk, see profiles/r2_hashgrid_bench.json).
+      const bool writer = (peers == 0xffffffffu) ? (lane == leader) : true;
+      if (valid && writer)
         asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(tl + 4 * (size_t)idx), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
     }
   }

@@ -106,7 +106,7 @@ gp_linear_tc_kernel(int M, int K, int Nout, const float* __restrict__ A, int lda
   __shared__ uint32_t s_tmem;
 
   const int tid = threadIdx.x, warp = tid >> 5;
-  const int row0 = blockIdx.x * GP_LT_ROWS;
+  const int n_tiles = (M + GP_LT_ROWS - 1) / GP_LT_ROWS;
 
   if (tid == 0) {
     gp_lt_mbar_init(&bar_free[0], 1);
@@ -135,7 +135,7 @@ gp_linear_tc_kernel(int M, int K, int Nout, const float* __restrict__ A, int lda
   constexpr int A_IT = GP_LT_ROWS * GP_LT_SLABS / GP_LT_THREADS;   // 4
   constexpr int W_IT = (NP * GP_LT_SLABS + GP_LT_THREADS - 1) / GP_LT_THREADS;
   float4 ra[A_IT], rw[W_IT];
-  auto load_chunk = [&](int c) {
+  auto load_chunk = [&](int row0, int c) {
     const int k0 = c * GP_LT_KC;
 #pragma unroll
     for (int it = 0; it < A_IT; it++) {
@@ -172,11 +172,16 @@ gp_linear_tc_kernel(int M, int K, int Nout, const float* __restrict__ A, int lda
       rw[it] = v;
     }
   };
-  load_chunk(0);
-
-  for (int c = 0; c < n_chunks; c++) {
-    const int s = c & 1;
-    if (c >= 2) gp_lt_mbar_wait(&bar_free[s], ((c >> 1) - 1) & 1);   // the MMAs of chunk c - 2 have read this stage
+  // Persistent: a CTA walks row tiles blockIdx.x, blockIdx.x + gridDim.x, ...; the TMEM columns, the barriers and their
+  // phases carry over (g counts the chunks this CTA has issued, over all its tiles), and the first chunk of the NEXT
+  // tile is already being loaded while this tile's accumulator is read back.
+  int g = 0, tiles_done = 0;
+  if ((int)blockIdx.x < n_tiles) load_chunk(blockIdx.x * GP_LT_ROWS, 0);
+  for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, tiles_done++) {
+  const int row0 = tile * GP_LT_ROWS;
+  for (int c = 0; c < n_chunks; c++, g++) {
+    const int s = g & 1;
+    if (g >= 2) gp_lt_mbar_wait(&bar_free[s], ((g >> 1) - 1) & 1);   // the MMAs of two chunks ago have read this stage
     unsigned char* st = smem + (size_t)s * STAGE;
     const int k0 = c * GP_LT_KC;
 #pragma unroll
@@ -199,7 +204,8 @@ gp_linear_tc_kernel(int M, int K, int Nout, const float* __restrict__ A, int lda
         *(float4*)(st + 2 * A_BYTES + B_BYTES + j * B_SLAB + r * 16) = lo;
       }
     }
-    if (c + 1 < n_chunks) load_chunk(c + 1);
+    if (c + 1 < n_chunks) load_chunk(row0, c + 1);
+    else if (tile + (int)gridDim.x < n_tiles) load_chunk((tile + gridDim.x) * GP_LT_ROWS, 0);
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy stores -> visible to the tensor core
     __syncthreads();
     if (tid == 0) {
@@ -219,7 +225,7 @@ gp_linear_tc_kernel(int M, int K, int Nout, const float* __restrict__ A, int lda
   }
 
   // ---- epilogue: warps 0..3 own TMEM lanes 32 w .. 32 w + 31 = rows of the tile ----
-  gp_lt_mbar_wait(&bar_done, 0);
+  gp_lt_mbar_wait(&bar_done, tiles_done & 1);
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   if (warp < 4) {
     const int r = row0 + warp * 32 + (tid & 31);
@@ -255,8 +261,11 @@ gp_linear_tc_kernel(int M, int K, int Nout, const float* __restrict__ A, int lda
       }
     }
   }
+  // the accumulator has been read: the next tile's first MMA (accumulate = 0) may overwrite it
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  }  // tiles
   if (warp == 0) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(TMEM_COLS) : "memory");
   }
@@ -269,7 +278,12 @@ static int gp_linear_launch(int M, int K, int Nout, const float* A, int lda, con
   const size_t smem = 2 * (2 * A_BYTES + 2 * B_BYTES);
   auto kern = gp_linear_tc_kernel<NP>;
   GP_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  GP_KERNEL("gp_linear_tc_kernel", stream, kern<<<(M + GP_LT_ROWS - 1) / GP_LT_ROWS, GP_LT_THREADS, smem, stream>>>(
+  const int n_tiles = (M + GP_LT_ROWS - 1) / GP_LT_ROWS;
+  int dev = 0, sms = 148;
+  GP_CUDA_TRY(cudaGetDevice(&dev));
+  GP_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  const int grid = n_tiles < 2 * sms ? n_tiles : 2 * sms;          // persistent: two CTAs per SM
+  GP_KERNEL("gp_linear_tc_kernel", stream, kern<<<grid, GP_LT_THREADS, smem, stream>>>(
       M, K, Nout, A, lda, mask, ldm, W, bias, relu, C, ldc));
   GP_LAUNCH_CHECK();
   return GP_OK;

@@ -32,3 +32,18 @@ for N in [int(a) for a in sys.argv[1:]] or [100_000, 1_000_000, 2_000_000]:
             (net(xyz) * cot).sum().backward()
         r[name] = dict(encode_ms=round(timeit(enc_f), 4), forward_ms=round(timeit(fwd), 4), fwd_bwd_ms=round(timeit(fb), 4))
     print(json.dumps(r))
+
+# per-kernel split of one forward + backward at the last N (library kernels only; torch.mm weight gradients are the rest)
+import ctypes
+from gaussianprediction_b200 import _lib
+L = _lib.lib()
+for name, order in (("index_order", None), ("morton_order", spatial_order(xyz))):
+    net.order = order
+    L.gp_profile_enable(1)
+    for _ in range(3):
+        for p in net.parameters(): p.grad = None
+        (net(xyz) * cot).sum().backward()
+    torch.cuda.synchronize()
+    buf = ctypes.create_string_buffer(1 << 14)
+    L.gp_profile_report(buf, len(buf)); L.gp_profile_enable(0)
+    print(name, {l.split()[0]: round(float(l.split()[2]) / 3, 3) for l in buf.value.decode().splitlines()})
