@@ -13,16 +13,17 @@
 //
 // i.e. three tcgen05.mma per K step, accumulated in fp32 in tensor memory.
 //
-// One CTA = one 128-row tile of C = act(A W^T + b):
+// A CTA walks 128-row tiles of C = act(A W^T + b) (persistent grid, two CTAs per SM):
 //   * A [M,K] row major and W [Nout,K] row major (nn.Linear layout) are both "K-major" operands.  K is walked in chunks
-//     of 32; all 256 threads load a chunk of A and W with 128-bit loads, split it into hi / lo and store it in the
+//     of 16; all 256 threads load a chunk of A and W with 128-bit loads, split it into hi / lo and store it in the
 //     canonical no-swizzle K-major core-matrix layout: 16-byte K slabs, inside a slab the rows are 16 bytes apart
 //     (8 rows = one 8 x 16 B core matrix), slab stride = rows * 16 + 16 bytes (the +16 spreads the slabs over the
 //     banks).  Descriptor: start, LBO = slab stride, SBO = 128 B, version 1, no swizzle.
-//   * two smem stages: while the tensor core works on chunk c the threads load chunk c + 1; `tcgen05.commit` to an
-//     mbarrier frees a stage.
+//   * two smem stages: while the tensor core works on chunk c the loads of chunk c + 1 are already in flight (registers);
+//     `tcgen05.commit` to an mbarrier frees a stage.  TMEM columns, barriers and their phases carry over from tile to
+//     tile, and the first chunk of the next tile is loaded while this tile's accumulator is read back.
 //   * the accumulator (128 lanes x Nout columns fp32) lives in TMEM; after the last chunk four warps read it back with
-//     tcgen05.ld (32 lanes x 32 columns per instruction), add the bias, apply ReLU and write C.
+//     tcgen05.ld (32 lanes x 16 columns per instruction), add the bias, apply ReLU and write C.
 // An optional mask [M,Nout] (the saved output of the ReLU below) zeroes C where mask <= 0: with W passed transposed the
 // same kernel is the backward of a layer, dZ_below = (dZ W) * [h > 0].
 #include "../../include/gp_b200.h"
