@@ -67,7 +67,7 @@ gp_render_bwd_butterfly_kernel(const uint2* __restrict__ ranges, const uint32_t*
                      const float4* __restrict__ conic_opacity, const float4* __restrict__ rgb4,
                      const float* __restrict__ colors_precomp, const float* __restrict__ final_Ts,
                      const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpixels,
-                     const int* __restrict__ hdr, float* __restrict__ grec) {
+                     const int* __restrict__ hdr, bool packed, float* __restrict__ grec) {
   __shared__ float4 s_co[GP_TILE_PIX];
   __shared__ float4 s_xyd[GP_TILE_PIX];
   __shared__ float4 s_rgb[GP_TILE_PIX];
@@ -118,7 +118,7 @@ gp_render_bwd_butterfly_kernel(const uint2* __restrict__ ranges, const uint32_t*
     const int progress = i * GP_TILE_PIX + t;
     unsigned pmask = 0u;
     if (range.x + progress < range.y) {
-      const int id = point_list[range.y - progress - 1];
+      const int id = (int)gp_list_id(point_list[range.y - progress - 1], packed);
       s_id[t] = id;
       const float4 co = __ldg(conic_opacity + id);
       const float4 xyd = __ldg(xy_depth + id);
@@ -258,17 +258,22 @@ gp_render_bwd_butterfly_kernel(const uint2* __restrict__ ranges, const uint32_t*
 // ------------------------------------------------------------------------------------------------
 #define GP_BW_SLOTS 16
 #define GP_BW_STRIDE 33
+#define GP_BW_BATCH 128
 // dynamic shared memory, byte offsets (explicit shared-space addressing: a generic pointer into dynamic shared memory
-// costs S2R CgaCtaId + LEA at every access, ~8 % of the round-1 kernel's instructions)
-#define GP_BW_CO 0
-#define GP_BW_XYD (GP_TILE_PIX * 16)
-#define GP_BW_RGB (2 * GP_TILE_PIX * 16)
-#define GP_BW_DPX (3 * GP_TILE_PIX * 16)
-#define GP_BW_ID (4 * GP_TILE_PIX * 16)
-#define GP_BW_MASK (GP_BW_ID + GP_TILE_PIX * 4)
-#define GP_BW_W (GP_BW_MASK + GP_TILE_PIX * 4)
+// costs S2R CgaCtaId + LEA at every access, ~8 % of the round-1 kernel's instructions).
+// Two batch buffers [co | x, y, id, - | rgb | mask] of 128 entries, the pixels' dL/dpixel, the warps' (Wg, U) slots
+// and the warps' slot tables (what phase 2 needs of each slot's Gaussian): 55,296 B, four blocks per SM.
+#define GP_BW_B_CO 0
+#define GP_BW_B_XYD (GP_BW_BATCH * 16)
+#define GP_BW_B_RGB (2 * GP_BW_BATCH * 16)
+#define GP_BW_B_MASK (3 * GP_BW_BATCH * 16)
+#define GP_BW_BUF (GP_BW_B_MASK + GP_BW_BATCH * 4)
+#define GP_BW_DPX (2 * GP_BW_BUF)
+#define GP_BW_W (GP_BW_DPX + GP_TILE_PIX * 16)
 #define GP_BW_WARP_BYTES (2 * GP_BW_SLOTS * GP_BW_STRIDE * 4)
-#define GP_BW_SMEM (GP_BW_W + 8 * GP_BW_WARP_BYTES)
+#define GP_BW_TAB (GP_BW_W + 8 * GP_BW_WARP_BYTES)
+#define GP_BW_TAB_BYTES (GP_BW_SLOTS * 32)
+#define GP_BW_SMEM (GP_BW_TAB + 8 * GP_BW_TAB_BYTES)
 
 __global__ void __launch_bounds__(GP_TILE_PIX, 4)
 gp_render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H,
@@ -276,8 +281,9 @@ gp_render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
                      const float4* __restrict__ conic_opacity, const float4* __restrict__ rgb4,
                      const float* __restrict__ colors_precomp, const float* __restrict__ final_Ts,
                      const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpixels,
-                     const int* __restrict__ hdr, float* __restrict__ grec) {
+                     const int* __restrict__ hdr, bool packed, float* __restrict__ grec) {
   extern __shared__ __align__(16) unsigned char s_raw[];
+  __shared__ unsigned s_last[8];
   const uint32_t sb = gp_smem_base(s_raw);
 
   if (hdr[GP_HDR_OVERFLOW]) return;
@@ -292,9 +298,6 @@ gp_render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
   const float pixfx = (float)px, pixfy = (float)py;
 
   const uint2 range = ranges[tile];
-  const int rounds = ((range.y - range.x + GP_TILE_PIX - 1) / GP_TILE_PIX);
-  int toDo = range.y - range.x;
-  const int total = toDo;
 
   const float T_final = inside ? final_Ts[pix_id] : 0.f;
   float T = T_final;
@@ -312,22 +315,40 @@ gp_render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
   unsigned warp_last = last_contributor;
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) warp_last = max(warp_last, __shfl_xor_sync(0xffffffffu, warp_last, o));
+  // Entries behind the last contributor of EVERY pixel of the tile are never visited: the walk (and the staging)
+  // starts at the tile's last contributor instead of the end of its list.
+  if (lane == 0) s_last[w] = warp_last;
+  __syncthreads();
+  unsigned block_last = 0u;
+#pragma unroll
+  for (int k = 0; k < 8; k++) block_last = max(block_last, s_last[k]);
+  const int total = (int)min(block_last, range.y - range.x);   // list positions 0 .. total-1 matter, walked back to front
+  const int rounds = (total + GP_BW_BATCH - 1) / GP_BW_BATCH;
+  int toDo = total;
+  const uint32_t* list_end = point_list + range.x + total;     // entry k (from the back) is list_end[-1 - k]
 
   // phase-2 identity of this lane
   const int slot = lane & (GP_BW_SLOTS - 1), half = lane >> 4;
   const uint32_t bufW = sb + GP_BW_W + w * GP_BW_WARP_BYTES;                       // [slot][33] Wg, then [slot][33] U
   const uint32_t rowW = bufW + (slot * GP_BW_STRIDE + half * 16) * 4;
   const uint32_t rowD = sb + GP_BW_DPX + (w * 32 + half * 16) * 16;
+  const uint32_t tab = sb + GP_BW_TAB + w * GP_BW_TAB_BYTES;                       // [slot] {conic, opacity | x, y, id, -}
+  // lanes 0-6 copy one word each of a visited Gaussian's record into the slot table (no divergent branch)
+  const uint32_t tsrc = lane < 4 ? GP_BW_B_CO + 4 * lane : GP_BW_B_XYD + 4 * (lane - 4);
+  uint32_t tw = tab + lane * 4;
+  const uint32_t tcopy = lane < 7 ? 1u : 0u;
   const float fx0 = (float)px0, fy0 = (float)(py0 + 2 * half);
   const float half_w = 0.5f * W, half_h = 0.5f * H;
   int nslots = 0;                    // warp-uniform
   uint32_t wr = bufW + lane * 4;     // where this lane's (Wg, U) of the next visit go
-  int myj = 0;                       // batch index of the Gaussian in this lane's slot
 
+  // Slots outlive the batch their Gaussian came from (its conic, centre and index are copied into the warp's slot
+  // table at the visit), so every splat pass but the last one of a tile runs with all 16 slots filled -- at 2 M
+  // Gaussians a warp meets only two or three Gaussians per batch.
   auto splat_pass = [&]() {
     __syncwarp();
-    const float4 xyd = gp_lds128(sb + GP_BW_XYD + myj * 16);
-    const float bx = xyd.x - fx0, by = xyd.y - fy0;
+    const uint4 tb = gp_lds128u(tab + slot * 32 + 16);
+    const float bx = __uint_as_float(tb.x) - fx0, by = __uint_as_float(tb.y) - fy0;
     float m0 = 0.f, mx = 0.f, my = 0.f, mxx = 0.f, mxy = 0.f, myy = 0.f, c0 = 0.f, c1 = 0.f, c2 = 0.f;
 #pragma unroll
     for (int i = 0; i < 16; i++) {
@@ -355,8 +376,8 @@ gp_render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
     c1 += __shfl_xor_sync(0xffffffffu, c1, 16);
     c2 += __shfl_xor_sync(0xffffffffu, c2, 16);
     if (half == 0 && slot < nslots) {
-      const float4 co = gp_lds128(sb + GP_BW_CO + myj * 16);
-      float* dst = grec + (size_t)gp_lds32u(sb + GP_BW_ID + myj * 4) * GP_GREC;
+      const float4 co = gp_lds128(tab + slot * 32);
+      float* dst = grec + (size_t)tb.z * GP_GREC;
       const float no = -co.w;
       red_add_v4(dst, no * (co.x * mx + co.y * my) * half_w, no * (co.z * my + co.y * mx) * half_h, 0.5f * no * mxx,
                  0.5f * no * mxy);
@@ -366,61 +387,65 @@ gp_render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
     __syncwarp();
     nslots = 0;
     wr = bufW + lane * 4;
+    tw = tab + lane * 4;
   };
 
-  const float tile_fx0 = (float)(tile_x * GP_TILE_X), tile_fy0 = (float)(tile_y * GP_TILE_Y);
-  // The per-Gaussian records of a batch are gathered from all over the geometry arrays (DRAM at 2 M Gaussians).  The
-  // list entry of batch i + 1 is read one batch ahead and its three records are prefetched into L2 while batch i is
-  // being processed, so the gather at the top of the next round is served by L2 instead of HBM.
-  int id_cur = (range.x + (unsigned)t < range.y) ? (int)point_list[range.y - t - 1] : -1;
-  for (int i = 0; i < rounds; i++, toDo -= GP_TILE_PIX) {
-    __syncthreads();
-    const int progress = i * GP_TILE_PIX + t;
-    const int progress_next = progress + GP_TILE_PIX;
-    const int id_next = (range.x + (unsigned)progress_next < range.y) ? (int)point_list[range.y - progress_next - 1] : -1;
-    unsigned pmask = 0u;
-    if (range.x + progress < range.y) {
-      const int id = id_cur;
-      gp_sts32u(sb + GP_BW_ID + t * 4, (uint32_t)id);
-      const float4 co = __ldg(conic_opacity + id);
-      const float4 xyd = __ldg(xy_depth + id);
-      gp_sts128(sb + GP_BW_CO + t * 16, co);
-      gp_sts128(sb + GP_BW_XYD + t * 16, xyd);
-      float4 col;
-      if (colors_precomp != nullptr)
-        col = make_float4(colors_precomp[3 * (size_t)id], colors_precomp[3 * (size_t)id + 1],
-                          colors_precomp[3 * (size_t)id + 2], 0.f);
-      else
-        col = __ldg(rgb4 + id);
-      gp_sts128(sb + GP_BW_RGB + t * 16, col);
-      pmask = gp_patch_mask(co, xyd.x, xyd.y, tile_fx0, tile_fy0);
+  // Staging, double-buffered: the 128 entries of a batch are copied by the 256 threads (threads 0-127: conic+opacity,
+  // centre, index, mask of entry t; threads 128-255: the colour of entry t-128) with cp.async, one batch AHEAD of the
+  // blend; the list entries themselves are read one batch earlier still.  One barrier per batch.  The depth is not
+  // needed here, so the index takes its place next to the centre.
+  const int e = t & (GP_BW_BATCH - 1);
+  const bool first_half = t < GP_BW_BATCH;
+  auto stage = [&](const uint32_t buf, const uint32_t v, const bool valid) {
+    if (valid) {
+      const uint32_t id = gp_list_id(v, packed);
+      if (first_half) {
+        gp_cp_async16(buf + GP_BW_B_CO + e * 16, conic_opacity + id);
+        gp_cp_async8(buf + GP_BW_B_XYD + e * 16, xy_depth + id);
+        gp_sts32u(buf + GP_BW_B_XYD + e * 16 + 8, id);
+      } else if (colors_precomp != nullptr) {
+        const float* c = colors_precomp + 3 * (size_t)id;
+        gp_cp_async4(buf + GP_BW_B_RGB + e * 16, c);
+        gp_cp_async4(buf + GP_BW_B_RGB + e * 16 + 4, c + 1);
+        gp_cp_async4(buf + GP_BW_B_RGB + e * 16 + 8, c + 2);
+      } else {
+        gp_cp_async16(buf + GP_BW_B_RGB + e * 16, rgb4 + id);
+      }
     }
-    gp_sts32u(sb + GP_BW_MASK + t * 4, pmask);
-    __syncthreads();
-    if (id_next >= 0) {
-      asm volatile("prefetch.global.L2 [%0];" ::"l"(conic_opacity + id_next));
-      asm volatile("prefetch.global.L2 [%0];" ::"l"(xy_depth + id_next));
-      if (colors_precomp == nullptr) asm volatile("prefetch.global.L2 [%0];" ::"l"(rgb4 + id_next));
-    }
-    id_cur = id_next;
+    if (first_half) gp_sts32u(buf + GP_BW_B_MASK + e * 4, valid ? gp_list_mask(v, packed) : 0u);
+    gp_cp_async_commit();
+  };
 
-    const int nb = min(GP_TILE_PIX, toDo);
+  uint32_t v_next = e < total ? list_end[-1 - e] : 0u;
+  stage(sb, v_next, e < total);
+  v_next = e + GP_BW_BATCH < total ? list_end[-1 - e - GP_BW_BATCH] : 0u;
+  for (int i = 0; i < rounds; i++, toDo -= GP_BW_BATCH) {
+    gp_cp_async_wait_all();
+    __syncthreads();   // batch i has landed for every thread, and nobody reads batch i - 1 any more
+    const uint32_t cur = sb + (uint32_t)(i & 1) * GP_BW_BUF;
+    if (i + 1 < rounds) {
+      const int k1 = (i + 1) * GP_BW_BATCH + e;
+      stage(sb + (uint32_t)((i + 1) & 1) * GP_BW_BUF, v_next, k1 < total);
+      v_next = k1 + GP_BW_BATCH < total ? list_end[-1 - k1 - GP_BW_BATCH] : 0u;
+    }
+
+    const int nb = min(GP_BW_BATCH, toDo);
     // list position (0-based, front to back) of batch element j is base - j
-    const int base = total - 1 - i * GP_TILE_PIX;
+    const int base = total - 1 - i * GP_BW_BATCH;
     // elements of this batch in front of index (total - warp_last) lie behind the last contributor of every pixel
     // of this warp: start at the first 32-chunk that can matter
-    const int first = total - (int)warp_last - i * GP_TILE_PIX;
+    const int first = total - (int)warp_last - i * GP_BW_BATCH;
     for (int c0 = max(first, 0) & ~31; c0 < nb; c0 += 32) {
-      unsigned bits = __ballot_sync(0xffffffffu, (gp_lds32u(sb + GP_BW_MASK + (c0 + lane) * 4) >> w) & 1u);
+      unsigned bits = __ballot_sync(0xffffffffu, (gp_lds32u(cur + GP_BW_B_MASK + (c0 + lane) * 4) >> w) & 1u);
       while (bits) {
         const int j = c0 + __ffs(bits) - 1;
         bits &= bits - 1;
         const uint32_t contributor = (uint32_t)(base - j);
         if (contributor >= warp_last) continue;  // warp-uniform: nobody in this warp reaches it
         bool active = inside && contributor < last_contributor;
-        const uint32_t aj = sb + j * 16;
-        const float4 xyd = gp_lds128(aj + GP_BW_XYD);
-        const float4 co = gp_lds128(aj + GP_BW_CO);
+        const uint32_t aj = cur + j * 16;
+        const float4 xyd = gp_lds128(aj + GP_BW_B_XYD);
+        const float4 co = gp_lds128(aj + GP_BW_B_CO);
         const float dx = xyd.x - pixfx;
         const float dy = xyd.y - pixfy;
         const float qa = __fmul_rn(co.x, dx);
@@ -444,7 +469,7 @@ gp_render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
         float inv1ma;
         asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv1ma) : "f"(1.f - alpha));
         const float Tn = T * inv1ma;
-        const float4 col = gp_lds128(aj + GP_BW_RGB);
+        const float4 col = gp_lds128(aj + GP_BW_B_RGB);
         const float cd = col.x * dpx0 + col.y * dpx1 + col.z * dpx2;
         const float dL_dalpha = Tn * cd - S * inv1ma;
         const float Un = alpha * Tn;
@@ -453,12 +478,14 @@ gp_render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
         gp_sts32(wr, active ? G * dL_dalpha : 0.f);
         gp_sts32(wr + GP_BW_SLOTS * GP_BW_STRIDE * 4, active ? Un : 0.f);
         wr += GP_BW_STRIDE * 4;
-        if (slot == nslots) myj = j;
+        // what phase 2 needs of this Gaussian (conic, opacity, centre, index) goes into the slot table
+        gp_copy_word_if(aj + tsrc, tw, tcopy);
+        tw += 32;
         if (++nslots == GP_BW_SLOTS) splat_pass();
       }
     }
-    if (nslots) splat_pass();   // the batch in shared memory is about to be replaced
   }
+  if (nslots) splat_pass();
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -836,7 +863,7 @@ extern "C" int gp_raster_backward(const gp_raster_cfg* cfg, const float* bg, con
   if (use_butterfly) {
     GP_KERNEL("gp_render_bwd_kernel", stream, gp_render_bwd_butterfly_kernel<<<gx * gy, GP_TILE_PIX, 0, stream>>>(
         im.ranges, point_list, W, H, gx, bg, g.xy_depth, g.conic_opacity, g.rgb, colors_precomp, im.final_T,
-        im.n_contrib, dL_dpix, g.hdr, grec));
+        im.n_contrib, dL_dpix, g.hdr, gp_list_packed(P), grec));
   } else {
     static bool attr_set[GP_STATIC_MAX_DEVICES_ATTR] = {};
     int dev = 0;
@@ -847,7 +874,7 @@ extern "C" int gp_raster_backward(const gp_raster_cfg* cfg, const float* bg, con
     }
     GP_KERNEL("gp_render_bwd_kernel", stream, gp_render_bwd_kernel<<<gx * gy, GP_TILE_PIX, GP_BW_SMEM, stream>>>(
         im.ranges, point_list, W, H, gx, bg, g.xy_depth, g.conic_opacity, g.rgb, colors_precomp, im.final_T,
-        im.n_contrib, dL_dpix, g.hdr, grec));
+        im.n_contrib, dL_dpix, g.hdr, gp_list_packed(P), grec));
   }
   GP_LAUNCH_CHECK();
   const float* cov3D_ptr = cov3D_precomp ? cov3D_precomp : g.cov3D;

@@ -25,21 +25,28 @@
 //   the divisions, square roots and the products below.  rho is itself computed from det_c, so a Gaussian whose
 //   rho_c exceeds 1e5 (relative bound 0.2: an extremely elongated, strongly rotated splat) is not culled at all.
 //   * centre +- half-extent minus the tile origin: three roundings at magnitude <= 2^13 px -> 0.002 px added.
-__device__ __forceinline__ unsigned gp_patch_mask(const float4 co, const float cx, const float cy, const float tile_x0,
-                                                  const float tile_y0) {
+// The box of one Gaussian (xlo, xhi, ylo, yhi in pixels) -- the part of the mask that does not depend on the tile.
+// "No culling" is the box of everything, "never visible" an empty box.
+__device__ __forceinline__ float4 gp_patch_extent(const float4 co, const float cx, const float cy) {
+  const float4 all = make_float4(-1e30f, 1e30f, -1e30f, 1e30f);
   const float o = co.w;
-  if (o < 1.0f / 255.0f) return 0u;  // alpha <= opacity < 1/255 everywhere (NaN opacity is not culled, like fminf)
+  if (o < 1.0f / 255.0f) return make_float4(1e30f, -1e30f, 1e30f, -1e30f);  // alpha <= opacity < 1/255 everywhere (NaN opacity is not culled, like fminf)
   const float a = co.x, b = co.y, c = co.z;
   const float det = a * c - b * b;
-  if (!(det > 0.f) || !(a > 0.f) || !(c > 0.f)) return 0xFFu;  // not a proper ellipse: no culling
+  if (!(det > 0.f) || !(a > 0.f) || !(c > 0.f)) return all;  // not a proper ellipse: no culling
   const float rho = (a * c + b * b) / det;
-  if (!(rho < 1e5f)) return 0xFFu;
+  if (!(rho < 1e5f)) return all;
   const float k = 2.0f * (logf(255.0f * o) + 1e-6f) / det * (1.0f + 1e-5f + 2e-6f * rho);
   const float hx = sqrtf(k * c) + 0.002f;
   const float hy = sqrtf(k * a) + 0.002f;
-  if (!(hx < 1e30f) || !(hy < 1e30f) || !(fabsf(cx) < 8192.f) || !(fabsf(cy) < 8192.f)) return 0xFFu;
-  const float xlo = cx - hx - tile_x0, xhi = cx + hx - tile_x0;  // relative to the tile origin
-  const float ylo = cy - hy - tile_y0, yhi = cy + hy - tile_y0;
+  if (!(hx < 1e30f) || !(hy < 1e30f) || !(fabsf(cx) < 8192.f) || !(fabsf(cy) < 8192.f)) return all;
+  return make_float4(cx - hx, cx + hx, cy - hy, cy + hy);
+}
+
+// Bit w of the result: does the box meet patch w = 2 * row + col of the tile with origin (tile_x0, tile_y0)?
+__device__ __forceinline__ unsigned gp_patch_mask_of(const float4 ext, const float tile_x0, const float tile_y0) {
+  const float xlo = ext.x - tile_x0, xhi = ext.y - tile_x0;  // relative to the tile origin
+  const float ylo = ext.z - tile_y0, yhi = ext.w - tile_y0;
   unsigned colm = 0u, rowm = 0u;
   if (xhi >= 0.f && xlo <= 7.f) colm |= 1u;
   if (xhi >= 8.f && xlo <= 15.f) colm |= 2u;
@@ -51,6 +58,11 @@ __device__ __forceinline__ unsigned gp_patch_mask(const float4 co, const float c
   for (int r = 0; r < 4; r++)
     if (rowm & (1u << r)) m |= colm << (2 * r);
   return m;
+}
+
+__device__ __forceinline__ unsigned gp_patch_mask(const float4 co, const float cx, const float cy, const float tile_x0,
+                                                  const float tile_y0) {
+  return gp_patch_mask_of(gp_patch_extent(co, cx, cy), tile_x0, tile_y0);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -77,6 +89,44 @@ __device__ __forceinline__ void gp_sts32u(uint32_t a, uint32_t v) { asm volatile
 __device__ __forceinline__ void gp_sts128(uint32_t a, float4 v) {
   asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(a), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
+
+__device__ __forceinline__ void gp_sts128u(uint32_t a, uint32_t x, uint32_t y, uint32_t z, uint32_t w) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(x), "r"(y), "r"(z), "r"(w) : "memory");
+}
+__device__ __forceinline__ uint4 gp_lds128u(uint32_t a) {
+  uint4 v;
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a));
+  return v;
+}
+
+// shared -> shared copy of one word by the lanes whose predicate holds (predicated, not branched)
+__device__ __forceinline__ void gp_copy_word_if(uint32_t src, uint32_t dst, uint32_t p) {
+  asm volatile("{\n\t.reg .pred q;\n\t.reg .b32 v;\n\tsetp.ne.u32 q, %2, 0;\n\t@q ld.shared.b32 v, [%0];\n\t@q st.shared.b32 [%1], v;\n\t}"
+               ::"r"(src), "r"(dst), "r"(p) : "memory");
+}
+
+// Asynchronous global -> shared copies (LDGSTS): the blend kernels stage the records of the NEXT batch of a tile's list
+// while the current one is being blended, so the gather latency (DRAM at 2 M Gaussians) is off the critical path.
+__device__ __forceinline__ void gp_cp_async16(uint32_t dst, const void* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void gp_cp_async8(uint32_t dst, const void* src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void gp_cp_async4(uint32_t dst, const void* src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void gp_cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void gp_cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+// Entries of the sorted instance list.  The patch mask of a (tile, Gaussian) pair depends only on the pair, so it is
+// computed ONCE, where the instance is emitted (gp_duplicate_kernel), and travels through the tile sort in the top
+// 8 bits of the 32-bit value next to the 24-bit Gaussian index.  Frames with more than 2^24 Gaussians keep plain
+// indices and every mask reads as 0xFF (no culling, same results).
+#define GP_LIST_ID_BITS 24
+__host__ __device__ __forceinline__ bool gp_list_packed(int P) { return P <= (1 << GP_LIST_ID_BITS); }
+__device__ __forceinline__ uint32_t gp_list_id(uint32_t v, bool packed) { return packed ? (v & ((1u << GP_LIST_ID_BITS) - 1u)) : v; }
+__device__ __forceinline__ uint32_t gp_list_mask(uint32_t v, bool packed) { return packed ? (v >> GP_LIST_ID_BITS) : 0xFFu; }
 
 __device__ __forceinline__ uint32_t gp_smem_base(const void* p) {
   uint32_t sb = (uint32_t)__cvta_generic_to_shared(p);

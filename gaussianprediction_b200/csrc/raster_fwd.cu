@@ -294,16 +294,19 @@ gp_block_sum_kernel(int P, const uint32_t* __restrict__ sorted_idx, const uint32
 // reference's per-Gaussian loop (rasterizer_impl.cu:98-109).
 __global__ void __launch_bounds__(GP_SCAN_BLOCK)
 gp_duplicate_kernel(int P, const uint32_t* __restrict__ sorted_idx, const uint32_t* __restrict__ tiles_touched,
-                    const float4* __restrict__ xy_depth, const int* __restrict__ radii,
-                    const uint32_t* __restrict__ block_excl, int* hdr, unsigned grid_x,
+                    const float4* __restrict__ xy_depth, const float4* __restrict__ conic_opacity,
+                    const int* __restrict__ radii, const uint32_t* __restrict__ block_excl, int* hdr, unsigned grid_x,
                     unsigned grid_y, uint32_t* __restrict__ tkeys, uint32_t* __restrict__ tvals, GpRadixTemp tile_radix,
                     int passes, long long capacity, uint2* __restrict__ ranges, int tiles) {
   __shared__ uint32_t s_hist[GP_RS_MAX_PASSES][GP_RS_RADIX];  // digit counts of the tile ids this block emits
   __shared__ uint32_t s_off[GP_SCAN_BLOCK + 1];  // exclusive offsets inside the block
   __shared__ uint32_t s_g[GP_SCAN_BLOCK];
   __shared__ uint32_t s_rx[GP_SCAN_BLOCK], s_ry[GP_SCAN_BLOCK], s_rw[GP_SCAN_BLOCK];
+  __shared__ float4 s_ext[GP_SCAN_BLOCK];  // 1/255-alpha boxes of the block's Gaussians: the patch mask of every emitted
+                                           // instance is computed here, once (raster_common.cuh)
   __shared__ uint32_t ws[GP_SCAN_BLOCK / 32];
   const int t = threadIdx.x, lane = t & 31, w = t >> 5;
+  const bool packed = gp_list_packed(P);
   // does the frame fit the binning buffers?  Every block decides for itself from R (no block reads the flag another
   // one writes); block 0 publishes the decision for the kernels that follow.  Tiles without instances keep range (0,0).
   const long long R = hdr[GP_HDR_NUM_RENDERED];
@@ -330,6 +333,7 @@ gp_duplicate_kernel(int P, const uint32_t* __restrict__ sorted_idx, const uint32
   if (tt) {
     const float4 xyd = xy_depth[gidx];
     tile_rect(xyd.x, xyd.y, radii[gidx], grid_x, grid_y, rmin, rmax);
+    if (packed) s_ext[t] = gp_patch_extent(conic_opacity[gidx], xyd.x, xyd.y);
   }
   s_g[t] = gidx;
   s_rx[t] = rmin.x;
@@ -364,7 +368,9 @@ gp_duplicate_kernel(int P, const uint32_t* __restrict__ sorted_idx, const uint32
     const uint32_t tx = s_rx[lo] + local % rw;
     const uint32_t key = ty * grid_x + tx;
     tkeys[base + e] = key;
-    tvals[base + e] = s_g[lo];
+    uint32_t val = s_g[lo];
+    if (packed) val |= gp_patch_mask_of(s_ext[lo], (float)(tx * GP_TILE_X), (float)(ty * GP_TILE_Y)) << GP_LIST_ID_BITS;
+    tvals[base + e] = val;
     for (int p = 0; p < passes; p++) atomicAdd(&s_hist[p][(key >> (8 * p)) & 0xFFu], 1u);
   }
   __syncthreads();
@@ -398,23 +404,31 @@ gp_tile_ranges_kernel(const int* __restrict__ hdr, const uint32_t* __restrict__ 
 // ------------------------------------------------------------------------------------------------
 
 // One 16x16 tile per block; warp w owns an 8x4 pixel patch (lane = 8*row + col) so that the 32
-// pixels of a warp are spatially compact.  Batches of 256 Gaussians are staged in shared memory:
-// conic+opacity, centre+depth, colour and index (52 B each).  The per-pair arithmetic is written
-// with explicit round-to-nearest intrinsics in the exact sequence the reference build executes
-// (forward.cu:341-379 as contracted by nvcc), because median depth / tidx / n_contrib are discrete
-// picks that flip on a 1-ulp change.
+// pixels of a warp are spatially compact.  Batches of 256 list entries are staged in shared memory:
+// conic+opacity, centre+depth, colour, index and patch mask (56 B each), in TWO buffers: while batch i is
+// blended, the records of batch i + 1 are already on their way (cp.async; the list entries themselves are read
+// one batch earlier still), so a round costs one barrier and no exposed gather latency -- at 2 M Gaussians a
+// warp finds only a few Gaussians of a batch on its patch, and the gather was ~40 % of the kernel's stall samples.
+// The per-pair arithmetic is written with explicit round-to-nearest intrinsics in the exact sequence the
+// reference build executes (forward.cu:341-379 as contracted by nvcc), because median depth / tidx / n_contrib
+// are discrete picks that flip on a 1-ulp change.
+#define GP_FW_CO 0
+#define GP_FW_XYD (GP_TILE_PIX * 16)
+#define GP_FW_RGB (2 * GP_TILE_PIX * 16)
+#define GP_FW_ID (3 * GP_TILE_PIX * 16)
+#define GP_FW_MASK (GP_FW_ID + GP_TILE_PIX * 4)
+#define GP_FW_BUF (GP_FW_MASK + GP_TILE_PIX * 4)
+
 __global__ void __launch_bounds__(GP_TILE_PIX)
 gp_render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H,
                      unsigned grid_x, const float4* __restrict__ xy_depth, const float4* __restrict__ conic_opacity,
                      const float4* __restrict__ rgb4, const float* __restrict__ colors_precomp,
-                     const float* __restrict__ bg_color, const int* __restrict__ hdr, float* __restrict__ final_T,
-                     uint32_t* __restrict__ n_contrib, float* __restrict__ out_color, float* __restrict__ out_depth,
-                     int* __restrict__ out_tidx) {
-  // one shared block addressed through an opaque 32-bit base (raster_common.cuh): [co | xyd | rgb | id | mask]
-  __shared__ __align__(16) unsigned char s_raw[GP_TILE_PIX * (3 * 16 + 2 * 4)];
+                     const float* __restrict__ bg_color, const int* __restrict__ hdr, bool packed,
+                     float* __restrict__ final_T, uint32_t* __restrict__ n_contrib, float* __restrict__ out_color,
+                     float* __restrict__ out_depth, int* __restrict__ out_tidx) {
+  // one shared block addressed through an opaque 32-bit base (raster_common.cuh): 2 x [co | xyd | rgb | id | mask]
+  __shared__ __align__(16) unsigned char s_raw[2 * GP_FW_BUF];
   const uint32_t sb = gp_smem_base(s_raw);
-  constexpr uint32_t S_CO = 0, S_XYD = GP_TILE_PIX * 16, S_RGB = 2 * GP_TILE_PIX * 16, S_ID = 3 * GP_TILE_PIX * 16,
-                     S_MASK = S_ID + GP_TILE_PIX * 4;
 
   const int t = threadIdx.x, w = t >> 5, lane = t & 31;
   const unsigned tile = blockIdx.x;
@@ -429,8 +443,9 @@ gp_render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
   // (background, depth sentinel, no Gaussian), so a caller that misses the overflow flag never reads stale memory.
   // Tile ranges are all (0,0) in that case (gp_duplicate_kernel), so the loop below simply does not run.
   const uint2 range = hdr[GP_HDR_OVERFLOW] ? make_uint2(0u, 0u) : ranges[tile];
-  const int rounds = ((range.y - range.x + GP_TILE_PIX - 1) / GP_TILE_PIX);
-  int toDo = range.y - range.x;
+  const unsigned n = range.y - range.x;
+  const int rounds = (int)((n + GP_TILE_PIX - 1) / GP_TILE_PIX);
+  int toDo = (int)n;
   bool done = !inside;
 
   float T = 1.0f;
@@ -439,51 +454,53 @@ gp_render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
   float Dm = 15.0f;  // median-depth sentinel of this fork (forward.cu:310)
   int tid = -1;
 
-  const float tile_fx0 = (float)(tile_x * GP_TILE_X), tile_fy0 = (float)(tile_y * GP_TILE_Y);
-  // list entries are read one batch ahead and the records of the next batch prefetched into L2 (see the backward kernel)
-  int id_cur = (range.x + (unsigned)t < range.y) ? (int)point_list[range.x + t] : -1;
+  // this thread's entry of a batch: records -> shared memory (asynchronously), index and patch mask beside them
+  auto stage = [&](const uint32_t buf, const uint32_t v, const bool valid) {
+    uint32_t m = 0u;
+    if (valid) {
+      const uint32_t id = gp_list_id(v, packed);
+      m = gp_list_mask(v, packed);
+      gp_cp_async16(buf + GP_FW_CO + t * 16, conic_opacity + id);
+      gp_cp_async16(buf + GP_FW_XYD + t * 16, xy_depth + id);
+      if (colors_precomp != nullptr) {
+        const float* c = colors_precomp + 3 * (size_t)id;
+        gp_cp_async4(buf + GP_FW_RGB + t * 16, c);
+        gp_cp_async4(buf + GP_FW_RGB + t * 16 + 4, c + 1);
+        gp_cp_async4(buf + GP_FW_RGB + t * 16 + 8, c + 2);
+      } else {
+        gp_cp_async16(buf + GP_FW_RGB + t * 16, rgb4 + id);
+      }
+      gp_sts32u(buf + GP_FW_ID + t * 4, id);
+    }
+    gp_sts32u(buf + GP_FW_MASK + t * 4, m);
+    gp_cp_async_commit();
+  };
+
+  uint32_t v_next = (unsigned)t < n ? point_list[range.x + t] : 0u;
+  stage(sb, v_next, (unsigned)t < n);
+  v_next = (unsigned)t + GP_TILE_PIX < n ? point_list[range.x + GP_TILE_PIX + t] : 0u;
   for (int i = 0; i < rounds; i++, toDo -= GP_TILE_PIX) {
+    gp_cp_async_wait_all();
+    // batch i is complete for every thread past this barrier, and nobody reads batch i - 1 any more
     const int num_done = __syncthreads_count(done);
     if (num_done == GP_TILE_PIX) break;
-    const int progress = i * GP_TILE_PIX + t;
-    const int progress_next = progress + GP_TILE_PIX;
-    const int id_next = (range.x + (unsigned)progress_next < range.y) ? (int)point_list[range.x + progress_next] : -1;
-    unsigned pmask = 0u;
-    if (range.x + progress < range.y) {
-      const int id = id_cur;
-      gp_sts32u(sb + S_ID + t * 4, (uint32_t)id);
-      const float4 co = __ldg(conic_opacity + id);
-      const float4 xyd = __ldg(xy_depth + id);
-      gp_sts128(sb + S_CO + t * 16, co);
-      gp_sts128(sb + S_XYD + t * 16, xyd);
-      float4 col;
-      if (colors_precomp != nullptr)
-        col = make_float4(colors_precomp[3 * (size_t)id], colors_precomp[3 * (size_t)id + 1],
-                          colors_precomp[3 * (size_t)id + 2], 0.f);
-      else
-        col = __ldg(rgb4 + id);
-      gp_sts128(sb + S_RGB + t * 16, col);
-      pmask = gp_patch_mask(co, xyd.x, xyd.y, tile_fx0, tile_fy0);
+    const uint32_t cur = sb + (uint32_t)(i & 1) * GP_FW_BUF;
+    if (i + 1 < rounds) {
+      const unsigned k1 = (unsigned)(i + 1) * GP_TILE_PIX + t;
+      stage(sb + (uint32_t)((i + 1) & 1) * GP_FW_BUF, v_next, k1 < n);
+      v_next = k1 + GP_TILE_PIX < n ? point_list[range.x + k1 + GP_TILE_PIX] : 0u;
     }
-    gp_sts32u(sb + S_MASK + t * 4, pmask);
-    __syncthreads();
-    if (id_next >= 0) {
-      asm volatile("prefetch.global.L2 [%0];" ::"l"(conic_opacity + id_next));
-      asm volatile("prefetch.global.L2 [%0];" ::"l"(xy_depth + id_next));
-      if (colors_precomp == nullptr) asm volatile("prefetch.global.L2 [%0];" ::"l"(rgb4 + id_next));
-    }
-    id_cur = id_next;
     const int nb = min(GP_TILE_PIX, toDo);
     for (int c0 = 0; c0 < nb; c0 += 32) {
       if (__all_sync(0xffffffffu, done)) break;
-      unsigned bits = __ballot_sync(0xffffffffu, (gp_lds32u(sb + S_MASK + (c0 + lane) * 4) >> w) & 1u);
+      unsigned bits = __ballot_sync(0xffffffffu, (gp_lds32u(cur + GP_FW_MASK + (c0 + lane) * 4) >> w) & 1u);
       while (bits) {
         const int j = c0 + __ffs(bits) - 1;
         bits &= bits - 1;
         if (done) continue;
-        const uint32_t aj = sb + j * 16;
-        const float4 xyd = gp_lds128(aj + S_XYD);
-        const float4 co = gp_lds128(aj + S_CO);
+        const uint32_t aj = cur + j * 16;
+        const float4 xyd = gp_lds128(aj + GP_FW_XYD);
+        const float4 co = gp_lds128(aj + GP_FW_CO);
         const float dx = xyd.x - pixfx;
         const float dy = xyd.y - pixfy;
         const float qa = __fmul_rn(co.x, dx);
@@ -499,19 +516,20 @@ gp_render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
           done = true;
           continue;
         }
-        const float4 col = gp_lds128(aj + S_RGB);
+        const float4 col = gp_lds128(aj + GP_FW_RGB);
         C0 = __fmaf_rn(T, __fmul_rn(alpha, col.x), C0);
         C1 = __fmaf_rn(T, __fmul_rn(alpha, col.y), C1);
         C2 = __fmaf_rn(T, __fmul_rn(alpha, col.z), C2);
         if (T > 0.5f && test_T < 0.5f) {
           Dm = xyd.z;
-          tid = (int)gp_lds32u(sb + S_ID + j * 4);
+          tid = (int)gp_lds32u(cur + GP_FW_ID + j * 4);
         }
         T = test_T;
         last_contributor = (uint32_t)(i * GP_TILE_PIX + j + 1);  // position in the tile list, 1-based
       }
     }
   }
+  gp_cp_async_wait_all();
   if (inside) {
     final_T[pix_id] = T;
     n_contrib[pix_id] = last_contributor;
@@ -617,7 +635,7 @@ extern "C" int gp_raster_render(const gp_raster_cfg* cfg, const float* bg, const
   const int bits = gp_tile_bits(W, H);
   b.radix.hist = g.tile_hist;        // counters of the tile sort live in the geometry workspace (zeroed by the
   b.radix.tickets = g.tile_tickets;  // preprocess stage); the status words are the binning workspace's own
-  GP_KERNEL("gp_duplicate_kernel", stream, gp_duplicate_kernel<<<nb, GP_SCAN_BLOCK, 0, stream>>>(P, g.dvals[0], g.tiles_touched, g.xy_depth, radii, g.block_sums,
+  GP_KERNEL("gp_duplicate_kernel", stream, gp_duplicate_kernel<<<nb, GP_SCAN_BLOCK, 0, stream>>>(P, g.dvals[0], g.tiles_touched, g.xy_depth, g.conic_opacity, radii, g.block_sums,
                                                         g.hdr, gx, gy, b.tkeys[0], b.tvals[0], b.radix, (bits + 7) / 8,
                                                         capacity, im.ranges, (int)(gx * gy)));
   GP_LAUNCH_CHECK();
@@ -628,7 +646,7 @@ extern "C" int gp_raster_render(const gp_raster_cfg* cfg, const float* bg, const
   GP_LAUNCH_CHECK();
   GP_KERNEL("gp_render_fwd_kernel", stream, gp_render_fwd_kernel<<<gx * gy, GP_TILE_PIX, 0, stream>>>(im.ranges, b.tvals[sel], W, H, gx, g.xy_depth,
                                                            g.conic_opacity, g.rgb, colors_precomp, bg, g.hdr,
-                                                           im.final_T, im.n_contrib, out_color, out_depth, out_tidx));
+                                                           gp_list_packed(P), im.final_T, im.n_contrib, out_color, out_depth, out_tidx));
   GP_LAUNCH_CHECK();
   return GP_OK;
 }
@@ -685,10 +703,10 @@ __global__ void gp_export_geom_kernel(int P, GpGeom g, float* depths,
 
 __global__ void gp_export_binning_kernel(const int* __restrict__ hdr, const uint32_t* __restrict__ tkeys,
                                          const uint32_t* __restrict__ tvals, const float4* __restrict__ xy_depth,
-                                         uint32_t* point_list, uint64_t* keys) {
+                                         uint32_t* point_list, uint64_t* keys, bool packed) {
   const int L = hdr[GP_HDR_NUM_SORTED];
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < L; i += gridDim.x * blockDim.x) {
-    const uint32_t gidx = tvals[i];
+    const uint32_t gidx = gp_list_id(tvals[i], packed);
     if (point_list) point_list[i] = gidx;
     if (keys) keys[i] = ((uint64_t)tkeys[i] << 32) | (uint64_t)__float_as_uint(xy_depth[gidx].z);
   }
@@ -725,7 +743,7 @@ extern "C" int gp_raster_export_binning(const gp_raster_cfg* cfg, const void* ge
   GpBinning b = gp_carve_binning(const_cast<void*>(binning_ws), capacity);
   const int sel = gp_tile_sort_sel(cfg->width, cfg->height);
   GP_KERNEL("gp_export_binning_kernel", stream, gp_export_binning_kernel<<<148 * 4, 256, 0, stream>>>(g.hdr, b.tkeys[sel], b.tvals[sel], g.xy_depth, point_list,
-                                                       point_list_keys));
+                                                       point_list_keys, gp_list_packed(cfg->P)));
   GP_LAUNCH_CHECK();
   return GP_OK;
 }
