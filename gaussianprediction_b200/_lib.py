@@ -20,7 +20,7 @@ class RasterCfg(ctypes.Structure):
     _fields_ = [
         ("P", c_int), ("width", c_int), ("height", c_int), ("sh_degree", c_int), ("sh_coeffs", c_int),
         ("tanfovx", c_float), ("tanfovy", c_float), ("scale_modifier", c_float), ("prefiltered", c_int),
-        ("sh_rest", c_void_p), ("dL_dsh_rest", c_void_p),
+        ("sh_rest", c_void_p), ("dL_dsh_rest", c_void_p), ("dL_dsh_accumulate", c_int),
     ]
 
 
@@ -64,6 +64,7 @@ SIGNATURES = {
     "gp_spatial_order": (c_int, [c_int, _P, _P, _P, _P]),
     "gp_blend_forward": (c_int, [c_int, c_int, c_int] + [_P] * 14),
     "gp_blend_backward": (c_int, [c_int, c_int, c_int] + [_P] * 20),
+    "gp_blend_backward_accumulate": (c_int, [c_int, c_int, c_int] + [_P] * 20),
     "gp_blend_dense_weights": (c_int, [c_int, c_int, c_int] + [_P] * 7),
     "gp_dist2_ws_bytes": (c_size_t, [c_int]),
     "gp_dist2_knn3": (c_int, [c_int, _P, _P, _P, _P]),

@@ -9,10 +9,16 @@ slice of the flat buffer -- and nothing is copied.  Parameters that get their gr
 miss the sink and are packed the usual way by the reducer.  A sink holds what ONE producer wrote: a parameter that feeds
 two of this package's Functions at once would have its sink overwritten rather than summed, which is why the only
 user, ``pipeline.TrainStep``, compares the result with a plain ``loss.backward()`` once before capturing anything.
+
+Accumulating sinks (``accumulate=`` of ``grad_sinks``): destinations the kernels ADD to instead of overwriting -- the
+running sum over the samples of a gradient-accumulation step (pipeline.BatchStep).  Only Functions whose kernels can add
+in place look them up (``acc_sink_for``: the rasterizer's SH gradients, the keypoint blend's per-Gaussian gradients);
+everything else keeps using the plain sink and is summed by the caller.
 """
 import contextlib
 
 _SINKS = {}
+_ACC_SINKS = {}
 
 
 def _key(t):
@@ -20,18 +26,19 @@ def _key(t):
 
 
 @contextlib.contextmanager
-def grad_sinks(pairs):
-    """``pairs``: iterable of (parameter, destination tensor of the same shape, contiguous float32)."""
-    global _SINKS
-    old = _SINKS
-    _SINKS = dict(old)
-    for p, dst in pairs:
-        assert dst.is_contiguous() and dst.shape == p.shape and dst.dtype == p.dtype
-        _SINKS[_key(p)] = dst
+def grad_sinks(pairs, accumulate=()):
+    """``pairs`` / ``accumulate``: iterables of (parameter, destination tensor of the same shape, contiguous float32)."""
+    global _SINKS, _ACC_SINKS
+    old, old_acc = _SINKS, _ACC_SINKS
+    _SINKS, _ACC_SINKS = dict(old), dict(old_acc)
+    for table, items in ((_SINKS, pairs), (_ACC_SINKS, accumulate)):
+        for p, dst in items:
+            assert dst.is_contiguous() and dst.shape == p.shape and dst.dtype == p.dtype
+            table[_key(p)] = dst
     try:
         yield
     finally:
-        _SINKS = old
+        _SINKS, _ACC_SINKS = old, old_acc
 
 
 def sink_for(t):
@@ -39,6 +46,13 @@ def sink_for(t):
     if not _SINKS or t is None or t.numel() == 0:
         return None
     return _SINKS.get(_key(t))
+
+
+def acc_sink_for(t):
+    """The accumulating destination registered for ``t`` (None if there is none)."""
+    if not _ACC_SINKS or t is None or t.numel() == 0:
+        return None
+    return _ACC_SINKS.get(_key(t))
 
 
 def out_like(sink, shape, **kw):

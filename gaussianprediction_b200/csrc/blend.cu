@@ -159,7 +159,10 @@ gp_blend_bwd_kernel(int N, int Kp, int Kr, const float* __restrict__ logits, con
                     const float* __restrict__ o_t, const float* __restrict__ g_xyz_t, const float* __restrict__ g_q_t,
                     const float* __restrict__ g_s_t, const float* __restrict__ g_o_t, float* __restrict__ g_logits,
                     float* __restrict__ g_xyz, float* __restrict__ g_rot, float* __restrict__ g_scaling,
-                    float* __restrict__ g_opacity, float* __restrict__ g_kp_dxyz, float* __restrict__ g_kp_dq) {
+                    float* __restrict__ g_opacity, float* __restrict__ g_kp_dxyz, float* __restrict__ g_kp_dq,
+                    const bool acc) {
+  // acc: the per-Gaussian outputs are ADDED to what the arrays hold (a running sum over the samples of a gradient-
+  // accumulation step: no scratch copy and no separate add pass); the keypoint outputs are always plain sums
   extern __shared__ __align__(16) float smem[];
   float* s_kp = smem;            // [Kp][8]
   float* s_g = smem + Kp * 8;    // [Kp][9] gradient accumulators (7 used; odd stride spreads the banks)
@@ -204,12 +207,20 @@ gp_blend_bwd_kernel(int N, int Kp, int Kr, const float* __restrict__ logits, con
     g2.y = -gm.x * q1.y + gm.y * q1.x + gm.z * q1.w - gm.w * q1.z;
     g2.z = -gm.x * q1.z - gm.y * q1.w + gm.z * q1.x + gm.w * q1.y;
     g2.w = -gm.x * q1.w + gm.y * q1.z - gm.z * q1.y + gm.w * q1.x;
-    if (g_rot) *(float4*)(g_rot + (size_t)i * 4) = g2;
+    if (g_rot) {
+      float4* o = (float4*)(g_rot + (size_t)i * 4);
+      if (acc) {
+        const float4 old = *o;
+        g2.x += old.x; g2.y += old.y; g2.z += old.z; g2.w += old.w;
+      }
+      *o = g2;
+    }
     const float4 gdq = normalize_bwd(dq, g1);   // w.r.t. the blended (un-normalised) delta quaternion
     const float gx = g_xyz_t ? g_xyz_t[(size_t)i * 3] : 0.f, gy = g_xyz_t ? g_xyz_t[(size_t)i * 3 + 1] : 0.f,
                 gz = g_xyz_t ? g_xyz_t[(size_t)i * 3 + 2] : 0.f;
     if (g_xyz) {
-      g_xyz[(size_t)i * 3] = gx; g_xyz[(size_t)i * 3 + 1] = gy; g_xyz[(size_t)i * 3 + 2] = gz;
+      float* o = g_xyz + (size_t)i * 3;
+      o[0] = acc ? o[0] + gx : gx; o[1] = acc ? o[1] + gy : gy; o[2] = acc ? o[2] + gz : gz;
     }
     // weights and keypoints
     float gwx[GP_BLEND_KMAX], gwr[GP_BLEND_KMAX];
@@ -235,26 +246,37 @@ gp_blend_bwd_kernel(int N, int Kp, int Kr, const float* __restrict__ logits, con
     }
     if (g_logits && VEC6) {
       float4* o4 = reinterpret_cast<float4*>(g_logits + (size_t)i * 12);
-      o4[0] = make_float4(wx[0] * (gwx[0] - sx), wx[1] * (gwx[1] - sx), wx[2] * (gwx[2] - sx), wx[3] * (gwx[3] - sx));
-      o4[1] = make_float4(wx[4] * (gwx[4] - sx), wx[5] * (gwx[5] - sx), wr[0] * (gwr[0] - sr), wr[1] * (gwr[1] - sr));
-      o4[2] = make_float4(wr[2] * (gwr[2] - sr), wr[3] * (gwr[3] - sr), wr[4] * (gwr[4] - sr), wr[5] * (gwr[5] - sr));
+      float4 a = make_float4(wx[0] * (gwx[0] - sx), wx[1] * (gwx[1] - sx), wx[2] * (gwx[2] - sx), wx[3] * (gwx[3] - sx));
+      float4 b = make_float4(wx[4] * (gwx[4] - sx), wx[5] * (gwx[5] - sx), wr[0] * (gwr[0] - sr), wr[1] * (gwr[1] - sr));
+      float4 c = make_float4(wr[2] * (gwr[2] - sr), wr[3] * (gwr[3] - sr), wr[4] * (gwr[4] - sr), wr[5] * (gwr[5] - sr));
+      if (acc) {
+        const float4 oa = o4[0], ob = o4[1], oc = o4[2];
+        a.x += oa.x; a.y += oa.y; a.z += oa.z; a.w += oa.w;
+        b.x += ob.x; b.y += ob.y; b.z += ob.z; b.w += ob.w;
+        c.x += oc.x; c.y += oc.y; c.z += oc.z; c.w += oc.w;
+      }
+      o4[0] = a; o4[1] = b; o4[2] = c;
     } else if (g_logits) {
 #pragma unroll
       for (int k = 0; k < GP_BLEND_KMAX; k++) {
         if (k < K) {
-          g_logits[(size_t)i * 2 * K + k] = wx[k] * (gwx[k] - sx);
-          g_logits[(size_t)i * 2 * K + K + k] = wr[k] * (gwr[k] - sr);
+          float* o = g_logits + (size_t)i * 2 * K;
+          o[k] = (acc ? o[k] : 0.f) + wx[k] * (gwx[k] - sx);
+          o[K + k] = (acc ? o[K + k] : 0.f) + wr[k] * (gwr[k] - sr);
         }
       }
     }
     if (g_scaling) {
 #pragma unroll
-      for (int c = 0; c < 3; c++)
-        g_scaling[(size_t)i * 3 + c] = g_s_t ? g_s_t[(size_t)i * 3 + c] * s_t[(size_t)i * 3 + c] : 0.f;
+      for (int c = 0; c < 3; c++) {
+        const float v = g_s_t ? g_s_t[(size_t)i * 3 + c] * s_t[(size_t)i * 3 + c] : 0.f;
+        g_scaling[(size_t)i * 3 + c] = acc ? g_scaling[(size_t)i * 3 + c] + v : v;
+      }
     }
     if (g_opacity) {
       const float o = o_t[i];
-      g_opacity[i] = g_o_t ? g_o_t[i] * o * (1.0f - o) : 0.f;
+      const float v = g_o_t ? g_o_t[i] * o * (1.0f - o) : 0.f;
+      g_opacity[i] = acc ? g_opacity[i] + v : v;
     }
   }
   __syncthreads();
@@ -327,11 +349,12 @@ extern "C" int gp_blend_forward(int N, int Kp, int K, const float* logits, const
   return GP_OK;
 }
 
-extern "C" int gp_blend_backward(int N, int Kp, int K, const float* logits, const int* idx32, const long long* idx64,
-                                 const float* kp_delta_xyz, const float* kp_delta_q, const float* rot, const float* s_t,
-                                 const float* o_t, const float* g_xyz_t, const float* g_q_t, const float* g_s_t,
-                                 const float* g_o_t, float* g_logits, float* g_xyz, float* g_rot, float* g_scaling,
-                                 float* g_opacity, float* g_kp_delta_xyz, float* g_kp_delta_q, gp_stream_t stream_) {
+static int blend_backward_impl(int N, int Kp, int K, const float* logits, const int* idx32, const long long* idx64,
+                               const float* kp_delta_xyz, const float* kp_delta_q, const float* rot, const float* s_t,
+                               const float* o_t, const float* g_xyz_t, const float* g_q_t, const float* g_s_t,
+                               const float* g_o_t, float* g_logits, float* g_xyz, float* g_rot, float* g_scaling,
+                               float* g_opacity, float* g_kp_delta_xyz, float* g_kp_delta_q, bool acc,
+                               gp_stream_t stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   int rc = blend_check(N, Kp, K);
   if (rc) return rc;
@@ -349,9 +372,30 @@ extern "C" int gp_blend_backward(int N, int Kp, int K, const float* logits, cons
     GP_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   GP_KERNEL("gp_blend_bwd_kernel", stream, kernel<<<gp_blend_grid(N, vec6 ? 4 : 2), GP_BLEND_THREADS, smem, stream>>>(
       N, Kp, K, logits, idx32, idx64, kp_delta_xyz, kp_delta_q, rot, s_t, o_t, g_xyz_t, g_q_t, g_s_t, g_o_t, g_logits,
-      g_xyz, g_rot, g_scaling, g_opacity, g_kp_delta_xyz, g_kp_delta_q));
+      g_xyz, g_rot, g_scaling, g_opacity, g_kp_delta_xyz, g_kp_delta_q, acc));
   GP_LAUNCH_CHECK();
   return GP_OK;
+}
+
+extern "C" int gp_blend_backward(int N, int Kp, int K, const float* logits, const int* idx32, const long long* idx64,
+                                 const float* kp_delta_xyz, const float* kp_delta_q, const float* rot, const float* s_t,
+                                 const float* o_t, const float* g_xyz_t, const float* g_q_t, const float* g_s_t,
+                                 const float* g_o_t, float* g_logits, float* g_xyz, float* g_rot, float* g_scaling,
+                                 float* g_opacity, float* g_kp_delta_xyz, float* g_kp_delta_q, gp_stream_t stream) {
+  return blend_backward_impl(N, Kp, K, logits, idx32, idx64, kp_delta_xyz, kp_delta_q, rot, s_t, o_t, g_xyz_t, g_q_t,
+                             g_s_t, g_o_t, g_logits, g_xyz, g_rot, g_scaling, g_opacity, g_kp_delta_xyz, g_kp_delta_q,
+                             false, stream);
+}
+
+extern "C" int gp_blend_backward_accumulate(int N, int Kp, int K, const float* logits, const int* idx32,
+                                            const long long* idx64, const float* kp_delta_xyz, const float* kp_delta_q,
+                                            const float* rot, const float* s_t, const float* o_t, const float* g_xyz_t,
+                                            const float* g_q_t, const float* g_s_t, const float* g_o_t, float* g_logits,
+                                            float* g_xyz, float* g_rot, float* g_scaling, float* g_opacity,
+                                            float* g_kp_delta_xyz, float* g_kp_delta_q, gp_stream_t stream) {
+  return blend_backward_impl(N, Kp, K, logits, idx32, idx64, kp_delta_xyz, kp_delta_q, rot, s_t, o_t, g_xyz_t, g_q_t,
+                             g_s_t, g_o_t, g_logits, g_xyz, g_rot, g_scaling, g_opacity, g_kp_delta_xyz, g_kp_delta_q,
+                             true, stream);
 }
 
 extern "C" int gp_blend_dense_weights(int N, int Kp, int K, const float* logits, const int* idx32,

@@ -787,7 +787,7 @@ gp_preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
                          float* __restrict__ dL_dopacity_out, float* __restrict__ dL_dmeans_out,
                          float* __restrict__ dL_dcov3D_out, float* __restrict__ dL_dsh_out,
                          float* __restrict__ dL_dsh_rest_out, float* __restrict__ dL_dscale_out,
-                         float* __restrict__ dL_drot_out, int staged) {
+                         float* __restrict__ dL_drot_out, int staged, int sh_accumulate) {
   extern __shared__ __align__(16) float s_tiles[];  // staged: [8 warps][GP_SH_TILE], coefficients in / gradients out IN PLACE
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
@@ -824,15 +824,27 @@ gp_preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
   if (staged && rows > 0) {
     __syncwarp();
     if (SPLIT) {
-      gp_warp_copy_out(dL_dsh_out + (size_t)warp_base * 3, tout, rows * 3, lane);
-      gp_warp_copy_out(dL_dsh_rest_out + (size_t)warp_base * 45, tout + GP_SH_SPLIT_REST, rows * 45, lane);
+      if (sh_accumulate) {   // running sum over the samples of a gradient-accumulation step (gp_b200.h)
+        gp_warp_add_out(dL_dsh_out + (size_t)warp_base * 3, tout, rows * 3, lane);
+        gp_warp_add_out(dL_dsh_rest_out + (size_t)warp_base * 45, tout + GP_SH_SPLIT_REST, rows * 45, lane);
+      } else {
+        gp_warp_copy_out(dL_dsh_out + (size_t)warp_base * 3, tout, rows * 3, lane);
+        gp_warp_copy_out(dL_dsh_rest_out + (size_t)warp_base * 45, tout + GP_SH_SPLIT_REST, rows * 45, lane);
+      }
     } else {
       float4* dst = (float4*)(dL_dsh_out + (size_t)warp_base * 48);
 #pragma unroll
       for (int it = 0; it < 12; it++) {
         const int i4 = it * 32 + lane;
         const int row = i4 / 12, c4 = i4 - row * 12;
-        if (row < rows) dst[i4] = *(const float4*)(tout + row * GP_SH_ROW + 4 * c4);
+        if (row < rows) {
+          float4 v = *(const float4*)(tout + row * GP_SH_ROW + 4 * c4);
+          if (sh_accumulate) {
+            const float4 o = dst[i4];
+            v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w;
+          }
+          dst[i4] = v;
+        }
       }
     }
   }
@@ -893,6 +905,7 @@ extern "C" int gp_raster_backward(const gp_raster_cfg* cfg, const float* bg, con
   const int staged = (shs != nullptr && cfg->sh_coeffs == 16 &&
                       ((((size_t)shs) | ((size_t)dL_dsh) | ((size_t)cfg->sh_rest) | ((size_t)cfg->dL_dsh_rest)) & 15) == 0) ? 1 : 0;
   if (cfg->sh_rest && (!staged || !cfg->dL_dsh_rest)) return GP_ERR_UNSUPPORTED;  // split SH storage (gp_b200.h)
+  if (cfg->dL_dsh_accumulate && !staged) return GP_ERR_UNSUPPORTED;               // only the staged rows are summed in place
   const size_t pb_smem = staged ? (size_t)8 * GP_SH_TILE * sizeof(float) : 0;
   auto kernel = cfg->sh_rest ? gp_preprocess_bwd_kernel<true> : gp_preprocess_bwd_kernel<false>;
   if (pb_smem > 48 * 1024)
@@ -901,7 +914,7 @@ extern "C" int gp_raster_backward(const gp_raster_cfg* cfg, const float* bg, con
       P, cfg->sh_degree, cfg->sh_coeffs, means3D, radii, shs, cfg->sh_rest, g.clamped, has_sr ? scales : nullptr,
       has_sr ? rotations : nullptr, cfg->scale_modifier, cov3D_ptr, viewmatrix, projmatrix, focal_x, focal_y,
       cfg->tanfovx, cfg->tanfovy, campos, grec, dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh,
-      cfg->dL_dsh_rest, dL_dscales, dL_drots, staged));
+      cfg->dL_dsh_rest, dL_dscales, dL_drots, staged, cfg->dL_dsh_accumulate));
   GP_LAUNCH_CHECK();
   return GP_OK;
 }

@@ -174,6 +174,19 @@ __device__ __forceinline__ void gp_warp_copy_in(float* dst_s, const float* __res
   for (int i = lane; i < n4; i += 32) reinterpret_cast<float4*>(dst_s)[i] = __ldg(reinterpret_cast<const float4*>(src) + i);
   for (int e = (n4 << 2) + lane; e < n; e += 32) dst_s[e] = __ldg(src + e);
 }
+// dst[0..n) += src_s[0..n) by one warp (same alignment rules as gp_warp_copy_out)
+__device__ __forceinline__ void gp_warp_add_out(float* __restrict__ dst, const float* src_s, int n, int lane) {
+  const int n4 = n >> 2;
+#pragma unroll 4
+  for (int i = lane; i < n4; i += 32) {
+    float4 v = reinterpret_cast<const float4*>(src_s)[i];
+    const float4 o = reinterpret_cast<float4*>(dst)[i];
+    v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w;
+    reinterpret_cast<float4*>(dst)[i] = v;
+  }
+  for (int e = (n4 << 2) + lane; e < n; e += 32) dst[e] += src_s[e];
+}
+
 __device__ __forceinline__ void gp_warp_copy_out(float* __restrict__ dst, const float* src_s, int n, int lane) {
   const int n4 = n >> 2;
 #pragma unroll 4

@@ -19,7 +19,7 @@ import torch.nn as nn
 
 from . import _lib
 from ._lib import check, ptr
-from ._sinks import out_like, sink_for
+from ._sinks import acc_sink_for, out_like, sink_for
 
 
 # ------------------------------------------------------------------------------------------------ small torch pieces
@@ -157,6 +157,7 @@ class _KeypointBlend(torch.autograd.Function):
         ctx.save_for_backward(logits_c, idx32, kpx, kpq, rot_c, s_t, o_t)
         ctx.dims = (N, Kp, K)
         ctx.sinks = [sink_for(t) for t in (logits, xyz, rot, scaling, opacity)]
+        ctx.acc_sinks = [acc_sink_for(t) for t in (logits, xyz, rot, scaling, opacity)]
         return xyz_t, q_t, s_t, o_t
 
     @staticmethod
@@ -167,6 +168,10 @@ class _KeypointBlend(torch.autograd.Function):
         f = dict(dtype=torch.float32, device=logits.device)
         need = ctx.needs_input_grad
         sk = ctx.sinks
+        # every per-Gaussian output has a running sum to add to: the kernel adds in place (gp_blend_backward_accumulate)
+        accumulate = all(need[i] and a is not None for i, a in zip((0, 4, 5, 6, 7), ctx.acc_sinks))
+        if accumulate:
+            sk = ctx.acc_sinks
         g_logits = out_like(sk[0], (N, 2 * K), **f) if need[0] else None
         g_kpx, g_kpq = torch.empty((Kp, 3), **f), torch.empty((Kp, 4), **f)
         g_xyz = out_like(sk[1], (N, 3), **f) if need[4] else None
@@ -174,10 +179,11 @@ class _KeypointBlend(torch.autograd.Function):
         g_sc = out_like(sk[3], (N, 3), **f) if need[6] else None
         g_op = out_like(sk[4], (N, 1), **f) if need[7] else None
         g_in = [None if g is None else _c(g) for g in (g_xyz_t, g_q_t, g_s_t, g_o_t)]   # kept alive until the launch
-        check(L.gp_blend_backward(N, Kp, K, ptr(logits), ptr(idx32), None, ptr(kpx), ptr(kpq), ptr(rot), ptr(s_t), ptr(o_t),
-                                  ptr(g_in[0]), ptr(g_in[1]), ptr(g_in[2]), ptr(g_in[3]), ptr(g_logits),
-                                  ptr(g_xyz), ptr(g_rot), ptr(g_sc), ptr(g_op), ptr(g_kpx), ptr(g_kpq),
-                                  _lib.stream_ptr()), "gp_blend_backward")
+        entry = L.gp_blend_backward_accumulate if accumulate else L.gp_blend_backward
+        check(entry(N, Kp, K, ptr(logits), ptr(idx32), None, ptr(kpx), ptr(kpq), ptr(rot), ptr(s_t), ptr(o_t),
+                    ptr(g_in[0]), ptr(g_in[1]), ptr(g_in[2]), ptr(g_in[3]), ptr(g_logits),
+                    ptr(g_xyz), ptr(g_rot), ptr(g_sc), ptr(g_op), ptr(g_kpx), ptr(g_kpq),
+                    _lib.stream_ptr()), "gp_blend_backward")
         return g_logits, None, (g_kpx if need[2] else None), (g_kpq if need[3] else None), g_xyz, g_rot, g_sc, g_op
 
 

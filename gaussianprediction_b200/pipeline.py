@@ -96,6 +96,8 @@ class TrainStep:
         self.pc = pc
         self.reducer = reducer
         self.accumulate_into = accumulate_into
+        # A/B knob: 0 = every gradient goes through the scratch buffer and one add per stage
+        self.accumulate_in_kernels = os.environ.get("GP_ACCUMULATE_IN_KERNELS", "1") != "0"
         if accumulate_into is not None:
             assert reducer is not None and accumulate_into.flat.shape == reducer.flat.shape and \
                 accumulate_into.bucket_ranges == reducer.bucket_ranges, "accumulate_into must mirror the reducer"
@@ -124,11 +126,13 @@ class TrainStep:
         self.max_stages = int(os.environ.get("GP_TRAINSTEP_STAGES", "3"))   # A/B knob: 2 merges the last two stages
         self._stages = self._stage_fns() if self.two_stage else None
         self._cut1 = self._cut2 = None
-        self.packed = 0
+        self.packed = self.in_place = 0
         side = torch.cuda.Stream(device=dev)
         side.wait_stream(torch.cuda.current_stream(dev))
         with torch.cuda.stream(side):
             for _ in range(max(warmup, 1)):       # also resolves lazy inits (cuBLAS handles, cached tables)
+                if accumulate_into is not None:   # the check below compares ONE sample's gradients
+                    accumulate_into.flat.zero_()
                 self._body()
             if self.two_stage:
                 self._verify_staging()
@@ -215,10 +219,29 @@ class TrainStep:
 
         def finish(k, last):
             lo, hi, e0, _ = r.bucket_ranges[k]
-            self.packed += r.pack(lo, len(r.params) if last else hi)
-            if self.accumulate_into is not None:      # running sum of the step's samples (captured with the stage)
-                e1 = r.flat.numel() if last else r.bucket_ranges[k][3]
-                self.accumulate_into.flat[e0:e1].add_(r.flat[e0:e1])
+            hi = len(r.params) if last else hi
+            acc = self.accumulate_into
+            if acc is None:
+                self.packed += r.pack(lo, hi)
+                return
+            # Running sum of the step's samples (captured with the stage).  Gradients a kernel has already ADDED to the
+            # sum (accumulating sinks) are done; the others are packed into the scratch buffer and added run by run.
+            runs = []
+            for i in range(lo, hi):
+                p, av = r.params[i], acc.views[i]
+                if p.grad is not None and p.grad.data_ptr() == av.data_ptr():
+                    p.grad = av
+                    self.in_place += 1
+                    continue
+                self.packed += r.pack(i, i + 1)
+                o0 = r.views[i].storage_offset() - r.flat.storage_offset()
+                o1 = o0 + r.views[i].numel()
+                if runs and runs[-1][1] >= o0 - 4:      # (alignment padding between two views is zero on both sides)
+                    runs[-1][1] = o1
+                else:
+                    runs.append([o0, o1])
+            for o0, o1 in runs:
+                acc.flat[o0:o1].add_(r.flat[o0:o1])
 
         split = self.split_forward and nb > 1
 
@@ -227,9 +250,12 @@ class TrainStep:
                 for p in self.params:
                     p.grad = None
                 self.packed = 0               # diagnostics: gradients that did NOT arrive through a sink
+                self.in_place = 0             # ... and gradients a kernel added to the running sum itself
                 if can_cut_mlp:
                     model.keep_kp_deltas = True
-            with grad_sinks(zip(r.params, r.views)):      # looked up while the autograd graph is being built
+            acc = self.accumulate_into
+            in_place = zip(r.params, acc.views) if (acc is not None and self.accumulate_in_kernels) else ()
+            with grad_sinks(zip(r.params, r.views), accumulate=in_place):   # looked up while the autograd graph is built
                 self._render_aliased(phase)
             if phase != "raster" and can_cut_mlp:
                 model.keep_kp_deltas = False

@@ -20,7 +20,7 @@ import torch
 import torch.nn as nn
 
 from . import _lib
-from ._sinks import out_like, sink_for
+from ._sinks import acc_sink_for, out_like, sink_for
 from ._lib import RasterCfg, check, ptr
 
 
@@ -136,7 +136,7 @@ def raster_forward(means3D, sh, colors_precomp, opacities, scales, rotations, co
 
 
 def raster_backward(st, grad_out_color, means3D, sh, colors_precomp, scales, rotations, cov3Ds_precomp,
-                    raster_settings, sh_rest=None, sinks=(None, None)):
+                    raster_settings, sh_rest=None, sinks=(None, None), sh_accumulate=False):
     """Returns (grad_means2D, grad_colors, grad_opacity, grad_means3D, grad_cov3D, grad_sh, grad_scales, grad_rots);
     with split SH storage grad_sh is the pair (grad_sh_dc [P,1,3], grad_sh_rest [P,15,3])."""
     L = _lib.lib()
@@ -165,6 +165,9 @@ def raster_backward(st, grad_out_color, means3D, sh, colors_precomp, scales, rot
         g_sh_rest = out_like(sinks[1], (P, int(sh_rest.shape[1]), 3), **f)
         cfg = RasterCfg.from_buffer_copy(st.cfg)
         cfg.sh_rest, cfg.dL_dsh_rest = ptr(sh_rest), ptr(g_sh_rest)
+    if sh_accumulate:      # ``sinks`` hold a running sum: the kernel adds the SH gradients to it (gp_b200.h)
+        cfg = RasterCfg.from_buffer_copy(cfg)
+        cfg.dL_dsh_accumulate = 1
     bg = _f32c(raster_settings.bg)
     view, proj, campos = _f32c(raster_settings.viewmatrix), _f32c(raster_settings.projmatrix), _f32c(raster_settings.campos)
     means3D, grad_out_color = _f32c(means3D), _f32c(grad_out_color)   # named: copies must outlive the launch
@@ -190,6 +193,15 @@ class _RasterizeGaussians(torch.autograd.Function):
         ctx.num_rendered = st.num_rendered
         ctx.split_sh = sh_rest is not None
         ctx.sinks = (sink_for(sh), sink_for(sh_rest))      # where the SH gradients go, if the caller registered a place
+        # running sums the SH gradients are added to (gradient accumulation): needs the staged kernel path, i.e. 16
+        # coefficients in 16-byte aligned arrays, and a sum for every SH array in use
+        acc = (acc_sink_for(sh), acc_sink_for(sh_rest))
+        arrays = [(t, a) for t, a in zip((sh, sh_rest), acc) if t is not None and t.numel()]
+        M = sum(int(t.shape[1]) for t, _ in arrays)
+        ctx.sh_accumulate = bool(arrays) and M == 16 and all(
+            a is not None and t.data_ptr() % 16 == 0 and a.data_ptr() % 16 == 0 for t, a in arrays)
+        if ctx.sh_accumulate:
+            ctx.sinks = acc
         ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, sh, sh_rest)
         ctx.mark_non_differentiable(radii, depth, tidx)  # the reference has no depth gradient (:88)
         ctx.set_materialize_grads(False)                 # no zero tensors built for the outputs that take no gradient
@@ -203,7 +215,7 @@ class _RasterizeGaussians(torch.autograd.Function):
                                           int(ctx.raster_settings.image_width)), dtype=torch.float32, device=means3D.device)
         (g_means2D, g_colors, g_opacity, g_means3D, g_cov3D, g_sh, g_scales, g_rots) = raster_backward(
             ctx.state, grad_out_color, means3D, sh, colors_precomp, scales, rotations, cov3Ds_precomp,
-            ctx.raster_settings, sh_rest if ctx.split_sh else None, ctx.sinks)
+            ctx.raster_settings, sh_rest if ctx.split_sh else None, ctx.sinks, ctx.sh_accumulate)
         g_sh, g_sh_rest = g_sh if ctx.split_sh else (g_sh, None)
         # order of the reference's backward (:120-130)
         return (g_means3D, g_means2D, g_sh, g_colors, g_opacity, g_scales, g_rots, g_cov3D, None, None, g_sh_rest)

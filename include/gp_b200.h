@@ -67,6 +67,11 @@ typedef struct {
    * then writes dL_dsh as [P,1,3] and dL_dsh_rest as [P,15,3].  NULL: `shs` is the concatenated [P,sh_coeffs,3]. */
   const float* sh_rest;
   float* dL_dsh_rest;
+  /* Non-zero: gp_raster_backward ADDS the SH gradients to what dL_dsh (and dL_dsh_rest) hold instead of overwriting
+   * them -- the running sum over the samples of a gradient-accumulation step (the reference's batch loop,
+   * train.py:99-124, sums them through autograd's .grad accumulation).  Needs the staged SH path (sh_coeffs = 16,
+   * 16-byte aligned arrays); GP_ERR_UNSUPPORTED otherwise.  All other gradients are written as usual. */
+  int dL_dsh_accumulate;
 } gp_raster_cfg;
 
 /* Header words at the start of the geometry workspace (int32 each); readable by the host. */
@@ -207,6 +212,15 @@ int gp_blend_backward(int N, int Kp, int K, const float* logits, const int* idx3
                       const float* o_t, const float* g_xyz_t, const float* g_q_t, const float* g_s_t,
                       const float* g_o_t, float* g_logits, float* g_xyz, float* g_rot, float* g_scaling,
                       float* g_opacity, float* g_kp_delta_xyz, float* g_kp_delta_q, gp_stream_t stream);
+
+/* Same, but the per-Gaussian outputs (g_logits, g_xyz, g_rot, g_scaling, g_opacity) are ADDED to what the arrays hold:
+ * the running sum over the samples of a gradient-accumulation step (train.py:99-124), with no scratch copy and no
+ * separate add pass.  The keypoint outputs are zeroed and summed as in gp_blend_backward. */
+int gp_blend_backward_accumulate(int N, int Kp, int K, const float* logits, const int* idx32, const long long* idx64,
+                                 const float* kp_delta_xyz, const float* kp_delta_q, const float* rot, const float* s_t,
+                                 const float* o_t, const float* g_xyz_t, const float* g_q_t, const float* g_s_t,
+                                 const float* g_o_t, float* g_logits, float* g_xyz, float* g_rot, float* g_scaling,
+                                 float* g_opacity, float* g_kp_delta_xyz, float* g_kp_delta_q, gp_stream_t stream);
 
 /* Dense [N,Kp] weight matrices for API parity: weights_xyz / weights_r (return_weights=True,
  * scene/gaussian_model.py:302-303) and weights_sum (:263).  Any output may be NULL. */

@@ -458,6 +458,8 @@ def test_batch_step_accumulates_samples(gplib):
         p.grad = None
     del pkg, loss
     batch = BatchStep(pc, cams[0], 400_000, lambda: FlatGradAllReduce(with_grad), 3, bg=bg)
+    # samples 2.. add their SH and per-Gaussian gradients to the running sum inside the kernels (no scratch copy)
+    assert batch.rest.in_place == 7, batch.rest.in_place
     for mode in ("device", "host", "host"):
         if mode == "device":
             loss = batch.step(dev_samples)
@@ -667,3 +669,41 @@ def test_knn_pruning_adversarial_lattice(gplib):
             i64, _, d = knn_keypoints(qc, mf.cuda(), kc, kf.cuda(), 6, mode, 1.0, return_dists=True, order=o, hint=hint)
             assert count_diff(to_np(d), od) == 0, (mode, o is not None, h)
             assert count_diff(to_np(i64), oi) == 0, (mode, o is not None, h)
+
+
+def test_blend_backward_adds_to_a_running_sum(gplib):
+    """gp_blend_backward_accumulate (accumulating gradient sinks): the per-Gaussian gradients of a second backward are
+    added to the destination; keypoint gradients are returned as usual."""
+    from gaussianprediction_b200._sinks import grad_sinks
+    from gaussianprediction_b200.deform import keypoint_blend, knn_keypoints
+    N, Kp = 5003, 64
+    gs, kp, kf, logits = scene(N, Kp, seed=9)
+    g = torch.Generator().manual_seed(4)
+    leaf = dict(logits=logits, kp_dxyz=0.2 * torch.randn(Kp, 3, generator=g),
+                kp_dq=torch.nn.functional.normalize(torch.randn(Kp, 4, generator=g)), xyz=gs.xyz, rot=gs.rotation,
+                sc=gs.scaling, op=gs.opacity)
+    leaf = {k: v.clone().cuda().requires_grad_(True) for k, v in leaf.items()}
+    _, idx32, _ = knn_keypoints(gs.xyz.cuda(), gs.motion_feature.cuda(), kp.cuda(), kf.cuda(), 6, "hybird", 0.5)
+    per_gaussian = ("logits", "xyz", "rot", "sc", "op")
+    gens = None
+
+    def run(scale, sums=None):
+        nonlocal gens
+        pairs = [(leaf[k], sums[k]) for k in per_gaussian] if sums is not None else ()
+        with grad_sinks((), accumulate=pairs):
+            outs = keypoint_blend(leaf["logits"], idx32, leaf["kp_dxyz"], leaf["kp_dq"], leaf["xyz"], leaf["rot"],
+                                  leaf["sc"], leaf["op"])
+        if gens is None:
+            gens = [torch.randn(o.shape, generator=g).cuda() for o in outs]
+        for v in leaf.values():
+            v.grad = None
+        sum((o * w * scale).sum() for o, w in zip(outs, gens)).backward()
+        return {k: v.grad for k, v in leaf.items()}
+    g1 = {k: v.clone() for k, v in run(1.0).items()}
+    sums = {k: g1[k].clone() for k in per_gaussian}
+    g2 = run(0.5, sums)
+    for k in per_gaussian:
+        assert g2[k].data_ptr() == sums[k].data_ptr()
+        assert float(g1[k].abs().sum()) > 0 and rel_err(sums[k], 1.5 * g1[k]) <= 1e-5, k
+    for k in ("kp_dxyz", "kp_dq"):
+        assert rel_err(g2[k], 0.5 * g1[k]) <= 1e-4, k

@@ -360,3 +360,39 @@ def test_patch_culling_adversarial_vs_reference(gplib):
         print(k, "ours vs ref %.3g, ref vs ref %.3g" % (e, noise))
         assert e <= max(GRAD_TOL, 3 * noise), (k, e, noise)
 
+
+
+@pytest.mark.parametrize("split,N", [(True, 1003), (False, 4096), (True, 31)])
+def test_sh_gradients_added_to_a_running_sum(gplib, split, N):
+    """gp_raster_cfg.dL_dsh_accumulate (accumulating gradient sinks): the SH gradients of a second backward are ADDED to
+    what the destination holds -- equal to the first gradient plus the second, every other gradient unchanged."""
+    from gaussianprediction_b200 import GaussianRasterizer
+    from gaussianprediction_b200._sinks import grad_sinks
+    case = raster_case(N=N, W=96, H=64, seed=12)
+    c = {k: (v.cuda() if torch.is_tensor(v) else v) for k, v in case.items()}
+    rast = GaussianRasterizer(settings_of(c))
+    gout = seeded_grad(case).cuda()
+    dc = c["shs"][:, :1].contiguous().requires_grad_(True)
+    rest = c["shs"][:, 1:].contiguous().requires_grad_(True)
+    full = c["shs"].clone().requires_grad_(True)
+    sh_leaves = [dc, rest] if split else [full]
+
+    def run(scale, sums=None):
+        leaf = {k: c[k].clone().requires_grad_(True) for k in ("means3D", "opacities", "scales", "rotations")}
+        means2D = torch.zeros_like(leaf["means3D"], requires_grad=True)
+        kw = dict(shs=dc, shs_rest=rest) if split else dict(shs=full)
+        with grad_sinks((), accumulate=zip(sh_leaves, sums) if sums is not None else ()):
+            color, _, _, _ = rast(means3D=leaf["means3D"], means2D=means2D, opacities=leaf["opacities"],
+                                  scales=leaf["scales"], rotations=leaf["rotations"], **kw)
+        for p in sh_leaves:
+            p.grad = None
+        (color * gout * scale).sum().backward()
+        return [p.grad for p in sh_leaves], leaf["means3D"].grad
+    g1, m1 = run(1.0)
+    g1 = [g.clone() for g in g1]
+    sums = [g.clone() for g in g1]
+    got, m2 = run(0.5, sums)
+    for s, g, a in zip(sums, got, g1):
+        assert g.data_ptr() == s.data_ptr()                     # the kernel wrote into the running sum itself
+        assert float(a.abs().sum()) > 0 and rel_err(s, 1.5 * a) <= 1e-5
+    assert rel_err(m2, 0.5 * m1) <= 1e-5
