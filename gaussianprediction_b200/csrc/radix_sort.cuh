@@ -124,7 +124,9 @@ gp_rs_pass_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restri
   __shared__ uint32_t tstart[GP_RS_RADIX];   // slot of the tile's first key of digit d
   __shared__ uint32_t digit_base[GP_RS_RADIX];
   __shared__ uint32_t warp_tot[GP_RS_WARPS];
-  __shared__ uint32_t sk[TILE], sv[TILE];
+  __shared__ uint32_t skv[2 * TILE];
+  uint32_t* const sk = skv;
+  uint32_t* const sv = skv + TILE;
   __shared__ int s_tile;
   const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
   const int n = *n_ptr;
@@ -149,6 +151,7 @@ gp_rs_pass_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restri
   };
   // this pass's digit histogram -> first output position of every digit
   digit_base[tid] = digit_scan(t.hist[pass * GP_RS_RADIX + tid]);
+
   for (;;) {
     __syncthreads();
     if (tid == 0) s_tile = (int)atomicAdd(&t.tickets[pass], 1u);
@@ -170,11 +173,21 @@ gp_rs_pass_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restri
       const int i = base + u * 32 + lane;
       const bool valid = i < n;
       const uint32_t d = valid ? ((k[u] >> shift) & 0xFFu) : 0x100u;
-      const unsigned peers = __match_any_sync(0xffffffffu, d);
+      // lanes with the same digit find each other through 8 ballots (one per digit bit): constant cost, whereas
+      // match.any takes time that grows with the number of distinct digits in the warp (~30 on a low byte)
+      unsigned peers = __ballot_sync(0xffffffffu, valid);
+#pragma unroll
+      for (int b = 0; b < 8; b++) {
+        const bool bit = (d >> b) & 1u;
+        const unsigned m = __ballot_sync(0xffffffffu, bit);
+        peers &= bit ? m : ~m;
+      }
       const unsigned before = peers & gp_lanemask_lt();
       local[u] = valid ? wcnt[w][d] + __popc(before) : 0u;
       __syncwarp();
-      if (valid && before == 0) wcnt[w][d] += __popc(peers);
+      if (valid && before == 0) {
+        wcnt[w][d] += __popc(peers);
+      }
       __syncwarp();
     }
     __syncthreads();

@@ -353,9 +353,10 @@ def test_patch_culling_adversarial_vs_reference(gplib):
     # The needles make the scale / rotation gradients ill-conditioned: the reference's own result moves from run to run
     # with the order of its atomicAdds.  Bar = north_star's 1e-3, or three times the reference's own run-to-run
     # deviation where that is larger.
-    ref2 = run_ref(case, seeded_grad(case))
+    # (the deviation of ONE pair of runs is itself a random draw: take the largest of three reruns)
+    reruns = [run_ref(case, seeded_grad(case))["grads"] for _ in range(3)]
     for k in ("means2D", "opacity", "means3D", "sh", "scales", "rotations"):
-        noise = rel_err(ref2["grads"][k], ref["grads"][k])
+        noise = max(rel_err(r[k], ref["grads"][k]) for r in reruns)
         e = rel_err(mine["grads"][k], ref["grads"][k])
         print(k, "ours vs ref %.3g, ref vs ref %.3g" % (e, noise))
         assert e <= max(GRAD_TOL, 3 * noise), (k, e, noise)
