@@ -117,7 +117,7 @@ template <int STEPS>
 static __global__ void __launch_bounds__(GP_RS_THREADS)
 gp_rs_pass_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                   uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, const int* __restrict__ n_ptr,
-                  int shift, int pass, GpRadixTemp t) {
+                  int shift, int nbits, int pass, GpRadixTemp t) {
   constexpr int TILE = GP_RS_WARPS * STEPS * 32;
   __shared__ uint32_t wcnt[GP_RS_WARPS][GP_RS_RADIX];
   __shared__ uint32_t gshift[GP_RS_RADIX];   // (global position of the tile's first key of digit d) - (its slot in the tile)
@@ -176,11 +176,14 @@ gp_rs_pass_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restri
       // lanes with the same digit find each other through 8 ballots (one per digit bit): constant cost, whereas
       // match.any takes time that grows with the number of distinct digits in the warp (~30 on a low byte)
       unsigned peers = __ballot_sync(0xffffffffu, valid);
+      // (bits of the digit above the sort's last bit are zero in every key: no ballot for them)
 #pragma unroll
       for (int b = 0; b < 8; b++) {
-        const bool bit = (d >> b) & 1u;
-        const unsigned m = __ballot_sync(0xffffffffu, bit);
-        peers &= bit ? m : ~m;
+        if (b < nbits) {
+          const bool bit = (d >> b) & 1u;
+          const unsigned m = __ballot_sync(0xffffffffu, bit);
+          peers &= bit ? m : ~m;
+        }
       }
       const unsigned before = peers & gp_lanemask_lt();
       local[u] = valid ? wcnt[w][d] + __popc(before) : 0u;
@@ -259,7 +262,8 @@ gp_rs_pass_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restri
 
 #define GP_RS_BIG_SORT (1 << 19)  // from this many keys (upper bound known to the host) on: 4096-key tiles
 
-// Sort bits [begin_bit, end_bit) of keys (at most 32 bits = 4 passes).  keys[0]/vals[0] hold the input; buffers
+// Sort bits [begin_bit, end_bit) of keys (at most 32 bits = 4 passes); the keys must be ZERO above end_bit (the last
+// pass ranks on the bits below end_bit only, but buckets by the whole byte).  keys[0]/vals[0] hold the input; buffers
 // ping-pong.  Returns the index (0/1) of the buffer pair holding the sorted result.
 static inline int gp_radix_sort_pairs(uint32_t* keys[2], uint32_t* vals[2], const int* n_ptr, int begin_bit,
                                       int end_bit, const GpRadixTemp& tmp, cudaStream_t stream, bool reset = true,
@@ -276,7 +280,7 @@ static inline int gp_radix_sort_pairs(uint32_t* keys[2], uint32_t* vals[2], cons
     auto kernel = (long long)tmp.tiles_max * GP_RS_TILE >= GP_RS_BIG_SORT ? gp_rs_pass_kernel<16> : gp_rs_pass_kernel<GP_RS_STEPS>;
     GP_KERNEL("gp_rs_pass_kernel", stream,
               kernel<<<GP_RS_BLOCKS, GP_RS_THREADS, 0, stream>>>(keys[sel], vals[sel], keys[sel ^ 1], vals[sel ^ 1], n_ptr,
-                                                                  begin_bit + 8 * p, p, tmp));
+                                                                  begin_bit + 8 * p, min(8, end_bit - begin_bit - 8 * p), p, tmp));
     sel ^= 1;
   }
   return sel;

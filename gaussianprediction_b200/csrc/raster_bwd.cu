@@ -254,7 +254,8 @@ gp_render_bwd_butterfly_kernel(const uint2* __restrict__ ranges, const uint32_t*
 //           (1, dx, dy, dx^2, dx dy, dy^2) and sum U dpx_c.  All nine reference gradients are linear in those:
 //             dL/dmean2D = -o (a Mx + b My) W/2, -o (c My + b Mx) H/2;  dL/dconic = -o/2 (Mxx, Mxy, Myy);  dL/dopacity = M0.
 //           One shuffle per value joins the two halves; three red.global.add.v4.f32 per visit add the result to the
-//           Gaussian's packed record.  No shared-memory atomics, no cross-warp accumulator, conflict-free rows (stride 33).
+//           Gaussian's packed record.  No shared-memory atomics, no cross-warp accumulator, conflict-free rows (stride 33;
+//           interleaving Wg and U as 64-bit pairs was measured slower: the splat pass then spills).
 // ------------------------------------------------------------------------------------------------
 #define GP_BW_SLOTS 16
 #define GP_BW_STRIDE 33

@@ -410,7 +410,8 @@ class KeypointDeformation(nn.Module):
         self.weights_model = weights_model
         self.second_stage_iter = args.second_stage_iteration
         self.beta = args.beta
-        self.nearest_mask = None
+        self._nearest_mask = None
+        self._nearest_flat = False
         self.lifecycle_opacity = None
         self._idx32 = None
         self._last_logits = None
@@ -451,11 +452,25 @@ class KeypointDeformation(nn.Module):
     def get_nearest_mask(self, keepshape=False):
         if self._knn_order is None or self._knn_order.shape[0] != self._xyz.shape[0]:
             self.refresh_knn_order()
-        idx64, idx32, _ = knn_keypoints(self._xyz, self.motion_feature, self.super_gaussians, self.super_gaussians_feature,
-                                        self.args.nearest_num, self.args.knn_type, self.args.feature_amplify,
-                                        order=self._knn_order, hint=self._idx32)
+        _, idx32, _ = knn_keypoints(self._xyz, self.motion_feature, self.super_gaussians, self.super_gaussians_feature,
+                                    self.args.nearest_num, self.args.knn_type, self.args.feature_amplify,
+                                    idx32_only=True, order=self._knn_order, hint=self._idx32)
         self._idx32 = idx32
-        self.nearest_mask = idx64 if keepshape else idx64.view([-1])
+        self._nearest_mask, self._nearest_flat = None, not keepshape
+
+    @property
+    def nearest_mask(self):
+        """The reference's int64 attribute (scene/gaussian_model.py:123-125), widened from the int32 search result on
+        access: the blend kernels read the int32 form, so a training step never writes the 48 B per Gaussian.  Not
+        cached: a replayed CUDA graph refreshes the int32 buffer in place."""
+        if self._nearest_mask is None and self._idx32 is not None:
+            m = self._idx32.long()
+            return m.view([-1]) if self._nearest_flat else m
+        return self._nearest_mask
+
+    @nearest_mask.setter
+    def nearest_mask(self, value):
+        self._nearest_mask = value
 
     def get_motion_delta(self, xyz_embed, motion_feature, t):
         t = t.repeat((motion_feature.shape[0], 1))
