@@ -336,6 +336,8 @@ gp_duplicate_kernel(int P, const uint32_t* __restrict__ sorted_idx, const uint32
   __shared__ uint32_t ws[GP_SCAN_BLOCK / 32];
   const int t = threadIdx.x, lane = t & 31, w = t >> 5;
   const bool packed = gp_list_packed(P);
+  const int s = blockIdx.x * GP_SCAN_BLOCK + t;
+  const uint32_t gidx_early = s < P ? sorted_idx[s] : 0u;   // in flight together with the header word below
   // does the frame fit the binning buffers?  Every block decides for itself from R (no block reads the flag another
   // one writes); block 0 publishes the decision for the kernels that follow.  Tiles without instances keep range (0,0).
   const long long R = hdr[GP_HDR_NUM_RENDERED];
@@ -352,17 +354,22 @@ gp_duplicate_kernel(int P, const uint32_t* __restrict__ sorted_idx, const uint32
   // are produced, instead of by a separate pass over the R keys (the counters were zeroed by gp_block_sum_kernel)
   gp_rs_clear_status(tile_radix, (int)R, passes);
   for (int e = t; e < GP_RS_MAX_PASSES * GP_RS_RADIX; e += GP_SCAN_BLOCK) (&s_hist[0][0])[e] = 0u;
-  const int s = blockIdx.x * GP_SCAN_BLOCK + t;
+  // One dependent round trip after the sorted index, not three: everything that is known per Gaussian is loaded at once
+  // (the ~2 % culled Gaussians load a record nobody uses).
   uint32_t gidx = 0, tt = 0;
+  int rad = 0;
+  float4 xyd = make_float4(0.f, 0.f, 0.f, 0.f), co = make_float4(0.f, 0.f, 0.f, 0.f);
   if (s < P) {
-    gidx = sorted_idx[s];
+    gidx = gidx_early;
     tt = tiles_touched[gidx];
+    xyd = xy_depth[gidx];
+    rad = radii[gidx];
+    if (packed) co = conic_opacity[gidx];
   }
   uint2 rmin = {0, 0}, rmax = {0, 0};
   if (tt) {
-    const float4 xyd = xy_depth[gidx];
-    tile_rect(xyd.x, xyd.y, radii[gidx], grid_x, grid_y, rmin, rmax);
-    if (packed) s_ext[t] = gp_patch_extent(conic_opacity[gidx], xyd.x, xyd.y);
+    tile_rect(xyd.x, xyd.y, rad, grid_x, grid_y, rmin, rmax);
+    if (packed) s_ext[t] = gp_patch_extent(co, xyd.x, xyd.y);
   }
   s_g[t] = gidx;
   s_rx[t] = rmin.x;
