@@ -262,13 +262,13 @@ gp_render_bwd_butterfly_kernel(const uint2* __restrict__ ranges, const uint32_t*
 #define GP_BW_BATCH 128
 // dynamic shared memory, byte offsets (explicit shared-space addressing: a generic pointer into dynamic shared memory
 // costs S2R CgaCtaId + LEA at every access, ~8 % of the round-1 kernel's instructions).
-// Two batch buffers [co | x, y, id, - | rgb | mask] of 128 entries, the pixels' dL/dpixel, the warps' (Wg, U) slots
-// and the warps' slot tables (what phase 2 needs of each slot's Gaussian): 55,296 B, four blocks per SM.
+// Two batch buffers [co | x, y, id, - | rgb | patch bits] of 128 entries, the pixels' dL/dpixel, the warps' (Wg, U) slots
+// and the warps' slot tables (what phase 2 needs of each slot's Gaussian): 54,528 B, four blocks per SM.
 #define GP_BW_B_CO 0
 #define GP_BW_B_XYD (GP_BW_BATCH * 16)
 #define GP_BW_B_RGB (2 * GP_BW_BATCH * 16)
-#define GP_BW_B_MASK (3 * GP_BW_BATCH * 16)
-#define GP_BW_BUF (GP_BW_B_MASK + GP_BW_BATCH * 4)
+#define GP_BW_B_BITS (3 * GP_BW_BATCH * 16)    // [warp][chunk of 32 entries]: which entries of the chunk meet the warp's patch
+#define GP_BW_BUF (GP_BW_B_BITS + 8 * 4 * 4)
 #define GP_BW_DPX (2 * GP_BW_BUF)
 #define GP_BW_W (GP_BW_DPX + GP_TILE_PIX * 16)
 #define GP_BW_WARP_BYTES (2 * GP_BW_SLOTS * GP_BW_STRIDE * 4)
@@ -325,7 +325,6 @@ gp_render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
   for (int k = 0; k < 8; k++) block_last = max(block_last, s_last[k]);
   const int total = (int)min(block_last, range.y - range.x);   // list positions 0 .. total-1 matter, walked back to front
   const int rounds = (total + GP_BW_BATCH - 1) / GP_BW_BATCH;
-  int toDo = total;
   const uint32_t* list_end = point_list + range.x + total;     // entry k (from the back) is list_end[-1 - k]
 
   // phase-2 identity of this lane
@@ -413,14 +412,23 @@ gp_render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
         gp_cp_async16(buf + GP_BW_B_RGB + e * 16, rgb4 + id);
       }
     }
-    if (first_half) gp_sts32u(buf + GP_BW_B_MASK + e * 4, valid ? gp_list_mask(v, packed) : 0u);
+    if (first_half) {   // warp w (< 4) holds chunk w: one word of patch bits per consumer warp (see the forward kernel)
+      const unsigned m = valid ? gp_list_mask(v, packed) : 0u;
+      unsigned mine = 0u;
+#pragma unroll
+      for (int ww = 0; ww < 8; ww++) {
+        const unsigned b = __ballot_sync(0xffffffffu, (m >> ww) & 1u);
+        if (lane == ww) mine = b;
+      }
+      if (lane < 8) gp_sts32u(buf + GP_BW_B_BITS + (lane * 4 + w) * 4, mine);
+    }
     gp_cp_async_commit();
   };
 
   uint32_t v_next = e < total ? list_end[-1 - e] : 0u;
   stage(sb, v_next, e < total);
   v_next = e + GP_BW_BATCH < total ? list_end[-1 - e - GP_BW_BATCH] : 0u;
-  for (int i = 0; i < rounds; i++, toDo -= GP_BW_BATCH) {
+  for (int i = 0; i < rounds; i++) {
     gp_cp_async_wait_all();
     __syncthreads();   // batch i has landed for every thread, and nobody reads batch i - 1 any more
     const uint32_t cur = sb + (uint32_t)(i & 1) * GP_BW_BUF;
@@ -430,14 +438,19 @@ gp_render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
       v_next = k1 + GP_BW_BATCH < total ? list_end[-1 - k1 - GP_BW_BATCH] : 0u;
     }
 
-    const int nb = min(GP_BW_BATCH, toDo);
     // list position (0-based, front to back) of batch element j is base - j
     const int base = total - 1 - i * GP_BW_BATCH;
     // elements of this batch in front of index (total - warp_last) lie behind the last contributor of every pixel
     // of this warp: start at the first 32-chunk that can matter
     const int first = total - (int)warp_last - i * GP_BW_BATCH;
-    for (int c0 = max(first, 0) & ~31; c0 < nb; c0 += 32) {
-      unsigned bits = __ballot_sync(0xffffffffu, (gp_lds32u(cur + GP_BW_B_MASK + (c0 + lane) * 4) >> w) & 1u);
+    const int start = max(first, 0) >> 5;
+    const unsigned chunk_bits = lane < 4 ? gp_lds32u(cur + GP_BW_B_BITS + (w * 4 + lane) * 4) : 0u;
+    unsigned chunks = __ballot_sync(0xffffffffu, chunk_bits != 0u) & (start < 4 ? (0xFu << start) : 0u);
+    while (chunks) {
+      const int c0 = (__ffs(chunks) - 1) * 32;
+      const unsigned chunk_word = __shfl_sync(0xffffffffu, chunk_bits, c0 >> 5);
+      chunks &= chunks - 1;
+      unsigned bits = chunk_word;
       while (bits) {
         const int j = c0 + __ffs(bits) - 1;
         bits &= bits - 1;

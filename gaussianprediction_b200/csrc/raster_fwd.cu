@@ -441,7 +441,8 @@ gp_tile_ranges_kernel(const int* __restrict__ hdr, const uint32_t* __restrict__ 
 
 // One 16x16 tile per block; warp w owns an 8x4 pixel patch (lane = 8*row + col) so that the 32
 // pixels of a warp are spatially compact.  Batches of 256 list entries are staged in shared memory:
-// conic+opacity, centre+depth, colour, index and patch mask (56 B each), in TWO buffers: while batch i is
+// conic+opacity, centre+depth, colour and index (52 B each) plus one word of patch bits per (warp, 32-entry chunk), in
+// TWO buffers: while batch i is
 // blended, the records of batch i + 1 are already on their way (cp.async; the list entries themselves are read
 // one batch earlier still), so a round costs one barrier and no exposed gather latency -- at 2 M Gaussians a
 // warp finds only a few Gaussians of a batch on its patch, and the gather was ~40 % of the kernel's stall samples.
@@ -452,8 +453,8 @@ gp_tile_ranges_kernel(const int* __restrict__ hdr, const uint32_t* __restrict__ 
 #define GP_FW_XYD (GP_TILE_PIX * 16)
 #define GP_FW_RGB (2 * GP_TILE_PIX * 16)
 #define GP_FW_ID (3 * GP_TILE_PIX * 16)
-#define GP_FW_MASK (GP_FW_ID + GP_TILE_PIX * 4)
-#define GP_FW_BUF (GP_FW_MASK + GP_TILE_PIX * 4)
+#define GP_FW_BITS (GP_FW_ID + GP_TILE_PIX * 4)   // [warp][chunk of 32 entries]: which entries of the chunk meet the warp's patch
+#define GP_FW_BUF (GP_FW_BITS + 8 * 8 * 4)
 
 __global__ void __launch_bounds__(GP_TILE_PIX)
 gp_render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H,
@@ -462,7 +463,7 @@ gp_render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
                      const float* __restrict__ bg_color, const int* __restrict__ hdr, bool packed,
                      float* __restrict__ final_T, uint32_t* __restrict__ n_contrib, float* __restrict__ out_color,
                      float* __restrict__ out_depth, int* __restrict__ out_tidx) {
-  // one shared block addressed through an opaque 32-bit base (raster_common.cuh): 2 x [co | xyd | rgb | id | mask]
+  // one shared block addressed through an opaque 32-bit base (raster_common.cuh): 2 x [co | xyd | rgb | id | patch bits]
   __shared__ __align__(16) unsigned char s_raw[2 * GP_FW_BUF];
   const uint32_t sb = gp_smem_base(s_raw);
 
@@ -481,7 +482,6 @@ gp_render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
   const uint2 range = hdr[GP_HDR_OVERFLOW] ? make_uint2(0u, 0u) : ranges[tile];
   const unsigned n = range.y - range.x;
   const int rounds = (int)((n + GP_TILE_PIX - 1) / GP_TILE_PIX);
-  int toDo = (int)n;
   bool done = !inside;
 
   float T = 1.0f;
@@ -508,14 +508,23 @@ gp_render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
       }
       gp_sts32u(buf + GP_FW_ID + t * 4, id);
     }
-    gp_sts32u(buf + GP_FW_MASK + t * 4, m);
+    // The staging warp w holds chunk w of the batch: it transposes its 32 patch masks into one 32-bit word per
+    // consumer warp, so that a consumer reads its eight chunk words with one load and skips empty chunks outright (at
+    // 2 M Gaussians a warp finds two or three entries of a 256-entry batch on its patch).
+    unsigned mine = 0u;
+#pragma unroll
+    for (int ww = 0; ww < 8; ww++) {
+      const unsigned b = __ballot_sync(0xffffffffu, (m >> ww) & 1u);
+      if (lane == ww) mine = b;
+    }
+    if (lane < 8) gp_sts32u(buf + GP_FW_BITS + (lane * 8 + w) * 4, mine);
     gp_cp_async_commit();
   };
 
   uint32_t v_next = (unsigned)t < n ? point_list[range.x + t] : 0u;
   stage(sb, v_next, (unsigned)t < n);
   v_next = (unsigned)t + GP_TILE_PIX < n ? point_list[range.x + GP_TILE_PIX + t] : 0u;
-  for (int i = 0; i < rounds; i++, toDo -= GP_TILE_PIX) {
+  for (int i = 0; i < rounds; i++) {
     gp_cp_async_wait_all();
     // batch i is complete for every thread past this barrier, and nobody reads batch i - 1 any more
     const int num_done = __syncthreads_count(done);
@@ -526,10 +535,14 @@ gp_render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
       stage(sb + (uint32_t)((i + 1) & 1) * GP_FW_BUF, v_next, k1 < n);
       v_next = k1 + GP_TILE_PIX < n ? point_list[range.x + k1 + GP_TILE_PIX] : 0u;
     }
-    const int nb = min(GP_TILE_PIX, toDo);
-    for (int c0 = 0; c0 < nb; c0 += 32) {
+    const unsigned chunk_bits = lane < 8 ? gp_lds32u(cur + GP_FW_BITS + (w * 8 + lane) * 4) : 0u;
+    unsigned chunks = __ballot_sync(0xffffffffu, chunk_bits != 0u);
+    while (chunks) {
+      const int c = __ffs(chunks) - 1;
+      chunks &= chunks - 1;
       if (__all_sync(0xffffffffu, done)) break;
-      unsigned bits = __ballot_sync(0xffffffffu, (gp_lds32u(cur + GP_FW_MASK + (c0 + lane) * 4) >> w) & 1u);
+      const int c0 = c * 32;
+      unsigned bits = __shfl_sync(0xffffffffu, chunk_bits, c);
       while (bits) {
         const int j = c0 + __ffs(bits) - 1;
         bits &= bits - 1;
