@@ -458,9 +458,11 @@ def workload_stats(runner):
 
 # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full captures (profiles/), keyed
 # by workload; other workloads report null
-NCU_DRAM_BYTES = {"c2_dnerf_100k_800x800": {"gp_render_bwd_kernel": 24.20e6, "gp_render_fwd_kernel": 6.97e6},
-                  "c5_2m_800x800": {"gp_render_bwd_kernel": 435.09e6, "gp_render_fwd_kernel": 161.73e6,
-                                    "gp_knn_kernel": 762.02e6}}
+# ncu dram__bytes_read.sum + dram__bytes_write.sum per launch of the kernels as committed (profiles/r2_ncu_full.md, C5)
+NCU_DRAM_BYTES = {"c5_2m_800x800": {"gp_render_bwd_kernel": 219.5e6, "gp_render_fwd_kernel": 181.4e6,
+                                    "gp_knn_kernel": 514.4e6, "gp_preprocess_bwd_kernel": 1074.4e6,
+                                    "gp_blend_bwd_kernel": 445.6e6, "gp_preprocess_kernel": 629.6e6,
+                                    "gp_duplicate_kernel": 242.4e6, "gp_blend_fwd_kernel": 297.0e6}}
 NCU_DRAM_SOURCE = "profiles/r2_ncu_full.md"
 
 
@@ -535,6 +537,8 @@ def rooflines(prof, stats, wl, steps, samples, peaks, fp32_peak, fp32_src):
             else:
                 ach, peak, unit = w / sec / 1e12, fp32_peak, "TFLOP/s"
             row.update(achieved=round(ach, 3), peak=round(peak, 3), unit=unit, frac=round(ach / peak, 4))
+        if k in NCU_DRAM_BYTES.get(wl.get("name"), {}):
+            row["traffic"] = NCU_DRAM_BYTES[wl["name"]][k]      # measured DRAM bytes per launch (ncu), next to the algorithmic ones
         table[k] = row
     # the dominant kernel that HAS a roofline: the neighbour search (pruned, no algorithmic-work figure) is named beside it
     # when it is the longer one

@@ -40,16 +40,17 @@ def render(viewpoint_camera, pc, pipe=None, bg_color=None, scaling_modifier=1.0,
            time=None, it=1, capacity=None, deformed=None):
     """``deformed`` (extra, keyword only): the result of an earlier ``pc(time, it)`` call to use instead of calling it
     here -- lets a captured step put the deformation forward and the rasterizer into different CUDA graphs."""
-    screenspace_points = torch.zeros_like(pc.get_xyz, dtype=pc.get_xyz.dtype, requires_grad=True, device="cuda") + 0
+    # (the reference adds 0 to get a non-leaf tensor and retains its grad, gaussian_renderer/__init__.py; a leaf receives
+    # .grad just the same and saves a 24 MB read-modify-write per frame at 2 M Gaussians)
+    screenspace_points = torch.zeros_like(pc.get_xyz, dtype=pc.get_xyz.dtype, requires_grad=True, device="cuda")
     try:
         screenspace_points.retain_grad()
     except Exception:
         pass
     rasterizer = GaussianRasterizer(_settings(viewpoint_camera, pc, bg_color, scaling_modifier), capacity=capacity)
-    opacity = pc.get_opacity
     if time is None:
         means3D = pc.get_xyz + delta if delta is not None else pc.get_xyz
-        scales, rotations = pc.get_scaling, pc.get_rotation
+        scales, rotations, opacity = pc.get_scaling, pc.get_rotation, pc.get_opacity
     elif deformed is not None:
         means3D, rotations, scales, opacity = deformed
     else:
@@ -67,7 +68,9 @@ def render(viewpoint_camera, pc, pipe=None, bg_color=None, scaling_modifier=1.0,
 
 def render_motion(viewpoint_camera, pc, pipe=None, bg_color=None, scaling_modifier=1.0, override_color=None, xyz_t=None,
                   r_t=None, opacity=None, capacity=None):
-    screenspace_points = torch.zeros_like(pc.get_xyz, dtype=pc.get_xyz.dtype, requires_grad=True, device="cuda") + 0
+    # (the reference adds 0 to get a non-leaf tensor and retains its grad, gaussian_renderer/__init__.py; a leaf receives
+    # .grad just the same and saves a 24 MB read-modify-write per frame at 2 M Gaussians)
+    screenspace_points = torch.zeros_like(pc.get_xyz, dtype=pc.get_xyz.dtype, requires_grad=True, device="cuda")
     rasterizer = GaussianRasterizer(_settings(viewpoint_camera, pc, bg_color, scaling_modifier), capacity=capacity)
     opacity = pc.get_opacity if opacity is None else opacity
     shs, shs_rest, colors_precomp = _sh_inputs(pc, override_color)
