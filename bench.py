@@ -926,6 +926,20 @@ def main():
         chk = exchange_check(runner, warmup + steps)
         line["exchange_check"] = chk
         line["exchange_alone_ms"] = round(exchange_time(runner), 4)
+        # how much of the exchange the step hides: the same steps once more with the exchange switched off (diagnostic
+        # pass, never the reported value), max over ranks like the value itself
+        runner.batch.flush()
+        runner.batch.exchange = False
+        k = max(3, min(steps, 10))
+        per0, _ = timed_steps(runner, k, 2, eff_world, False, flush, graph=True)
+        runner.batch.exchange = True
+        compute_only = max_over_ranks(sum(per0), eff_world, dev) / k
+        exposed = max(0.0, line["ms_per_step"] - compute_only)
+        line["exchange_overlap"] = {"compute_only_ms_per_step": round(compute_only, 4),
+                                    "exposed_ms_per_step": round(exposed, 4),
+                                    "hidden_frac": round(max(0.0, 1.0 - exposed / max(line["exchange_alone_ms"], 1e-9)), 4),
+                                    "note": "exposed = step time - the same steps with the exchange off; hidden = 1 - "
+                                            "exposed / exchange_alone (the exchange run alone on idle GPUs)"}
         if not chk["ok"]:
             if rank == 0:
                 print(json.dumps(line))
