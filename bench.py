@@ -236,9 +236,14 @@ class OurRunner:
                   second=[d._rotation, d._scaling, d._opacity] + list(d.weights_model.parameters()),
                   aux_int32=self.wl["N"] if first_call else 0)       # the radii ride the same exchange (MAX)
         if first_call:
-            self.exchange_kind = ("gp_allreduce_sum_kernel over symmetric memory (" +
-                                  ("NVSwitch multicast, multimem.ld_reduce" if red.multicast else "peer loads/stores") + ")") \
-                if cls is not parallel.FlatGradAllReduce else "NCCL all_reduce per bucket"
+            if cls is parallel.FlatGradAllReduce:
+                self.exchange_kind = "NCCL all_reduce per bucket"
+            elif getattr(red, "copy_engine", False):
+                self.exchange_kind = ("symmetric memory, 2 ranks: copy engines pull the peer's ranges (cudaMemcpyAsync), "
+                                      "gp_add_inplace_kernel in front of each first reader")
+            else:
+                self.exchange_kind = ("gp_allreduce_sum_kernel over symmetric memory (" +
+                                      ("NVSwitch multicast, multimem.ld_reduce" if red.multicast else "peer loads/stores") + ")")
         return red
 
     def enable_graph(self):

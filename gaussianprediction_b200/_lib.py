@@ -83,6 +83,10 @@ SIGNATURES = {
     "gp_exchange_segments": (c_int, [c_int, c_int, _P, POINTER(c_void_p), c_size_t, c_int, c_int, POINTER(c_size_t),
                                      POINTER(c_size_t), POINTER(c_int), _P, ctypes.c_uint, _P]),
     "gp_stream_wait_word": (c_int, [_P, ctypes.c_uint, _P]),
+    "gp_peer_barrier_launch": (c_int, [c_int, c_int, POINTER(c_void_p), c_size_t, c_int, _P]),
+    "gp_copy_async": (c_int, [_P, _P, c_size_t, _P]),
+    "gp_add_inplace_f32": (c_int, [_P, _P, c_size_t, _P]),
+    "gp_max_inplace_s32": (c_int, [_P, _P, c_size_t, _P]),
     "gp_linear_forward": (c_int, [c_int, c_int, c_int, _P, c_int, _P, c_int, _P, _P, c_int, _P, c_int, _P]),
     "gp_hashgrid_entries": (c_longlong, [c_int, c_int, c_float, c_int]),
     "gp_hashgrid_forward": (c_int, [c_int, c_int, c_int, c_float, c_int, _P, _P, _P, _P, _P]),

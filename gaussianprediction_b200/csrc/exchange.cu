@@ -298,6 +298,83 @@ extern "C" int gp_exchange_segments(int rank, int world, void* multicast_base, v
   return GP_OK;
 }
 
+// ------------------------------------------------------------------------------------------------
+// Two ranks: the copy engines move the bytes.  A rank pulls its peer's range into local staging with cudaMemcpyAsync (no
+// SM involved: measured 733 GB/s for 544 MiB, and the neighbour search next to it runs at full speed, whereas it
+// crawls next to the 148-CTA peer-load kernel, tools/ce_copy_probe.py) and adds it in place right in front of the first
+// reader.  The kernels below are the pieces: a barrier between the ranks on one flag slot (before the copy: the peer's
+// gradients are final; before the in-place add: the peer has finished reading this rank's range), the copy, the add.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(32) gp_barrier_kernel(GpPeers peers, int rank, int world, size_t flags_off, int slot) {
+  uint32_t* my_epoch = (uint32_t*)(peers.p[rank] + flags_off) + (size_t)slot * GP_AR_FLAG_WORDS + GP_AR_MAX_WORLD;
+  const uint32_t e = *my_epoch + 1;
+  __syncwarp();
+  if (threadIdx.x < (unsigned)world) {
+    const int q = threadIdx.x;
+    __threadfence_system();
+    gp_st_release_sys((uint32_t*)(peers.p[q] + flags_off) + (size_t)slot * GP_AR_FLAG_WORDS + rank, e);
+    const uint32_t* mine = (const uint32_t*)(peers.p[rank] + flags_off) + (size_t)slot * GP_AR_FLAG_WORDS + q;
+    unsigned long long polls = 0;
+    while ((int)(gp_ld_acquire_sys(mine) - e) < 0) {
+      if (++polls > (1ull << 26)) __trap();     // a peer that never arrives: fail loudly (~half a minute)
+    }
+  }
+  __syncwarp();
+  if (threadIdx.x == 0) *my_epoch = e;
+}
+
+__global__ void __launch_bounds__(256) gp_add_inplace_kernel(float4* __restrict__ dst, const float4* __restrict__ src, size_t n4) {
+  for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n4; i += (size_t)gridDim.x * 256) {
+    float4 a = dst[i];
+    const float4 b = src[i];
+    a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+    dst[i] = a;
+  }
+}
+
+__global__ void __launch_bounds__(256) gp_max_inplace_kernel(int* __restrict__ dst, const int* __restrict__ src, size_t n) {
+  for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (size_t)gridDim.x * 256) dst[i] = max(dst[i], src[i]);
+}
+
+extern "C" int gp_peer_barrier_launch(int rank, int world, void* const* peer_bases, size_t flags_byte_offset, int slot,
+                                      gp_stream_t stream_) {
+  if (world < 1 || world > GP_AR_MAX_WORLD || rank < 0 || rank >= world || !peer_bases || slot < 0) return GP_ERR_BAD_ARG;
+  if (flags_byte_offset & 15) return GP_ERR_BAD_ARG;
+  GpPeers peers;
+  for (int q = 0; q < GP_AR_MAX_WORLD; q++) peers.p[q] = q < world ? (char*)peer_bases[q] : nullptr;
+  for (int q = 0; q < world; q++)
+    if (!peers.p[q]) return GP_ERR_BAD_ARG;
+  cudaStream_t stream = (cudaStream_t)stream_;
+  GP_KERNEL("gp_barrier_kernel", stream, gp_barrier_kernel<<<1, 32, 0, stream>>>(peers, rank, world, flags_byte_offset, slot));
+  GP_LAUNCH_CHECK();
+  return GP_OK;
+}
+
+extern "C" int gp_copy_async(void* dst, const void* src, size_t bytes, gp_stream_t stream_) {
+  if (bytes == 0) return GP_OK;
+  if (!dst || !src) return GP_ERR_BAD_ARG;
+  GP_CUDA_TRY(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToDevice, (cudaStream_t)stream_));
+  return GP_OK;
+}
+
+extern "C" int gp_add_inplace_f32(float* dst, const float* src, size_t n_floats, gp_stream_t stream_) {
+  if (n_floats == 0) return GP_OK;
+  if (!dst || !src || (n_floats & 3) || (((size_t)dst | (size_t)src) & 15)) return GP_ERR_BAD_ARG;
+  cudaStream_t stream = (cudaStream_t)stream_;
+  GP_KERNEL("gp_add_inplace_kernel", stream, gp_add_inplace_kernel<<<148 * 8, 256, 0, stream>>>((float4*)dst, (const float4*)src, n_floats / 4));
+  GP_LAUNCH_CHECK();
+  return GP_OK;
+}
+
+extern "C" int gp_max_inplace_s32(int* dst, const int* src, size_t n, gp_stream_t stream_) {
+  if (n == 0) return GP_OK;
+  if (!dst || !src) return GP_ERR_BAD_ARG;
+  cudaStream_t stream = (cudaStream_t)stream_;
+  GP_KERNEL("gp_max_inplace_kernel", stream, gp_max_inplace_kernel<<<148 * 4, 256, 0, stream>>>(dst, src, n));
+  GP_LAUNCH_CHECK();
+  return GP_OK;
+}
+
 extern "C" int gp_exchange_sync_words(void) { return 2 * GP_XS_MAX; }
 
 extern "C" int gp_stream_wait_word(const unsigned* word, unsigned value, gp_stream_t stream_) {

@@ -178,7 +178,7 @@ class NvlsFlatGradAllReduce(FlatGradAllReduce):
         from . import _lib
         assert dtype == torch.float32
         L = _lib.lib()
-        self._flag_bytes = int(L.gp_allreduce_flag_bytes(max(self.BLOCKS, 148)))
+        self._flag_bytes = int(L.gp_allreduce_flag_bytes(max(self.BLOCKS, 148) + 4))   # + the copy-engine path's own slots
         data_bytes = (n * 4 + 255) // 256 * 256
         self._aux_off = data_bytes
         data_bytes += (self._aux_n * 4 + 255) // 256 * 256
@@ -200,8 +200,43 @@ class NvlsFlatGradAllReduce(FlatGradAllReduce):
         if "GP_EXCHANGE_BLOCKS" not in os.environ:
             self.BLOCKS = 24 if self.multicast else 148
         self._side = torch.cuda.Stream(device=device)
+        # Two ranks: the copy engines move the bytes (``ce_pull``): the neighbour search of the next step runs at full
+        # speed next to a cudaMemcpyAsync, while it crawls next to the 148-CTA peer-load kernel (tools/ce_copy_probe.py)
+        self.copy_engine = self._world == 2 and os.environ.get("GP_EXCHANGE_CE", "1") != "0"
+        self._ce_streams, self._stage = None, None
+        self._ce_slot0 = max(self.BLOCKS, 148)       # flag slots of the copy-engine path (the kernels use the ones below)
         self.aux = self._symm[self._aux_off // 4:self._aux_off // 4 + self._aux_n].view(torch.int32) if self._aux_n else None
         return self._symm[:n]
+
+    def ce_pull(self, segment, lane):
+        """Two ranks.  Start pulling the peer's copy of ``segment`` (a slice of ``flat``, or "aux") into local staging
+        on copy stream ``lane`` (0 or 1): a flag barrier with the peer (its gradients are final), then one
+        cudaMemcpyAsync over NVLink -- no SM takes part.  Returns a handle whose ``wait()``, on the current stream,
+        joins the copy, meets the peer once more (it has finished reading THIS rank's range, which is about to change)
+        and adds the staged range in place (``gp_add_inplace_f32`` / ``gp_max_inplace_s32``).  a + b is commutative, so
+        both ranks end with the same bits.  Calls and waits must come in the same order on both ranks."""
+        from . import _lib
+        L = _lib.lib()
+        dev = self.flat.device
+        if self._ce_streams is None:
+            self._ce_streams = [torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)]
+            self._stage = torch.empty(self._flags_off // 4, dtype=torch.float32, device=dev)
+        if isinstance(segment, str):
+            off, nbytes, op = self._aux_off, self._aux_n * 4, 1
+        else:
+            off, nbytes, op = segment.data_ptr() - self._symm.data_ptr(), segment.numel() * 4, 0
+            assert off % 16 == 0 and nbytes % 16 == 0 and 0 <= off and off + nbytes <= self._aux_off
+        st = self._ce_streams[lane]
+        ready = torch.cuda.Event()
+        ready.record(torch.cuda.current_stream(dev))
+        st.wait_event(ready)
+        _lib.check(L.gp_peer_barrier_launch(self._rank, self._world, self._peers, self._flags_off, self._ce_slot0 + lane,
+                                            st.cuda_stream), "gp_peer_barrier_launch")
+        peer_base = int(self._peers[1 - self._rank])
+        _lib.check(L.gp_copy_async(self._stage.data_ptr() + off, peer_base + off, nbytes, st.cuda_stream), "gp_copy_async")
+        done = torch.cuda.Event()
+        done.record(st)
+        return _CeJoin(self, done, off, nbytes, op)
 
     def _launch(self, fn, what, byte_off, n):
         from . import _lib
@@ -271,6 +306,37 @@ class NvlsFlatGradAllReduce(FlatGradAllReduce):
         for w in works:
             w.wait()
         return None
+
+
+class _CeJoin:
+    """Second half of ``NvlsFlatGradAllReduce.ce_pull`` (runs on the stream that calls ``wait()``)."""
+
+    def __init__(self, red, done, off, nbytes, op):
+        self.red, self.done, self.off, self.nbytes, self.op = red, done, off, nbytes, op
+
+    def wait(self):
+        from . import _lib
+        L, r = _lib.lib(), self.red
+        cur = torch.cuda.current_stream(r.flat.device)
+        cur.wait_event(self.done)
+        _lib.check(L.gp_peer_barrier_launch(r._rank, r._world, r._peers, r._flags_off, r._ce_slot0 + 2, cur.cuda_stream),
+                   "gp_peer_barrier_launch")
+        dst, src = r._symm.data_ptr() + self.off, r._stage.data_ptr() + self.off
+        if self.op == 0:
+            _lib.check(L.gp_add_inplace_f32(dst, src, self.nbytes // 4, cur.cuda_stream), "gp_add_inplace_f32")
+        else:
+            _lib.check(L.gp_max_inplace_s32(dst, src, self.nbytes // 4, cur.cuda_stream), "gp_max_inplace_s32")
+
+
+class _Joins:
+    """Several handles joined in order."""
+
+    def __init__(self, handles):
+        self.handles = [h for h in handles if h is not None]
+
+    def wait(self):
+        for h in self.handles:
+            h.wait()
 
 
 class _StreamJoin:

@@ -523,30 +523,52 @@ class TrainStep:
                             works.append(exchange.all_reduce_bucket(b))
                 else:
                     sh = buckets[0]
-                    cut = int(sh.numel() * EARLY_FRACTION) // 4 * 4
                     stages[0].replay()
                     _mark("stage 0 done")
-                    if cut:
-                        works.append(exchange.all_reduce_bucket(sh[:cut]))
-                    stages[1].replay()
-                    _mark("stage 1 done")
-                    stages[2].replay()
-                    _mark("stage 2 done")
-                    if hasattr(exchange, "exchange_segments") and RESIDENT_EXCHANGE:
-                        # one resident kernel: it takes its CTAs now, while the GPU is between steps, and is not locked
-                        # out by the persistent blocks of the next step's neighbour search
-                        segs = [buckets[2], buckets[1]] + (["aux"] if self.exchange_radii else []) + \
-                            ([sh[cut:]] if cut < sh.numel() else [])
-                        hs = exchange.exchange_segments(segs)
-                        works.append(hs[0])
-                        self.deferred_blend = hs[2] if self.exchange_radii else hs[1]
-                        self.deferred_raster = hs[-1]
+                    if getattr(exchange, "copy_engine", False):
+                        # Two ranks: copy engines.  A copy costs the SMs nothing (the next step's neighbour search runs
+                        # at full speed next to it; next to the 148-CTA peer-load kernel it took 1.2 ms instead of
+                        # 0.45), so the SH range -- 2/3 of the bytes -- starts crossing the link as soon as it is final,
+                        # underneath the rest of this backward, and the other ranges follow on a second copy stream
+                        # when the last gradients are final.  Every range is added in place in front of its first
+                        # reader (parallel.NvlsFlatGradAllReduce.ce_pull).  What stays exposed is link time: 569 MB at
+                        # 730 GB/s do not fit under the 0.3 ms of backward + 0.55 ms of search and blend that precede
+                        # the SH range's first reader.  Measured at C5 (step of 4 samples per rank): 10.54 ms; all
+                        # ranges after the last stage, one after the other: 10.62; the small first range through the
+                        # peer-load kernel instead: 10.60; the resident peer-load kernel for everything: 10.69.
+                        from .parallel import _Joins
+                        h_sh = exchange.ce_pull(sh, 0)
+                        stages[1].replay()
+                        _mark("stage 1 done")
+                        stages[2].replay()
+                        _mark("stage 2 done")
+                        works.append(exchange.ce_pull(buckets[2], 1))
+                        h_aux = exchange.ce_pull("aux", 1) if self.exchange_radii else None
+                        self.deferred_blend = _Joins([h_aux, exchange.ce_pull(buckets[1], 1)])
+                        self.deferred_raster = h_sh
                     else:
-                        works.append(exchange.all_reduce_bucket(buckets[2]))
-                        if self.exchange_radii:   # MAX of the radii: in front of the per-Gaussian bucket, joined with it
-                            exchange.all_reduce_max_aux()
-                        self.deferred_blend = exchange.all_reduce_bucket(buckets[1])
-                        self.deferred_raster = exchange.all_reduce_bucket(sh[cut:]) if cut < sh.numel() else self.deferred_blend
+                        cut = int(sh.numel() * EARLY_FRACTION) // 4 * 4
+                        if cut:
+                            works.append(exchange.all_reduce_bucket(sh[:cut]))
+                        stages[1].replay()
+                        _mark("stage 1 done")
+                        stages[2].replay()
+                        _mark("stage 2 done")
+                        if hasattr(exchange, "exchange_segments") and RESIDENT_EXCHANGE:
+                            # one resident kernel: it takes its CTAs now, while the GPU is between steps, and is not
+                            # locked out by the persistent blocks of the next step's neighbour search
+                            segs = [buckets[2], buckets[1]] + (["aux"] if self.exchange_radii else []) + \
+                                ([sh[cut:]] if cut < sh.numel() else [])
+                            hs = exchange.exchange_segments(segs)
+                            works.append(hs[0])
+                            self.deferred_blend = hs[2] if self.exchange_radii else hs[1]
+                            self.deferred_raster = hs[-1]
+                        else:
+                            works.append(exchange.all_reduce_bucket(buckets[2]))
+                            if self.exchange_radii:   # MAX of the radii: in front of the per-Gaussian bucket, joined with it
+                                exchange.all_reduce_max_aux()
+                            self.deferred_blend = exchange.all_reduce_bucket(buckets[1])
+                            self.deferred_raster = exchange.all_reduce_bucket(sh[cut:]) if cut < sh.numel() else self.deferred_blend
                 for w in works:
                     if w is not None:
                         w.wait()

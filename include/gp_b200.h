@@ -366,6 +366,17 @@ int gp_exchange_segments(int rank, int world, void* multicast_base, void* const*
                          unsigned* sync_words, unsigned call_id, gp_stream_t stream);
 int gp_stream_wait_word(const unsigned* word, unsigned value, gp_stream_t stream);
 
+/* Two ranks: the pieces of an exchange whose bytes are moved by the copy engines instead of SMs.
+ * gp_peer_barrier_launch: a one-warp kernel on `stream` that meets the same call of every peer on flag slot `slot` of
+ * the symmetric allocation (slots are the per-CTA flag groups of gp_allreduce_flag_bytes; calls on one slot must come
+ * in the same order on every rank and never overlap in time).  gp_copy_async: cudaMemcpyAsync device-to-device (a
+ * peer's mapped buffer as source pulls it over NVLink).  gp_add_inplace_f32 / gp_max_inplace_s32: dst op= src. */
+int gp_peer_barrier_launch(int rank, int world, void* const* peer_bases, size_t flags_byte_offset, int slot,
+                           gp_stream_t stream);
+int gp_copy_async(void* dst, const void* src, size_t bytes, gp_stream_t stream);
+int gp_add_inplace_f32(float* dst, const float* src, size_t n_floats, gp_stream_t stream);
+int gp_max_inplace_s32(int* dst, const int* src, size_t n, gp_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
