@@ -336,6 +336,7 @@ extern "C" int gp_blend_forward(int N, int Kp, int K, const float* logits, const
   if (rc) return rc;
   if (N == 0) return GP_OK;
   if (!logits || (!idx32 && !idx64) || !xyz || !rot || !xyz_t || !q_t) return GP_ERR_BAD_ARG;
+  if ((((size_t)rot) | ((size_t)q_t)) & 15) return GP_ERR_BAD_ARG;   // quaternion rows move as 128-bit words
   if (Kp > 0 && (!kp_delta_xyz || !kp_delta_q)) return GP_ERR_BAD_ARG;
   if ((s_t && !scaling) || (o_t && !opacity)) return GP_ERR_BAD_ARG;
   const size_t smem = (size_t)Kp * 8 * 4;
@@ -363,6 +364,7 @@ static int blend_backward_impl(int N, int Kp, int K, const float* logits, const 
   GP_CUDA_TRY(cudaMemsetAsync(g_kp_delta_q, 0, (size_t)Kp * 4 * 4, stream));
   if (N == 0) return GP_OK;
   if (!logits || (!idx32 && !idx64) || !rot || !kp_delta_xyz || !kp_delta_q) return GP_ERR_BAD_ARG;
+  if ((((size_t)rot) | ((size_t)g_q_t) | ((size_t)g_rot)) & 15) return GP_ERR_BAD_ARG;   // 128-bit quaternion rows (NULL is fine)
   if ((g_scaling && g_s_t && !s_t) || (g_opacity && !o_t)) return GP_ERR_BAD_ARG;
   const size_t smem = (size_t)Kp * 17 * 4;
   const bool vec6 = K == 6 && idx32 && ((((size_t)logits) & 15) == 0) && ((((size_t)idx32) & 7) == 0) &&

@@ -613,6 +613,7 @@ extern "C" int gp_kpmlp_backward(const gp_mlp_cfg* cfg, const float* kp_xyz, con
   MlpPtrs p = {};
   for (int l = 0; l <= d.depth; l++) {
     if (!weights[l] || !dL_dweights[l] || !dL_dbiases[l]) return GP_ERR_BAD_ARG;
+    if (((size_t)dL_dweights[l]) & 15) return GP_ERR_BAD_ARG;   // the weight gradients are written with 128-bit stores
     p.W[l] = weights[l];
     p.gW[l] = dL_dweights[l];
     p.gb[l] = dL_dbiases[l];

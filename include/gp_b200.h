@@ -199,7 +199,8 @@ int gp_spatial_order(int N, const float* xyz, int* order /*[N]*/, void* ws, gp_s
 /* logits [N,2K] (translation weights then rotation weights, softmax-ed inside), idx (int32 or int64, [N,K]),
  * per-keypoint deltas [Kp,3] / [Kp,4], canonical xyz [N,3], raw rotation [N,4], log-scale [N,3], opacity
  * logit [N,1].  Outputs xyz_t [N,3], q_t [N,4] (normalised), s_t [N,3] = exp, o_t [N,1] = sigmoid (the last
- * two optional).  K <= 16, Kp <= 3200. */
+ * two optional).  K <= 16, Kp <= 3200.  rot, q_t (and g_q_t, g_rot in the backward) are moved as 128-bit rows: 16-byte
+ * aligned, GP_ERR_BAD_ARG otherwise. */
 int gp_blend_forward(int N, int Kp, int K, const float* logits, const int* idx32, const long long* idx64,
                      const float* kp_delta_xyz, const float* kp_delta_q, const float* xyz, const float* rot,
                      const float* scaling, const float* opacity, float* xyz_t, float* q_t, float* s_t, float* o_t,
