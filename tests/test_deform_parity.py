@@ -707,3 +707,25 @@ def test_blend_backward_adds_to_a_running_sum(gplib):
         assert float(g1[k].abs().sum()) > 0 and rel_err(sums[k], 1.5 * g1[k]) <= 1e-5, k
     for k in ("kp_dxyz", "kp_dq"):
         assert rel_err(g2[k], 0.5 * g1[k]) <= 1e-4, k
+
+
+def test_blend_entries_refuse_misaligned_quaternion_rows(gplib):
+    """rot / q_t / g_rot / g_q_t move as 128-bit rows: a base pointer off a 16-byte boundary is an error, not a fault."""
+    from gaussianprediction_b200 import _lib
+    from gaussianprediction_b200._lib import ptr
+    L = gplib
+    N, Kp, K = 64, 8, 6
+    dev = "cuda"
+    f = dict(dtype=torch.float32, device=dev)
+    logits, idx = torch.zeros(N, 2 * K, **f), torch.zeros(N, K, dtype=torch.int32, device=dev)
+    kpx, kpq = torch.zeros(Kp, 3, **f), torch.zeros(Kp, 4, **f)
+    xyz, sc, op = torch.zeros(N, 3, **f), torch.zeros(N, 3, **f), torch.zeros(N, 1, **f)
+    pool = torch.ones(4 * N + 4, **f)
+    rot_ok, rot_bad = pool[:4 * N].view(N, 4), pool[1:4 * N + 1].view(N, 4)          # the second starts 4 bytes in
+    outs = [torch.empty(N, 3, **f), torch.empty(N, 4, **f), torch.empty(N, 3, **f), torch.empty(N, 1, **f)]
+    s = _lib.stream_ptr()
+    call = lambda rot: L.gp_blend_forward(N, Kp, K, ptr(logits), ptr(idx), None, ptr(kpx), ptr(kpq), ptr(xyz), ptr(rot),
+                                          ptr(sc), ptr(op), ptr(outs[0]), ptr(outs[1]), ptr(outs[2]), ptr(outs[3]), s)
+    assert call(rot_ok) == 0
+    assert call(rot_bad) != 0
+    torch.cuda.synchronize()
