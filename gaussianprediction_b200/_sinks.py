@@ -30,11 +30,12 @@ def grad_sinks(pairs, accumulate=()):
     """``pairs`` / ``accumulate``: iterables of (parameter, destination tensor of the same shape, contiguous float32)."""
     global _SINKS, _ACC_SINKS
     old, old_acc = _SINKS, _ACC_SINKS
-    _SINKS, _ACC_SINKS = dict(old), dict(old_acc)
-    for table, items in ((_SINKS, pairs), (_ACC_SINKS, accumulate)):
+    new, new_acc = dict(old), dict(old_acc)
+    for table, items in ((new, pairs), (new_acc, accumulate)):
         for p, dst in items:
             assert dst.is_contiguous() and dst.shape == p.shape and dst.dtype == p.dtype
             table[_key(p)] = dst
+    _SINKS, _ACC_SINKS = new, new_acc          # installed only once every pair has been checked
     try:
         yield
     finally:

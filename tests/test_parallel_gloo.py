@@ -117,3 +117,26 @@ def test_flat_views_are_16_byte_aligned_for_any_gaussian_count():
     # views do not overlap
     ends = sorted(((v.data_ptr() - base) // 4, (v.data_ptr() - base) // 4 + v.numel()) for v in red.views)
     assert all(a[1] <= b[0] for a, b in zip(ends, ends[1:]))
+
+
+def test_accumulating_sinks_are_a_separate_nested_map():
+    """``grad_sinks(pairs, accumulate=...)``: plain and accumulating destinations are looked up separately (only kernels
+    that can add in place ask for the second kind), nested scopes extend the maps and restore them on exit."""
+    from gaussianprediction_b200._sinks import acc_sink_for, grad_sinks, sink_for
+    a, b, c = torch.zeros(8, 3), torch.zeros(5), torch.zeros(4, 4)
+    da, db, sb = torch.zeros(8, 3), torch.zeros(5), torch.zeros(5)
+    assert sink_for(a) is None and acc_sink_for(a) is None
+    with grad_sinks([(a, da), (b, db)], accumulate=[(b, sb)]):
+        assert sink_for(a) is da and sink_for(b) is db and sink_for(c) is None
+        assert acc_sink_for(b) is sb and acc_sink_for(a) is None
+        assert sink_for(a.view(-1)) is da                       # matched by storage, not by tensor identity
+        assert sink_for(torch.zeros(0)) is None and acc_sink_for(None) is None
+        dc = torch.zeros(4, 4)
+        with grad_sinks([], accumulate=[(c, dc)]):
+            assert acc_sink_for(c) is dc and acc_sink_for(b) is sb and sink_for(a) is da
+        assert acc_sink_for(c) is None
+        with pytest.raises(AssertionError):
+            with grad_sinks([], accumulate=[(a, torch.zeros(3, 8))]):   # shape mismatch is refused
+                pass
+        assert acc_sink_for(b) is sb                            # ... and leaves the maps as they were
+    assert sink_for(a) is None and acc_sink_for(b) is None
